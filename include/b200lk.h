@@ -1,0 +1,175 @@
+/*
+ * b200lk.h -- C ABI of the B200 tree-likelihood engine (drop-in boundary).
+ *
+ * The reference (IQ-TREE 2) has no FFI on this path: kernel variants are
+ * PhyloTree member-function templates bound to member-function pointers by
+ * PhyloTree::setLikelihoodKernel (tree/phylotreesse.cpp:91-199).  This header is
+ * what a `setLikelihoodKernelCUDA()` translation unit binds instead of the
+ * templates of tree/phylokernelnew.h.  Each entry point names the reference
+ * function it replaces.  INTEGRATION.md shows the adapter a maintainer adds.
+ *
+ * Conventions
+ *  - plain C types only; every call returns an int status (B200LK_OK == 0,
+ *    negative = hard error, positive = numerical-warning bit mask).  Nothing
+ *    throws and nothing calls exit() across this boundary.
+ *  - partial-likelihood vectors, scale counters, tip states, theta and the
+ *    per-pattern buffers live in HBM for the life of the context.  A *slot* is
+ *    one partial vector + its scale counters; the host addresses slots with
+ *    the same index it uses for its own storage:
+ *        slot = (PhyloNeighbor::partial_lh - central_partial_lh) / block_size
+ *    (tree/phylotree.cpp:1145-1163); the two NNI scratch vectors
+ *    (nni_partial_lh, tree/phylotree.cpp:1066-1070) are slots nslots-2, nslots-1
+ *    when the host reserves them.
+ *  - category index is mixture-major c = m*ncat + k, block = nstates*ncat_mix
+ *    (tree/phylokernelnew.h:1322-1331).
+ *  - a context is bound to one device and one stream; distinct contexts may be
+ *    driven from distinct host threads concurrently (PhyloSuperTree runs
+ *    partitions under OpenMP, tree/phylosupertree.cpp:716).
+ */
+#ifndef B200LK_H_
+#define B200LK_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200LK_OK 0
+#define B200LK_ERR_ARG (-1)      /* bad argument / dimension */
+#define B200LK_ERR_CUDA (-2)     /* CUDA runtime error, see b200lk_last_error */
+#define B200LK_ERR_STATE (-3)    /* call order violated (e.g. derv before theta) */
+#define B200LK_ERR_NOMEM (-4)
+#define B200LK_ERR_UNSUPPORTED (-5)
+/* numerical warnings (positive bit mask), mirroring the reference's outWarning /
+ * outError texts at tree/phylokernelnew.h:2573-2578, 3077-3094, 3333-3336 */
+#define B200LK_WARN_LNL_NONFINITE 1  /* "Numerical underflow for lh-branch" */
+#define B200LK_WARN_DERV_NONFINITE 2 /* "Numerical underflow (lh-derivative)" */
+
+#define B200LK_CHILD_LEAF 0
+#define B200LK_CHILD_INTERNAL 1
+
+typedef struct b200lk_ctx b200lk_ctx;
+
+/* Problem dimensions; fixed for the life of a context
+ * (what PhyloTree::initializeAllPartialLh sizes its buffers from,
+ * tree/phylotree.cpp:890-934, 1054-1110). */
+typedef struct b200lk_dims {
+    int32_t ntaxa;          /* leafNum */
+    int32_t nstates;        /* aln->num_states */
+    int32_t ncat;           /* site_rate->getNRate() */
+    int32_t nmix;           /* model->getNMixtures() */
+    int32_t fused_mix_rate; /* model_factory->fused_mix_rate (0/1) */
+    int32_t safe_numeric;   /* 0 = NORM_LH (scale per pattern), 1 = SAFE_LH (per pattern and category) */
+    int32_t n_state_codes;  /* aln->STATE_UNKNOWN + 1 */
+    int32_t nslots;         /* number of partial-vector slots (max_lh_slots [+2 NNI]) */
+    int64_t nptn;           /* aln->size(): observed site patterns */
+    int64_t n_unobserved;   /* model_factory->unobserved_ptns.size() (+ASC), 0 otherwise */
+    int32_t device;         /* CUDA device ordinal */
+    int32_t reserved;
+} b200lk_dims;
+
+/* One directed branch of a traversal (TraversalInfo, tree/phylotree.h:320-331):
+ * the partial vector at `out_slot` is computed from children
+ * [child_begin, child_begin + nchild) of the child array. */
+typedef struct b200lk_node {
+    int32_t out_slot;
+    int32_t child_begin;
+    int32_t nchild; /* 2 for a bifurcating node, >2 multifurcating */
+    int32_t reserved;
+} b200lk_node;
+
+typedef struct b200lk_child {
+    int32_t kind; /* B200LK_CHILD_LEAF: id = taxon (alignment row); B200LK_CHILD_INTERNAL: id = slot */
+    int32_t id;
+    double length; /* branch length to the child (child->length) */
+} b200lk_child;
+
+/* One end of the branch an lnL / theta is taken at.  kind LEAF: id = taxon;
+ * INTERNAL: id = slot holding the partial that points toward that end. */
+typedef struct b200lk_end {
+    int32_t kind;
+    int32_t id;
+} b200lk_end;
+
+/* ---- life cycle ------------------------------------------------------- */
+int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims);
+int b200lk_destroy(b200lk_ctx *ctx);
+const char *b200lk_last_error(const b200lk_ctx *ctx);
+const char *b200lk_version(void);
+
+/* Optional: run on a caller-owned stream (e.g. the stream NCCL is enqueued on).
+ * `stream` is a cudaStream_t passed as void*; NULL restores the context's own. */
+int b200lk_set_stream(b200lk_ctx *ctx, void *stream);
+
+/* ---- inputs (one-time / per model change) ----------------------------- */
+/* Tip data + pattern weights.  states: [ntaxa][nptn] uint8 state codes
+ * (aln->at(ptn)[taxon], tree/phylotree.cpp:3242-3247); unobserved: [ntaxa][n_unobserved]
+ * or NULL; ptn_freq: [nptn] (computePtnFreq, tree/phylotreesse.cpp:537-547). */
+int b200lk_upload_tips(b200lk_ctx *ctx, const uint8_t *states, const uint8_t *unobserved,
+                       const double *ptn_freq);
+/* ptn_invar[nptn + n_unobserved] (computePtnInvar, tree/phylotreesse.cpp:549-612). */
+int b200lk_set_ptn_invar(b200lk_ctx *ctx, const double *ptn_invar);
+/* Eigen-system and rate model: what the kernels read through
+ * model->getEigenvalues()/getEigenvectors()/getInverseEigenvectors()
+ * (model/modelmarkov.cpp:1904-1916), site_rate->getRate/getProp, getMixtureWeight and
+ * tip_partial_lh (computeTipPartialLikelihood, tree/phylotreesse.cpp:243-375).
+ * eval[nmix*n], evec[nmix*n*n] (row = state), inv_evec[nmix*n*n] (row = eigen index),
+ * rates[ncat], props[ncat], mixw[nmix], tip_partial_lh[n_state_codes*nmix*n]. */
+int b200lk_set_model(b200lk_ctx *ctx, const double *eval, const double *evec, const double *inv_evec,
+                     const double *rates, const double *props, const double *mixw,
+                     const double *tip_partial_lh);
+
+/* ---- the four kernel entry points -------------------------------------- */
+/* computePartialLikelihood over a whole traversal list
+ * (computeTraversalInfo + computePartialInfo + computePartialLikelihood*SIMD,
+ * tree/phylokernelnew.h:900-1110, 1150-1281, 1291-2039).  `nodes` is in post-order
+ * (children before parents); independent nodes are batched into one launch. */
+int b200lk_update_partials(b200lk_ctx *ctx, const b200lk_node *nodes, int32_t nnodes,
+                           const b200lk_child *children, int32_t nchildren);
+
+/* computeLikelihoodBranch*SIMD (tree/phylokernelnew.h:2643-3185) on branch (dad, node) of
+ * length `length`: writes _pattern_lh / _pattern_lh_cat on the device, returns lnL.
+ * `dad` may be a leaf (tip-internal case); `node` must be INTERNAL. */
+int b200lk_branch_lnl(b200lk_ctx *ctx, b200lk_end dad, b200lk_end node, double length, double *lnl);
+
+/* computeLikelihoodBuffer*SIMD (tree/phylokernelnew.h:2050-2231): theta_all and buffer_scale_all. */
+int b200lk_build_theta(b200lk_ctx *ctx, b200lk_end dad, b200lk_end node);
+
+/* computeLikelihoodDerv*SIMD (tree/phylokernelnew.h:2235-2633) from theta_all. */
+int b200lk_derv(b200lk_ctx *ctx, double length, double *df, double *ddf);
+
+/* computeLikelihoodFromBuffer*SIMD (tree/phylokernelnew.h:3196-3392) from theta_all. */
+int b200lk_lnl_from_buffer(b200lk_ctx *ctx, double length, double *lnl);
+
+/* One round trip for a whole evaluation: update_partials + branch_lnl + build_theta + derv
+ * (what computeLikelihood followed by the first computeFuncDerv of optimizeOneBranch costs,
+ * tree/phylotree.cpp:1227-1268, 2520-2527).  Any of lnl/df/ddf may be NULL. */
+int b200lk_evaluate(b200lk_ctx *ctx, const b200lk_node *nodes, int32_t nnodes,
+                    const b200lk_child *children, int32_t nchildren, b200lk_end dad, b200lk_end node,
+                    double length, double *lnl, double *df, double *ddf);
+
+/* ---- device-resident results on demand --------------------------------- */
+/* Unreduced per-shard sums for multi-GPU runs: out[0] = lnL (if requested), out[1] = df,
+ * out[2] = ddf are left in a device buffer; this returns its device pointer (3 doubles)
+ * so the caller can all-reduce it in place (NCCL) on the context's stream. */
+int b200lk_result_device_ptr(b200lk_ctx *ctx, void **dptr);
+
+/* Host readers of device data (tree/phylotree.cpp:1252-1259, 1463-1581). */
+int b200lk_fetch_pattern_lh(b200lk_ctx *ctx, double *pattern_lh /* [nptn] */);
+int b200lk_fetch_pattern_lh_cat(b200lk_ctx *ctx, double *pattern_lh_cat /* [nptn][ncat_mix] */);
+int b200lk_fetch_scale_num(b200lk_ctx *ctx, int32_t slot, uint8_t *scale /* [nptn] or [nptn][ncat_mix] */);
+int b200lk_fetch_partial(b200lk_ctx *ctx, int32_t slot, double *partial /* [nptn][ncat_mix][nstates] */);
+int b200lk_fetch_theta(b200lk_ctx *ctx, double *theta /* [nptn][ncat_mix][nstates] */,
+                       double *buffer_scale_all /* [nptn] or NULL */);
+
+/* Counters for the metric: pattern-node updates and kernel launches since create/reset. */
+int b200lk_get_counters(b200lk_ctx *ctx, int64_t *pattern_node_updates, int64_t *kernel_launches);
+int b200lk_reset_counters(b200lk_ctx *ctx);
+int b200lk_synchronize(b200lk_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200LK_H_ */

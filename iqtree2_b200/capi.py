@@ -1,0 +1,232 @@
+"""ctypes binding of the C ABI in include/b200lk.h.
+
+The same binding class drives any library that exports the ABI under a symbol
+prefix: the product (``libb200lk.so``, prefix ``b200lk_``) and -- from tests
+only -- the CPU oracle (prefix ``orc_``).  There is no fallback: loading the
+product library fails loudly when it has not been built or cannot be loaded.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libb200lk.so")
+
+LEAF, INTERNAL = 0, 1
+WARN_LNL_NONFINITE, WARN_DERV_NONFINITE = 1, 2
+
+
+class Dims(C.Structure):
+    _fields_ = [("ntaxa", C.c_int32), ("nstates", C.c_int32), ("ncat", C.c_int32), ("nmix", C.c_int32),
+                ("fused_mix_rate", C.c_int32), ("safe_numeric", C.c_int32), ("n_state_codes", C.c_int32),
+                ("nslots", C.c_int32), ("nptn", C.c_int64), ("n_unobserved", C.c_int64),
+                ("device", C.c_int32), ("reserved", C.c_int32)]
+
+
+class Node(C.Structure):
+    _fields_ = [("out_slot", C.c_int32), ("child_begin", C.c_int32), ("nchild", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
+class Child(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("id", C.c_int32), ("length", C.c_double)]
+
+
+class End(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("id", C.c_int32)]
+
+
+class B200LKError(RuntimeError):
+    pass
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _u8p(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint8))
+
+
+def pack_traversal(entries):
+    """entries: [(node, dad, out_slot, [(kind, id, length), ...]), ...] (workload.traversal)
+    -> (Node array, nnodes, Child array, nchildren)."""
+    nch = sum(len(e[3]) for e in entries)
+    nodes = (Node * max(1, len(entries)))()
+    kids = (Child * max(1, nch))()
+    j = 0
+    for i, e in enumerate(entries):
+        nodes[i] = Node(e[2], j, len(e[3]), 0)
+        for kind, cid, ln in e[3]:
+            kids[j] = Child(kind, cid, ln)
+            j += 1
+    return nodes, len(entries), kids, nch
+
+
+class Engine:
+    """One likelihood context.  Methods mirror include/b200lk.h one to one."""
+
+    def __init__(self, *, ntaxa, nstates, ncat, nmix=1, nptn, nslots, n_state_codes, safe_numeric=False,
+                 fused_mix_rate=False, n_unobserved=0, device=0, lib_path=LIB_PATH, prefix="b200lk_"):
+        if not os.path.exists(lib_path):
+            raise B200LKError(
+                "%s is missing: build it first (python -c 'import __graft_entry__ as g; g.build()'). "
+                "There is no CPU fallback on this path." % lib_path)
+        self.lib = C.CDLL(lib_path)
+        self.prefix = prefix
+        self.dims = Dims(ntaxa, nstates, ncat, nmix, int(fused_mix_rate), int(safe_numeric), n_state_codes,
+                         nslots, nptn, n_unobserved, device, 0)
+        self.ncat_mix = ncat if fused_mix_rate else ncat * nmix
+        self.block = nstates * self.ncat_mix
+        self.ctx = C.c_void_p()
+        self._check(self._f("create")(C.byref(self.ctx), C.byref(self.dims)))
+        self._keep = []
+
+    # -- plumbing ------------------------------------------------------------
+    def _f(self, name):
+        return getattr(self.lib, self.prefix + name)
+
+    def _check(self, rc):
+        if rc < 0:
+            msg = ""
+            if self.prefix == "b200lk_" and self.ctx:
+                self.lib.b200lk_last_error.restype = C.c_char_p
+                msg = (self.lib.b200lk_last_error(self.ctx) or b"").decode()
+            raise B200LKError("%s call failed with status %d %s" % (self.prefix, rc, msg))
+        return rc
+
+    def close(self):
+        if self.ctx:
+            self._f("destroy")(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- inputs --------------------------------------------------------------
+    def upload_tips(self, states, ptn_freq, unobserved=None):
+        states = np.ascontiguousarray(states, dtype=np.uint8)
+        ptn_freq = np.ascontiguousarray(ptn_freq, dtype=np.float64)
+        assert states.shape == (self.dims.ntaxa, self.dims.nptn)
+        un = None
+        if unobserved is not None:
+            unobserved = np.ascontiguousarray(unobserved, dtype=np.uint8)
+            un = _u8p(unobserved)
+        self._check(self._f("upload_tips")(self.ctx, _u8p(states), un, _dp(ptn_freq)))
+
+    def set_ptn_invar(self, ptn_invar):
+        a = np.ascontiguousarray(ptn_invar, dtype=np.float64)
+        assert a.size == self.dims.nptn + self.dims.n_unobserved
+        self._check(self._f("set_ptn_invar")(self.ctx, _dp(a)))
+
+    def set_model(self, eval_, evec, inv_evec, rates, props, mixw, tip_partial_lh):
+        arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in
+                (eval_, evec, inv_evec, rates, props, mixw, tip_partial_lh)]
+        n, nmix = self.dims.nstates, self.dims.nmix
+        assert arrs[0].size == nmix * n and arrs[1].size == nmix * n * n and arrs[2].size == nmix * n * n
+        assert arrs[3].size == self.dims.ncat and arrs[4].size == self.dims.ncat and arrs[5].size == nmix
+        assert arrs[6].size == self.dims.n_state_codes * nmix * n
+        self._check(self._f("set_model")(self.ctx, *[_dp(a) for a in arrs]))
+
+    # -- kernels -------------------------------------------------------------
+    def update_partials(self, entries):
+        nodes, nn, kids, nk = pack_traversal(entries)
+        return self._check(self._f("update_partials")(self.ctx, nodes, nn, kids, nk))
+
+    def branch_lnl(self, dad, node, length):
+        out = C.c_double()
+        f = self._f("branch_lnl")
+        f.argtypes = [C.c_void_p, End, End, C.c_double, C.POINTER(C.c_double)]
+        self.last_status = self._check(f(self.ctx, End(*dad), End(*node), length, C.byref(out)))
+        return out.value
+
+    def build_theta(self, dad, node):
+        f = self._f("build_theta")
+        f.argtypes = [C.c_void_p, End, End]
+        return self._check(f(self.ctx, End(*dad), End(*node)))
+
+    def derv(self, length):
+        df, ddf = C.c_double(), C.c_double()
+        f = self._f("derv")
+        f.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        self.last_status = self._check(f(self.ctx, length, C.byref(df), C.byref(ddf)))
+        return df.value, ddf.value
+
+    def lnl_from_buffer(self, length):
+        out = C.c_double()
+        f = self._f("lnl_from_buffer")
+        f.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_double)]
+        self.last_status = self._check(f(self.ctx, length, C.byref(out)))
+        return out.value
+
+    def evaluate(self, entries, dad, node, length, want_lnl=True, want_derv=True):
+        nodes, nn, kids, nk = pack_traversal(entries)
+        lnl, df, ddf = C.c_double(), C.c_double(), C.c_double()
+        f = self._f("evaluate")
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, End, End, C.c_double,
+                      C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        self.last_status = self._check(
+            f(self.ctx, nodes, nn, kids, nk, End(*dad), End(*node), length,
+              C.byref(lnl) if want_lnl else None, C.byref(df) if want_derv else None,
+              C.byref(ddf) if want_derv else None))
+        return lnl.value, df.value, ddf.value
+
+    # -- readers -------------------------------------------------------------
+    def fetch_pattern_lh(self):
+        out = np.empty(self.dims.nptn)
+        self._check(self._f("fetch_pattern_lh")(self.ctx, _dp(out)))
+        return out
+
+    def fetch_pattern_lh_cat(self):
+        out = np.empty((self.dims.nptn, self.ncat_mix))
+        self._check(self._f("fetch_pattern_lh_cat")(self.ctx, _dp(out)))
+        return out
+
+    def fetch_scale_num(self, slot):
+        shape = (self.dims.nptn, self.ncat_mix) if self.dims.safe_numeric else (self.dims.nptn,)
+        out = np.empty(shape, dtype=np.uint8)
+        self._check(self._f("fetch_scale_num")(self.ctx, C.c_int32(slot), _u8p(out)))
+        return out
+
+    def fetch_partial(self, slot):
+        out = np.empty((self.dims.nptn, self.ncat_mix, self.dims.nstates))
+        self._check(self._f("fetch_partial")(self.ctx, C.c_int32(slot), _dp(out)))
+        return out
+
+    def fetch_theta(self):
+        th = np.empty((self.dims.nptn, self.ncat_mix, self.dims.nstates))
+        bs = np.empty(self.dims.nptn)
+        self._check(self._f("fetch_theta")(self.ctx, _dp(th), _dp(bs)))
+        return th, bs
+
+    def counters(self):
+        a, b = C.c_int64(), C.c_int64()
+        self._check(self._f("get_counters")(self.ctx, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def synchronize(self):
+        if self.prefix == "b200lk_":
+            self._check(self.lib.b200lk_synchronize(self.ctx))
+
+
+def engine_for(aln, model, rates, props, *, nslots, p_invar=0.0, safe_numeric=False, device=0,
+               lib_path=LIB_PATH, prefix="b200lk_"):
+    """Create a context for a workload.Alignment + workload.EigenModel and load
+    tips, pattern weights and the model (the one-time uploads of
+    initializeAllPartialLh / computeTipPartialLikelihood)."""
+    from . import workload as W
+    eng = Engine(ntaxa=aln.ntaxa, nstates=aln.nstates, ncat=len(rates), nmix=model.nmix, nptn=aln.nptn,
+                 nslots=nslots, n_state_codes=aln.state_unknown + 1, safe_numeric=safe_numeric,
+                 device=device, lib_path=lib_path, prefix=prefix)
+    eng.upload_tips(aln.states, aln.ptn_freq)
+    eng.set_ptn_invar(W.ptn_invar(aln, model, p_invar))
+    scale = 1.0 - p_invar
+    eng.set_model(model.eval, model.evec, model.inv_evec, np.asarray(rates) , np.asarray(props) * scale,
+                  model.mixw, W.tip_partial_lh(model))
+    return eng
