@@ -1,0 +1,266 @@
+// api.cu -- the four kernel entry points of include/b200lk.h.
+//
+// b200lk_update_partials turns the host's post-order TraversalInfo list into
+//   (1) one tables launch (P-factor tables for every child, on device),
+//   (2) one update launch per LEVEL: nodes whose internal children are all at lower levels are
+//       independent and share a launch (grid.y = nodes of the level).
+// Only the node/child descriptors (16 + 32 bytes each, incl. branch lengths) cross PCIe.
+#include <algorithm>
+
+#include "common.cuh"
+
+static int check_ready(b200lk_ctx *c) {
+    if (!c) return B200LK_ERR_ARG;
+    if (!c->model_set || !c->tips_set) {
+        snprintf(c->err, sizeof(c->err), "upload_tips and set_model must precede kernel calls");
+        return B200LK_ERR_STATE;
+    }
+    return B200LK_OK;
+}
+
+static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
+                          int32_t nchildren) {
+    if (nnodes == 0) return B200LK_OK;
+    if (!nodes || !children || nnodes < 0 || nchildren < 0) return B200LK_ERR_ARG;
+    if (nnodes > c->nodes_cap || nchildren > c->children_cap) {
+        snprintf(c->err, sizeof(c->err), "traversal too long: %d nodes / %d children (cap %d / %d)", nnodes,
+                 nchildren, c->nodes_cap, c->children_cap);
+        return B200LK_ERR_ARG;
+    }
+    const int n = c->d.nstates, block = c->block, nslots = c->d.nslots;
+    // level of each node = 1 + max level of the children produced earlier in this same list
+    // (slots may be recycled inside one list in memory-saving mode: a write also waits for earlier
+    // readers and writers of the same slot, so batching never reorders a hazard)
+    std::vector<int> level_of_slot(nslots, -1), reader_level(nslots, -1), level(nnodes, 0);
+    int nlevels = 0;
+    for (int i = 0; i < nnodes; i++) {
+        const b200lk_node &nd = nodes[i];
+        if (nd.out_slot < 0 || nd.out_slot >= nslots || nd.nchild < 2 || nd.child_begin < 0 ||
+            nd.child_begin + nd.nchild > nchildren) {
+            snprintf(c->err, sizeof(c->err), "bad traversal entry %d", i);
+            return B200LK_ERR_ARG;
+        }
+        int lv = 0;
+        for (int k = 0; k < nd.nchild; k++) {
+            const b200lk_child &ch = children[nd.child_begin + k];
+            if (ch.kind == B200LK_CHILD_LEAF) {
+                if (ch.id < 0 || ch.id >= c->d.ntaxa) return B200LK_ERR_ARG;
+            } else {
+                if (ch.id < 0 || ch.id >= nslots || ch.id == nd.out_slot) return B200LK_ERR_ARG;
+                lv = std::max(lv, level_of_slot[ch.id] + 1);
+            }
+        }
+        lv = std::max(lv, std::max(reader_level[nd.out_slot], level_of_slot[nd.out_slot]) + 1);
+        for (int k = 0; k < nd.nchild; k++) {
+            const b200lk_child &ch = children[nd.child_begin + k];
+            if (ch.kind != B200LK_CHILD_LEAF) reader_level[ch.id] = std::max(reader_level[ch.id], lv);
+        }
+        level[i] = lv;
+        level_of_slot[nd.out_slot] = lv;
+        nlevels = std::max(nlevels, lv + 1);
+    }
+    // children: table offsets; the reference puts a leaf child first ("left") when exactly one child
+    // of a bifurcating node is a leaf (tree/phylokernelnew.h:1395-1405)
+    size_t off = 0;
+    for (int j = 0; j < nchildren; j++) {
+        DevChild &dc = c->h_children[j];
+        dc.kind = children[j].kind;
+        dc.id = children[j].id;
+        dc.length = children[j].length;
+        dc.echild_off = (int64_t)off;
+        off += (size_t)block * n;
+        if (dc.kind == B200LK_CHILD_LEAF) {
+            dc.leaf_off = (int64_t)off;
+            off += (size_t)c->d.n_state_codes * block;
+        } else {
+            dc.leaf_off = -1;
+        }
+    }
+    if (off > c->tables_cap) return B200LK_ERR_NOMEM;
+    // level-sorted node array, bifurcating before multifurcating inside a level
+    std::vector<std::vector<int>> levels(nlevels);
+    int pos = 0;
+    for (int lv = 0; lv < nlevels; lv++) {
+        for (int pass = 0; pass < 2; pass++)
+            for (int i = 0; i < nnodes; i++) {
+                if (level[i] != lv || (nodes[i].nchild > 2) != (pass == 1)) continue;
+                DevNode &dn = c->h_nodes[pos];
+                dn.out_slot = nodes[i].out_slot;
+                dn.child_begin = nodes[i].child_begin;
+                dn.nchild = nodes[i].nchild;
+                if (dn.nchild > 2) {
+                    dn.kind = 3;
+                } else {
+                    DevChild &a = c->h_children[dn.child_begin], &b = c->h_children[dn.child_begin + 1];
+                    if (a.kind != B200LK_CHILD_LEAF && b.kind == B200LK_CHILD_LEAF) std::swap(a, b);
+                    dn.kind = (a.kind == B200LK_CHILD_LEAF) ? (b.kind == B200LK_CHILD_LEAF ? 0 : 1) : 2;
+                }
+                levels[lv].push_back(pos);
+                pos++;
+            }
+    }
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_children, c->h_children, sizeof(DevChild) * nchildren, cudaMemcpyHostToDevice,
+                                c->stream));
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_nodes, c->h_nodes, sizeof(DevNode) * nnodes, cudaMemcpyHostToDevice, c->stream));
+    int rc = launch_tables(c, nchildren);
+    if (rc) return rc;
+    rc = launch_partials(c, levels);
+    if (rc) return rc;
+    c->n_updates += (int64_t)nnodes * c->ntot;
+    c->theta_computed = false;
+    return B200LK_OK;
+}
+
+static int check_ends(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
+    if (node.kind != B200LK_CHILD_INTERNAL || node.id < 0 || node.id >= c->d.nslots) return B200LK_ERR_ARG;
+    if (dad.kind == B200LK_CHILD_LEAF) return (dad.id >= 0 && dad.id < c->d.ntaxa) ? B200LK_OK : B200LK_ERR_ARG;
+    if (dad.kind != B200LK_CHILD_INTERNAL || dad.id < 0 || dad.id >= c->d.nslots || dad.id == node.id)
+        return B200LK_ERR_ARG;
+    return B200LK_OK;
+}
+
+// copy `count` result doubles to the pinned host buffer and wait: the only D2H of an evaluation
+static int read_results(b200lk_ctx *c, int first, int count) {
+    CUDA_TRY(c, cudaMemcpyAsync(c->h_result + first, c->d_result + first, sizeof(double) * count,
+                                cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return B200LK_OK;
+}
+
+static int finish_lnl(b200lk_ctx *c, double *lnl) {
+    int rc = read_results(c, 0, 1);
+    if (rc) return rc;
+    int warn = 0;
+    if (!isfinite(c->h_result[0])) {  // tree/phylokernelnew.h:3077-3094
+        warn = B200LK_WARN_LNL_NONFINITE;
+        rc = launch_repair(c);
+        if (rc) return rc;
+        rc = read_results(c, 0, 1);
+        if (rc) return rc;
+    }
+    *lnl = c->h_result[0];
+    return warn;
+}
+
+static int finish_derv(b200lk_ctx *c, double *df, double *ddf) {
+    int rc = read_results(c, 1, 2);
+    if (rc) return rc;
+    double a = c->h_result[1], b = c->h_result[2];
+    int warn = 0;
+    if (!isfinite(a)) {  // tree/phylokernelnew.h:2573-2578, 2629-2632
+        warn = B200LK_WARN_DERV_NONFINITE;
+        if (c->d.safe_numeric) a = b = 0.0;
+    }
+    if (df) *df = a;
+    if (ddf) *ddf = b;
+    return warn;
+}
+
+extern "C" int b200lk_update_partials(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes,
+                                      const b200lk_child *children, int32_t nchildren) {
+    int rc = check_ready(c);
+    if (rc) return rc;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    rc = enqueue_update(c, nodes, nnodes, children, nchildren);
+    if (rc) return rc;
+    // the pinned staging buffers are reused by the next call
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length, double *lnl) {
+    int rc = check_ready(c);
+    if (rc) return rc;
+    if (!lnl || check_ends(c, dad, node)) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->d.nptn == 0) { *lnl = 0.0; return B200LK_OK; }
+    rc = launch_branch_lnl(c, dad, node, length);
+    if (rc) return rc;
+    return finish_lnl(c, lnl);
+}
+
+extern "C" int b200lk_build_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
+    int rc = check_ready(c);
+    if (rc) return rc;
+    if (check_ends(c, dad, node)) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->ntot > 0) {
+        rc = launch_theta(c, dad, node);
+        if (rc) return rc;
+    }
+    c->theta_computed = true;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_derv(b200lk_ctx *c, double length, double *df, double *ddf) {
+    int rc = check_ready(c);
+    if (rc) return rc;
+    if (!c->theta_computed) return B200LK_ERR_STATE;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->d.nptn == 0) { if (df) *df = 0; if (ddf) *ddf = 0; return B200LK_OK; }
+    rc = launch_derv(c, length);
+    if (rc) return rc;
+    return finish_derv(c, df, ddf);
+}
+
+extern "C" int b200lk_lnl_from_buffer(b200lk_ctx *c, double length, double *lnl) {
+    int rc = check_ready(c);
+    if (rc) return rc;
+    if (!lnl) return B200LK_ERR_ARG;
+    if (!c->theta_computed) return B200LK_ERR_STATE;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->d.nptn == 0) { *lnl = 0.0; return B200LK_OK; }
+    rc = launch_from_buffer(c, length);
+    if (rc) return rc;
+    return finish_lnl(c, lnl);
+}
+
+extern "C" int b200lk_evaluate(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
+                               int32_t nchildren, b200lk_end dad, b200lk_end node, double length, double *lnl,
+                               double *df, double *ddf) {
+    int rc = check_ready(c);
+    if (rc) return rc;
+    if (check_ends(c, dad, node)) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    rc = enqueue_update(c, nodes, nnodes, children, nchildren);
+    if (rc) return rc;
+    const bool want_derv = df || ddf;
+    if (c->d.nptn == 0) {
+        if (lnl) *lnl = 0; if (df) *df = 0; if (ddf) *ddf = 0;
+        return B200LK_OK;
+    }
+    if (lnl) {
+        rc = launch_branch_lnl(c, dad, node, length);
+        if (rc) return rc;
+    }
+    if (want_derv) {
+        rc = launch_theta(c, dad, node);
+        if (rc) return rc;
+        c->theta_computed = true;
+        rc = launch_derv(c, length);
+        if (rc) return rc;
+    }
+    // one synchronising read for everything
+    int warn = 0;
+    rc = read_results(c, 0, 3);
+    if (rc) return rc;
+    if (lnl) {
+        if (!isfinite(c->h_result[0])) {
+            rc = finish_lnl(c, lnl);
+            if (rc < 0) return rc;
+            warn |= rc;
+        } else {
+            *lnl = c->h_result[0];
+        }
+    }
+    if (want_derv) {
+        double a = c->h_result[1], b = c->h_result[2];
+        if (!isfinite(a)) {
+            warn |= B200LK_WARN_DERV_NONFINITE;
+            if (c->d.safe_numeric) a = b = 0.0;
+        }
+        if (df) *df = a;
+        if (ddf) *ddf = b;
+    }
+    return warn;
+}

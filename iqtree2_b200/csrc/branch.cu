@@ -1,0 +1,402 @@
+// branch.cu -- branch-level steps of the likelihood path, all HBM-bound streams:
+//   theta build       computeLikelihoodBuffer*SIMD     tree/phylokernelnew.h:2050-2231
+//   lnL at a branch   computeLikelihoodBranch*SIMD     tree/phylokernelnew.h:2643-3185
+//   df, ddf           computeLikelihoodDerv*SIMD       tree/phylokernelnew.h:2235-2633
+//   lnL from theta    computeLikelihoodFromBuffer*SIMD tree/phylokernelnew.h:3196-3392
+//
+// A group of G lanes (power of two <= 32) owns one pattern and strides over its flat
+// [block] vector so that consecutive lanes read consecutive doubles; per-pattern sums
+// finish with warp shuffles.  Sums over patterns are deterministic: fixed grid, fixed
+// per-thread order, shuffle tree, then a fixed-order pass over the per-CTA partials.
+#include "common.cuh"
+
+#define RED_THREADS 256
+
+struct BranchArgs {
+    const double *pdad;    // dad_branch->partial_lh  (subtree on the node side)
+    const double *pnode;   // node_branch->partial_lh (subtree on the dad side), null if dad is a leaf
+    const uint8_t *sdad, *snode;
+    const uint8_t *dad_states;  // tip states of the leaf dad
+    const double *tip_partial_lh, *val, *tip_val;
+    const double *ptn_freq, *ptn_invar;
+    double *theta, *buffer_scale_all, *pattern_lh, *pattern_lh_cat;
+    double *red_partial;
+    int64_t nptn, ntot;
+    int n, ncm, block, denom, nmix, G, safe;
+};
+
+// val0[c][i] = exp(eval*rate*len)*prop*mixw, val1 = cof*val0, val2 = cof*val1 (:2342-2357);
+// tip_val[s][c][i] = val0[c][i] * tip_partial_lh[s][m][i] (:2757-2785)
+__global__ void val_kernel(DevModel m, double len, double *val, double *tip_val, int n, int ncat, int ncm,
+                           int denom, int nmix, int codes, int want_tip) {
+    const int block = n * ncm;
+    for (int idx = threadIdx.x; idx < block; idx += blockDim.x) {
+        int c = idx / n, i = idx - c * n, mm = c / denom, k = c % ncat;
+        double prop = m.props[k] * m.mixw[mm];
+        double cof = m.eval[mm * n + i] * m.rates[k];
+        double v = exp(cof * len) * prop;
+        double v1 = cof * v;
+        val[idx] = v;
+        val[block + idx] = v1;
+        val[2 * block + idx] = cof * v1;
+    }
+    if (!want_tip) return;
+    __syncthreads();
+    const int tip_block = n * nmix;
+    for (int idx = threadIdx.x; idx < codes * block; idx += blockDim.x) {
+        int s = idx / block, r = idx - s * block, c = r / n, i = r - c * n;
+        tip_val[idx] = val[r] * m.tip_partial_lh[(size_t)s * tip_block + (c / denom) * n + i];
+    }
+}
+
+template <int K>
+__device__ __forceinline__ void block_reduce_store(double (&acc)[K], double *red_partial, int red_blocks) {
+    __shared__ double sh[K][RED_THREADS / 32];
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        double v = acc[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) sh[k][threadIdx.x >> 5] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < K) {
+        double v = 0.0;
+        for (int w = 0; w < RED_THREADS / 32; w++) v += sh[threadIdx.x][w];
+        red_partial[(size_t)threadIdx.x * red_blocks + blockIdx.x] = v;
+    }
+}
+
+// fixed-order final pass: result[k] = sum_b red_partial[k][b]
+__global__ void final_reduce_kernel(const double *red_partial, int red_blocks, int K, double *result, int dst0) {
+    __shared__ double sh[RED_THREADS];
+    for (int k = 0; k < K; k++) {
+        double v = 0.0;
+        for (int b = threadIdx.x; b < red_blocks; b += RED_THREADS) v += red_partial[(size_t)k * red_blocks + b];
+        sh[threadIdx.x] = v;
+        __syncthreads();
+        for (int s = RED_THREADS / 2; s > 0; s >>= 1) {
+            if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) result[dst0 + k] = sh[0];
+        __syncthreads();
+    }
+}
+
+__device__ __forceinline__ double group_sum(double v, int G) {
+    for (int o = G >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ int group_min(int v, int G) {
+    for (int o = G >> 1; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// ---- theta ---------------------------------------------------------------
+// theta[p][c][i] = partial_dad * partial_node (or * tip_partial_lh[state][m][i] when dad is a leaf);
+// buffer_scale_all[p] = LOG_SCALING_THRESHOLD * (NORM: summed scale; SAFE: min over categories, with
+// categories scaled once more multiplied by 2^-256 and those scaled more set to 0) (:2142-2175, 2190-2228)
+__global__ void __launch_bounds__(RED_THREADS) theta_kernel(BranchArgs a) {
+    const int G = a.G, g = threadIdx.x & (G - 1);
+    const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
+    const int n = a.n, ncm = a.ncm, block = a.block;
+    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.ntot; pb += groups_per_grid) {
+        int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
+        const bool valid = p < a.ntot;
+        if (!valid) p = a.ntot - 1;
+        const double *pd = a.pdad + (size_t)p * block;
+        double *th = a.theta + (size_t)p * block;
+        int min_scale = 0;
+        if (a.safe) {
+            int ms = 0x7fffffff;
+            for (int c = g; c < ncm; c += G) {
+                int s = a.sdad[p * ncm + c] + (a.pnode ? a.snode[p * ncm + c] : 0);
+                ms = min(ms, s & 0xff);
+            }
+            min_scale = group_min(ms, G);
+        } else {
+            min_scale = a.sdad[p] + (a.pnode ? a.snode[p] : 0);
+        }
+        const double *other;
+        int tip_mode = a.pnode == nullptr;
+        if (tip_mode) other = a.tip_partial_lh + (size_t)a.dad_states[p] * (n * a.nmix);
+        else other = a.pnode + (size_t)p * block;
+        for (int j = g; j < block; j += G) {
+            int c = j / n;
+            double o = tip_mode ? other[(c / a.denom) * n + (j - c * n)] : other[j];
+            double t = o * pd[j];
+            if (a.safe) {
+                int s = (a.sdad[p * ncm + c] + (a.pnode ? a.snode[p * ncm + c] : 0)) & 0xff;
+                if (s == min_scale + 1) t *= B200_SCALING_THRESHOLD;
+                else if (s > min_scale + 1) t = 0.0;
+            }
+            if (valid) th[j] = t;
+        }
+        if (g == 0 && valid) a.buffer_scale_all[p] = (double)min_scale * B200_LOG_SCALING_THRESHOLD;
+    }
+}
+
+// ---- df, ddf -------------------------------------------------------------
+__global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red_blocks) {
+    const int G = a.G, g = threadIdx.x & (G - 1);
+    const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
+    const int block = a.block;
+    const double *v0 = a.val, *v1 = a.val + block, *v2 = a.val + 2 * block;
+    double acc[2] = {0.0, 0.0};
+    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.nptn; pb += groups_per_grid) {
+        int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
+        const bool valid = p < a.nptn;
+        if (!valid) p = a.nptn - 1;
+        const double *th = a.theta + (size_t)p * block;
+        double lh = 0.0, df = 0.0, ddf = 0.0;
+        for (int j = g; j < block; j += G) {
+            double t = th[j];
+            lh = fma(v0[j], t, lh);
+            df = fma(v1[j], t, df);
+            ddf = fma(v2[j], t, ddf);
+        }
+        lh = group_sum(lh, G);
+        df = group_sum(df, G);
+        ddf = group_sum(ddf, G);
+        if (g == 0 && valid) {
+            lh = fabs(lh) + a.ptn_invar[p];  // :2494
+            double inv = 1.0 / lh;           // :2497-2505
+            double df_frac = df * inv, ddf_frac = ddf * inv, freq = a.ptn_freq[p];
+            double tmp1 = df_frac * freq, tmp2 = ddf_frac * freq;
+            acc[0] += tmp1;
+            acc[1] += fma(-tmp1, df_frac, tmp2);
+        }
+    }
+    block_reduce_store<2>(acc, a.red_partial, red_blocks);
+}
+
+// ---- lnL from theta --------------------------------------------------------
+__global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(BranchArgs a, int red_blocks) {
+    const int G = a.G, g = threadIdx.x & (G - 1);
+    const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
+    const int block = a.block;
+    double acc[1] = {0.0};
+    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.nptn; pb += groups_per_grid) {
+        int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
+        const bool valid = p < a.nptn;
+        if (!valid) p = a.nptn - 1;
+        const double *th = a.theta + (size_t)p * block;
+        double lh = 0.0;
+        for (int j = g; j < block; j += G) lh = fma(a.val[j], th[j], lh);
+        lh = group_sum(lh, G);
+        if (g == 0 && valid) {
+            lh = fabs(lh) + a.ptn_invar[p];               // :3295
+            lh = log(fabs(lh)) + a.buffer_scale_all[p];   // :3300
+            a.pattern_lh[p] = lh;
+            acc[0] = fma(lh, a.ptn_freq[p], acc[0]);
+        }
+    }
+    block_reduce_store<1>(acc, a.red_partial, red_blocks);
+}
+
+// ---- lnL at a branch -------------------------------------------------------
+// lane g of a group owns categories g, g+G, ...; lh_cat[c] = sum_i val[c][i]*node[c][i]*dad[c][i]
+// (or tip_val[state][c][i]*dad[c][i] when dad is a leaf).
+__global__ void __launch_bounds__(RED_THREADS) lnl_kernel(BranchArgs a, int red_blocks) {
+    const int G = a.G, g = threadIdx.x & (G - 1);
+    const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
+    const int n = a.n, ncm = a.ncm, block = a.block;
+    const bool tip_mode = a.pnode == nullptr;
+    double acc[1] = {0.0};
+    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.nptn; pb += groups_per_grid) {
+        int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
+        const bool valid = p < a.nptn;
+        if (!valid) p = a.nptn - 1;
+        const double *pd = a.pdad + (size_t)p * block;
+        const double *w = tip_mode ? a.tip_val + (size_t)a.dad_states[p] * block : a.val;
+        const double *pn = tip_mode ? nullptr : a.pnode + (size_t)p * block;
+        double lh = 0.0;
+        int min_scale;
+        if (a.safe) {
+            int ms = 0x7fffffff;
+            for (int c = g; c < ncm; c += G) {
+                int s = (a.sdad[p * ncm + c] + (tip_mode ? 0 : a.snode[p * ncm + c])) & 0xff;
+                ms = min(ms, s);
+            }
+            min_scale = group_min(ms, G);
+        } else {
+            min_scale = a.sdad[p] + (tip_mode ? 0 : a.snode[p]);
+        }
+        for (int c = g; c < ncm; c += G) {
+            double s0 = 0.0, s1 = 0.0;
+            const double *wd = w + c * n, *d = pd + c * n;
+            if (tip_mode) {
+                for (int i = 0; i + 1 < n; i += 2) {
+                    s0 = fma(wd[i], d[i], s0);
+                    s1 = fma(wd[i + 1], d[i + 1], s1);
+                }
+                if (n & 1) s0 = fma(wd[n - 1], d[n - 1], s0);
+            } else {
+                const double *nd = pn + c * n;
+                for (int i = 0; i + 1 < n; i += 2) {
+                    s0 = fma(wd[i] * nd[i], d[i], s0);
+                    s1 = fma(wd[i + 1] * nd[i + 1], d[i + 1], s1);
+                }
+                if (n & 1) s0 = fma(wd[n - 1] * nd[n - 1], d[n - 1], s0);
+            }
+            double lc = s0 + s1;
+            if (a.safe) {  // :2886-2893, 3018-3025
+                int s = (a.sdad[p * ncm + c] + (tip_mode ? 0 : a.snode[p * ncm + c])) & 0xff;
+                if (s == min_scale + 1) lc *= B200_SCALING_THRESHOLD;
+                else if (s > min_scale + 1) lc = 0.0;
+            }
+            if (valid) a.pattern_lh_cat[(size_t)p * ncm + c] = lc;
+            lh += lc;
+        }
+        lh = group_sum(lh, G);
+        if (g == 0 && valid) {
+            lh = fabs(lh) + a.ptn_invar[p];                                        // :2907, 3038
+            lh = log(lh) + (double)min_scale * B200_LOG_SCALING_THRESHOLD;        // :2909, 3041
+            a.pattern_lh[p] = lh;
+            acc[0] = fma(lh, a.ptn_freq[p], acc[0]);
+        }
+    }
+    block_reduce_store<1>(acc, a.red_partial, red_blocks);
+}
+
+// repair pass for non-finite per-pattern lnL (:3085-3094, 3338-3347)
+__global__ void __launch_bounds__(RED_THREADS) repair_kernel(double *pattern_lh, const double *ptn_freq, int64_t nptn,
+                                                            double *red_partial, int red_blocks) {
+    double acc[1] = {0.0};
+    for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < nptn; p += (int64_t)gridDim.x * RED_THREADS) {
+        double v = pattern_lh[p];
+        if (!isfinite(v)) {
+            v = B200_LOG_SCALING_THRESHOLD * 4;
+            pattern_lh[p] = v;
+        }
+        acc[0] += v * ptn_freq[p];
+    }
+    block_reduce_store<1>(acc, red_partial, red_blocks);
+}
+
+// ---- host-side launchers -----------------------------------------------------
+static int pick_group(int count) {  // largest power of two <= min(32, count)
+    int G = 1;
+    while (G * 2 <= count && G * 2 <= 32) G *= 2;
+    return G;
+}
+
+static void fill_args(b200lk_ctx *c, BranchArgs &a, b200lk_end dad, b200lk_end node) {
+    memset(&a, 0, sizeof(a));
+    a.pdad = slot_partial(c, node.id);
+    a.sdad = slot_scale(c, node.id);
+    if (dad.kind == B200LK_CHILD_LEAF) {
+        a.dad_states = c->states + (size_t)dad.id * c->ntot_pad;
+    } else {
+        a.pnode = slot_partial(c, dad.id);
+        a.snode = slot_scale(c, dad.id);
+    }
+}
+
+static void fill_common(b200lk_ctx *c, BranchArgs &a) {
+    a.tip_partial_lh = c->m.tip_partial_lh;
+    a.val = c->val;
+    a.tip_val = c->tip_val;
+    a.ptn_freq = c->ptn_freq;
+    a.ptn_invar = c->ptn_invar;
+    a.theta = c->theta_all;
+    a.buffer_scale_all = c->buffer_scale_all;
+    a.pattern_lh = c->pattern_lh;
+    a.pattern_lh_cat = c->pattern_lh_cat;
+    a.red_partial = c->red_partial;
+    a.nptn = c->d.nptn;
+    a.ntot = c->ntot;
+    a.n = c->d.nstates;
+    a.ncm = c->ncat_mix;
+    a.block = c->block;
+    a.denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
+    a.nmix = c->d.nmix;
+    a.safe = c->d.safe_numeric;
+}
+
+static int grid_for(const b200lk_ctx *c, int G, int64_t npat) {
+    int64_t per_block = RED_THREADS / G;
+    int64_t need = (npat + per_block - 1) / per_block;
+    if (need < 1) need = 1;
+    return (int)(need < c->red_blocks ? need : c->red_blocks);
+}
+
+static int launch_val(b200lk_ctx *c, double length, int want_tip) {
+    const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
+    val_kernel<<<1, 256, 0, c->stream>>>(c->m, length, c->val, c->tip_val, c->d.nstates, c->d.ncat, c->ncat_mix,
+                                         denom, c->d.nmix, c->d.n_state_codes, want_tip);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches++;
+    return B200LK_OK;
+}
+
+int launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length) {
+    int rc = launch_val(c, length, dad.kind == B200LK_CHILD_LEAF);
+    if (rc) return rc;
+    BranchArgs a;
+    fill_args(c, a, dad, node);
+    fill_common(c, a);
+    a.G = pick_group(c->ncat_mix);
+    int grid = grid_for(c, a.G, c->d.nptn);
+    lnl_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, grid);
+    CUDA_TRY(c, cudaGetLastError());
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 1, c->d_result, 0);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches += 2;
+    return B200LK_OK;
+}
+
+int launch_repair(b200lk_ctx *c) {
+    int grid = grid_for(c, 1, c->d.nptn);
+    repair_kernel<<<grid, RED_THREADS, 0, c->stream>>>(c->pattern_lh, c->ptn_freq, c->d.nptn, c->red_partial, grid);
+    CUDA_TRY(c, cudaGetLastError());
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 1, c->d_result, 0);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches += 2;
+    return B200LK_OK;
+}
+
+int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
+    BranchArgs a;
+    fill_args(c, a, dad, node);
+    fill_common(c, a);
+    a.G = pick_group(c->block);
+    int grid = grid_for(c, a.G, c->ntot);
+    theta_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches++;
+    return B200LK_OK;
+}
+
+int launch_derv(b200lk_ctx *c, double length) {
+    int rc = launch_val(c, length, 0);
+    if (rc) return rc;
+    BranchArgs a;
+    memset(&a, 0, sizeof(a));
+    fill_common(c, a);
+    a.G = pick_group(c->block);
+    int grid = grid_for(c, a.G, c->d.nptn);
+    derv_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, grid);
+    CUDA_TRY(c, cudaGetLastError());
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 2, c->d_result, 1);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches += 2;
+    return B200LK_OK;
+}
+
+int launch_from_buffer(b200lk_ctx *c, double length) {
+    int rc = launch_val(c, length, 0);
+    if (rc) return rc;
+    BranchArgs a;
+    memset(&a, 0, sizeof(a));
+    fill_common(c, a);
+    a.G = pick_group(c->block);
+    int grid = grid_for(c, a.G, c->d.nptn);
+    frombuf_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, grid);
+    CUDA_TRY(c, cudaGetLastError());
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 1, c->d_result, 0);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches += 2;
+    return B200LK_OK;
+}

@@ -1,0 +1,97 @@
+// common.cuh -- context layout and helpers shared by the CUDA translation units.
+//
+// HBM layout (all private to the engine; the host sees only the C ABI):
+//   states      uint8  [ntaxa][ntot_pad]             tip state codes, taxon-major (coalesced per taxon)
+//   ptn_freq    double [ntot_pad]   ptn_invar double [ntot_pad]
+//   partial     double [nslots][ntot][block]         element (p,c,x) at p*block + c*nstates + x
+//   scale       uint8  [nslots][ntot] (NORM) | [nslots][ntot][ncat_mix] (SAFE)
+//   theta_all   double [ntot][block]   buffer_scale_all double [ntot]
+//   pattern_lh  double [ntot]          pattern_lh_cat double [ntot][ncat_mix]
+//   tables      per child of the current traversal: echild[ncat_mix][n][n] (+ leaf[codes][ncat_mix][n])
+// ntot = nptn + n_unobserved (+ASC patterns appended after the observed ones,
+// tree/phylokernelnew.h:1314-1316 with VectorClass::size() == 1).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "../../include/b200lk.h"
+
+#define B200_SCALING_THRESHOLD 8.636168555094444625386e-78  // 2^-256, tree/phylotree.h:77
+#define B200_LOG_SCALING_THRESHOLD (-177.4456782233459932741)  // tree/phylotree.h:80
+#define B200_TWO_256 1.157920892373161954235709850086879e77    // 2^256: ldexp(x,256) as an exact multiply
+
+struct DevModel {
+    double *eval, *evec, *inv_evec, *rates, *props, *mixw, *tip_partial_lh;
+};
+
+// One child of one traversal entry, device view.
+struct DevChild {
+    int32_t kind;        // B200LK_CHILD_LEAF / INTERNAL
+    int32_t id;          // taxon or slot
+    double length;
+    int64_t echild_off;  // offset (doubles) into tables
+    int64_t leaf_off;    // offset (doubles) into tables, -1 if internal
+};
+
+struct DevNode {
+    int32_t out_slot, child_begin, nchild, kind;  // kind: 0 TT, 1 TI, 2 II, 3 multifurcating
+};
+
+struct b200lk_ctx {
+    b200lk_dims d;
+    int ncat_mix, block, scale_per_ptn;
+    int64_t ntot, ntot_pad;
+    int device;
+    cudaStream_t stream, own_stream;
+    char err[512];
+
+    uint8_t *states;
+    double *ptn_freq, *ptn_invar;
+    double *partial;   // arena
+    uint8_t *scale;    // arena
+    size_t slot_doubles, slot_scale_bytes;
+    DevModel m;
+    double *theta_all, *buffer_scale_all, *pattern_lh, *pattern_lh_cat;
+    double *val;        // [3][block] branch coefficient tables
+    double *tip_val;    // [codes][block] val * tip_partial_lh (tip-internal branch lnL)
+    double *tables;     // per-traversal P-factor tables
+    size_t tables_cap;  // doubles
+    DevNode *d_nodes;
+    DevChild *d_children;
+    int nodes_cap, children_cap;
+    DevNode *h_nodes;      // pinned staging
+    DevChild *h_children;  // pinned staging
+    double *red_partial;   // [3][red_blocks] block partial sums
+    int red_blocks;
+    double *d_result;      // [4] lnL, df, ddf, prob_const
+    double *h_result;      // pinned
+    bool model_set, tips_set, theta_computed;
+    int theta_dad_kind;
+    int64_t n_updates, n_launches;
+};
+
+#define CUDA_TRY(ctx, expr)                                                                      \
+    do {                                                                                         \
+        cudaError_t e__ = (expr);                                                                \
+        if (e__ != cudaSuccess) {                                                                \
+            snprintf((ctx)->err, sizeof((ctx)->err), "%s:%d %s: %s", __FILE__, __LINE__, #expr,  \
+                     cudaGetErrorString(e__));                                                   \
+            return B200LK_ERR_CUDA;                                                              \
+        }                                                                                        \
+    } while (0)
+
+static inline double *slot_partial(const b200lk_ctx *c, int s) { return c->partial + (size_t)s * c->slot_doubles; }
+static inline uint8_t *slot_scale(const b200lk_ctx *c, int s) { return c->scale + (size_t)s * c->slot_scale_bytes; }
+
+// launchers implemented in tables.cu / partial.cu / branch.cu
+int launch_tables(b200lk_ctx *c, int nchildren);
+int launch_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels);
+int launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length);
+int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node);
+int launch_derv(b200lk_ctx *c, double length);
+int launch_from_buffer(b200lk_ctx *c, double length);
+int launch_repair(b200lk_ctx *c);

@@ -1,0 +1,228 @@
+// context.cu -- device residency: creation, one-time uploads, host readers.
+// Replaces the allocation side of PhyloTree::initializeAllPartialLh
+// (tree/phylotree.cpp:890-934, 1054-1182): one arena of nslots partial vectors and
+// scale counters, theta_all, buffer_scale_all, _pattern_lh, _pattern_lh_cat, ptn_freq,
+// ptn_invar and the tip-state matrix all stay in HBM for the life of the context.
+#include "common.cuh"
+
+extern "C" const char *b200lk_version(void) { return "b200lk 0.1 (sm_100a)"; }
+
+extern "C" const char *b200lk_last_error(const b200lk_ctx *c) { return c ? c->err : "null context"; }
+
+static int alloc_all(b200lk_ctx *c) {
+    const b200lk_dims &d = c->d;
+    const int n = d.nstates, nmix = d.nmix;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    CUDA_TRY(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    c->stream = c->own_stream;
+    CUDA_TRY(c, cudaMalloc(&c->states, (size_t)d.ntaxa * c->ntot_pad));
+    CUDA_TRY(c, cudaMemset(c->states, d.n_state_codes - 1, (size_t)d.ntaxa * c->ntot_pad));
+    CUDA_TRY(c, cudaMalloc(&c->ptn_freq, sizeof(double) * c->ntot_pad));
+    CUDA_TRY(c, cudaMalloc(&c->ptn_invar, sizeof(double) * c->ntot_pad));
+    CUDA_TRY(c, cudaMemset(c->ptn_freq, 0, sizeof(double) * c->ntot_pad));
+    CUDA_TRY(c, cudaMemset(c->ptn_invar, 0, sizeof(double) * c->ntot_pad));
+    c->slot_doubles = (size_t)c->ntot * c->block;
+    c->slot_scale_bytes = (((size_t)c->ntot * c->scale_per_ptn) + 15) & ~(size_t)15;
+    // keep every slot 16-byte aligned for vector loads
+    if (c->slot_doubles & 1) c->slot_doubles++;
+    if (d.nslots > 0) {
+        cudaError_t e = cudaMalloc(&c->partial, sizeof(double) * c->slot_doubles * d.nslots);
+        if (e != cudaSuccess) {
+            snprintf(c->err, sizeof(c->err), "cannot allocate %zu bytes for %d partial-likelihood slots: %s",
+                     sizeof(double) * c->slot_doubles * d.nslots, d.nslots, cudaGetErrorString(e));
+            cudaGetLastError();
+            return B200LK_ERR_NOMEM;
+        }
+        CUDA_TRY(c, cudaMalloc(&c->scale, c->slot_scale_bytes * d.nslots));
+        CUDA_TRY(c, cudaMemset(c->scale, 0, c->slot_scale_bytes * d.nslots));
+    }
+    CUDA_TRY(c, cudaMalloc(&c->m.eval, sizeof(double) * nmix * n));
+    CUDA_TRY(c, cudaMalloc(&c->m.evec, sizeof(double) * nmix * n * n));
+    CUDA_TRY(c, cudaMalloc(&c->m.inv_evec, sizeof(double) * nmix * n * n));
+    CUDA_TRY(c, cudaMalloc(&c->m.rates, sizeof(double) * d.ncat));
+    CUDA_TRY(c, cudaMalloc(&c->m.props, sizeof(double) * d.ncat));
+    CUDA_TRY(c, cudaMalloc(&c->m.mixw, sizeof(double) * nmix));
+    CUDA_TRY(c, cudaMalloc(&c->m.tip_partial_lh, sizeof(double) * d.n_state_codes * nmix * n));
+    CUDA_TRY(c, cudaMalloc(&c->theta_all, sizeof(double) * (c->slot_doubles + 2)));
+    CUDA_TRY(c, cudaMalloc(&c->buffer_scale_all, sizeof(double) * c->ntot_pad));
+    CUDA_TRY(c, cudaMalloc(&c->pattern_lh, sizeof(double) * c->ntot_pad));
+    CUDA_TRY(c, cudaMalloc(&c->pattern_lh_cat, sizeof(double) * c->ntot_pad * c->ncat_mix));
+    CUDA_TRY(c, cudaMalloc(&c->val, sizeof(double) * 3 * c->block));
+    CUDA_TRY(c, cudaMalloc(&c->tip_val, sizeof(double) * d.n_state_codes * c->block));
+    // tables for a full traversal: at most 2*(ntaxa-2)+ntaxa children
+    size_t per_child = (size_t)c->block * n + (size_t)d.n_state_codes * c->block;
+    c->children_cap = 3 * d.ntaxa + 8;
+    c->nodes_cap = 2 * d.ntaxa + 8;
+    c->tables_cap = per_child * c->children_cap;
+    CUDA_TRY(c, cudaMalloc(&c->tables, sizeof(double) * c->tables_cap));
+    CUDA_TRY(c, cudaMalloc(&c->d_nodes, sizeof(DevNode) * c->nodes_cap));
+    CUDA_TRY(c, cudaMalloc(&c->d_children, sizeof(DevChild) * c->children_cap));
+    CUDA_TRY(c, cudaMallocHost(&c->h_nodes, sizeof(DevNode) * c->nodes_cap));
+    CUDA_TRY(c, cudaMallocHost(&c->h_children, sizeof(DevChild) * c->children_cap));
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    c->red_blocks = sms * 8;
+    CUDA_TRY(c, cudaMalloc(&c->red_partial, sizeof(double) * 8 * c->red_blocks));
+    CUDA_TRY(c, cudaMalloc(&c->d_result, sizeof(double) * 8));
+    CUDA_TRY(c, cudaMemset(c->d_result, 0, sizeof(double) * 8));
+    CUDA_TRY(c, cudaMallocHost(&c->h_result, sizeof(double) * 8));
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
+    if (!out || !dims) return B200LK_ERR_ARG;
+    *out = nullptr;
+    if (dims->ntaxa < 2 || dims->nstates < 1 || dims->nstates > 64 || dims->ncat < 1 || dims->nmix < 1 ||
+        dims->nptn < 0 || dims->nslots < 0 || dims->n_state_codes < dims->nstates + 1 ||
+        dims->n_state_codes > 256 || dims->n_unobserved < 0)
+        return B200LK_ERR_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || dims->device < 0 || dims->device >= ndev) {
+        cudaGetLastError();
+        return B200LK_ERR_CUDA;  // no CPU fallback on this path
+    }
+    b200lk_ctx *c = new b200lk_ctx();
+    memset(c, 0, sizeof(*c));
+    c->d = *dims;
+    c->device = dims->device;
+    c->ncat_mix = dims->fused_mix_rate ? dims->ncat : dims->ncat * dims->nmix;  // tree/phylokernelnew.h:1323
+    c->block = dims->nstates * c->ncat_mix;
+    c->scale_per_ptn = dims->safe_numeric ? c->ncat_mix : 1;
+    c->ntot = dims->nptn + dims->n_unobserved;
+    c->ntot_pad = ((c->ntot + 127) / 128) * 128;
+    if (c->ntot_pad == 0) c->ntot_pad = 128;
+    int rc = alloc_all(c);
+    if (rc != B200LK_OK) {
+        // keep the context alive long enough for the caller to read the message? no: report and free
+        fprintf(stderr, "b200lk_create: %s\n", c->err);
+        b200lk_destroy(c);
+        return rc;
+    }
+    *out = c;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_destroy(b200lk_ctx *c) {
+    if (!c) return B200LK_OK;
+    cudaSetDevice(c->device);
+    if (c->own_stream) cudaStreamSynchronize(c->own_stream);
+    void *dev[] = {c->states, c->ptn_freq, c->ptn_invar, c->partial, c->scale, c->m.eval, c->m.evec,
+                   c->m.inv_evec, c->m.rates, c->m.props, c->m.mixw, c->m.tip_partial_lh, c->theta_all,
+                   c->buffer_scale_all, c->pattern_lh, c->pattern_lh_cat, c->val, c->tip_val, c->tables,
+                   c->d_nodes, c->d_children, c->red_partial, c->d_result};
+    for (void *p : dev)
+        if (p) cudaFree(p);
+    if (c->h_nodes) cudaFreeHost(c->h_nodes);
+    if (c->h_children) cudaFreeHost(c->h_children);
+    if (c->h_result) cudaFreeHost(c->h_result);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_set_stream(b200lk_ctx *c, void *stream) {
+    if (!c) return B200LK_ERR_ARG;
+    c->stream = stream ? (cudaStream_t)stream : c->own_stream;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_synchronize(b200lk_ctx *c) {
+    if (!c) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_upload_tips(b200lk_ctx *c, const uint8_t *states, const uint8_t *unobserved,
+                                  const double *ptn_freq) {
+    if (!c || (!states && c->d.nptn) || !ptn_freq || (c->d.n_unobserved && !unobserved)) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    const int64_t nptn = c->d.nptn, nun = c->d.n_unobserved;
+    if (nptn)
+        CUDA_TRY(c, cudaMemcpy2DAsync(c->states, c->ntot_pad, states, nptn, nptn, c->d.ntaxa,
+                                      cudaMemcpyHostToDevice, c->stream));
+    if (nun)
+        CUDA_TRY(c, cudaMemcpy2DAsync(c->states + nptn, c->ntot_pad, unobserved, nun, nun, c->d.ntaxa,
+                                      cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaMemcpyAsync(c->ptn_freq, ptn_freq, sizeof(double) * nptn, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    c->tips_set = true;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_set_ptn_invar(b200lk_ctx *c, const double *ptn_invar) {
+    if (!c || !ptn_invar) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    CUDA_TRY(c, cudaMemcpyAsync(c->ptn_invar, ptn_invar, sizeof(double) * c->ntot, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    c->theta_computed = false;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_set_model(b200lk_ctx *c, const double *eval, const double *evec, const double *inv_evec,
+                                const double *rates, const double *props, const double *mixw,
+                                const double *tip_partial_lh) {
+    if (!c || !eval || !evec || !inv_evec || !rates || !props || !mixw || !tip_partial_lh) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    const int n = c->d.nstates, nmix = c->d.nmix;
+    cudaStream_t s = c->stream;
+    CUDA_TRY(c, cudaMemcpyAsync(c->m.eval, eval, sizeof(double) * nmix * n, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaMemcpyAsync(c->m.evec, evec, sizeof(double) * nmix * n * n, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaMemcpyAsync(c->m.inv_evec, inv_evec, sizeof(double) * nmix * n * n, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaMemcpyAsync(c->m.rates, rates, sizeof(double) * c->d.ncat, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaMemcpyAsync(c->m.props, props, sizeof(double) * c->d.ncat, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaMemcpyAsync(c->m.mixw, mixw, sizeof(double) * nmix, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaMemcpyAsync(c->m.tip_partial_lh, tip_partial_lh, sizeof(double) * c->d.n_state_codes * nmix * n,
+                                cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaStreamSynchronize(s));  // the host arrays may be reused by the caller
+    c->model_set = true;
+    c->theta_computed = false;
+    return B200LK_OK;
+}
+
+// ---- host readers (lazy D2H of device-resident results) --------------------
+static int d2h(b200lk_ctx *c, void *dst, const void *src, size_t bytes) {
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    CUDA_TRY(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_fetch_pattern_lh(b200lk_ctx *c, double *out) {
+    if (!c || !out) return B200LK_ERR_ARG;
+    return d2h(c, out, c->pattern_lh, sizeof(double) * c->d.nptn);
+}
+extern "C" int b200lk_fetch_pattern_lh_cat(b200lk_ctx *c, double *out) {
+    if (!c || !out) return B200LK_ERR_ARG;
+    return d2h(c, out, c->pattern_lh_cat, sizeof(double) * c->d.nptn * c->ncat_mix);
+}
+extern "C" int b200lk_fetch_scale_num(b200lk_ctx *c, int32_t slot, uint8_t *out) {
+    if (!c || !out || slot < 0 || slot >= c->d.nslots) return B200LK_ERR_ARG;
+    return d2h(c, out, slot_scale(c, slot), (size_t)c->d.nptn * c->scale_per_ptn);
+}
+extern "C" int b200lk_fetch_partial(b200lk_ctx *c, int32_t slot, double *out) {
+    if (!c || !out || slot < 0 || slot >= c->d.nslots) return B200LK_ERR_ARG;
+    return d2h(c, out, slot_partial(c, slot), sizeof(double) * c->d.nptn * c->block);
+}
+extern "C" int b200lk_fetch_theta(b200lk_ctx *c, double *theta, double *bscale) {
+    if (!c || !theta) return B200LK_ERR_ARG;
+    int rc = d2h(c, theta, c->theta_all, sizeof(double) * c->d.nptn * c->block);
+    if (rc == B200LK_OK && bscale) rc = d2h(c, bscale, c->buffer_scale_all, sizeof(double) * c->d.nptn);
+    return rc;
+}
+extern "C" int b200lk_get_counters(b200lk_ctx *c, int64_t *updates, int64_t *launches) {
+    if (!c) return B200LK_ERR_ARG;
+    if (updates) *updates = c->n_updates;
+    if (launches) *launches = c->n_launches;
+    return B200LK_OK;
+}
+extern "C" int b200lk_reset_counters(b200lk_ctx *c) {
+    if (!c) return B200LK_ERR_ARG;
+    c->n_updates = c->n_launches = 0;
+    return B200LK_OK;
+}
+extern "C" int b200lk_result_device_ptr(b200lk_ctx *c, void **dptr) {
+    if (!c || !dptr) return B200LK_ERR_ARG;
+    *dptr = c->d_result;
+    return B200LK_OK;
+}

@@ -1,0 +1,51 @@
+// tables.cu -- P-factor tables on device (replaces PhyloTree::computePartialInfo,
+// tree/phylokernelnew.h:900-1110, reversible branch :1008-1109).
+//
+//   echild[c][x][i] = evec[m][x][i] * exp(eval[m][i] * rate[c % ncat] * len)        (:1016-1031)
+//   leaf[s][c][x]   = sum_i echild[c][x][i] * tip_partial_lh[s][m][i], row s = UNKNOWN := 1   (:1036-1056)
+//
+// One CTA per child of the traversal; only branch lengths travel host -> device.
+#include "common.cuh"
+
+__global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict__ children, DevModel m,
+                                                      double *__restrict__ tables, int n, int ncat, int ncm,
+                                                      int denom, int nmix, int codes) {
+    const DevChild ch = children[blockIdx.x];
+    const int block = n * ncm, nn = n * n;
+    double *echild = tables + ch.echild_off;
+    // phase 1: echild
+    for (int idx = threadIdx.x; idx < block * n; idx += blockDim.x) {
+        int c = idx / nn, r = idx - c * nn, i = r % n;
+        int mm = c / denom;
+        double len_child = m.rates[c % ncat] * ch.length;
+        echild[idx] = m.evec[(size_t)mm * nn + r] * exp(m.eval[mm * n + i] * len_child);
+    }
+    if (ch.leaf_off < 0) return;
+    __syncthreads();
+    double *leaf = tables + ch.leaf_off;
+    const int tip_block = n * nmix;
+    for (int idx = threadIdx.x; idx < codes * block; idx += blockDim.x) {
+        int s = idx / block, r = idx - s * block;  // r = c*n + x
+        double v;
+        if (s == codes - 1) {
+            v = 1.0;
+        } else {
+            int c = r / n;
+            const double *e = echild + (size_t)r * n;
+            const double *tip = m.tip_partial_lh + (size_t)s * tip_block + (c / denom) * n;
+            v = e[0] * tip[0];
+            for (int i = 1; i < n; i++) v += e[i] * tip[i];
+        }
+        leaf[idx] = v;
+    }
+}
+
+int launch_tables(b200lk_ctx *c, int nchildren) {
+    if (nchildren <= 0) return B200LK_OK;
+    const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
+    tables_kernel<<<nchildren, 256, 0, c->stream>>>(c->d_children, c->m, c->tables, c->d.nstates, c->d.ncat,
+                                                    c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches++;
+    return B200LK_OK;
+}

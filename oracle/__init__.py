@@ -27,3 +27,11 @@ def oracle_engine(aln, model, rates, props, **kw):
     if not os.path.exists(ORACLE_LIB):
         build(with_ref=False)
     return engine_for(aln, model, rates, props, lib_path=ORACLE_LIB, prefix="orc_", **kw)
+
+
+def set_ref_quirks(on: bool) -> None:
+    """Toggle the reference's odd-nstates dotProductTriple quirk in the restatement (default on)."""
+    import ctypes
+    if not os.path.exists(ORACLE_LIB):
+        build(with_ref=False)
+    ctypes.CDLL(ORACLE_LIB).orc_set_ref_quirks(int(bool(on)))

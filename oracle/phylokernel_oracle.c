@@ -184,8 +184,18 @@ static inline double dot3(const double *A, const double *B, const double *C, int
 
 /* dotProductTriple<ADD=false>, tree/phylokernelnew.h:666-725: two interleaved
  * accumulators over the flat block of N elements */
+/* REFERENCE QUIRK (kept by default, orc_set_ref_quirks(0) turns it off): the parity test is on
+ * nstates while the loop runs over N = block (:2491).  For odd nstates with even ncat_mix the
+ * "odd" branch visits every element in the loop AND adds element N-1 once more, so the reference's
+ * lh/df/ddf count the last (category, eigen index) entry twice.  nstates 4 and 20 are unaffected. */
+static int orc_ref_quirks = 1;
+int orc_set_ref_quirks(int on) {
+    orc_ref_quirks = on;
+    return 0;
+}
 static inline void dot_triple(const double *A, const double *B, const double *C, const double *D,
                               double *X, double *Y, double *Z, int N, int nstates) {
+    if (!orc_ref_quirks) nstates = N;
     double AD[2], BD[2], CD[2];
     for (int j = 0; j < 2; j++) {
         AD[j] = A[j] * D[j];

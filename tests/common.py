@@ -1,0 +1,67 @@
+"""Shared helpers for the parity tests: seeded problems and the call sequence
+that is run identically against the CUDA engine and the CPU oracle."""
+import numpy as np
+
+from iqtree2_b200 import workload as W
+from iqtree2_b200.capi import INTERNAL, LEAF
+
+
+def make_problem(ntaxa, nsite, nstates=4, ncat=4, nmix=1, seed=1, alpha=0.5, compress=True,
+                 gaps=0.0, mean_len=0.1):
+    tree = W.random_tree(ntaxa, seed, mean_len=mean_len)
+    if nstates == 4 and nmix == 1:
+        model = W.gtr_model()
+    else:
+        model = W.random_reversible_model(nstates, seed + 100, nmix)
+    rates, props = W.discrete_gamma(alpha, ncat)
+    aln = W.simulate_alignment(tree, model, rates, props, nsite, seed + 7, compress=compress)
+    if gaps > 0:
+        rng = np.random.default_rng(seed + 13)
+        mask = rng.random(aln.states.shape) < gaps
+        amb = rng.integers(nstates, aln.state_unknown + 1, size=aln.states.shape).astype(np.uint8)
+        aln.states[mask] = amb[mask]
+    return tree, model, rates, props, aln
+
+
+def full_eval(eng, tree, leaf=0, slot_base=0):
+    """All partials stale -> traversal toward `leaf`, lnL at its branch, theta, df/ddf,
+    lnL from buffer.  Returns a dict of everything comparable."""
+    c = tree.adj[leaf][0]
+    tr = W.traversal(tree, c, leaf)
+    if slot_base:
+        tr = [(a, b, s + slot_base, [(k, (i + slot_base if k == INTERNAL else i), l) for k, i, l in ch])
+              for a, b, s, ch in tr]
+    eng.update_partials(tr)
+    L = tree.get_length(leaf, c)
+    top = tr[-1][2]
+    out = {"traversal": tr, "top": top}
+    out["lnl"] = eng.branch_lnl((LEAF, leaf), (INTERNAL, top), L)
+    out["pattern_lh"] = eng.fetch_pattern_lh()
+    out["pattern_lh_cat"] = eng.fetch_pattern_lh_cat()
+    eng.build_theta((LEAF, leaf), (INTERNAL, top))
+    out["df"], out["ddf"] = eng.derv(L)
+    out["lnl_buf"] = eng.lnl_from_buffer(L)
+    out["theta"], out["bscale"] = eng.fetch_theta()
+    out["scale"] = {s: eng.fetch_scale_num(s) for (_, _, s, _) in tr}
+    out["partial_top"] = eng.fetch_partial(top)
+    return out
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b) / np.maximum(1.0, np.maximum(np.abs(a), np.abs(b))))) if a.size else 0.0
+
+
+def assert_parity(got, want, tol=1e-9):
+    """north_star tolerance: scale counts bit-exact; lnL, df, ddf, per-pattern values 1e-9 relative."""
+    for s in want["scale"]:
+        assert np.array_equal(got["scale"][s], want["scale"][s]), "scale_num differs in slot %d" % s
+    for k in ("lnl", "lnl_buf", "df", "ddf"):
+        assert rel(got[k], want[k]) <= tol, (k, got[k], want[k])
+    for k in ("pattern_lh", "bscale"):
+        assert rel(got[k], want[k]) <= tol, k
+    # values that underflow toward 0 are compared relative to the row's largest magnitude
+    for k in ("theta", "partial_top", "pattern_lh_cat"):
+        g, w = got[k].reshape(got[k].shape[0], -1), want[k].reshape(want[k].shape[0], -1)
+        denom = np.maximum(np.abs(w).max(axis=1, keepdims=True), 1e-300)
+        assert float(np.max(np.abs(g - w) / denom)) <= tol, k
