@@ -29,6 +29,7 @@ kinds = [sum(1 for k in e[3] if k[0] == 1) for e in tr]
 B = sum(8 * 4 * n * (1 + k) + (1 + k) + (2 - k) for k in kinds) * N
 print('partials only ms', dt * 1e3, 'updates/s %.3e' % (len(tr) * N / dt), 'GB/s algorithmic', B / dt / 1e9)
 L = tree.get_length(0, c)
+g.build_theta((LEAF, 0), (INTERNAL, tr[-1][2]))
 for name, f in (('derv', lambda: g.derv(L)), ('frombuf', lambda: g.lnl_from_buffer(L)), ('theta', lambda: g.build_theta((LEAF, 0), (INTERNAL, tr[-1][2]))), ('lnl', lambda: g.branch_lnl((LEAF, 0), (INTERNAL, tr[-1][2]), L))):
     f(); t0 = time.time()
     for i in range(10): f()
