@@ -1,0 +1,319 @@
+#!/usr/bin/env python
+"""bench.py -- the tree-likelihood hot path on B200, one JSON line per run.
+
+A *step* is one full evaluation of the workload through the C ABI (include/b200lk.h):
+every partial-likelihood vector stale -> post-order update of all T-2 internal nodes ->
+lnL at the root branch -> theta -> (df, ddf): SURVEY.md section 8(d), metric (1)+(2).
+
+  value  pattern-node likelihood updates/s, device-timed (CUDA events on the launching stream),
+         inputs resident in HBM, results left on the device (b200lk_evaluate_async)
+  e2e    the same through the blocking call a host caller makes per model probe:
+         b200lk_set_model (eigen-system + rates H2D) + b200lk_evaluate (traversal descriptors and
+         branch lengths H2D, lnL/df/ddf D2H)
+  roofline      the partial-update kernel: algorithmic bytes (B_K per node kind) /
+                its CUDA-event time inside the timed region, against MEASURED_PEAKS.json
+  cpu_baseline  the CPU checker (oracle/) on a bounded pattern sample, all host threads
+
+N > 1 (torchrun): every rank owns an independent pattern shard of the same size (weak scaling); the
+only exchange is an NCCL all-reduce of [lnL, df, ddf] in place on the device result buffer.
+
+`--impl reference` times the CPU implementation only (oracle/_ref when built, else the oracle port).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "pattern_node_likelihood_updates_per_sec"
+UNIT = "updates/s"
+
+WORKLOADS = {
+    # name: (ntaxa, npatterns, nstates, ncat, nmix, alpha, seed, description)
+    "cfg2": (200, 1_000_000, 4, 4, 1, 0.5, 1, "synthetic DNA 200 taxa x 1M patterns, GTR+G4, full traversal + lnL + derv"),
+    "cfg3": (500, 200_000, 20, 4, 1, 0.7, 2, "synthetic protein 500 taxa x 200k patterns, 20-state reversible +G4"),
+    "small": (50, 100_000, 4, 4, 1, 0.5, 5, "synthetic DNA 50 taxa x 100k patterns, GTR+G4 (smoke size)"),
+}
+
+
+def build_workload(name, npatterns=None, seed_shift=0):
+    from iqtree2_b200 import workload as W
+    T, N, n, ncat, nmix, alpha, seed, _ = WORKLOADS[name]
+    if npatterns:
+        N = npatterns
+    tree = W.random_tree(T, seed)
+    model = W.gtr_model() if (n == 4 and nmix == 1) else W.random_reversible_model(n, seed + 100, nmix)
+    rates, props = W.discrete_gamma(alpha, ncat)
+    aln = W.simulate_alignment(tree, model, rates, props, N, seed + 1000 + seed_shift, compress=False)
+    return tree, model, rates, props, aln
+
+
+def traversal_bytes(tr, N, nstates, ncat_mix, safe=False):
+    """Algorithmic bytes of the partial updates of one traversal:
+    B_K = 8*block*(1+k_int) + S*(1+k_int) + s*(2-k_int) per pattern for a bifurcating node with
+    k_int internal children."""
+    block = nstates * ncat_mix
+    S = ncat_mix if safe else 1
+    total = 0
+    kinds = {0: 0, 1: 0, 2: 0}
+    for e in tr:
+        k = sum(1 for ch in e[3] if ch[0] == 1)
+        nleaf = len(e[3]) - k
+        total += 8 * block * (1 + k) + S * (1 + k) + nleaf
+        kinds[min(k, 2)] += 1
+    return total * N, kinds
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.sm, self.reasons, self.max_mhz = index, False, [], set(), None
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                     nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+            while not self.stop_flag:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+                time.sleep(0.02)
+        except Exception as ex:  # no NVML: report that instead of guessing
+            self.reasons.add("nvml_unavailable:%s" % type(ex).__name__)
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
+
+
+def cpu_engine(aln, model, rates, props, nslots):
+    """(engine, kind): the reference's own kernels (oracle/_ref) when built, else the C restatement."""
+    import oracle
+    try:
+        from oracle import ref_engine  # provided when oracle/_ref is built
+        eng = ref_engine(aln, model, rates, props, nslots=nslots)
+        if eng is not None:
+            return eng, "reference"
+    except Exception:
+        pass
+    return oracle.oracle_engine(aln, model, rates, props, nslots=nslots), "port"
+
+
+def time_cpu(tree, model, rates, props, aln, sample, steps, warmup):
+    """CPU baseline on the first `sample` patterns of the same alignment, all host threads."""
+    from iqtree2_b200 import workload as W
+    from iqtree2_b200.capi import INTERNAL, LEAF
+    sub = W.Alignment(aln.nstates, aln.names, np.ascontiguousarray(aln.states[:, :sample]),
+                      np.ascontiguousarray(aln.ptn_freq[:sample]))
+    eng, kind = cpu_engine(sub, model, rates, props, tree.ntaxa)
+    cores = os.cpu_count() or 1
+    if hasattr(eng.lib, eng.prefix + "set_threads"):
+        eng._f("set_threads")(eng.ctx, cores)
+    c = tree.adj[0][0]
+    tr = W.traversal(tree, c, 0)
+    args = (tr, (LEAF, 0), (INTERNAL, tr[-1][2]), tree.get_length(0, c))
+    for _ in range(warmup):
+        eng.evaluate(*args)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        res = eng.evaluate(*args)
+    dt = (time.perf_counter() - t0) / steps
+    return {"value": len(tr) * sub.nptn / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": "first %d of %d patterns, same tree/model, %d full evaluations" % (sub.nptn, aln.nptn, steps),
+            "ms_per_eval": dt * 1e3, "evals_per_sec": 1.0 / dt, "lnl": res[0]}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    T, N, n, ncat, nmix, *_ = WORKLOADS[args.workload]
+    sample = min(args.cpu_sample, args.patterns or N)
+    tree, model, rates, props, aln = build_workload(args.workload, sample)
+    r = time_cpu(tree, model, rates, props, aln, sample, max(1, args.steps), max(1, args.warmup))
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_eval"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic (seeded AliSim-equivalent sampler)",
+            "config": {"workload": args.workload + ": " + WORKLOADS[args.workload][7], "ntaxa": T,
+                       "patterns_timed": sample, "nstates": n, "ncat": ncat},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "evals_per_sec": r["evals_per_sec"], "gpu_launches": 0,
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--patterns", type=int, default=0, help="override patterns per GPU (debug)")
+    ap.add_argument("--cpu-sample", type=int, default=100_000, help="patterns in the CPU-baseline sample")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from iqtree2_b200 import workload as W
+    from iqtree2_b200.capi import INTERNAL, LEAF, engine_for, pack_traversal
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback on this path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    T, N, n, ncat, nmix, *_ = WORKLOADS[args.workload]
+    if args.patterns:
+        N = args.patterns
+    # every rank: same tree and model, its own pattern shard (seed shifted by rank)
+    tree, model, rates, props, aln = build_workload(args.workload, N, seed_shift=rank)
+    eng = engine_for(aln, model, rates, props, nslots=T, device=local)
+    # a dedicated (non-default) stream shared by the engine, NCCL and the timing events
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    eng.set_stream(stream.cuda_stream)
+    root = tree.adj[0][0]
+    tr = W.traversal(tree, root, 0)
+    packed = pack_traversal(tr)
+    dad, node, L = (LEAF, 0), (INTERNAL, tr[-1][2]), tree.get_length(0, root)
+    res_t = eng.result_tensor()
+    tipl = W.tip_partial_lh(model)
+    model_args = (model.eval, model.evec, model.inv_evec, np.asarray(rates), np.asarray(props), model.mixw, tipl)
+    h2d = sum(np.asarray(a).nbytes for a in model_args) + 16 * packed[1] + 16 * packed[3]
+    alg_bytes, kinds = traversal_bytes(tr, N, n, ncat * nmix)
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        eng.evaluate_async(packed, dad, node, L)
+        if world > 1:
+            dist.all_reduce(res_t)
+
+    def step_e2e():
+        eng.set_model(*model_args)
+        eng.evaluate_async(packed, dad, node, L)
+        if world > 1:
+            dist.all_reduce(res_t)
+        return eng.read_results()
+
+    for _ in range(max(3, args.warmup)):
+        step_device()
+    sync_all()
+    eng.synchronize()
+    eng.get_profile(reset=True)
+    eng.reset_counters()
+
+    # ---- device-timed region -------------------------------------------------------------------
+    sampler = ClockSampler(local)
+    sampler.start()
+    eng.set_profiling(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    sync_all()
+    ms = e0.elapsed_time(e1)
+    eng.set_profiling(False)
+    partial_ms, partial_launches = eng.get_profile(reset=True)
+    _, launches = eng.counters()
+    result = eng.read_results()
+
+    # ---- end-to-end region ---------------------------------------------------------------------
+    for _ in range(2):
+        step_e2e()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        result = step_e2e()
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    sampler.stop_flag = True
+    sampler.join()
+
+    t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = (float(x) for x in t.cpu())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    updates_per_step = len(tr) * N * world
+    peaks = {}
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk):
+        peaks = json.load(open(pk))
+    peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = alg_bytes * args.steps / (partial_ms * 1e-3) / 1e9 if partial_ms > 0 else None
+    line = {
+        "metric": METRIC, "value": updates_per_step * args.steps / (ms * 1e-3), "unit": UNIT,
+        "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic (seeded AliSim-equivalent sampler, every column its own pattern)",
+        "config": {"workload": args.workload + ": " + WORKLOADS[args.workload][7], "ntaxa": T,
+                   "patterns_per_gpu": N, "nstates": n, "ncat": ncat, "nmix": nmix,
+                   "node_kinds_TT_TI_II": [kinds[0], kinds[1], kinds[2]],
+                   "sharding": "pattern shards, one per GPU; NCCL all-reduce of [lnL, df, ddf] only",
+                   "l2": "inputs larger than L2 (partials %.1f GB per GPU)" % (len(tr) * N * n * ncat * nmix * 8 / 1e9)},
+        "evals_per_sec": args.steps / (ms * 1e-3),
+        "e2e": {"value": updates_per_step * args.steps / (e2e_ms * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 24,
+                "ms_per_step": e2e_ms / args.steps, "evals_per_sec": args.steps / (e2e_ms * 1e-3)},
+        "gpu_launches": int(launches),
+        "clocks": sampler.summary(),
+        "roofline": {"bound": "hbm", "kernel": "partial update (pruning step)", "achieved": achieved,
+                     "peak": peak_gbs, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                     "unit": "GB/s", "frac": (achieved / peak_gbs) if achieved else None, "traffic": None,
+                     "algorithmic_bytes_per_step": int(alg_bytes), "kernel_ms_per_step": partial_ms / args.steps,
+                     "launches_per_step": partial_launches / max(1, args.steps)},
+        "lnl_df_ddf": list(result),
+    }
+    if not args.no_cpu and world == 1:
+        sample = min(args.cpu_sample, N)
+        line["cpu_baseline"] = {k: v for k, v in time_cpu(tree, model, rates, props, aln, sample, 3, 1).items()
+                                if k in ("value", "unit", "cores", "kind", "sample", "evals_per_sec")}
+    tr_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr_file):  # dram bytes per launch from the committed ncu --set full capture
+        try:
+            line["roofline"]["traffic"] = json.load(open(tr_file)).get(args.workload)
+        except Exception:
+            pass
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

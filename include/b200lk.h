@@ -150,6 +150,15 @@ int b200lk_evaluate(b200lk_ctx *ctx, const b200lk_node *nodes, int32_t nnodes,
                     const b200lk_child *children, int32_t nchildren, b200lk_end dad, b200lk_end node,
                     double length, double *lnl, double *df, double *ddf);
 
+/* Asynchronous form of b200lk_evaluate: everything is enqueued on the context's stream and the sums
+ * stay in the device result buffer (b200lk_result_device_ptr) -- e.g. to be all-reduced across
+ * pattern shards by NCCL on the same stream -- until b200lk_read_results copies them back
+ * (the only device->host transfer of an evaluation: 3 doubles). */
+int b200lk_evaluate_async(b200lk_ctx *ctx, const b200lk_node *nodes, int32_t nnodes,
+                          const b200lk_child *children, int32_t nchildren, b200lk_end dad, b200lk_end node,
+                          double length, int want_lnl, int want_derv);
+int b200lk_read_results(b200lk_ctx *ctx, double *lnl, double *df, double *ddf);
+
 /* ---- device-resident results on demand --------------------------------- */
 /* Unreduced per-shard sums for multi-GPU runs: out[0] = lnL (if requested), out[1] = df,
  * out[2] = ddf are left in a device buffer; this returns its device pointer (3 doubles)
@@ -168,6 +177,11 @@ int b200lk_fetch_theta(b200lk_ctx *ctx, double *theta /* [nptn][ncat_mix][nstate
 int b200lk_get_counters(b200lk_ctx *ctx, int64_t *pattern_node_updates, int64_t *kernel_launches);
 int b200lk_reset_counters(b200lk_ctx *ctx);
 int b200lk_synchronize(b200lk_ctx *ctx);
+/* Optional per-launch CUDA-event timing of the partial-update kernels (the dominant kernel):
+ * accumulated milliseconds and launch count since the last reset.  Replaces nothing in the
+ * reference (its only timers are getRealTime/getCPUTime, utils/timeutil.h:95-134). */
+int b200lk_set_profiling(b200lk_ctx *ctx, int on);
+int b200lk_get_profile(b200lk_ctx *ctx, double *partial_ms, int64_t *partial_launches, int reset);
 
 #ifdef __cplusplus
 }

@@ -177,6 +177,44 @@ class Engine:
               C.byref(ddf) if want_derv else None))
         return lnl.value, df.value, ddf.value
 
+    def evaluate_async(self, packed, dad, node, length, want_lnl=True, want_derv=True):
+        """Enqueue a whole evaluation; ``packed`` = pack_traversal(entries) (reusable).  Results stay
+        on the device (result_tensor) until read_results()."""
+        nodes, nn, kids, nk = packed
+        f = self._f("evaluate_async")
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, End, End, C.c_double,
+                      C.c_int, C.c_int]
+        return self._check(f(self.ctx, nodes, nn, kids, nk, End(*dad), End(*node), length,
+                             int(want_lnl), int(want_derv)))
+
+    def read_results(self):
+        lnl, df, ddf = C.c_double(), C.c_double(), C.c_double()
+        self.last_status = self._check(self._f("read_results")(self.ctx, C.byref(lnl), C.byref(df), C.byref(ddf)))
+        return lnl.value, df.value, ddf.value
+
+    def set_stream(self, cuda_stream_ptr):
+        """Run on a caller-owned stream (an int cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream)."""
+        return self._check(self._f("set_stream")(self.ctx, C.c_void_p(cuda_stream_ptr)))
+
+    def set_profiling(self, on=True):
+        return self._check(self._f("set_profiling")(self.ctx, int(on)))
+
+    def get_profile(self, reset=True):
+        ms, n = C.c_double(), C.c_int64()
+        self._check(self._f("get_profile")(self.ctx, C.byref(ms), C.byref(n), int(reset)))
+        return ms.value, n.value
+
+    def result_tensor(self):
+        """The device result buffer [lnL, df, ddf] as a torch tensor aliasing device memory, so that
+        pattern shards can be all-reduced in place (NCCL) on the context's stream."""
+        import torch
+        p = C.c_void_p()
+        self._check(self._f("result_device_ptr")(self.ctx, C.byref(p)))
+
+        class _Buf:
+            __cuda_array_interface__ = {"shape": (3,), "typestr": "<f8", "data": (p.value, False), "version": 3}
+        return torch.as_tensor(_Buf(), device="cuda:%d" % self.dims.device)
+
     # -- readers -------------------------------------------------------------
     def fetch_pattern_lh(self):
         out = np.empty(self.dims.nptn)
@@ -209,6 +247,9 @@ class Engine:
         a, b = C.c_int64(), C.c_int64()
         self._check(self._f("get_counters")(self.ctx, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def reset_counters(self):
+        self._check(self._f("reset_counters")(self.ctx))
 
     def synchronize(self):
         if self.prefix == "b200lk_":

@@ -28,6 +28,11 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
         return B200LK_ERR_ARG;
     }
     const int n = c->d.nstates, block = c->block, nslots = c->d.nslots;
+    // next slice of the pinned staging ring; wait only if its previous copy is still in flight
+    const int ring = c->stage_idx++ % B200_STAGE_RING;
+    if (c->stage_used[ring]) CUDA_TRY(c, cudaEventSynchronize(c->stage_ev[ring]));
+    c->h_nodes = c->h_nodes_ring + (size_t)ring * c->nodes_cap;
+    c->h_children = c->h_children_ring + (size_t)ring * c->children_cap;
     // level of each node = 1 + max level of the children produced earlier in this same list
     // (slots may be recycled inside one list in memory-saving mode: a write also waits for earlier
     // readers and writers of the same slot, so batching never reorders a hazard)
@@ -102,6 +107,8 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
     CUDA_TRY(c, cudaMemcpyAsync(c->d_children, c->h_children, sizeof(DevChild) * nchildren, cudaMemcpyHostToDevice,
                                 c->stream));
     CUDA_TRY(c, cudaMemcpyAsync(c->d_nodes, c->h_nodes, sizeof(DevNode) * nnodes, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaEventRecord(c->stage_ev[ring], c->stream));
+    c->stage_used[ring] = true;
     int rc = launch_tables(c, nchildren);
     if (rc) return rc;
     rc = launch_partials(c, levels);
@@ -163,9 +170,7 @@ extern "C" int b200lk_update_partials(b200lk_ctx *c, const b200lk_node *nodes, i
     CUDA_TRY(c, cudaSetDevice(c->device));
     rc = enqueue_update(c, nodes, nnodes, children, nchildren);
     if (rc) return rc;
-    // the pinned staging buffers are reused by the next call
-    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-    return B200LK_OK;
+    return B200LK_OK;  // asynchronous: later calls on this context are stream-ordered after it
 }
 
 extern "C" int b200lk_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length, double *lnl) {
@@ -215,21 +220,20 @@ extern "C" int b200lk_lnl_from_buffer(b200lk_ctx *c, double length, double *lnl)
     return finish_lnl(c, lnl);
 }
 
-extern "C" int b200lk_evaluate(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
-                               int32_t nchildren, b200lk_end dad, b200lk_end node, double length, double *lnl,
-                               double *df, double *ddf) {
+extern "C" int b200lk_evaluate_async(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes,
+                                     const b200lk_child *children, int32_t nchildren, b200lk_end dad,
+                                     b200lk_end node, double length, int want_lnl, int want_derv) {
     int rc = check_ready(c);
     if (rc) return rc;
     if (check_ends(c, dad, node)) return B200LK_ERR_ARG;
     CUDA_TRY(c, cudaSetDevice(c->device));
     rc = enqueue_update(c, nodes, nnodes, children, nchildren);
     if (rc) return rc;
-    const bool want_derv = df || ddf;
     if (c->d.nptn == 0) {
-        if (lnl) *lnl = 0; if (df) *df = 0; if (ddf) *ddf = 0;
+        CUDA_TRY(c, cudaMemsetAsync(c->d_result, 0, sizeof(double) * 3, c->stream));
         return B200LK_OK;
     }
-    if (lnl) {
+    if (want_lnl) {
         rc = launch_branch_lnl(c, dad, node, length);
         if (rc) return rc;
     }
@@ -240,12 +244,18 @@ extern "C" int b200lk_evaluate(b200lk_ctx *c, const b200lk_node *nodes, int32_t 
         rc = launch_derv(c, length);
         if (rc) return rc;
     }
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_read_results(b200lk_ctx *c, double *lnl, double *df, double *ddf) {
+    if (!c) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
     // one synchronising read for everything
     int warn = 0;
-    rc = read_results(c, 0, 3);
+    int rc = read_results(c, 0, 3);
     if (rc) return rc;
     if (lnl) {
-        if (!isfinite(c->h_result[0])) {
+        if (!isfinite(c->h_result[0]) && c->d.nptn > 0) {
             rc = finish_lnl(c, lnl);
             if (rc < 0) return rc;
             warn |= rc;
@@ -253,7 +263,7 @@ extern "C" int b200lk_evaluate(b200lk_ctx *c, const b200lk_node *nodes, int32_t 
             *lnl = c->h_result[0];
         }
     }
-    if (want_derv) {
+    if (df || ddf) {
         double a = c->h_result[1], b = c->h_result[2];
         if (!isfinite(a)) {
             warn |= B200LK_WARN_DERV_NONFINITE;
@@ -263,4 +273,13 @@ extern "C" int b200lk_evaluate(b200lk_ctx *c, const b200lk_node *nodes, int32_t 
         if (ddf) *ddf = b;
     }
     return warn;
+}
+
+extern "C" int b200lk_evaluate(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
+                               int32_t nchildren, b200lk_end dad, b200lk_end node, double length, double *lnl,
+                               double *df, double *ddf) {
+    int rc = b200lk_evaluate_async(c, nodes, nnodes, children, nchildren, dad, node, length, lnl != nullptr,
+                                   df != nullptr || ddf != nullptr);
+    if (rc) return rc;
+    return b200lk_read_results(c, lnl, df, ddf);
 }

@@ -24,6 +24,8 @@
 #define B200_LOG_SCALING_THRESHOLD (-177.4456782233459932741)  // tree/phylotree.h:80
 #define B200_TWO_256 1.157920892373161954235709850086879e77    // 2^256: ldexp(x,256) as an exact multiply
 
+#define B200_STAGE_RING 4
+
 struct DevModel {
     double *eval, *evec, *inv_evec, *rates, *props, *mixw, *tip_partial_lh;
 };
@@ -63,8 +65,18 @@ struct b200lk_ctx {
     DevNode *d_nodes;
     DevChild *d_children;
     int nodes_cap, children_cap;
-    DevNode *h_nodes;      // pinned staging
+    DevNode *h_nodes;      // pinned staging: slice of the ring used by the call in flight
     DevChild *h_children;  // pinned staging
+    DevNode *h_nodes_ring;      // B200_STAGE_RING slices of nodes_cap / children_cap entries, so that
+    DevChild *h_children_ring;  // asynchronous evaluations never overwrite a copy still in flight
+    cudaEvent_t stage_ev[B200_STAGE_RING];
+    bool stage_used[B200_STAGE_RING];
+    int stage_idx;
+    // optional per-launch timing of the partial-update kernels (b200lk_set_profiling)
+    bool profiling;
+    std::vector<cudaEvent_t> *prof_events;  // start/stop pairs
+    double prof_ms;
+    int64_t prof_launches;
     double *red_partial;   // [3][red_blocks] block partial sums
     int red_blocks;
     double *d_result;      // [4] lnL, df, ddf, prob_const
@@ -86,6 +98,15 @@ struct b200lk_ctx {
 
 static inline double *slot_partial(const b200lk_ctx *c, int s) { return c->partial + (size_t)s * c->slot_doubles; }
 static inline uint8_t *slot_scale(const b200lk_ctx *c, int s) { return c->scale + (size_t)s * c->slot_scale_bytes; }
+
+// record one end of a timed partial-update launch (pairs: before, after)
+static inline void prof_mark(b200lk_ctx *c) {
+    if (!c->profiling) return;
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, c->stream);
+    c->prof_events->push_back(e);
+}
 
 // launchers implemented in tables.cu / partial.cu / branch.cu
 int launch_tables(b200lk_ctx *c, int nchildren);

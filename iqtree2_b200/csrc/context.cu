@@ -57,8 +57,13 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->tables, sizeof(double) * c->tables_cap));
     CUDA_TRY(c, cudaMalloc(&c->d_nodes, sizeof(DevNode) * c->nodes_cap));
     CUDA_TRY(c, cudaMalloc(&c->d_children, sizeof(DevChild) * c->children_cap));
-    CUDA_TRY(c, cudaMallocHost(&c->h_nodes, sizeof(DevNode) * c->nodes_cap));
-    CUDA_TRY(c, cudaMallocHost(&c->h_children, sizeof(DevChild) * c->children_cap));
+    CUDA_TRY(c, cudaMallocHost(&c->h_nodes_ring, sizeof(DevNode) * c->nodes_cap * B200_STAGE_RING));
+    CUDA_TRY(c, cudaMallocHost(&c->h_children_ring, sizeof(DevChild) * c->children_cap * B200_STAGE_RING));
+    c->h_nodes = c->h_nodes_ring;
+    c->h_children = c->h_children_ring;
+    for (int i = 0; i < B200_STAGE_RING; i++)
+        CUDA_TRY(c, cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming));
+    c->prof_events = new std::vector<cudaEvent_t>();
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
     c->red_blocks = sms * 8;
@@ -112,8 +117,14 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
                    c->d_nodes, c->d_children, c->red_partial, c->d_result};
     for (void *p : dev)
         if (p) cudaFree(p);
-    if (c->h_nodes) cudaFreeHost(c->h_nodes);
-    if (c->h_children) cudaFreeHost(c->h_children);
+    if (c->h_nodes_ring) cudaFreeHost(c->h_nodes_ring);
+    if (c->h_children_ring) cudaFreeHost(c->h_children_ring);
+    for (int i = 0; i < B200_STAGE_RING; i++)
+        if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
+    if (c->prof_events) {
+        for (cudaEvent_t e : *c->prof_events) cudaEventDestroy(e);
+        delete c->prof_events;
+    }
     if (c->h_result) cudaFreeHost(c->h_result);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
@@ -224,5 +235,31 @@ extern "C" int b200lk_reset_counters(b200lk_ctx *c) {
 extern "C" int b200lk_result_device_ptr(b200lk_ctx *c, void **dptr) {
     if (!c || !dptr) return B200LK_ERR_ARG;
     *dptr = c->d_result;
+    return B200LK_OK;
+}
+
+// ---- per-launch timing of the partial-update kernels -------------------------
+extern "C" int b200lk_set_profiling(b200lk_ctx *c, int on) {
+    if (!c) return B200LK_ERR_ARG;
+    c->profiling = on != 0;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_get_profile(b200lk_ctx *c, double *partial_ms, int64_t *partial_launches, int reset) {
+    if (!c) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    std::vector<cudaEvent_t> &ev = *c->prof_events;
+    for (size_t i = 0; i + 1 < ev.size(); i += 2) {
+        float ms = 0.f;
+        CUDA_TRY(c, cudaEventElapsedTime(&ms, ev[i], ev[i + 1]));
+        c->prof_ms += ms;
+        c->prof_launches++;
+    }
+    for (cudaEvent_t e : ev) cudaEventDestroy(e);
+    ev.clear();
+    if (partial_ms) *partial_ms = c->prof_ms;
+    if (partial_launches) *partial_launches = c->prof_launches;
+    if (reset) { c->prof_ms = 0.0; c->prof_launches = 0; }
     return B200LK_OK;
 }

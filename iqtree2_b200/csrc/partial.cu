@@ -299,17 +299,21 @@ int launch_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels) 
         if (nb) {
             a.node_base = base;
             dim3 grid((unsigned)((c->ntot + a.PT - 1) / a.PT), nb);
+            prof_mark(c);
             if (n == 4) launch_one<4>(a, safe, grid, threads, smem, c->stream);
             else if (n == 20) launch_one<20>(a, safe, grid, threads, smem, c->stream);
             else launch_one<0>(a, safe, grid, threads, smem, c->stream);
+            prof_mark(c);
             CUDA_TRY(c, cudaGetLastError());
             c->n_launches++;
         }
         if (nm) {
             a.node_base = base + nb;
             dim3 grid((unsigned)((c->ntot + 127) / 128), nm);
+            prof_mark(c);
             if (safe) partial_multi_kernel<true><<<grid, 128, 0, c->stream>>>(a);
             else partial_multi_kernel<false><<<grid, 128, 0, c->stream>>>(a);
+            prof_mark(c);
             CUDA_TRY(c, cudaGetLastError());
             c->n_launches++;
         }

@@ -15,7 +15,7 @@ REF_LIB = os.path.join(HERE, "_ref", "libiqtree_ref.so")
 
 def build(with_ref: bool = True, verbose: bool = False) -> None:
     targets = ["liboracle.so"]
-    if with_ref and os.path.isdir("/root/reference/tree"):
+    if with_ref and os.path.isdir("/root/reference/tree") and os.path.exists(os.path.join(HERE, "Makefile.ref")):
         targets.append("ref")
     out = None if verbose else subprocess.DEVNULL
     subprocess.check_call(["make", "-s", "-C", HERE, "-j8"] + targets, stdout=out)
