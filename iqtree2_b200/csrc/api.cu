@@ -33,6 +33,7 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
     if (c->stage_used[ring]) CUDA_TRY(c, cudaEventSynchronize(c->stage_ev[ring]));
     c->h_nodes = c->h_nodes_ring + (size_t)ring * c->nodes_cap;
     c->h_children = c->h_children_ring + (size_t)ring * c->children_cap;
+    c->h_prog = (char *)c->h_prog_ring + (size_t)ring * c->prog_stride;
     // level of each node = 1 + max level of the children produced earlier in this same list
     // (slots may be recycled inside one list in memory-saving mode: a write also waits for earlier
     // readers and writers of the same slot, so batching never reorders a hazard)
@@ -82,6 +83,20 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
         }
     }
     if (off > c->tables_cap) return B200LK_ERR_NOMEM;
+    if (traverse4_supported(c, nodes, nnodes)) {
+        // 4-state fast path: the whole list in one pattern-stationary launch (traverse.cu)
+        CUDA_TRY(c, cudaMemcpyAsync(c->d_children, c->h_children, sizeof(DevChild) * nchildren,
+                                    cudaMemcpyHostToDevice, c->stream));
+        int rc = launch_tables(c, nchildren);
+        if (rc) return rc;
+        rc = launch_traverse4(c, nodes, nnodes);
+        if (rc) return rc;
+        CUDA_TRY(c, cudaEventRecord(c->stage_ev[ring], c->stream));
+        c->stage_used[ring] = true;
+        c->n_updates += (int64_t)nnodes * c->ntot;
+        c->theta_computed = false;
+        return B200LK_OK;
+    }
     // level-sorted node array, bifurcating before multifurcating inside a level
     std::vector<std::vector<int>> levels(nlevels);
     int pos = 0;

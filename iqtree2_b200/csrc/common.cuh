@@ -69,6 +69,10 @@ struct b200lk_ctx {
     DevChild *h_children;  // pinned staging
     DevNode *h_nodes_ring;      // B200_STAGE_RING slices of nodes_cap / children_cap entries, so that
     DevChild *h_children_ring;  // asynchronous evaluations never overwrite a copy still in flight
+    size_t prog_stride;
+    void *h_prog, *h_prog_ring, *d_prog;  // device program of the pattern-stationary traversal (traverse.cu)
+    bool trav_attr_set, force_level_batched;
+    int max_stack_depth;  // shared-memory stack entries per thread (default 8; B200LK_STACK_DEPTH)
     cudaEvent_t stage_ev[B200_STAGE_RING];
     bool stage_used[B200_STAGE_RING];
     int stage_idx;
@@ -116,3 +120,6 @@ int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node);
 int launch_derv(b200lk_ctx *c, double length);
 int launch_from_buffer(b200lk_ctx *c, double length);
 int launch_repair(b200lk_ctx *c);
+#define B200_PROG_BYTES 48  // sizeof(FNode), traverse.cu
+bool traverse4_supported(const b200lk_ctx *c, const b200lk_node *nodes, int nnodes);
+int launch_traverse4(b200lk_ctx *c, const b200lk_node *nodes, int nnodes);

@@ -3,6 +3,8 @@
 // (tree/phylotree.cpp:890-934, 1054-1182): one arena of nslots partial vectors and
 // scale counters, theta_all, buffer_scale_all, _pattern_lh, _pattern_lh_cat, ptn_freq,
 // ptn_invar and the tip-state matrix all stay in HBM for the life of the context.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 extern "C" const char *b200lk_version(void) { return "b200lk 0.1 (sm_100a)"; }
@@ -59,6 +61,20 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->d_children, sizeof(DevChild) * c->children_cap));
     CUDA_TRY(c, cudaMallocHost(&c->h_nodes_ring, sizeof(DevNode) * c->nodes_cap * B200_STAGE_RING));
     CUDA_TRY(c, cudaMallocHost(&c->h_children_ring, sizeof(DevChild) * c->children_cap * B200_STAGE_RING));
+    // device program of the pattern-stationary traversal: FNode[nodes_cap] then the tip-state row
+    // sequence (chunk-padded: at most one pad chunk per node plus the children themselves)
+    c->prog_stride = (size_t)B200_PROG_BYTES * c->nodes_cap + sizeof(int32_t) * ((size_t)c->children_cap + 8192);
+    CUDA_TRY(c, cudaMallocHost(&c->h_prog_ring, c->prog_stride * B200_STAGE_RING));
+    CUDA_TRY(c, cudaMalloc(&c->d_prog, c->prog_stride));
+    c->h_prog = c->h_prog_ring;
+    {
+        const char *e = getenv("B200LK_LEVEL_BATCHED");  // debugging/A-B switch: disable the fused traversal
+        c->force_level_batched = e && *e == '1';
+        const char *sd = getenv("B200LK_STACK_DEPTH");  // test hook: force the stack-overflow path
+        c->max_stack_depth = sd ? atoi(sd) : 8;
+        if (c->max_stack_depth < 0) c->max_stack_depth = 0;
+        if (c->max_stack_depth > 10) c->max_stack_depth = 10;
+    }
     c->h_nodes = c->h_nodes_ring;
     c->h_children = c->h_children_ring;
     for (int i = 0; i < B200_STAGE_RING; i++)
@@ -94,8 +110,8 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
     c->block = dims->nstates * c->ncat_mix;
     c->scale_per_ptn = dims->safe_numeric ? c->ncat_mix : 1;
     c->ntot = dims->nptn + dims->n_unobserved;
-    c->ntot_pad = ((c->ntot + 127) / 128) * 128;
-    if (c->ntot_pad == 0) c->ntot_pad = 128;
+    c->ntot_pad = ((c->ntot + 255) / 256) * 256;  // a CTA tile of tip states never leaves its row
+    if (c->ntot_pad == 0) c->ntot_pad = 256;
     int rc = alloc_all(c);
     if (rc != B200LK_OK) {
         // keep the context alive long enough for the caller to read the message? no: report and free
@@ -119,6 +135,8 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
         if (p) cudaFree(p);
     if (c->h_nodes_ring) cudaFreeHost(c->h_nodes_ring);
     if (c->h_children_ring) cudaFreeHost(c->h_children_ring);
+    if (c->h_prog_ring) cudaFreeHost(c->h_prog_ring);
+    if (c->d_prog) cudaFree(c->d_prog);
     for (int i = 0; i < B200_STAGE_RING; i++)
         if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
     if (c->prof_events) {

@@ -111,3 +111,41 @@ def test_large_problem_properties():
         fd = (g.lnl_from_buffer(L + h) - g.lnl_from_buffer(L - h)) / (2 * h)
         assert abs(fd - r["df"]) <= 1e-5 * max(1.0, abs(r["df"]))
     assert abs(vals[0] - vals[1]) <= 1e-10 * abs(vals[0])
+
+
+@pytest.mark.parametrize("env", [{"B200LK_LEVEL_BATCHED": "1"}, {"B200LK_STACK_DEPTH": "0"},
+                                 {"B200LK_STACK_DEPTH": "1"}, {}])
+@pytest.mark.parametrize("safe", [False, True])
+def test_dna_paths_agree_with_oracle(oracle_lib, monkeypatch, env, safe):
+    """The 4-state traversal has three routes -- one pattern-stationary launch (default), the same with
+    the shared-memory stack overflowing into global re-reads, and the level-batched kernels -- and all
+    of them must match the oracle, scale counts included (deep tree so that rescaling fires)."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    tree, model, rates, props, aln = make_problem(300, 300, seed=5, mean_len=0.4, gaps=0.02)
+    g, o = both(aln, model, rates, props, nslots=300, safe_numeric=safe)
+    rg, ro = full_eval(g, tree, 3), full_eval(o, tree, 3)
+    assert max(int(s.max()) for s in ro["scale"].values()) >= 1
+    assert_parity(rg, ro, TOL)
+
+
+def test_partial_retraversal_reads_resident_partials(oracle_lib):
+    """After a full traversal only part of the list is recomputed (what a branch-length change does):
+    children outside the list come from the resident slots."""
+    tree, model, rates, props, aln = make_problem(40, 600, seed=12)
+    g, o = both(aln, model, rates, props, nslots=40)
+    full_eval(g, tree, 0), full_eval(o, tree, 0)
+    c = tree.adj[0][0]
+    tr = W.traversal(tree, c, 0)
+    tail = tr[-7:]                       # the last seven nodes; their other children stay resident
+    u, v = tail[0][0], tail[0][1]
+    tree.set_length(u, v, 0.37)
+    tr2 = W.traversal(tree, c, 0)[-7:]
+    for e in (g, o):
+        e.update_partials(tr2)
+    L = tree.get_length(0, c)
+    a = g.branch_lnl((LEAF, 0), (INTERNAL, tr2[-1][2]), L)
+    b = o.branch_lnl((LEAF, 0), (INTERNAL, tr2[-1][2]), L)
+    assert rel(a, b) <= TOL
+    for e in tr2:
+        assert np.array_equal(g.fetch_scale_num(e[2]), o.fetch_scale_num(e[2]))
