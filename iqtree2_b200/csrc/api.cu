@@ -74,7 +74,7 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
         dc.id = children[j].id;
         dc.length = children[j].length;
         dc.echild_off = (int64_t)off;
-        off += (size_t)block * n;
+        off += (size_t)block * n + block;  // echild, then expv
         if (dc.kind == B200LK_CHILD_LEAF) {
             dc.leaf_off = (int64_t)off;
             off += (size_t)c->d.n_state_codes * block;
@@ -83,14 +83,39 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
         }
     }
     if (off > c->tables_cap) return B200LK_ERR_NOMEM;
-    if (traverse4_supported(c, nodes, nnodes)) {
-        // 4-state fast path: the whole list in one pattern-stationary launch (traverse.cu)
+    if (c->tile == 32) {
+        // 4-state path (s4.cu): every run of bifurcating nodes is ONE pattern-stationary launch;
+        // a multifurcating node is its own launch in between (stream order keeps the dependencies)
         CUDA_TRY(c, cudaMemcpyAsync(c->d_children, c->h_children, sizeof(DevChild) * nchildren,
                                     cudaMemcpyHostToDevice, c->stream));
         int rc = launch_tables(c, nchildren);
         if (rc) return rc;
-        rc = launch_traverse4(c, nodes, nnodes);
-        if (rc) return rc;
+        bool any_multi = false;
+        for (int i = 0; i < nnodes; i++) {
+            DevNode &dn = c->h_nodes[i];
+            dn.out_slot = nodes[i].out_slot;
+            dn.child_begin = nodes[i].child_begin;
+            dn.nchild = nodes[i].nchild;
+            dn.kind = nodes[i].nchild > 2 ? 3 : 2;
+            any_multi |= nodes[i].nchild > 2;
+        }
+        if (any_multi)
+            CUDA_TRY(c, cudaMemcpyAsync(c->d_nodes, c->h_nodes, sizeof(DevNode) * nnodes, cudaMemcpyHostToDevice,
+                                        c->stream));
+        int prog_used = 0, seq_used = 0;
+        for (int i = 0; i < nnodes;) {
+            if (nodes[i].nchild > 2) {
+                rc = launch_partial_multi(c, i);
+                if (rc) return rc;
+                i++;
+                continue;
+            }
+            int j = i;
+            while (j < nnodes && nodes[j].nchild == 2) j++;
+            rc = launch_s4_traverse(c, nodes, i, j - i, &prog_used, &seq_used);
+            if (rc) return rc;
+            i = j;
+        }
         CUDA_TRY(c, cudaEventRecord(c->stage_ev[ring], c->stream));
         c->stage_used[ring] = true;
         c->n_updates += (int64_t)nnodes * c->ntot;

@@ -11,6 +11,8 @@
 #include "common.cuh"
 
 #define RED_THREADS 256
+// element e of the current pattern p under the context's layout (common.cuh)
+#define E(e) elem_off(p, (e), block, a.tile)
 
 struct BranchArgs {
     const double *pdad;    // dad_branch->partial_lh  (subtree on the node side)
@@ -22,7 +24,7 @@ struct BranchArgs {
     double *theta, *buffer_scale_all, *pattern_lh, *pattern_lh_cat;
     double *red_partial;
     int64_t nptn, ntot;
-    int n, ncm, block, denom, nmix, G, safe;
+    int n, ncm, block, denom, nmix, G, safe, tile;
 };
 
 // val0[c][i] = exp(eval*rate*len)*prop*mixw, val1 = cof*val0, val2 = cof*val1 (:2342-2357);
@@ -105,8 +107,8 @@ __global__ void __launch_bounds__(RED_THREADS) theta_kernel(BranchArgs a) {
         int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
         const bool valid = p < a.ntot;
         if (!valid) p = a.ntot - 1;
-        const double *pd = a.pdad + (size_t)p * block;
-        double *th = a.theta + (size_t)p * block;
+        const double *pd = a.pdad;
+        double *th = a.theta;
         int min_scale = 0;
         if (a.safe) {
             int ms = 0x7fffffff;
@@ -121,17 +123,17 @@ __global__ void __launch_bounds__(RED_THREADS) theta_kernel(BranchArgs a) {
         const double *other;
         int tip_mode = a.pnode == nullptr;
         if (tip_mode) other = a.tip_partial_lh + (size_t)a.dad_states[p] * (n * a.nmix);
-        else other = a.pnode + (size_t)p * block;
+        else other = a.pnode;
         for (int j = g; j < block; j += G) {
             int c = j / n;
-            double o = tip_mode ? other[(c / a.denom) * n + (j - c * n)] : other[j];
-            double t = o * pd[j];
+            double o = tip_mode ? other[(c / a.denom) * n + (j - c * n)] : other[E(j)];
+            double t = o * pd[E(j)];
             if (a.safe) {
                 int s = (a.sdad[p * ncm + c] + (a.pnode ? a.snode[p * ncm + c] : 0)) & 0xff;
                 if (s == min_scale + 1) t *= B200_SCALING_THRESHOLD;
                 else if (s > min_scale + 1) t = 0.0;
             }
-            if (valid) th[j] = t;
+            if (valid) th[E(j)] = t;
         }
         if (g == 0 && valid) a.buffer_scale_all[p] = (double)min_scale * B200_LOG_SCALING_THRESHOLD;
     }
@@ -148,10 +150,10 @@ __global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red
         int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
         const bool valid = p < a.nptn;
         if (!valid) p = a.nptn - 1;
-        const double *th = a.theta + (size_t)p * block;
+        const double *th = a.theta;
         double lh = 0.0, df = 0.0, ddf = 0.0;
         for (int j = g; j < block; j += G) {
-            double t = th[j];
+            double t = th[E(j)];
             lh = fma(v0[j], t, lh);
             df = fma(v1[j], t, df);
             ddf = fma(v2[j], t, ddf);
@@ -181,9 +183,9 @@ __global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(BranchArgs a, int 
         int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
         const bool valid = p < a.nptn;
         if (!valid) p = a.nptn - 1;
-        const double *th = a.theta + (size_t)p * block;
+        const double *th = a.theta;
         double lh = 0.0;
-        for (int j = g; j < block; j += G) lh = fma(a.val[j], th[j], lh);
+        for (int j = g; j < block; j += G) lh = fma(a.val[j], th[E(j)], lh);
         lh = group_sum(lh, G);
         if (g == 0 && valid) {
             lh = fabs(lh) + a.ptn_invar[p];               // :3295
@@ -208,9 +210,9 @@ __global__ void __launch_bounds__(RED_THREADS) lnl_kernel(BranchArgs a, int red_
         int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
         const bool valid = p < a.nptn;
         if (!valid) p = a.nptn - 1;
-        const double *pd = a.pdad + (size_t)p * block;
+        const double *pd = a.pdad;
         const double *w = tip_mode ? a.tip_val + (size_t)a.dad_states[p] * block : a.val;
-        const double *pn = tip_mode ? nullptr : a.pnode + (size_t)p * block;
+        const double *pn = a.pnode;
         double lh = 0.0;
         int min_scale;
         if (a.safe) {
@@ -225,20 +227,20 @@ __global__ void __launch_bounds__(RED_THREADS) lnl_kernel(BranchArgs a, int red_
         }
         for (int c = g; c < ncm; c += G) {
             double s0 = 0.0, s1 = 0.0;
-            const double *wd = w + c * n, *d = pd + c * n;
+            const double *wd = w + c * n;
+            const int cb = c * n;
             if (tip_mode) {
                 for (int i = 0; i + 1 < n; i += 2) {
-                    s0 = fma(wd[i], d[i], s0);
-                    s1 = fma(wd[i + 1], d[i + 1], s1);
+                    s0 = fma(wd[i], pd[E(cb + i)], s0);
+                    s1 = fma(wd[i + 1], pd[E(cb + i + 1)], s1);
                 }
-                if (n & 1) s0 = fma(wd[n - 1], d[n - 1], s0);
+                if (n & 1) s0 = fma(wd[n - 1], pd[E(cb + n - 1)], s0);
             } else {
-                const double *nd = pn + c * n;
                 for (int i = 0; i + 1 < n; i += 2) {
-                    s0 = fma(wd[i] * nd[i], d[i], s0);
-                    s1 = fma(wd[i + 1] * nd[i + 1], d[i + 1], s1);
+                    s0 = fma(wd[i] * pn[E(cb + i)], pd[E(cb + i)], s0);
+                    s1 = fma(wd[i + 1] * pn[E(cb + i + 1)], pd[E(cb + i + 1)], s1);
                 }
-                if (n & 1) s0 = fma(wd[n - 1] * nd[n - 1], d[n - 1], s0);
+                if (n & 1) s0 = fma(wd[n - 1] * pn[E(cb + n - 1)], pd[E(cb + n - 1)], s0);
             }
             double lc = s0 + s1;
             if (a.safe) {  // :2886-2893, 3018-3025
@@ -313,6 +315,7 @@ static void fill_common(b200lk_ctx *c, BranchArgs &a) {
     a.denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     a.nmix = c->d.nmix;
     a.safe = c->d.safe_numeric;
+    a.tile = c->tile;
 }
 
 static int grid_for(const b200lk_ctx *c, int G, int64_t npat) {

@@ -3,7 +3,9 @@
 // HBM layout (all private to the engine; the host sees only the C ABI):
 //   states      uint8  [ntaxa][ntot_pad]             tip state codes, taxon-major (coalesced per taxon)
 //   ptn_freq    double [ntot_pad]   ptn_invar double [ntot_pad]
-//   partial     double [nslots][ntot][block]         element (p,c,x) at p*block + c*nstates + x
+//   partial     double [nslots][ntot][block]         element (p,c,x) at elem_off(p, c*nstates + x): pattern-major
+//                                                    (tile == 1), or "T32" for the 4-state path (tile == 32):
+//                                                    32-pattern tiles, pair j of pattern l at j*64 + l*2
 //   scale       uint8  [nslots][ntot] (NORM) | [nslots][ntot][ncat_mix] (SAFE)
 //   theta_all   double [ntot][block]   buffer_scale_all double [ntot]
 //   pattern_lh  double [ntot]          pattern_lh_cat double [ntot][ncat_mix]
@@ -46,6 +48,8 @@ struct DevNode {
 struct b200lk_ctx {
     b200lk_dims d;
     int ncat_mix, block, scale_per_ptn;
+    int tile;  // HBM layout of partial vectors and theta: 1 = pattern-major, 32 = T32 (s4.cu)
+    double *h_evec, *h_inv_evec;  // host copies of the eigenvectors (kernel parameters of the 4-state path)
     int64_t ntot, ntot_pad;
     int device;
     cudaStream_t stream, own_stream;
@@ -100,6 +104,12 @@ struct b200lk_ctx {
         }                                                                                        \
     } while (0)
 
+// offset (doubles) of element e of pattern p inside one partial vector / theta
+__host__ __device__ __forceinline__ size_t elem_off(int64_t p, int e, int block, int tile) {
+    if (tile == 1) return (size_t)p * block + e;
+    return (size_t)(p >> 5) * ((size_t)32 * block) + (size_t)(e >> 1) * 64 + (size_t)(p & 31) * 2 + (e & 1);
+}
+
 static inline double *slot_partial(const b200lk_ctx *c, int s) { return c->partial + (size_t)s * c->slot_doubles; }
 static inline uint8_t *slot_scale(const b200lk_ctx *c, int s) { return c->scale + (size_t)s * c->slot_scale_bytes; }
 
@@ -121,5 +131,5 @@ int launch_derv(b200lk_ctx *c, double length);
 int launch_from_buffer(b200lk_ctx *c, double length);
 int launch_repair(b200lk_ctx *c);
 #define B200_PROG_BYTES 48  // sizeof(FNode), traverse.cu
-bool traverse4_supported(const b200lk_ctx *c, const b200lk_node *nodes, int nnodes);
-int launch_traverse4(b200lk_ctx *c, const b200lk_node *nodes, int nnodes);
+int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used);
+int launch_partial_multi(b200lk_ctx *c, int node_index);

@@ -23,7 +23,7 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->ptn_invar, sizeof(double) * c->ntot_pad));
     CUDA_TRY(c, cudaMemset(c->ptn_freq, 0, sizeof(double) * c->ntot_pad));
     CUDA_TRY(c, cudaMemset(c->ptn_invar, 0, sizeof(double) * c->ntot_pad));
-    c->slot_doubles = (size_t)c->ntot * c->block;
+    c->slot_doubles = (size_t)(c->tile == 32 ? ((c->ntot + 31) / 32) * 32 : c->ntot) * c->block;
     c->slot_scale_bytes = (((size_t)c->ntot * c->scale_per_ptn) + 15) & ~(size_t)15;
     // keep every slot 16-byte aligned for vector loads
     if (c->slot_doubles & 1) c->slot_doubles++;
@@ -52,7 +52,9 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->val, sizeof(double) * 3 * c->block));
     CUDA_TRY(c, cudaMalloc(&c->tip_val, sizeof(double) * d.n_state_codes * c->block));
     // tables for a full traversal: at most 2*(ntaxa-2)+ntaxa children
-    size_t per_child = (size_t)c->block * n + (size_t)d.n_state_codes * c->block;
+    size_t per_child = (size_t)c->block * n + c->block + (size_t)d.n_state_codes * c->block;  // echild, expv, leaf
+    c->h_evec = (double *)malloc(sizeof(double) * nmix * n * n);
+    c->h_inv_evec = (double *)malloc(sizeof(double) * nmix * n * n);
     c->children_cap = 3 * d.ntaxa + 8;
     c->nodes_cap = 2 * d.ntaxa + 8;
     c->tables_cap = per_child * c->children_cap;
@@ -68,12 +70,10 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->d_prog, c->prog_stride));
     c->h_prog = c->h_prog_ring;
     {
-        const char *e = getenv("B200LK_LEVEL_BATCHED");  // debugging/A-B switch: disable the fused traversal
-        c->force_level_batched = e && *e == '1';
         const char *sd = getenv("B200LK_STACK_DEPTH");  // test hook: force the stack-overflow path
-        c->max_stack_depth = sd ? atoi(sd) : 8;
+        c->max_stack_depth = sd ? atoi(sd) : 4;
         if (c->max_stack_depth < 0) c->max_stack_depth = 0;
-        if (c->max_stack_depth > 10) c->max_stack_depth = 10;
+        if (c->max_stack_depth > 12) c->max_stack_depth = 12;
     }
     c->h_nodes = c->h_nodes_ring;
     c->h_children = c->h_children_ring;
@@ -112,6 +112,12 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
     c->ntot = dims->nptn + dims->n_unobserved;
     c->ntot_pad = ((c->ntot + 255) / 256) * 256;  // a CTA tile of tip states never leaves its row
     if (c->ntot_pad == 0) c->ntot_pad = 256;
+    {
+        const char *e = getenv("B200LK_LEVEL_BATCHED");  // A/B switch: generic level-batched kernels only
+        c->force_level_batched = e && *e == '1';
+    }
+    // 4-state models with <= 4 categories run the pattern-stationary path on the T32 layout (s4.cu)
+    c->tile = (dims->nstates == 4 && c->ncat_mix <= 4 && !c->force_level_batched) ? 32 : 1;
     int rc = alloc_all(c);
     if (rc != B200LK_OK) {
         // keep the context alive long enough for the caller to read the message? no: report and free
@@ -137,6 +143,8 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (c->h_children_ring) cudaFreeHost(c->h_children_ring);
     if (c->h_prog_ring) cudaFreeHost(c->h_prog_ring);
     if (c->d_prog) cudaFree(c->d_prog);
+    free(c->h_evec);
+    free(c->h_inv_evec);
     for (int i = 0; i < B200_STAGE_RING; i++)
         if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
     if (c->prof_events) {
@@ -204,6 +212,8 @@ extern "C" int b200lk_set_model(b200lk_ctx *c, const double *eval, const double 
     CUDA_TRY(c, cudaMemcpyAsync(c->m.tip_partial_lh, tip_partial_lh, sizeof(double) * c->d.n_state_codes * nmix * n,
                                 cudaMemcpyHostToDevice, s));
     CUDA_TRY(c, cudaStreamSynchronize(s));  // the host arrays may be reused by the caller
+    memcpy(c->h_evec, evec, sizeof(double) * nmix * n * n);
+    memcpy(c->h_inv_evec, inv_evec, sizeof(double) * nmix * n * n);
     c->model_set = true;
     c->theta_computed = false;
     return B200LK_OK;
@@ -229,13 +239,23 @@ extern "C" int b200lk_fetch_scale_num(b200lk_ctx *c, int32_t slot, uint8_t *out)
     if (!c || !out || slot < 0 || slot >= c->d.nslots) return B200LK_ERR_ARG;
     return d2h(c, out, slot_scale(c, slot), (size_t)c->d.nptn * c->scale_per_ptn);
 }
+// device layout -> the host's pattern-major [nptn][ncat_mix][nstates]
+static int d2h_vector(b200lk_ctx *c, double *out, const double *dev) {
+    if (c->tile == 1) return d2h(c, out, dev, sizeof(double) * c->d.nptn * c->block);
+    std::vector<double> tmp(c->slot_doubles);
+    int rc = d2h(c, tmp.data(), dev, sizeof(double) * c->slot_doubles);
+    if (rc) return rc;
+    for (int64_t p = 0; p < c->d.nptn; p++)
+        for (int e = 0; e < c->block; e++) out[(size_t)p * c->block + e] = tmp[elem_off(p, e, c->block, c->tile)];
+    return B200LK_OK;
+}
 extern "C" int b200lk_fetch_partial(b200lk_ctx *c, int32_t slot, double *out) {
     if (!c || !out || slot < 0 || slot >= c->d.nslots) return B200LK_ERR_ARG;
-    return d2h(c, out, slot_partial(c, slot), sizeof(double) * c->d.nptn * c->block);
+    return d2h_vector(c, out, slot_partial(c, slot));
 }
 extern "C" int b200lk_fetch_theta(b200lk_ctx *c, double *theta, double *bscale) {
     if (!c || !theta) return B200LK_ERR_ARG;
-    int rc = d2h(c, theta, c->theta_all, sizeof(double) * c->d.nptn * c->block);
+    int rc = d2h_vector(c, theta, c->theta_all);
     if (rc == B200LK_OK && bscale) rc = d2h(c, bscale, c->buffer_scale_all, sizeof(double) * c->d.nptn);
     return rc;
 }

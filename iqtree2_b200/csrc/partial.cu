@@ -23,7 +23,7 @@ struct PartialArgs {
     uint8_t *scale;
     size_t slot_doubles, slot_scale_bytes;
     int64_t ntot, ntot_pad;
-    int node_base, n, ncm, denom, nmix, codes, PT, tables_in_smem;
+    int node_base, n, ncm, denom, nmix, codes, PT, tables_in_smem, tile;
 };
 
 __device__ __forceinline__ double dabs(double x) { return fabs(x); }
@@ -193,50 +193,50 @@ __global__ void __launch_bounds__(256) partial_kernel(PartialArgs a) {
 // one thread per pattern, the output vector doubles as scratch for the running product.
 template <bool SAFE>
 __global__ void __launch_bounds__(128) partial_multi_kernel(PartialArgs a) {
-    const int n = a.n, ncm = a.ncm, block = n * ncm, nn = n * n;
+    const int n = a.n, ncm = a.ncm, block = n * ncm, nn = n * n, tile = a.tile;
     const DevNode nd = a.nodes[a.node_base + blockIdx.y];
     const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= a.ntot) return;
-    double *all = a.partial + (size_t)nd.out_slot * a.slot_doubles + (size_t)p * block;
+    double *all = a.partial + (size_t)nd.out_slot * a.slot_doubles;  // element e of this pattern at E(e)
+#define E(e) elem_off(p, (e), block, tile)
     uint8_t *sd = a.scale + (size_t)nd.out_slot * a.slot_scale_bytes + (SAFE ? p * ncm : p);
-    for (int i = 0; i < block; i++) all[i] = 1.0;
+    for (int i = 0; i < block; i++) all[E(i)] = 1.0;
     for (int i = 0; i < (SAFE ? ncm : 1); i++) sd[i] = 0;
     const bool invar0 = a.ptn_invar[p] == 0.0;
     for (int k = 0; k < nd.nchild; k++) {
         const DevChild ch = a.children[nd.child_begin + k];
         if (ch.kind == B200LK_CHILD_LEAF) {
             const double *lf = a.tables + ch.leaf_off + (size_t)a.states[(size_t)ch.id * a.ntot_pad + p] * block;
-            for (int i = 0; i < block; i++) all[i] *= lf[i];
+            for (int i = 0; i < block; i++) all[E(i)] *= lf[i];
         } else {
-            const double *pc = a.partial + (size_t)ch.id * a.slot_doubles + (size_t)p * block;
+            const double *pc = a.partial + (size_t)ch.id * a.slot_doubles;
             const uint8_t *sc = a.scale + (size_t)ch.id * a.slot_scale_bytes;
             if (!SAFE) sd[0] += sc[p];
             const double *e = a.tables + ch.echild_off;
             for (int c = 0; c < ncm; c++) {
                 if (SAFE) sd[c] += sc[p * ncm + c];
                 for (int x = 0; x < n; x++) {
-                    double v = e[0] * pc[0];
-                    for (int i = 1; i < n; i++) v = fma(e[i], pc[i], v);
+                    double v = e[0] * pc[E(c * n)];
+                    for (int i = 1; i < n; i++) v = fma(e[i], pc[E(c * n + i)], v);
                     e += n;
-                    all[c * n + x] *= v;
+                    all[E(c * n + x)] *= v;
                 }
-                pc += n;
             }
         }
         if (SAFE) {
             for (int c = 0; c < ncm; c++) {
                 double mx = 0.0;
-                for (int x = 0; x < n; x++) mx = fmax(mx, fabs(all[c * n + x]));
+                for (int x = 0; x < n; x++) mx = fmax(mx, fabs(all[E(c * n + x)]));
                 if (mx < B200_SCALING_THRESHOLD && invar0) {
-                    for (int x = 0; x < n; x++) all[c * n + x] *= B200_TWO_256;
+                    for (int x = 0; x < n; x++) all[E(c * n + x)] *= B200_TWO_256;
                     sd[c] += 1;
                 }
             }
         } else {
             double mx = 0.0;
-            for (int x = 0; x < block; x++) mx = fmax(mx, fabs(all[x]));
+            for (int x = 0; x < block; x++) mx = fmax(mx, fabs(all[E(x)]));
             if (mx < B200_SCALING_THRESHOLD && invar0) {
-                for (int x = 0; x < block; x++) all[x] *= B200_TWO_256;
+                for (int x = 0; x < block; x++) all[E(x)] *= B200_TWO_256;
                 sd[0] += 1;
             }
         }
@@ -244,9 +244,10 @@ __global__ void __launch_bounds__(128) partial_multi_kernel(PartialArgs a) {
     double tmp[64];
     for (int c = 0; c < ncm; c++) {
         const double *M = a.inv_evec + (size_t)(c / a.denom) * nn;
-        for (int x = 0; x < n; x++) tmp[x] = all[c * n + x];
-        for (int i = 0; i < n; i++) all[c * n + i] = dotN<0>(M + i * n, tmp, n);
+        for (int x = 0; x < n; x++) tmp[x] = all[E(c * n + x)];
+        for (int i = 0; i < n; i++) all[E(c * n + i)] = dotN<0>(M + i * n, tmp, n);
     }
+#undef E
 }
 
 template <int N>
@@ -262,10 +263,7 @@ static void launch_one(PartialArgs &a, bool safe, dim3 grid, int threads, size_t
     }
 }
 
-// levels[l] = indices (into the level-sorted device node array) of the nodes of level l;
-// nodes of one level are contiguous: [base, base + count).
-int launch_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels) {
-    PartialArgs a;
+static void fill_partial_args(b200lk_ctx *c, PartialArgs &a) {
     a.nodes = c->d_nodes;
     a.children = c->d_children;
     a.tables = c->tables;
@@ -283,6 +281,32 @@ int launch_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels) 
     a.denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     a.nmix = c->d.nmix;
     a.codes = c->d.n_state_codes;
+    a.tile = c->tile;
+    a.PT = 0;
+    a.tables_in_smem = 0;
+    a.node_base = 0;
+}
+
+// one multifurcating node (index into the device node array); works on either layout
+int launch_partial_multi(b200lk_ctx *c, int node_index) {
+    PartialArgs a;
+    fill_partial_args(c, a);
+    a.node_base = node_index;
+    dim3 grid((unsigned)((c->ntot + 127) / 128), 1);
+    prof_mark(c);
+    if (c->d.safe_numeric) partial_multi_kernel<true><<<grid, 128, 0, c->stream>>>(a);
+    else partial_multi_kernel<false><<<grid, 128, 0, c->stream>>>(a);
+    prof_mark(c);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches++;
+    return B200LK_OK;
+}
+
+// levels[l] = indices (into the level-sorted device node array) of the nodes of level l;
+// nodes of one level are contiguous: [base, base + count).  Pattern-major layout only (tile == 1).
+int launch_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels) {
+    PartialArgs a;
+    fill_partial_args(c, a);
     const int n = a.n, block = c->block;
     const int threads = 256;
     a.PT = threads / a.ncm > 0 ? threads / a.ncm : 1;

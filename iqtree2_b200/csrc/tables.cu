@@ -20,6 +20,12 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
         double len_child = m.rates[c % ncat] * ch.length;
         echild[idx] = m.evec[(size_t)mm * nn + r] * exp(m.eval[mm * n + i] * len_child);
     }
+    // expv[c][i] = exp(eval[m][i] * rate * len): what the 4-state path reads per child (s4.cu)
+    double *expv = echild + (size_t)block * n;
+    for (int idx = threadIdx.x; idx < block; idx += blockDim.x) {
+        int c = idx / n, i = idx - c * n;
+        expv[idx] = exp(m.eval[(c / denom) * n + i] * (m.rates[c % ncat] * ch.length));
+    }
     if (ch.leaf_off < 0) return;
     __syncthreads();
     double *leaf = tables + ch.leaf_off;

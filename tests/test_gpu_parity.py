@@ -20,7 +20,7 @@ def both(aln, model, rates, props, **kw):
 
 @pytest.mark.parametrize("safe", [False, True])
 @pytest.mark.parametrize("nstates,ncat,nmix,ntaxa,nsite", [
-    (4, 4, 1, 12, 700), (4, 1, 1, 7, 301), (20, 4, 1, 10, 300), (20, 4, 3, 6, 120), (5, 3, 2, 9, 257),
+    (4, 4, 1, 12, 700), (4, 1, 1, 7, 301), (4, 3, 1, 9, 333), (4, 2, 2, 11, 200), (4, 2, 1, 40, 150), (20, 4, 1, 10, 300), (20, 4, 3, 6, 120), (5, 3, 2, 9, 257),
     (61, 2, 1, 5, 40),
 ])
 def test_full_evaluation_matches_oracle(oracle_lib, safe, nstates, ncat, nmix, ntaxa, nsite):
