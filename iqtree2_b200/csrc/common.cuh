@@ -49,7 +49,7 @@ struct b200lk_ctx {
     b200lk_dims d;
     int ncat_mix, block, scale_per_ptn;
     int tile;  // HBM layout of partial vectors and theta: 1 = pattern-major, 32 = T32 (s4.cu)
-    double *h_evec, *h_inv_evec;  // host copies of the eigenvectors (kernel parameters of the 4-state path)
+    double *h_evec, *h_inv_evec, *h_eval, *h_rates;  // host copies of the model (kernel parameters of the 4-state path)
     int64_t ntot, ntot_pad;
     int device;
     cudaStream_t stream, own_stream;
@@ -130,6 +130,5 @@ int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node);
 int launch_derv(b200lk_ctx *c, double length);
 int launch_from_buffer(b200lk_ctx *c, double length);
 int launch_repair(b200lk_ctx *c);
-#define B200_PROG_BYTES 48  // sizeof(FNode), traverse.cu
 int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used);
 int launch_partial_multi(b200lk_ctx *c, int node_index);

@@ -55,6 +55,8 @@ static int alloc_all(b200lk_ctx *c) {
     size_t per_child = (size_t)c->block * n + c->block + (size_t)d.n_state_codes * c->block;  // echild, expv, leaf
     c->h_evec = (double *)malloc(sizeof(double) * nmix * n * n);
     c->h_inv_evec = (double *)malloc(sizeof(double) * nmix * n * n);
+    c->h_eval = (double *)malloc(sizeof(double) * nmix * n);
+    c->h_rates = (double *)malloc(sizeof(double) * d.ncat);
     c->children_cap = 3 * d.ntaxa + 8;
     c->nodes_cap = 2 * d.ntaxa + 8;
     c->tables_cap = per_child * c->children_cap;
@@ -63,9 +65,9 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->d_children, sizeof(DevChild) * c->children_cap));
     CUDA_TRY(c, cudaMallocHost(&c->h_nodes_ring, sizeof(DevNode) * c->nodes_cap * B200_STAGE_RING));
     CUDA_TRY(c, cudaMallocHost(&c->h_children_ring, sizeof(DevChild) * c->children_cap * B200_STAGE_RING));
-    // device program of the pattern-stationary traversal: FNode[nodes_cap] then the tip-state row
-    // sequence (chunk-padded: at most one pad chunk per node plus the children themselves)
-    c->prog_stride = (size_t)B200_PROG_BYTES * c->nodes_cap + sizeof(int32_t) * ((size_t)c->children_cap + 8192);
+    // tip-state row sequence of the pattern-stationary traversal (chunk-padded: the children themselves,
+    // at most one pad row per node and one pad chunk per launch)
+    c->prog_stride = sizeof(int32_t) * (2 * (size_t)c->children_cap + 8192);
     CUDA_TRY(c, cudaMallocHost(&c->h_prog_ring, c->prog_stride * B200_STAGE_RING));
     CUDA_TRY(c, cudaMalloc(&c->d_prog, c->prog_stride));
     c->h_prog = c->h_prog_ring;
@@ -145,6 +147,8 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (c->d_prog) cudaFree(c->d_prog);
     free(c->h_evec);
     free(c->h_inv_evec);
+    free(c->h_eval);
+    free(c->h_rates);
     for (int i = 0; i < B200_STAGE_RING; i++)
         if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]);
     if (c->prof_events) {
@@ -214,6 +218,8 @@ extern "C" int b200lk_set_model(b200lk_ctx *c, const double *eval, const double 
     CUDA_TRY(c, cudaStreamSynchronize(s));  // the host arrays may be reused by the caller
     memcpy(c->h_evec, evec, sizeof(double) * nmix * n * n);
     memcpy(c->h_inv_evec, inv_evec, sizeof(double) * nmix * n * n);
+    memcpy(c->h_eval, eval, sizeof(double) * nmix * n);
+    memcpy(c->h_rates, rates, sizeof(double) * c->d.ncat);
     c->model_set = true;
     c->theta_computed = false;
     return B200LK_OK;

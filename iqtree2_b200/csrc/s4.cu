@@ -18,9 +18,9 @@
 //    pattern l sits at j*64 + l*2 doubles, so a warp's 128-bit access is one contiguous 512 B
 //    segment for every load and store (common.cuh: elem_off).
 //  * Everything that is the same for all patterns is kept OFF the L1/shared-memory data path, which is
-//    what bounds this kernel after HBM (measured: the first version sat at 94 % L1TEX throughput):
-//    eigenvectors live in kernel parameters (constant bank, read as instruction operands), and per child
-//    only expv[c][i] = exp(lambda_i r_c t) is fetched (warp-uniform loads):
+//    what bounds this kernel after HBM (measured: the first version sat at 94 % L1TEX throughput, the
+//    second waited on dependent global loads): the node program, the eigenvectors and, per child, only
+//    expv[c][i] = exp(lambda_i r_c t) are KERNEL PARAMETERS (constant bank -> uniform registers -> operands):
 //        sum_i (U[x][i] expv[c][i]) v[i]  ==  sum_i U[x][i] (expv[c][i] v[i])
 //    The reference multiplies U*expv first (echild); the association differs by rounding only (parity is
 //    judged at 1e-9; a scale count could flip only if max|x| were within ~1e-15 relative of 2^-256).
@@ -33,32 +33,44 @@
 #define SRC_GLOBAL 2  // id = slot: resident partial vector
 #define SRC_PREV 3    // the node computed immediately before (still in registers)
 
-struct FNode {
+// One node of the device program.  The program, the per-child factors expv[c][i] = exp(lambda_i r_c t)
+// and the eigenvectors travel as KERNEL PARAMETERS: they sit in the constant bank, are read through the
+// uniform datapath (LDCU -> uniform registers -> operands of DFMA/DMUL) and never touch L1, shared
+// memory or a vector register.  A launch carries at most S4_MAXN nodes (parameter space is 32 KB).
+template <int NCM>
+struct PNode {
     int32_t out_slot;
-    int32_t out_stack;   // stack entry to push to, -1 = none
-    int32_t lk, lid, rk, rid;
-    int32_t ltab, rtab;  // table offset (doubles): leaf table for SRC_LEAF, expv otherwise
-    int32_t refill;      // >= 0: before this node, stage chunk `refill` of the tip-state rows
-    int32_t pad[3];
+    int32_t info;        // lk | rk << 2 | (out_stack + 1) << 4 | (refill + 1) << 12
+    int32_t lid, rid;    // SRC_LEAF: row in the staged chunk; SRC_STACK: entry; SRC_GLOBAL: slot
+    int32_t ltab, rtab;  // SRC_LEAF: offset (doubles) of the child's leaf lookup table in `tables`
+    int32_t pad[2];
+    double lexp[NCM * 4], rexp[NCM * 4];
 };
-static_assert(sizeof(FNode) == B200_PROG_BYTES, "B200_PROG_BYTES must equal sizeof(FNode)");
 
 template <int NCM>
-struct S4Model {        // per category: eigenvectors of its mixture class, passed by value (constant bank)
+struct S4Model {        // per category: eigenvectors of its mixture class
     double U[NCM][16];  // evec[x][i]
     double M[NCM][16];  // inv_evec[i][x]
 };
 
 struct TravArgs {
-    const FNode *prog;
-    const int32_t *leaf_seq;
+    const int32_t *leaf_seq;  // taxon of every staged tip-state row, in order of use, chunk-padded
     const double *tables, *ptn_invar;
     const uint8_t *states;
     double *partial;
     uint8_t *scale;
     size_t slot_doubles, slot_scale_bytes;
     int64_t ntot, ntot_pad;
-    int nnodes, depth, chunk;
+    int nnodes, depth, chunk, pad;
+};
+
+#define S4_PARAM_BYTES 32000
+template <int NCM>
+struct S4Launch {
+    static constexpr int MAXN = (S4_PARAM_BYTES - (int)sizeof(S4Model<NCM>) - (int)sizeof(TravArgs)) / (int)sizeof(PNode<NCM>);
+    TravArgs a;
+    S4Model<NCM> mdl;
+    PNode<NCM> nodes[MAXN];
 };
 
 #define S4_THREADS 128
@@ -76,13 +88,12 @@ __device__ __forceinline__ unsigned long long abs_bits(double x) {
     return (unsigned long long)__double_as_longlong(x) & 0x7fffffffffffffffull;
 }
 
-// One child of one node -> its factor f[c*4+x] for every category.  `sc` accumulates the child's scale
-// counter(s): NORM one integer, SAFE four bytes packed (UBYTE arithmetic per category).
-template <int NCM, bool SAFE, bool PLAIN>
-__device__ __forceinline__ void child_factor(const TravArgs &a, const S4Model<NCM> &mdl, int kind, int id, int tab,
-                                             const double *prev, unsigned prev_sc, const double2 *stk,
-                                             const unsigned *stk_sc, const uint8_t *st_buf, int tid, size_t poff,
-                                             int64_t p, double *f, unsigned &sc) {
+// raw operand of one child: the leaf-table row (SRC_LEAF, already the factor) or the child's partial vector
+template <int NCM, bool SAFE>
+__device__ __forceinline__ void child_load(const TravArgs &a, int kind, int id, int tab, const double *prev,
+                                           unsigned prev_sc, const double2 *stk, const unsigned *stk_sc,
+                                           const uint8_t *st_buf, int tid, size_t poff, int64_t p, double *v,
+                                           unsigned &sc) {
     constexpr int BLOCK = NCM * 4;
     if (kind == SRC_LEAF) {
         const int st = st_buf[id * S4_THREADS + tid];
@@ -90,12 +101,11 @@ __device__ __forceinline__ void child_factor(const TravArgs &a, const S4Model<NC
 #pragma unroll
         for (int j = 0; j < BLOCK / 2; j++) {
             const double2 u = __ldg(lf + j);
-            f[2 * j] = u.x;
-            f[2 * j + 1] = u.y;
+            v[2 * j] = u.x;
+            v[2 * j + 1] = u.y;
         }
         return;
     }
-    double v[BLOCK];
     unsigned s;
     if (kind == SRC_PREV) {
 #pragma unroll
@@ -127,24 +137,27 @@ __device__ __forceinline__ void child_factor(const TravArgs &a, const S4Model<NC
         }
     }
     sc = SAFE ? __vadd4(sc, s) : sc + s;
-    const double2 *ev = reinterpret_cast<const double2 *>(a.tables + tab);  // expv[c][i], same address in every lane
+}
+
+// internal child: v <- U (expv (.) v) per category, in place
+template <int NCM, bool PLAIN>
+__device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const double *ev, double *v) {
 #pragma unroll
     for (int c = 0; c < NCM; c++) {
-        const double2 e0 = __ldg(ev + 2 * c), e1 = __ldg(ev + 2 * c + 1);
-        double w[4];
-        w[0] = __dmul_rn(e0.x, v[c * 4]);
-        w[1] = __dmul_rn(e0.y, v[c * 4 + 1]);
-        w[2] = __dmul_rn(e1.x, v[c * 4 + 2]);
-        w[3] = __dmul_rn(e1.y, v[c * 4 + 3]);
+        double w[4], f[4];
 #pragma unroll
-        for (int x = 0; x < 4; x++)
-            f[c * 4 + x] = PLAIN ? s4_plain(&mdl.U[c][4 * x], w) : s4_tree(&mdl.U[c][4 * x], w);
+        for (int i = 0; i < 4; i++) w[i] = __dmul_rn(ev[c * 4 + i], v[c * 4 + i]);
+#pragma unroll
+        for (int x = 0; x < 4; x++) f[x] = PLAIN ? s4_plain(&mdl.U[c][4 * x], w) : s4_tree(&mdl.U[c][4 * x], w);
+#pragma unroll
+        for (int x = 0; x < 4; x++) v[c * 4 + x] = f[x];
     }
 }
 
 template <int NCM, bool SAFE>
-__global__ void __launch_bounds__(S4_THREADS, 3) s4_traverse_kernel(const TravArgs a, const S4Model<NCM> mdl) {
+__global__ void __launch_bounds__(S4_THREADS, 3) s4_traverse_kernel(const __grid_constant__ S4Launch<NCM> P) {
     constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
+    const TravArgs &a = P.a;
     // [depth][PAIRS][S4_THREADS] double2 | unsigned [depth][S4_THREADS] scale | uint8 [chunk][S4_THREADS] tip states
     extern __shared__ double2 stk[];
     unsigned *stk_sc = reinterpret_cast<unsigned *>(stk + (size_t)a.depth * PAIRS * S4_THREADS);
@@ -162,13 +175,15 @@ __global__ void __launch_bounds__(S4_THREADS, 3) s4_traverse_kernel(const TravAr
     unsigned prev_sc = 0;
 
     for (int i = 0; i < a.nnodes; i++) {
-        const FNode nd = a.prog[i];  // the same address in every thread
-        if (nd.refill >= 0) {
+        const PNode<NCM> &nd = P.nodes[i];  // constant bank, uniform index
+        const int info = nd.info;
+        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 12) - 1;
+        if (refill >= 0) {
             // stage the next chunk of tip-state rows of this CTA's pattern tile: all loads in flight at once
             __syncthreads();
             constexpr int VPR = S4_THREADS / 16;
             const int nvec = a.chunk * VPR;
-            const int32_t *seq = a.leaf_seq + (size_t)nd.refill * a.chunk;
+            const int32_t *seq = a.leaf_seq + (size_t)refill * a.chunk;
             for (int v = tid; v < nvec; v += S4_THREADS) {
                 const int row = v / VPR, q = v - row * VPR;
                 const uint4 *src = reinterpret_cast<const uint4 *>(a.states + (size_t)seq[row] * a.ntot_pad + p0) + q;
@@ -176,18 +191,18 @@ __global__ void __launch_bounds__(S4_THREADS, 3) s4_traverse_kernel(const TravAr
             }
             __syncthreads();
         }
+        // both children's operands are requested before either is used: one memory latency per node
         double l[BLOCK], r[BLOCK];
         unsigned sc = 0;
-        child_factor<NCM, SAFE, false>(a, mdl, nd.lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff,
-                                       p, l, sc);
-        if (nd.lk == SRC_LEAF)  // tip-internal: dotProductVec for the internal child (:1853)
-            child_factor<NCM, SAFE, true>(a, mdl, nd.rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid,
-                                          poff, p, r, sc);
-        else                    // internal-internal: dotProductDualVec (:1975-1983)
-            child_factor<NCM, SAFE, false>(a, mdl, nd.rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid,
-                                           poff, p, r, sc);
+        child_load<NCM, SAFE>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
+        child_load<NCM, SAFE>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
+        if (lk != SRC_LEAF) child_apply<NCM, false>(P.mdl, nd.lexp, l);
+        if (rk != SRC_LEAF) {
+            if (lk == SRC_LEAF) child_apply<NCM, true>(P.mdl, nd.rexp, r);   // tip-internal: dotProductVec (:1853)
+            else child_apply<NCM, false>(P.mdl, nd.rexp, r);                 // internal-internal (:1975-1983)
+        }
         // ---- product, back to eigen-space (productVecMat), rescale --------------------------------
-        const bool tiptip = nd.lk == SRC_LEAF && nd.rk == SRC_LEAF;
+        const bool tiptip = lk == SRC_LEAF && rk == SRC_LEAF;
         unsigned long long mxall = 0ull;
 #pragma unroll
         for (int c = 0; c < NCM; c++) {
@@ -197,7 +212,7 @@ __global__ void __launch_bounds__(S4_THREADS, 3) s4_traverse_kernel(const TravAr
             unsigned long long mx = 0ull;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-                const double o = s4_tree(&mdl.M[c][4 * k], tmp);
+                const double o = s4_tree(&P.mdl.M[c][4 * k], tmp);
                 prev[c * 4 + k] = o;
                 const unsigned long long b = abs_bits(o);  // |x| order == unsigned order of the bit pattern
                 mx = b > mx ? b : mx;
@@ -233,18 +248,16 @@ __global__ void __launch_bounds__(S4_THREADS, 3) s4_traverse_kernel(const TravAr
                 gs[p] = (uint8_t)sc;
             }
         }
-        if (nd.out_stack >= 0) {
+        if (out_stack >= 0) {
 #pragma unroll
             for (int j = 0; j < PAIRS; j++)
-                stk[(nd.out_stack * PAIRS + j) * S4_THREADS + tid] = make_double2(prev[2 * j], prev[2 * j + 1]);
-            stk_sc[nd.out_stack * S4_THREADS + tid] = sc;
+                stk[(out_stack * PAIRS + j) * S4_THREADS + tid] = make_double2(prev[2 * j], prev[2 * j + 1]);
+            stk_sc[out_stack * S4_THREADS + tid] = sc;
         }
     }
 }
 
 // ---- host side -------------------------------------------------------------------------------------------
-bool s4_layout(const b200lk_ctx *c) { return c->tile == 32; }
-
 template <int NCM>
 static void fill_model(const b200lk_ctx *c, S4Model<NCM> &m) {
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
@@ -255,29 +268,28 @@ static void fill_model(const b200lk_ctx *c, S4Model<NCM> &m) {
     }
 }
 
+// expv[c][i] = exp(eval[m][i] * rate[c % ncat] * len), the factor of computePartialInfo (:1016-1031)
 template <int NCM>
-static cudaError_t launch_trav(b200lk_ctx *c, const TravArgs &a, unsigned grid, size_t smem) {
-    S4Model<NCM> m;
-    fill_model<NCM>(c, m);
-    if (!c->trav_attr_set) {
-        cudaFuncSetAttribute(s4_traverse_kernel<NCM, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-        cudaFuncSetAttribute(s4_traverse_kernel<NCM, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-        c->trav_attr_set = true;
+static void fill_expv(const b200lk_ctx *c, double len, double *ev) {
+    const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
+    for (int cc = 0; cc < NCM; cc++) {
+        const double len_child = c->h_rates[cc % c->d.ncat] * len;
+        for (int i = 0; i < 4; i++) ev[cc * 4 + i] = exp(c->h_eval[(cc / denom) * 4 + i] * len_child);
     }
-    if (c->d.safe_numeric) s4_traverse_kernel<NCM, true><<<grid, S4_THREADS, smem, c->stream>>>(a, m);
-    else s4_traverse_kernel<NCM, false><<<grid, S4_THREADS, smem, c->stream>>>(a, m);
-    return cudaGetLastError();
 }
 
-// Build the device program for nodes [first, first+count) of the host's post-order list (all bifurcating;
-// children already carry table offsets in c->h_children) and launch.  Stack entries are handed out on the
-// host: a value goes to the stack when a later node of this run consumes it and it is not simply the next
-// node's operand; when the stack is full the consumer re-reads the resident copy instead.
-int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used) {
+// One launch: nodes [first, first + count) of the host's post-order list, all bifurcating, count <= MAXN.
+// Stack entries are handed out here: a value goes to the stack when a later node of this launch consumes
+// it and it is not simply the next node's operand; when the stack is full (or the consumer is in a later
+// launch) the consumer re-reads the resident copy instead.
+template <int NCM>
+static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *seq_used) {
+    static thread_local S4Launch<NCM> *Lp = nullptr;  // 32 KB of launch parameters, one per host thread
+    if (!Lp) Lp = new S4Launch<NCM>();
+    S4Launch<NCM> &P = *Lp;
     const int nslots = c->d.nslots;
     const int max_depth = c->max_stack_depth;
-    const b200lk_node *nl = nodes + first;
-    std::vector<int> producer(nslots, -1);  // slot -> index of the node of this run that last wrote it
+    std::vector<int> producer(nslots, -1);  // slot -> index of the node of this launch that last wrote it
     std::vector<int> consumer(count, -1);   // node -> index of the node that consumes its output
     for (int i = 0; i < count; i++) {
         for (int k = 0; k < 2; k++) {
@@ -292,13 +304,11 @@ int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int c
     std::vector<int> free_list;
     for (int e = max_depth - 1; e >= 0; e--) free_list.push_back(e);
     int depth_used = 0;
-    FNode *prog = reinterpret_cast<FNode *>(c->h_prog) + *prog_used;
-    int32_t *leaf_seq = reinterpret_cast<int32_t *>((char *)c->h_prog + (size_t)B200_PROG_BYTES * c->nodes_cap) + *seq_used;
+    int32_t *leaf_seq = reinterpret_cast<int32_t *>(c->h_prog) + *seq_used;
     const int chunk = S4_STATE_BYTES / S4_THREADS;
-    const int block = c->block, n = 4;
     int nseq = 0;
     for (int i = 0; i < count; i++) {
-        FNode f;
+        PNode<NCM> &f = P.nodes[i];
         memset(&f, 0, sizeof(f));
         f.out_slot = nl[i].out_slot;
         int kind[2], id[2], tab[2];
@@ -309,19 +319,20 @@ int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int c
         }
         int nleaf = 0;
         for (int k = 0; k < 2; k++) nleaf += c->h_children[nl[i].child_begin + k].kind == B200LK_CHILD_LEAF;
-        f.refill = -1;
+        int refill = -1;
         if (nleaf) {  // tip-state rows are staged chunk by chunk in order of use; a node never straddles
             if (nseq % chunk + nleaf > chunk)
                 while (nseq % chunk) leaf_seq[nseq++] = 0;
-            if (nseq % chunk == 0) f.refill = nseq / chunk;
+            if (nseq % chunk == 0) refill = nseq / chunk;
         }
         for (int k = 0; k < 2; k++) {
             const DevChild &ch = c->h_children[nl[i].child_begin + order[k]];
+            tab[k] = 0;
             if (ch.kind == B200LK_CHILD_LEAF) {
                 kind[k] = SRC_LEAF; id[k] = nseq % chunk; tab[k] = (int)ch.leaf_off;
                 leaf_seq[nseq++] = ch.id;
             } else {
-                tab[k] = (int)ch.echild_off + block * n;  // expv follows echild
+                fill_expv<NCM>(c, ch.length, k == 0 ? f.lexp : f.rexp);
                 const int pr = producer[ch.id];
                 if (pr >= 0 && consumer[pr] == i && pr == i - 1) {
                     kind[k] = SRC_PREV; id[k] = 0;
@@ -334,29 +345,25 @@ int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int c
                 }
             }
         }
-        f.lk = kind[0]; f.lid = id[0]; f.ltab = tab[0];
-        f.rk = kind[1]; f.rid = id[1]; f.rtab = tab[1];
-        f.out_stack = -1;
+        f.lid = id[0]; f.ltab = tab[0];
+        f.rid = id[1]; f.rtab = tab[1];
+        int out_stack = -1;
         if (consumer[i] >= 0 && consumer[i] != i + 1 && !free_list.empty()) {
-            f.out_stack = free_list.back();
+            out_stack = free_list.back();
             free_list.pop_back();
-            entry_of[i] = f.out_stack;
-            depth_used = std::max(depth_used, f.out_stack + 1);
+            entry_of[i] = out_stack;
+            depth_used = std::max(depth_used, out_stack + 1);
         }
+        f.info = kind[0] | kind[1] << 2 | (out_stack + 1) << 4 | (refill + 1) << 12;
         producer[nl[i].out_slot] = i;
-        prog[i] = f;
     }
     while (nseq % chunk) leaf_seq[nseq++] = 0;  // a refill always reads a whole chunk of rows
-    char *d_prog = (char *)c->d_prog + sizeof(FNode) * (size_t)*prog_used;
-    char *d_seq = (char *)c->d_prog + (size_t)B200_PROG_BYTES * c->nodes_cap + sizeof(int32_t) * (size_t)*seq_used;
-    CUDA_TRY(c, cudaMemcpyAsync(d_prog, prog, sizeof(FNode) * count, cudaMemcpyHostToDevice, c->stream));
+    int32_t *d_seq = reinterpret_cast<int32_t *>(c->d_prog) + *seq_used;
     if (nseq)
         CUDA_TRY(c, cudaMemcpyAsync(d_seq, leaf_seq, sizeof(int32_t) * nseq, cudaMemcpyHostToDevice, c->stream));
-    *prog_used += count;
     *seq_used += nseq;
-    TravArgs a;
-    a.prog = reinterpret_cast<const FNode *>(d_prog);
-    a.leaf_seq = reinterpret_cast<const int32_t *>(d_seq);
+    TravArgs &a = P.a;
+    a.leaf_seq = d_seq;
     a.tables = c->tables;
     a.ptn_invar = c->ptn_invar;
     a.states = c->states;
@@ -369,19 +376,43 @@ int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int c
     a.nnodes = count;
     a.depth = depth_used;
     a.chunk = chunk;
-    const int ncm = c->ncat_mix;
-    const size_t smem = (size_t)depth_used * S4_THREADS * (2 * ncm * sizeof(double2) + sizeof(unsigned)) + S4_STATE_BYTES;
+    a.pad = 0;
+    fill_model<NCM>(c, P.mdl);
+    const size_t smem = (size_t)depth_used * S4_THREADS * (2 * NCM * sizeof(double2) + sizeof(unsigned)) + S4_STATE_BYTES;
     const unsigned grid = (unsigned)((c->ntot + S4_THREADS - 1) / S4_THREADS);
-    prof_mark(c);
-    cudaError_t e;
-    switch (ncm) {
-        case 1: e = launch_trav<1>(c, a, grid, smem); break;
-        case 2: e = launch_trav<2>(c, a, grid, smem); break;
-        case 3: e = launch_trav<3>(c, a, grid, smem); break;
-        default: e = launch_trav<4>(c, a, grid, smem); break;
+    if (!c->trav_attr_set) {
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        c->trav_attr_set = true;
     }
     prof_mark(c);
-    CUDA_TRY(c, e);
+    if (c->d.safe_numeric) s4_traverse_kernel<NCM, true><<<grid, S4_THREADS, smem, c->stream>>>(P);
+    else s4_traverse_kernel<NCM, false><<<grid, S4_THREADS, smem, c->stream>>>(P);
+    prof_mark(c);
+    CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
     return B200LK_OK;
+}
+
+template <int NCM>
+static int launch_run(b200lk_ctx *c, const b200lk_node *nl, int count, int *seq_used) {
+    for (int done = 0; done < count;) {
+        const int seg = std::min(count - done, (int)S4Launch<NCM>::MAXN);
+        int rc = launch_segment<NCM>(c, nl + done, seg, seq_used);
+        if (rc) return rc;
+        done += seg;
+    }
+    return B200LK_OK;
+}
+
+// nodes [first, first + count) of the host's post-order list, all bifurcating (children already carry their
+// leaf-table offsets in c->h_children)
+int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used) {
+    (void)prog_used;
+    switch (c->ncat_mix) {
+        case 1: return launch_run<1>(c, nodes + first, count, seq_used);
+        case 2: return launch_run<2>(c, nodes + first, count, seq_used);
+        case 3: return launch_run<3>(c, nodes + first, count, seq_used);
+        default: return launch_run<4>(c, nodes + first, count, seq_used);
+    }
 }
