@@ -155,7 +155,7 @@ __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const doubl
 }
 
 template <int NCM, bool SAFE>
-__global__ void __launch_bounds__(S4_THREADS, 3) s4_traverse_kernel(const __grid_constant__ S4Launch<NCM> P) {
+__global__ void __launch_bounds__(S4_THREADS, 4) s4_traverse_kernel(const __grid_constant__ S4Launch<NCM> P) {
     constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
     const TravArgs &a = P.a;
     // [depth][PAIRS][S4_THREADS] double2 | unsigned [depth][S4_THREADS] scale | uint8 [chunk][S4_THREADS] tip states
