@@ -35,3 +35,101 @@ def set_ref_quirks(on: bool) -> None:
     if not os.path.exists(ORACLE_LIB):
         build(with_ref=False)
     ctypes.CDLL(ORACLE_LIB).orc_set_ref_quirks(int(bool(on)))
+
+
+# ---- the reference's own kernels (oracle/_ref, built by Makefile.ref where /root/reference exists) ----------
+LK_SSE2, LK_AVX, LK_AVX_FMA = 2, 7, 8   # enum LikelihoodKernel, utils/tools.h:526-528
+
+
+def ref_available() -> bool:
+    return os.path.exists(REF_LIB)
+
+
+class RefRun:
+    """One PhyloTree of the reference with caller-supplied alignment, tree, eigen-system and rates
+    (ref_harness.cpp).  kernel: LK_SSE2 (Vec2d), LK_AVX (Vec4d), LK_AVX_FMA (Vec4d + FMA)."""
+
+    def __init__(self, tree, aln, model, rates, props, *, kernel=LK_AVX_FMA, safe=False, threads=1, p_invar=0.0):
+        import ctypes as C
+        import numpy as np
+        from iqtree2_b200 import workload as W
+        if not ref_available():
+            raise RuntimeError("oracle/_ref/libiqtree_ref.so is not built (needs /root/reference)")
+        self.C, self.np = C, np
+        self.lib = C.CDLL(REF_LIB)
+
+        class Problem(C.Structure):
+            _fields_ = [(k, C.c_int32) for k in ("ntaxa", "nstates", "ncat", "nmix", "n_state_codes", "kernel",
+                                                 "safe", "threads")] + \
+                       [("nptn", C.c_int64), ("states", C.c_void_p), ("ptn_freq", C.c_void_p),
+                        ("newick", C.c_char_p), ("tipvec", C.c_void_p), ("rates", C.c_void_p),
+                        ("props", C.c_void_p), ("pinvar", C.c_double), ("eval", C.c_void_p), ("evec", C.c_void_p),
+                        ("inv_evec", C.c_void_p), ("mixw", C.c_void_p), ("freqs", C.c_void_p)]
+        names = ["T%d" % i for i in range(tree.ntaxa)]
+        old = tree.names
+        tree.names = names
+        newick = tree.to_newick(0, digits=17).encode()
+        tree.names = old
+        f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        scale = 1.0 - p_invar
+        self._keep = [np.ascontiguousarray(aln.states, dtype=np.uint8), f64(aln.ptn_freq),
+                      f64(W.state_indicators(aln.nstates)), f64(rates), f64(np.asarray(props) * scale),
+                      f64(model.eval), f64(model.evec), f64(model.inv_evec), f64(model.mixw), f64(model.freqs)]
+        k = self._keep
+        ptr = lambda a: a.ctypes.data
+        pb = Problem(aln.ntaxa, aln.nstates, len(rates), model.nmix, aln.state_unknown + 1, kernel, int(safe),
+                     threads, aln.nptn, ptr(k[0]), ptr(k[1]), newick, ptr(k[2]), ptr(k[3]), ptr(k[4]), p_invar,
+                     ptr(k[5]), ptr(k[6]), ptr(k[7]), ptr(k[8]), ptr(k[9]))
+        self.lib.ref_create.restype = C.c_void_p
+        self.h = C.c_void_p(self.lib.ref_create(C.byref(pb)))
+        self.nptn, self.ncm, self.n = aln.nptn, len(rates) * model.nmix, aln.nstates
+        self.tree = tree
+        for fn in ("ref_lnl_at_leaf", "ref_lnl_again", "ref_from_buffer", "ref_optimize_current_branch"):
+            getattr(self.lib, fn).restype = C.c_double
+        self.safe_numeric = bool(self.lib.ref_safe_numeric(self.h))
+        self.vector_size = self.lib.ref_vector_size(self.h)
+
+    def lnl_at_leaf(self, taxon):
+        return self.lib.ref_lnl_at_leaf(self.h, taxon)
+
+    def derv(self, again=False):
+        C = self.C
+        df, ddf = C.c_double(), C.c_double()
+        (self.lib.ref_derv_again if again else self.lib.ref_derv)(self.h, C.byref(df), C.byref(ddf))
+        return df.value, ddf.value
+
+    def set_current_length(self, t):
+        self.lib.ref_set_current_length(self.h, self.C.c_double(t))
+
+    def from_buffer(self):
+        return self.lib.ref_from_buffer(self.h)
+
+    def optimize_current_branch(self, max_steps=100):
+        return self.lib.ref_optimize_current_branch(self.h, max_steps)
+
+    def pattern_lh(self):
+        out = self.np.empty(self.nptn)
+        self.lib.ref_pattern_lh(self.h, out.ctypes.data_as(self.C.c_void_p))
+        return out
+
+    def pattern_lh_cat(self):
+        out = self.np.empty((self.nptn, self.ncm))
+        self.lib.ref_pattern_lh_cat(self.h, out.ctypes.data_as(self.C.c_void_p))
+        return out
+
+    def fetch_branch(self, leaves, from_taxon):
+        """(partial [nptn][ncm][n], scale) of the directed branch whose subtree has exactly `leaves`."""
+        np, C = self.np, self.C
+        ls = np.ascontiguousarray(sorted(leaves), dtype=np.int32)
+        part = np.empty((self.nptn, self.ncm, self.n))
+        sc = np.empty((self.nptn, self.ncm) if self.safe_numeric else (self.nptn,), dtype=np.uint8)
+        rc = self.lib.ref_fetch_branch(self.h, ls.ctypes.data_as(C.c_void_p), len(ls), from_taxon,
+                                       part.ctypes.data_as(C.c_void_p), sc.ctypes.data_as(C.c_void_p))
+        if rc:
+            raise RuntimeError("ref_fetch_branch failed (%d)" % rc)
+        return part, sc
+
+    def close(self):
+        if self.h:
+            self.lib.ref_destroy(self.h)
+            self.h = None

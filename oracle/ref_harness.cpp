@@ -1,0 +1,398 @@
+// ref_harness.cpp -- drives the REFERENCE's own likelihood kernels (TEST INFRASTRUCTURE ONLY).
+//
+// oracle/Makefile.ref compiles, unmodified and in place from /root/reference, the translation units
+//   tree/phylokernelsse.cpp, tree/phylotreeavx.cpp, tree/phylokernelfma.cpp     (the SIMD kernel instantiations
+//                                                                               of tree/phylokernelnew.h)
+//   tree/phylotreesse.cpp (setLikelihoodKernel, computeTipPartialLikelihood, computePtnInvar/Freq, wrappers)
+//   tree/phylotree.cpp (buffers, computeTraversalInfo, optimizeOneBranch ...), tree/mtree.cpp, tree/node.cpp,
+//   tree/phylonode.cpp, tree/memslot.cpp, utils/optimization.cpp, utils/tools.cpp, utils/checkpoint.cpp,
+//   utils/MPIHelper.cpp, utils/progress.cpp, model/modelsubst.cpp, model/rateheterogeneity.cpp,
+//   alignment/pattern.cpp
+// and links them with THIS file into oracle/_ref/libiqtree_ref.so.  Nothing of the reference is copied.
+//
+// What this file supplies is the scaffolding the kernels read their inputs through, because the reference's
+// own producers cannot be built here (alignment/alignment.cpp and model/modelmarkov.cpp need Eigen3/Boost,
+// which are not installed): minimal bodies for the few Alignment / ModelFactory / StateSpace members the
+// path touches, and ModelSubst / RateHeterogeneity subclasses that hand the kernels a caller-supplied
+// eigen-system and rate categories through the reference's virtual interface
+// (model/modelsubst.h:360-372, model/rateheterogeneity.h:107-172).  Every other unresolved symbol of the
+// reference objects is an auto-generated trap (oracle/gen_ref_stubs.py): reaching one aborts loudly.
+#include <sstream>
+#include <string>
+#include <vector>
+#include <algorithm>
+#include <cstring>
+
+// the harness reads kernel-private buffers (_pattern_lh, partial_lh, scale_num, current_it): open the
+// access specifiers for THIS translation unit only (object layout is unaffected)
+#define private public
+#define protected public
+#include "tree/phylotree.h"
+#include "tree/phylonode.h"
+#include "model/modelsubst.h"
+#include "model/rateheterogeneity.h"
+#include "model/modelfactory.h"
+#include "alignment/alignment.h"
+#include "utils/tools.h"
+#include "utils/starttree.h"
+#undef private
+#undef protected
+
+int NNI_MAX_NR_STEP = 10;  // tree/phylotree.cpp global defined in main/phyloanalysis.cpp (off the path)
+
+// parseArg() asks for this default (utils/tools.cpp:1362); the distance-tree builders are off the path
+const std::string &StartTree::Factory::getNameOfDefaultTreeBuilder() {
+    static const std::string name = "none";
+    return name;
+}
+
+// ---- minimal bodies for members whose translation units cannot be built here ------------------------------
+PML::StateSpace::StateSpace() : space_name(), num_states(0), num_all_states(0) {}
+PML::StateSpace::~StateSpace() {}
+
+Alignment::Alignment() : vector<Pattern>() {
+    num_states = 0;
+    frac_const_sites = 0.0;
+    frac_invariant_sites = 0.0;
+    codon_table = NULL;
+    genetic_code = NULL;
+    non_stop_codon = NULL;
+    seq_type = SEQ_UNKNOWN;
+    STATE_UNKNOWN = 126;
+    pars_lower_bound = NULL;
+}
+Alignment::~Alignment() {}
+string &Alignment::getSeqName(int i) { return seq_names[i]; }
+vector<string> &Alignment::getSeqNames() { return seq_names; }
+int Alignment::getSeqID(string &seq_name) {
+    for (size_t i = 0; i < seq_names.size(); i++)
+        if (seq_names[i] == seq_name) return (int)i;
+    return -1;
+}
+
+ModelFactory::ModelFactory() : CheckpointFactory() {
+    model = NULL;
+    site_rate = NULL;
+    store_trans_matrix = false;
+    is_storing = false;
+    joint_optimize = false;
+    fused_mix_rate = false;
+    ASC_type = ASC_NONE;
+}
+ModelFactory::~ModelFactory() {}
+void ModelFactory::setCheckpoint(Checkpoint *checkpoint) { CheckpointFactory::setCheckpoint(checkpoint); }
+
+// ---- caller-supplied model and rates behind the reference's virtual interface -----------------------------
+class HarnessModel : public ModelSubst {
+public:
+    int nmix;
+    // the kernels read the eigen-system with aligned SIMD loads (tree/phylokernelnew.h:1019-1026): 64-byte aligned
+    double *eval, *evec, *inv_evec;
+    std::vector<double> mixw, freqs, tipvec;  // tipvec[code][x]
+    int ncodes;
+    static double *aligned_copy(const double *src, size_t count) {
+        void *p = NULL;
+        if (posix_memalign(&p, 64, sizeof(double) * (count + 8))) return NULL;
+        memcpy(p, src, sizeof(double) * count);
+        return (double *)p;
+    }
+    HarnessModel(int n, int nmix_) : ModelSubst(n), nmix(nmix_), eval(NULL), evec(NULL), inv_evec(NULL), ncodes(0) {}
+    virtual ~HarnessModel() { free(eval); free(evec); free(inv_evec); }
+    virtual bool isReversible() { return true; }
+    virtual bool isMixture() { return nmix > 1; }
+    virtual int getNMixtures() { return nmix; }
+    virtual double getMixtureWeight(int cat) { return mixw[cat]; }
+    virtual double *getEigenvalues() const { return eval; }
+    virtual double *getEigenvectors() const { return evec; }
+    virtual double *getInverseEigenvectors() const { return inv_evec; }
+    virtual void getStateFrequency(double *f, int mixture = 0) {
+        for (int i = 0; i < num_states; i++) {
+            if (mixture >= 0) {
+                f[i] = freqs[(size_t)mixture * num_states + i];
+            } else {  // -1: the weighted average over classes (computePtnInvar, tree/phylotreesse.cpp:570)
+                f[i] = 0.0;
+                for (int m = 0; m < nmix; m++) f[i] += mixw[m] * freqs[(size_t)m * num_states + i];
+            }
+        }
+    }
+    // the 0/1 indicator of a state code, ambiguity codes included (input data)
+    virtual void computeTipLikelihood(PML::StateType state, double *state_lk) {
+        for (int i = 0; i < num_states; i++) state_lk[i] = tipvec[(size_t)state * num_states + i];
+    }
+};
+
+class HarnessRate : public RateHeterogeneity {
+public:
+    std::vector<double> rates, props;
+    double pinvar;
+    HarnessRate() : RateHeterogeneity(), pinvar(0.0) {}
+    virtual int getNRate() { return (int)rates.size(); }
+    virtual int getNDiscreteRate() { return (int)rates.size(); }
+    virtual double getRate(int c) { return rates[c]; }
+    virtual double getProp(int c) { return props[c]; }
+    virtual double getPInvar() { return pinvar; }
+    virtual int isGammaRate() { return 0; }
+};
+
+struct RefHandle {
+    PhyloTree *tree;
+    Alignment *aln;
+    HarnessModel *model;
+    HarnessRate *rate;
+    ModelFactory *factory;
+    PhyloNeighbor *cur_dad_branch;
+    PhyloNode *cur_dad;
+    int ncm, block;
+};
+
+extern "C" {
+
+struct ref_problem {
+    int32_t ntaxa, nstates, ncat, nmix, n_state_codes, kernel, safe, threads;
+    int64_t nptn;
+    const uint8_t *states;      // [ntaxa][nptn]
+    const double *ptn_freq;     // [nptn] (integers)
+    const char *newick;         // leaves named T<taxon>
+    const double *tipvec;       // [n_state_codes][nstates]
+    const double *rates, *props;
+    double pinvar;
+    const double *eval, *evec, *inv_evec, *mixw, *freqs;
+};
+
+static bool params_ready = false;
+
+#include <execinfo.h>
+#include <signal.h>
+#include <unistd.h>
+static void segv_backtrace(int sig) {  // debugging aid: REF_HARNESS_BACKTRACE=1
+    void *frames[64];
+    int n = backtrace(frames, 64);
+    backtrace_symbols_fd(frames, n, 2);
+    _exit(139);
+}
+
+void *ref_create(const ref_problem *pb) {
+    if (getenv("REF_HARNESS_BACKTRACE")) signal(SIGSEGV, segv_backtrace);
+    if (!params_ready) {
+        const char *argv[] = {"iqtree2", "-s", "harness", NULL};
+        parseArg(3, const_cast<char **>(argv), Params::getInstance());  // the reference's own defaults
+        params_ready = true;
+    }
+    Params &params = Params::getInstance();
+    params.lk_safe_scaling = pb->safe != 0;
+    RefHandle *h = new RefHandle();
+    const int n = pb->nstates;
+    // alignment: pattern-major vector<Pattern>, aln->at(ptn)[taxon] (alignment/pattern.h:29)
+    Alignment *aln = new Alignment();
+    aln->num_states = n;
+    aln->STATE_UNKNOWN = pb->n_state_codes - 1;
+    aln->seq_type = n == 4 ? SEQ_DNA : (n == 20 ? SEQ_PROTEIN : SEQ_MORPH);
+    for (int t = 0; t < pb->ntaxa; t++) aln->getSeqNames().push_back("T" + std::to_string(t));
+    aln->reserve(pb->nptn);
+    int site = 0;
+    for (int64_t p = 0; p < pb->nptn; p++) {
+        Pattern pat;
+        pat.resize(pb->ntaxa);
+        for (int t = 0; t < pb->ntaxa; t++) pat[t] = pb->states[(size_t)t * pb->nptn + p];
+        pat.frequency = (int)pb->ptn_freq[p];
+        // constant-pattern bookkeeping of Alignment::computeConst for unambiguous data: a pattern is
+        // constant when all non-gap characters agree (gaps alone count as constant UNKNOWN)
+        int first = -1;
+        bool is_const = true, ambiguous = false;
+        for (int t = 0; t < pb->ntaxa; t++) {
+            int s = pat[t];
+            if (s == (int)aln->STATE_UNKNOWN) continue;
+            if (s >= n) ambiguous = true;
+            if (first < 0) first = s;
+            else if (s != first) is_const = false;
+        }
+        pat.flag = 0;
+        pat.const_char = aln->STATE_UNKNOWN + 1;
+        if (is_const && !ambiguous) {
+            pat.flag |= PAT_CONST;
+            pat.const_char = first < 0 ? (int)aln->STATE_UNKNOWN : first;
+        }
+        aln->push_back(pat);
+        for (int f = 0; f < pat.frequency; f++) aln->site_pattern.push_back((int)p), site++;
+    }
+    h->aln = aln;
+    // model, rates, factory
+    HarnessModel *m = new HarnessModel(n, pb->nmix);
+    m->eval = HarnessModel::aligned_copy(pb->eval, (size_t)pb->nmix * n);
+    m->evec = HarnessModel::aligned_copy(pb->evec, (size_t)pb->nmix * n * n);
+    m->inv_evec = HarnessModel::aligned_copy(pb->inv_evec, (size_t)pb->nmix * n * n);
+    m->mixw.assign(pb->mixw, pb->mixw + pb->nmix);
+    m->freqs.assign(pb->freqs, pb->freqs + (size_t)pb->nmix * n);
+    m->ncodes = pb->n_state_codes;
+    m->tipvec.assign(pb->tipvec, pb->tipvec + (size_t)pb->n_state_codes * n);
+    HarnessRate *r = new HarnessRate();
+    r->rates.assign(pb->rates, pb->rates + pb->ncat);
+    r->props.assign(pb->props, pb->props + pb->ncat);
+    r->pinvar = pb->pinvar;
+    ModelFactory *f = new ModelFactory();
+    f->model = m;
+    f->site_rate = r;
+    h->model = m;
+    h->rate = r;
+    h->factory = f;
+    // tree
+    PhyloTree *tree = new PhyloTree();
+    tree->params = &params;
+    std::stringstream ss;
+    ss << pb->newick;
+    bool rooted = false;
+    tree->readTree(ss, rooted);
+    tree->setAlignment(aln);
+    tree->setModelFactory(f);
+    tree->setLikelihoodKernel((LikelihoodKernel)pb->kernel);
+    tree->setNumThreads(pb->threads);
+    tree->initializeAllPartialLh();
+    h->tree = tree;
+    h->ncm = pb->ncat * pb->nmix;
+    h->block = h->ncm * n;
+    h->cur_dad_branch = NULL;
+    h->cur_dad = NULL;
+    return h;
+}
+
+int ref_vector_size(void *hv) { return (int)((RefHandle *)hv)->tree->vector_size; }
+int ref_safe_numeric(void *hv) { return ((RefHandle *)hv)->tree->safe_numeric ? 1 : 0; }
+
+static PhyloNode *find_leaf(PhyloTree *tree, int taxon) {
+    NodeVector leaves;
+    tree->getTaxa(leaves);
+    for (size_t i = 0; i < leaves.size(); i++)
+        if (leaves[i]->id == taxon) return (PhyloNode *)leaves[i];
+    return NULL;
+}
+
+// All partials stale -> computeLikelihoodBranch at the branch (leaf, its neighbour), the root choice of
+// PhyloTree::computeLikelihood (tree/phylotree.cpp:1227-1268) made explicit.
+double ref_lnl_at_leaf(void *hv, int taxon) {
+    RefHandle *h = (RefHandle *)hv;
+    PhyloTree *tree = h->tree;
+    PhyloNode *leaf = find_leaf(tree, taxon);
+    if (!leaf) return 1.0;
+    tree->clearAllPartialLH();
+    PhyloNeighbor *dad_branch = (PhyloNeighbor *)leaf->neighbors[0];
+    h->cur_dad_branch = dad_branch;
+    h->cur_dad = leaf;
+    tree->current_it = dad_branch;
+    tree->current_it_back = (PhyloNeighbor *)dad_branch->node->findNeighbor(leaf);
+    return tree->computeLikelihoodBranch(dad_branch, leaf);
+}
+
+// lnL at the same branch again WITHOUT invalidating partials (after a length change)
+double ref_lnl_again(void *hv) {
+    RefHandle *h = (RefHandle *)hv;
+    return h->tree->computeLikelihoodBranch(h->cur_dad_branch, h->cur_dad);
+}
+
+void ref_set_current_length(void *hv, double len) {
+    RefHandle *h = (RefHandle *)hv;
+    h->tree->current_it->length = len;
+    h->tree->current_it_back->length = len;
+}
+
+void ref_derv(void *hv, double *df, double *ddf) {
+    RefHandle *h = (RefHandle *)hv;
+    h->tree->theta_computed = false;
+    h->tree->computeLikelihoodDerv(h->cur_dad_branch, h->cur_dad, df, ddf);
+}
+// further derivative evaluations reuse theta (what minimizeNewton's later steps do)
+void ref_derv_again(void *hv, double *df, double *ddf) {
+    RefHandle *h = (RefHandle *)hv;
+    h->tree->computeLikelihoodDerv(h->cur_dad_branch, h->cur_dad, df, ddf);
+}
+double ref_from_buffer(void *hv) { return ((RefHandle *)hv)->tree->computeLikelihoodFromBuffer(); }
+
+// Newton-Raphson on the current branch exactly as the reference runs it (tree/phylotree.cpp:2585-2635)
+double ref_optimize_current_branch(void *hv, int max_steps) {
+    RefHandle *h = (RefHandle *)hv;
+    PhyloNode *n1 = h->cur_dad, *n2 = (PhyloNode *)h->cur_dad_branch->node;
+    h->tree->optimizeOneBranch(n1, n2, false, max_steps);
+    return h->tree->current_it->length;
+}
+
+void ref_pattern_lh(void *hv, double *out) {
+    RefHandle *h = (RefHandle *)hv;
+    memcpy(out, h->tree->_pattern_lh, sizeof(double) * h->aln->size());
+}
+
+// _pattern_lh_cat is V-interleaved: (p/V)*V*ncm + c*V + p%V (tree/phylokernelnew.h:2801, 2857-2867)
+void ref_pattern_lh_cat(void *hv, double *out) {
+    RefHandle *h = (RefHandle *)hv;
+    const size_t V = h->tree->vector_size, ncm = h->ncm, nptn = h->aln->size();
+    for (size_t p = 0; p < nptn; p++)
+        for (size_t c = 0; c < ncm; c++) out[p * ncm + c] = h->tree->_pattern_lh_cat[(p / V) * V * ncm + c * V + p % V];
+}
+
+static void leaf_set(Node *node, Node *dad, std::vector<int> &out) {
+    if (node->isLeaf()) {
+        out.push_back(node->id);
+        return;
+    }
+    for (size_t i = 0; i < node->neighbors.size(); i++)
+        if (node->neighbors[i]->node != dad) leaf_set(node->neighbors[i]->node, node, out);
+}
+
+static PhyloNeighbor *find_branch(Node *node, Node *dad, const std::vector<int> &want) {
+    // the neighbour record (dad -> node) whose subtree at `node` has exactly the leaf set `want`
+    for (size_t i = 0; i < node->neighbors.size(); i++) {
+        Node *nx = node->neighbors[i]->node;
+        if (nx == dad) continue;
+        std::vector<int> ls;
+        leaf_set(nx, node, ls);
+        std::sort(ls.begin(), ls.end());
+        if (ls == want) return (PhyloNeighbor *)node->neighbors[i];
+        if (ls.size() > want.size()) {
+            PhyloNeighbor *r = find_branch(nx, node, want);
+            if (r) return r;
+        }
+    }
+    return NULL;
+}
+
+// partial_lh and scale_num of the directed branch whose subtree carries the given (sorted) leaf set,
+// de-interleaved to [nptn][ncm][n] and [nptn] (NORM) / [nptn][ncm] (SAFE)
+// (layout tree/phylokernelnew.h:1914-1931).  Returns 0 on success.
+int ref_fetch_branch(void *hv, const int32_t *leaves, int nleaves, int from_taxon, double *partial, uint8_t *scale) {
+    RefHandle *h = (RefHandle *)hv;
+    std::vector<int> want(leaves, leaves + nleaves);
+    PhyloNode *start = find_leaf(h->tree, from_taxon);
+    if (!start) return -1;
+    PhyloNeighbor *nb = find_branch(start, NULL, want);
+    if (!nb || !nb->partial_lh) return -2;
+    const size_t V = h->tree->vector_size, ncm = h->ncm, n = h->aln->num_states, block = h->block;
+    const size_t nptn = h->aln->size();
+    const bool safe = h->tree->safe_numeric;
+    for (size_t p = 0; p < nptn; p++) {
+        for (size_t e = 0; e < block; e++) partial[p * block + e] = nb->partial_lh[(p / V) * V * block + e * V + p % V];
+        if (safe)
+            for (size_t c = 0; c < ncm; c++) scale[p * ncm + c] = nb->scale_num[p * ncm + c];
+        else
+            scale[p] = nb->scale_num[p];
+    }
+    (void)n;
+    return 0;
+}
+
+void ref_destroy(void *hv) {
+    RefHandle *h = (RefHandle *)hv;
+    // the tree owns its buffers; model/rate/factory are ours
+    h->tree->setModelFactory(NULL);
+    delete h->tree;
+    delete h->factory;
+    delete h->model;
+    delete h->rate;
+    delete h->aln;
+    delete h;
+}
+
+}  // extern "C"
+
+// target of the generated traps (oracle/gen_ref_stubs.py)
+extern "C" void ref_stub_trap(const char *symbol) {
+    fprintf(stderr, "oracle/_ref: reference symbol outside the likelihood path was reached: %s\n", symbol);
+    abort();
+}
