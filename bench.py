@@ -103,40 +103,44 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
-def cpu_engine(aln, model, rates, props, nslots):
-    """(engine, kind): the reference's own kernels (oracle/_ref) when built, else the C restatement."""
-    import oracle
-    try:
-        from oracle import ref_engine  # provided when oracle/_ref is built
-        eng = ref_engine(aln, model, rates, props, nslots=nslots)
-        if eng is not None:
-            return eng, "reference"
-    except Exception:
-        pass
-    return oracle.oracle_engine(aln, model, rates, props, nslots=nslots), "port"
-
-
 def time_cpu(tree, model, rates, props, aln, sample, steps, warmup):
-    """CPU baseline on the first `sample` patterns of the same alignment, all host threads."""
+    """CPU baseline on the first `sample` patterns of the same alignment, all host threads: the reference's
+    own AVX+FMA kernel with OpenMP (oracle/_ref, kind "reference") when that library was built, else the C
+    restatement (kind "port").  One evaluation = all partials stale -> lnL at the root branch -> theta ->
+    df/ddf, exactly the GPU step."""
+    import oracle
     from iqtree2_b200 import workload as W
     from iqtree2_b200.capi import INTERNAL, LEAF
     sub = W.Alignment(aln.nstates, aln.names, np.ascontiguousarray(aln.states[:, :sample]),
                       np.ascontiguousarray(aln.ptn_freq[:sample]))
-    eng, kind = cpu_engine(sub, model, rates, props, tree.ntaxa)
     cores = os.cpu_count() or 1
-    if hasattr(eng.lib, eng.prefix + "set_threads"):
-        eng._f("set_threads")(eng.ctx, cores)
     c = tree.adj[0][0]
     tr = W.traversal(tree, c, 0)
-    args = (tr, (LEAF, 0), (INTERNAL, tr[-1][2]), tree.get_length(0, c))
+    if oracle.ref_available():
+        kind = "reference"
+        ref = oracle.RefRun(tree, sub, model, rates, props, kernel=oracle.LK_AVX_FMA, threads=cores)
+
+        def one():
+            lnl = ref.lnl_at_leaf(0)
+            df, ddf = ref.derv()
+            return lnl, df, ddf
+    else:
+        kind = "port"
+        eng = oracle.oracle_engine(sub, model, rates, props, nslots=tree.ntaxa)
+        eng._f("set_threads")(eng.ctx, cores)
+        args = (tr, (LEAF, 0), (INTERNAL, tr[-1][2]), tree.get_length(0, c))
+
+        def one():
+            return eng.evaluate(*args)
     for _ in range(warmup):
-        eng.evaluate(*args)
+        one()
     t0 = time.perf_counter()
     for _ in range(steps):
-        res = eng.evaluate(*args)
+        res = one()
     dt = (time.perf_counter() - t0) / steps
+    what = "reference AVX+FMA kernel (-lk FMA), OpenMP" if kind == "reference" else "C restatement, OpenMP"
     return {"value": len(tr) * sub.nptn / dt, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": "first %d of %d patterns, same tree/model, %d full evaluations" % (sub.nptn, aln.nptn, steps),
+            "sample": "%s; first %d of %d patterns, same tree/model, %d full evaluations" % (what, sub.nptn, aln.nptn, steps),
             "ms_per_eval": dt * 1e3, "evals_per_sec": 1.0 / dt, "lnl": res[0]}
 
 

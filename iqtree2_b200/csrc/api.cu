@@ -75,6 +75,11 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
         dc.length = children[j].length;
         dc.echild_off = (int64_t)off;
         off += (size_t)block * n + block;  // echild, then expv
+        dc.frag_off = -1;
+        if (c->dense20) {
+            dc.frag_off = (int64_t)off;
+            off += (size_t)c->ncat_mix * B200_FRAG20;
+        }
         if (dc.kind == B200LK_CHILD_LEAF) {
             dc.leaf_off = (int64_t)off;
             off += (size_t)c->d.n_state_codes * block;

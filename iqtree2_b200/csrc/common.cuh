@@ -30,7 +30,9 @@
 
 struct DevModel {
     double *eval, *evec, *inv_evec, *rates, *props, *mixw, *tip_partial_lh;
+    double *inv_frag;  // 20-state tensor path: inv_evec per class in mma fragment order [nmix][15][32]
 };
+#define B200_FRAG20 480  // doubles of one 20x20 matrix in fragment order: 3 n-tiles x 5 k-steps x 32 lanes
 
 // One child of one traversal entry, device view.
 struct DevChild {
@@ -39,6 +41,7 @@ struct DevChild {
     double length;
     int64_t echild_off;  // offset (doubles) into tables
     int64_t leaf_off;    // offset (doubles) into tables, -1 if internal
+    int64_t frag_off;    // 20-state tensor path: echild in mma fragment order (dense.cu), -1 if unused
 };
 
 struct DevNode {
@@ -48,6 +51,7 @@ struct DevNode {
 struct b200lk_ctx {
     b200lk_dims d;
     int ncat_mix, block, scale_per_ptn;
+    bool dense20;  // nstates == 20: FP64 tensor-core (DMMA) partial update, dense.cu
     int tile;  // HBM layout of partial vectors and theta: 1 = pattern-major, 32 = T32 (s4.cu)
     double *h_evec, *h_inv_evec, *h_eval, *h_rates;  // host copies of the model (kernel parameters of the 4-state path)
     int64_t ntot, ntot_pad;
@@ -75,7 +79,7 @@ struct b200lk_ctx {
     DevChild *h_children_ring;  // asynchronous evaluations never overwrite a copy still in flight
     size_t prog_stride;
     void *h_prog, *h_prog_ring, *d_prog;  // device program of the pattern-stationary traversal (traverse.cu)
-    bool trav_attr_set, force_level_batched;
+    bool trav_attr_set, dense_attr_set, force_level_batched;
     int max_stack_depth;  // shared-memory stack entries per thread (default 8; B200LK_STACK_DEPTH)
     cudaEvent_t stage_ev[B200_STAGE_RING];
     bool stage_used[B200_STAGE_RING];
@@ -132,3 +136,5 @@ int launch_from_buffer(b200lk_ctx *c, double length);
 int launch_repair(b200lk_ctx *c);
 int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used);
 int launch_partial_multi(b200lk_ctx *c, int node_index);
+int launch_dense20(b200lk_ctx *c, int node_base, int nnodes);
+int launch_inv_frag(b200lk_ctx *c);

@@ -53,6 +53,8 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->tip_val, sizeof(double) * d.n_state_codes * c->block));
     // tables for a full traversal: at most 2*(ntaxa-2)+ntaxa children
     size_t per_child = (size_t)c->block * n + c->block + (size_t)d.n_state_codes * c->block;  // echild, expv, leaf
+    if (c->dense20) per_child += (size_t)c->ncat_mix * B200_FRAG20;
+    CUDA_TRY(c, cudaMalloc(&c->m.inv_frag, sizeof(double) * nmix * B200_FRAG20));
     c->h_evec = (double *)malloc(sizeof(double) * nmix * n * n);
     c->h_inv_evec = (double *)malloc(sizeof(double) * nmix * n * n);
     c->h_eval = (double *)malloc(sizeof(double) * nmix * n);
@@ -119,6 +121,10 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
         c->force_level_batched = e && *e == '1';
     }
     // 4-state models with <= 4 categories run the pattern-stationary path on the T32 layout (s4.cu)
+    {
+        const char *e = getenv("B200LK_NO_DMMA");  // A/B switch: generic kernels for 20-state models
+        c->dense20 = dims->nstates == 20 && !(e && *e == '1') && !c->force_level_batched;
+    }
     c->tile = (dims->nstates == 4 && c->ncat_mix <= 4 && !c->force_level_batched) ? 32 : 1;
     int rc = alloc_all(c);
     if (rc != B200LK_OK) {
@@ -136,7 +142,7 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     cudaSetDevice(c->device);
     if (c->own_stream) cudaStreamSynchronize(c->own_stream);
     void *dev[] = {c->states, c->ptn_freq, c->ptn_invar, c->partial, c->scale, c->m.eval, c->m.evec,
-                   c->m.inv_evec, c->m.rates, c->m.props, c->m.mixw, c->m.tip_partial_lh, c->theta_all,
+                   c->m.inv_evec, c->m.inv_frag, c->m.rates, c->m.props, c->m.mixw, c->m.tip_partial_lh, c->theta_all,
                    c->buffer_scale_all, c->pattern_lh, c->pattern_lh_cat, c->val, c->tip_val, c->tables,
                    c->d_nodes, c->d_children, c->red_partial, c->d_result};
     for (void *p : dev)
@@ -215,6 +221,10 @@ extern "C" int b200lk_set_model(b200lk_ctx *c, const double *eval, const double 
     CUDA_TRY(c, cudaMemcpyAsync(c->m.mixw, mixw, sizeof(double) * nmix, cudaMemcpyHostToDevice, s));
     CUDA_TRY(c, cudaMemcpyAsync(c->m.tip_partial_lh, tip_partial_lh, sizeof(double) * c->d.n_state_codes * nmix * n,
                                 cudaMemcpyHostToDevice, s));
+    if (c->dense20) {
+        int rc = launch_inv_frag(c);
+        if (rc) return rc;
+    }
     CUDA_TRY(c, cudaStreamSynchronize(s));  // the host arrays may be reused by the caller
     memcpy(c->h_evec, evec, sizeof(double) * nmix * n * n);
     memcpy(c->h_inv_evec, inv_evec, sizeof(double) * nmix * n * n);

@@ -320,7 +320,10 @@ int launch_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels) 
         // within a level: bifurcating nodes first [base, base+nb), multifurcating after
         int nb = 0, nm = 0;
         for (int idx : levels[l]) (c->h_nodes[idx].kind == 3 ? nm : nb)++;
-        if (nb) {
+        if (nb && c->dense20) {
+            int rc = launch_dense20(c, base, nb);  // FP64 tensor-core path (dense.cu)
+            if (rc) return rc;
+        } else if (nb) {
             a.node_base = base;
             dim3 grid((unsigned)((c->ntot + a.PT - 1) / a.PT), nb);
             prof_mark(c);

@@ -26,6 +26,18 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
         int c = idx / n, i = idx - c * n;
         expv[idx] = exp(m.eval[(c / denom) * n + i] * (m.rates[c % ncat] * ch.length));
     }
+    if (ch.frag_off >= 0) {
+        // 20-state tensor path (dense.cu): echild as the B operand of mma.m8n8k4, fragment order
+        //   frag[c][j][s][lane] = echild[c][x = 8j + lane/4][i = 4s + lane%4]   (x >= 20 -> 0)
+        __syncthreads();
+        double *frag = tables + ch.frag_off;
+        for (int idx = threadIdx.x; idx < ncm * B200_FRAG20; idx += blockDim.x) {
+            int c = idx / B200_FRAG20, r = idx - c * B200_FRAG20;
+            int j = r / 160, s = (r / 32) % 5, lane = r & 31;
+            int x = 8 * j + (lane >> 2), i = 4 * s + (lane & 3);
+            frag[idx] = x < n ? echild[(size_t)c * nn + x * n + i] : 0.0;
+        }
+    }
     if (ch.leaf_off < 0) return;
     __syncthreads();
     double *leaf = tables + ch.leaf_off;
@@ -53,5 +65,27 @@ int launch_tables(b200lk_ctx *c, int nchildren) {
                                                     c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
+    return B200LK_OK;
+}
+
+// inv_evec per mixture class as the B operand of the final product out[p][i] = sum_x tmp[p][x] inv[i][x]:
+// the A operand is the accumulator fragment of the previous mma (lane (g, q) holds x = 8j + 2q + r), so the
+// contraction index is permuted instead of shuffling registers:
+//   k-step kk = 2j + r (j < 2):  frag[jo][kk][lane] = inv[i = 8jo + lane/4][x = 8j + 2(lane%4) + r]
+//   k-step 4 (x = 16..19):       frag[jo][4][lane]  = inv[i = 8jo + lane/4][x = 16 + lane%4]
+__global__ void inv_frag_kernel(const double *__restrict__ inv_evec, double *__restrict__ frag, int nmix) {
+    const int n = 20;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nmix * B200_FRAG20; idx += gridDim.x * blockDim.x) {
+        int m = idx / B200_FRAG20, r = idx - m * B200_FRAG20;
+        int jo = r / 160, kk = (r / 32) % 5, lane = r & 31;
+        int i = 8 * jo + (lane >> 2);
+        int x = kk < 4 ? 8 * (kk >> 1) + 2 * (lane & 3) + (kk & 1) : 16 + (lane & 3);
+        frag[idx] = i < n ? inv_evec[(size_t)m * n * n + i * n + x] : 0.0;
+    }
+}
+
+int launch_inv_frag(b200lk_ctx *c) {
+    inv_frag_kernel<<<(c->d.nmix * B200_FRAG20 + 255) / 256, 256, 0, c->stream>>>(c->m.inv_evec, c->m.inv_frag, c->d.nmix);
+    CUDA_TRY(c, cudaGetLastError());
     return B200LK_OK;
 }

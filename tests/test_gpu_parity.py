@@ -149,3 +149,26 @@ def test_partial_retraversal_reads_resident_partials(oracle_lib):
     assert rel(a, b) <= TOL
     for e in tr2:
         assert np.array_equal(g.fetch_scale_num(e[2]), o.fetch_scale_num(e[2]))
+
+
+@pytest.mark.parametrize("env", [{}, {"B200LK_NO_DMMA": "1"}])
+@pytest.mark.parametrize("safe", [False, True])
+def test_protein_tensor_path_deep_tree(oracle_lib, monkeypatch, env, safe):
+    """20-state path: FP64 tensor-core tiles (default) and the generic kernels agree with the oracle on a
+    tree deep enough for rescaling to fire; pattern count not a multiple of the 64-pattern tile."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    tree, model, rates, props, aln = make_problem(160, 333, nstates=20, seed=14, mean_len=0.5, gaps=0.02,
+                                                  compress=False)
+    g, o = both(aln, model, rates, props, nslots=160, safe_numeric=safe)
+    rg, ro = full_eval(g, tree, 1), full_eval(o, tree, 1)
+    assert max(int(s.max()) for s in ro["scale"].values()) >= 1
+    assert_parity(rg, ro, TOL)
+
+
+def test_protein_mixture_many_categories(oracle_lib):
+    """C-series shape: 6 classes x 4 rates = 24 categories, i.e. six staged category groups per node."""
+    tree, model, rates, props, aln = make_problem(12, 150, nstates=20, nmix=6, seed=15)
+    for safe in (False, True):
+        g, o = both(aln, model, rates, props, nslots=12, safe_numeric=safe)
+        assert_parity(full_eval(g, tree, 0), full_eval(o, tree, 0), TOL)
