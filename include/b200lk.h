@@ -143,6 +143,23 @@ int b200lk_derv(b200lk_ctx *ctx, double length, double *df, double *ddf);
 /* computeLikelihoodFromBuffer*SIMD (tree/phylokernelnew.h:3196-3392) from theta_all. */
 int b200lk_lnl_from_buffer(b200lk_ctx *ctx, double length, double *lnl);
 
+/* Newton-Raphson on one branch, whole iteration on the device: what PhyloTree::optimizeOneBranch asks of
+ * Optimization::minimizeNewton (tree/phylotree.cpp:2585-2635, utils/optimization.cpp:422-499) with
+ * computeFuncDerv = computeLikelihoodDerv (tree/phylotree.cpp:2520-2527).  Builds theta for branch (dad, node),
+ * then runs the bisection-safeguarded iteration t <- t - f/f' (f = -df, f' = -ddf) inside [min_len, max_len]
+ * without a host round trip per step.  Returns the optimised length, d2l (= -ddf at the last evaluation, the
+ * reference's `negative_lh` out-parameter) and the number of derivative evaluations.  theta stays valid for a
+ * following b200lk_lnl_from_buffer. */
+typedef struct b200lk_newton {
+    double min_len, max_len; /* params->min_branch_length, max_branch_length */
+    double xacc;             /* accuracy: the reference passes min_branch_length */
+    double guess;            /* current_it->length */
+    int32_t max_steps;       /* maxNRStep (default 100) */
+    int32_t reserved;
+} b200lk_newton;
+int b200lk_optimize_branch(b200lk_ctx *ctx, b200lk_end dad, b200lk_end node, const b200lk_newton *nr,
+                           double *optx, double *d2l, int32_t *nsteps);
+
 /* One round trip for a whole evaluation: update_partials + branch_lnl + build_theta + derv
  * (what computeLikelihood followed by the first computeFuncDerv of optimizeOneBranch costs,
  * tree/phylotree.cpp:1227-1268, 2520-2527).  Any of lnl/df/ddf may be NULL. */

@@ -1,0 +1,37 @@
+#!/bin/bash
+# One GPU-box pass.  Usage (repo root, on the GPU box): bash tools/gpu_check.sh <tag> [stages...]
+# stages: test bench launches prof_s4 prof_d20   (default: test bench)
+# gpurun copies back at most 64 MiB of gpurun_out/: keep full ncu captures to a few launches.
+TAG=${1:-rX}; shift
+STAGES=${@:-test bench}
+OUT=gpurun_out
+mkdir -p $OUT
+has() { [[ " $STAGES " == *" $1 "* ]]; }
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/smi_$TAG.txt
+if has test; then
+python -m pytest tests -m gpu -x -q > $OUT/pytest_$TAG.log 2>&1; echo "pytest rc=$?" >> $OUT/pytest_$TAG.log
+python -c "import __graft_entry__ as g; g.smoke()" > $OUT/smoke_$TAG.log 2>&1; echo "smoke rc=$?" >> $OUT/smoke_$TAG.log
+tail -3 $OUT/pytest_$TAG.log; tail -2 $OUT/smoke_$TAG.log
+fi
+if has bench; then
+python bench.py > $OUT/bench_cfg2_$TAG.json 2> $OUT/bench_cfg2_$TAG.err
+python bench.py --workload cfg3 --steps 5 > $OUT/bench_cfg3_$TAG.json 2> $OUT/bench_cfg3_$TAG.err
+python bench.py --impl reference --steps 3 --warmup 1 > $OUT/bench_ref_$TAG.json 2> $OUT/bench_ref_$TAG.err
+cut -c1-300 $OUT/bench_cfg2_$TAG.json; cut -c1-300 $OUT/bench_cfg3_$TAG.json
+fi
+if has launches; then
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_cfg2_$TAG.csv \
+    python bench.py --steps 2 --warmup 3 --no-cpu > $OUT/ncu_l2_$TAG.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches_cfg3_$TAG.csv \
+    python bench.py --workload cfg3 --patterns 50000 --steps 2 --warmup 3 --no-cpu > $OUT/ncu_l3_$TAG.log 2>&1
+fi
+if has prof_s4; then
+ncu --set full --clock-control none --import-source on -k regex:s4_traverse --launch-skip 6 -c 2 -f -o $OUT/prof_s4_$TAG \
+    python bench.py --steps 1 --warmup 3 --no-cpu > $OUT/ncu_s4_$TAG.log 2>&1
+fi
+if has prof_d20; then
+# one step of cfg3 at 50k patterns has 31 dense20 launches (levels); take the first (TT-heavy), and three deeper ones
+ncu --set full --clock-control none --import-source on -k regex:dense20 --launch-skip 93 -c 4 -f -o $OUT/prof_dense20_$TAG \
+    python bench.py --workload cfg3 --patterns 50000 --steps 1 --warmup 3 --no-cpu > $OUT/ncu_d20_$TAG.log 2>&1
+fi
+du -sh $OUT
