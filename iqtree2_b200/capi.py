@@ -165,6 +165,22 @@ class Engine:
         self.last_status = self._check(f(self.ctx, length, C.byref(out)))
         return out.value
 
+    def optimize_branch(self, dad, node, guess, min_len=1e-6, max_len=10.0, xacc=None, max_steps=100):
+        """b200lk_optimize_branch: theta + the whole safeguarded Newton-Raphson iteration on the device.
+        Returns (optimised length, d2l, derivative evaluations)."""
+
+        class Newton(C.Structure):
+            _fields_ = [("min_len", C.c_double), ("max_len", C.c_double), ("xacc", C.c_double),
+                        ("guess", C.c_double), ("max_steps", C.c_int32), ("reserved", C.c_int32)]
+        nr = Newton(min_len, max_len, min_len if xacc is None else xacc, guess, max_steps, 0)
+        optx, d2l, steps = C.c_double(), C.c_double(), C.c_int32()
+        f = self._f("optimize_branch")
+        f.argtypes = [C.c_void_p, End, End, C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                      C.POINTER(C.c_int32)]
+        self.last_status = self._check(f(self.ctx, End(*dad), End(*node), C.byref(nr), C.byref(optx), C.byref(d2l),
+                                         C.byref(steps)))
+        return optx.value, d2l.value, steps.value
+
     def evaluate(self, entries, dad, node, length, want_lnl=True, want_derv=True):
         nodes, nn, kids, nk = pack_traversal(entries)
         lnl, df, ddf = C.c_double(), C.c_double(), C.c_double()

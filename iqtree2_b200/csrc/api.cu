@@ -265,6 +265,32 @@ extern "C" int b200lk_lnl_from_buffer(b200lk_ctx *c, double length, double *lnl)
     return finish_lnl(c, lnl);
 }
 
+extern "C" int b200lk_optimize_branch(b200lk_ctx *c, b200lk_end dad, b200lk_end node, const b200lk_newton *nr,
+                                      double *optx, double *d2l, int32_t *nsteps) {
+    int rc = check_ready(c);
+    if (rc) return rc;
+    if (!nr || !optx || check_ends(c, dad, node) || !(nr->min_len <= nr->max_len) || nr->max_steps < 1)
+        return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->d.nptn == 0) {
+        *optx = nr->guess;
+        if (d2l) *d2l = 0.0;
+        if (nsteps) *nsteps = 0;
+        return B200LK_OK;
+    }
+    rc = launch_theta(c, dad, node);
+    if (rc) return rc;
+    c->theta_computed = true;
+    rc = launch_newton(c, nr);
+    if (rc) return rc;
+    rc = read_results(c, 4, 4);  // optx, d2l, evaluations, status: the only D2H of the whole iteration
+    if (rc) return rc;
+    *optx = c->h_result[4];
+    if (d2l) *d2l = c->h_result[5];
+    if (nsteps) *nsteps = (int32_t)c->h_result[6];
+    return c->h_result[7] != 0.0 ? B200LK_WARN_DERV_NONFINITE : B200LK_OK;
+}
+
 extern "C" int b200lk_evaluate_async(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes,
                                      const b200lk_child *children, int32_t nchildren, b200lk_end dad,
                                      b200lk_end node, double length, int want_lnl, int want_derv) {

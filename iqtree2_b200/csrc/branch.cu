@@ -8,6 +8,8 @@
 // [block] vector so that consecutive lanes read consecutive doubles; per-pattern sums
 // finish with warp shuffles.  Sums over patterns are deterministic: fixed grid, fixed
 // per-thread order, shuffle tree, then a fixed-order pass over the per-CTA partials.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 #define RED_THREADS 256
@@ -171,6 +173,148 @@ __global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red
         }
     }
     block_reduce_store<2>(acc, a.red_partial, red_blocks);
+}
+
+// ---- Newton-Raphson on the device ---------------------------------------------
+// Optimization::minimizeNewton (utils/optimization.cpp:422-499) with computeFuncDerv = the derv pass above, as ONE
+// cooperative launch: every iteration all CTAs stream theta once, leave their partial sums in a parity buffer,
+// cross a grid barrier, and then EVERY CTA reduces the partials in the same fixed order and advances the same
+// safeguarded-Newton state machine, so all CTAs agree on the next branch length without a second barrier or a
+// host round trip.  val0/1/2 for the current length are rebuilt per CTA in shared memory.
+struct NewtonArgs {
+    DevModel m;
+    double x1, x2, xacc, guess;
+    int max_steps, ncat, safe_zero;
+    double *out;  // [0] optx, [1] d2l, [2] derivative evaluations, [3] status (0 ok, 1 non-finite derivative)
+    double *red;  // [2 parities][2][red_blocks]
+};
+
+__global__ void __launch_bounds__(RED_THREADS) newton_kernel(BranchArgs a, NewtonArgs nr, int red_blocks) {
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    extern __shared__ double sval[];  // [3][block]
+    __shared__ double sh_red[RED_THREADS];
+    __shared__ double sh_state[4];     // rts, stop flag
+    const int G = a.G, g = threadIdx.x & (G - 1);
+    const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
+    const int block = a.block, n = a.n;
+    const double *v0 = sval, *v1 = sval + block, *v2 = sval + 2 * block;
+    // Newton state, replicated in thread 0 of every CTA
+    double rts = fmin(fmax(nr.guess, nr.x1), nr.x2), xl = 0.0, xh = 0.0, dx = 0.0, rts_old = rts, d2l = 0.0, result = rts;
+    int j = 0, evals = 0, status = 0;
+    bool started = false;
+    for (int iter = 0;; iter++) {
+        // val tables for the current length (val_kernel)
+        for (int idx = threadIdx.x; idx < block; idx += RED_THREADS) {
+            const int c = idx / n, i = idx - c * n, mm = c / a.denom, k = c % nr.ncat;
+            const double prop = nr.m.props[k] * nr.m.mixw[mm];
+            const double cof = nr.m.eval[mm * n + i] * nr.m.rates[k];
+            const double v = exp(cof * rts) * prop, w = cof * v;
+            sval[idx] = v;
+            sval[block + idx] = w;
+            sval[2 * block + idx] = cof * w;
+        }
+        __syncthreads();
+        double acc[2] = {0.0, 0.0};
+        for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.nptn; pb += groups_per_grid) {
+            int64_t p = pb + threadIdx.x / G;
+            const bool valid = p < a.nptn;
+            if (!valid) p = a.nptn - 1;
+            const double *th = a.theta;
+            double lh = 0.0, df = 0.0, ddf = 0.0;
+            for (int e = g; e < block; e += G) {
+                const double t = th[E(e)];
+                lh = fma(v0[e], t, lh);
+                df = fma(v1[e], t, df);
+                ddf = fma(v2[e], t, ddf);
+            }
+            lh = group_sum(lh, G);
+            df = group_sum(df, G);
+            ddf = group_sum(ddf, G);
+            if (g == 0 && valid) {
+                lh = fabs(lh) + a.ptn_invar[p];
+                const double inv = 1.0 / lh;
+                const double df_frac = df * inv, ddf_frac = ddf * inv, freq = a.ptn_freq[p];
+                const double tmp1 = df_frac * freq, tmp2 = ddf_frac * freq;
+                acc[0] += tmp1;
+                acc[1] += fma(-tmp1, df_frac, tmp2);
+            }
+        }
+        double *red = nr.red + (size_t)(iter & 1) * 2 * red_blocks;
+        block_reduce_store<2>(acc, red, red_blocks);
+        __threadfence();
+        grid.sync();
+        // every CTA: the fixed-order final reduction of final_reduce_kernel, on its own
+        double sums[2];
+        for (int k = 0; k < 2; k++) {
+            double v = 0.0;
+            for (int b = threadIdx.x; b < (int)gridDim.x; b += RED_THREADS) v += __ldcg(red + (size_t)k * red_blocks + b);
+            sh_red[threadIdx.x] = v;
+            __syncthreads();
+            for (int s = RED_THREADS / 2; s > 0; s >>= 1) {
+                if (threadIdx.x < s) sh_red[threadIdx.x] += sh_red[threadIdx.x + s];
+                __syncthreads();
+            }
+            sums[k] = sh_red[0];
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) {
+            double f = -sums[0], df = -sums[1];  // computeFuncDerv negates (tree/phylotree.cpp:2520-2527)
+            evals++;
+            bool stop = false;
+            if (!isfinite(f) || !isfinite(df)) {
+                if (nr.safe_zero) { f = 0.0; df = 0.0; }  // SAFE_LH: df = ddf = 0 and carry on (:2629-2632)
+                else { status = 1; stop = true; result = rts; }
+            }
+            if (!stop) {
+                if (!started) {
+                    started = true;
+                    d2l = df;
+                    if (df >= 0.0 && fabs(f) < nr.xacc) { stop = true; result = rts; }
+                    else {
+                        if (f < 0.0) { xl = rts; xh = nr.x2; } else { xh = rts; xl = nr.x1; }
+                        dx = fabs(xh - xl);
+                        j = 1;
+                    }
+                } else {
+                    if (df > 0.0 && fabs(f) < nr.xacc) { d2l = df; stop = true; result = rts; }
+                    else {
+                        if (f < 0.0) xl = rts;
+                        else if (f > 0.0) xh = rts;
+                        j++;
+                    }
+                }
+            }
+            if (!stop) {  // one step of the safeguarded iteration
+                rts_old = rts;
+                if (df <= 0.0 || (((rts - xh) * df - f) * ((rts - xl) * df - f) >= 0.0)) {
+                    dx = 0.5 * (xh - xl);
+                    rts = xl + dx;
+                    d2l = df;
+                    if (xl == rts) { stop = true; result = rts; }
+                } else {
+                    dx = f / df;
+                    const double temp = rts;
+                    rts -= dx;
+                    d2l = df;
+                    if (temp == rts) { stop = true; result = rts; }
+                }
+                if (!stop && (fabs(dx) < nr.xacc || j == nr.max_steps)) { stop = true; result = rts_old; }
+            }
+            sh_state[0] = rts;
+            sh_state[1] = stop ? 1.0 : 0.0;
+            if (stop && blockIdx.x == 0) {
+                nr.out[0] = result;
+                nr.out[1] = d2l;
+                nr.out[2] = (double)evals;
+                nr.out[3] = (double)status;
+            }
+        }
+        __syncthreads();
+        rts = sh_state[0];
+        const bool stop = sh_state[1] != 0.0;
+        __syncthreads();
+        if (stop) return;
+    }
 }
 
 // ---- lnL from theta --------------------------------------------------------
@@ -401,5 +545,40 @@ int launch_from_buffer(b200lk_ctx *c, double length) {
     final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 1, c->d_result, 0);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches += 2;
+    return B200LK_OK;
+}
+
+// b200lk_optimize_branch: theta for (dad, node) must already be built
+int launch_newton(b200lk_ctx *c, const b200lk_newton *nr) {
+    BranchArgs a;
+    memset(&a, 0, sizeof(a));
+    fill_common(c, a);
+    a.G = pick_group(c->block);
+    NewtonArgs na;
+    na.m = c->m;
+    na.x1 = nr->min_len;
+    na.x2 = nr->max_len;
+    na.xacc = nr->xacc;
+    na.guess = nr->guess;
+    na.max_steps = nr->max_steps;
+    na.ncat = c->d.ncat;
+    na.safe_zero = c->d.safe_numeric;
+    na.out = c->d_result + 4;
+    na.red = c->red_partial;  // [2 parities][2][red_blocks] of its 8 * red_blocks doubles
+    const size_t smem = sizeof(double) * 3 * c->block;
+    if (smem > 200 * 1024) return B200LK_ERR_UNSUPPORTED;
+    if (smem > 48 * 1024)
+        CUDA_TRY(c, cudaFuncSetAttribute(newton_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0, sms = 148, coop = 0;
+    CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, newton_kernel, RED_THREADS, smem));
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device);
+    if (!coop || per_sm < 1) return B200LK_ERR_UNSUPPORTED;
+    int grid = grid_for(c, a.G, c->d.nptn);
+    if (grid > per_sm * sms) grid = per_sm * sms;
+    int red_blocks = c->red_blocks;
+    void *args[] = {&a, &na, &red_blocks};
+    CUDA_TRY(c, cudaLaunchCooperativeKernel((void *)newton_kernel, dim3(grid), dim3(RED_THREADS), args, smem, c->stream));
+    c->n_launches++;
     return B200LK_OK;
 }

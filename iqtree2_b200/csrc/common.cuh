@@ -134,6 +134,7 @@ int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node);
 int launch_derv(b200lk_ctx *c, double length);
 int launch_from_buffer(b200lk_ctx *c, double length);
 int launch_repair(b200lk_ctx *c);
+int launch_newton(b200lk_ctx *c, const b200lk_newton *nr);
 int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used);
 int launch_partial_multi(b200lk_ctx *c, int node_index);
 int launch_dense20(b200lk_ctx *c, int node_base, int nnodes);

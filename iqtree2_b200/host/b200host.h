@@ -324,4 +324,10 @@ public:
     double optimizeAllBranches(int my_iterations = 100, double tolerance = TOL_LIKELIHOOD, int maxNRStep = 100) override;
 };
 
+// ---- multi-GPU sharding (shard.cpp) ------------------------------------------------
+// contiguous pattern range [begin, end) of `rank`, whole 32-pattern tiles
+void shardPatterns(int64_t nptn, int world, int rank, int tile, int64_t *begin, int64_t *end);
+// longest-processing-time-first placement of partitions on GPUs by cost (tree/phylosupertree.cpp:664-667)
+void placePartitions(const double *cost, int nparts, int world, int32_t *gpu_of_part);
+
 }  // namespace b200

@@ -172,3 +172,67 @@ def test_protein_mixture_many_categories(oracle_lib):
     for safe in (False, True):
         g, o = both(aln, model, rates, props, nslots=12, safe_numeric=safe)
         assert_parity(full_eval(g, tree, 0), full_eval(o, tree, 0), TOL)
+
+
+def _newton_reference(eng, dad, node, guess, lo=1e-6, hi=10.0, max_steps=100):
+    """minimizeNewton (utils/optimization.cpp:422-499) driven through build_theta/derv of an engine."""
+    eng.build_theta(dad, node)
+    evals = [0]
+
+    def fd(t):
+        evals[0] += 1
+        df, ddf = eng.derv(t)
+        return -df, -ddf
+    rts = min(max(guess, lo), hi)
+    f, df = fd(rts)
+    if df >= 0.0 and abs(f) < lo:
+        return rts, evals[0]
+    if f < 0.0:
+        xl, xh = rts, hi
+    else:
+        xh, xl = rts, lo
+    for j in range(1, max_steps + 1):
+        old = rts
+        if df <= 0.0 or ((rts - xh) * df - f) * ((rts - xl) * df - f) >= 0.0:
+            dx = 0.5 * (xh - xl)
+            rts = xl + dx
+            if xl == rts:
+                return rts, evals[0]
+        else:
+            dx = f / df
+            tmp = rts
+            rts -= dx
+            if tmp == rts:
+                return rts, evals[0]
+        if abs(dx) < lo or j == max_steps:
+            return old, evals[0]
+        f, df = fd(rts)
+        if df > 0.0 and abs(f) < lo:
+            return rts, evals[0]
+        if f < 0.0:
+            xl = rts
+        elif f > 0.0:
+            xh = rts
+    raise AssertionError("not reached")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nstates,safe", [(4, False), (4, True), (20, False)])
+def test_device_newton_raphson_follows_the_reference_iteration(oracle_lib, nstates, safe):
+    """b200lk_optimize_branch == the reference's minimizeNewton driven step by step through the oracle:
+    same optimum, same number of derivative evaluations, from starts on both sides of the optimum."""
+    tree, model, rates, props, aln = make_problem(10, 600 if nstates == 4 else 120, nstates=nstates, seed=17)
+    gpu, cpu = both(aln, model, rates, props, nslots=tree.ntaxa, safe_numeric=safe)
+    leaf = 0
+    c = tree.adj[leaf][0]
+    tr = W.traversal(tree, c, leaf)
+    gpu.update_partials(tr)
+    cpu.update_partials(tr)
+    dad, node = (LEAF, leaf), (INTERNAL, tr[-1][2])
+    for guess in (tree.get_length(leaf, c), 1e-6, 0.9, 5.0, 10.0):
+        want, nev = _newton_reference(cpu, dad, node, guess)
+        got, d2l, steps = gpu.optimize_branch(dad, node, guess)
+        assert abs(got - want) <= 1e-9 * max(1.0, abs(want)), (guess, got, want)
+        assert steps == nev, (guess, steps, nev)
+        # theta stays valid: lnL from buffer at the optimum equals the oracle's
+        assert abs(gpu.lnl_from_buffer(got) - cpu.lnl_from_buffer(want)) <= 1e-9 * abs(cpu.lnl_from_buffer(want))
