@@ -39,8 +39,20 @@ WORKLOADS = {
     # name: (ntaxa, npatterns, nstates, ncat, nmix, alpha, seed, description)
     "cfg2": (200, 1_000_000, 4, 4, 1, 0.5, 1, "synthetic DNA 200 taxa x 1M patterns, GTR+G4, full traversal + lnL + derv"),
     "cfg3": (500, 200_000, 20, 4, 1, 0.7, 2, "synthetic protein 500 taxa x 200k patterns, 20-state reversible +G4"),
+    # cfg4 is 100k patterns over 8 GPUs (376 GB of partial vectors in all): 12 500 patterns = 47 GB per GPU
+    "cfg4": (100, 12_500, 20, 4, 60, 0.7, 3, "synthetic protein 100 taxa x 100k patterns / 8 GPUs (12.5k per GPU), 20-state 60-class mixture +G4"),
     "small": (50, 100_000, 4, 4, 1, 0.5, 5, "synthetic DNA 50 taxa x 100k patterns, GTR+G4 (smoke size)"),
 }
+
+
+def traversal_flops(tr, N, nstates, ncat_mix):
+    """Algorithmic flops of the partial updates of one traversal:
+    F_K = C * (2 n^2 (k_int + 1) + n) per pattern for a bifurcating node with k_int internal children."""
+    total = 0
+    for e in tr:
+        k = sum(1 for ch in e[3] if ch[0] == 1)
+        total += ncat_mix * (2 * nstates * nstates * (k + 1) + nstates)
+    return total * N
 
 
 def build_workload(name, npatterns=None, seed_shift=0):
@@ -281,6 +293,12 @@ def main():
         peaks = json.load(open(pk))
     peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
     achieved = alg_bytes * args.steps / (partial_ms * 1e-3) / 1e9 if partial_ms > 0 else None
+    alg_flops = traversal_flops(tr, N, n, ncat * nmix)
+    fp64_peak, fp64_src = 37.1, "fallback: DMMA peak measured once with tools/fp64_peak.cu (37.1)"
+    fp = os.path.join(ROOT, "profiles", "r1g_fp64_peak.json")
+    if os.path.exists(fp):
+        fp64_peak, fp64_src = float(json.load(open(fp))["dmma_tflops"]), "profiles/r1g_fp64_peak.json (measured DMMA m8n8k4 peak, tools/fp64_peak.cu)"
+    tflops = alg_flops * args.steps / (partial_ms * 1e-3) / 1e12 if partial_ms > 0 else None
     line = {
         "metric": METRIC, "value": updates_per_step * args.steps / (ms * 1e-3), "unit": UNIT,
         "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps,
@@ -297,17 +315,29 @@ def main():
                 "ms_per_step": e2e_ms / args.steps, "evals_per_sec": args.steps / (e2e_ms * 1e-3)},
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
-        "roofline": {"bound": "hbm", "kernel": "partial update (pruning step)", "achieved": achieved,
+        "roofline": {"bound": "hbm", "kernel": "s4_traverse_kernel (4-state partial update, whole traversal)" if n == 4 else "partial update (pruning step)",
+                     "achieved": achieved,
                      "peak": peak_gbs, "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                      "unit": "GB/s", "frac": (achieved / peak_gbs) if achieved else None, "traffic": None,
                      "algorithmic_bytes_per_step": int(alg_bytes), "kernel_ms_per_step": partial_ms / args.steps,
-                     "launches_per_step": partial_launches / max(1, args.steps)},
+                     "launches_per_step": partial_launches / max(1, args.steps),
+                     "note": "achieved = ALGORITHMIC bytes / kernel time; the 4-state kernel keeps children in registers/shared memory "
+                             "across the traversal and moves fewer bytes than that (see traffic), so frac can exceed 1"},
         "lnl_df_ddf": list(result),
     }
     if not args.no_cpu and world == 1:
         sample = min(args.cpu_sample, N)
         line["cpu_baseline"] = {k: v for k, v in time_cpu(tree, model, rates, props, aln, sample, 3, 1).items()
                                 if k in ("value", "unit", "cores", "kind", "sample", "evals_per_sec")}
+    if n == 20:
+        # 20-state path: FP64 tensor pipe (DMMA) is the bounding unit next to HBM (AI ~ 5 flop/B, at the ridge)
+        hbm = dict(line["roofline"])
+        line["roofline"] = {"bound": "tensor", "kernel": "dense20_kernel (20-state partial update, FP64 DMMA, level-batched)",
+                            "achieved": tflops, "peak": fp64_peak, "peak_source": fp64_src, "unit": "TFLOP/s",
+                            "frac": tflops / fp64_peak if tflops else None, "traffic": None,
+                            "algorithmic_flops_per_step": int(alg_flops), "kernel_ms_per_step": partial_ms / args.steps,
+                            "launches_per_step": partial_launches / max(1, args.steps),
+                            "hbm": {k: hbm[k] for k in ("achieved", "peak", "unit", "frac", "algorithmic_bytes_per_step")}}
     tr_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr_file):  # dram bytes per launch from the committed ncu --set full capture
         try:
