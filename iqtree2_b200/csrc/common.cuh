@@ -89,6 +89,8 @@ struct b200lk_ctx {
     std::vector<cudaEvent_t> *prof_events;  // start/stop pairs
     double prof_ms;
     int64_t prof_launches;
+    unsigned long long *pmax;  // mixture launches of dense.cu: per (node of the level, pattern) max|x| bits
+    size_t pmax_bytes;
     double *red_partial;   // [3][red_blocks] block partial sums
     int red_blocks;
     double *d_result;      // [4] lnL, df, ddf, prob_const

@@ -17,6 +17,8 @@
 // NORM_LH needs max|out| over ALL categories of a pattern before it can decide to rescale: results are
 // stored unscaled, the running max is kept per pattern, and the rare underflowing pattern is rescaled in
 // place afterwards (SAFE_LH decides per category on the spot).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 #define DN_THREADS 128
@@ -35,6 +37,11 @@ struct DenseArgs {
     size_t slot_doubles, slot_scale_bytes;
     int64_t ntot, ntot_pad;
     int node_base, ncm, denom, codes, tiles_per_cta;
+    // mixtures (ncm > DN_CG): grid.z runs over the category groups, so a CTA stages ONE group's tables for all its
+    // tiles and the upper, narrow levels of the tree still fill the machine; the NORM_LH per-pattern maximum is then
+    // combined across CTAs in `pmax` [node of the level][pattern] and applied by dense20_fix_kernel
+    unsigned long long *pmax;
+    int split;
 };
 
 __device__ __forceinline__ void dmma(double &d0, double &d1, double a, double b) {
@@ -89,8 +96,8 @@ __device__ __forceinline__ void dense_child(const DenseArgs &a, const DevChild &
     }
 }
 
-template <bool SAFE>
-__global__ void __launch_bounds__(DN_THREADS, 3) dense20_kernel(DenseArgs a) {
+template <bool SAFE, int MINB>
+__global__ void __launch_bounds__(DN_THREADS, MINB) dense20_kernel(DenseArgs a) {
     extern __shared__ double sm[];
     const int ncm = a.ncm, block = ncm * 20;
     const DevNode nd = a.nodes[a.node_base + blockIdx.y];
@@ -111,7 +118,9 @@ __global__ void __launch_bounds__(DN_THREADS, 3) dense20_kernel(DenseArgs a) {
     if (!SAFE)
         for (int i = tid; i < a.tiles_per_cta * DN_PT; i += DN_THREADS) smax[i] = 0ull;
 
-    for (int c0 = 0; c0 < ncm; c0 += DN_CG) {
+    const int cbeg = a.split ? (int)blockIdx.z * DN_CG : 0;
+    const int cend = a.split ? min(ncm, cbeg + DN_CG) : ncm;
+    for (int c0 = cbeg; c0 < cend; c0 += DN_CG) {
         const int cg = min(DN_CG, ncm - c0);
         __syncthreads();
         // ---- stage this group's tables --------------------------------------------------------------
@@ -227,6 +236,10 @@ __global__ void __launch_bounds__(DN_THREADS, 3) dense20_kernel(DenseArgs a) {
         for (int mt = 0; mt < DN_MT; mt++) {
             const int64_t p = pbase + mt * 8 + g;
             if (p >= a.ntot) continue;
+            if (a.split) {  // this CTA saw one category group only: combine across groups, decide in the fix kernel
+                if (q == 0) atomicMax(&a.pmax[(size_t)blockIdx.y * a.ntot + p], smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g]);
+                continue;
+            }
             const double mx = __longlong_as_double((long long)smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g]);
             const bool under = !tiptip && mx < B200_SCALING_THRESHOLD && a.ptn_invar[p] == 0.0;
             if (under) {  // rare: rescale the stored block in place, the quad shares the work
@@ -236,6 +249,26 @@ __global__ void __launch_bounds__(DN_THREADS, 3) dense20_kernel(DenseArgs a) {
             if (q == 0) sc_out[p] = (uint8_t)((Lleaf ? 0 : scL[p]) + (Rleaf ? 0 : scR[p]) + (under ? 1 : 0));
         }
     }
+}
+
+// NORM_LH decision of the split (mixture) launch: one thread per (node of the level, pattern)
+__global__ void __launch_bounds__(256) dense20_fix_kernel(DenseArgs a) {
+    const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (p >= a.ntot) return;
+    const DevNode nd = a.nodes[a.node_base + blockIdx.y];
+    const DevChild L = a.children[nd.child_begin];
+    const DevChild R = a.children[nd.child_begin + 1];
+    const bool Lleaf = L.kind == B200LK_CHILD_LEAF, Rleaf = R.kind == B200LK_CHILD_LEAF;
+    const double mx = __longlong_as_double((long long)a.pmax[(size_t)blockIdx.y * a.ntot + p]);
+    const bool under = !(Lleaf && Rleaf) && mx < B200_SCALING_THRESHOLD && a.ptn_invar[p] == 0.0;
+    const int block = a.ncm * 20;
+    if (under) {
+        double *po = a.partial + (size_t)nd.out_slot * a.slot_doubles + (size_t)p * block;
+        for (int e = 0; e < block; e++) po[e] *= B200_TWO_256;
+    }
+    const int sl = Lleaf ? 0 : a.scale[(size_t)L.id * a.slot_scale_bytes + p];
+    const int sr = Rleaf ? 0 : a.scale[(size_t)R.id * a.slot_scale_bytes + p];
+    a.scale[(size_t)nd.out_slot * a.slot_scale_bytes + p] = (uint8_t)(sl + sr + (under ? 1 : 0));
 }
 
 // bifurcating nodes [node_base, node_base + nnodes) of the level-sorted device node array
@@ -259,21 +292,52 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes) {
     a.codes = c->d.n_state_codes;
     const int64_t tiles = (c->ntot + DN_PT - 1) / DN_PT;
     // enough CTAs to fill the machine a few times over, but amortise the table staging over several tiles
+    const int ngroups = (a.ncm + DN_CG - 1) / DN_CG;
+    a.split = ngroups > 1;
+    a.pmax = nullptr;
     int tpc = DN_MAX_TILES;
-    while (tpc > 1 && (tiles + tpc - 1) / tpc * nnodes < 148 * 6) tpc >>= 1;
+    while (tpc > 1 && (tiles + tpc - 1) / tpc * nnodes * (a.split ? ngroups : 1) < 148 * 6) tpc >>= 1;
     a.tiles_per_cta = tpc;
+    if (a.split && !c->d.safe_numeric) {
+        const size_t need = sizeof(unsigned long long) * (size_t)nnodes * c->ntot;
+        if (need > c->pmax_bytes) {
+            if (c->pmax) CUDA_TRY(c, cudaFree(c->pmax));
+            c->pmax = nullptr;
+            c->pmax_bytes = 0;
+            CUDA_TRY(c, cudaMalloc(&c->pmax, need));
+            c->pmax_bytes = need;
+        }
+        CUDA_TRY(c, cudaMemsetAsync(c->pmax, 0, need, c->stream));
+        a.pmax = c->pmax;
+    }
     const int leaf_doubles = a.codes * DN_CG * 20, frag_doubles = DN_CG * B200_FRAG20;
     const size_t smem = sizeof(double) * (2 * (size_t)std::max(leaf_doubles, frag_doubles) + frag_doubles) +
                         sizeof(unsigned long long) * tpc * DN_PT;
+    static int occ = -1;  // A/B switch: resident CTAs per SM the kernel is compiled for (registers 160 / 128)
+    if (occ < 0) {
+        const char *e = getenv("B200LK_DENSE_OCC");
+        occ = (e && atoi(e) == 3) ? 3 : 4;
+    }
     if (!c->dense_attr_set) {
-        CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         c->dense_attr_set = true;
     }
-    dim3 grid((unsigned)((tiles + tpc - 1) / tpc), nnodes);
+    dim3 grid((unsigned)((tiles + tpc - 1) / tpc), nnodes, a.split ? ngroups : 1);
     prof_mark(c);
-    if (c->d.safe_numeric) dense20_kernel<true><<<grid, DN_THREADS, smem, c->stream>>>(a);
-    else dense20_kernel<false><<<grid, DN_THREADS, smem, c->stream>>>(a);
+    if (occ == 3) {
+        if (c->d.safe_numeric) dense20_kernel<true, 3><<<grid, DN_THREADS, smem, c->stream>>>(a);
+        else dense20_kernel<false, 3><<<grid, DN_THREADS, smem, c->stream>>>(a);
+    } else {
+        if (c->d.safe_numeric) dense20_kernel<true, 4><<<grid, DN_THREADS, smem, c->stream>>>(a);
+        else dense20_kernel<false, 4><<<grid, DN_THREADS, smem, c->stream>>>(a);
+    }
+    if (a.split && !c->d.safe_numeric) {
+        dense20_fix_kernel<<<dim3((unsigned)((c->ntot + 255) / 256), nnodes), 256, 0, c->stream>>>(a);
+        c->n_launches++;
+    }
     prof_mark(c);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;

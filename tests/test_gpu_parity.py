@@ -174,6 +174,18 @@ def test_protein_mixture_many_categories(oracle_lib):
         assert_parity(full_eval(g, tree, 0), full_eval(o, tree, 0), TOL)
 
 
+@pytest.mark.parametrize("safe", [False, True])
+def test_protein_mixture_deep_tree_rescales_across_category_groups(oracle_lib, safe):
+    """Mixture launches split the category groups over CTAs (grid.z): the NORM_LH decision needs the maximum over
+    ALL groups of a pattern.  Deep tree so that rescaling fires; scale counts must stay bit-exact."""
+    tree, model, rates, props, aln = make_problem(150, 141, nstates=20, nmix=3, seed=19, mean_len=0.5, gaps=0.02,
+                                                  compress=False)
+    g, o = both(aln, model, rates, props, nslots=150, safe_numeric=safe)
+    rg, ro = full_eval(g, tree, 2), full_eval(o, tree, 2)
+    assert max(int(s.max()) for s in ro["scale"].values()) >= 1
+    assert_parity(rg, ro, TOL)
+
+
 def _newton_reference(eng, dad, node, guess, lo=1e-6, hi=10.0, max_steps=100):
     """minimizeNewton (utils/optimization.cpp:422-499) driven through build_theta/derv of an engine."""
     eng.build_theta(dad, node)
