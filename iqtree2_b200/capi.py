@@ -273,16 +273,22 @@ class Engine:
 
 
 def engine_for(aln, model, rates, props, *, nslots, p_invar=0.0, safe_numeric=False, device=0,
-               lib_path=LIB_PATH, prefix="b200lk_"):
+               lib_path=LIB_PATH, prefix="b200lk_", unobserved=None):
     """Create a context for a workload.Alignment + workload.EigenModel and load
     tips, pattern weights and the model (the one-time uploads of
     initializeAllPartialLh / computeTipPartialLikelihood)."""
     from . import workload as W
     eng = Engine(ntaxa=aln.ntaxa, nstates=aln.nstates, ncat=len(rates), nmix=model.nmix, nptn=aln.nptn,
                  nslots=nslots, n_state_codes=aln.state_unknown + 1, safe_numeric=safe_numeric,
-                 device=device, lib_path=lib_path, prefix=prefix)
-    eng.upload_tips(aln.states, aln.ptn_freq)
-    eng.set_ptn_invar(W.ptn_invar(aln, model, p_invar))
+                 device=device, lib_path=lib_path, prefix=prefix,
+                 n_unobserved=0 if unobserved is None else np.asarray(unobserved).shape[1])
+    eng.upload_tips(aln.states, aln.ptn_freq, unobserved)
+    inv = W.ptn_invar(aln, model, p_invar)
+    if unobserved is not None:
+        # +ASC: the unobserved patterns follow the observed ones; their ptn_invar entries are the reference's
+        # "dummy values" p_invar (tree/phylotreesse.cpp:607-609)
+        inv = np.concatenate([inv, np.full(np.asarray(unobserved).shape[1], p_invar)])
+    eng.set_ptn_invar(inv)
     scale = 1.0 - p_invar
     eng.set_model(model.eval, model.evec, model.inv_evec, np.asarray(rates) , np.asarray(props) * scale,
                   model.mixw, W.tip_partial_lh(model))

@@ -10,6 +10,8 @@
 // per-thread order, shuffle tree, then a fixed-order pass over the per-CTA partials.
 #include <cooperative_groups.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 #define RED_THREADS 256
@@ -72,7 +74,9 @@ __device__ __forceinline__ void block_reduce_store(double (&acc)[K], double *red
 }
 
 // fixed-order final pass: result[k] = sum_b red_partial[k][b]
-__global__ void final_reduce_kernel(const double *red_partial, int red_blocks, int K, double *result, int dst0) {
+// (sums k < K0 go to result[dst0 + k], the +ASC sums k >= K0 to result[dst1 + k - K0])
+__global__ void final_reduce_kernel(const double *red_partial, int red_blocks, int K, double *result, int dst0,
+                                    int K0 = 8, int dst1 = 0) {
     __shared__ double sh[RED_THREADS];
     for (int k = 0; k < K; k++) {
         double v = 0.0;
@@ -83,7 +87,7 @@ __global__ void final_reduce_kernel(const double *red_partial, int red_blocks, i
             if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
             __syncthreads();
         }
-        if (threadIdx.x == 0) result[dst0 + k] = sh[0];
+        if (threadIdx.x == 0) result[k < K0 ? dst0 + k : dst1 + k - K0] = sh[0];
         __syncthreads();
     }
 }
@@ -147,11 +151,11 @@ __global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int block = a.block;
     const double *v0 = a.val, *v1 = a.val + block, *v2 = a.val + 2 * block;
-    double acc[2] = {0.0, 0.0};
-    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.nptn; pb += groups_per_grid) {
+    double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};  // df, ddf | +ASC: prob_const, df_const, ddf_const
+    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.ntot; pb += groups_per_grid) {
         int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
-        const bool valid = p < a.nptn;
-        if (!valid) p = a.nptn - 1;
+        const bool valid = p < a.ntot;
+        if (!valid) p = a.ntot - 1;
         const double *th = a.theta;
         double lh = 0.0, df = 0.0, ddf = 0.0;
         for (int j = g; j < block; j += G) {
@@ -165,14 +169,47 @@ __global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red
         ddf = group_sum(ddf, G);
         if (g == 0 && valid) {
             lh = fabs(lh) + a.ptn_invar[p];  // :2494
-            double inv = 1.0 / lh;           // :2497-2505
-            double df_frac = df * inv, ddf_frac = ddf * inv, freq = a.ptn_freq[p];
-            double tmp1 = df_frac * freq, tmp2 = ddf_frac * freq;
-            acc[0] += tmp1;
-            acc[1] += fma(-tmp1, df_frac, tmp2);
+            if (p < a.nptn) {
+                double inv = 1.0 / lh;           // :2497-2505
+                double df_frac = df * inv, ddf_frac = ddf * inv, freq = a.ptn_freq[p];
+                double tmp1 = df_frac * freq, tmp2 = ddf_frac * freq;
+                acc[0] += tmp1;
+                acc[1] += fma(-tmp1, df_frac, tmp2);
+            } else {  // +ASC (Lewis) unobserved pattern, :2506-2534
+                if (a.buffer_scale_all[p] != 0.0) {
+                    lh *= B200_SCALING_THRESHOLD;
+                    df *= B200_SCALING_THRESHOLD;
+                    ddf *= B200_SCALING_THRESHOLD;
+                }
+                acc[2] += lh;
+                acc[3] += df;
+                acc[4] += ddf;
+            }
         }
     }
-    block_reduce_store<2>(acc, a.red_partial, red_blocks);
+    if (a.ntot > a.nptn) block_reduce_store<5>(acc, a.red_partial, red_blocks);
+    else {
+        double acc2[2] = {acc[0], acc[1]};
+        block_reduce_store<2>(acc2, a.red_partial, red_blocks);
+    }
+}
+
+// +ASC (Lewis) corrections applied to the reduced sums (:2620-2628, 3160-3182).  result: [0] lnL, [1] df, [2] ddf,
+// [8] prob_const, [9] df_const, [10] ddf_const.  mode 0: lnL (+ per-pattern lnL), mode 1: derivatives.
+__global__ void asc_fix_kernel(double *result, double *pattern_lh, int64_t nptn, double nsite, int mode) {
+    if (mode == 1) {
+        if (blockIdx.x == 0 && threadIdx.x == 0 && isfinite(result[1])) {
+            const double prob = 1.0 - result[8];
+            const double df_frac = result[9] / prob, ddf_frac = result[10] / prob;
+            result[1] += nsite * df_frac;
+            result[2] += nsite * (ddf_frac + df_frac * df_frac);
+        }
+        return;
+    }
+    const double pc = log(1.0 - result[8]);
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < nptn; p += (int64_t)gridDim.x * blockDim.x)
+        pattern_lh[p] -= pc;
+    if (blockIdx.x == 0 && threadIdx.x == 0) result[0] -= nsite * pc;
 }
 
 // ---- Newton-Raphson on the device ---------------------------------------------
@@ -322,23 +359,29 @@ __global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(BranchArgs a, int 
     const int G = a.G, g = threadIdx.x & (G - 1);
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int block = a.block;
-    double acc[1] = {0.0};
-    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.nptn; pb += groups_per_grid) {
+    double acc[2] = {0.0, 0.0};  // lnL | +ASC prob_const
+    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.ntot; pb += groups_per_grid) {
         int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
-        const bool valid = p < a.nptn;
-        if (!valid) p = a.nptn - 1;
+        const bool valid = p < a.ntot;
+        if (!valid) p = a.ntot - 1;
         const double *th = a.theta;
         double lh = 0.0;
         for (int j = g; j < block; j += G) lh = fma(a.val[j], th[E(j)], lh);
         lh = group_sum(lh, G);
         if (g == 0 && valid) {
             lh = fabs(lh) + a.ptn_invar[p];               // :3295
-            lh = log(fabs(lh)) + a.buffer_scale_all[p];   // :3300
-            a.pattern_lh[p] = lh;
-            acc[0] = fma(lh, a.ptn_freq[p], acc[0]);
+            if (p < a.nptn) {
+                lh = log(fabs(lh)) + a.buffer_scale_all[p];   // :3300
+                a.pattern_lh[p] = lh;
+                acc[0] = fma(lh, a.ptn_freq[p], acc[0]);
+            } else {  // +ASC unobserved pattern
+                if (a.buffer_scale_all[p] != 0.0) lh *= B200_SCALING_THRESHOLD;
+                a.pattern_lh[p] = lh;
+                acc[1] += lh;
+            }
         }
     }
-    block_reduce_store<1>(acc, a.red_partial, red_blocks);
+    block_reduce_store<2>(acc, a.red_partial, red_blocks);
 }
 
 // ---- lnL at a branch -------------------------------------------------------
@@ -349,11 +392,11 @@ __global__ void __launch_bounds__(RED_THREADS) lnl_kernel(BranchArgs a, int red_
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int n = a.n, ncm = a.ncm, block = a.block;
     const bool tip_mode = a.pnode == nullptr;
-    double acc[1] = {0.0};
-    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.nptn; pb += groups_per_grid) {
+    double acc[2] = {0.0, 0.0};  // lnL | +ASC prob_const
+    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.ntot; pb += groups_per_grid) {
         int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
-        const bool valid = p < a.nptn;
-        if (!valid) p = a.nptn - 1;
+        const bool valid = p < a.ntot;
+        if (!valid) p = a.ntot - 1;
         const double *pd = a.pdad;
         const double *w = tip_mode ? a.tip_val + (size_t)a.dad_states[p] * block : a.val;
         const double *pn = a.pnode;
@@ -398,12 +441,18 @@ __global__ void __launch_bounds__(RED_THREADS) lnl_kernel(BranchArgs a, int red_
         lh = group_sum(lh, G);
         if (g == 0 && valid) {
             lh = fabs(lh) + a.ptn_invar[p];                                        // :2907, 3038
-            lh = log(lh) + (double)min_scale * B200_LOG_SCALING_THRESHOLD;        // :2909, 3041
-            a.pattern_lh[p] = lh;
-            acc[0] = fma(lh, a.ptn_freq[p], acc[0]);
+            if (p < a.nptn) {
+                lh = log(lh) + (double)min_scale * B200_LOG_SCALING_THRESHOLD;    // :2909, 3041
+                a.pattern_lh[p] = lh;
+                acc[0] = fma(lh, a.ptn_freq[p], acc[0]);
+            } else {  // +ASC unobserved pattern (:2912-2930)
+                if (min_scale != 0) lh *= B200_SCALING_THRESHOLD;
+                a.pattern_lh[p] = lh;
+                acc[1] += lh;
+            }
         }
     }
-    block_reduce_store<1>(acc, a.red_partial, red_blocks);
+    block_reduce_store<2>(acc, a.red_partial, red_blocks);
 }
 
 // repair pass for non-finite per-pattern lnL (:3085-3094, 3338-3347)
@@ -469,6 +518,15 @@ static int grid_for(const b200lk_ctx *c, int G, int64_t npat) {
     return (int)(need < c->red_blocks ? need : c->red_blocks);
 }
 
+static int launch_asc_fix(b200lk_ctx *c, int mode) {
+    if (c->d.n_unobserved == 0) return B200LK_OK;
+    const int grid = mode == 1 ? 1 : (int)std::min<int64_t>(c->red_blocks, (c->d.nptn + 255) / 256);
+    asc_fix_kernel<<<grid, 256, 0, c->stream>>>(c->d_result, c->pattern_lh, c->d.nptn, c->nsite, mode);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches++;
+    return B200LK_OK;
+}
+
 static int launch_val(b200lk_ctx *c, double length, int want_tip) {
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     val_kernel<<<1, 256, 0, c->stream>>>(c->m, length, c->val, c->tip_val, c->d.nstates, c->d.ncat, c->ncat_mix,
@@ -485,13 +543,13 @@ int launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double len
     fill_args(c, a, dad, node);
     fill_common(c, a);
     a.G = pick_group(c->ncat_mix);
-    int grid = grid_for(c, a.G, c->d.nptn);
+    int grid = grid_for(c, a.G, c->ntot);
     lnl_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, grid);
     CUDA_TRY(c, cudaGetLastError());
-    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 1, c->d_result, 0);
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 2, c->d_result, 0, 1, 8);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches += 2;
-    return B200LK_OK;
+    return launch_asc_fix(c, 0);
 }
 
 int launch_repair(b200lk_ctx *c) {
@@ -523,13 +581,13 @@ int launch_derv(b200lk_ctx *c, double length) {
     memset(&a, 0, sizeof(a));
     fill_common(c, a);
     a.G = pick_group(c->block);
-    int grid = grid_for(c, a.G, c->d.nptn);
+    int grid = grid_for(c, a.G, c->ntot);
     derv_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, grid);
     CUDA_TRY(c, cudaGetLastError());
-    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 2, c->d_result, 1);
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, c->d.n_unobserved ? 5 : 2, c->d_result, 1, 2, 8);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches += 2;
-    return B200LK_OK;
+    return launch_asc_fix(c, 1);
 }
 
 int launch_from_buffer(b200lk_ctx *c, double length) {
@@ -539,13 +597,13 @@ int launch_from_buffer(b200lk_ctx *c, double length) {
     memset(&a, 0, sizeof(a));
     fill_common(c, a);
     a.G = pick_group(c->block);
-    int grid = grid_for(c, a.G, c->d.nptn);
+    int grid = grid_for(c, a.G, c->ntot);
     frombuf_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, grid);
     CUDA_TRY(c, cudaGetLastError());
-    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 1, c->d_result, 0);
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 2, c->d_result, 0, 1, 8);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches += 2;
-    return B200LK_OK;
+    return launch_asc_fix(c, 0);
 }
 
 // b200lk_optimize_branch: theta for (dad, node) must already be built
@@ -566,7 +624,7 @@ int launch_newton(b200lk_ctx *c, const b200lk_newton *nr) {
     na.out = c->d_result + 4;
     na.red = c->red_partial;  // [2 parities][2][red_blocks] of its 8 * red_blocks doubles
     const size_t smem = sizeof(double) * 3 * c->block;
-    if (smem > 200 * 1024) return B200LK_ERR_UNSUPPORTED;
+    if (smem > 200 * 1024 || c->d.n_unobserved > 0) return B200LK_ERR_UNSUPPORTED;  // +ASC: host-driven iteration
     if (smem > 48 * 1024)
         CUDA_TRY(c, cudaFuncSetAttribute(newton_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0, sms = 148, coop = 0;

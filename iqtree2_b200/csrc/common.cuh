@@ -93,7 +93,8 @@ struct b200lk_ctx {
     size_t pmax_bytes;
     double *red_partial;   // [3][red_blocks] block partial sums
     int red_blocks;
-    double *d_result;      // [4] lnL, df, ddf, prob_const
+    double nsite;          // sum of ptn_freq (aln->getNSite()), for the +ASC correction
+    double *d_result;      // [16] lnL, df, ddf, -, optx, d2l, evals, status, prob_const, df_const, ddf_const
     double *h_result;      // pinned
     bool model_set, tips_set, theta_computed;
     int theta_dad_kind;

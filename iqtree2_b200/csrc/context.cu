@@ -88,8 +88,8 @@ static int alloc_all(b200lk_ctx *c) {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
     c->red_blocks = sms * 8;
     CUDA_TRY(c, cudaMalloc(&c->red_partial, sizeof(double) * 8 * c->red_blocks));
-    CUDA_TRY(c, cudaMalloc(&c->d_result, sizeof(double) * 8));
-    CUDA_TRY(c, cudaMemset(c->d_result, 0, sizeof(double) * 8));
+    CUDA_TRY(c, cudaMalloc(&c->d_result, sizeof(double) * 16));
+    CUDA_TRY(c, cudaMemset(c->d_result, 0, sizeof(double) * 16));
     CUDA_TRY(c, cudaMallocHost(&c->h_result, sizeof(double) * 8));
     return B200LK_OK;
 }
@@ -194,6 +194,8 @@ extern "C" int b200lk_upload_tips(b200lk_ctx *c, const uint8_t *states, const ui
                                       cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(c, cudaMemcpyAsync(c->ptn_freq, ptn_freq, sizeof(double) * nptn, cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    c->nsite = 0.0;
+    for (int64_t p = 0; p < nptn; p++) c->nsite += ptn_freq[p];
     c->tips_set = true;
     return B200LK_OK;
 }

@@ -157,10 +157,11 @@ class HostTree:
     """b200::PhyloTree set up in the reference's order (readTree, setAlignment, setModel, setLikelihoodKernel
     (LK_CUDA), initializeAllPartialLh)."""
 
-    def __init__(self, newick, aln, model, rate, safe=False, device=0, device_newton=True):
+    def __init__(self, newick, aln, model, rate, safe=False, device=0, device_newton=True, asc=False):
         self.h = C.c_void_p()
         self._keep = (aln, model, rate)
-        _ck(lib().b200host_tree_new(C.byref(self.h), newick.encode(), aln.h, model.h, rate.h, int(safe), device,
+        _ck(lib().b200host_tree_new(C.byref(self.h), newick.encode(), aln.h, model.h, rate.h,
+                                    int(bool(safe)) | (2 if asc else 0), device,
                                     int(device_newton)))
         self.aln = aln
 

@@ -185,6 +185,7 @@ struct Params {  // the few fields of utils/tools.h Params the path reads
     double min_branch_length = 1e-6;  // utils/tools.cpp:1209, main/phyloanalysis.cpp:4171-4175
     double max_branch_length = 10.0;  // utils/tools.cpp:1212
     bool lk_safe_scaling = false;     // -safe
+    bool asc_lewis = false;           // +ASC: Lewis' correction for variable-sites-only data
     int numseq_safe_scaling = 2000;   // utils/tools.cpp:1235-1236
     int device = 0;
     bool device_newton = true;        // run minimizeNewton's iteration on the device when the library offers it

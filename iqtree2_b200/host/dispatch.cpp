@@ -111,7 +111,10 @@ void PhyloTree::initializeAllPartialLh() {
     d.n_state_codes = aln->STATE_UNKNOWN + 1;
     d.nslots = nint + 2;
     d.nptn = (int64_t)aln->getNPattern();
-    d.n_unobserved = 0;
+    // +ASC (Lewis): the nstates constant patterns are the unobserved ones (ModelFactory, model/modelfactory.cpp:
+    // "unobserved_ptns" built by Alignment::getUnobservedConstPatterns for ASC_VARIANT)
+    const bool asc = params && params->asc_lewis;
+    d.n_unobserved = asc ? aln->num_states : 0;
     d.device = params ? params->device : 0;
     int rc = k.create(&ctx, &d);
     if (rc != B200LK_OK || !ctx) {
@@ -121,7 +124,13 @@ void PhyloTree::initializeAllPartialLh() {
     }
     kernel_calls++;
     // tip states in alignment-row order == taxon id used in traversal descriptors
-    check(k.upload_tips(ctx, aln->states.data(), NULL, aln->ptn_freq.data()), "b200lk_upload_tips");
+    std::vector<uint8_t> unobs;
+    if (asc) {
+        unobs.resize((size_t)leafNum * aln->num_states);
+        for (int t = 0; t < leafNum; t++)
+            for (int x = 0; x < aln->num_states; x++) unobs[(size_t)t * aln->num_states + x] = (uint8_t)x;
+    }
+    check(k.upload_tips(ctx, aln->states.data(), asc ? unobs.data() : NULL, aln->ptn_freq.data()), "b200lk_upload_tips");
     kernel_calls++;
     model_changed = true;
     buffers_ready = true;
@@ -153,8 +162,11 @@ void PhyloTree::syncModel() {
           "b200lk_set_model");
     // ptn_invar
     const size_t nptn = aln->getNPattern();
-    std::vector<double> inv(nptn, 0.0), fr(n);
+    const size_t nunobs = (params && params->asc_lewis) ? (size_t)n : 0;
     const double p_invar = site_rate->getPInvar();
+    // entries of the unobserved (+ASC) patterns are the reference's "dummy values" p_invar (:607-609)
+    std::vector<double> inv(nptn + nunobs, p_invar), fr(n);
+    std::fill(inv.begin(), inv.begin() + nptn, 0.0);
     if (p_invar != 0.0) {
         model->getStateFrequency(fr.data(), -1);
         for (size_t p = 0; p < nptn; p++) {
@@ -429,10 +441,15 @@ void PhyloTree::optimizeOneBranch(PhyloNode *node1, PhyloNode *node2, bool clear
         nr.min_len = lo; nr.max_len = hi; nr.xacc = lo; nr.guess = current_len;
         nr.max_steps = maxNRStep; nr.reserved = 0;
         int32_t steps = 0;
-        check(k.optimize_branch(ctx, de, ne, &nr, &optx, &negative_lh, &steps), "b200lk_optimize_branch");
+        const int rc = k.optimize_branch(ctx, de, ne, &nr, &optx, &negative_lh, &steps);
         kernel_calls++;
-        theta_computed = true;
-        current_it->length = current_it_back->length = optx;
+        if (rc == B200LK_ERR_UNSUPPORTED) {  // e.g. +ASC: the iteration is driven from the host instead
+            optx = minimizeNewton(lo, current_len, hi, lo, negative_lh, maxNRStep);
+        } else {
+            check(rc, "b200lk_optimize_branch");
+            theta_computed = true;
+            current_it->length = current_it_back->length = optx;
+        }
     } else {
         optx = minimizeNewton(lo, current_len, hi, lo, negative_lh, maxNRStep);
     }

@@ -115,7 +115,8 @@ int b200host_tree_new(void **out, const char *newick, void *aln, void *model, vo
                       int device_newton) {
     HostTree *h = new HostTree();
     try {
-        h->params.lk_safe_scaling = safe != 0;
+        h->params.lk_safe_scaling = (safe & 1) != 0;
+        h->params.asc_lewis = (safe & 2) != 0;  // bit 1 of `safe`: +ASC
         h->params.device = device;
         h->params.device_newton = device_newton != 0;
         h->tree = new PhyloTree();

@@ -49,7 +49,8 @@ class RefRun:
     """One PhyloTree of the reference with caller-supplied alignment, tree, eigen-system and rates
     (ref_harness.cpp).  kernel: LK_SSE2 (Vec2d), LK_AVX (Vec4d), LK_AVX_FMA (Vec4d + FMA)."""
 
-    def __init__(self, tree, aln, model, rates, props, *, kernel=LK_AVX_FMA, safe=False, threads=1, p_invar=0.0):
+    def __init__(self, tree, aln, model, rates, props, *, kernel=LK_AVX_FMA, safe=False, threads=1, p_invar=0.0,
+                 unobserved=None):
         import ctypes as C
         import numpy as np
         from iqtree2_b200 import workload as W
@@ -80,14 +81,28 @@ class RefRun:
         pb = Problem(aln.ntaxa, aln.nstates, len(rates), model.nmix, aln.state_unknown + 1, kernel, int(safe),
                      threads, aln.nptn, ptr(k[0]), ptr(k[1]), newick, ptr(k[2]), ptr(k[3]), ptr(k[4]), p_invar,
                      ptr(k[5]), ptr(k[6]), ptr(k[7]), ptr(k[8]), ptr(k[9]))
+        if unobserved is not None:  # +ASC (Lewis): [ntaxa][n_unobserved] state codes
+            un = np.ascontiguousarray(unobserved, dtype=np.uint8)
+            self.lib.ref_set_next_unobserved(un.shape[1], C.c_void_p(un.ctypes.data), un.shape[0])
         self.lib.ref_create.restype = C.c_void_p
         self.h = C.c_void_p(self.lib.ref_create(C.byref(pb)))
         self.nptn, self.ncm, self.n = aln.nptn, len(rates) * model.nmix, aln.nstates
         self.tree = tree
-        for fn in ("ref_lnl_at_leaf", "ref_lnl_again", "ref_from_buffer", "ref_optimize_current_branch"):
+        for fn in ("ref_lnl_at_leaf", "ref_lnl_again", "ref_from_buffer", "ref_optimize_current_branch",
+                   "ref_optimize_all_branches", "ref_compute_likelihood", "ref_branch_length"):
             getattr(self.lib, fn).restype = C.c_double
         self.safe_numeric = bool(self.lib.ref_safe_numeric(self.h))
         self.vector_size = self.lib.ref_vector_size(self.h)
+
+    def optimize_all_branches(self, iterations=100, tolerance=0.001):
+        return self.lib.ref_optimize_all_branches(self.h, iterations, self.C.c_double(tolerance))
+
+    def compute_likelihood(self):
+        return self.lib.ref_compute_likelihood(self.h)
+
+    def branch_length(self, leaves, from_taxon=0):
+        arr = self.np.ascontiguousarray(sorted(leaves), dtype=self.np.int32)
+        return self.lib.ref_branch_length(self.h, self.C.c_void_p(arr.ctypes.data), len(arr), from_taxon)
 
     def lnl_at_leaf(self, taxon):
         return self.lib.ref_lnl_at_leaf(self.h, taxon)

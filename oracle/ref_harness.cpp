@@ -161,6 +161,15 @@ struct ref_problem {
 
 static bool params_ready = false;
 
+// +ASC (Lewis): unobserved patterns of the NEXT ref_create, [ntaxa][n] state codes (model_factory->unobserved_ptns,
+// model/modelfactory.h:241; read by the kernels at tree/phylokernelnew.h:1500-1512, 2912-2930, 3137-3183)
+static std::vector<uint8_t> next_unobserved;
+static int next_n_unobserved = 0;
+void ref_set_next_unobserved(int n_unobserved, const uint8_t *codes, int ntaxa) {
+    next_n_unobserved = n_unobserved;
+    next_unobserved.assign(codes, codes + (size_t)(n_unobserved > 0 ? n_unobserved : 0) * ntaxa);
+}
+
 #include <execinfo.h>
 #include <signal.h>
 #include <unistd.h>
@@ -232,6 +241,17 @@ void *ref_create(const ref_problem *pb) {
     ModelFactory *f = new ModelFactory();
     f->model = m;
     f->site_rate = r;
+    if (next_n_unobserved > 0) {
+        f->ASC_type = ASC_VARIANT;  // Lewis (utils/tools.h:549-555)
+        for (int u = 0; u < next_n_unobserved; u++) {
+            Pattern pat;
+            pat.resize(pb->ntaxa);
+            for (int t = 0; t < pb->ntaxa; t++) pat[t] = next_unobserved[(size_t)t * next_n_unobserved + u];
+            pat.frequency = 0;
+            f->unobserved_ptns.push_back(pat);
+        }
+        next_n_unobserved = 0;
+    }
     h->model = m;
     h->rate = r;
     h->factory = f;
@@ -314,6 +334,23 @@ double ref_optimize_current_branch(void *hv, int max_steps) {
     return h->tree->current_it->length;
 }
 
+// PhyloTree::optimizeAllBranches as the reference runs it (tree/phylotree.cpp:2689-2765)
+double ref_optimize_all_branches(void *hv, int iterations, double tolerance) {
+    RefHandle *h = (RefHandle *)hv;
+    h->tree->clearAllPartialLH();
+    h->tree->current_it = h->tree->current_it_back = NULL;
+    return h->tree->optimizeAllBranches(iterations, tolerance);
+}
+// PhyloTree::computeLikelihood (tree/phylotree.cpp:1227-1268): the reference's own root choice
+double ref_compute_likelihood(void *hv) {
+    RefHandle *h = (RefHandle *)hv;
+    h->tree->clearAllPartialLH();
+    h->tree->current_it = h->tree->current_it_back = NULL;
+    return h->tree->computeLikelihood();
+}
+// length of the branch that separates the (sorted) leaf set from the rest
+double ref_branch_length(void *hv, const int32_t *leaves, int nleaves, int from_taxon);
+
 void ref_pattern_lh(void *hv, double *out) {
     RefHandle *h = (RefHandle *)hv;
     memcpy(out, h->tree->_pattern_lh, sizeof(double) * h->aln->size());
@@ -375,6 +412,16 @@ int ref_fetch_branch(void *hv, const int32_t *leaves, int nleaves, int from_taxo
     }
     (void)n;
     return 0;
+}
+
+double ref_branch_length(void *hv, const int32_t *leaves, int nleaves, int from_taxon) {
+    RefHandle *h = (RefHandle *)hv;
+    std::vector<int> want(leaves, leaves + nleaves);
+    PhyloNode *start = find_leaf(h->tree, from_taxon);
+    if (!start) return -1.0;
+    if (nleaves == 1 && leaves[0] == from_taxon) return start->neighbors[0]->length;
+    PhyloNeighbor *nb = find_branch(start, NULL, want);
+    return nb ? nb->length : -2.0;
 }
 
 void ref_destroy(void *hv) {

@@ -248,3 +248,21 @@ def test_device_newton_raphson_follows_the_reference_iteration(oracle_lib, nstat
         assert steps == nev, (guess, steps, nev)
         # theta stays valid: lnL from buffer at the optimum equals the oracle's
         assert abs(gpu.lnl_from_buffer(got) - cpu.lnl_from_buffer(want)) <= 1e-9 * abs(cpu.lnl_from_buffer(want))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nstates,safe", [(4, False), (4, True), (20, False), (5, True)])
+def test_ascertainment_bias_correction(oracle_lib, nstates, safe):
+    """+ASC (Lewis): unobserved constant patterns appended after the observed ones; the log(1 - prob_const)
+    correction reaches lnL, per-pattern lnL, df/ddf and lnL-from-buffer (oracle pinned against the reference's own
+    kernel in tests/test_oracle_vs_ref.py::test_ascertainment_bias_correction_lewis)."""
+    tree, model, rates, props, aln = make_problem(11, 333 if nstates == 4 else 77, nstates=nstates, seed=29)
+    unobs = np.repeat(np.arange(nstates, dtype=np.uint8)[None, :], tree.ntaxa, axis=0)
+    g, o = both(aln, model, rates, props, nslots=tree.ntaxa, safe_numeric=safe, unobserved=unobs)
+    rg, ro = full_eval(g, tree, 0), full_eval(o, tree, 0)
+    assert_parity(rg, ro, TOL)
+    for t in (0.01, 0.3):
+        a, b = g.lnl_from_buffer(t), o.lnl_from_buffer(t)
+        assert abs(a - b) <= TOL * abs(b)
+        da, db = g.derv(t), o.derv(t)
+        assert all(abs(x - y) <= TOL * max(1.0, abs(y)) for x, y in zip(da, db))

@@ -319,3 +319,39 @@ def test_host_example_phy_cuda(cuda_backend):
     opt = t.optimize_all_branches()
     if "opt_lnl" in g.files:
         assert abs(opt - float(g["opt_lnl"])) < 2e-3
+
+
+def scenario_asc():
+    """+ASC through the host layer: Params::asc_lewis appends the constant patterns; Newton-Raphson falls back to
+    the host-driven iteration where the device one does not offer the correction."""
+    import oracle
+    from iqtree2_b200.capi import INTERNAL, LEAF
+    tree, model, rates, props, aln = make_problem(8, 200, seed=41)
+    unobs = np.repeat(np.arange(4, dtype=np.uint8)[None, :], tree.ntaxa, axis=0)
+    eng = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa, unobserved=unobs)
+    c = tree.adj[0][0]
+    tr = W.traversal(tree, c, 0)
+    want = eng.evaluate(tr, (LEAF, 0), (INTERNAL, tr[-1][2]), tree.get_length(0, c))[0]
+    cols = np.repeat(aln.states, aln.ptn_freq.astype(int), axis=1)
+    ha = H.HostAlignment.from_states(cols, 4, compress=True)
+    t = H.HostTree(relabel(tree), ha, H.HostModel.from_eigen(model), H.HostRate.categories(rates, props), asc=True)
+    got = t.compute_likelihood()
+    assert abs(got - want) <= 1e-9 * abs(want)
+    better = t.optimize_all_branches()
+    assert better >= got
+    return got, better
+
+
+def test_host_asc_oracle_backend(oracle_backend):
+    scenario_asc()
+
+
+@pytest.mark.gpu
+def test_host_asc_cuda(cuda_backend, oracle_lib):
+    a = scenario_asc()
+    H.set_kernel_library(oracle_lib, "orc_")
+    try:
+        b = scenario_asc()
+    finally:
+        H.set_kernel_library(None, None)
+    assert abs(a[0] - b[0]) <= 1e-9 * abs(b[0]) and abs(a[1] - b[1]) <= 1e-7 * abs(b[1])

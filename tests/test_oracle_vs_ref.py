@@ -7,6 +7,7 @@ import pytest
 
 import oracle
 from iqtree2_b200 import workload as W
+from iqtree2_b200.capi import INTERNAL, LEAF
 from tests.common import full_eval, make_problem, rel
 
 pytestmark = pytest.mark.skipif(not oracle.ref_available(), reason="oracle/_ref not built")
@@ -139,3 +140,35 @@ def test_odd_state_count_quirk_is_the_reference_s(oracle_lib):
     oracle.set_ref_quirks(True)
     assert rel(rdf[0], out[True]["df"]) <= 1e-9
     ref.close()
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates", [4, 20])
+def test_ascertainment_bias_correction_lewis(oracle_lib, safe, nstates):
+    """+ASC (Lewis): the nstates constant patterns are appended as unobserved patterns; lnL, per-pattern lnL,
+    df/ddf and lnL-from-buffer carry the log(1 - prob_const) correction (tree/phylokernelnew.h:2506-2534,
+    2620-2628, 2912-2930, 3160-3182)."""
+    tree, model, rates, props, aln = make_problem(9, 150 if nstates == 4 else 40, nstates=nstates, seed=23)
+    unobs = np.repeat(np.arange(nstates, dtype=np.uint8)[None, :], tree.ntaxa, axis=0)
+    ref = oracle.RefRun(tree, aln, model, rates, props, kernel=oracle.LK_AVX_FMA, safe=safe, unobserved=unobs)
+    eng = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa, safe_numeric=safe, unobserved=unobs)
+    leaf = 0
+    c = tree.adj[leaf][0]
+    tr = W.traversal(tree, c, leaf)
+    L = tree.get_length(leaf, c)
+    eng.update_partials(tr)
+    dad, node = (LEAF, leaf), (INTERNAL, tr[-1][2])
+    want = ref.lnl_at_leaf(leaf)
+    got = eng.branch_lnl(dad, node, L)
+    plain = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa, safe_numeric=safe)
+    plain.update_partials(tr)
+    assert abs(plain.branch_lnl(dad, node, L) - want) > 1e-3  # the correction is not a no-op
+    assert abs(got - want) <= 1e-11 * abs(want)
+    assert np.allclose(eng.fetch_pattern_lh(), ref.pattern_lh(), rtol=1e-11, atol=1e-11)
+    eng.build_theta(dad, node)
+    df, ddf = eng.derv(L)
+    rdf, rddf = ref.derv()
+    assert abs(df - rdf) <= 1e-9 * max(1.0, abs(rdf)) and abs(ddf - rddf) <= 1e-9 * max(1.0, abs(rddf))
+    for t in (0.5 * L, 2.0 * L):
+        ref.set_current_length(t)
+        assert abs(eng.lnl_from_buffer(t) - ref.from_buffer()) <= 1e-11 * abs(want)
