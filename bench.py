@@ -41,6 +41,7 @@ WORKLOADS = {
     "cfg3": (500, 200_000, 20, 4, 1, 0.7, 2, "synthetic protein 500 taxa x 200k patterns, 20-state reversible +G4"),
     # cfg4 is 100k patterns over 8 GPUs (376 GB of partial vectors in all): 12 500 patterns = 47 GB per GPU
     "cfg4": (100, 12_500, 20, 4, 60, 0.7, 3, "synthetic protein 100 taxa x 100k patterns / 8 GPUs (12.5k per GPU), 20-state 60-class mixture +G4"),
+    "cfg5": (100, 1000, 4, 4, 1, 0.5, 4, "partitioned supermatrix (see run_partitioned)"),
     "small": (50, 100_000, 4, 4, 1, 0.5, 5, "synthetic DNA 50 taxa x 100k patterns, GTR+G4 (smoke size)"),
 }
 
@@ -176,6 +177,118 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def run_partitioned(args):
+    """cfg5: supermatrix of `--genes` genes x ~1k patterns, alternating GTR+G4 / 20-state+G4, edge-linked
+    proportional branch lengths, through the C++ host layer's PhyloSuperTree (one context and stream per gene,
+    all genes of an evaluation enqueued before any result is read).  A step = every partial of every gene stale
+    -> PhyloSuperTree::computeLikelihood.  N > 1: whole genes placed on GPUs by LPT on the reference's cost
+    T*N*n (b200::placePartitions); the only exchange is the all-reduce of the summed lnL."""
+    import torch
+    import torch.distributed as dist
+    from iqtree2_b200 import build_host, host as H, multigpu as MG, workload as W
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback on this path")
+    torch.cuda.set_device(local)
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    build_host.build()
+    T, G = 100, args.genes
+    rng = np.random.default_rng(4)
+    lengths = rng.integers(500, 1501, size=G)
+    part_rates = rng.gamma(2.0, 0.5, size=G)
+    nst = np.where(np.arange(G) % 2 == 0, 4, 20)
+    cost = T * lengths.astype(float) * nst
+    place = MG.place_partitions(cost, world)
+    mine = [g for g in range(G) if place[g] == rank]
+    tree = W.random_tree(T, 4)
+    names = tree.names
+    tree.names = ["T%d" % i for i in range(T)]
+    newick = tree.to_newick(0, 17)
+    tree.names = names
+    st = H.HostSuperTree(newick, edge_linked=True, device=local)
+    dna, aa = W.gtr_model(), W.random_reversible_model(20, 104)
+    rates, props = W.discrete_gamma(0.5)
+    updates = 0
+    for g in mine:
+        model = dna if nst[g] == 4 else aa
+        scaled = W.random_tree(T, 4)
+        for (u, v) in scaled.branches():
+            scaled.set_length(u, v, min(9.0, tree.get_length(u, v) * part_rates[g]))
+        aln = W.simulate_alignment(scaled, model, rates, props, int(lengths[g]), 5000 + g, compress=False)
+        st.add_partition("gene%d" % g, H.HostAlignment.from_states(aln.states, int(nst[g]), compress=False),
+                         H.HostModel.from_eigen(model), H.HostRate.categories(rates, props), float(part_rates[g]))
+        updates += (T - 2) * aln.nptn
+    st.initialize()
+    total = torch.zeros(1, dtype=torch.float64, device="cuda")
+
+    def step():
+        st.clear_partials()
+        lnl = st.compute_likelihood()
+        if world > 1:
+            total[0] = lnl
+            dist.all_reduce(total)
+            return float(total[0])
+        return lnl
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        lnl = step()
+    calls0 = st.kernel_calls()
+    sampler = ClockSampler(local)
+    sampler.start()
+    sync_all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        lnl = step()
+    e1.record()
+    sync_all()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    ms = max(e0.elapsed_time(e1), wall_ms)  # every step ends with a blocking read: wall clock and events agree
+    sampler.stop_flag = True
+    sampler.join()
+    t = torch.tensor([ms, float(updates)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tm = t.clone()
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t)
+        ms, updates_all = float(tm[0]), float(t[1])
+    else:
+        updates_all = float(updates)
+    if rank == 0:
+        val = updates_all * args.steps / (ms * 1e-3)
+        line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic (seeded AliSim-equivalent sampler per gene)",
+                "config": {"workload": "cfg5: partitioned supermatrix, %d genes x U(500,1500) patterns, 100 taxa, alternating "
+                                       "GTR+G4 / 20-state+G4, edge-linked proportional; lnL evaluation of the whole supermatrix" % G,
+                           "genes": G, "genes_this_rank": len(mine), "placement": "LPT on T*N*n",
+                           "l2": "every gene's partial vectors are rewritten each step (%.1f GB in all, larger than L2)" % (updates_all * 8 * 48 / 1e9)},
+                "evals_per_sec": args.steps / (ms * 1e-3),
+                "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": int(G * (198 * 16 + 98 * 16)),
+                        "d2h_bytes_per_step": 8 * G,
+                        "note": "the timed call IS the host-facing call (b200::PhyloSuperTree::computeLikelihood): traversal "
+                                "descriptors H2D and per-gene lnL D2H are inside the timed region"},
+                "gpu_launches": None, "kernel_abi_calls_per_step": (st.kernel_calls() - calls0) / args.steps,
+                "clocks": sampler.summary(), "lnl": lnl,
+                "roofline": {"bound": "hbm", "kernel": "launch-bound regime (1000 small contexts): see DESIGN.md 6",
+                             "achieved": None, "peak": None, "unit": "GB/s", "frac": None, "traffic": None}}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -186,9 +299,12 @@ def main():
     ap.add_argument("--patterns", type=int, default=0, help="override patterns per GPU (debug)")
     ap.add_argument("--cpu-sample", type=int, default=100_000, help="patterns in the CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--genes", type=int, default=1000, help="cfg5: number of genes")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "cfg5":
+        return run_partitioned(args)
 
     import torch
     import torch.distributed as dist

@@ -7,7 +7,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "libb200host.so")
 CXX = os.environ.get("B200_CXX", "/usr/bin/g++")  # the system compiler: its libstdc++.so is the one python extensions share
-FLAGS = ["-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-Wno-unused-function"]
+FLAGS = ["-O2", "-std=c++17", "-fPIC", "-shared", "-fopenmp", "-Wall", "-Wno-unused-function"]
 
 
 def sources():

@@ -231,7 +231,7 @@ public:
     void computeFuncDerv(double value, double &df, double &ddf);             // tree/phylotree.cpp:2520-2527
     void optimizeOneBranch(PhyloNode *node1, PhyloNode *node2, bool clearLH = true, int maxNRStep = 100);
     virtual double optimizeAllBranches(int my_iterations = 100, double tolerance = TOL_LIKELIHOOD, int maxNRStep = 100);
-    void clearAllPartialLH();
+    virtual void clearAllPartialLH();
     // utils/optimization.cpp:422-499
     double minimizeNewton(double x1, double xguess, double x2, double xacc, double &d2l, int maxNRStep = 100);
 
@@ -312,6 +312,7 @@ public:
     std::vector<PartitionInfo> part_info;
     std::vector<int> part_order;     // by decreasing cost (computePartitionOrder, tree/phylosupertree.cpp:654-700)
     bool edge_linked = true;
+    int num_threads_partitions = 0;  // host threads that enqueue partitions (0: all cores, at most 16)
     ~PhyloSuperTree();
     // partition p: its alignment, model and rates (ownership stays with the caller); the topology is the super-tree's
     void addPartition(const std::string &name, Alignment *a, ModelSubst *m, RateHeterogeneity *r, double part_rate = 1.0);
@@ -319,6 +320,7 @@ public:
     void setLikelihoodKernel(LikelihoodKernel lk) override;  // tree/phylosupertree.cpp:211-215: propagate
     void initializeAllPartialLh() override;
     void mapBranchLengths();  // super-tree lengths x part_rate -> partition trees (edge-linked)
+    void clearAllPartialLH() override;
     double computeLikelihood(double *pattern_lh = NULL) override;  // tree/phylosupertree.cpp:701-725: sum over partitions
     // edge-linked Newton-Raphson: df = sum_p rate_p df_p, ddf = sum_p rate_p^2 ddf_p (phylosupertreeplen.cpp:400-402)
     void computeFuncDervLinked(PhyloNode *node1, PhyloNode *node2, double value, double &df, double &ddf);

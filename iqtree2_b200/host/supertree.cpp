@@ -9,6 +9,8 @@
 #include <math.h>
 
 #include <algorithm>
+#include <stdexcept>
+#include <thread>
 
 #include "b200host.h"
 
@@ -44,6 +46,11 @@ void PhyloSuperTree::computePartitionOrder() {
     std::stable_sort(part_order.begin(), part_order.end(), [&](int a, int b) { return cost[a] > cost[b]; });
 }
 
+void PhyloSuperTree::clearAllPartialLH() {
+    PhyloTree::clearAllPartialLH();
+    for (PhyloTree *t : parts) t->clearAllPartialLH();
+}
+
 void PhyloSuperTree::setLikelihoodKernel(LikelihoodKernel lk) {
     sse = lk;
     if (lk != LK_CUDA)
@@ -54,6 +61,10 @@ void PhyloSuperTree::setLikelihoodKernel(LikelihoodKernel lk) {
 
 void PhyloSuperTree::initializeAllPartialLh() {
     computePartitionOrder();
+    if (num_threads_partitions <= 0) {
+        const unsigned hw = std::thread::hardware_concurrency();
+        num_threads_partitions = (int)std::max(1u, std::min(hw, 16u));
+    }
     for (PhyloTree *t : parts) t->initializeAllPartialLh();
     mapBranchLengths();
 }
@@ -83,28 +94,43 @@ double PhyloSuperTree::computeLikelihood(double *pattern_lh) {
         curScore = total;
         return total;
     }
-    // enqueue every partition (own stream each), then collect: the partitions overlap on the device
-    std::vector<std::vector<b200lk_node>> nodes(parts.size());
-    std::vector<std::vector<b200lk_child>> children(parts.size());
-    for (int p : part_order) {
-        PhyloTree *t = parts[p];
-        t->syncModel();
-        if (!t->current_it) {
-            PhyloNode *leaf = t->findFarthestLeaf();
-            t->current_it = leaf->neighbors[0];
-            t->current_it_back = t->current_it->node->findNeighbor(leaf);
+    // enqueue every partition (own stream each), then collect: the partitions overlap on the device.  Like the
+    // reference (tree/phylosupertree.cpp:716, OpenMP over partitions) the fan-out runs on host threads: every
+    // context is independently thread-safe, and a launch-bound supermatrix (1000 small genes) is limited by how fast
+    // the host can enqueue.
+    const int np = (int)part_order.size();
+    std::vector<std::string> errors(np);
+#ifdef _OPENMP
+#pragma omp parallel for schedule(dynamic, 4) num_threads(num_threads_partitions)
+#endif
+    for (int i = 0; i < np; i++) {
+        const int p = part_order[i];
+        try {
+            PhyloTree *t = parts[p];
+            std::vector<b200lk_node> nodes;
+            std::vector<b200lk_child> children;
+            t->syncModel();
+            if (!t->current_it) {
+                PhyloNode *leaf = t->findFarthestLeaf();
+                t->current_it = leaf->neighbors[0];
+                t->current_it_back = t->current_it->node->findNeighbor(leaf);
+            }
+            PhyloNode *dad = t->current_it_back->node;
+            t->computeTraversalInfo(t->current_it->node, dad);
+            t->packTraversal(nodes, children);
+            t->traversal_info.clear();
+            b200lk_end de, ne;
+            t->branchEnds(t->current_it, dad, de, ne);
+            t->check(k.evaluate_async(t->ctx, nodes.data(), (int32_t)nodes.size(), children.data(),
+                                      (int32_t)children.size(), de, ne, t->current_it->length, 1, 0),
+                     "b200lk_evaluate_async");
+            t->kernel_calls++;
+        } catch (const std::exception &e) {
+            errors[i] = e.what();
         }
-        PhyloNode *dad = t->current_it_back->node;
-        t->computeTraversalInfo(t->current_it->node, dad);
-        t->packTraversal(nodes[p], children[p]);
-        t->traversal_info.clear();
-        b200lk_end de, ne;
-        t->branchEnds(t->current_it, dad, de, ne);
-        t->check(k.evaluate_async(t->ctx, nodes[p].data(), (int32_t)nodes[p].size(), children[p].data(),
-                                  (int32_t)children[p].size(), de, ne, t->current_it->length, 1, 0),
-                 "b200lk_evaluate_async");
-        t->kernel_calls++;
     }
+    for (const std::string &e : errors)
+        if (!e.empty()) outError(e);
     for (int p : part_order) {
         double lnl = 0.0;
         parts[p]->check(k.read_results(parts[p]->ctx, &lnl, NULL, NULL), "b200lk_read_results");
