@@ -251,6 +251,475 @@ __global__ void __launch_bounds__(DN_THREADS, MINB) dense20_kernel(DenseArgs a) 
     }
 }
 
+// ---- pipelined variant --------------------------------------------------------------------------------------------
+// Same arithmetic, different operand path: every warp prefetches the [16 patterns x 20] operand tiles of the NEXT
+// (tile, category) step of its internal children into a private shared-memory double buffer with cp.async (16-byte
+// chunks, L2 only) while its tensor-core chain works on the current step, so that HBM latency is no longer exposed
+// between the load and the first DMMA (the level-batched kernel above sat on long_scoreboard at 12-16 warps per SM).
+#define DN_STAGE_DOUBLES (2 * 16 * 20)  // one stage of one warp: two children x 16 patterns x 20
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N)); }
+
+// factor of an internal child from the staged operand tile `sa` ([16][20] doubles), fragment tables `sT`
+__device__ __forceinline__ void dense_child_staged(const double *sa, const double *sT, int cl, int lane,
+                                                   double (&f)[DN_MT][6]) {
+    const int g = lane >> 2, q = lane & 3;
+    double A[DN_MT][5];
+#pragma unroll
+    for (int mt = 0; mt < DN_MT; mt++) {
+#pragma unroll
+        for (int s = 0; s < 5; s++) A[mt][s] = sa[(mt * 8 + g) * 20 + 4 * s + q];
+#pragma unroll
+        for (int k = 0; k < 6; k++) f[mt][k] = 0.0;
+    }
+    const double *B = sT + (size_t)cl * B200_FRAG20 + lane;
+#pragma unroll
+    for (int s = 0; s < 5; s++) {
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const double b = B[(j * 5 + s) * 32];
+#pragma unroll
+            for (int mt = 0; mt < DN_MT; mt++) dmma(f[mt][2 * j], f[mt][2 * j + 1], A[mt][s], b);
+        }
+    }
+}
+
+__device__ __forceinline__ void dense_leaf_lookup(const double *sT, int cg, int cl, const int (&st)[DN_MT], int lane,
+                                                  double (&f)[DN_MT][6]) {
+    const int q = lane & 3;
+#pragma unroll
+    for (int mt = 0; mt < DN_MT; mt++) {
+        const double *row = sT + ((size_t)st[mt] * cg + cl) * 20;
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            if (8 * j + 2 * q < 20) {
+                const double2 v = *reinterpret_cast<const double2 *>(row + 8 * j + 2 * q);
+                f[mt][2 * j] = v.x;
+                f[mt][2 * j + 1] = v.y;
+            } else {
+                f[mt][2 * j] = 0.0;
+                f[mt][2 * j + 1] = 0.0;
+            }
+        }
+    }
+}
+
+template <bool SAFE>
+__global__ void __launch_bounds__(DN_THREADS, 2) dense20_pipe_kernel(DenseArgs a) {
+    extern __shared__ double sm[];
+    const int ncm = a.ncm, block = ncm * 20;
+    const DevNode nd = a.nodes[a.node_base + blockIdx.y];
+    const DevChild L = a.children[nd.child_begin];
+    const DevChild R = a.children[nd.child_begin + 1];
+    const bool Lleaf = L.kind == B200LK_CHILD_LEAF, Rleaf = R.kind == B200LK_CHILD_LEAF;
+    const bool tiptip = Lleaf && Rleaf;
+    const int leaf_doubles = a.codes * DN_CG * 20, frag_doubles = DN_CG * B200_FRAG20;
+    const int child_doubles = leaf_doubles > frag_doubles ? leaf_doubles : frag_doubles;
+    double *sL = sm, *sR = sL + child_doubles, *sI = sR + child_doubles;
+    unsigned long long *smax = reinterpret_cast<unsigned long long *>(sI + frag_doubles);
+    double *stage_all = reinterpret_cast<double *>(smax + a.tiles_per_cta * DN_PT);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, q = lane & 3;
+    double *wbuf = stage_all + (size_t)warp * 2 * DN_STAGE_DOUBLES;  // [2 stages][2 children][16][20]
+    const int64_t tile0 = (int64_t)blockIdx.x * a.tiles_per_cta;
+    double *out_base = a.partial + (size_t)nd.out_slot * a.slot_doubles;
+    uint8_t *sc_out = a.scale + (size_t)nd.out_slot * a.slot_scale_bytes;
+    const uint8_t *scL = Lleaf ? nullptr : a.scale + (size_t)L.id * a.slot_scale_bytes;
+    const uint8_t *scR = Rleaf ? nullptr : a.scale + (size_t)R.id * a.slot_scale_bytes;
+    const double *pL = Lleaf ? nullptr : a.partial + (size_t)L.id * a.slot_doubles;
+    const double *pR = Rleaf ? nullptr : a.partial + (size_t)R.id * a.slot_doubles;
+    if (!SAFE)
+        for (int i = tid; i < a.tiles_per_cta * DN_PT; i += DN_THREADS) smax[i] = 0ull;
+    // tiles this warp really has (its 16-pattern strip of each 64-pattern tile)
+    int my_tiles = 0;
+    for (int t = 0; t < a.tiles_per_cta; t++)
+        if ((tile0 + t) * DN_PT + warp * (8 * DN_MT) < a.ntot) my_tiles = t + 1;
+
+    const int cbeg = a.split ? (int)blockIdx.z * DN_CG : 0;
+    const int cend = a.split ? min(ncm, cbeg + DN_CG) : ncm;
+    for (int c0 = cbeg; c0 < cend; c0 += DN_CG) {
+        const int cg = min(DN_CG, ncm - c0);
+        __syncthreads();
+        if (Lleaf) {
+            const double *src = a.tables + L.leaf_off;
+            for (int i = tid; i < a.codes * cg * 20; i += DN_THREADS) {
+                const int s = i / (cg * 20), r = i - s * (cg * 20);
+                sL[i] = src[(size_t)s * block + c0 * 20 + r];
+            }
+        } else {
+            const double *src = a.tables + L.frag_off + (size_t)c0 * B200_FRAG20;
+            for (int i = tid; i < cg * B200_FRAG20; i += DN_THREADS) sL[i] = src[i];
+        }
+        if (Rleaf) {
+            const double *src = a.tables + R.leaf_off;
+            for (int i = tid; i < a.codes * cg * 20; i += DN_THREADS) {
+                const int s = i / (cg * 20), r = i - s * (cg * 20);
+                sR[i] = src[(size_t)s * block + c0 * 20 + r];
+            }
+        } else {
+            const double *src = a.tables + R.frag_off + (size_t)c0 * B200_FRAG20;
+            for (int i = tid; i < cg * B200_FRAG20; i += DN_THREADS) sR[i] = src[i];
+        }
+        for (int i = tid; i < cg * B200_FRAG20; i += DN_THREADS) {
+            const int cl = i / B200_FRAG20;
+            sI[i] = a.inv_frag[(size_t)((c0 + cl) / a.denom) * B200_FRAG20 + (i - cl * B200_FRAG20)];
+        }
+        __syncthreads();
+
+        const int nsteps = my_tiles * cg;
+        // operand tiles of step `step` -> stage `stage` of this warp's buffer
+        auto prefetch = [&](int step, int stage) {
+            const int t = step / cg, cl = step - t * cg;
+            const int64_t pbase = (tile0 + t) * DN_PT + warp * (8 * DN_MT);
+            double *dst = wbuf + (size_t)stage * DN_STAGE_DOUBLES;
+#pragma unroll
+            for (int j = 0; j < 5; j++) {
+                const int k = lane + 32 * j, row = k / 10, col = k - row * 10;
+                int64_t p = pbase + row;
+                if (p >= a.ntot) p = a.ntot - 1;
+                const size_t off = (size_t)p * block + (size_t)(c0 + cl) * 20 + col * 2;
+                if (!Lleaf) cp_async16(dst + row * 20 + col * 2, pL + off);
+                if (!Rleaf) cp_async16(dst + 320 + row * 20 + col * 2, pR + off);
+            }
+        };
+        if (nsteps > 0 && !tiptip) prefetch(0, 0);
+        cp_async_commit();
+        int stL[DN_MT] = {0, 0}, stR[DN_MT] = {0, 0};
+        int64_t p[DN_MT] = {0, 0}, pc[DN_MT] = {0, 0};
+        bool invar0[DN_MT] = {false, false};
+        unsigned long long rmax[DN_MT] = {0ull, 0ull};
+        for (int step = 0; step < nsteps; step++) {
+            const int t = step / cg, cl = step - t * cg, c = c0 + cl;
+            if (step + 1 < nsteps && !tiptip) prefetch(step + 1, (step + 1) & 1);
+            cp_async_commit();
+            if (cl == 0) {  // new tile: rows, tip states
+                const int64_t pbase = (tile0 + t) * DN_PT + warp * (8 * DN_MT);
+#pragma unroll
+                for (int mt = 0; mt < DN_MT; mt++) {
+                    p[mt] = pbase + mt * 8 + g;
+                    pc[mt] = p[mt] < a.ntot ? p[mt] : a.ntot - 1;
+                    invar0[mt] = a.ptn_invar[pc[mt]] == 0.0;
+                    if (Lleaf) stL[mt] = a.states[(size_t)L.id * a.ntot_pad + pc[mt]];
+                    if (Rleaf) stR[mt] = a.states[(size_t)R.id * a.ntot_pad + pc[mt]];
+                    rmax[mt] = 0ull;
+                }
+            }
+            cp_async_wait<1>();
+            __syncwarp();
+            const double *sa = wbuf + (size_t)(step & 1) * DN_STAGE_DOUBLES;
+            double fl[DN_MT][6], fr[DN_MT][6];
+            if (Lleaf) dense_leaf_lookup(sL, cg, cl, stL, lane, fl);
+            else dense_child_staged(sa, sL, cl, lane, fl);
+            if (Rleaf) dense_leaf_lookup(sR, cg, cl, stR, lane, fr);
+            else dense_child_staged(sa + 320, sR, cl, lane, fr);
+            __syncwarp();  // the stage may be overwritten by the prefetch issued in the next iteration
+            const double *B = sI + (size_t)cl * B200_FRAG20 + lane;
+#pragma unroll
+            for (int mt = 0; mt < DN_MT; mt++) {
+                double tmp[6];
+#pragma unroll
+                for (int k = 0; k < 6; k++) tmp[k] = fl[mt][k] * fr[mt][k];
+                const int srcl = (lane & ~3) | (q >> 1);
+                const double v0 = __shfl_sync(0xffffffffu, tmp[4], srcl), v1 = __shfl_sync(0xffffffffu, tmp[5], srcl);
+                const double a4 = (q & 1) ? v1 : v0;
+                double o[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                for (int jo = 0; jo < 3; jo++) {
+#pragma unroll
+                    for (int kk = 0; kk < 4; kk++) dmma(o[2 * jo], o[2 * jo + 1], tmp[kk], B[(jo * 5 + kk) * 32]);
+                    dmma(o[2 * jo], o[2 * jo + 1], a4, B[(jo * 5 + 4) * 32]);
+                }
+                unsigned long long mx = 0ull;
+#pragma unroll
+                for (int k = 0; k < 6; k++) {
+                    const unsigned long long b = (unsigned long long)__double_as_longlong(o[k]) & 0x7fffffffffffffffull;
+                    mx = b > mx ? b : mx;
+                }
+                int sc = 0;
+                if (SAFE) {
+                    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+                    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+                    sc = (Lleaf ? 0 : scL[pc[mt] * ncm + c]) + (Rleaf ? 0 : scR[pc[mt] * ncm + c]);
+                    if (!tiptip && __longlong_as_double((long long)mx) < B200_SCALING_THRESHOLD && invar0[mt]) {
+#pragma unroll
+                        for (int k = 0; k < 6; k++) o[k] *= B200_TWO_256;
+                        sc += 1;
+                    }
+                } else {
+                    rmax[mt] = mx > rmax[mt] ? mx : rmax[mt];
+                }
+                if (p[mt] < a.ntot) {
+                    double *po = out_base + (size_t)p[mt] * block + c * 20 + 2 * q;
+                    *reinterpret_cast<double2 *>(po) = make_double2(o[0], o[1]);
+                    *reinterpret_cast<double2 *>(po + 8) = make_double2(o[2], o[3]);
+                    if (q < 2) *reinterpret_cast<double2 *>(po + 16) = make_double2(o[4], o[5]);
+                    if (SAFE && q == 0) sc_out[p[mt] * ncm + c] = (uint8_t)sc;
+                }
+            }
+            if (!SAFE && cl == cg - 1) {  // last category of this group for the tile: fold the running maximum
+#pragma unroll
+                for (int mt = 0; mt < DN_MT; mt++) {
+                    unsigned long long mx = rmax[mt];
+                    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+                    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+                    if (q == 0) {
+                        unsigned long long *slot = &smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g];
+                        if (mx > *slot) *slot = mx;
+                    }
+                }
+            }
+        }
+        cp_async_wait<0>();
+    }
+    if (SAFE) return;
+    __syncwarp();
+    for (int t = 0; t < a.tiles_per_cta; t++) {
+        const int64_t pbase = (tile0 + t) * DN_PT + warp * (8 * DN_MT);
+        if (pbase >= a.ntot) break;
+#pragma unroll
+        for (int mt = 0; mt < DN_MT; mt++) {
+            const int64_t pp = pbase + mt * 8 + g;
+            if (pp >= a.ntot) continue;
+            if (a.split) {
+                if (q == 0) atomicMax(&a.pmax[(size_t)blockIdx.y * a.ntot + pp], smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g]);
+                continue;
+            }
+            const double mx = __longlong_as_double((long long)smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g]);
+            const bool under = !tiptip && mx < B200_SCALING_THRESHOLD && a.ptn_invar[pp] == 0.0;
+            if (under) {
+                double *po = out_base + (size_t)pp * block;
+                for (int e = q; e < block; e += 4) po[e] *= B200_TWO_256;
+            }
+            if (q == 0) sc_out[pp] = (uint8_t)((Lleaf ? 0 : scL[pp]) + (Rleaf ? 0 : scR[pp]) + (under ? 1 : 0));
+        }
+    }
+}
+
+// ---- register-prefetch variant ------------------------------------------------------------------------------------
+// The operand fragments of BOTH internal children of step s+1 are requested while the tensor-core chain of step s
+// is still running: the left child's fragments right after its product has consumed them, the right child's after
+// its product; HBM latency then hides behind >= 60 DMMAs of the same warp instead of stalling the first DMMA of
+// every product (ncu: ~40 % of all stall samples sat on those DMMAs).
+__device__ __forceinline__ void dense_load_A(const double *base, size_t block, int c, const int64_t (&pc)[DN_MT], int q,
+                                             double (&A)[DN_MT][5]) {
+#pragma unroll
+    for (int mt = 0; mt < DN_MT; mt++) {
+        const double *src = base + (size_t)pc[mt] * block + c * 20 + q;
+#pragma unroll
+        for (int s = 0; s < 5; s++) A[mt][s] = __ldg(src + 4 * s);
+    }
+}
+__device__ __forceinline__ void dense_mma_child(const double (&A)[DN_MT][5], const double *sT, int cl, int lane,
+                                                double (&f)[DN_MT][6]) {
+#pragma unroll
+    for (int mt = 0; mt < DN_MT; mt++)
+#pragma unroll
+        for (int k = 0; k < 6; k++) f[mt][k] = 0.0;
+    const double *B = sT + (size_t)cl * B200_FRAG20 + lane;
+#pragma unroll
+    for (int s = 0; s < 5; s++) {
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const double b = B[(j * 5 + s) * 32];
+#pragma unroll
+            for (int mt = 0; mt < DN_MT; mt++) dmma(f[mt][2 * j], f[mt][2 * j + 1], A[mt][s], b);
+        }
+    }
+}
+
+template <bool SAFE>
+__global__ void __launch_bounds__(DN_THREADS, 3) dense20_rp_kernel(DenseArgs a) {
+    extern __shared__ double sm[];
+    const int ncm = a.ncm, block = ncm * 20;
+    const DevNode nd = a.nodes[a.node_base + blockIdx.y];
+    const DevChild L = a.children[nd.child_begin];
+    const DevChild R = a.children[nd.child_begin + 1];
+    const bool Lleaf = L.kind == B200LK_CHILD_LEAF, Rleaf = R.kind == B200LK_CHILD_LEAF;
+    const bool tiptip = Lleaf && Rleaf;
+    const int leaf_doubles = a.codes * DN_CG * 20, frag_doubles = DN_CG * B200_FRAG20;
+    const int child_doubles = leaf_doubles > frag_doubles ? leaf_doubles : frag_doubles;
+    double *sL = sm, *sR = sL + child_doubles, *sI = sR + child_doubles;
+    unsigned long long *smax = reinterpret_cast<unsigned long long *>(sI + frag_doubles);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, q = lane & 3;
+    const int64_t tile0 = (int64_t)blockIdx.x * a.tiles_per_cta;
+    double *out_base = a.partial + (size_t)nd.out_slot * a.slot_doubles;
+    uint8_t *sc_out = a.scale + (size_t)nd.out_slot * a.slot_scale_bytes;
+    const uint8_t *scL = Lleaf ? nullptr : a.scale + (size_t)L.id * a.slot_scale_bytes;
+    const uint8_t *scR = Rleaf ? nullptr : a.scale + (size_t)R.id * a.slot_scale_bytes;
+    const double *pL = Lleaf ? nullptr : a.partial + (size_t)L.id * a.slot_doubles;
+    const double *pR = Rleaf ? nullptr : a.partial + (size_t)R.id * a.slot_doubles;
+    if (!SAFE)
+        for (int i = tid; i < a.tiles_per_cta * DN_PT; i += DN_THREADS) smax[i] = 0ull;
+    int my_tiles = 0;
+    for (int t = 0; t < a.tiles_per_cta; t++)
+        if ((tile0 + t) * DN_PT + warp * (8 * DN_MT) < a.ntot) my_tiles = t + 1;
+
+    const int cbeg = a.split ? (int)blockIdx.z * DN_CG : 0;
+    const int cend = a.split ? min(ncm, cbeg + DN_CG) : ncm;
+    for (int c0 = cbeg; c0 < cend; c0 += DN_CG) {
+        const int cg = min(DN_CG, ncm - c0);
+        __syncthreads();
+        if (Lleaf) {
+            const double *src = a.tables + L.leaf_off;
+            for (int i = tid; i < a.codes * cg * 20; i += DN_THREADS) {
+                const int s = i / (cg * 20), r = i - s * (cg * 20);
+                sL[i] = src[(size_t)s * block + c0 * 20 + r];
+            }
+        } else {
+            const double *src = a.tables + L.frag_off + (size_t)c0 * B200_FRAG20;
+            for (int i = tid; i < cg * B200_FRAG20; i += DN_THREADS) sL[i] = src[i];
+        }
+        if (Rleaf) {
+            const double *src = a.tables + R.leaf_off;
+            for (int i = tid; i < a.codes * cg * 20; i += DN_THREADS) {
+                const int s = i / (cg * 20), r = i - s * (cg * 20);
+                sR[i] = src[(size_t)s * block + c0 * 20 + r];
+            }
+        } else {
+            const double *src = a.tables + R.frag_off + (size_t)c0 * B200_FRAG20;
+            for (int i = tid; i < cg * B200_FRAG20; i += DN_THREADS) sR[i] = src[i];
+        }
+        for (int i = tid; i < cg * B200_FRAG20; i += DN_THREADS) {
+            const int cl = i / B200_FRAG20;
+            sI[i] = a.inv_frag[(size_t)((c0 + cl) / a.denom) * B200_FRAG20 + (i - cl * B200_FRAG20)];
+        }
+        __syncthreads();
+
+        const int nsteps = my_tiles * cg;
+        // rows of the tile a step belongs to (clamped so that out-of-range rows read the last pattern)
+        auto rows_of = [&](int step, int64_t (&pp)[DN_MT], int64_t (&ppc)[DN_MT]) {
+            const int t = step / cg;
+            const int64_t pbase = (tile0 + t) * DN_PT + warp * (8 * DN_MT);
+#pragma unroll
+            for (int mt = 0; mt < DN_MT; mt++) {
+                pp[mt] = pbase + mt * 8 + g;
+                ppc[mt] = pp[mt] < a.ntot ? pp[mt] : a.ntot - 1;
+            }
+        };
+        double AL[DN_MT][5], AR[DN_MT][5];
+        int64_t p[DN_MT] = {0, 0}, pc[DN_MT] = {0, 0}, pn[DN_MT], pcn[DN_MT];
+        if (nsteps > 0) {
+            rows_of(0, pn, pcn);
+            if (!Lleaf) dense_load_A(pL, block, c0, pcn, q, AL);
+            if (!Rleaf) dense_load_A(pR, block, c0, pcn, q, AR);
+        }
+        int stL[DN_MT] = {0, 0}, stR[DN_MT] = {0, 0};
+        bool invar0[DN_MT] = {false, false};
+        unsigned long long rmax[DN_MT] = {0ull, 0ull};
+        for (int step = 0; step < nsteps; step++) {
+            const int t = step / cg, cl = step - t * cg, c = c0 + cl;
+            const bool more = step + 1 < nsteps;
+            const int cn = c0 + (more ? (step + 1) % cg : 0);
+            if (more) rows_of(step + 1, pn, pcn);
+            if (cl == 0) {
+                rows_of(step, p, pc);
+#pragma unroll
+                for (int mt = 0; mt < DN_MT; mt++) {
+                    invar0[mt] = a.ptn_invar[pc[mt]] == 0.0;
+                    if (Lleaf) stL[mt] = a.states[(size_t)L.id * a.ntot_pad + pc[mt]];
+                    if (Rleaf) stR[mt] = a.states[(size_t)R.id * a.ntot_pad + pc[mt]];
+                    rmax[mt] = 0ull;
+                }
+            }
+            double fl[DN_MT][6], fr[DN_MT][6];
+            if (Lleaf) dense_leaf_lookup(sL, cg, cl, stL, lane, fl);
+            else {
+                dense_mma_child(AL, sL, cl, lane, fl);
+                if (more) dense_load_A(pL, block, cn, pcn, q, AL);  // next step's left operands, in flight from here
+            }
+            if (Rleaf) dense_leaf_lookup(sR, cg, cl, stR, lane, fr);
+            else {
+                dense_mma_child(AR, sR, cl, lane, fr);
+                if (more) dense_load_A(pR, block, cn, pcn, q, AR);
+            }
+            const double *B = sI + (size_t)cl * B200_FRAG20 + lane;
+#pragma unroll
+            for (int mt = 0; mt < DN_MT; mt++) {
+                double tmp[6];
+#pragma unroll
+                for (int k = 0; k < 6; k++) tmp[k] = fl[mt][k] * fr[mt][k];
+                const int srcl = (lane & ~3) | (q >> 1);
+                const double v0 = __shfl_sync(0xffffffffu, tmp[4], srcl), v1 = __shfl_sync(0xffffffffu, tmp[5], srcl);
+                const double a4 = (q & 1) ? v1 : v0;
+                double o[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                for (int jo = 0; jo < 3; jo++) {
+#pragma unroll
+                    for (int kk = 0; kk < 4; kk++) dmma(o[2 * jo], o[2 * jo + 1], tmp[kk], B[(jo * 5 + kk) * 32]);
+                    dmma(o[2 * jo], o[2 * jo + 1], a4, B[(jo * 5 + 4) * 32]);
+                }
+                // |x| < 2^-256  <=>  high word of |x| < 0x2FF00000: the running maximum needs the high words only
+                unsigned hmx = 0u;
+#pragma unroll
+                for (int k = 0; k < 6; k++) {
+                    const unsigned h = (unsigned)__double2hiint(o[k]) & 0x7fffffffu;
+                    hmx = h > hmx ? h : hmx;
+                }
+                unsigned long long mx = (unsigned long long)hmx << 32;
+                int sc = 0;
+                if (SAFE) {
+                    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+                    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+                    sc = (Lleaf ? 0 : scL[pc[mt] * ncm + c]) + (Rleaf ? 0 : scR[pc[mt] * ncm + c]);
+                    if (!tiptip && __longlong_as_double((long long)mx) < B200_SCALING_THRESHOLD && invar0[mt]) {
+#pragma unroll
+                        for (int k = 0; k < 6; k++) o[k] *= B200_TWO_256;
+                        sc += 1;
+                    }
+                } else {
+                    rmax[mt] = mx > rmax[mt] ? mx : rmax[mt];
+                }
+                if (p[mt] < a.ntot) {
+                    double *po = out_base + (size_t)p[mt] * block + c * 20 + 2 * q;
+                    *reinterpret_cast<double2 *>(po) = make_double2(o[0], o[1]);
+                    *reinterpret_cast<double2 *>(po + 8) = make_double2(o[2], o[3]);
+                    if (q < 2) *reinterpret_cast<double2 *>(po + 16) = make_double2(o[4], o[5]);
+                    if (SAFE && q == 0) sc_out[p[mt] * ncm + c] = (uint8_t)sc;
+                }
+            }
+            if (!SAFE && cl == cg - 1) {
+#pragma unroll
+                for (int mt = 0; mt < DN_MT; mt++) {
+                    unsigned long long mx = rmax[mt];
+                    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+                    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+                    if (q == 0) {
+                        unsigned long long *slot = &smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g];
+                        if (mx > *slot) *slot = mx;
+                    }
+                }
+            }
+        }
+    }
+    if (SAFE) return;
+    __syncwarp();
+    for (int t = 0; t < a.tiles_per_cta; t++) {
+        const int64_t pbase = (tile0 + t) * DN_PT + warp * (8 * DN_MT);
+        if (pbase >= a.ntot) break;
+#pragma unroll
+        for (int mt = 0; mt < DN_MT; mt++) {
+            const int64_t pp = pbase + mt * 8 + g;
+            if (pp >= a.ntot) continue;
+            if (a.split) {
+                if (q == 0) atomicMax(&a.pmax[(size_t)blockIdx.y * a.ntot + pp], smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g]);
+                continue;
+            }
+            const double mx = __longlong_as_double((long long)smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g]);
+            const bool under = !tiptip && mx < B200_SCALING_THRESHOLD && a.ptn_invar[pp] == 0.0;
+            if (under) {
+                double *po = out_base + (size_t)pp * block;
+                for (int e = q; e < block; e += 4) po[e] *= B200_TWO_256;
+            }
+            if (q == 0) sc_out[pp] = (uint8_t)((Lleaf ? 0 : scL[pp]) + (Rleaf ? 0 : scR[pp]) + (under ? 1 : 0));
+        }
+    }
+}
+
 // NORM_LH decision of the split (mixture) launch: one thread per (node of the level, pattern)
 __global__ void __launch_bounds__(256) dense20_fix_kernel(DenseArgs a) {
     const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;
@@ -313,6 +782,12 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes) {
     const int leaf_doubles = a.codes * DN_CG * 20, frag_doubles = DN_CG * B200_FRAG20;
     const size_t smem = sizeof(double) * (2 * (size_t)std::max(leaf_doubles, frag_doubles) + frag_doubles) +
                         sizeof(unsigned long long) * tpc * DN_PT;
+    static int pipe = -1;  // A/B switch: cp.async operand pipeline (default) / direct loads (B200LK_DENSE_PIPE=0)
+    if (pipe < 0) {
+        const char *e = getenv("B200LK_DENSE_PIPE");
+        pipe = e ? atoi(e) : 2;  // 0 direct loads, 1 cp.async double buffer, 2 register prefetch (default)
+    }
+    const size_t smem_pipe = smem + sizeof(double) * (DN_THREADS / 32) * 2 * DN_STAGE_DOUBLES;
     static int occ = -1;  // A/B switch: resident CTAs per SM the kernel is compiled for (registers 160 / 128)
     if (occ < 0) {
         const char *e = getenv("B200LK_DENSE_OCC");
@@ -323,11 +798,21 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes) {
         CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_pipe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_pipe_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_rp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_rp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         c->dense_attr_set = true;
     }
     dim3 grid((unsigned)((tiles + tpc - 1) / tpc), nnodes, a.split ? ngroups : 1);
     prof_mark(c);
-    if (occ == 3) {
+    if (pipe == 2) {
+        if (c->d.safe_numeric) dense20_rp_kernel<true><<<grid, DN_THREADS, smem, c->stream>>>(a);
+        else dense20_rp_kernel<false><<<grid, DN_THREADS, smem, c->stream>>>(a);
+    } else if (pipe == 1) {
+        if (c->d.safe_numeric) dense20_pipe_kernel<true><<<grid, DN_THREADS, smem_pipe, c->stream>>>(a);
+        else dense20_pipe_kernel<false><<<grid, DN_THREADS, smem_pipe, c->stream>>>(a);
+    } else if (occ == 3) {
         if (c->d.safe_numeric) dense20_kernel<true, 3><<<grid, DN_THREADS, smem, c->stream>>>(a);
         else dense20_kernel<false, 3><<<grid, DN_THREADS, smem, c->stream>>>(a);
     } else {
