@@ -76,6 +76,7 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
         dc.echild_off = (int64_t)off;
         off += (size_t)block * n + block;  // echild, then expv
         dc.frag_off = -1;
+        dc.aux_off = -1;
         if (c->dense20) {
             dc.frag_off = (int64_t)off;
             off += (size_t)c->ncat_mix * B200_FRAG20;
@@ -127,27 +128,45 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
         c->theta_computed = false;
         return B200LK_OK;
     }
-    // level-sorted node array, bifurcating before multifurcating inside a level
+    // level-sorted node array; inside a level: tip-tip nodes (20-state path: answered from a per-node table over
+    // state pairs, dense.cu), then the other bifurcating nodes, then multifurcating ones
+    std::vector<int> kind_of(nnodes, 3);
+    for (int i = 0; i < nnodes; i++) {
+        if (nodes[i].nchild > 2) continue;
+        DevChild &a = c->h_children[nodes[i].child_begin], &b = c->h_children[nodes[i].child_begin + 1];
+        if (a.kind != B200LK_CHILD_LEAF && b.kind == B200LK_CHILD_LEAF) std::swap(a, b);  // a single leaf goes first
+        kind_of[i] = (a.kind == B200LK_CHILD_LEAF) ? (b.kind == B200LK_CHILD_LEAF ? 0 : 1) : 2;
+    }
     std::vector<std::vector<int>> levels(nlevels);
     int pos = 0;
+    size_t tt_off = 0;
+    const size_t tt_doubles = (size_t)c->d.n_state_codes * c->d.n_state_codes * block;
     for (int lv = 0; lv < nlevels; lv++) {
-        for (int pass = 0; pass < 2; pass++)
+        for (int pass = 0; pass < 3; pass++)
             for (int i = 0; i < nnodes; i++) {
-                if (level[i] != lv || (nodes[i].nchild > 2) != (pass == 1)) continue;
+                if (level[i] != lv) continue;
+                const int want = kind_of[i] == 0 ? 0 : (kind_of[i] == 3 ? 2 : 1);
+                if (want != pass) continue;
                 DevNode &dn = c->h_nodes[pos];
                 dn.out_slot = nodes[i].out_slot;
                 dn.child_begin = nodes[i].child_begin;
                 dn.nchild = nodes[i].nchild;
-                if (dn.nchild > 2) {
-                    dn.kind = 3;
-                } else {
-                    DevChild &a = c->h_children[dn.child_begin], &b = c->h_children[dn.child_begin + 1];
-                    if (a.kind != B200LK_CHILD_LEAF && b.kind == B200LK_CHILD_LEAF) std::swap(a, b);
-                    dn.kind = (a.kind == B200LK_CHILD_LEAF) ? (b.kind == B200LK_CHILD_LEAF ? 0 : 1) : 2;
+                dn.kind = kind_of[i];
+                // state-pair table of a tip-tip node: worth building when there are clearly more patterns than pairs
+                if (dn.kind == 0 && c->dense20 && (int64_t)c->d.n_state_codes * c->d.n_state_codes * 4 <= c->ntot) {
+                    c->h_children[dn.child_begin].aux_off = (int64_t)tt_off;
+                    tt_off += tt_doubles;
                 }
                 levels[lv].push_back(pos);
                 pos++;
             }
+    }
+    if (tt_off > c->tt_cap) {
+        if (c->tt_tables) CUDA_TRY(c, cudaFree(c->tt_tables));
+        c->tt_tables = nullptr;
+        c->tt_cap = 0;
+        CUDA_TRY(c, cudaMalloc(&c->tt_tables, sizeof(double) * tt_off));
+        c->tt_cap = tt_off;
     }
     CUDA_TRY(c, cudaMemcpyAsync(c->d_children, c->h_children, sizeof(DevChild) * nchildren, cudaMemcpyHostToDevice,
                                 c->stream));
@@ -156,6 +175,10 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
     c->stage_used[ring] = true;
     int rc = launch_tables(c, nchildren);
     if (rc) return rc;
+    if (tt_off > 0) {
+        rc = launch_tt_tables(c, nnodes);
+        if (rc) return rc;
+    }
     rc = launch_partials(c, levels);
     if (rc) return rc;
     c->n_updates += (int64_t)nnodes * c->ntot;

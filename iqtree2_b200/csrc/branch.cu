@@ -36,7 +36,10 @@ struct BranchArgs {
 __global__ void val_kernel(DevModel m, double len, double *val, double *tip_val, int n, int ncat, int ncm,
                            int denom, int nmix, int codes, int want_tip) {
     const int block = n * ncm;
-    for (int idx = threadIdx.x; idx < block; idx += blockDim.x) {
+    // every CTA owns a slice of the block (mixtures: block = 4800); tip_val recomputes its val0 entry instead of
+    // waiting for another CTA's
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
+    for (int idx = gtid; idx < block; idx += gsz) {
         int c = idx / n, i = idx - c * n, mm = c / denom, k = c % ncat;
         double prop = m.props[k] * m.mixw[mm];
         double cof = m.eval[mm * n + i] * m.rates[k];
@@ -45,13 +48,11 @@ __global__ void val_kernel(DevModel m, double len, double *val, double *tip_val,
         val[idx] = v;
         val[block + idx] = v1;
         val[2 * block + idx] = cof * v1;
-    }
-    if (!want_tip) return;
-    __syncthreads();
-    const int tip_block = n * nmix;
-    for (int idx = threadIdx.x; idx < codes * block; idx += blockDim.x) {
-        int s = idx / block, r = idx - s * block, c = r / n, i = r - c * n;
-        tip_val[idx] = val[r] * m.tip_partial_lh[(size_t)s * tip_block + (c / denom) * n + i];
+        if (want_tip) {
+            const int tip_block = n * nmix;
+            for (int s = 0; s < codes; s++)
+                tip_val[(size_t)s * block + idx] = v * m.tip_partial_lh[(size_t)s * tip_block + mm * n + i];
+        }
     }
 }
 
@@ -529,7 +530,7 @@ static int launch_asc_fix(b200lk_ctx *c, int mode) {
 
 static int launch_val(b200lk_ctx *c, double length, int want_tip) {
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
-    val_kernel<<<1, 256, 0, c->stream>>>(c->m, length, c->val, c->tip_val, c->d.nstates, c->d.ncat, c->ncat_mix,
+    val_kernel<<<(c->block + 255) / 256, 256, 0, c->stream>>>(c->m, length, c->val, c->tip_val, c->d.nstates, c->d.ncat, c->ncat_mix,
                                          denom, c->d.nmix, c->d.n_state_codes, want_tip);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;

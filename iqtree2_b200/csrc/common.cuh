@@ -42,6 +42,7 @@ struct DevChild {
     int64_t echild_off;  // offset (doubles) into tables
     int64_t leaf_off;    // offset (doubles) into tables, -1 if internal
     int64_t frag_off;    // 20-state tensor path: echild in mma fragment order (dense.cu), -1 if unused
+    int64_t aux_off;     // left child of a tip-tip node (20-state path): offset of the node's state-pair table in tt_tables
 };
 
 struct DevNode {
@@ -89,6 +90,8 @@ struct b200lk_ctx {
     std::vector<cudaEvent_t> *prof_events;  // start/stop pairs
     double prof_ms;
     int64_t prof_launches;
+    double *tt_tables;  // 20-state path: per tip-tip node, the partial vector of every (left state, right state) pair
+    size_t tt_cap;      // doubles
     unsigned long long *pmax;  // mixture launches of dense.cu: per (node of the level, pattern) max|x| bits
     size_t pmax_bytes;
     double *red_partial;   // [3][red_blocks] block partial sums
@@ -142,3 +145,5 @@ int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int c
 int launch_partial_multi(b200lk_ctx *c, int node_index);
 int launch_dense20(b200lk_ctx *c, int node_base, int nnodes);
 int launch_inv_frag(b200lk_ctx *c);
+int launch_tt_tables(b200lk_ctx *c, int nnodes);
+int launch_dense20_tt(b200lk_ctx *c, int node_base, int nnodes);

@@ -152,6 +152,7 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (c->h_prog_ring) cudaFreeHost(c->h_prog_ring);
     if (c->d_prog) cudaFree(c->d_prog);
     if (c->pmax) cudaFree(c->pmax);
+    if (c->tt_tables) cudaFree(c->tt_tables);
     free(c->h_evec);
     free(c->h_inv_evec);
     free(c->h_eval);

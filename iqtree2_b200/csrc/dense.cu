@@ -722,22 +722,84 @@ __global__ void __launch_bounds__(DN_THREADS, 3) dense20_rp_kernel(DenseArgs a) 
 
 // NORM_LH decision of the split (mixture) launch: one thread per (node of the level, pattern)
 __global__ void __launch_bounds__(256) dense20_fix_kernel(DenseArgs a) {
-    const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;
-    if (p >= a.ntot) return;
+    const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;  // whole warps stay alive for the ballot below
+    const bool valid = p < a.ntot;
     const DevNode nd = a.nodes[a.node_base + blockIdx.y];
     const DevChild L = a.children[nd.child_begin];
     const DevChild R = a.children[nd.child_begin + 1];
     const bool Lleaf = L.kind == B200LK_CHILD_LEAF, Rleaf = R.kind == B200LK_CHILD_LEAF;
-    const double mx = __longlong_as_double((long long)a.pmax[(size_t)blockIdx.y * a.ntot + p]);
-    const bool under = !(Lleaf && Rleaf) && mx < B200_SCALING_THRESHOLD && a.ptn_invar[p] == 0.0;
-    const int block = a.ncm * 20;
-    if (under) {
-        double *po = a.partial + (size_t)nd.out_slot * a.slot_doubles + (size_t)p * block;
-        for (int e = 0; e < block; e++) po[e] *= B200_TWO_256;
+    bool under = false;
+    if (valid) {
+        const double mx = __longlong_as_double((long long)a.pmax[(size_t)blockIdx.y * a.ntot + p]);
+        under = !(Lleaf && Rleaf) && mx < B200_SCALING_THRESHOLD && a.ptn_invar[p] == 0.0;
+        const int sl = Lleaf ? 0 : a.scale[(size_t)L.id * a.slot_scale_bytes + p];
+        const int sr = Rleaf ? 0 : a.scale[(size_t)R.id * a.slot_scale_bytes + p];
+        a.scale[(size_t)nd.out_slot * a.slot_scale_bytes + p] = (uint8_t)(sl + sr + (under ? 1 : 0));
     }
-    const int sl = Lleaf ? 0 : a.scale[(size_t)L.id * a.slot_scale_bytes + p];
-    const int sr = Rleaf ? 0 : a.scale[(size_t)R.id * a.slot_scale_bytes + p];
-    a.scale[(size_t)nd.out_slot * a.slot_scale_bytes + p] = (uint8_t)(sl + sr + (under ? 1 : 0));
+    // underflowing patterns are rescaled by the whole warp, one pattern at a time (coalesced over the block)
+    const int block = a.ncm * 20, lane = threadIdx.x & 31;
+    unsigned todo = __ballot_sync(0xffffffffu, under);
+    const int64_t p0 = p - lane;
+    while (todo) {
+        const int l = __ffs(todo) - 1;
+        todo &= todo - 1;
+        double *po = a.partial + (size_t)nd.out_slot * a.slot_doubles + (size_t)(p0 + l) * block;
+        for (int e = lane; e < block; e += 32) po[e] *= B200_TWO_256;
+    }
+}
+
+// Tip-tip nodes: gather the node's partial vector from its state-pair table (tables.cu).  Four lanes copy one
+// pattern's block; scale counters of a tip-tip node are zero (:1640).
+struct DenseTTArgs {
+    const DevNode *nodes;
+    const DevChild *children;
+    const double *tt;
+    const uint8_t *states;
+    double *partial;
+    uint8_t *scale;
+    size_t slot_doubles, slot_scale_bytes;
+    int64_t ntot, ntot_pad;
+    int node_base, block, codes, scale_per_ptn;
+};
+
+__global__ void __launch_bounds__(256) dense20_tt_kernel(DenseTTArgs a) {
+    const DevNode nd = a.nodes[a.node_base + blockIdx.y];
+    const DevChild L = a.children[nd.child_begin], R = a.children[nd.child_begin + 1];
+    const int q = threadIdx.x & 3;
+    const int64_t p = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 2;
+    if (p >= a.ntot) return;
+    const int sl = a.states[(size_t)L.id * a.ntot_pad + p], sr = a.states[(size_t)R.id * a.ntot_pad + p];
+    const double2 *src = reinterpret_cast<const double2 *>(a.tt + L.aux_off + (size_t)(sl * a.codes + sr) * a.block);
+    double2 *dst = reinterpret_cast<double2 *>(a.partial + (size_t)nd.out_slot * a.slot_doubles + (size_t)p * a.block);
+    const int pairs = a.block >> 1;
+#pragma unroll 5
+    for (int e = q; e < pairs; e += 4) __stcs(dst + e, __ldg(src + e));
+    uint8_t *sc = a.scale + (size_t)nd.out_slot * a.slot_scale_bytes + (size_t)p * a.scale_per_ptn;
+    for (int k = q; k < a.scale_per_ptn; k += 4) sc[k] = 0;
+}
+
+int launch_dense20_tt(b200lk_ctx *c, int node_base, int nnodes) {
+    DenseTTArgs a;
+    a.nodes = c->d_nodes;
+    a.children = c->d_children;
+    a.tt = c->tt_tables;
+    a.states = c->states;
+    a.partial = c->partial;
+    a.scale = c->scale;
+    a.slot_doubles = c->slot_doubles;
+    a.slot_scale_bytes = c->slot_scale_bytes;
+    a.ntot = c->ntot;
+    a.ntot_pad = c->ntot_pad;
+    a.node_base = node_base;
+    a.block = c->block;
+    a.codes = c->d.n_state_codes;
+    a.scale_per_ptn = c->scale_per_ptn;
+    prof_mark(c);
+    dense20_tt_kernel<<<dim3((unsigned)((c->ntot * 4 + 255) / 256), nnodes), 256, 0, c->stream>>>(a);
+    prof_mark(c);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches++;
+    return B200LK_OK;
 }
 
 // bifurcating nodes [node_base, node_base + nnodes) of the level-sorted device node array

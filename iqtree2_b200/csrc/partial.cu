@@ -321,8 +321,17 @@ int launch_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels) 
         int nb = 0, nm = 0;
         for (int idx : levels[l]) (c->h_nodes[idx].kind == 3 ? nm : nb)++;
         if (nb && c->dense20) {
-            int rc = launch_dense20(c, base, nb);  // FP64 tensor-core path (dense.cu)
-            if (rc) return rc;
+            int ntt = 0;  // tip-tip nodes come first inside a level (api.cu)
+            for (int idx : levels[l])
+                ntt += c->h_nodes[idx].kind == 0 && c->h_children[c->h_nodes[idx].child_begin].aux_off >= 0;
+            if (ntt) {
+                int rc = launch_dense20_tt(c, base, ntt);  // gather from the state-pair tables
+                if (rc) return rc;
+            }
+            if (nb > ntt) {
+                int rc = launch_dense20(c, base + ntt, nb - ntt);  // FP64 tensor-core path (dense.cu)
+                if (rc) return rc;
+            }
         } else if (nb) {
             a.node_base = base;
             dim3 grid((unsigned)((c->ntot + a.PT - 1) / a.PT), nb);

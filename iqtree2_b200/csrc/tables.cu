@@ -5,6 +5,8 @@
 //   leaf[s][c][x]   = sum_i echild[c][x][i] * tip_partial_lh[s][m][i], row s = UNKNOWN := 1   (:1036-1056)
 //
 // One CTA per child of the traversal; only branch lengths travel host -> device.
+#include <algorithm>
+
 #include "common.cuh"
 
 __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict__ children, DevModel m,
@@ -63,6 +65,55 @@ int launch_tables(b200lk_ctx *c, int nchildren) {
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     tables_kernel<<<nchildren, 256, 0, c->stream>>>(c->d_children, c->m, c->tables, c->d.nstates, c->d.ncat,
                                                     c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches++;
+    return B200LK_OK;
+}
+
+// Tip-tip nodes of the 20-state path: both children are leaves, so the node's partial vector is a function of the
+// (left state, right state) pair only -- 24 x 24 pairs for amino acids against hundreds of thousands of patterns.
+//   tt[sl][sr][c][i] = sum_x inv_evec[m][i][x] * leafL[sl][c][x] * leafR[sr][c][x]       (:1632-1746 per pattern)
+// The update of such a node is then a gather from this table (dense20_tt_kernel), bounded by the HBM write only.
+__global__ void __launch_bounds__(256) tt_tables_kernel(const DevNode *__restrict__ nodes, const DevChild *__restrict__ children,
+                                                         const double *__restrict__ tables, const double *__restrict__ inv_evec,
+                                                         double *__restrict__ tt, int n, int ncm, int denom, int codes) {
+    const DevNode nd = nodes[blockIdx.x];
+    if (nd.kind != 0) return;
+    const DevChild L = children[nd.child_begin], R = children[nd.child_begin + 1];
+    if (L.aux_off < 0) return;
+    const int block = n * ncm;
+    const double *leafL = tables + L.leaf_off, *leafR = tables + R.leaf_off;
+    double *out = tt + L.aux_off;
+    // one thread per (category, state pair): pairs vary fastest, so a warp shares the category and reads the same
+    // row of inv_evec (broadcast); the n products leafL * leafR stay in registers for all n outputs
+    const int npairs = codes * codes;
+    const size_t total = (size_t)ncm * npairs;
+    for (size_t idx = (size_t)blockIdx.y * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.y * blockDim.x) {
+        const int cc = (int)(idx / npairs), pair = (int)(idx - (size_t)cc * npairs);
+        const int sl = pair / codes, sr = pair - sl * codes;
+        const double *a = leafL + (size_t)sl * block + cc * n, *b = leafR + (size_t)sr * block + cc * n;
+        const double *M = inv_evec + (size_t)(cc / denom) * n * n;
+        constexpr int N = 20;  // the tensor path is the 20-state path: registers, fully unrolled
+        double tmp[N];
+#pragma unroll
+        for (int x = 0; x < N; x++) tmp[x] = a[x] * b[x];
+        double *o = out + (size_t)pair * block + cc * N;
+        for (int i = 0; i < N; i++) {
+            double v = 0.0;
+#pragma unroll
+            for (int x = 0; x < N; x++) v = fma(__ldg(M + i * N + x), tmp[x], v);
+            o[i] = v;
+        }
+    }
+}
+
+int launch_tt_tables(b200lk_ctx *c, int nnodes) {
+    const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
+    const size_t total = (size_t)c->d.n_state_codes * c->d.n_state_codes * c->ncat_mix;
+    const int gy = (int)std::min<size_t>(4096, (total + 255) / 256);
+    tt_tables_kernel<<<dim3(nnodes, gy), 256, 0, c->stream>>>(c->d_nodes, c->d_children, c->tables, c->m.inv_evec,
+                                                             c->tt_tables, c->d.nstates, c->ncat_mix, denom,
+                                                             c->d.n_state_codes);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
     return B200LK_OK;
