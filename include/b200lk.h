@@ -190,6 +190,17 @@ int b200lk_fetch_partial(b200lk_ctx *ctx, int32_t slot, double *partial /* [nptn
 int b200lk_fetch_theta(b200lk_ctx *ctx, double *theta /* [nptn][ncat_mix][nstates] */,
                        double *buffer_scale_all /* [nptn] or NULL */);
 
+/* ---- UFBoot RELL ------------------------------------ */
+/* IQTree::saveCurrentTree (tree/iqtree.cpp:3553-3650): for every bootstrap resample b,
+ *     rell[b] = dotProduct(pattern_lh, boot_samples[b], nptn)      (tree/phylokernel.h:64-77, BootValType = float)
+ * with pattern_lh the per-pattern log-likelihoods of the tree just evaluated.  The resampled pattern frequencies
+ * are uploaded once and stay resident ([nsamples][nptn] float, the reference's own BootValType); _pattern_lh never
+ * leaves the device (it is what the last b200lk_branch_lnl / b200lk_lnl_from_buffer / b200lk_evaluate wrote), which
+ * removes the largest recurring device->host copy of a tree search (nptn doubles per candidate tree).  Products are
+ * formed in float like the reference's, sums are accumulated in double in a fixed order. */
+int b200lk_upload_boot_samples(b200lk_ctx *ctx, const float *samples /* [nsamples][nptn] */, int32_t nsamples);
+int b200lk_rell(b200lk_ctx *ctx, double *rell /* [nsamples] */);
+
 /* Counters for the metric: pattern-node updates and kernel launches since create/reset. */
 int b200lk_get_counters(b200lk_ctx *ctx, int64_t *pattern_node_updates, int64_t *kernel_launches);
 int b200lk_reset_counters(b200lk_ctx *ctx);

@@ -259,6 +259,19 @@ class Engine:
         self._check(self._f("fetch_theta")(self.ctx, _dp(th), _dp(bs)))
         return th, bs
 
+    def upload_boot_samples(self, samples):
+        """UFBoot: [nsamples][nptn] float32 resampled pattern frequencies, resident on the device."""
+        a = np.ascontiguousarray(samples, dtype=np.float32)
+        assert a.ndim == 2 and a.shape[1] == self.dims.nptn
+        self._check(self._f("upload_boot_samples")(self.ctx, a.ctypes.data_as(C.c_void_p), C.c_int32(a.shape[0])))
+        self._nboot = a.shape[0]
+
+    def rell(self):
+        """RELL log-likelihood of every resample from the device-resident per-pattern lnL of the last evaluation."""
+        out = np.empty(self._nboot)
+        self._check(self._f("rell")(self.ctx, _dp(out)))
+        return out
+
     def counters(self):
         a, b = C.c_int64(), C.c_int64()
         self._check(self._f("get_counters")(self.ctx, C.byref(a), C.byref(b)))

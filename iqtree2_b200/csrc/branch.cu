@@ -641,3 +641,27 @@ int launch_newton(b200lk_ctx *c, const b200lk_newton *nr) {
     c->n_launches++;
     return B200LK_OK;
 }
+
+// ---- UFBoot RELL: rell[b] = sum_p (float)pattern_lh[p] * boot_samples[b][p] ------------------------------------
+// One CTA per resample streams its row once (HBM-bound: 4 bytes per pattern and resample); _pattern_lh stays in L2.
+__global__ void __launch_bounds__(RED_THREADS) rell_kernel(const float *__restrict__ samples, const double *__restrict__ pattern_lh,
+                                                            int64_t nptn, double *__restrict__ rell) {
+    const float *row = samples + (size_t)blockIdx.x * nptn;
+    double acc = 0.0;
+    for (int64_t p = threadIdx.x; p < nptn; p += RED_THREADS) acc += (double)((float)pattern_lh[p] * __ldg(row + p));
+    __shared__ double sh[RED_THREADS];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = RED_THREADS / 2; s > 0; s >>= 1) {
+        if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) rell[blockIdx.x] = sh[0];
+}
+
+int launch_rell(b200lk_ctx *c) {
+    rell_kernel<<<c->nboot, RED_THREADS, 0, c->stream>>>(c->boot_samples, c->pattern_lh, c->d.nptn, c->d_rell);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches++;
+    return B200LK_OK;
+}

@@ -90,6 +90,9 @@ struct b200lk_ctx {
     std::vector<cudaEvent_t> *prof_events;  // start/stop pairs
     double prof_ms;
     int64_t prof_launches;
+    float *boot_samples;  // UFBoot: [nboot][nptn] resampled pattern frequencies (b200lk_upload_boot_samples)
+    double *d_rell, *h_rell;
+    int nboot;
     double *tt_tables;  // 20-state path: per tip-tip node, the partial vector of every (left state, right state) pair
     size_t tt_cap;      // doubles
     unsigned long long *pmax;  // mixture launches of dense.cu: per (node of the level, pattern) max|x| bits
@@ -141,6 +144,7 @@ int launch_derv(b200lk_ctx *c, double length);
 int launch_from_buffer(b200lk_ctx *c, double length);
 int launch_repair(b200lk_ctx *c);
 int launch_newton(b200lk_ctx *c, const b200lk_newton *nr);
+int launch_rell(b200lk_ctx *c);
 int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used);
 int launch_partial_multi(b200lk_ctx *c, int node_index);
 int launch_dense20(b200lk_ctx *c, int node_base, int nnodes);

@@ -151,6 +151,9 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (c->h_children_ring) cudaFreeHost(c->h_children_ring);
     if (c->h_prog_ring) cudaFreeHost(c->h_prog_ring);
     if (c->d_prog) cudaFree(c->d_prog);
+    if (c->boot_samples) cudaFree(c->boot_samples);
+    if (c->d_rell) cudaFree(c->d_rell);
+    if (c->h_rell) cudaFreeHost(c->h_rell);
     if (c->pmax) cudaFree(c->pmax);
     if (c->tt_tables) cudaFree(c->tt_tables);
     free(c->h_evec);
@@ -319,5 +322,44 @@ extern "C" int b200lk_get_profile(b200lk_ctx *c, double *partial_ms, int64_t *pa
     if (partial_ms) *partial_ms = c->prof_ms;
     if (partial_launches) *partial_launches = c->prof_launches;
     if (reset) { c->prof_ms = 0.0; c->prof_launches = 0; }
+    return B200LK_OK;
+}
+
+// ---- UFBoot RELL ---------------------------------------------------------------------------------------------
+extern "C" int b200lk_upload_boot_samples(b200lk_ctx *c, const float *samples, int32_t nsamples) {
+    if (!c || !samples || nsamples < 1) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->boot_samples) CUDA_TRY(c, cudaFree(c->boot_samples));
+    if (c->d_rell) CUDA_TRY(c, cudaFree(c->d_rell));
+    if (c->h_rell) CUDA_TRY(c, cudaFreeHost(c->h_rell));
+    c->boot_samples = nullptr;
+    c->d_rell = c->h_rell = nullptr;
+    c->nboot = 0;
+    const size_t bytes = sizeof(float) * (size_t)nsamples * c->d.nptn;
+    if (cudaMalloc(&c->boot_samples, bytes ? bytes : 4) != cudaSuccess) {
+        cudaGetLastError();
+        snprintf(c->err, sizeof(c->err), "cannot allocate %zu bytes for %d bootstrap resamples", bytes, nsamples);
+        return B200LK_ERR_NOMEM;
+    }
+    CUDA_TRY(c, cudaMalloc(&c->d_rell, sizeof(double) * nsamples));
+    CUDA_TRY(c, cudaMallocHost(&c->h_rell, sizeof(double) * nsamples));
+    CUDA_TRY(c, cudaMemcpyAsync(c->boot_samples, samples, bytes, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    c->nboot = nsamples;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_rell(b200lk_ctx *c, double *rell) {
+    if (!c || !rell) return B200LK_ERR_ARG;
+    if (c->nboot < 1) {
+        snprintf(c->err, sizeof(c->err), "b200lk_rell: upload the bootstrap resamples first");
+        return B200LK_ERR_STATE;
+    }
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    int rc = launch_rell(c);
+    if (rc) return rc;
+    CUDA_TRY(c, cudaMemcpyAsync(c->h_rell, c->d_rell, sizeof(double) * c->nboot, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    memcpy(rell, c->h_rell, sizeof(double) * c->nboot);
     return B200LK_OK;
 }

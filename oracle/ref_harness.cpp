@@ -186,6 +186,9 @@ void *ref_create(const ref_problem *pb) {
         const char *argv[] = {"iqtree2", "-s", "harness", NULL};
         parseArg(3, const_cast<char **>(argv), Params::getInstance());  // the reference's own defaults
         params_ready = true;
+        // main/phyloanalysis.cpp:4171-4175 (off the path, not compiled here) turns the parseArg default 0.0 into the
+        // working lower bound before any branch is optimised
+        if (Params::getInstance().min_branch_length <= 0.0) Params::getInstance().min_branch_length = 1e-6;
     }
     Params &params = Params::getInstance();
     params.lk_safe_scaling = pb->safe != 0;

@@ -73,6 +73,22 @@ def main():
             ll.append(ref.from_buffer())
         out["other_t"], out["other_derv"], out["other_lnl"] = ts, np.array(dd), np.array(ll)
         ref.close()
+        if name in ("example_phy", "dna_gtr_g4", "aa_g4"):
+            # branch-length optimisation by the reference's own PhyloTree::optimizeAllBranches (Newton-Raphson,
+            # tree/phylotree.cpp:2689-2765) from the stored starting lengths: final lnL, the reference's own root
+            # choice lnL (computeLikelihood) and every optimised length keyed by the leaf set behind the branch
+            ref = oracle.RefRun(tree, aln, model, rates, props, kernel=oracle.LK_AVX_FMA, safe=safe, p_invar=pinv)
+            out["lnl_compute_likelihood"] = ref.compute_likelihood()
+            out["opt_lnl"] = ref.optimize_all_branches()
+            splits, lens = [], []
+            for slot, ls in leaf_sets(tree, W.traversal(tree, tree.adj[0][0], 0)).items():
+                splits.append(",".join(str(x) for x in sorted(ls)))
+                lens.append(ref.branch_length(ls, 0))
+            for t in range(tree.ntaxa):
+                splits.append(str(t))
+                lens.append(ref.branch_length([t], t) if t != 0 else ref.branch_length([0], 0))
+            out["opt_splits"], out["opt_lengths"] = np.array(splits), np.array(lens)
+            ref.close()
         path = os.path.join(HERE, "ref_%s.npz" % name)
         np.savez_compressed(path, **out)
         print("%-18s lnL %.10f  -> %s (%d kB)" % (name, out["lnl"], os.path.basename(path), os.path.getsize(path) // 1024))

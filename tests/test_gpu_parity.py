@@ -266,3 +266,29 @@ def test_ascertainment_bias_correction(oracle_lib, nstates, safe):
         assert abs(a - b) <= TOL * abs(b)
         da, db = g.derv(t), o.derv(t)
         assert all(abs(x - y) <= TOL * max(1.0, abs(y)) for x, y in zip(da, db))
+
+
+def test_ufboot_rell_from_resident_pattern_lh(oracle_lib):
+    """UFBoot RELL (IQTree::saveCurrentTree, tree/iqtree.cpp:3606-3616): rell[b] = dotProduct(pattern_lh, boot_samples[b])
+    in the reference's BootValType = float.  Restated here with numpy on the oracle's per-pattern lnL; the float
+    products are identical, the sum is accumulated in double on the device, so agreement is bounded by the float
+    rounding of the reference's own accumulation: |d| <= 1e-6 * sum |terms|."""
+    tree, model, rates, props, aln = make_problem(10, 3000, seed=33, compress=False)
+    g, o = both(aln, model, rates, props, nslots=tree.ntaxa)
+    rg, ro = full_eval(g, tree, 0), full_eval(o, tree, 0)
+    rng = np.random.default_rng(5)
+    nsite = int(aln.ptn_freq.sum())
+    samples = rng.multinomial(nsite, aln.ptn_freq / nsite, size=200).astype(np.float32)  # Alignment::createBootstrapAlignment
+    g.upload_boot_samples(samples)
+    got = g.rell()
+    plh32 = ro["pattern_lh"].astype(np.float32)
+    want = (plh32[None, :] * samples).astype(np.float64).sum(axis=1)
+    bound = 1e-6 * (np.abs(plh32[None, :] * samples)).astype(np.float64).sum(axis=1)
+    assert np.all(np.abs(got - want) <= bound)
+    # the original alignment as a "resample" reproduces lnL to float precision
+    g.upload_boot_samples(aln.ptn_freq[None, :].astype(np.float32))
+    assert abs(g.rell()[0] - rg["lnl"]) <= 1e-6 * abs(rg["lnl"])
+    # RELL follows the tree: after lnL-from-buffer at another length the resident per-pattern lnL changed
+    g.build_theta((LEAF, 0), (INTERNAL, rg["top"]))
+    other = g.lnl_from_buffer(0.77)
+    assert abs(g.rell()[0] - other) <= 1e-6 * abs(other)
