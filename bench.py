@@ -223,6 +223,7 @@ def run_partitioned(args):
         st.add_partition("gene%d" % g, H.HostAlignment.from_states(aln.states, int(nst[g]), compress=False),
                          H.HostModel.from_eigen(model), H.HostRate.categories(rates, props), float(part_rates[g]))
         updates += (T - 2) * aln.nptn
+    st.set_batching(not args.no_batch)
     st.initialize()
     total = torch.zeros(1, dtype=torch.float64, device="cuda")
 
@@ -243,6 +244,7 @@ def run_partitioned(args):
     for _ in range(max(3, args.warmup)):
         lnl = step()
     calls0 = st.kernel_calls()
+    launches0 = st.gpu_launches()
     sampler = ClockSampler(local)
     sampler.start()
     sync_all()
@@ -280,7 +282,9 @@ def run_partitioned(args):
                         "d2h_bytes_per_step": 8 * G,
                         "note": "the timed call IS the host-facing call (b200::PhyloSuperTree::computeLikelihood): traversal "
                                 "descriptors H2D and per-gene lnL D2H are inside the timed region"},
-                "gpu_launches": None, "kernel_abi_calls_per_step": (st.kernel_calls() - calls0) / args.steps,
+                "gpu_launches": int(st.gpu_launches() - launches0),
+                "kernel_abi_calls_per_step": (st.kernel_calls() - calls0) / args.steps,
+                "batches": dict(zip(("batches", "genes_in_batches", "batched_calls"), st.batch_info())),
                 "clocks": sampler.summary(), "lnl": lnl,
                 "roofline": {"bound": "hbm", "kernel": "launch-bound regime (1000 small contexts): see DESIGN.md 6",
                              "achieved": None, "peak": None, "unit": "GB/s", "frac": None, "traffic": None}}
@@ -296,6 +300,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-batch", action="store_true", help="cfg5: one launch sequence per gene instead of batched launches")
     ap.add_argument("--patterns", type=int, default=0, help="override patterns per GPU (debug)")
     ap.add_argument("--cpu-sample", type=int, default=100_000, help="patterns in the CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

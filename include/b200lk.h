@@ -201,6 +201,36 @@ int b200lk_fetch_theta(b200lk_ctx *ctx, double *theta /* [nptn][ncat_mix][nstate
 int b200lk_upload_boot_samples(b200lk_ctx *ctx, const float *samples /* [nsamples][nptn] */, int32_t nsamples);
 int b200lk_rell(b200lk_ctx *ctx, double *rell /* [nsamples] */);
 
+/* ---- partition dispatch as batched launches --------- */
+/* PhyloSuperTree::computeLikelihood (tree/phylosupertree.cpp:701-725) evaluates every partition's own tree with an
+ * OpenMP loop over partitions; PhyloSuperTreePlen::computeFuncDerv (tree/phylosupertreeplen.cpp:250-330) does the
+ * same for the derivatives of one linked edge.  A batch is the device form of that loop: contexts with the same
+ * dimensions (ntaxa, nstates, ncat, nmix, safe_numeric, n_state_codes, nslots; no +ASC), evaluated on the SAME
+ * topology and traversal list, run each step as one launch whose extra grid dimension is the partition.  Models,
+ * alignments, pattern counts and every branch length stay per partition.
+ *   nodes/children: the traversal of the first context (b200lk_child::length is ignored);
+ *   child_len[i*nchildren + k]: length of the branch to children[k] in context i;  branch_len[i]: the dad-node branch.
+ * Configurations a batched launch cannot express (other state counts, mixtures of more than 4 category-classes,
+ * multifurcations, +ASC) return B200LK_ERR_UNSUPPORTED and the caller uses the per-context calls.
+ * Results per context: lnl[n] (and df[n], ddf[n] when want_derv; theta is then left built in every context). */
+typedef struct b200lk_batch b200lk_batch;
+int b200lk_batch_create(b200lk_batch **out, b200lk_ctx **ctxs, int32_t n);
+int b200lk_batch_destroy(b200lk_batch *batch); /* the contexts stay owned by the caller */
+const char *b200lk_batch_last_error(const b200lk_batch *batch);
+int b200lk_batch_evaluate(b200lk_batch *batch, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
+                          int32_t nchildren, const double *child_len /* [n][nchildren] */, b200lk_end dad,
+                          b200lk_end node, const double *branch_len /* [n] */, int want_derv, double *lnl /* [n] */,
+                          double *df /* [n] or NULL */, double *ddf /* [n] or NULL */);
+/* The same in two halves, so that several batches (say the DNA genes and the protein genes of one supermatrix) are
+ * all enqueued before any result is waited for; read_results blocks and fills what the evaluation asked for. */
+int b200lk_batch_evaluate_async(b200lk_batch *batch, const b200lk_node *nodes, int32_t nnodes,
+                                const b200lk_child *children, int32_t nchildren, const double *child_len,
+                                b200lk_end dad, b200lk_end node, const double *branch_len, int want_derv);
+int b200lk_batch_read_results(b200lk_batch *batch, double *lnl, double *df, double *ddf);
+int b200lk_batch_build_theta(b200lk_batch *batch, b200lk_end dad, b200lk_end node);
+int b200lk_batch_derv(b200lk_batch *batch, const double *branch_len /* [n] */, double *df, double *ddf);
+int b200lk_batch_lnl_from_buffer(b200lk_batch *batch, const double *branch_len /* [n] */, double *lnl);
+
 /* Counters for the metric: pattern-node updates and kernel launches since create/reset. */
 int b200lk_get_counters(b200lk_ctx *ctx, int64_t *pattern_node_updates, int64_t *kernel_launches);
 int b200lk_reset_counters(b200lk_ctx *ctx);

@@ -285,6 +285,87 @@ class Engine:
             self._check(self.lib.b200lk_synchronize(self.ctx))
 
 
+class Batch:
+    """Engines of one supermatrix that share dimensions and topology, evaluated with batched launches
+    (include/b200lk.h, b200lk_batch_*).  Raises B200LKError(status -5) for configurations a batch cannot express."""
+
+    def __init__(self, engines):
+        self.engines = list(engines)
+        self.n = len(self.engines)
+        self.lib = self.engines[0].lib
+        arr = (C.c_void_p * self.n)(*[e.ctx for e in self.engines])
+        self.h = C.c_void_p()
+        f = self.lib.b200lk_batch_create
+        f.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int32]
+        rc = f(C.byref(self.h), arr, self.n)
+        if rc < 0:
+            self._raise(rc)
+
+    def _raise(self, rc):
+        msg = ""
+        if self.h:
+            self.lib.b200lk_batch_last_error.restype = C.c_char_p
+            self.lib.b200lk_batch_last_error.argtypes = [C.c_void_p]
+            msg = (self.lib.b200lk_batch_last_error(self.h) or b"").decode()
+        raise B200LKError("b200lk_batch call failed with status %d %s" % (rc, msg))
+
+    def close(self):
+        if self.h:
+            self.lib.b200lk_batch_destroy.argtypes = [C.c_void_p]
+            self.lib.b200lk_batch_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def evaluate(self, entries, child_len, dad, node, branch_len, want_derv=True):
+        """entries: the shared traversal (lengths inside are ignored); child_len [n][nchildren]; branch_len [n].
+        -> (lnl[n], df[n], ddf[n])"""
+        nodes, nn, kids, nc = pack_traversal(entries)
+        child_len = np.ascontiguousarray(child_len, dtype=np.float64).reshape(self.n, max(nc, 0))
+        branch_len = np.ascontiguousarray(branch_len, dtype=np.float64).reshape(self.n)
+        lnl, df, ddf = (np.zeros(self.n) for _ in range(3))
+        f = self.lib.b200lk_batch_evaluate
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.POINTER(C.c_double), End, End,
+                      C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                      C.POINTER(C.c_double)]
+        rc = f(self.h, nodes, nn, kids, nc, _dp(child_len), End(*dad), End(*node), _dp(branch_len), int(want_derv),
+               _dp(lnl), _dp(df), _dp(ddf))
+        if rc < 0:
+            self._raise(rc)
+        return lnl, df, ddf
+
+    def build_theta(self, dad, node):
+        f = self.lib.b200lk_batch_build_theta
+        f.argtypes = [C.c_void_p, End, End]
+        rc = f(self.h, End(*dad), End(*node))
+        if rc < 0:
+            self._raise(rc)
+
+    def derv(self, branch_len):
+        branch_len = np.ascontiguousarray(branch_len, dtype=np.float64).reshape(self.n)
+        df, ddf = np.zeros(self.n), np.zeros(self.n)
+        f = self.lib.b200lk_batch_derv
+        f.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        rc = f(self.h, _dp(branch_len), _dp(df), _dp(ddf))
+        if rc < 0:
+            self._raise(rc)
+        return df, ddf
+
+    def lnl_from_buffer(self, branch_len):
+        branch_len = np.ascontiguousarray(branch_len, dtype=np.float64).reshape(self.n)
+        lnl = np.zeros(self.n)
+        f = self.lib.b200lk_batch_lnl_from_buffer
+        f.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        rc = f(self.h, _dp(branch_len), _dp(lnl))
+        if rc < 0:
+            self._raise(rc)
+        return lnl
+
+
 def engine_for(aln, model, rates, props, *, nslots, p_invar=0.0, safe_numeric=False, device=0,
                lib_path=LIB_PATH, prefix="b200lk_", unobserved=None):
     """Create a context for a workload.Alignment + workload.EigenModel and load

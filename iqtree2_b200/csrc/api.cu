@@ -18,7 +18,7 @@ static int check_ready(b200lk_ctx *c) {
     return B200LK_OK;
 }
 
-static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
+int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
                           int32_t nchildren) {
     if (nnodes == 0) return B200LK_OK;
     if (!nodes || !children || nnodes < 0 || nchildren < 0) return B200LK_ERR_ARG;
@@ -77,6 +77,7 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
         off += (size_t)block * n + block;  // echild, then expv
         dc.frag_off = -1;
         dc.aux_off = -1;
+        dc.src = j;
         if (c->dense20) {
             dc.frag_off = (int64_t)off;
             off += (size_t)c->ncat_mix * B200_FRAG20;
@@ -153,7 +154,7 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
                 dn.nchild = nodes[i].nchild;
                 dn.kind = kind_of[i];
                 // state-pair table of a tip-tip node: worth building when there are clearly more patterns than pairs
-                if (dn.kind == 0 && c->dense20 && (int64_t)c->d.n_state_codes * c->d.n_state_codes * 4 <= c->ntot) {
+                if (dn.kind == 0 && c->dense20 && !c->batch && (int64_t)c->d.n_state_codes * c->d.n_state_codes * 4 <= c->ntot) {
                     c->h_children[dn.child_begin].aux_off = (int64_t)tt_off;
                     tt_off += tt_doubles;
                 }
@@ -186,7 +187,7 @@ static int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
     return B200LK_OK;
 }
 
-static int check_ends(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
+int check_ends(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
     if (node.kind != B200LK_CHILD_INTERNAL || node.id < 0 || node.id >= c->d.nslots) return B200LK_ERR_ARG;
     if (dad.kind == B200LK_CHILD_LEAF) return (dad.id >= 0 && dad.id < c->d.ntaxa) ? B200LK_OK : B200LK_ERR_ARG;
     if (dad.kind != B200LK_CHILD_INTERNAL || dad.id < 0 || dad.id >= c->d.nslots || dad.id == node.id)

@@ -29,12 +29,48 @@ struct BranchArgs {
     double *red_partial;
     int64_t nptn, ntot;
     int n, ncm, block, denom, nmix, G, safe, tile;
+    int slot_pdad, slot_pnode, dad_taxon;  // batched launches rebuild the pointers above per context from these
 };
+
+// batched launch (grid.y = context of the supermatrix): same branch, same slots, the context's own buffers
+__device__ __forceinline__ void rebind_branch(BranchArgs &a, const BatchLaunch &bl) {
+    if (!bl.d_ctx) return;
+    const BatchCtxDev &b = bl.d_ctx[blockIdx.y];
+    if (a.slot_pdad >= 0) {
+        a.pdad = b.partial + (size_t)a.slot_pdad * b.slot_doubles;
+        a.sdad = b.scale + (size_t)a.slot_pdad * b.slot_scale_bytes;
+        if (a.slot_pnode >= 0) {
+            a.pnode = b.partial + (size_t)a.slot_pnode * b.slot_doubles;
+            a.snode = b.scale + (size_t)a.slot_pnode * b.slot_scale_bytes;
+        } else {
+            a.dad_states = b.states + (size_t)a.dad_taxon * b.ntot_pad;
+        }
+    }
+    a.tip_partial_lh = b.m.tip_partial_lh;
+    a.val = b.val;
+    a.tip_val = b.tip_val;
+    a.ptn_freq = b.ptn_freq;
+    a.ptn_invar = b.ptn_invar;
+    a.theta = b.theta;
+    a.buffer_scale_all = b.buffer_scale_all;
+    a.pattern_lh = b.pattern_lh;
+    a.pattern_lh_cat = b.pattern_lh_cat;
+    a.red_partial = b.red_partial;
+    a.nptn = b.nptn;
+    a.ntot = b.ntot;
+}
 
 // val0[c][i] = exp(eval*rate*len)*prop*mixw, val1 = cof*val0, val2 = cof*val1 (:2342-2357);
 // tip_val[s][c][i] = val0[c][i] * tip_partial_lh[s][m][i] (:2757-2785)
 __global__ void val_kernel(DevModel m, double len, double *val, double *tip_val, int n, int ncat, int ncm,
-                           int denom, int nmix, int codes, int want_tip) {
+                           int denom, int nmix, int codes, int want_tip, BatchLaunch bl) {
+    if (bl.d_ctx) {
+        const BatchCtxDev &b = bl.d_ctx[blockIdx.y];
+        m = b.m;
+        val = b.val;
+        tip_val = b.tip_val;
+        len = bl.d_branch_len[blockIdx.y];
+    }
     const int block = n * ncm;
     // every CTA owns a slice of the block (mixtures: block = 4800); tip_val recomputes its val0 entry instead of
     // waiting for another CTA's
@@ -77,8 +113,12 @@ __device__ __forceinline__ void block_reduce_store(double (&acc)[K], double *red
 // fixed-order final pass: result[k] = sum_b red_partial[k][b]
 // (sums k < K0 go to result[dst0 + k], the +ASC sums k >= K0 to result[dst1 + k - K0])
 __global__ void final_reduce_kernel(const double *red_partial, int red_blocks, int K, double *result, int dst0,
-                                    int K0 = 8, int dst1 = 0) {
+                                    int K0, int dst1, BatchLaunch bl) {
     __shared__ double sh[RED_THREADS];
+    if (bl.d_ctx) {
+        red_partial = bl.d_ctx[blockIdx.y].red_partial;
+        result = bl.d_ctx[blockIdx.y].d_result;
+    }
     for (int k = 0; k < K; k++) {
         double v = 0.0;
         for (int b = threadIdx.x; b < red_blocks; b += RED_THREADS) v += red_partial[(size_t)k * red_blocks + b];
@@ -106,7 +146,8 @@ __device__ __forceinline__ int group_min(int v, int G) {
 // theta[p][c][i] = partial_dad * partial_node (or * tip_partial_lh[state][m][i] when dad is a leaf);
 // buffer_scale_all[p] = LOG_SCALING_THRESHOLD * (NORM: summed scale; SAFE: min over categories, with
 // categories scaled once more multiplied by 2^-256 and those scaled more set to 0) (:2142-2175, 2190-2228)
-__global__ void __launch_bounds__(RED_THREADS) theta_kernel(BranchArgs a) {
+__global__ void __launch_bounds__(RED_THREADS) theta_kernel(BranchArgs a, BatchLaunch bl) {
+    rebind_branch(a, bl);
     const int G = a.G, g = threadIdx.x & (G - 1);
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int n = a.n, ncm = a.ncm, block = a.block;
@@ -147,7 +188,8 @@ __global__ void __launch_bounds__(RED_THREADS) theta_kernel(BranchArgs a) {
 }
 
 // ---- df, ddf -------------------------------------------------------------
-__global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red_blocks) {
+__global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red_blocks, BatchLaunch bl) {
+    rebind_branch(a, bl);
     const int G = a.G, g = threadIdx.x & (G - 1);
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int block = a.block;
@@ -356,7 +398,8 @@ __global__ void __launch_bounds__(RED_THREADS) newton_kernel(BranchArgs a, Newto
 }
 
 // ---- lnL from theta --------------------------------------------------------
-__global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(BranchArgs a, int red_blocks) {
+__global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(BranchArgs a, int red_blocks, BatchLaunch bl) {
+    rebind_branch(a, bl);
     const int G = a.G, g = threadIdx.x & (G - 1);
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int block = a.block;
@@ -388,7 +431,8 @@ __global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(BranchArgs a, int 
 // ---- lnL at a branch -------------------------------------------------------
 // lane g of a group owns categories g, g+G, ...; lh_cat[c] = sum_i val[c][i]*node[c][i]*dad[c][i]
 // (or tip_val[state][c][i]*dad[c][i] when dad is a leaf).
-__global__ void __launch_bounds__(RED_THREADS) lnl_kernel(BranchArgs a, int red_blocks) {
+__global__ void __launch_bounds__(RED_THREADS) lnl_kernel(BranchArgs a, int red_blocks, BatchLaunch bl) {
+    rebind_branch(a, bl);
     const int G = a.G, g = threadIdx.x & (G - 1);
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int n = a.n, ncm = a.ncm, block = a.block;
@@ -482,11 +526,16 @@ static void fill_args(b200lk_ctx *c, BranchArgs &a, b200lk_end dad, b200lk_end n
     memset(&a, 0, sizeof(a));
     a.pdad = slot_partial(c, node.id);
     a.sdad = slot_scale(c, node.id);
+    a.slot_pdad = node.id;
+    a.slot_pnode = -1;
+    a.dad_taxon = -1;
     if (dad.kind == B200LK_CHILD_LEAF) {
         a.dad_states = c->states + (size_t)dad.id * c->ntot_pad;
+        a.dad_taxon = dad.id;
     } else {
         a.pnode = slot_partial(c, dad.id);
         a.snode = slot_scale(c, dad.id);
+        a.slot_pnode = dad.id;
     }
 }
 
@@ -512,7 +561,16 @@ static void fill_common(b200lk_ctx *c, BranchArgs &a) {
     a.tile = c->tile;
 }
 
+static BatchLaunch batch_of(const b200lk_ctx *c) {
+    BatchLaunch bl;
+    memset(&bl, 0, sizeof(bl));
+    if (c->batch) bl = *c->batch;
+    return bl;
+}
+static dim3 grid2(const b200lk_ctx *c, int gx) { return dim3(gx, c->batch ? c->batch->n : 1); }
+
 static int grid_for(const b200lk_ctx *c, int G, int64_t npat) {
+    if (c->batch) npat = c->batch->max_ntot;
     int64_t per_block = RED_THREADS / G;
     int64_t need = (npat + per_block - 1) / per_block;
     if (need < 1) need = 1;
@@ -530,8 +588,9 @@ static int launch_asc_fix(b200lk_ctx *c, int mode) {
 
 static int launch_val(b200lk_ctx *c, double length, int want_tip) {
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
-    val_kernel<<<(c->block + 255) / 256, 256, 0, c->stream>>>(c->m, length, c->val, c->tip_val, c->d.nstates, c->d.ncat, c->ncat_mix,
-                                         denom, c->d.nmix, c->d.n_state_codes, want_tip);
+    val_kernel<<<grid2(c, (c->block + 255) / 256), 256, 0, c->stream>>>(c->m, length, c->val, c->tip_val, c->d.nstates,
+                                                                        c->d.ncat, c->ncat_mix, denom, c->d.nmix,
+                                                                        c->d.n_state_codes, want_tip, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
     return B200LK_OK;
@@ -545,9 +604,9 @@ int launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double len
     fill_common(c, a);
     a.G = pick_group(c->ncat_mix);
     int grid = grid_for(c, a.G, c->ntot);
-    lnl_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, grid);
+    lnl_kernel<<<grid2(c, grid), RED_THREADS, 0, c->stream>>>(a, grid, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
-    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 2, c->d_result, 0, 1, 8);
+    final_reduce_kernel<<<grid2(c, 1), RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 2, c->d_result, 0, 1, 8, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches += 2;
     return launch_asc_fix(c, 0);
@@ -557,7 +616,7 @@ int launch_repair(b200lk_ctx *c) {
     int grid = grid_for(c, 1, c->d.nptn);
     repair_kernel<<<grid, RED_THREADS, 0, c->stream>>>(c->pattern_lh, c->ptn_freq, c->d.nptn, c->red_partial, grid);
     CUDA_TRY(c, cudaGetLastError());
-    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 1, c->d_result, 0);
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 1, c->d_result, 0, 8, 0, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches += 2;
     return B200LK_OK;
@@ -569,7 +628,7 @@ int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
     fill_common(c, a);
     a.G = pick_group(c->block);
     int grid = grid_for(c, a.G, c->ntot);
-    theta_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a);
+    theta_kernel<<<grid2(c, grid), RED_THREADS, 0, c->stream>>>(a, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
     return B200LK_OK;
@@ -583,9 +642,9 @@ int launch_derv(b200lk_ctx *c, double length) {
     fill_common(c, a);
     a.G = pick_group(c->block);
     int grid = grid_for(c, a.G, c->ntot);
-    derv_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, grid);
+    derv_kernel<<<grid2(c, grid), RED_THREADS, 0, c->stream>>>(a, grid, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
-    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, c->d.n_unobserved ? 5 : 2, c->d_result, 1, 2, 8);
+    final_reduce_kernel<<<grid2(c, 1), RED_THREADS, 0, c->stream>>>(c->red_partial, grid, c->d.n_unobserved ? 5 : 2, c->d_result, 1, 2, 8, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches += 2;
     return launch_asc_fix(c, 1);
@@ -599,9 +658,9 @@ int launch_from_buffer(b200lk_ctx *c, double length) {
     fill_common(c, a);
     a.G = pick_group(c->block);
     int grid = grid_for(c, a.G, c->ntot);
-    frombuf_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, grid);
+    frombuf_kernel<<<grid2(c, grid), RED_THREADS, 0, c->stream>>>(a, grid, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
-    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 2, c->d_result, 0, 1, 8);
+    final_reduce_kernel<<<grid2(c, 1), RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 2, c->d_result, 0, 1, 8, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches += 2;
     return launch_asc_fix(c, 0);

@@ -43,13 +43,40 @@ struct DevChild {
     int64_t leaf_off;    // offset (doubles) into tables, -1 if internal
     int64_t frag_off;    // 20-state tensor path: echild in mma fragment order (dense.cu), -1 if unused
     int64_t aux_off;     // left child of a tip-tip node (20-state path): offset of the node's state-pair table in tt_tables
+    int64_t src;         // position in the caller's children array (entries are reordered leaf-first): indexes
+                         // BatchLaunch::d_child_len
 };
 
 struct DevNode {
     int32_t out_slot, child_begin, nchild, kind;  // kind: 0 TT, 1 TI, 2 II, 3 multifurcating
 };
 
+// ---- batched launches over the contexts of a supermatrix (batch.cu) ----------------------------------------------
+// Device view of one context of a batch: what a kernel of a batched launch substitutes for the launch's own
+// pointers and sizes (the traversal STRUCTURE -- nodes, child kinds, slots, table offsets -- is shared by all
+// contexts of a batch and comes from the first one).
+struct BatchCtxDev {
+    double *partial;
+    uint8_t *scale;
+    const uint8_t *states;
+    const double *ptn_invar, *ptn_freq;
+    double *tables;
+    DevModel m;
+    double *theta, *buffer_scale_all, *pattern_lh, *pattern_lh_cat, *val, *tip_val, *red_partial, *d_result;
+    size_t slot_doubles, slot_scale_bytes;
+    int64_t ntot, nptn, ntot_pad;
+};
+struct BatchLaunch {           // non-null in b200lk_ctx::batch while a batched call is being enqueued
+    const BatchCtxDev *d_ctx;  // [n]
+    int n;
+    int64_t max_ntot;          // grids are sized for the largest context
+    const double *d_child_len; // [n][nchildren] branch length to every child, per context
+    int nchildren;
+    const double *d_branch_len;  // [n] length of the branch the likelihood is taken at
+};
+
 struct b200lk_ctx {
+    const BatchLaunch *batch;
     b200lk_dims d;
     int ncat_mix, block, scale_per_ptn;
     bool dense20;  // nstates == 20: FP64 tensor-core (DMMA) partial update, dense.cu
@@ -137,6 +164,8 @@ static inline void prof_mark(b200lk_ctx *c) {
 
 // launchers implemented in tables.cu / partial.cu / branch.cu
 int launch_tables(b200lk_ctx *c, int nchildren);
+int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children, int32_t nchildren);
+int check_ends(b200lk_ctx *c, b200lk_end dad, b200lk_end node);
 int launch_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels);
 int launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length);
 int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node);

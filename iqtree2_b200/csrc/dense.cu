@@ -533,8 +533,22 @@ __device__ __forceinline__ void dense_mma_child(const double (&A)[DN_MT][5], con
 }
 
 template <bool SAFE>
-__global__ void __launch_bounds__(DN_THREADS, 3) dense20_rp_kernel(DenseArgs a) {
+__global__ void __launch_bounds__(DN_THREADS, 3) dense20_rp_kernel(DenseArgs a, BatchLaunch bl) {
     extern __shared__ double sm[];
+    if (bl.d_ctx) {  // batched launch: grid.z = context of the supermatrix, same node structure, own data
+        const BatchCtxDev &b = bl.d_ctx[blockIdx.z];
+        a.tables = b.tables;
+        a.inv_frag = b.m.inv_frag;
+        a.ptn_invar = b.ptn_invar;
+        a.states = b.states;
+        a.partial = b.partial;
+        a.scale = b.scale;
+        a.slot_doubles = b.slot_doubles;
+        a.slot_scale_bytes = b.slot_scale_bytes;
+        a.ntot = b.ntot;
+        a.ntot_pad = b.ntot_pad;
+        if ((int64_t)blockIdx.x * a.tiles_per_cta * DN_PT >= a.ntot) return;  // smaller context than the grid
+    }
     const int ncm = a.ncm, block = ncm * 20;
     const DevNode nd = a.nodes[a.node_base + blockIdx.y];
     const DevChild L = a.children[nd.child_begin];
@@ -821,13 +835,14 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes) {
     a.ncm = c->ncat_mix;
     a.denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     a.codes = c->d.n_state_codes;
-    const int64_t tiles = (c->ntot + DN_PT - 1) / DN_PT;
+    const int64_t tiles = ((c->batch ? c->batch->max_ntot : c->ntot) + DN_PT - 1) / DN_PT;
     // enough CTAs to fill the machine a few times over, but amortise the table staging over several tiles
     const int ngroups = (a.ncm + DN_CG - 1) / DN_CG;
     a.split = ngroups > 1;
+    if (c->batch && a.split) return B200LK_ERR_UNSUPPORTED;  // grid.z is taken by the category groups
     a.pmax = nullptr;
     int tpc = DN_MAX_TILES;
-    while (tpc > 1 && (tiles + tpc - 1) / tpc * nnodes * (a.split ? ngroups : 1) < 148 * 6) tpc >>= 1;
+    while (tpc > 1 && (tiles + tpc - 1) / tpc * nnodes * (a.split ? ngroups : 1) * (c->batch ? c->batch->n : 1) < 148 * 6) tpc >>= 1;
     a.tiles_per_cta = tpc;
     if (a.split && !c->d.safe_numeric) {
         const size_t need = sizeof(unsigned long long) * (size_t)nnodes * c->ntot;
@@ -866,11 +881,14 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes) {
         CUDA_TRY(c, cudaFuncSetAttribute(dense20_rp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         c->dense_attr_set = true;
     }
-    dim3 grid((unsigned)((tiles + tpc - 1) / tpc), nnodes, a.split ? ngroups : 1);
+    dim3 grid((unsigned)((tiles + tpc - 1) / tpc), nnodes, a.split ? ngroups : (c->batch ? c->batch->n : 1));
+    BatchLaunch bl;
+    memset(&bl, 0, sizeof(bl));
+    if (c->batch) bl = *c->batch;
     prof_mark(c);
-    if (pipe == 2) {
-        if (c->d.safe_numeric) dense20_rp_kernel<true><<<grid, DN_THREADS, smem, c->stream>>>(a);
-        else dense20_rp_kernel<false><<<grid, DN_THREADS, smem, c->stream>>>(a);
+    if (pipe == 2 || c->batch) {
+        if (c->d.safe_numeric) dense20_rp_kernel<true><<<grid, DN_THREADS, smem, c->stream>>>(a, bl);
+        else dense20_rp_kernel<false><<<grid, DN_THREADS, smem, c->stream>>>(a, bl);
     } else if (pipe == 1) {
         if (c->d.safe_numeric) dense20_pipe_kernel<true><<<grid, DN_THREADS, smem_pipe, c->stream>>>(a);
         else dense20_pipe_kernel<false><<<grid, DN_THREADS, smem_pipe, c->stream>>>(a);

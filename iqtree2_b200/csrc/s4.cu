@@ -43,7 +43,7 @@ struct PNode {
     int32_t info;        // lk | rk << 2 | (out_stack + 1) << 4 | (refill + 1) << 12
     int32_t lid, rid;    // SRC_LEAF: row in the staged chunk; SRC_STACK: entry; SRC_GLOBAL: slot
     int32_t ltab, rtab;  // SRC_LEAF: offset (doubles) of the child's leaf lookup table in `tables`
-    int32_t pad[2];
+    int32_t lexp_off, rexp_off;  // batched launches: offset (doubles) of the child's expv[c][i] in the context's tables
     double lexp[NCM * 4], rexp[NCM * 4];
 };
 
@@ -61,7 +61,7 @@ struct TravArgs {
     uint8_t *scale;
     size_t slot_doubles, slot_scale_bytes;
     int64_t ntot, ntot_pad;
-    int nnodes, depth, chunk, pad;
+    int nnodes, depth, chunk, denom;
 };
 
 #define S4_PARAM_BYTES 32000
@@ -257,6 +257,141 @@ __global__ void __launch_bounds__(S4_THREADS, 4) s4_traverse_kernel(const __grid
     }
 }
 
+// ---- batched variant: one launch for all 4-state contexts of a supermatrix (grid.y = context) -----------------------
+// Same node program (the contexts share topology and traversal), but eigenvectors and exp(lambda r t) factors differ
+// per context (own model, own branch lengths x partition rate): they are read from the context's device tables
+// (warp-uniform loads through L1) instead of the launch parameters.  Used for many small alignments, where launch
+// count, not per-launch speed, is what matters.
+template <int NCM, bool PLAIN>
+__device__ __forceinline__ void child_apply_batch(const double *U, int denom, const double *ev, double *v) {
+#pragma unroll
+    for (int c = 0; c < NCM; c++) {
+        const double *Uc = U + (c / denom) * 16;
+        double w[4], f[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) w[i] = __dmul_rn(__ldg(ev + c * 4 + i), v[c * 4 + i]);
+#pragma unroll
+        for (int x = 0; x < 4; x++) {
+            const double u[4] = {__ldg(Uc + 4 * x), __ldg(Uc + 4 * x + 1), __ldg(Uc + 4 * x + 2), __ldg(Uc + 4 * x + 3)};
+            f[x] = PLAIN ? s4_plain(u, w) : s4_tree(u, w);
+        }
+#pragma unroll
+        for (int x = 0; x < 4; x++) v[c * 4 + x] = f[x];
+    }
+}
+
+template <int NCM, bool SAFE>
+__global__ void __launch_bounds__(S4_THREADS, 2) s4_traverse_batch_kernel(const __grid_constant__ S4Launch<NCM> P, BatchLaunch bl) {
+    constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
+    TravArgs a = P.a;
+    const BatchCtxDev &bc = bl.d_ctx[blockIdx.y];
+    a.tables = bc.tables;
+    a.ptn_invar = bc.ptn_invar;
+    a.states = bc.states;
+    a.partial = bc.partial;
+    a.scale = bc.scale;
+    a.slot_doubles = bc.slot_doubles;
+    a.slot_scale_bytes = bc.slot_scale_bytes;
+    a.ntot = bc.ntot;
+    a.ntot_pad = bc.ntot_pad;
+    const double *Ug = bc.m.evec, *Mg = bc.m.inv_evec;
+    const int64_t p0 = (int64_t)blockIdx.x * S4_THREADS;
+    if (p0 >= a.ntot) return;  // smaller context than the grid
+    extern __shared__ double2 stk[];
+    unsigned *stk_sc = reinterpret_cast<unsigned *>(stk + (size_t)a.depth * PAIRS * S4_THREADS);
+    uint8_t *st_buf = reinterpret_cast<uint8_t *>(stk_sc + (size_t)a.depth * S4_THREADS);
+    const int tid = threadIdx.x;
+    int64_t p = p0 + tid;
+    const bool valid = p < a.ntot;
+    if (!valid) p = a.ntot - 1;
+    const size_t poff = (size_t)(p >> 5) * (32 * BLOCK) + (size_t)(p & 31) * 2;
+    const bool invar0 = a.ptn_invar[p] == 0.0;
+    double prev[BLOCK];
+#pragma unroll
+    for (int j = 0; j < BLOCK; j++) prev[j] = 0.0;
+    unsigned prev_sc = 0;
+    for (int i = 0; i < a.nnodes; i++) {
+        const PNode<NCM> &nd = P.nodes[i];
+        const int info = nd.info;
+        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 12) - 1;
+        if (refill >= 0) {
+            __syncthreads();
+            constexpr int VPR = S4_THREADS / 16;
+            const int nvec = a.chunk * VPR;
+            const int32_t *seq = a.leaf_seq + (size_t)refill * a.chunk;
+            for (int v = tid; v < nvec; v += S4_THREADS) {
+                const int row = v / VPR, q = v - row * VPR;
+                const uint4 *src = reinterpret_cast<const uint4 *>(a.states + (size_t)seq[row] * a.ntot_pad + p0) + q;
+                reinterpret_cast<uint4 *>(st_buf)[v] = __ldg(src);
+            }
+            __syncthreads();
+        }
+        double l[BLOCK], r[BLOCK];
+        unsigned sc = 0;
+        child_load<NCM, SAFE>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
+        child_load<NCM, SAFE>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
+        if (lk != SRC_LEAF) child_apply_batch<NCM, false>(Ug, a.denom, a.tables + nd.lexp_off, l);
+        if (rk != SRC_LEAF) {
+            if (lk == SRC_LEAF) child_apply_batch<NCM, true>(Ug, a.denom, a.tables + nd.rexp_off, r);
+            else child_apply_batch<NCM, false>(Ug, a.denom, a.tables + nd.rexp_off, r);
+        }
+        const bool tiptip = lk == SRC_LEAF && rk == SRC_LEAF;
+        unsigned long long mxall = 0ull;
+#pragma unroll
+        for (int c = 0; c < NCM; c++) {
+            const double *Mc = Mg + (c / a.denom) * 16;
+            double tmp[4];
+#pragma unroll
+            for (int x = 0; x < 4; x++) tmp[x] = __dmul_rn(l[c * 4 + x], r[c * 4 + x]);
+            unsigned long long mx = 0ull;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const double m4[4] = {__ldg(Mc + 4 * k), __ldg(Mc + 4 * k + 1), __ldg(Mc + 4 * k + 2), __ldg(Mc + 4 * k + 3)};
+                const double o = s4_tree(m4, tmp);
+                prev[c * 4 + k] = o;
+                const unsigned long long b = abs_bits(o);
+                mx = b > mx ? b : mx;
+            }
+            if (SAFE) {
+                if (!tiptip && __longlong_as_double((long long)mx) < B200_SCALING_THRESHOLD && invar0) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) prev[c * 4 + k] *= B200_TWO_256;
+                    sc = __vadd4(sc, 1u << (8 * c));
+                }
+            } else {
+                mxall = mx > mxall ? mx : mxall;
+            }
+        }
+        if (!SAFE) {
+            if (!tiptip && __longlong_as_double((long long)mxall) < B200_SCALING_THRESHOLD && invar0) {
+#pragma unroll
+                for (int j = 0; j < BLOCK; j++) prev[j] *= B200_TWO_256;
+                sc += 1;
+            }
+            sc &= 0xff;
+        }
+        prev_sc = sc;
+        if (valid) {
+            double2 *g = reinterpret_cast<double2 *>(a.partial + (size_t)nd.out_slot * a.slot_doubles + poff);
+#pragma unroll
+            for (int j = 0; j < PAIRS; j++) g[j * 32] = make_double2(prev[2 * j], prev[2 * j + 1]);
+            uint8_t *gs = a.scale + (size_t)nd.out_slot * a.slot_scale_bytes;
+            if (SAFE) {
+#pragma unroll
+                for (int c = 0; c < NCM; c++) gs[p * NCM + c] = (uint8_t)(sc >> (8 * c));
+            } else {
+                gs[p] = (uint8_t)sc;
+            }
+        }
+        if (out_stack >= 0) {
+#pragma unroll
+            for (int j = 0; j < PAIRS; j++)
+                stk[(out_stack * PAIRS + j) * S4_THREADS + tid] = make_double2(prev[2 * j], prev[2 * j + 1]);
+            stk_sc[out_stack * S4_THREADS + tid] = sc;
+        }
+    }
+}
+
 // ---- host side -------------------------------------------------------------------------------------------
 template <int NCM>
 static void fill_model(const b200lk_ctx *c, S4Model<NCM> &m) {
@@ -333,6 +468,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
                 leaf_seq[nseq++] = ch.id;
             } else {
                 fill_expv<NCM>(c, ch.length, k == 0 ? f.lexp : f.rexp);
+                (k == 0 ? f.lexp_off : f.rexp_off) = (int32_t)(ch.echild_off + (int64_t)c->block * c->d.nstates);
                 const int pr = producer[ch.id];
                 if (pr >= 0 && consumer[pr] == i && pr == i - 1) {
                     kind[k] = SRC_PREV; id[k] = 0;
@@ -376,17 +512,23 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     a.nnodes = count;
     a.depth = depth_used;
     a.chunk = chunk;
-    a.pad = 0;
+    a.denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     fill_model<NCM>(c, P.mdl);
     const size_t smem = (size_t)depth_used * S4_THREADS * (2 * NCM * sizeof(double2) + sizeof(unsigned)) + S4_STATE_BYTES;
-    const unsigned grid = (unsigned)((c->ntot + S4_THREADS - 1) / S4_THREADS);
+    const unsigned grid = (unsigned)(((c->batch ? c->batch->max_ntot : c->ntot) + S4_THREADS - 1) / S4_THREADS);
     if (!c->trav_attr_set) {
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         c->trav_attr_set = true;
     }
     prof_mark(c);
-    if (c->d.safe_numeric) s4_traverse_kernel<NCM, true><<<grid, S4_THREADS, smem, c->stream>>>(P);
+    if (c->batch) {
+        const dim3 g2(grid, c->batch->n);
+        if (c->d.safe_numeric) s4_traverse_batch_kernel<NCM, true><<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
+        else s4_traverse_batch_kernel<NCM, false><<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
+    } else if (c->d.safe_numeric) s4_traverse_kernel<NCM, true><<<grid, S4_THREADS, smem, c->stream>>>(P);
     else s4_traverse_kernel<NCM, false><<<grid, S4_THREADS, smem, c->stream>>>(P);
     prof_mark(c);
     CUDA_TRY(c, cudaGetLastError());

@@ -11,8 +11,14 @@
 
 __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict__ children, DevModel m,
                                                       double *__restrict__ tables, int n, int ncat, int ncm,
-                                                      int denom, int nmix, int codes) {
-    const DevChild ch = children[blockIdx.x];
+                                                      int denom, int nmix, int codes, BatchLaunch bl) {
+    DevChild ch = children[blockIdx.x];
+    if (bl.d_ctx) {  // batched: context blockIdx.y, its own model, tables and branch lengths
+        const BatchCtxDev &b = bl.d_ctx[blockIdx.y];
+        m = b.m;
+        tables = b.tables;
+        ch.length = bl.d_child_len[(size_t)blockIdx.y * bl.nchildren + ch.src];
+    }
     const int block = n * ncm, nn = n * n;
     double *echild = tables + ch.echild_off;
     // phase 1: echild
@@ -63,8 +69,11 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
 int launch_tables(b200lk_ctx *c, int nchildren) {
     if (nchildren <= 0) return B200LK_OK;
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
-    tables_kernel<<<nchildren, 256, 0, c->stream>>>(c->d_children, c->m, c->tables, c->d.nstates, c->d.ncat,
-                                                    c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes);
+    BatchLaunch bl;
+    memset(&bl, 0, sizeof(bl));
+    if (c->batch) bl = *c->batch;
+    tables_kernel<<<dim3(nchildren, c->batch ? c->batch->n : 1), 256, 0, c->stream>>>(
+        c->d_children, c->m, c->tables, c->d.nstates, c->d.ncat, c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes, bl);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
     return B200LK_OK;

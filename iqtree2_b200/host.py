@@ -28,6 +28,7 @@ def lib():
         _lib.b200host_alignment_npattern.restype = C.c_int64
         _lib.b200host_alignment_name.restype = C.c_char_p
         _lib.b200host_tree_kernel_calls.restype = C.c_int64
+        _lib.b200host_tree_gpu_launches.restype = C.c_int64
     return _lib
 
 
@@ -240,6 +241,10 @@ class HostTree:
     def kernel_calls(self):
         return lib().b200host_tree_kernel_calls(self.h)
 
+    def gpu_launches(self):
+        """Kernels launched by this tree's device context(s) since creation."""
+        return lib().b200host_tree_gpu_launches(self.h)
+
     def safe_numeric(self):
         return bool(lib().b200host_tree_safe_numeric(self.h))
 
@@ -260,6 +265,16 @@ class HostSuperTree(HostTree):
         self._keep.append((aln, model, rate))
         _ck(lib().b200host_super_add(self.h, name.encode(), aln.h, model.h, rate.h, C.c_double(part_rate)))
         self.nparts += 1
+
+    def set_batching(self, on):
+        """Batched launches over partitions of equal dimensions (default on); call before initialize()."""
+        lib().b200host_super_set_batching(self.h, int(on))
+
+    def batch_info(self):
+        """-> (number of batches, partitions inside batches, batched calls made so far)"""
+        nb, npart, calls = C.c_int32(), C.c_int32(), C.c_int64()
+        lib().b200host_super_batch_info(self.h, C.byref(nb), C.byref(npart), C.byref(calls))
+        return nb.value, npart.value, calls.value
 
     def initialize(self):
         _ck(lib().b200host_super_init(self.h))

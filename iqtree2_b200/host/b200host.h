@@ -60,6 +60,18 @@ struct KernelABI {
     int (*optimize_branch)(b200lk_ctx *, b200lk_end, b200lk_end, const b200lk_newton *, double *, double *,
                            int32_t *);                                    // optional
     const char *(*last_error)(const b200lk_ctx *);                        // optional
+    int (*get_counters)(b200lk_ctx *, int64_t *, int64_t *);              // optional
+    // batched launches over the partitions of a supermatrix (optional; NULL when the library has none)
+    int (*batch_create)(b200lk_batch **, b200lk_ctx **, int32_t);
+    int (*batch_destroy)(b200lk_batch *);
+    const char *(*batch_last_error)(const b200lk_batch *);
+    int (*batch_evaluate)(b200lk_batch *, const b200lk_node *, int32_t, const b200lk_child *, int32_t, const double *,
+                          b200lk_end, b200lk_end, const double *, int, double *, double *, double *);
+    int (*batch_evaluate_async)(b200lk_batch *, const b200lk_node *, int32_t, const b200lk_child *, int32_t,
+                                const double *, b200lk_end, b200lk_end, const double *, int);
+    int (*batch_read_results)(b200lk_batch *, double *, double *, double *);
+    int (*batch_derv)(b200lk_batch *, const double *, double *, double *);
+    int (*batch_lnl_from_buffer)(b200lk_batch *, const double *, double *);
 };
 // default: libb200lk.so beside this library, prefix "b200lk_"
 void setKernelLibrary(const std::string &path, const std::string &prefix);
@@ -313,6 +325,16 @@ public:
     std::vector<int> part_order;     // by decreasing cost (computePartitionOrder, tree/phylosupertree.cpp:654-700)
     bool edge_linked = true;
     int num_threads_partitions = 0;  // host threads that enqueue partitions (0: all cores, at most 16)
+    // Partitions with equal dimensions form a batch: every step of an evaluation is ONE launch over all of them
+    // (b200lk_batch_*, include/b200lk.h) instead of one launch per partition.  Off: per-partition streams only.
+    bool batch_partitions = true;
+    struct PartitionBatch {
+        b200lk_batch *handle = NULL;
+        std::vector<int> members;  // partition ids
+    };
+    std::vector<PartitionBatch> batches;
+    std::vector<int> unbatched;     // partitions evaluated on their own streams
+    int64_t batch_calls = 0;
     ~PhyloSuperTree();
     // partition p: its alignment, model and rates (ownership stays with the caller); the topology is the super-tree's
     void addPartition(const std::string &name, Alignment *a, ModelSubst *m, RateHeterogeneity *r, double part_rate = 1.0);
@@ -325,6 +347,15 @@ public:
     // edge-linked Newton-Raphson: df = sum_p rate_p df_p, ddf = sum_p rate_p^2 ddf_p (phylosupertreeplen.cpp:400-402)
     void computeFuncDervLinked(PhyloNode *node1, PhyloNode *node2, double value, double &df, double &ddf);
     double optimizeAllBranches(int my_iterations = 100, double tolerance = TOL_LIKELIHOOD, int maxNRStep = 100) override;
+
+private:
+    void buildBatches();
+    void destroyBatches();
+    // enqueue the evaluation of one batch's members at their current_it branch; false: the members' traversals
+    // differ (or the library refused) and nothing was enqueued -- the caller takes the per-partition path for them
+    bool enqueueBatch(PartitionBatch &b, bool want_derv);
+    void readBatch(PartitionBatch &b, std::vector<double> &lnl, std::vector<double> &df, std::vector<double> &ddf);
+    void evaluatePartitionsAsync(const std::vector<int> &which);
 };
 
 // ---- multi-GPU sharding (shard.cpp) ------------------------------------------------

@@ -232,6 +232,20 @@ int64_t b200host_tree_kernel_calls(void *hv) {
     for (PhyloTree *t : h->super->parts) n += t->kernel_calls;
     return n;
 }
+// kernels launched by the tree's context(s) since creation (b200lk_get_counters); -1 when the library has no counters
+int64_t b200host_tree_gpu_launches(void *hv) {
+    HostTree *h = (HostTree *)hv;
+    const KernelABI &k = kernelABI();
+    if (!k.get_counters) return -1;
+    int64_t total = 0, upd = 0, n = 0;
+    if (!h->super) {
+        if (h->tree->ctx && k.get_counters(h->tree->ctx, &upd, &n) == 0) total = n;
+        return total;
+    }
+    for (PhyloTree *t : h->super->parts)
+        if (t->ctx && k.get_counters(t->ctx, &upd, &n) == 0) total += n;
+    return total;
+}
 int b200host_tree_safe_numeric(void *hv) { return T(hv)->safe_numeric ? 1 : 0; }
 int b200host_tree_set_kernel(void *hv, int lk) { GUARD(T(hv)->setLikelihoodKernel((LikelihoodKernel)lk)) }
 
@@ -264,6 +278,20 @@ int b200host_super_init(void *hv) {
         h->super->initializeAllPartialLh();
         h->super->getBranches(h->b1, h->b2);
     })
+}
+// batched launches over partitions: switch (before init) and what was formed
+int b200host_super_set_batching(void *hv, int on) {
+    ((HostTree *)hv)->super->batch_partitions = on != 0;
+    return 0;
+}
+int b200host_super_batch_info(void *hv, int32_t *nbatches, int32_t *nbatched_parts, int64_t *batch_calls) {
+    PhyloSuperTree *s = ((HostTree *)hv)->super;
+    int32_t members = 0;
+    for (const PhyloSuperTree::PartitionBatch &b : s->batches) members += (int32_t)b.members.size();
+    *nbatches = (int32_t)s->batches.size();
+    *nbatched_parts = members;
+    *batch_calls = s->batch_calls;
+    return 0;
 }
 int b200host_super_part_scores(void *hv, double *out) {
     HostTree *h = (HostTree *)hv;

@@ -65,6 +65,15 @@ const KernelABI &kernelABI() {
     bind(g_abi.read_results, "read_results", false);
     bind(g_abi.optimize_branch, "optimize_branch", false);
     bind(g_abi.last_error, "last_error", false);
+    bind(g_abi.get_counters, "get_counters", false);
+    bind(g_abi.batch_create, "batch_create", false);
+    bind(g_abi.batch_destroy, "batch_destroy", false);
+    bind(g_abi.batch_last_error, "batch_last_error", false);
+    bind(g_abi.batch_evaluate, "batch_evaluate", false);
+    bind(g_abi.batch_evaluate_async, "batch_evaluate_async", false);
+    bind(g_abi.batch_read_results, "batch_read_results", false);
+    bind(g_abi.batch_derv, "batch_derv", false);
+    bind(g_abi.batch_lnl_from_buffer, "batch_lnl_from_buffer", false);
     return g_abi;
 }
 

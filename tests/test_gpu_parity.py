@@ -292,3 +292,77 @@ def test_ufboot_rell_from_resident_pattern_lh(oracle_lib):
     g.build_theta((LEAF, 0), (INTERNAL, rg["top"]))
     other = g.lnl_from_buffer(0.77)
     assert abs(g.rell()[0] - other) <= 1e-6 * abs(other)
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates,ntaxa,mean_len", [(4, 30, 0.1), (4, 150, 0.4), (20, 24, 0.1), (20, 90, 0.5)])
+def test_batched_launches_over_partitions_match_per_partition_results(oracle_lib, nstates, ntaxa, mean_len, safe):
+    """b200lk_batch_*: genes of a supermatrix on one topology, own alignments (different pattern counts), models and
+    branch lengths, evaluated by batched launches -- against the oracle gene by gene
+    (the loop of tree/phylosupertree.cpp:701-725)."""
+    import copy
+    from iqtree2_b200.capi import Batch
+    ngenes = 5
+    rng = np.random.default_rng(77)
+    base, _, rates, props, _ = make_problem(ntaxa, 10, nstates=nstates, seed=31, mean_len=mean_len)
+    trees, engines, oracles = [], [], []
+    for gene in range(ngenes):
+        t = copy.deepcopy(base)
+        for (u, v) in t.branches():
+            t.set_length(u, v, base.get_length(u, v) * (0.5 + gene * 0.3) * rng.uniform(0.8, 1.25))
+        model = W.gtr_model(rates=tuple(rng.uniform(0.5, 3.0, 6))) if nstates == 4 else \
+            W.random_reversible_model(nstates, 500 + gene)
+        aln = W.simulate_alignment(t, model, rates, props, 120 + 173 * gene, 900 + gene)
+        g, o = both(aln, model, rates, props, nslots=ntaxa, safe_numeric=safe)
+        trees.append(t)
+        engines.append(g)
+        oracles.append(o)
+    leaf = 3
+    c = base.adj[leaf][0]
+    tr = W.traversal(base, c, leaf)
+    top = tr[-1][2]
+    child_len = np.array([[t.get_length(e[0], ch_node) for e, ch_node in _children_of(base, tr)] for t in trees])
+    blen = np.array([t.get_length(leaf, c) for t in trees])
+    batch = Batch(engines)
+    lnl, df, ddf = batch.evaluate(tr, child_len, (LEAF, leaf), (INTERNAL, top), blen)
+    pattern_lh = [e.fetch_pattern_lh() for e in engines]
+    blen2 = blen * 1.7
+    df2, ddf2 = batch.derv(blen2)
+    lnl2 = batch.lnl_from_buffer(blen2)
+    if ntaxa >= 90:
+        assert max(int(engines[-1].fetch_scale_num(s).max()) for (_, _, s, _) in tr) >= 1
+    for gene in range(ngenes):
+        want = full_eval(oracles[gene], trees[gene], leaf)
+        assert rel(lnl[gene], want["lnl"]) <= TOL and rel(df[gene], want["df"]) <= TOL and rel(ddf[gene], want["ddf"]) <= TOL
+        for (_, _, s, _) in tr:
+            assert np.array_equal(engines[gene].fetch_scale_num(s), want["scale"][s])
+        assert rel(pattern_lh[gene], want["pattern_lh"]) <= TOL
+        wdf, wddf = oracles[gene].derv(blen2[gene])
+        assert rel(df2[gene], wdf) <= TOL and rel(ddf2[gene], wddf) <= TOL
+        assert rel(lnl2[gene], oracles[gene].lnl_from_buffer(blen2[gene])) <= TOL
+        # the per-context calls still work on a context that belongs to a batch
+        assert rel(engines[gene].lnl_from_buffer(blen2[gene]), lnl2[gene]) <= 1e-12
+
+
+def _children_of(tree, tr):
+    """(entry, neighbour node) for every child of a traversal list, in child order."""
+    out = []
+    for e in tr:
+        node, dad = e[0], e[1]
+        kids = [w for w in tree.adj[node] if w != dad]
+        assert len(kids) == len(e[3])
+        out += [(e, w) for w in kids]
+    return out
+
+
+def test_batch_refuses_what_it_cannot_express(oracle_lib):
+    from iqtree2_b200.capi import B200LKError, Batch
+    tree, model, rates, props, aln = make_problem(8, 100, nstates=5, ncat=2, seed=3)
+    g = engine_for(aln, model, rates, props, nslots=8)
+    with pytest.raises(B200LKError, match="-5"):
+        Batch([g])
+    tree, model, rates, props, aln = make_problem(8, 100, seed=3)
+    a = engine_for(aln, model, rates, props, nslots=8)
+    b = engine_for(aln, model, rates, props, nslots=8, safe_numeric=True)
+    with pytest.raises(B200LKError, match="-5"):
+        Batch([a, b])

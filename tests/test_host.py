@@ -193,7 +193,7 @@ def scenario_optimize_all_branches(device_newton=True):
     return final, t.lengths()
 
 
-def scenario_supertree(edge_linked):
+def scenario_supertree(edge_linked, batching=True):
     tree = W.random_tree(7, 5)
     newick = relabel(tree)
     rng = np.random.default_rng(3)
@@ -216,6 +216,7 @@ def scenario_supertree(edge_linked):
         ha = H.HostAlignment.from_states(cols, nst, compress=True)
         st.add_partition("gene%d" % g, ha, H.HostModel.from_eigen(model), H.HostRate.categories(rates, props), rate)
         parts.append((nst, aln.nptn))
+    st.set_batching(batching)
     st.initialize()
     total = st.compute_likelihood()
     scores = st.part_scores()
@@ -227,6 +228,7 @@ def scenario_supertree(edge_linked):
     assert [cost[i] for i in order] == sorted(cost, reverse=True)
     better = st.optimize_all_branches()
     assert better >= total - 1e-6
+    scenario_supertree.batch_info = st.batch_info()
     return total, better
 
 
@@ -321,6 +323,12 @@ def test_host_device_newton_equals_host_newton(cuda_backend, oracle_lib):
 @pytest.mark.parametrize("edge_linked", [True, False])
 def test_host_supertree_cuda(cuda_backend, oracle_lib, edge_linked):
     total, better = scenario_supertree(edge_linked)
+    # the three DNA genes and the two protein genes each ran as one batch of launches
+    nbatches, nbatched, calls = scenario_supertree.batch_info
+    assert (nbatches, nbatched) == (2, 5) and calls > 0
+    t1, b1 = scenario_supertree(edge_linked, batching=False)
+    assert scenario_supertree.batch_info[0] == 0
+    assert abs(total - t1) <= 1e-10 * abs(t1) and abs(better - b1) <= 1e-8 * abs(b1)
     H.set_kernel_library(oracle_lib, "orc_")
     try:
         t2, b2 = scenario_supertree(edge_linked)
