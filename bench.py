@@ -43,6 +43,8 @@ WORKLOADS = {
     "cfg4": (100, 12_500, 20, 4, 60, 0.7, 3, "synthetic protein 100 taxa x 100k patterns / 8 GPUs (12.5k per GPU), 20-state 60-class mixture +G4"),
     "cfg5": (100, 1000, 4, 4, 1, 0.5, 4, "partitioned supermatrix (see run_partitioned)"),
     "small": (50, 100_000, 4, 4, 1, 0.5, 5, "synthetic DNA 50 taxa x 100k patterns, GTR+G4 (smoke size)"),
+    # not a BASELINE config: the 61-state codon case north_star names for the tensor path
+    "codon": (100, 50_000, 61, 4, 1, 0.5, 6, "synthetic codon 100 taxa x 50k patterns, 61-state reversible +G4"),
 }
 
 
@@ -452,10 +454,12 @@ def main():
         sample = min(args.cpu_sample, N)
         line["cpu_baseline"] = {k: v for k, v in time_cpu(tree, model, rates, props, aln, sample, 3, 1).items()
                                 if k in ("value", "unit", "cores", "kind", "sample", "evals_per_sec")}
-    if n == 20:
-        # 20-state path: FP64 tensor pipe (DMMA) is the bounding unit next to HBM (AI ~ 5 flop/B, at the ridge)
+    if n >= 9:
+        # dense paths: FP64 tensor pipe (DMMA) is the bounding unit next to HBM (20 states: AI ~ 5 flop/B, at the
+        # ridge; 61 states: ~ 15 flop/B, compute-bound)
         hbm = dict(line["roofline"])
-        line["roofline"] = {"bound": "tensor", "kernel": "dense20_kernel (20-state partial update, FP64 DMMA, level-batched)",
+        line["roofline"] = {"bound": "tensor", "kernel": "dense20_rp_kernel + dense20_tt_kernel (20-state partial update, FP64 DMMA, level-batched)" if n == 20
+                            else "denseN_kernel (%d-state partial update, FP64 DMMA on 8-state tiles, level-batched)" % n,
                             "achieved": tflops, "peak": fp64_peak, "peak_source": fp64_src, "unit": "TFLOP/s",
                             "frac": tflops / fp64_peak if tflops else None, "traffic": None,
                             "algorithmic_flops_per_step": int(alg_flops), "kernel_ms_per_step": partial_ms / args.steps,

@@ -78,9 +78,9 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
         dc.frag_off = -1;
         dc.aux_off = -1;
         dc.src = j;
-        if (c->dense20) {
+        if (c->frag_cat) {
             dc.frag_off = (int64_t)off;
-            off += (size_t)c->ncat_mix * B200_FRAG20;
+            off += (size_t)c->ncat_mix * c->frag_cat;
         }
         if (dc.kind == B200LK_CHILD_LEAF) {
             dc.leaf_off = (int64_t)off;

@@ -80,6 +80,8 @@ struct b200lk_ctx {
     b200lk_dims d;
     int ncat_mix, block, scale_per_ptn;
     bool dense20;  // nstates == 20: FP64 tensor-core (DMMA) partial update, dense.cu
+    int dense_nt;  // 9 <= nstates <= 64 (not 20): 8-state tiles of the generic tensor-core path (densen.cu); else 0
+    int frag_cat;  // doubles of one category's P-factor table in mma fragment order (0: no tensor path)
     int tile;  // HBM layout of partial vectors and theta: 1 = pattern-major, 32 = T32 (s4.cu)
     double *h_evec, *h_inv_evec, *h_eval, *h_rates;  // host copies of the model (kernel parameters of the 4-state path)
     int64_t ntot, ntot_pad;
@@ -180,3 +182,4 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes);
 int launch_inv_frag(b200lk_ctx *c);
 int launch_tt_tables(b200lk_ctx *c, int nnodes);
 int launch_dense20_tt(b200lk_ctx *c, int node_base, int nnodes);
+int launch_denseN(b200lk_ctx *c, int node_base, int nnodes);

@@ -53,8 +53,8 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->tip_val, sizeof(double) * d.n_state_codes * c->block));
     // tables for a full traversal: at most 2*(ntaxa-2)+ntaxa children
     size_t per_child = (size_t)c->block * n + c->block + (size_t)d.n_state_codes * c->block;  // echild, expv, leaf
-    if (c->dense20) per_child += (size_t)c->ncat_mix * B200_FRAG20;
-    CUDA_TRY(c, cudaMalloc(&c->m.inv_frag, sizeof(double) * nmix * B200_FRAG20));
+    per_child += (size_t)c->ncat_mix * c->frag_cat;
+    CUDA_TRY(c, cudaMalloc(&c->m.inv_frag, sizeof(double) * nmix * std::max(c->frag_cat, B200_FRAG20)));
     c->h_evec = (double *)malloc(sizeof(double) * nmix * n * n);
     c->h_inv_evec = (double *)malloc(sizeof(double) * nmix * n * n);
     c->h_eval = (double *)malloc(sizeof(double) * nmix * n);
@@ -123,7 +123,10 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
     // 4-state models with <= 4 categories run the pattern-stationary path on the T32 layout (s4.cu)
     {
         const char *e = getenv("B200LK_NO_DMMA");  // A/B switch: generic kernels for 20-state models
-        c->dense20 = dims->nstates == 20 && !(e && *e == '1') && !c->force_level_batched;
+        const bool dmma = !(e && *e == '1') && !c->force_level_batched;
+        c->dense20 = dims->nstates == 20 && dmma;
+        c->dense_nt = (dmma && !c->dense20 && dims->nstates >= 9 && dims->nstates <= 64) ? (dims->nstates + 7) / 8 : 0;
+        c->frag_cat = c->dense20 ? B200_FRAG20 : c->dense_nt * 2 * c->dense_nt * 32;
     }
     c->tile = (dims->nstates == 4 && c->ncat_mix <= 4 && !c->force_level_batched) ? 32 : 1;
     int rc = alloc_all(c);
@@ -228,7 +231,7 @@ extern "C" int b200lk_set_model(b200lk_ctx *c, const double *eval, const double 
     CUDA_TRY(c, cudaMemcpyAsync(c->m.mixw, mixw, sizeof(double) * nmix, cudaMemcpyHostToDevice, s));
     CUDA_TRY(c, cudaMemcpyAsync(c->m.tip_partial_lh, tip_partial_lh, sizeof(double) * c->d.n_state_codes * nmix * n,
                                 cudaMemcpyHostToDevice, s));
-    if (c->dense20) {
+    if (c->dense20 || c->dense_nt) {
         int rc = launch_inv_frag(c);
         if (rc) return rc;
     }

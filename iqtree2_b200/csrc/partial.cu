@@ -332,6 +332,9 @@ int launch_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels) 
                 int rc = launch_dense20(c, base + ntt, nb - ntt);  // FP64 tensor-core path (dense.cu)
                 if (rc) return rc;
             }
+        } else if (nb && c->dense_nt) {
+            int rc = launch_denseN(c, base, nb);  // generic FP64 tensor-core path (densen.cu)
+            if (rc) return rc;
         } else if (nb) {
             a.node_base = base;
             dim3 grid((unsigned)((c->ntot + a.PT - 1) / a.PT), nb);

@@ -11,7 +11,8 @@
 
 __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict__ children, DevModel m,
                                                       double *__restrict__ tables, int n, int ncat, int ncm,
-                                                      int denom, int nmix, int codes, BatchLaunch bl) {
+                                                      int denom, int nmix, int codes, int frag_nt, int frag_ks,
+                                                      BatchLaunch bl) {
     DevChild ch = children[blockIdx.x];
     if (bl.d_ctx) {  // batched: context blockIdx.y, its own model, tables and branch lengths
         const BatchCtxDev &b = bl.d_ctx[blockIdx.y];
@@ -35,15 +36,17 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
         expv[idx] = exp(m.eval[(c / denom) * n + i] * (m.rates[c % ncat] * ch.length));
     }
     if (ch.frag_off >= 0) {
-        // 20-state tensor path (dense.cu): echild as the B operand of mma.m8n8k4, fragment order
-        //   frag[c][j][s][lane] = echild[c][x = 8j + lane/4][i = 4s + lane%4]   (x >= 20 -> 0)
+        // tensor paths (dense.cu: 3 n-tiles x 5 k-steps for 20 states; densen.cu: NT x 2NT): echild as the B operand
+        // of mma.m8n8k4, fragment order
+        //   frag[c][j][s][lane] = echild[c][x = 8j + lane/4][i = 4s + lane%4]   (x >= n or i >= n -> 0)
         __syncthreads();
         double *frag = tables + ch.frag_off;
-        for (int idx = threadIdx.x; idx < ncm * B200_FRAG20; idx += blockDim.x) {
-            int c = idx / B200_FRAG20, r = idx - c * B200_FRAG20;
-            int j = r / 160, s = (r / 32) % 5, lane = r & 31;
+        const int fc = frag_nt * frag_ks * 32;
+        for (int idx = threadIdx.x; idx < ncm * fc; idx += blockDim.x) {
+            int c = idx / fc, r = idx - c * fc;
+            int j = r / (frag_ks * 32), s = (r >> 5) % frag_ks, lane = r & 31;
             int x = 8 * j + (lane >> 2), i = 4 * s + (lane & 3);
-            frag[idx] = x < n ? echild[(size_t)c * nn + x * n + i] : 0.0;
+            frag[idx] = (x < n && i < n) ? echild[(size_t)c * nn + x * n + i] : 0.0;
         }
     }
     if (ch.leaf_off < 0) return;
@@ -73,7 +76,8 @@ int launch_tables(b200lk_ctx *c, int nchildren) {
     memset(&bl, 0, sizeof(bl));
     if (c->batch) bl = *c->batch;
     tables_kernel<<<dim3(nchildren, c->batch ? c->batch->n : 1), 256, 0, c->stream>>>(
-        c->d_children, c->m, c->tables, c->d.nstates, c->d.ncat, c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes, bl);
+        c->d_children, c->m, c->tables, c->d.nstates, c->d.ncat, c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes,
+        c->dense20 ? 3 : c->dense_nt, c->dense20 ? 5 : 2 * c->dense_nt, bl);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
     return B200LK_OK;
@@ -144,7 +148,26 @@ __global__ void inv_frag_kernel(const double *__restrict__ inv_evec, double *__r
     }
 }
 
+// generic tensor path (densen.cu): every k-step pairs with an accumulator register of the child products,
+//   k-step kk = 2j + b:  frag[jo][kk][lane] = inv[i = 8jo + lane/4][x = 8j + 2(lane%4) + b]   (i >= n or x >= n -> 0)
+__global__ void inv_fragN_kernel(const double *__restrict__ inv_evec, double *__restrict__ frag, int nmix, int n, int nt) {
+    const int ks = 2 * nt, fc = nt * ks * 32;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nmix * fc; idx += gridDim.x * blockDim.x) {
+        int m = idx / fc, r = idx - m * fc;
+        int jo = r / (ks * 32), kk = (r >> 5) % ks, lane = r & 31;
+        int i = 8 * jo + (lane >> 2), x = 8 * (kk >> 1) + 2 * (lane & 3) + (kk & 1);
+        frag[idx] = (i < n && x < n) ? inv_evec[(size_t)m * n * n + i * n + x] : 0.0;
+    }
+}
+
 int launch_inv_frag(b200lk_ctx *c) {
+    if (c->dense_nt) {
+        const int total = c->d.nmix * c->frag_cat;
+        inv_fragN_kernel<<<(total + 255) / 256, 256, 0, c->stream>>>(c->m.inv_evec, c->m.inv_frag, c->d.nmix, c->d.nstates,
+                                                                     c->dense_nt);
+        CUDA_TRY(c, cudaGetLastError());
+        return B200LK_OK;
+    }
     inv_frag_kernel<<<(c->d.nmix * B200_FRAG20 + 255) / 256, 256, 0, c->stream>>>(c->m.inv_evec, c->m.inv_frag, c->d.nmix);
     CUDA_TRY(c, cudaGetLastError());
     return B200LK_OK;

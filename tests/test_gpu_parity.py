@@ -366,3 +366,29 @@ def test_batch_refuses_what_it_cannot_express(oracle_lib):
     b = engine_for(aln, model, rates, props, nslots=8, safe_numeric=True)
     with pytest.raises(B200LKError, match="-5"):
         Batch([a, b])
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates,ncat,nmix,ntaxa,nsite", [
+    (9, 2, 1, 8, 150), (12, 3, 2, 9, 130), (16, 1, 1, 6, 100), (17, 2, 1, 7, 90), (24, 2, 1, 7, 90), (32, 2, 1, 6, 70),
+    (33, 1, 1, 6, 70), (40, 2, 1, 6, 60), (48, 1, 1, 5, 60), (56, 1, 2, 5, 50), (61, 4, 1, 8, 130), (64, 1, 1, 5, 45),
+])
+def test_generic_tensor_path_all_tile_counts(oracle_lib, safe, nstates, ncat, nmix, ntaxa, nsite):
+    """densen.cu: 9 <= nstates <= 64 (codon 61, padded to 8-state tiles) on the FP64 tensor cores."""
+    tree, model, rates, props, aln = make_problem(ntaxa, nsite, nstates=nstates, ncat=ncat, nmix=nmix, seed=41,
+                                                  gaps=0.08)
+    g, o = both(aln, model, rates, props, nslots=ntaxa, safe_numeric=safe)
+    for leaf in (0, ntaxa - 1):
+        assert_parity(full_eval(g, tree, leaf), full_eval(o, tree, leaf), TOL)
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates", [13, 61])
+def test_generic_tensor_path_deep_tree_rescales(oracle_lib, nstates, safe):
+    ntaxa = 140 if nstates == 13 else 70
+    tree, model, rates, props, aln = make_problem(ntaxa, 300 if nstates == 13 else 150, nstates=nstates, ncat=2, seed=9,
+                                                  mean_len=0.6)
+    g, o = both(aln, model, rates, props, nslots=ntaxa, safe_numeric=safe)
+    rg, ro = full_eval(g, tree, 0), full_eval(o, tree, 0)
+    assert max(int(s.max()) for s in ro["scale"].values()) >= 1
+    assert_parity(rg, ro, TOL)
