@@ -367,14 +367,14 @@ class Batch:
 
 
 def engine_for(aln, model, rates, props, *, nslots, p_invar=0.0, safe_numeric=False, device=0,
-               lib_path=LIB_PATH, prefix="b200lk_", unobserved=None):
+               lib_path=LIB_PATH, prefix="b200lk_", unobserved=None, fused=False):
     """Create a context for a workload.Alignment + workload.EigenModel and load
     tips, pattern weights and the model (the one-time uploads of
     initializeAllPartialLh / computeTipPartialLikelihood)."""
     from . import workload as W
     eng = Engine(ntaxa=aln.ntaxa, nstates=aln.nstates, ncat=len(rates), nmix=model.nmix, nptn=aln.nptn,
                  nslots=nslots, n_state_codes=aln.state_unknown + 1, safe_numeric=safe_numeric,
-                 device=device, lib_path=lib_path, prefix=prefix,
+                 device=device, lib_path=lib_path, prefix=prefix, fused_mix_rate=fused,
                  n_unobserved=0 if unobserved is None else np.asarray(unobserved).shape[1])
     eng.upload_tips(aln.states, aln.ptn_freq, unobserved)
     inv = W.ptn_invar(aln, model, p_invar)

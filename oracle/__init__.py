@@ -50,7 +50,7 @@ class RefRun:
     (ref_harness.cpp).  kernel: LK_SSE2 (Vec2d), LK_AVX (Vec4d), LK_AVX_FMA (Vec4d + FMA)."""
 
     def __init__(self, tree, aln, model, rates, props, *, kernel=LK_AVX_FMA, safe=False, threads=1, p_invar=0.0,
-                 unobserved=None):
+                 unobserved=None, fused=False):
         import ctypes as C
         import numpy as np
         from iqtree2_b200 import workload as W
@@ -84,9 +84,11 @@ class RefRun:
         if unobserved is not None:  # +ASC (Lewis): [ntaxa][n_unobserved] state codes
             un = np.ascontiguousarray(unobserved, dtype=np.uint8)
             self.lib.ref_set_next_unobserved(un.shape[1], C.c_void_p(un.ctypes.data), un.shape[0])
+        if fused:  # model_factory->fused_mix_rate: category c = mixture class c at rate category c
+            self.lib.ref_set_next_fused(1)
         self.lib.ref_create.restype = C.c_void_p
         self.h = C.c_void_p(self.lib.ref_create(C.byref(pb)))
-        self.nptn, self.ncm, self.n = aln.nptn, len(rates) * model.nmix, aln.nstates
+        self.nptn, self.ncm, self.n = aln.nptn, (len(rates) if fused else len(rates) * model.nmix), aln.nstates
         self.tree = tree
         for fn in ("ref_lnl_at_leaf", "ref_lnl_again", "ref_from_buffer", "ref_optimize_current_branch",
                    "ref_optimize_all_branches", "ref_compute_likelihood", "ref_branch_length"):

@@ -170,6 +170,11 @@ void ref_set_next_unobserved(int n_unobserved, const uint8_t *codes, int ntaxa) 
     next_unobserved.assign(codes, codes + (size_t)(n_unobserved > 0 ? n_unobserved : 0) * ntaxa);
 }
 
+// model_factory->fused_mix_rate of the NEXT ref_create (model/modelfactory.h; category c = mixture class c with rate
+// category c, tree/phylokernelnew.h:1322-1331)
+static int next_fused = 0;
+void ref_set_next_fused(int fused) { next_fused = fused; }
+
 #include <execinfo.h>
 #include <signal.h>
 #include <unistd.h>
@@ -244,6 +249,8 @@ void *ref_create(const ref_problem *pb) {
     ModelFactory *f = new ModelFactory();
     f->model = m;
     f->site_rate = r;
+    f->fused_mix_rate = next_fused != 0;
+    next_fused = 0;
     if (next_n_unobserved > 0) {
         f->ASC_type = ASC_VARIANT;  // Lewis (utils/tools.h:549-555)
         for (int u = 0; u < next_n_unobserved; u++) {
@@ -271,7 +278,7 @@ void *ref_create(const ref_problem *pb) {
     tree->setNumThreads(pb->threads);
     tree->initializeAllPartialLh();
     h->tree = tree;
-    h->ncm = pb->ncat * pb->nmix;
+    h->ncm = f->fused_mix_rate ? pb->ncat : pb->ncat * pb->nmix;  // tree/phylokernelnew.h:1323
     h->block = h->ncm * n;
     h->cur_dad_branch = NULL;
     h->cur_dad = NULL;

@@ -392,3 +392,13 @@ def test_generic_tensor_path_deep_tree_rescales(oracle_lib, nstates, safe):
     rg, ro = full_eval(g, tree, 0), full_eval(o, tree, 0)
     assert max(int(s.max()) for s in ro["scale"].values()) >= 1
     assert_parity(rg, ro, TOL)
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates,k", [(4, 4), (4, 2), (20, 3), (12, 2), (6, 2)])
+def test_fused_mixture_rate_categories(oracle_lib, nstates, k, safe):
+    """fused_mix_rate: category c = mixture class c at rate category c, on every kernel family."""
+    tree, model, rates, props, aln = make_problem(11, 260, nstates=nstates, ncat=k, nmix=k, seed=14, gaps=0.04)
+    g, o = both(aln, model, rates, props, nslots=11, safe_numeric=safe, fused=True)
+    assert g.ncat_mix == k
+    assert_parity(full_eval(g, tree, 2), full_eval(o, tree, 2), TOL)

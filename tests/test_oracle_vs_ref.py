@@ -33,11 +33,12 @@ def leaf_sets(tree, entries):
     return out
 
 
-def compare(tree, aln, model, rates, props, kernel, safe, leaf=0, p_invar=0.0, tol=1e-11, check_nodes=True):
-    ref = oracle.RefRun(tree, aln, model, rates, props, kernel=kernel, safe=safe, p_invar=p_invar)
+def compare(tree, aln, model, rates, props, kernel, safe, leaf=0, p_invar=0.0, tol=1e-11, check_nodes=True, fused=False):
+    ref = oracle.RefRun(tree, aln, model, rates, props, kernel=kernel, safe=safe, p_invar=p_invar, fused=fused)
     safe_eff = ref.safe_numeric       # forced for nstates not in {4, 20} (tree/phylotreesse.cpp:95-96)
     oracle.set_ref_quirks(True)
-    eng = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa, safe_numeric=safe_eff, p_invar=p_invar)
+    eng = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa, safe_numeric=safe_eff, p_invar=p_invar,
+                               fused=fused)
     lnl = ref.lnl_at_leaf(leaf)
     o = full_eval(eng, tree, leaf)
     assert rel(lnl, o["lnl"]) <= tol
@@ -89,6 +90,15 @@ def test_mixture_and_generic_states(oracle_lib, kernel):
     # generic nstates (SAFE forced by the reference): even state count
     tree, model, rates, props, aln = make_problem(8, 200, nstates=6, ncat=3, nmix=2, seed=6)
     compare(tree, aln, model, rates, props, kernel, False)
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates,k", [(4, 4), (20, 3), (6, 2)])
+def test_fused_mixture_rate_categories(oracle_lib, nstates, k, safe):
+    """model_factory->fused_mix_rate: category c pairs mixture class c with rate category c (ncat_mix = ncat,
+    tree/phylokernelnew.h:1322-1331)."""
+    tree, model, rates, props, aln = make_problem(9, 180, nstates=nstates, ncat=k, nmix=k, seed=12, gaps=0.04)
+    compare(tree, aln, model, rates, props, oracle.LK_AVX_FMA, safe, fused=True)
 
 
 @pytest.mark.parametrize("safe", [False, True])
