@@ -121,6 +121,18 @@ int b200lk_set_model(b200lk_ctx *ctx, const double *eval, const double *evec, co
                      const double *rates, const double *props, const double *mixw,
                      const double *tip_partial_lh);
 
+/* The same from the model's free parameters, eigen-decomposition on the device:
+ * ModelMarkov::decomposeRateMatrix for reversible models (model/modelmarkov.cpp:1386-1632 ->
+ * EigenDecomposition::eigensystem_sym, utils/eigendecomposition.cpp:165-317) + computeTipPartialLikelihood.
+ * exch[nmix][n(n-1)/2]: upper triangle of the exchangeabilities, row-major (ModelMarkov::rates, half_matrix);
+ * freqs[nmix][n]; total_num_subst[nmix] or NULL (1.0 each; the class rate of a mixture);
+ * tipvec[n_state_codes][n]: 0/1 indicator (ambiguity) vectors of the state codes (computeTipLikelihood,
+ * model/modelsubst.cpp:182-207).  nstates <= 64.  Eigenpairs come out in the solver's own order. */
+int b200lk_set_model_rates(b200lk_ctx *ctx, const double *exch, const double *freqs, const double *total_num_subst,
+                           const double *tipvec, const double *rates, const double *props, const double *mixw);
+/* the eigen-system the context currently holds (eval[nmix*n], evec[nmix*n*n], inv_evec[nmix*n*n]) */
+int b200lk_fetch_model(b200lk_ctx *ctx, double *eval, double *evec, double *inv_evec);
+
 /* ---- the four kernel entry points -------------------------------------- */
 /* computePartialLikelihood over a whole traversal list
  * (computeTraversalInfo + computePartialInfo + computePartialLikelihood*SIMD,

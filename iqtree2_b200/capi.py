@@ -135,6 +135,24 @@ class Engine:
         self._check(self._f("set_model")(self.ctx, *[_dp(a) for a in arrs]))
 
     # -- kernels -------------------------------------------------------------
+    def set_model_rates(self, exch, freqs, rates, props, mixw, tipvec, total_num_subst=None):
+        """Model from its free parameters; the eigen-decomposition runs on the device (b200lk_set_model_rates).
+        exch [nmix][n(n-1)/2] upper triangle, freqs [nmix][n], tipvec [n_state_codes][n]."""
+        arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in (exch, freqs, tipvec, rates, props, mixw)]
+        tot = None if total_num_subst is None else np.ascontiguousarray(total_num_subst, dtype=np.float64)
+        f = self._f("set_model_rates")
+        f.argtypes = [C.c_void_p] + [C.POINTER(C.c_double)] * 7
+        self._check(f(self.ctx, _dp(arrs[0]), _dp(arrs[1]), None if tot is None else _dp(tot), _dp(arrs[2]),
+                      _dp(arrs[3]), _dp(arrs[4]), _dp(arrs[5])))
+
+    def fetch_model(self):
+        n, nmix = self.dims.nstates, self.dims.nmix
+        ev, U, Ui = np.zeros((nmix, n)), np.zeros((nmix, n, n)), np.zeros((nmix, n, n))
+        f = self._f("fetch_model")
+        f.argtypes = [C.c_void_p] + [C.POINTER(C.c_double)] * 3
+        self._check(f(self.ctx, _dp(ev), _dp(U), _dp(Ui)))
+        return ev, U, Ui
+
     def update_partials(self, entries):
         nodes, nn, kids, nk = pack_traversal(entries)
         return self._check(self._f("update_partials")(self.ctx, nodes, nn, kids, nk))

@@ -126,6 +126,7 @@ struct b200lk_ctx {
     size_t tt_cap;      // doubles
     unsigned long long *pmax;  // mixture launches of dense.cu: per (node of the level, pattern) max|x| bits
     size_t pmax_bytes;
+    double *eig_in, *eig_host;  // staging of b200lk_set_model_rates (eigen.cu): device inputs, pinned host mirror
     double *red_partial;   // [3][red_blocks] block partial sums
     int red_blocks;
     double nsite;          // sum of ptn_freq (aln->getNSite()), for the +ASC correction

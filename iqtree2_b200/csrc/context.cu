@@ -159,6 +159,8 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (c->h_rell) cudaFreeHost(c->h_rell);
     if (c->pmax) cudaFree(c->pmax);
     if (c->tt_tables) cudaFree(c->tt_tables);
+    if (c->eig_in) cudaFree(c->eig_in);
+    if (c->eig_host) cudaFreeHost(c->eig_host);
     free(c->h_evec);
     free(c->h_inv_evec);
     free(c->h_eval);

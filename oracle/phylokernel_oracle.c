@@ -338,6 +338,43 @@ int orc_set_model(orc_ctx *c, const double *eval, const double *evec, const doub
     return B200LK_OK;
 }
 
+/* Model from exchangeabilities and frequencies: ModelMarkov::decomposeRateMatrix for reversible models
+ * (model/modelmarkov.cpp:1386-1632; eigen_oracle.c) followed by computeTipPartialLikelihood
+ * (tree/phylotreesse.cpp:243-375): tip_partial_lh[s][m][i] = sum_x inv_evec[m][i][x] * tipvec[s][x].
+ * exch [nmix][n(n-1)/2], freqs [nmix][n], total_num_subst [nmix] or NULL (1.0), tipvec [n_state_codes][n]. */
+int orc_eigen_rev(int n, const double *exch, const double *freqs, double total_num_subst, double *eval, double *evec,
+                  double *inv_evec);
+int orc_set_model_rates(orc_ctx *c, const double *exch, const double *freqs, const double *total_num_subst,
+                        const double *tipvec, const double *rates, const double *props, const double *mixw) {
+    int n = c->d.nstates, nmix = c->d.nmix, codes = c->d.n_state_codes, ne = n * (n - 1) / 2;
+    double *eval = malloc(sizeof(double) * nmix * n), *evec = malloc(sizeof(double) * nmix * n * n);
+    double *inv = malloc(sizeof(double) * nmix * n * n), *tip = malloc(sizeof(double) * codes * nmix * n);
+    int rc = B200LK_OK;
+    for (int m = 0; m < nmix; m++)
+        if (orc_eigen_rev(n, exch + (size_t)m * ne, freqs + (size_t)m * n, total_num_subst ? total_num_subst[m] : 1.0,
+                          eval + m * n, evec + (size_t)m * n * n, inv + (size_t)m * n * n))
+            rc = B200LK_ERR_ARG;
+    for (int s = 0; s < codes; s++)
+        for (int m = 0; m < nmix; m++)
+            for (int i = 0; i < n; i++) {
+                double v = 0.0;
+                for (int x = 0; x < n; x++) v += inv[(size_t)m * n * n + i * n + x] * tipvec[s * n + x];
+                tip[((size_t)s * nmix + m) * n + i] = v;
+            }
+    if (rc == B200LK_OK) rc = orc_set_model(c, eval, evec, inv, rates, props, mixw, tip);
+    free(eval); free(evec); free(inv); free(tip);
+    return rc;
+}
+
+/* the eigen-system a context currently holds (tests) */
+int orc_fetch_model(orc_ctx *c, double *eval, double *evec, double *inv_evec) {
+    int n = c->d.nstates, nmix = c->d.nmix;
+    memcpy(eval, c->eval, sizeof(double) * nmix * n);
+    memcpy(evec, c->evec, sizeof(double) * nmix * n * n);
+    memcpy(inv_evec, c->inv_evec, sizeof(double) * nmix * n * n);
+    return B200LK_OK;
+}
+
 /* --------------------------------------------------------- computePartialInfo */
 /* tree/phylokernelnew.h:1062-1108 (reversible, non-vectorised branch):
  * echild[c][x][i] = evec[m][x][i] * exp(eval[m][i] * rate[c%ncat] * len)

@@ -34,6 +34,7 @@
 #include "model/modelfactory.h"
 #include "alignment/alignment.h"
 #include "utils/tools.h"
+#include "utils/eigendecomposition.h"
 #include "utils/starttree.h"
 #undef private
 #undef protected
@@ -168,6 +169,26 @@ static int next_n_unobserved = 0;
 void ref_set_next_unobserved(int n_unobserved, const uint8_t *codes, int ntaxa) {
     next_n_unobserved = n_unobserved;
     next_unobserved.assign(codes, codes + (size_t)(n_unobserved > 0 ? n_unobserved : 0) * ntaxa);
+}
+
+// the reference's own reversible eigen-solver (utils/eigendecomposition.cpp:165-317) on caller-supplied
+// exchangeabilities (upper triangle) and frequencies, as ModelMarkov::decomposeRateMatrixRev calls it
+// (model/modelmarkov.cpp:1602-1632)
+void ref_eigensystem_sym(int n, const double *exch, const double *freqs, double total_num_subst, double *eval,
+                         double *evec, double *inv_evec) {
+    EigenDecomposition ed;
+    ed.total_num_subst = total_num_subst;
+    std::vector<std::vector<double>> rm(n, std::vector<double>(n, 0.0));
+    std::vector<double *> rows(n);
+    std::vector<double> fr(freqs, freqs + n);
+    for (int i = 0, k = 0; i < n; i++) {
+        rows[i] = rm[i].data();
+        for (int j = i + 1; j < n; j++, k++) {
+            const double r = (freqs[i] <= ZERO_FREQ || freqs[j] <= ZERO_FREQ) ? 0 : exch[k];
+            rm[i][j] = rm[j][i] = r;
+        }
+    }
+    ed.eigensystem_sym(rows.data(), fr.data(), eval, evec, inv_evec, n);
 }
 
 // model_factory->fused_mix_rate of the NEXT ref_create (model/modelfactory.h; category c = mixture class c with rate
