@@ -295,6 +295,64 @@ def run_partitioned(args):
         dist.destroy_process_group()
 
 
+def run_mem_save(args):
+    """A workload whose partial vectors do not fit one GPU with one slot per internal node (cfg4: 98 x 3.84 GB at
+    100k patterns), evaluated on ONE GPU through b200::PhyloTree with LM_MEM_SAVE (-mem, tree/memslot.cpp): the
+    traversal builder recycles log2(T)+1 slots.  A step = every partial stale -> computeLikelihood."""
+    import torch
+    from iqtree2_b200 import build_host, host as H, workload as W
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback on this path")
+    build_host.build()
+    T, N, n, ncat, nmix, *_ = WORKLOADS[args.workload]
+    N = args.patterns or N
+    tree, model, rates, props, aln = build_workload(args.workload, N)
+    names = tree.names
+    tree.names = ["T%d" % i for i in range(T)]
+    newick = tree.to_newick(0, 17)
+    tree.names = names
+    ha = H.HostAlignment.from_states(aln.states, n, compress=False)
+    t = H.HostTree(newick, ha, H.HostModel.from_eigen(model), H.HostRate.categories(rates, props), mem_save=args.mem_save)
+    slots = t.max_lh_slots
+    updates = (T - 2) * aln.nptn
+
+    def step():
+        t.clear_partials()
+        return t.compute_likelihood()
+
+    for _ in range(max(3, args.warmup)):
+        lnl = step()
+    sampler = ClockSampler(0)
+    sampler.start()
+    torch.cuda.synchronize()
+    launches0 = t.gpu_launches()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        lnl = step()
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3
+    sampler.stop_flag = True
+    sampler.join()
+    block = n * ncat * nmix
+    val = updates * args.steps / (ms * 1e-3)
+    line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic (seeded AliSim-equivalent sampler, every column its own pattern)",
+            "config": {"workload": "%s through b200::PhyloTree with -mem: %s" % (args.workload, WORKLOADS[args.workload][7]),
+                       "ntaxa": T, "patterns_per_gpu": int(aln.nptn), "nstates": n, "ncat": ncat, "nmix": nmix,
+                       "lh_slots": slots, "slots_without_mem_save": T - 2,
+                       "partial_vectors_gb": slots * aln.nptn * block * 8 / 1e9,
+                       "partial_vectors_gb_without_mem_save": (T - 2) * aln.nptn * block * 8 / 1e9,
+                       "l2": "every step rewrites %.1f GB of partial vectors" % (updates * block * 8 / 1e9)},
+            "evals_per_sec": args.steps / (ms * 1e-3),
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": int((T - 2) * 16 + (2 * T - 3) * 16), "d2h_bytes_per_step": 8,
+                    "note": "the timed call IS the host-facing call (b200::PhyloTree::computeLikelihood)"},
+            "gpu_launches": int(t.gpu_launches() - launches0), "clocks": sampler.summary(), "lnl": lnl,
+            "roofline": {"bound": "tensor" if n >= 9 else "hbm", "kernel": "whole evaluation (wall clock)",
+                         "achieved": None, "peak": None, "unit": "TFLOP/s", "frac": None, "traffic": None}}
+    print(json.dumps(line))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -302,6 +360,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--mem-save", type=float, default=None, metavar="FRACTION",
+                    help="run the workload through the host layer with -mem slot recycling (0: log2(T)+1 slots)")
     ap.add_argument("--no-batch", action="store_true", help="cfg5: one launch sequence per gene instead of batched launches")
     ap.add_argument("--patterns", type=int, default=0, help="override patterns per GPU (debug)")
     ap.add_argument("--cpu-sample", type=int, default=100_000, help="patterns in the CPU-baseline sample")
@@ -312,6 +372,8 @@ def main():
         return run_reference(args)
     if args.workload == "cfg5":
         return run_partitioned(args)
+    if args.mem_save is not None:
+        return run_mem_save(args)
 
     import torch
     import torch.distributed as dist

@@ -158,11 +158,15 @@ class HostTree:
     """b200::PhyloTree set up in the reference's order (readTree, setAlignment, setModel, setLikelihoodKernel
     (LK_CUDA), initializeAllPartialLh)."""
 
-    def __init__(self, newick, aln, model, rate, safe=False, device=0, device_newton=True, asc=False):
+    def __init__(self, newick, aln, model, rate, safe=False, device=0, device_newton=True, asc=False, mem_save=None):
+        """mem_save: None = one slot per internal node; a number = -mem (LM_MEM_SAVE) with that Params::max_mem_size
+        (0: the minimum log2(ntaxa)+1 slots; <= 1: that fraction of ntaxa-2)."""
         self.h = C.c_void_p()
         self._keep = (aln, model, rate)
+        if mem_save is not None:
+            lib().b200host_set_mem_fraction(C.c_double(float(mem_save)))
         _ck(lib().b200host_tree_new(C.byref(self.h), newick.encode(), aln.h, model.h, rate.h,
-                                    int(bool(safe)) | (2 if asc else 0), device,
+                                    int(bool(safe)) | (2 if asc else 0) | (4 if mem_save is not None else 0), device,
                                     int(device_newton)))
         self.aln = aln
 
@@ -176,6 +180,10 @@ class HostTree:
             self.close()
         except Exception:
             pass
+
+    @property
+    def max_lh_slots(self):
+        return lib().b200host_tree_max_lh_slots(self.h)
 
     @property
     def nbranches(self):

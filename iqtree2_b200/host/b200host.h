@@ -193,7 +193,14 @@ struct TraversalInfo {  // tree/phylotree.h:320-331
     PhyloNode *dad;
 };
 
+enum LhMemSave { LM_PER_NODE, LM_MEM_SAVE };  // utils/tools.h: -mem
+
 struct Params {  // the few fields of utils/tools.h Params the path reads
+    // -mem: LM_MEM_SAVE recycles max_lh_slots < leafNum-2 partial vectors (tree/memslot.cpp); max_mem_size as the
+    // reference reads it for values <= 1: 0 = the minimum log2(leafNum)+1, else that fraction of leafNum-2
+    // (tree/phylotree.cpp:993-1015)
+    LhMemSave lh_mem_save = LM_PER_NODE;
+    double max_mem_size = 0.0;
     double min_branch_length = 1e-6;  // utils/tools.cpp:1209, main/phyloanalysis.cpp:4171-4175
     double max_branch_length = 10.0;  // utils/tools.cpp:1212
     bool lk_safe_scaling = false;     // -safe
@@ -201,6 +208,33 @@ struct Params {  // the few fields of utils/tools.h Params the path reads
     int numseq_safe_scaling = 2000;   // utils/tools.cpp:1235-1236
     int device = 0;
     bool device_newton = true;        // run minimizeNewton's iteration on the device when the library offers it
+};
+
+// ---- memory slots of the -mem mode (tree/memslot.h:38-109) ------------------------------------------------
+// A slot is a device partial vector + its scale counters (index into the context's arena); with LM_MEM_SAVE the
+// traversal builder hands the few slots to the directed branches it is working on, locks the ones a pending node
+// still reads, and recycles the unlocked slot with the smallest subtree.
+struct MemSlot {
+    int status = 0;
+    PhyloNeighbor *nei = NULL;
+};
+class MemSlotVector : public std::vector<MemSlot> {
+public:
+    bool enabled = false;
+    void init(int num_slot);
+    void reset();
+    bool lock(PhyloNeighbor *nei);
+    void unlock(PhyloNeighbor *nei);
+    bool locked(PhyloNeighbor *nei);
+    int allocate(PhyloNeighbor *nei);  // -1: every slot is locked
+    void update(PhyloNeighbor *nei);
+    void takeover(PhyloNeighbor *nei, PhyloNeighbor *taken_nei);
+
+private:
+    std::map<PhyloNeighbor *, int> nei_id_map;
+    int free_count = 0;
+    int findNei(PhyloNeighbor *nei);
+    void addNei(PhyloNeighbor *nei, int id);
 };
 
 class PhyloTree {
@@ -281,6 +315,8 @@ public:
     std::vector<double> _pattern_lh, _pattern_lh_cat;  // filled lazily (computePatternLikelihood)
     int64_t kernel_calls = 0;  // C-ABI calls made (host-side statistic)
     b200lk_ctx *ctx = NULL;    // device residency of this tree
+    MemSlotVector mem_slots;   // -mem (tree/phylotree.h: mem_slots)
+    int max_lh_slots = 0;      // partial-vector slots handed out (leafNum-2, or fewer with LM_MEM_SAVE)
 
 protected:
     ComputePartialLikelihoodType computePartialLikelihoodPointer = NULL;

@@ -84,15 +84,29 @@ void PhyloTree::initializeAllPartialLh() {
     int nint = 0;
     for (PhyloNode *n : all_nodes)
         for (PhyloNeighbor *nb : n->neighbors) { nb->slot = -1; nb->partial_lh_computed = 0; }
-    std::vector<std::pair<PhyloNode *, PhyloNode *>> stack;
-    stack.push_back(std::make_pair(root, (PhyloNode *)NULL));
-    while (!stack.empty()) {
-        PhyloNode *node = stack.back().first, *dad = stack.back().second;
-        stack.pop_back();
-        if (dad && !node->isLeaf()) dad->findNeighbor(node)->slot = nint++;
-        for (PhyloNeighbor *nb : node->neighbors)
-            if (nb->node != dad) stack.push_back(std::make_pair(nb->node, node));
+    const bool mem_save = params && params->lh_mem_save == LM_MEM_SAVE;
+    if (!mem_save) {
+        std::vector<std::pair<PhyloNode *, PhyloNode *>> stack;
+        stack.push_back(std::make_pair(root, (PhyloNode *)NULL));
+        while (!stack.empty()) {
+            PhyloNode *node = stack.back().first, *dad = stack.back().second;
+            stack.pop_back();
+            if (dad && !node->isLeaf()) dad->findNeighbor(node)->slot = nint++;
+            for (PhyloNeighbor *nb : node->neighbors)
+                if (nb->node != dad) stack.push_back(std::make_pair(nb->node, node));
+        }
+        mem_slots.enabled = false;
+    } else {
+        // getMemoryRequired, tree/phylotree.cpp:993-1015: no slot is bound up front (:1153-1158); the traversal
+        // builder allocates them
+        const int full = leafNum - 2, min_slots = (int)log2((double)leafNum) + 1;  // LH_MIN_CONST = 1 (:42)
+        int want = params->max_mem_size == 0.0 ? min_slots
+                   : (params->max_mem_size <= 1.0 ? (int)floor(params->max_mem_size * full) : full);
+        nint = std::max(min_slots, std::min(want, full));
+        mem_slots.enabled = true;
+        mem_slots.init(nint);
     }
+    max_lh_slots = nint;
     computeSizes(root, NULL);
     for (PhyloNode *n : all_nodes)
         for (PhyloNeighbor *nb : n->neighbors)
@@ -194,38 +208,135 @@ void PhyloTree::reorientPartialLh(PhyloNeighbor *dad_branch, PhyloNode *dad) {
     for (PhyloNeighbor *nb : node->neighbors) {
         if (nb->node == dad) continue;
         PhyloNeighbor *back = nb->node->findNeighbor(node);
-        if (back->slot >= 0) {  // MemSlotVector::takeover, tree/memslot.cpp:206-213
-            dad_branch->slot = back->slot;
-            back->slot = -1;
-            back->partial_lh_computed &= ~1;
+        if (back->slot >= 0) {
+            mem_slots.takeover(dad_branch, back);  // tree/memslot.cpp:206-222
             break;
         }
     }
-    if (dad_branch->slot < 0) outError("partial_lh is not re-oriented");
+    if (!mem_slots.enabled && dad_branch->slot < 0) outError("partial_lh is not re-oriented");
 }
 
+// tree/phylotree.cpp:5907-6015.  Returns whether the branch's slot was locked here (the caller unlocks it once the
+// node that reads it has been added).
 bool PhyloTree::computeTraversalInfo(PhyloNeighbor *dad_branch, PhyloNode *dad) {
     PhyloNode *node = dad_branch->node;
-    if ((dad_branch->partial_lh_computed & 1) || node->isLeaf()) return false;
-    // children in descending subtree size (tree/phylotree.cpp:5920-5931), same exchange sort
+    if ((dad_branch->partial_lh_computed & 1) || node->isLeaf()) return mem_slots.lock(dad_branch);
+    // children in descending subtree size (:5920-5931), same exchange sort
     std::vector<PhyloNeighbor *> nv = node->neighbors;
     for (size_t i = 0; i < nv.size(); i++)
         for (size_t j = i + 1; j < nv.size(); j++)
             if (nv[i]->size < nv[j]->size) std::swap(nv[i], nv[j]);
-    for (PhyloNeighbor *nb : nv)
-        if (nb->node != dad) computeTraversalInfo(nb, node);
+    std::vector<char> locked(nv.size(), 0);
+    for (size_t i = 0; i < nv.size(); i++)
+        if (nv[i]->node != dad) locked[i] = computeTraversalInfo(nv[i], node);
     dad_branch->partial_lh_computed |= 1;
     reorientPartialLh(dad_branch, dad);
+    if (dad_branch->slot < 0 || mem_slots.locked(dad_branch)) {
+        // still no entry: memory-saving mode hands out a free or the smallest unlocked slot (:5951-5983)
+        if (mem_slots.allocate(dad_branch) < 0) outError("No free/unlocked mem slot found!");
+    } else {
+        mem_slots.update(dad_branch);
+    }
+    if (mem_slots.enabled)
+        for (size_t i = 0; i < nv.size(); i++)
+            if (nv[i]->node != dad && !nv[i]->node->isLeaf() && locked[i]) mem_slots.unlock(nv[i]);
     TraversalInfo info = {dad_branch, dad};
     traversal_info.push_back(info);
-    return true;
+    return mem_slots.lock(dad_branch);
 }
 
+// tree/phylokernelnew.h:1150-1200
 void PhyloTree::computeTraversalInfo(PhyloNode *node, PhyloNode *dad) {
     traversal_info.clear();
+    if (mem_slots.enabled) {  // larger side first (:1172-1186)
+        PhyloNeighbor *db = dad->findNeighbor(node), *nb = node->findNeighbor(dad);
+        if (db->size < nb->size) std::swap(node, dad);
+    }
     PhyloNeighbor *dad_branch = dad->findNeighbor(node), *node_branch = node->findNeighbor(dad);
-    computeTraversalInfo(dad_branch, dad);
-    computeTraversalInfo(node_branch, node);
+    const bool dad_locked = computeTraversalInfo(dad_branch, dad);
+    const bool node_locked = computeTraversalInfo(node_branch, node);
+    if (mem_slots.enabled) {
+        if (dad_locked) mem_slots.unlock(dad_branch);
+        if (node_locked) mem_slots.unlock(node_branch);
+    }
+}
+
+// ---- MemSlotVector (tree/memslot.cpp) ---------------------------------------------------------------------
+static const int MEM_LOCKED = 1;
+
+void MemSlotVector::init(int num_slot) {
+    assign(num_slot, MemSlot());
+    reset();
+}
+void MemSlotVector::reset() {
+    for (MemSlot &m : *this) { m.status = 0; m.nei = NULL; }
+    nei_id_map.clear();
+    free_count = 0;
+}
+int MemSlotVector::findNei(PhyloNeighbor *nei) {
+    std::map<PhyloNeighbor *, int>::iterator it = nei_id_map.find(nei);
+    if (it == nei_id_map.end()) outError("MemSlotVector: neighbour has no slot");
+    return it->second;
+}
+void MemSlotVector::addNei(PhyloNeighbor *nei, int id) {
+    nei->slot = id;
+    (*this)[id].nei = nei;
+    nei_id_map[nei] = id;
+}
+bool MemSlotVector::lock(PhyloNeighbor *nei) {
+    if (!enabled || nei->node->isLeaf()) return false;
+    MemSlot &m = (*this)[findNei(nei)];
+    if (m.status & MEM_LOCKED) outError("MemSlotVector: slot is already locked");
+    m.status |= MEM_LOCKED;
+    return true;
+}
+void MemSlotVector::unlock(PhyloNeighbor *nei) {
+    if (!enabled || nei->node->isLeaf()) return;
+    MemSlot &m = (*this)[findNei(nei)];
+    if (!(m.status & MEM_LOCKED)) outError("MemSlotVector: slot is not locked");
+    m.status &= ~MEM_LOCKED;
+}
+bool MemSlotVector::locked(PhyloNeighbor *nei) {
+    if (!enabled || nei->node->isLeaf()) return false;
+    return ((*this)[findNei(nei)].status & MEM_LOCKED) != 0;
+}
+int MemSlotVector::allocate(PhyloNeighbor *nei) {
+    if (!enabled) return -1;
+    if (free_count < (int)size()) {  // a slot never used so far
+        addNei(nei, free_count);
+        return free_count++;
+    }
+    int best = -1, min_size = INT32_MAX;
+    for (int i = 0; i < (int)size(); i++) {  // the unlocked slot whose subtree is cheapest to recompute
+        const MemSlot &m = (*this)[i];
+        if (!(m.status & MEM_LOCKED) && min_size > m.nei->size) {
+            best = i;
+            min_size = m.nei->size;
+            if (min_size == 2) break;
+        }
+    }
+    if (best < 0) return -1;
+    (*this)[best].nei->clearPartialLh();
+    addNei(nei, best);
+    return best;
+}
+void MemSlotVector::update(PhyloNeighbor *nei) {
+    if (!enabled) return;
+    const int id = findNei(nei);
+    if ((*this)[id].nei != nei) {  // the slot was lent to someone else meanwhile: take it back
+        (*this)[id].nei->clearPartialLh();
+        addNei(nei, id);
+    }
+}
+void MemSlotVector::takeover(PhyloNeighbor *nei, PhyloNeighbor *taken_nei) {
+    nei->slot = taken_nei->slot;
+    taken_nei->slot = -1;
+    taken_nei->partial_lh_computed &= ~1;
+    if (!enabled) return;
+    const int id = findNei(taken_nei);
+    nei_id_map.erase(taken_nei);
+    nei_id_map[nei] = id;
+    if ((*this)[id].nei == taken_nei) (*this)[id].nei = nei;
 }
 
 void PhyloTree::packTraversal(std::vector<b200lk_node> &nodes, std::vector<b200lk_child> &children) {

@@ -111,12 +111,19 @@ void b200host_rate_free(void *r) { delete (RateHeterogeneity *)r; }
 
 // ---- tree ------------------------------------------------------------------------------------------------------
 // the reference's set-up order: readTree, setAlignment, setModelFactory, setLikelihoodKernel, initializeAllPartialLh
+static double g_mem_fraction = 0.0;  // Params::max_mem_size of the next -mem tree (0: the minimum number of slots)
+void b200host_set_mem_fraction(double f) { g_mem_fraction = f; }
+
 int b200host_tree_new(void **out, const char *newick, void *aln, void *model, void *rate, int safe, int device,
                       int device_newton) {
     HostTree *h = new HostTree();
     try {
         h->params.lk_safe_scaling = (safe & 1) != 0;
         h->params.asc_lewis = (safe & 2) != 0;  // bit 1 of `safe`: +ASC
+        if (safe & 4) {                         // bit 2: -mem (LM_MEM_SAVE)
+            h->params.lh_mem_save = LM_MEM_SAVE;
+            h->params.max_mem_size = g_mem_fraction;
+        }
         h->params.device = device;
         h->params.device_newton = device_newton != 0;
         h->tree = new PhyloTree();
@@ -148,6 +155,7 @@ static PhyloTree *T(void *hv) {
     return h->super ? (PhyloTree *)h->super : h->tree;
 }
 int b200host_tree_nbranches(void *hv) { return T(hv)->branchNum; }
+int b200host_tree_max_lh_slots(void *hv) { return T(hv)->max_lh_slots; }
 int b200host_tree_set_min_branch(void *hv, double lo, double hi) {
     HostTree *h = (HostTree *)hv;
     h->params.min_branch_length = lo;

@@ -35,7 +35,7 @@ def cuda_backend(hostlib):
     yield
 
 
-def host_problem(tree, model, rates, props, aln, p_invar=0.0, safe=False, device_newton=True):
+def host_problem(tree, model, rates, props, aln, p_invar=0.0, safe=False, device_newton=True, mem_save=None):
     # the host compresses columns itself: expand the generator's weighted patterns back into columns (first
     # appearances keep their order, so pattern p of the host alignment is pattern p of `aln`)
     cols = np.repeat(aln.states, aln.ptn_freq.astype(int), axis=1)
@@ -43,7 +43,7 @@ def host_problem(tree, model, rates, props, aln, p_invar=0.0, safe=False, device
     assert ha.nptn == aln.nptn
     hm = H.HostModel.from_eigen(model)
     hr = H.HostRate.categories(rates, np.asarray(props) * (1.0 - p_invar), p_invar)
-    return H.HostTree(relabel(tree), ha, hm, hr, safe=safe, device_newton=device_newton), ha
+    return H.HostTree(relabel(tree), ha, hm, hr, safe=safe, device_newton=device_newton, mem_save=mem_save), ha
 
 
 def relabel(tree):
@@ -193,6 +193,30 @@ def scenario_optimize_all_branches(device_newton=True):
     return final, t.lengths()
 
 
+def scenario_mem_save(nstates):
+    """-mem (LM_MEM_SAVE, tree/memslot.cpp): log2(T)+1 recycled slots give the same likelihood at every branch, in
+    any visiting order, and the same branch-length optimum as one slot per internal node."""
+    ntaxa = 40
+    tree, model, rates, props, aln = make_problem(ntaxa, 150 if nstates == 4 else 50, nstates=nstates, seed=17,
+                                                  mean_len=0.15)
+    want = oracle_eval(tree, model, rates, props, aln)[0]
+    full, _ = host_problem(tree, model, rates, props, aln)
+    assert full.max_lh_slots == ntaxa - 2
+    final_full = full.optimize_all_branches()
+    for frac, slots in ((0, 6), (0.25, 9), (0.5, 19)):
+        t, _ = host_problem(tree, model, rates, props, aln, mem_save=frac)
+        assert t.max_lh_slots == slots
+        assert abs(t.compute_likelihood() - want) <= 1e-9 * abs(want)
+        order = list(range(t.nbranches))
+        np.random.default_rng(2).shuffle(order)
+        for b in order:
+            assert abs(t.branch_lnl(b) - want) <= 1e-9 * abs(want)
+        final = t.optimize_all_branches()
+        assert abs(final - final_full) <= 1e-7 * abs(final_full)
+        assert np.allclose(t.lengths(), full.lengths(), rtol=1e-5, atol=1e-7)
+    return final_full
+
+
 def scenario_supertree(edge_linked, batching=True):
     tree = W.random_tree(7, 5)
     newick = relabel(tree)
@@ -244,6 +268,11 @@ def test_host_newton_oracle_backend(oracle_backend):
 
 def test_host_optimize_all_branches_oracle_backend(oracle_backend):
     scenario_optimize_all_branches()
+
+
+@pytest.mark.parametrize("nstates", [4, 20])
+def test_host_mem_save_oracle_backend(oracle_backend, nstates):
+    scenario_mem_save(nstates)
 
 
 @pytest.mark.parametrize("edge_linked", [True, False])
@@ -317,6 +346,12 @@ def test_host_device_newton_equals_host_newton(cuda_backend, oracle_lib):
         H.set_kernel_library(None, None)
     assert abs(a - c) <= 1e-9 * abs(c)
     assert np.allclose(la, lc, rtol=1e-6, atol=1e-8)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nstates", [4, 20, 7])
+def test_host_mem_save_cuda(cuda_backend, nstates):
+    scenario_mem_save(nstates)
 
 
 @pytest.mark.gpu
