@@ -176,7 +176,7 @@ def run_reference(args):
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "evals_per_sec": r["evals_per_sec"], "gpu_launches": 0,
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_partitioned(args):
@@ -290,7 +290,7 @@ def run_partitioned(args):
                 "clocks": sampler.summary(), "lnl": lnl,
                 "roofline": {"bound": "hbm", "kernel": "launch-bound regime (1000 small contexts): see DESIGN.md 6",
                              "achieved": None, "peak": None, "unit": "GB/s", "frac": None, "traffic": None}}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -350,10 +350,33 @@ def run_mem_save(args):
             "gpu_launches": int(t.gpu_launches() - launches0), "clocks": sampler.summary(), "lnl": lnl,
             "roofline": {"bound": "tensor" if n >= 9 else "hbm", "kernel": "whole evaluation (wall clock)",
                          "achieved": None, "peak": None, "unit": "TFLOP/s", "frac": None, "traffic": None}}
-    print(json.dumps(line))
+    emit(line)
+
+
+_STDOUT_FD = None
+
+
+def own_stdout():
+    """stdout carries exactly ONE JSON line: libraries that write banners to fd 1 (NCCL's version line, compiler
+    chatter of an on-demand build) are sent to stderr for the life of the process; emit() writes to the real stdout."""
+    global _STDOUT_FD
+    if _STDOUT_FD is None:
+        sys.stdout.flush()
+        _STDOUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _STDOUT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_STDOUT_FD, data)
 
 
 def main():
+    own_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -533,7 +556,7 @@ def main():
             line["roofline"]["traffic"] = json.load(open(tr_file)).get(args.workload)
         except Exception:
             pass
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
