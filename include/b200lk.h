@@ -67,7 +67,7 @@ typedef struct b200lk_dims {
     int64_t nptn;           /* aln->size(): observed site patterns */
     int64_t n_unobserved;   /* model_factory->unobserved_ptns.size() (+ASC), 0 otherwise */
     int32_t device;         /* CUDA device ordinal */
-    int32_t reserved;
+    int32_t site_specific;  /* model->isSiteSpecificModel() (ModelSet, PMSF): per-pattern eigen-systems, nmix = 1 */
 } b200lk_dims;
 
 /* One directed branch of a traversal (TraversalInfo, tree/phylotree.h:320-331):

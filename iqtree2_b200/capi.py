@@ -23,7 +23,7 @@ class Dims(C.Structure):
     _fields_ = [("ntaxa", C.c_int32), ("nstates", C.c_int32), ("ncat", C.c_int32), ("nmix", C.c_int32),
                 ("fused_mix_rate", C.c_int32), ("safe_numeric", C.c_int32), ("n_state_codes", C.c_int32),
                 ("nslots", C.c_int32), ("nptn", C.c_int64), ("n_unobserved", C.c_int64),
-                ("device", C.c_int32), ("reserved", C.c_int32)]
+                ("device", C.c_int32), ("site_specific", C.c_int32)]
 
 
 class Node(C.Structure):
@@ -70,7 +70,8 @@ class Engine:
     """One likelihood context.  Methods mirror include/b200lk.h one to one."""
 
     def __init__(self, *, ntaxa, nstates, ncat, nmix=1, nptn, nslots, n_state_codes, safe_numeric=False,
-                 fused_mix_rate=False, n_unobserved=0, device=0, lib_path=LIB_PATH, prefix="b200lk_"):
+                 fused_mix_rate=False, n_unobserved=0, device=0, lib_path=LIB_PATH, prefix="b200lk_",
+                 site_specific=False):
         if not os.path.exists(lib_path):
             raise B200LKError(
                 "%s is missing: build it first (python -c 'import __graft_entry__ as g; g.build()'). "
@@ -78,7 +79,7 @@ class Engine:
         self.lib = C.CDLL(lib_path)
         self.prefix = prefix
         self.dims = Dims(ntaxa, nstates, ncat, nmix, int(fused_mix_rate), int(safe_numeric), n_state_codes,
-                         nslots, nptn, n_unobserved, device, 0)
+                         nslots, nptn, n_unobserved, device, int(site_specific))
         self.ncat_mix = ncat if fused_mix_rate else ncat * nmix
         self.block = nstates * self.ncat_mix
         self.ctx = C.c_void_p()
@@ -144,6 +145,13 @@ class Engine:
         f.argtypes = [C.c_void_p] + [C.POINTER(C.c_double)] * 7
         self._check(f(self.ctx, _dp(arrs[0]), _dp(arrs[1]), None if tot is None else _dp(tot), _dp(arrs[2]),
                       _dp(arrs[3]), _dp(arrs[4]), _dp(arrs[5])))
+
+    def set_site_models(self, eval_, evec, inv_evec, rates, props, tipvec):
+        """Site-specific models (PMSF / ModelSet): eval [nptn][n], evec / inv_evec [nptn][n][n], tipvec [codes][n]."""
+        arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in (eval_, evec, inv_evec, rates, props, tipvec)]
+        f = self._f("set_site_models")
+        f.argtypes = [C.c_void_p] + [C.POINTER(C.c_double)] * 6
+        self._check(f(self.ctx, *[_dp(a) for a in arrs]))
 
     def fetch_model(self):
         n, nmix = self.dims.nstates, self.dims.nmix

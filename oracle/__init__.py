@@ -50,7 +50,7 @@ class RefRun:
     (ref_harness.cpp).  kernel: LK_SSE2 (Vec2d), LK_AVX (Vec4d), LK_AVX_FMA (Vec4d + FMA)."""
 
     def __init__(self, tree, aln, model, rates, props, *, kernel=LK_AVX_FMA, safe=False, threads=1, p_invar=0.0,
-                 unobserved=None, fused=False):
+                 unobserved=None, fused=False, site_models=None):
         import ctypes as C
         import numpy as np
         from iqtree2_b200 import workload as W
@@ -84,6 +84,9 @@ class RefRun:
         if unobserved is not None:  # +ASC (Lewis): [ntaxa][n_unobserved] state codes
             un = np.ascontiguousarray(unobserved, dtype=np.uint8)
             self.lib.ref_set_next_unobserved(un.shape[1], C.c_void_p(un.ctypes.data), un.shape[0])
+        if site_models is not None:  # (eval [nptn][n], evec [nptn][n][n], inv_evec [nptn][n][n]): ModelSet / PMSF
+            sm = [np.ascontiguousarray(a, dtype=np.float64) for a in site_models]
+            self.lib.ref_set_next_site_models(C.c_int64(aln.nptn), aln.nstates, *[C.c_void_p(a.ctypes.data) for a in sm])
         if fused:  # model_factory->fused_mix_rate: category c = mixture class c at rate category c
             self.lib.ref_set_next_fused(1)
         self.lib.ref_create.restype = C.c_void_p

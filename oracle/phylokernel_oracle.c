@@ -49,6 +49,11 @@ typedef struct orc_ctx {
     double *theta_all, *buffer_scale_all, *pattern_lh, *pattern_lh_cat;
     int theta_computed;
     int64_t updates;
+    /* site-specific models (SITE_MODEL = true variants; ModelSet / PMSF): per-pattern eigen-systems
+     * s_eval[nptn][n], s_evec[nptn][n][n], s_inv[nptn][n][n]; s_tip[ntaxa][nptn][n] = the reference's
+     * tip_partial_lh of site models (tree/phylotreesse.cpp:257-340) */
+    int site;
+    double *s_eval, *s_evec, *s_inv, *s_tip;
 } orc_ctx;
 
 /* ------------------------------------------------------------------ helpers */
@@ -290,7 +295,7 @@ int orc_destroy(orc_ctx *c) {
     free(c->partial); free(c->scale); free(c->states); free(c->ptn_freq); free(c->ptn_invar);
     free(c->eval); free(c->evec); free(c->inv_evec); free(c->rates); free(c->props); free(c->mixw);
     free(c->tip_partial_lh); free(c->theta_all); free(c->buffer_scale_all); free(c->pattern_lh);
-    free(c->pattern_lh_cat); free(c);
+    free(c->pattern_lh_cat); free(c->s_eval); free(c->s_evec); free(c->s_inv); free(c->s_tip); free(c);
     return B200LK_OK;
 }
 
@@ -373,6 +378,111 @@ int orc_fetch_model(orc_ctx *c, double *eval, double *evec, double *inv_evec) {
     memcpy(evec, c->evec, sizeof(double) * nmix * n * n);
     memcpy(inv_evec, c->inv_evec, sizeof(double) * nmix * n * n);
     return B200LK_OK;
+}
+
+/* Site-specific models: what a ModelSet hands the SITE_MODEL kernels (model/modelset.cpp:129-200, de-interleaved)
+ * and computeTipPartialLikelihood's site-specific branch (tree/phylotreesse.cpp:257-340):
+ *   tip[t][p][i] = inv_p[i][state]            for a plain state,
+ *                = sum_x inv_p[i][x]          for STATE_UNKNOWN,
+ *                = sum over the ambiguity set for the other codes (ascending x)
+ * -- all three are sum_x inv_p[i][x] * tipvec[state][x] over the non-zero indicator entries. */
+int orc_set_site_models(orc_ctx *c, const double *eval, const double *evec, const double *inv_evec, const double *rates,
+                        const double *props, const double *tipvec) {
+    const int n = c->d.nstates;
+    const int64_t nptn = c->d.nptn;
+    if (!c->d.site_specific || c->d.nmix != 1 || c->d.n_unobserved != 0) return B200LK_ERR_ARG;
+    free(c->s_eval); free(c->s_evec); free(c->s_inv); free(c->s_tip);
+    c->s_eval = malloc(sizeof(double) * nptn * n);
+    c->s_evec = malloc(sizeof(double) * nptn * n * n);
+    c->s_inv = malloc(sizeof(double) * nptn * n * n);
+    c->s_tip = malloc(sizeof(double) * (size_t)c->d.ntaxa * nptn * n);
+    memcpy(c->s_eval, eval, sizeof(double) * nptn * n);
+    memcpy(c->s_evec, evec, sizeof(double) * nptn * n * n);
+    memcpy(c->s_inv, inv_evec, sizeof(double) * nptn * n * n);
+    memcpy(c->rates, rates, sizeof(double) * c->d.ncat);
+    memcpy(c->props, props, sizeof(double) * c->d.ncat);
+    c->mixw[0] = 1.0;
+    for (int t = 0; t < c->d.ntaxa; t++)
+        for (int64_t p = 0; p < nptn; p++) {
+            const double *tv = tipvec + (size_t)c->states[(size_t)t * c->ntot + p] * n;
+            const double *inv = c->s_inv + (size_t)p * n * n;
+            double *out = c->s_tip + ((size_t)t * nptn + p) * n;
+            for (int i = 0; i < n; i++) {
+                double v = 0.0;
+                for (int x = 0; x < n; x++)
+                    if (tv[x] != 0.0) v += inv[i * n + x];
+                out[i] = v;
+            }
+        }
+    c->site = 1;
+    c->theta_computed = 0;
+    return B200LK_OK;
+}
+
+/* dotProductExp, tree/phylokernelnew.h:808-842 */
+static inline double dot_exp3(const double *A, const double *B, const double *C, double D, int N) {
+    double X = exp(A[0] * D) * B[0] * C[0];
+    for (int i = 1; i < N; i++) X = fma(exp(A[i] * D), B[i] * C[i], X);
+    return X;
+}
+static inline double dot_exp2(const double *A, const double *B, double D, int N) {
+    double X = exp(A[0] * D) * B[0];
+    for (int i = 1; i < N; i++) X = fma(exp(A[i] * D), B[i], X);
+    return X;
+}
+
+static inline void rescale(double *v, int count);
+
+/* SITE_MODEL branches of computePartialLikelihoodGenericSIMD: tip-tip :1653-1680, tip-internal :1772-1800,
+ * internal-internal :1952-1968 (scaling as in the ordinary branches).  Bifurcating nodes only. */
+static void update_node_site(orc_ctx *c, const b200lk_node *nd, const b200lk_child *ch, int64_t lo, int64_t hi) {
+    const int n = c->d.nstates, ncat = c->d.ncat, block = c->block, safe = c->d.safe_numeric;
+    const int64_t nptn = c->d.nptn;
+    double *out = c->partial[nd->out_slot];
+    uint8_t *oscale = c->scale[nd->out_slot];
+    int il = 0, ir = 1;
+    if (ch[0].kind != B200LK_CHILD_LEAF && ch[1].kind == B200LK_CHILD_LEAF) { il = 1; ir = 0; }
+    const b200lk_child *L = &ch[il], *R = &ch[ir];
+    const int lleaf = L->kind == B200LK_CHILD_LEAF, rleaf = R->kind == B200LK_CHILD_LEAF;
+    double len_left[ncat], len_right[ncat], expl[n], expr[n], tmp[n];
+    for (int k = 0; k < ncat; k++) { /* :1362-1374 */
+        len_left[k] = c->rates[k] * L->length;
+        len_right[k] = c->rates[k] * R->length;
+    }
+    for (int64_t p = lo; p < hi; p++) {
+        const double *eval = c->s_eval + (size_t)p * n, *evec = c->s_evec + (size_t)p * n * n;
+        const double *inv = c->s_inv + (size_t)p * n * n;
+        uint8_t *sd = safe ? oscale + p * ncat : oscale + p;
+        double *po = out + (size_t)p * block;
+        const double *vl = lleaf ? c->s_tip + ((size_t)L->id * nptn + p) * n : c->partial[L->id] + (size_t)p * block;
+        const double *vr = rleaf ? c->s_tip + ((size_t)R->id * nptn + p) * n : c->partial[R->id] + (size_t)p * block;
+        const uint8_t *sl = lleaf ? NULL : c->scale[L->id], *sr = rleaf ? NULL : c->scale[R->id];
+        if (lleaf && rleaf) memset(sd, 0, safe ? ncat : 1);
+        else if (lleaf) memcpy(sd, safe ? sr + p * ncat : sr + p, safe ? ncat : 1);
+        else if (!safe) sd[0] = sl[p] + sr[p];
+        double lh_max = 0.0;
+        for (int k = 0; k < ncat; k++) {
+            if (safe) {
+                lh_max = 0.0;
+                if (!lleaf) sd[k] = sl[p * ncat + k] + sr[p * ncat + k];
+            }
+            for (int i = 0; i < n; i++) {
+                expl[i] = exp(eval[i] * len_left[k]) * (lleaf ? vl[i] : vl[k * n + i]);
+                expr[i] = exp(eval[i] * len_right[k]) * (rleaf ? vr[i] : vr[k * n + i]);
+            }
+            for (int x = 0; x < n; x++) /* dotProductDualVec */
+                tmp[x] = dot_tree(evec + (size_t)x * n, expl, n) * dot_tree_cd(evec + (size_t)x * n, expr, n);
+            prod_vec_mat(tmp, inv, po + k * n, &lh_max, n);
+            if (safe && !(lleaf && rleaf) && lh_max < SCALING_THRESHOLD && c->ptn_invar[p] == 0.0) {
+                rescale(po + k * n, n);
+                sd[k] += 1;
+            }
+        }
+        if (!safe && !(lleaf && rleaf) && lh_max < SCALING_THRESHOLD && c->ptn_invar[p] == 0.0) {
+            rescale(po, block);
+            sd[0] += 1;
+        }
+    }
 }
 
 /* --------------------------------------------------------- computePartialInfo */
@@ -577,6 +687,25 @@ int orc_update_partials(orc_ctx *c, const b200lk_node *nodes, int32_t nnodes, co
                         int32_t nchildren) {
     const int n = c->d.nstates, block = c->block;
     if (nnodes <= 0) return B200LK_OK;
+    if (c->site) { /* no P-factor tables: every pattern has its own eigen-system */
+        for (int i = 0; i < nnodes; i++) {
+            if (nodes[i].nchild != 2) return B200LK_ERR_UNSUPPORTED;
+            int rc = ensure_slot(c, nodes[i].out_slot);
+            if (rc) return rc;
+        }
+        int64_t ntot_s = c->ntot;
+        int nthr_s = c->nthreads;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) num_threads(nthr_s)
+#endif
+        for (int t = 0; t < nthr_s; t++) {
+            int64_t lo = ntot_s * t / nthr_s, hi = ntot_s * (t + 1) / nthr_s;
+            for (int i = 0; i < nnodes; i++) update_node_site(c, &nodes[i], children + nodes[i].child_begin, lo, hi);
+        }
+        c->updates += (int64_t)nnodes * ntot_s;
+        c->theta_computed = 0;
+        return B200LK_OK;
+    }
     double **echild = (double **)calloc(nchildren, sizeof(double *));
     double **leaf = (double **)calloc(nchildren, sizeof(double *));
     for (int i = 0; i < nnodes; i++) {
@@ -653,11 +782,11 @@ int orc_branch_lnl(orc_ctx *c, b200lk_end dad, b200lk_end node, double length, d
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     const int64_t nptn = c->d.nptn, ntot = c->ntot;
     double val[block];
-    branch_vals(c, length, val, NULL, NULL);
+    if (!c->site) branch_vals(c, length, val, NULL, NULL);
     const double *pdad_all = c->partial[node.id]; /* "partial_lh_dad" = dad_branch->partial_lh */
     const uint8_t *sdad = c->scale[node.id];
     double *lh_node_tab = NULL;
-    if (dad.kind == B200LK_CHILD_LEAF) { /* :2757-2785: partial_lh_node[s][c][i] = val[c][i]*tip[s][m][i] */
+    if (dad.kind == B200LK_CHILD_LEAF && !c->site) { /* :2757-2785: partial_lh_node[s][c][i] = val[c][i]*tip[s][m][i] */
         int tip_block = n * c->d.nmix;
         lh_node_tab = (double *)malloc(sizeof(double) * block * c->d.n_state_codes);
         for (int s = 0; s < c->d.n_state_codes; s++)
@@ -678,7 +807,23 @@ int orc_branch_lnl(orc_ctx *c, b200lk_end dad, b200lk_end node, double length, d
             const double *pdad = pdad_all + (size_t)p * block;
             double lh_ptn = 0.0, min_scale;
             uint8_t sum_scale[ncm];
-            if (dad.kind == B200LK_CHILD_LEAF) {
+            if (c->site) { /* :2815-2831, 2969-2985: dotProductExp per category, then * cat_prop */
+                const double *ev = c->s_eval + (size_t)p * n;
+                const int leafdad = dad.kind == B200LK_CHILD_LEAF;
+                const double *other = leafdad ? c->s_tip + ((size_t)dad.id * nptn + p) * n
+                                              : c->partial[dad.id] + (size_t)p * block;
+                const uint8_t *snode = leafdad ? NULL : c->scale[dad.id];
+                for (int cc = 0; cc < ncm; cc++) {
+                    lh_cat[cc] = dot_exp3(ev, leafdad ? other : other + cc * n, pdad + cc * n, c->rates[cc] * length, n);
+                    lh_cat[cc] *= c->props[cc];
+                    if (!safe) lh_ptn += lh_cat[cc];
+                }
+                if (safe)
+                    for (int cc = 0; cc < ncm; cc++)
+                        sum_scale[cc] = (uint8_t)(sdad[p * ncm + cc] + (leafdad ? 0 : snode[p * ncm + cc]));
+                else
+                    min_scale = (double)((int)sdad[p] + (leafdad ? 0 : (int)snode[p]));
+            } else if (dad.kind == B200LK_CHILD_LEAF) {
                 const double *lh_node = lh_node_tab + (size_t)block * tip_state(c, dad.id, p);
                 for (int cc = 0; cc < ncm; cc++) { /* :2857-2867 */
                     lh_cat[cc] = dot_vec(lh_node + cc * n, pdad + cc * n, n);
@@ -770,10 +915,11 @@ int orc_build_theta(orc_ctx *c, b200lk_end dad, b200lk_end node) {
             uint8_t sum_scale[ncm];
             int norm_scale;
             if (dad.kind == B200LK_CHILD_LEAF) { /* :2091-2141 */
-                const double *tip = c->tip_partial_lh + (size_t)tip_block * tip_state(c, dad.id, p);
+                const double *tip = c->site ? c->s_tip + ((size_t)dad.id * c->d.nptn + p) * n
+                                            : c->tip_partial_lh + (size_t)tip_block * tip_state(c, dad.id, p);
                 for (int cc = 0; cc < ncm; cc++)
                     for (int i = 0; i < n; i++)
-                        theta[cc * n + i] = tip[(cc / denom) * n + i] * pdad[cc * n + i];
+                        theta[cc * n + i] = tip[c->site ? i : (cc / denom) * n + i] * pdad[cc * n + i];
                 if (safe)
                     for (int cc = 0; cc < ncm; cc++) sum_scale[cc] = sdad[p * ncm + cc];
                 else
@@ -813,7 +959,7 @@ int orc_derv(orc_ctx *c, double length, double *df, double *ddf) {
     const int n = c->d.nstates, block = c->block;
     const int64_t nptn = c->d.nptn, ntot = c->ntot;
     double val0[block], val1[block], val2[block];
-    branch_vals(c, length, val0, val1, val2);
+    if (!c->site) branch_vals(c, length, val0, val1, val2);
     double all_df = 0.0, all_ddf = 0.0, prob_const = 0.0, df_const = 0.0, ddf_const = 0.0;
     int nthr = c->nthreads;
 #ifdef _OPENMP
@@ -824,6 +970,24 @@ int orc_derv(orc_ctx *c, double length, double *df, double *ddf) {
         double my_df = 0.0, my_ddf = 0.0;
         for (int64_t p = lo; p < hi; p++) {
             double lh, dfp, ddfp;
+            if (c->site) { /* :2469-2487 */
+                const double *ev = c->s_eval + (size_t)p * n, *theta = c->theta_all + (size_t)p * block;
+                lh = dfp = ddfp = 0.0;
+                for (int cc = 0; cc < c->d.ncat; cc++) {
+                    double lh_cat = 0.0, df_cat = 0.0, ddf_cat = 0.0;
+                    for (int i = 0; i < n; i++) {
+                        double cof = ev[i] * c->rates[cc];
+                        double val = exp(cof * length) * theta[cc * n + i];
+                        double v1 = cof * val;
+                        lh_cat += val;
+                        df_cat += v1;
+                        ddf_cat = fma(cof, v1, ddf_cat);
+                    }
+                    lh = fma(c->props[cc], lh_cat, lh);
+                    dfp = fma(c->props[cc], df_cat, dfp);
+                    ddfp = fma(c->props[cc], ddf_cat, ddfp);
+                }
+            } else
             dot_triple(val0, val1, val2, c->theta_all + (size_t)p * block, &lh, &dfp, &ddfp, block, n); /* :2489-2491 */
             lh = fabs(lh) + c->ptn_invar[p];                                                            /* :2494 */
             if (p < nptn) { /* :2496-2505 */
@@ -869,7 +1033,7 @@ int orc_lnl_from_buffer(orc_ctx *c, double length, double *lnl) {
     const int block = c->block;
     const int64_t nptn = c->d.nptn, ntot = c->ntot;
     double val0[block];
-    branch_vals(c, length, val0, NULL, NULL);
+    if (!c->site) branch_vals(c, length, val0, NULL, NULL);
     double tree_lh = 0.0, prob_const = 0.0;
     int nthr = c->nthreads;
 #ifdef _OPENMP
@@ -878,7 +1042,15 @@ int orc_lnl_from_buffer(orc_ctx *c, double length, double *lnl) {
     for (int t = 0; t < nthr; t++) {
         int64_t lo = ntot * t / nthr, hi = ntot * (t + 1) / nthr;
         for (int64_t p = lo; p < hi; p++) {
-            double lh = dot_vec(val0, c->theta_all + (size_t)p * block, block); /* :3291 */
+            double lh;
+            if (c->site) { /* :3278-3289 */
+                const int ns = c->d.nstates;
+                lh = 0.0;
+                for (int cc = 0; cc < c->d.ncat; cc++)
+                    lh = fma(dot_exp2(c->s_eval + (size_t)p * ns, c->theta_all + (size_t)p * block + cc * ns,
+                                      c->rates[cc] * length, ns), c->props[cc], lh);
+            } else
+            lh = dot_vec(val0, c->theta_all + (size_t)p * block, block); /* :3291 */
             lh = fabs(lh) + c->ptn_invar[p];                                     /* :3295 */
             if (p < nptn) {
                 lh = log(fabs(lh)) + c->buffer_scale_all[p]; /* :3300 */

@@ -97,8 +97,10 @@ public:
         memcpy(p, src, sizeof(double) * count);
         return (double *)p;
     }
-    HarnessModel(int n, int nmix_) : ModelSubst(n), nmix(nmix_), eval(NULL), evec(NULL), inv_evec(NULL), ncodes(0) {}
+    HarnessModel(int n, int nmix_) : ModelSubst(n), nmix(nmix_), eval(NULL), evec(NULL), inv_evec(NULL), ncodes(0), site(false) {}
     virtual ~HarnessModel() { free(eval); free(evec); free(inv_evec); }
+    bool site;  // ModelSet-like: per-pattern eigen-systems in the layout of ModelSet::decomposeRateMatrix
+    virtual bool isSiteSpecificModel() { return site; }
     virtual bool isReversible() { return true; }
     virtual bool isMixture() { return nmix > 1; }
     virtual int getNMixtures() { return nmix; }
@@ -189,6 +191,28 @@ void ref_eigensystem_sym(int n, const double *exch, const double *freqs, double 
         }
     }
     ed.eigensystem_sym(rows.data(), fr.data(), eval, evec, inv_evec, n);
+}
+
+// Site-specific models of the NEXT ref_create (what a ModelSet holds after decomposeRateMatrix): eval [nptn][n],
+// evec / inv_evec [nptn][n][n], pattern-major; ref_create re-arranges them to the kernel's vector width exactly like
+// ModelSet::decomposeRateMatrix (model/modelset.cpp:139-200): blocks of V patterns, element-major inside a block,
+// the last model repeated into the padding
+static std::vector<double> next_site_eval, next_site_evec, next_site_inv;
+void ref_set_next_site_models(int64_t nptn, int n, const double *eval, const double *evec, const double *inv_evec) {
+    next_site_eval.assign(eval, eval + (size_t)nptn * n);
+    next_site_evec.assign(evec, evec + (size_t)nptn * n * n);
+    next_site_inv.assign(inv_evec, inv_evec + (size_t)nptn * n * n);
+}
+static double *interleave_models(const std::vector<double> &src, size_t nptn, size_t per, size_t V) {
+    const size_t padded = (nptn + V - 1) / V * V;
+    void *p = NULL;
+    if (posix_memalign(&p, 64, sizeof(double) * (padded * per + 8))) return NULL;
+    double *out = (double *)p;
+    for (size_t q = 0; q < padded; q++) {
+        const double *m = &src[std::min(q, nptn - 1) * per];
+        for (size_t x = 0; x < per; x++) out[(q / V) * V * per + x * V + q % V] = m[x];
+    }
+    return out;
 }
 
 // model_factory->fused_mix_rate of the NEXT ref_create (model/modelfactory.h; category c = mixture class c with rate
@@ -295,7 +319,16 @@ void *ref_create(const ref_problem *pb) {
     tree->readTree(ss, rooted);
     tree->setAlignment(aln);
     tree->setModelFactory(f);
+    m->site = !next_site_eval.empty();
     tree->setLikelihoodKernel((LikelihoodKernel)pb->kernel);
+    if (m->site) {
+        const size_t V = tree->vector_size;
+        free(m->eval); free(m->evec); free(m->inv_evec);
+        m->eval = interleave_models(next_site_eval, pb->nptn, n, V);
+        m->evec = interleave_models(next_site_evec, pb->nptn, (size_t)n * n, V);
+        m->inv_evec = interleave_models(next_site_inv, pb->nptn, (size_t)n * n, V);
+        next_site_eval.clear(); next_site_evec.clear(); next_site_inv.clear();
+    }
     tree->setNumThreads(pb->threads);
     tree->initializeAllPartialLh();
     h->tree = tree;

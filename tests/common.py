@@ -65,3 +65,34 @@ def assert_parity(got, want, tol=1e-9):
         g, w = got[k].reshape(got[k].shape[0], -1), want[k].reshape(want[k].shape[0], -1)
         denom = np.maximum(np.abs(w).max(axis=1, keepdims=True), 1e-300)
         assert float(np.max(np.abs(g - w) / denom)) <= tol, k
+
+
+def site_models_for(aln, nstates, seed, exch=None):
+    """PMSF-shaped site-specific models: one exchangeability matrix, a frequency vector per PATTERN.
+    -> (eval [nptn][n], evec [nptn][n][n], inv_evec [nptn][n][n])"""
+    rng = np.random.default_rng(seed)
+    n = nstates
+    if exch is None:
+        R = np.zeros((n, n))
+        R[np.triu_indices(n, 1)] = rng.gamma(2.0, 1.0, n * (n - 1) // 2)
+        exch = R + R.T
+    ev, U, Ui = [], [], []
+    for _ in range(aln.nptn):
+        fr = rng.dirichlet(np.full(n, 3.0))
+        Q, pi = W.reversible_model(exch, fr)
+        w, evec, inv = W._decompose(Q, pi)
+        ev.append(w); U.append(evec); Ui.append(inv)
+    return np.ascontiguousarray(ev), np.ascontiguousarray(U), np.ascontiguousarray(Ui)
+
+
+def site_engine(aln, models, rates, props, *, nslots, safe_numeric=False, lib_path=None, prefix="b200lk_", p_invar=0.0):
+    """A context in site-specific mode (b200lk_dims.site_specific) with the per-pattern eigen-systems loaded."""
+    from iqtree2_b200 import capi
+    eng = capi.Engine(ntaxa=aln.ntaxa, nstates=aln.nstates, ncat=len(rates), nmix=1, nptn=aln.nptn, nslots=nslots,
+                      n_state_codes=aln.state_unknown + 1, safe_numeric=safe_numeric, site_specific=True,
+                      lib_path=lib_path or capi.LIB_PATH, prefix=prefix)
+    eng.upload_tips(aln.states, aln.ptn_freq)
+    eng.set_ptn_invar(np.zeros(aln.nptn))
+    eng.set_site_models(models[0], models[1], models[2], rates, np.asarray(props) * (1.0 - p_invar),
+                        W.state_indicators(aln.nstates))
+    return eng
