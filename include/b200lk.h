@@ -133,6 +133,16 @@ int b200lk_set_model_rates(b200lk_ctx *ctx, const double *exch, const double *fr
 /* the eigen-system the context currently holds (eval[nmix*n], evec[nmix*n*n], inv_evec[nmix*n*n]) */
 int b200lk_fetch_model(b200lk_ctx *ctx, double *eval, double *evec, double *inv_evec);
 
+/* Site-specific models (the SITE_MODEL = true kernel variants selected when
+ * model->isSiteSpecificModel(), tree/phylokernelfma.cpp:46-83): every pattern has its own eigen-system, as a ModelSet
+ * holds them after decomposeRateMatrix (model/modelset.cpp:129-200; PMSF frequency profiles).  The context must have
+ * been created with dims.site_specific = 1 (nmix = 1, no +ASC, nstates <= 32) and the tips uploaded; the per-taxon,
+ * per-pattern tip vectors of computeTipPartialLikelihood (tree/phylotreesse.cpp:257-340) are built on the device.
+ * eval[nptn][n], evec[nptn][n][n] (row = state), inv_evec[nptn][n][n] (row = eigen index), pattern-major (no vector
+ * interleaving), tipvec[n_state_codes][n] as in b200lk_set_model_rates. */
+int b200lk_set_site_models(b200lk_ctx *ctx, const double *eval, const double *evec, const double *inv_evec,
+                           const double *rates, const double *props, const double *tipvec);
+
 /* ---- the four kernel entry points -------------------------------------- */
 /* computePartialLikelihood over a whole traversal list
  * (computeTraversalInfo + computePartialInfo + computePartialLikelihood*SIMD,

@@ -174,6 +174,13 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
     CUDA_TRY(c, cudaMemcpyAsync(c->d_nodes, c->h_nodes, sizeof(DevNode) * nnodes, cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(c, cudaEventRecord(c->stage_ev[ring], c->stream));
     c->stage_used[ring] = true;
+    if (c->site) {  // site-specific models: no P-factor tables, per-pattern eigen-systems (site.cu)
+        int rs = launch_site_partials(c, levels);
+        if (rs) return rs;
+        c->n_updates += (int64_t)nnodes * c->ntot;
+        c->theta_computed = false;
+        return B200LK_OK;
+    }
     int rc = launch_tables(c, nchildren);
     if (rc) return rc;
     if (tt_off > 0) {

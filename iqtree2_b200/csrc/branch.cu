@@ -30,7 +30,27 @@ struct BranchArgs {
     int64_t nptn, ntot;
     int n, ncm, block, denom, nmix, G, safe, tile;
     int slot_pdad, slot_pnode, dad_taxon;  // batched launches rebuild the pointers above per context from these
+    // site-specific models (SITE_MODEL variants): the branch coefficients depend on the pattern,
+    //   val_p[c][i] = exp(eval_p[i] * rate_c * len) * prop_c   (tree/phylokernelnew.h:2469-2487, 2815-2831, 3278-3289)
+    // and a leaf dad contributes its per-pattern tip vector site_tip[taxon][p][i]
+    const double *site_eval, *site_tip, *rates, *props;
+    double len;
 };
+
+// coefficient of flat element j = c*n + i of pattern p: val0 (which = 0), val1 = cof*val0, val2 = cof*val1
+__device__ __forceinline__ void branch_coef(const BranchArgs &a, int64_t p, int j, double &v0, double &v1, double &v2) {
+    if (!a.site_eval) {
+        v0 = a.val[j];
+        v1 = a.val[a.block + j];
+        v2 = a.val[2 * a.block + j];
+        return;
+    }
+    const int c = j / a.n, i = j - c * a.n;
+    const double cof = a.site_eval[(size_t)p * a.n + i] * a.rates[c];
+    v0 = exp(cof * a.len) * a.props[c];
+    v1 = cof * v0;
+    v2 = cof * v1;
+}
 
 // batched launch (grid.y = context of the supermatrix): same branch, same slots, the context's own buffers
 __device__ __forceinline__ void rebind_branch(BranchArgs &a, const BatchLaunch &bl) {
@@ -170,11 +190,13 @@ __global__ void __launch_bounds__(RED_THREADS) theta_kernel(BranchArgs a, BatchL
         }
         const double *other;
         int tip_mode = a.pnode == nullptr;
-        if (tip_mode) other = a.tip_partial_lh + (size_t)a.dad_states[p] * (n * a.nmix);
+        if (tip_mode)
+            other = a.site_eval ? a.site_tip + ((size_t)a.dad_taxon * a.nptn + p) * n
+                                : a.tip_partial_lh + (size_t)a.dad_states[p] * (n * a.nmix);
         else other = a.pnode;
         for (int j = g; j < block; j += G) {
             int c = j / n;
-            double o = tip_mode ? other[(c / a.denom) * n + (j - c * n)] : other[E(j)];
+            double o = tip_mode ? other[(a.site_eval ? 0 : (c / a.denom) * n) + (j - c * n)] : other[E(j)];
             double t = o * pd[E(j)];
             if (a.safe) {
                 int s = (a.sdad[p * ncm + c] + (a.pnode ? a.snode[p * ncm + c] : 0)) & 0xff;
@@ -201,11 +223,21 @@ __global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red
         if (!valid) p = a.ntot - 1;
         const double *th = a.theta;
         double lh = 0.0, df = 0.0, ddf = 0.0;
-        for (int j = g; j < block; j += G) {
-            double t = th[E(j)];
-            lh = fma(v0[j], t, lh);
-            df = fma(v1[j], t, df);
-            ddf = fma(v2[j], t, ddf);
+        if (a.site_eval) {
+            for (int j = g; j < block; j += G) {
+                double t = th[E(j)], w0, w1, w2;
+                branch_coef(a, p, j, w0, w1, w2);
+                lh = fma(w0, t, lh);
+                df = fma(w1, t, df);
+                ddf = fma(w2, t, ddf);
+            }
+        } else {
+            for (int j = g; j < block; j += G) {
+                double t = th[E(j)];
+                lh = fma(v0[j], t, lh);
+                df = fma(v1[j], t, df);
+                ddf = fma(v2[j], t, ddf);
+            }
         }
         lh = group_sum(lh, G);
         df = group_sum(df, G);
@@ -410,7 +442,15 @@ __global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(BranchArgs a, int 
         if (!valid) p = a.ntot - 1;
         const double *th = a.theta;
         double lh = 0.0;
-        for (int j = g; j < block; j += G) lh = fma(a.val[j], th[E(j)], lh);
+        if (a.site_eval) {
+            for (int j = g; j < block; j += G) {
+                double w0, w1, w2;
+                branch_coef(a, p, j, w0, w1, w2);
+                lh = fma(w0, th[E(j)], lh);
+            }
+        } else {
+            for (int j = g; j < block; j += G) lh = fma(a.val[j], th[E(j)], lh);
+        }
         lh = group_sum(lh, G);
         if (g == 0 && valid) {
             lh = fabs(lh) + a.ptn_invar[p];               // :3295
@@ -443,7 +483,7 @@ __global__ void __launch_bounds__(RED_THREADS) lnl_kernel(BranchArgs a, int red_
         const bool valid = p < a.ntot;
         if (!valid) p = a.ntot - 1;
         const double *pd = a.pdad;
-        const double *w = tip_mode ? a.tip_val + (size_t)a.dad_states[p] * block : a.val;
+        const double *w = (tip_mode && !a.site_eval) ? a.tip_val + (size_t)a.dad_states[p] * block : a.val;
         const double *pn = a.pnode;
         double lh = 0.0;
         int min_scale;
@@ -461,7 +501,14 @@ __global__ void __launch_bounds__(RED_THREADS) lnl_kernel(BranchArgs a, int red_
             double s0 = 0.0, s1 = 0.0;
             const double *wd = w + c * n;
             const int cb = c * n;
-            if (tip_mode) {
+            if (a.site_eval) {
+                const double *tipv = tip_mode ? a.site_tip + ((size_t)a.dad_taxon * a.nptn + p) * n : nullptr;
+                for (int i = 0; i < n; i++) {
+                    double w0, w1, w2;
+                    branch_coef(a, p, cb + i, w0, w1, w2);
+                    s0 = fma(w0 * (tip_mode ? tipv[i] : pn[E(cb + i)]), pd[E(cb + i)], s0);
+                }
+            } else if (tip_mode) {
                 for (int i = 0; i + 1 < n; i += 2) {
                     s0 = fma(wd[i], pd[E(cb + i)], s0);
                     s1 = fma(wd[i + 1], pd[E(cb + i + 1)], s1);
@@ -559,6 +606,11 @@ static void fill_common(b200lk_ctx *c, BranchArgs &a) {
     a.nmix = c->d.nmix;
     a.safe = c->d.safe_numeric;
     a.tile = c->tile;
+    a.site_eval = c->site ? c->s_eval : nullptr;
+    a.site_tip = c->s_tip;
+    a.rates = c->m.rates;
+    a.props = c->m.props;
+    a.len = 0.0;
 }
 
 static BatchLaunch batch_of(const b200lk_ctx *c) {
@@ -587,6 +639,7 @@ static int launch_asc_fix(b200lk_ctx *c, int mode) {
 }
 
 static int launch_val(b200lk_ctx *c, double length, int want_tip) {
+    if (c->site) return B200LK_OK;  // per-pattern coefficients are formed inside the kernels
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     val_kernel<<<grid2(c, (c->block + 255) / 256), 256, 0, c->stream>>>(c->m, length, c->val, c->tip_val, c->d.nstates,
                                                                         c->d.ncat, c->ncat_mix, denom, c->d.nmix,
@@ -602,6 +655,7 @@ int launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double len
     BranchArgs a;
     fill_args(c, a, dad, node);
     fill_common(c, a);
+    a.len = length;
     a.G = pick_group(c->ncat_mix);
     int grid = grid_for(c, a.G, c->ntot);
     lnl_kernel<<<grid2(c, grid), RED_THREADS, 0, c->stream>>>(a, grid, batch_of(c));
@@ -640,6 +694,7 @@ int launch_derv(b200lk_ctx *c, double length) {
     BranchArgs a;
     memset(&a, 0, sizeof(a));
     fill_common(c, a);
+    a.len = length;
     a.G = pick_group(c->block);
     int grid = grid_for(c, a.G, c->ntot);
     derv_kernel<<<grid2(c, grid), RED_THREADS, 0, c->stream>>>(a, grid, batch_of(c));
@@ -656,6 +711,7 @@ int launch_from_buffer(b200lk_ctx *c, double length) {
     BranchArgs a;
     memset(&a, 0, sizeof(a));
     fill_common(c, a);
+    a.len = length;
     a.G = pick_group(c->block);
     int grid = grid_for(c, a.G, c->ntot);
     frombuf_kernel<<<grid2(c, grid), RED_THREADS, 0, c->stream>>>(a, grid, batch_of(c));
@@ -668,6 +724,7 @@ int launch_from_buffer(b200lk_ctx *c, double length) {
 
 // b200lk_optimize_branch: theta for (dad, node) must already be built
 int launch_newton(b200lk_ctx *c, const b200lk_newton *nr) {
+    if (c->site) return B200LK_ERR_UNSUPPORTED;  // per-pattern coefficients: the host iteration drives b200lk_derv
     BranchArgs a;
     memset(&a, 0, sizeof(a));
     fill_common(c, a);

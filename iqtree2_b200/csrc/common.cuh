@@ -126,6 +126,8 @@ struct b200lk_ctx {
     size_t tt_cap;      // doubles
     unsigned long long *pmax;  // mixture launches of dense.cu: per (node of the level, pattern) max|x| bits
     size_t pmax_bytes;
+    bool site;  // dims.site_specific: per-pattern eigen-systems (site.cu); no P-factor tables, pattern-major layout
+    double *s_eval, *s_evec, *s_inv, *s_tip, *s_tipvec;  // [nptn][n], [nptn][n][n] x2, [ntaxa][nptn][n], [codes][n]
     double *eig_in, *eig_host;  // staging of b200lk_set_model_rates (eigen.cu): device inputs, pinned host mirror
     double *red_partial;   // [3][red_blocks] block partial sums
     int red_blocks;
@@ -184,3 +186,4 @@ int launch_inv_frag(b200lk_ctx *c);
 int launch_tt_tables(b200lk_ctx *c, int nnodes);
 int launch_dense20_tt(b200lk_ctx *c, int node_base, int nnodes);
 int launch_denseN(b200lk_ctx *c, int node_base, int nnodes);
+int launch_site_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels);

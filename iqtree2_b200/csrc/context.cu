@@ -129,6 +129,17 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
         c->frag_cat = c->dense20 ? B200_FRAG20 : c->dense_nt * 2 * c->dense_nt * 32;
     }
     c->tile = (dims->nstates == 4 && c->ncat_mix <= 4 && !c->force_level_batched) ? 32 : 1;
+    c->site = dims->site_specific != 0;
+    if (c->site) {  // site-specific models: own kernels (site.cu) on the pattern-major layout
+        if (dims->nmix != 1 || dims->n_unobserved != 0 || dims->nstates > 32 || dims->fused_mix_rate) {
+            delete c;
+            return B200LK_ERR_UNSUPPORTED;
+        }
+        c->tile = 1;
+        c->dense20 = false;
+        c->dense_nt = 0;
+        c->frag_cat = 0;
+    }
     int rc = alloc_all(c);
     if (rc != B200LK_OK) {
         // keep the context alive long enough for the caller to read the message? no: report and free
@@ -159,6 +170,11 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (c->h_rell) cudaFreeHost(c->h_rell);
     if (c->pmax) cudaFree(c->pmax);
     if (c->tt_tables) cudaFree(c->tt_tables);
+    if (c->s_eval) cudaFree(c->s_eval);
+    if (c->s_evec) cudaFree(c->s_evec);
+    if (c->s_inv) cudaFree(c->s_inv);
+    if (c->s_tip) cudaFree(c->s_tip);
+    if (c->s_tipvec) cudaFree(c->s_tipvec);
     if (c->eig_in) cudaFree(c->eig_in);
     if (c->eig_host) cudaFreeHost(c->eig_host);
     free(c->h_evec);
@@ -222,6 +238,7 @@ extern "C" int b200lk_set_model(b200lk_ctx *c, const double *eval, const double 
                                 const double *rates, const double *props, const double *mixw,
                                 const double *tip_partial_lh) {
     if (!c || !eval || !evec || !inv_evec || !rates || !props || !mixw || !tip_partial_lh) return B200LK_ERR_ARG;
+    if (c->site) return B200LK_ERR_STATE;  // a site-specific context takes b200lk_set_site_models
     CUDA_TRY(c, cudaSetDevice(c->device));
     const int n = c->d.nstates, nmix = c->d.nmix;
     cudaStream_t s = c->stream;

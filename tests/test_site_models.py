@@ -60,3 +60,31 @@ def test_site_models_reduce_to_the_homogeneous_model(oracle_lib):
     for k in ("lnl", "df", "ddf", "lnl_buf"):
         assert rel(a[k], b[k]) <= 1e-11, k
     assert rel(a["pattern_lh"], b["pattern_lh"]) <= 1e-11
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates,ncat,ntaxa,nsite,mean_len", [(20, 4, 10, 90, 0.1), (4, 4, 12, 200, 0.1), (4, 1, 6, 64, 0.1), (7, 3, 8, 70, 0.1),
+                                                                (32, 2, 6, 40, 0.1), (20, 2, 130, 70, 0.5), (20, 9, 7, 40, 0.1)])
+def test_site_models_cuda_matches_oracle(oracle_lib, safe, nstates, ncat, ntaxa, nsite, mean_len):
+    oracle.set_ref_quirks(False)
+    tree, _, rates, props, aln = make_problem(ntaxa, nsite, nstates=nstates, ncat=ncat, seed=71, gaps=0.06, mean_len=mean_len)
+    models = site_models_for(aln, nstates, 72)
+    g = site_engine(aln, models, rates, props, nslots=ntaxa, safe_numeric=safe)
+    o = site_engine(aln, models, rates, props, nslots=ntaxa, safe_numeric=safe, lib_path=oracle.ORACLE_LIB, prefix="orc_")
+    for leaf in (0, ntaxa - 1):
+        rg, ro = full_eval(g, tree, leaf), full_eval(o, tree, leaf)
+        assert_parity(rg, ro, 1e-9)
+    if ntaxa >= 100:
+        assert max(int(s.max()) for s in ro["scale"].values()) >= 1
+
+
+@pytest.mark.gpu
+def test_site_context_refuses_what_it_cannot_express(oracle_lib):
+    from iqtree2_b200.capi import B200LKError, Engine
+    with pytest.raises(B200LKError, match="-5"):
+        Engine(ntaxa=4, nstates=20, ncat=2, nmix=2, nptn=10, nslots=4, n_state_codes=24, site_specific=True)
+    tree, model, rates, props, aln = make_problem(6, 50, nstates=20, seed=3)
+    g = site_engine(aln, site_models_for(aln, 20, 4), rates, props, nslots=6)
+    with pytest.raises(B200LKError, match="-3"):
+        g.set_model(model.eval, model.evec, model.inv_evec, rates, props, model.mixw, W.tip_partial_lh(model))
