@@ -49,6 +49,16 @@ extern "C" {
 
 #define B200LK_CHILD_LEAF 0
 #define B200LK_CHILD_INTERNAL 1
+/* non-reversible contexts only (dims.site_specific == B200LK_MODEL_NONREV) */
+#define B200LK_CHILD_ROOT 2            /* the root leaf of a rooted tree (isRootLeaf, tree/mtree.h:135); id ignored */
+#define B200LK_CHILD_TOWARD_ROOT 0x100 /* OR-ed into b200lk_child.kind: child->direction == TOWARD_ROOT */
+#define B200LK_CHILD_KIND_MASK 0xff
+
+/* values of b200lk_dims.site_specific: which kernel family setLikelihoodKernel selects
+ * (tree/phylokernelfma.cpp:41-104) */
+#define B200LK_MODEL_REV 0    /* reversible kernels, tree/phylokernelnew.h */
+#define B200LK_MODEL_SITE 1   /* SITE_MODEL variants: model->isSiteSpecificModel() */
+#define B200LK_MODEL_NONREV 2 /* computeNonrev*: !model->isReversible() || params->kernel_nonrev, tree/phylokernelnonrev.h */
 
 typedef struct b200lk_ctx b200lk_ctx;
 
@@ -67,7 +77,8 @@ typedef struct b200lk_dims {
     int64_t nptn;           /* aln->size(): observed site patterns */
     int64_t n_unobserved;   /* model_factory->unobserved_ptns.size() (+ASC), 0 otherwise */
     int32_t device;         /* CUDA device ordinal */
-    int32_t site_specific;  /* model->isSiteSpecificModel() (ModelSet, PMSF): per-pattern eigen-systems, nmix = 1 */
+    int32_t site_specific;  /* B200LK_MODEL_REV / _SITE (model->isSiteSpecificModel(): ModelSet, PMSF; per-pattern
+                             * eigen-systems, nmix = 1) / _NONREV (non-reversible kernel family) */
 } b200lk_dims;
 
 /* One directed branch of a traversal (TraversalInfo, tree/phylotree.h:320-331):
@@ -142,6 +153,32 @@ int b200lk_fetch_model(b200lk_ctx *ctx, double *eval, double *evec, double *inv_
  * interleaving), tipvec[n_state_codes][n] as in b200lk_set_model_rates. */
 int b200lk_set_site_models(b200lk_ctx *ctx, const double *eval, const double *evec, const double *inv_evec,
                            const double *rates, const double *props, const double *tipvec);
+
+/* Non-reversible kernel family (computeNonrevPartialLikelihood / LikelihoodBranch /
+ * LikelihoodDerv, tree/phylokernelnonrev.h:43-1517, selected when !model->isReversible() || params->kernel_nonrev,
+ * tree/phylokernelfma.cpp:92-100).  The context must have been created with dims.site_specific = B200LK_MODEL_NONREV
+ * (no +ASC: the reference's own tip-internal case indexes the unobserved patterns out of bounds,
+ * tree/phylokernelnonrev.h:399).  Partial vectors hold state likelihoods (no eigen-space), children are combined
+ * through transition matrices P(rate_c * length), transposed for a child that lies TOWARD_ROOT
+ * (tree/phylokernelnew.h:932-956), and the root leaf contributes the state frequencies (:959-964).
+ *   rate_matrix[nmix][n][n]  Q, row-major (ModelMarkov::rate_matrix): dP/dt = Q P, d2P/dt2 = Q Q P
+ *                            (model/modelmarkov.cpp:729-745)
+ *   ceval[nmix][n][2], cevec[nmix][n][n][2], cinv_evec[nmix][n][n][2]
+ *                            complex eigen-system (re, im interleaved): P(t) = Re(cevec exp(ceval t) cinv_evec)
+ *                            (ModelMarkov::computeTransMatrixNonrev, model/modelmarkov.cpp:481-488)
+ *   freqs[nmix][n]           state frequencies (root leaf; unrooted trees weight the branch by them)
+ *   tipvec[n_state_codes][n] as in b200lk_set_model_rates; the last code is the unknown state (all ones)
+ *   rooted                   tree->rooted
+ * Call sequence for a branch: the caller orders the two ends as the kernels do after their swap
+ * (tree/phylokernelnonrev.h:596-603, 1060-1067): `dad` is the leaf end if there is one (the ROOT leaf only when it
+ * is the original dad), otherwise the end farther from the root; b200lk_build_theta only records the ends,
+ * b200lk_derv recomputes from the two partial vectors as the reference does, b200lk_lnl_from_buffer is
+ * b200lk_branch_lnl at the recorded ends (the reference binds no from-buffer kernel, tree/phylokernelfma.cpp:99).
+ * b200lk_derv at a ROOT dad returns B200LK_ERR_UNSUPPORTED (the virtual root branch has no length,
+ * tree/phylokernelnonrev.h:667-670), and so do b200lk_optimize_branch and batches. */
+int b200lk_set_model_nonrev(b200lk_ctx *ctx, const double *rate_matrix, const double *ceval, const double *cevec,
+                            const double *cinv_evec, const double *freqs, const double *tipvec, const double *rates,
+                            const double *props, const double *mixw, int rooted);
 
 /* ---- the four kernel entry points -------------------------------------- */
 /* computePartialLikelihood over a whole traversal list

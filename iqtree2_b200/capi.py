@@ -16,6 +16,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb200lk.so")
 
 LEAF, INTERNAL = 0, 1
+ROOT, TOWARD_ROOT = 2, 0x100          # non-reversible contexts: the root leaf; child->direction == TOWARD_ROOT
+MODEL_REV, MODEL_SITE, MODEL_NONREV = 0, 1, 2   # b200lk_dims.site_specific
 WARN_LNL_NONFINITE, WARN_DERV_NONFINITE = 1, 2
 
 
@@ -71,7 +73,7 @@ class Engine:
 
     def __init__(self, *, ntaxa, nstates, ncat, nmix=1, nptn, nslots, n_state_codes, safe_numeric=False,
                  fused_mix_rate=False, n_unobserved=0, device=0, lib_path=LIB_PATH, prefix="b200lk_",
-                 site_specific=False):
+                 site_specific=False, nonrev=False):
         if not os.path.exists(lib_path):
             raise B200LKError(
                 "%s is missing: build it first (python -c 'import __graft_entry__ as g; g.build()'). "
@@ -79,7 +81,7 @@ class Engine:
         self.lib = C.CDLL(lib_path)
         self.prefix = prefix
         self.dims = Dims(ntaxa, nstates, ncat, nmix, int(fused_mix_rate), int(safe_numeric), n_state_codes,
-                         nslots, nptn, n_unobserved, device, int(site_specific))
+                         nslots, nptn, n_unobserved, device, MODEL_NONREV if nonrev else int(site_specific))
         self.ncat_mix = ncat if fused_mix_rate else ncat * nmix
         self.block = nstates * self.ncat_mix
         self.ctx = C.c_void_p()
@@ -152,6 +154,16 @@ class Engine:
         f = self._f("set_site_models")
         f.argtypes = [C.c_void_p] + [C.POINTER(C.c_double)] * 6
         self._check(f(self.ctx, *[_dp(a) for a in arrs]))
+
+    def set_model_nonrev(self, rate_matrix, ceval, cevec, cinv_evec, freqs, tipvec, rates, props, mixw, rooted):
+        """Non-reversible kernel family: Q [nmix][n][n], complex eigen-system of Q, state frequencies."""
+        n, nmix = self.dims.nstates, self.dims.nmix
+        cx = [np.ascontiguousarray(a, dtype=np.complex128).view(np.float64) for a in (ceval, cevec, cinv_evec)]
+        re = [np.ascontiguousarray(a, dtype=np.float64) for a in (rate_matrix, freqs, tipvec, rates, props, mixw)]
+        assert re[0].size == nmix * n * n and cx[0].size == 2 * nmix * n and cx[1].size == 2 * nmix * n * n
+        assert cx[2].size == 2 * nmix * n * n and re[1].size == nmix * n and re[2].size == self.dims.n_state_codes * n
+        self._check(self._f("set_model_nonrev")(self.ctx, _dp(re[0]), _dp(cx[0]), _dp(cx[1]), _dp(cx[2]), _dp(re[1]),
+                                                _dp(re[2]), _dp(re[3]), _dp(re[4]), _dp(re[5]), int(bool(rooted))))
 
     def fetch_model(self):
         n, nmix = self.dims.nstates, self.dims.nmix

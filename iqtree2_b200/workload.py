@@ -78,6 +78,36 @@ class Tree:
         return ("(" + self.names[root_leaf] + ":" +
                 repr(round(self.get_length(root_leaf, c), digits)) + "," + ",".join(inner) + ");")
 
+    def to_newick_rooted(self, root_leaf: int, digits: int = 10) -> str:
+        """Newick of a ROOTED tree whose root is marked by the leaf ``root_leaf``: the top node is that leaf's
+        neighbour and the root leaf itself is left out (the reference adds it when it reads a tree whose top node
+        has two children, tree/mtree.cpp:739-751)."""
+        import sys
+        sys.setrecursionlimit(max(10000, 4 * self.nnodes))
+
+        def rec(u, dad):
+            if self.is_leaf(u):
+                s = self.names[u]
+            else:
+                s = "(" + ",".join(rec(v, u) for v in self.adj[u] if v != dad) + ")"
+            return s + ":" + repr(round(self.get_length(u, dad), digits))
+
+        c = self.adj[root_leaf][0]
+        return "(" + ",".join(rec(v, c) for v in self.adj[c] if v != root_leaf) + ");"
+
+    def parents_from(self, root_leaf: int):
+        """parent[u] on the path toward ``root_leaf`` (-1 for the root leaf itself)."""
+        parent = [-1] * self.nnodes
+        order = [root_leaf]
+        seen = {root_leaf}
+        for u in order:
+            for v in self.adj[u]:
+                if v not in seen:
+                    seen.add(v)
+                    parent[v] = u
+                    order.append(v)
+        return parent
+
     @staticmethod
     def from_newick(text: str, taxon_names: list | None = None) -> "Tree":
         """Parse a Newick string.  A degree-2 root is suppressed (unrooted tree).
@@ -262,6 +292,25 @@ def traversal(tree: Tree, node: int, dad: int, slot_of=None):
     return out
 
 
+def traversal_rooted(tree: Tree, node: int, dad: int, root_leaf: int, slot_of=None):
+    """``traversal`` for the non-reversible kernel family on a rooted tree whose root is the leaf ``root_leaf``
+    (the tree's last leaf): the root leaf becomes a child of kind 2 (B200LK_CHILD_ROOT) and a child that lies on the
+    path to the root carries the flag 0x100 (child->direction == TOWARD_ROOT, tree/phylotree.cpp:5710-5725)."""
+    parent = tree.parents_from(root_leaf)
+    out = []
+    for v, u, slot, ch in traversal(tree, node, dad, slot_of):
+        kids = [w for w in tree.adj[v] if w != u]
+        new = []
+        for w, (kind, cid, ln) in zip(kids, ch):
+            if w == root_leaf:
+                kind, cid = 2, 0
+            if parent[v] == w:
+                kind |= 0x100
+            new.append((kind, cid, ln))
+        out.append((v, u, slot, new))
+    return out
+
+
 # --------------------------------------------------------------------------
 # substitution models -> eigen-systems
 # --------------------------------------------------------------------------
@@ -318,6 +367,62 @@ def make_model(classes, mixw=None) -> EigenModel:
     return EigenModel(nstates=len(F[0]), eval=np.ascontiguousarray(ev),
                       evec=np.ascontiguousarray(U), inv_evec=np.ascontiguousarray(Ui),
                       freqs=np.ascontiguousarray(F), mixw=mixw / mixw.sum(), Q=np.ascontiguousarray(Qs))
+
+
+@dataclass
+class NonrevModel:
+    """What the non-reversible kernel family takes from ModelMarkov: Q, its complex eigen-system
+    (P(t) = Re(cevec exp(ceval t) cinv_evec), model/modelmarkov.cpp:481-488) and the state frequencies."""
+    nstates: int
+    Q: np.ndarray          # [nmix][n][n]
+    ceval: np.ndarray      # [nmix][n]      complex
+    cevec: np.ndarray      # [nmix][n][n]   complex
+    cinv_evec: np.ndarray  # [nmix][n][n]   complex
+    freqs: np.ndarray      # [nmix][n]
+    mixw: np.ndarray       # [nmix]
+
+    @property
+    def nmix(self) -> int:
+        return int(self.Q.shape[0])
+
+
+def nonrev_from_Q(Qs, freqs, mixw=None) -> NonrevModel:
+    Qs = np.ascontiguousarray(Qs, dtype=np.float64)
+    ev, V, Vi = [], [], []
+    for Q in Qs:
+        w, v = np.linalg.eig(Q)
+        ev.append(w); V.append(v); Vi.append(np.linalg.inv(v))
+    nmix = len(Qs)
+    mixw = np.full(nmix, 1.0 / nmix) if mixw is None else np.asarray(mixw, dtype=np.float64)
+    return NonrevModel(nstates=Qs.shape[1], Q=Qs, ceval=np.ascontiguousarray(ev, dtype=np.complex128),
+                       cevec=np.ascontiguousarray(V, dtype=np.complex128),
+                       cinv_evec=np.ascontiguousarray(Vi, dtype=np.complex128),
+                       freqs=np.ascontiguousarray(freqs, dtype=np.float64), mixw=mixw / mixw.sum())
+
+
+def random_nonrev_model(nstates: int, seed: int, nmix: int = 1) -> NonrevModel:
+    """Seeded unrestricted (UNREST-like) rate matrices: free off-diagonal rates, the state frequencies are the
+    stationary distribution of Q, mean rate normalised to 1."""
+    rng = np.random.default_rng(seed)
+    Qs, F = [], []
+    for _ in range(nmix):
+        Q = rng.gamma(1.0, 1.0, size=(nstates, nstates)) + 0.02
+        np.fill_diagonal(Q, 0.0)
+        np.fill_diagonal(Q, -Q.sum(axis=1))
+        w, v = np.linalg.eig(Q.T)
+        pi = np.real(v[:, np.argmin(np.abs(w))])
+        pi = pi / pi.sum()
+        Q = Q / (-(pi * np.diag(Q)).sum())
+        Qs.append(Q); F.append(pi)
+    w = rng.dirichlet(np.full(nmix, 5.0)) if nmix > 1 else None
+    return nonrev_from_Q(Qs, F, w)
+
+
+def nonrev_from_reversible(model: EigenModel) -> NonrevModel:
+    """A reversible model in the form the non-reversible kernels take (params->kernel_nonrev)."""
+    return NonrevModel(nstates=model.nstates, Q=np.ascontiguousarray(model.Q),
+                       ceval=model.eval.astype(np.complex128), cevec=model.evec.astype(np.complex128),
+                       cinv_evec=model.inv_evec.astype(np.complex128), freqs=model.freqs, mixw=model.mixw)
 
 
 def gtr_model(rates=(1.0, 2.0, 1.5, 1.2, 2.5, 1.0), freqs=(0.3, 0.2, 0.2, 0.3)) -> EigenModel:

@@ -50,7 +50,7 @@ class RefRun:
     (ref_harness.cpp).  kernel: LK_SSE2 (Vec2d), LK_AVX (Vec4d), LK_AVX_FMA (Vec4d + FMA)."""
 
     def __init__(self, tree, aln, model, rates, props, *, kernel=LK_AVX_FMA, safe=False, threads=1, p_invar=0.0,
-                 unobserved=None, fused=False, site_models=None):
+                 unobserved=None, fused=False, site_models=None, nonrev=None):
         import ctypes as C
         import numpy as np
         from iqtree2_b200 import workload as W
@@ -66,10 +66,16 @@ class RefRun:
                         ("newick", C.c_char_p), ("tipvec", C.c_void_p), ("rates", C.c_void_p),
                         ("props", C.c_void_p), ("pinvar", C.c_double), ("eval", C.c_void_p), ("evec", C.c_void_p),
                         ("inv_evec", C.c_void_p), ("mixw", C.c_void_p), ("freqs", C.c_void_p)]
-        names = ["T%d" % i for i in range(tree.ntaxa)]
+        names = ["T%d" % i for i in range(aln.ntaxa)]
         old = tree.names
         tree.names = names
-        newick = tree.to_newick(0, digits=17).encode()
+        if nonrev is not None and nonrev[0] == 1:
+            # rooted: `tree` carries the root as its LAST leaf (id ntaxa of the alignment); the reference reads a newick
+            # whose top node has two children and adds that leaf itself (tree/mtree.cpp:739-751)
+            tree.names = names + ["__root__"]
+            newick = tree.to_newick_rooted(tree.ntaxa - 1, digits=17).encode()
+        else:
+            newick = tree.to_newick(0, digits=17).encode()
         tree.names = old
         f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
         scale = 1.0 - p_invar
@@ -87,6 +93,11 @@ class RefRun:
         if site_models is not None:  # (eval [nptn][n], evec [nptn][n][n], inv_evec [nptn][n][n]): ModelSet / PMSF
             sm = [np.ascontiguousarray(a, dtype=np.float64) for a in site_models]
             self.lib.ref_set_next_site_models(C.c_int64(aln.nptn), aln.nstates, *[C.c_void_p(a.ctypes.data) for a in sm])
+        if nonrev is not None:  # (mode, Q, ceval, cevec, cinv_evec): mode 1 rooted + non-reversible model, 2 kernel_nonrev
+            cx = [np.ascontiguousarray(a, dtype=np.complex128) for a in nonrev[2:5]]
+            q = f64(nonrev[1])
+            self.lib.ref_set_next_nonrev(int(nonrev[0]), aln.nstates, model.nmix, C.c_void_p(q.ctypes.data),
+                                         *[C.c_void_p(a.ctypes.data) for a in cx])
         if fused:  # model_factory->fused_mix_rate: category c = mixture class c at rate category c
             self.lib.ref_set_next_fused(1)
         self.lib.ref_create.restype = C.c_void_p
@@ -94,7 +105,7 @@ class RefRun:
         self.nptn, self.ncm, self.n = aln.nptn, (len(rates) if fused else len(rates) * model.nmix), aln.nstates
         self.tree = tree
         for fn in ("ref_lnl_at_leaf", "ref_lnl_again", "ref_from_buffer", "ref_optimize_current_branch",
-                   "ref_optimize_all_branches", "ref_compute_likelihood", "ref_branch_length"):
+                   "ref_optimize_all_branches", "ref_compute_likelihood", "ref_branch_length", "ref_lnl_at_branch"):
             getattr(self.lib, fn).restype = C.c_double
         self.safe_numeric = bool(self.lib.ref_safe_numeric(self.h))
         self.vector_size = self.lib.ref_vector_size(self.h)
@@ -111,6 +122,11 @@ class RefRun:
 
     def lnl_at_leaf(self, taxon):
         return self.lib.ref_lnl_at_leaf(self.h, taxon)
+
+    def lnl_at_branch(self, leaves, from_taxon=0):
+        """lnL at the internal branch whose far side (seen from leaf ``from_taxon``) has exactly ``leaves``."""
+        arr = self.np.ascontiguousarray(sorted(leaves), dtype=self.np.int32)
+        return self.lib.ref_lnl_at_branch(self.h, self.C.c_void_p(arr.ctypes.data), len(arr), from_taxon)
 
     def derv(self, again=False):
         C = self.C

@@ -54,6 +54,11 @@ typedef struct orc_ctx {
      * tip_partial_lh of site models (tree/phylotreesse.cpp:257-340) */
     int site;
     double *s_eval, *s_evec, *s_inv, *s_tip;
+    /* non-reversible kernel family (nonrev_oracle.inc): Q[nmix][n][n], complex eigen-system (re, im interleaved),
+     * state frequencies, tip indicator vectors; the ends recorded by orc_build_theta */
+    int nonrev, rooted;
+    double *nr_Q, *nr_ev, *nr_V, *nr_Vi, *nr_freq, *nr_tipvec;
+    b200lk_end nr_dad, nr_node;
 } orc_ctx;
 
 /* ------------------------------------------------------------------ helpers */
@@ -295,7 +300,9 @@ int orc_destroy(orc_ctx *c) {
     free(c->partial); free(c->scale); free(c->states); free(c->ptn_freq); free(c->ptn_invar);
     free(c->eval); free(c->evec); free(c->inv_evec); free(c->rates); free(c->props); free(c->mixw);
     free(c->tip_partial_lh); free(c->theta_all); free(c->buffer_scale_all); free(c->pattern_lh);
-    free(c->pattern_lh_cat); free(c->s_eval); free(c->s_evec); free(c->s_inv); free(c->s_tip); free(c);
+    free(c->pattern_lh_cat); free(c->s_eval); free(c->s_evec); free(c->s_inv); free(c->s_tip);
+    free(c->nr_Q); free(c->nr_ev); free(c->nr_V); free(c->nr_Vi); free(c->nr_freq); free(c->nr_tipvec);
+    free(c);
     return B200LK_OK;
 }
 
@@ -331,6 +338,7 @@ int orc_set_ptn_invar(orc_ctx *c, const double *ptn_invar) {
 
 int orc_set_model(orc_ctx *c, const double *eval, const double *evec, const double *inv_evec,
                   const double *rates, const double *props, const double *mixw, const double *tip_partial_lh) {
+    if (c->d.site_specific != B200LK_MODEL_REV) return B200LK_ERR_STATE;
     int n = c->d.nstates, nmix = c->d.nmix;
     memcpy(c->eval, eval, sizeof(double) * nmix * n);
     memcpy(c->evec, evec, sizeof(double) * nmix * n * n);
@@ -390,7 +398,7 @@ int orc_set_site_models(orc_ctx *c, const double *eval, const double *evec, cons
                         const double *props, const double *tipvec) {
     const int n = c->d.nstates;
     const int64_t nptn = c->d.nptn;
-    if (!c->d.site_specific || c->d.nmix != 1 || c->d.n_unobserved != 0) return B200LK_ERR_ARG;
+    if (c->d.site_specific != B200LK_MODEL_SITE || c->d.nmix != 1 || c->d.n_unobserved != 0) return B200LK_ERR_ARG;
     free(c->s_eval); free(c->s_evec); free(c->s_inv); free(c->s_tip);
     c->s_eval = malloc(sizeof(double) * nptn * n);
     c->s_evec = malloc(sizeof(double) * nptn * n * n);
@@ -683,10 +691,14 @@ static void update_node(orc_ctx *c, const b200lk_node *nd, const b200lk_child *c
 
 /* computeTraversalInfo(compute_partial_lh = true), tree/phylokernelnew.h:1150-1281:
  * tables for every entry, then every entry over every pattern range. */
+#include "nonrev_oracle.inc"
+
 int orc_update_partials(orc_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
                         int32_t nchildren) {
     const int n = c->d.nstates, block = c->block;
     if (nnodes <= 0) return B200LK_OK;
+    if (c->d.site_specific == B200LK_MODEL_NONREV)
+        return c->nonrev ? nr_update_partials(c, nodes, nnodes, children, nchildren) : B200LK_ERR_STATE;
     if (c->site) { /* no P-factor tables: every pattern has its own eigen-system */
         for (int i = 0; i < nnodes; i++) {
             if (nodes[i].nchild != 2) return B200LK_ERR_UNSUPPORTED;
@@ -776,6 +788,8 @@ static int check_ends(const orc_ctx *c, b200lk_end dad, b200lk_end node) {
  * `node` = slot of dad_branch->partial_lh (subtree on the node side);
  * `dad`  = the leaf dad (tip-internal, :2740-2941) or the slot of node_branch->partial_lh (:2942-3074). */
 int orc_branch_lnl(orc_ctx *c, b200lk_end dad, b200lk_end node, double length, double *lnl) {
+    if (c->d.site_specific == B200LK_MODEL_NONREV)
+        return c->nonrev ? nr_branch_lnl(c, dad, node, length, lnl) : B200LK_ERR_STATE;
     int rc = check_ends(c, dad, node);
     if (rc) return rc;
     const int n = c->d.nstates, ncm = c->ncat_mix, block = c->block, safe = c->d.safe_numeric;
@@ -895,6 +909,14 @@ int orc_branch_lnl(orc_ctx *c, b200lk_end dad, b200lk_end node, double length, d
 
 /* computeLikelihoodBufferGenericSIMD, tree/phylokernelnew.h:2050-2231 */
 int orc_build_theta(orc_ctx *c, b200lk_end dad, b200lk_end node) {
+    if (c->d.site_specific == B200LK_MODEL_NONREV) { /* no theta in this family: the ends are recorded */
+        int rn = c->nonrev ? nr_check_ends(c, dad, node) : B200LK_ERR_STATE;
+        if (rn) return rn;
+        c->nr_dad = dad;
+        c->nr_node = node;
+        c->theta_computed = 1;
+        return B200LK_OK;
+    }
     int rc = check_ends(c, dad, node);
     if (rc) return rc;
     const int n = c->d.nstates, ncm = c->ncat_mix, block = c->block, safe = c->d.safe_numeric;
@@ -956,6 +978,7 @@ int orc_build_theta(orc_ctx *c, b200lk_end dad, b200lk_end node) {
 /* computeLikelihoodDervGenericSIMD, tree/phylokernelnew.h:2235-2633 (joint branch-length model) */
 int orc_derv(orc_ctx *c, double length, double *df, double *ddf) {
     if (!c->theta_computed) return B200LK_ERR_STATE;
+    if (c->nonrev) return nr_derv(c, length, df, ddf);
     const int n = c->d.nstates, block = c->block;
     const int64_t nptn = c->d.nptn, ntot = c->ntot;
     double val0[block], val1[block], val2[block];
@@ -1030,6 +1053,7 @@ int orc_derv(orc_ctx *c, double length, double *df, double *ddf) {
 /* computeLikelihoodFromBufferGenericSIMD, tree/phylokernelnew.h:3196-3392 */
 int orc_lnl_from_buffer(orc_ctx *c, double length, double *lnl) {
     if (!c->theta_computed) return B200LK_ERR_STATE;
+    if (c->nonrev) return nr_branch_lnl(c, c->nr_dad, c->nr_node, length, lnl); /* tree/phylokernelfma.cpp:99 */
     const int block = c->block;
     const int64_t nptn = c->d.nptn, ntot = c->ntot;
     double val0[block];

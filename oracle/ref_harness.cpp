@@ -22,6 +22,7 @@
 #include <vector>
 #include <algorithm>
 #include <cstring>
+#include <complex>
 
 // the harness reads kernel-private buffers (_pattern_lh, partial_lh, scale_num, current_it): open the
 // access specifiers for THIS translation unit only (object layout is unaffected)
@@ -82,6 +83,14 @@ ModelFactory::ModelFactory() : CheckpointFactory() {
 }
 ModelFactory::~ModelFactory() {}
 void ModelFactory::setCheckpoint(Checkpoint *checkpoint) { CheckpointFactory::setCheckpoint(checkpoint); }
+// model/modelfactory.cpp:1517-1556 with store_trans_matrix off (the default): straight to the model
+void ModelFactory::computeTransMatrix(double time, double *trans_matrix, int mixture, int selected_row) {
+    model->computeTransMatrix(time, trans_matrix, mixture, selected_row);
+}
+void ModelFactory::computeTransDerv(double time, double *trans_matrix, double *trans_derv1, double *trans_derv2,
+                                    int mixture) {
+    model->computeTransDerv(time, trans_matrix, trans_derv1, trans_derv2, mixture);
+}
 
 // ---- caller-supplied model and rates behind the reference's virtual interface -----------------------------
 class HarnessModel : public ModelSubst {
@@ -97,11 +106,47 @@ public:
         memcpy(p, src, sizeof(double) * count);
         return (double *)p;
     }
-    HarnessModel(int n, int nmix_) : ModelSubst(n), nmix(nmix_), eval(NULL), evec(NULL), inv_evec(NULL), ncodes(0), site(false) {}
+    HarnessModel(int n, int nmix_) : ModelSubst(n), nmix(nmix_), eval(NULL), evec(NULL), inv_evec(NULL), ncodes(0), site(false), nonrev(false) {}
     virtual ~HarnessModel() { free(eval); free(evec); free(inv_evec); }
     bool site;  // ModelSet-like: per-pattern eigen-systems in the layout of ModelSet::decomposeRateMatrix
     virtual bool isSiteSpecificModel() { return site; }
-    virtual bool isReversible() { return true; }
+    // Non-reversible kernel family: what ModelMarkov hands the kernels through computeTransMatrix / computeTransDerv
+    // (model/modelmarkov.cpp:460-488, 729-745; that translation unit needs Eigen3 and cannot be built here): the
+    // caller supplies Q and its complex eigen-system, P(t) = Re(V exp(ev t) V^-1), dP = Q P, d2P = Q Q P.
+    // `nonrev` makes isReversible() false; with params->kernel_nonrev a reversible model takes the same route.
+    bool nonrev;
+    std::vector<double> Q;                       // [nmix][n][n]
+    std::vector<std::complex<double>> cev, cV, cVi;  // [nmix][n], [nmix][n][n] x2
+    virtual bool isReversible() { return !nonrev; }
+    virtual void computeTransMatrix(double time, double *trans_matrix, int mixture = 0, int selected_row = -1) {
+        const int n = num_states;
+        const std::complex<double> *ev = &cev[(size_t)mixture * n], *V = &cV[(size_t)mixture * n * n];
+        const std::complex<double> *Vi = &cVi[(size_t)mixture * n * n];
+        std::vector<std::complex<double>> e(n);
+        for (int k = 0; k < n; k++) e[k] = std::exp(ev[k] * time);
+        for (int i = 0; i < n; i++)
+            for (int j = 0; j < n; j++) {
+                std::complex<double> s(0.0, 0.0);
+                for (int k = 0; k < n; k++) s += V[(size_t)i * n + k] * e[k] * Vi[(size_t)k * n + j];
+                trans_matrix[(size_t)i * n + j] = s.real();
+            }
+    }
+    virtual void computeTransDerv(double time, double *trans_matrix, double *trans_derv1, double *trans_derv2,
+                                  int mixture = 0) {
+        const int n = num_states;
+        const double *q = &Q[(size_t)mixture * n * n];
+        computeTransMatrix(time, trans_matrix, mixture);
+        for (int pass = 0; pass < 2; pass++) {
+            const double *src = pass ? trans_derv1 : trans_matrix;
+            double *dst = pass ? trans_derv2 : trans_derv1;
+            for (int i = 0; i < n; i++)
+                for (int j = 0; j < n; j++) {
+                    double v = 0.0;
+                    for (int k = 0; k < n; k++) v += q[(size_t)i * n + k] * src[(size_t)k * n + j];
+                    dst[(size_t)i * n + j] = v;
+                }
+        }
+    }
     virtual bool isMixture() { return nmix > 1; }
     virtual int getNMixtures() { return nmix; }
     virtual double getMixtureWeight(int cat) { return mixw[cat]; }
@@ -220,6 +265,25 @@ static double *interleave_models(const std::vector<double> &src, size_t nptn, si
 static int next_fused = 0;
 void ref_set_next_fused(int fused) { next_fused = fused; }
 
+// Non-reversible kernel family for the NEXT ref_create.  mode 1: the model reports isReversible() == false and the
+// newick is read as a ROOTED tree (tree/mtree.cpp:739-751 adds the root leaf, tree/phylotree.cpp:5710 sets the branch
+// directions); mode 2: params->kernel_nonrev on an unrooted tree with a reversible model (what -asr and the marginal
+// ancestral state code switch on, tree/phylotreesse.cpp:1441-1446).  Q [nmix][n][n]; ceval [nmix][n], cevec / cinv
+// [nmix][n][n] as (re, im) pairs.
+static int next_nonrev_mode = 0;
+static std::vector<double> next_Q;
+static std::vector<std::complex<double>> next_cev, next_cV, next_cVi;
+void ref_set_next_nonrev(int mode, int n, int nmix, const double *Q, const double *ceval, const double *cevec,
+                         const double *cinv) {
+    next_nonrev_mode = mode;
+    next_Q.assign(Q, Q + (size_t)nmix * n * n);
+    const std::complex<double> *e = (const std::complex<double> *)ceval, *v = (const std::complex<double> *)cevec;
+    const std::complex<double> *w = (const std::complex<double> *)cinv;
+    next_cev.assign(e, e + (size_t)nmix * n);
+    next_cV.assign(v, v + (size_t)nmix * n * n);
+    next_cVi.assign(w, w + (size_t)nmix * n * n);
+}
+
 #include <execinfo.h>
 #include <signal.h>
 #include <unistd.h>
@@ -287,6 +351,16 @@ void *ref_create(const ref_problem *pb) {
     m->freqs.assign(pb->freqs, pb->freqs + (size_t)pb->nmix * n);
     m->ncodes = pb->n_state_codes;
     m->tipvec.assign(pb->tipvec, pb->tipvec + (size_t)pb->n_state_codes * n);
+    const int nonrev_mode = next_nonrev_mode;
+    next_nonrev_mode = 0;
+    params.kernel_nonrev = nonrev_mode == 2;
+    if (nonrev_mode) {
+        m->nonrev = nonrev_mode == 1;
+        m->Q.swap(next_Q);
+        m->cev.swap(next_cev);
+        m->cV.swap(next_cV);
+        m->cVi.swap(next_cVi);
+    }
     HarnessRate *r = new HarnessRate();
     r->rates.assign(pb->rates, pb->rates + pb->ncat);
     r->props.assign(pb->props, pb->props + pb->ncat);
@@ -315,7 +389,7 @@ void *ref_create(const ref_problem *pb) {
     tree->params = &params;
     std::stringstream ss;
     ss << pb->newick;
-    bool rooted = false;
+    bool rooted = nonrev_mode == 1;
     tree->readTree(ss, rooted);
     tree->setAlignment(aln);
     tree->setModelFactory(f);
@@ -476,6 +550,34 @@ int ref_fetch_branch(void *hv, const int32_t *leaves, int nleaves, int from_taxo
     }
     (void)n;
     return 0;
+}
+
+// lnL at the INTERNAL branch whose far side (seen from leaf `from_taxon`) carries exactly the given leaf set, all
+// partials stale: dad = the near end, dad_branch = (dad -> far end).  The kernels choose their own orientation
+// (tree/phylokernelnonrev.h:1060-1067 for the non-reversible family).
+static PhyloNode *owner_of(PhyloTree *tree, PhyloNeighbor *nb) {
+    PhyloNode *far = (PhyloNode *)nb->node;
+    for (size_t i = 0; i < far->neighbors.size(); i++) {
+        PhyloNode *cand = (PhyloNode *)far->neighbors[i]->node;
+        if (cand->findNeighbor(far) == nb) return cand;
+    }
+    return NULL;
+}
+double ref_lnl_at_branch(void *hv, const int32_t *leaves, int nleaves, int from_taxon) {
+    RefHandle *h = (RefHandle *)hv;
+    std::vector<int> want(leaves, leaves + nleaves);
+    PhyloNode *start = find_leaf(h->tree, from_taxon);
+    if (!start) return 1.0;
+    PhyloNeighbor *nb = find_branch(start, NULL, want);
+    if (!nb) return 2.0;
+    PhyloNode *dad = owner_of(h->tree, nb);
+    if (!dad) return 3.0;
+    h->tree->clearAllPartialLH();
+    h->cur_dad_branch = nb;
+    h->cur_dad = dad;
+    h->tree->current_it = nb;
+    h->tree->current_it_back = (PhyloNeighbor *)nb->node->findNeighbor(dad);
+    return h->tree->computeLikelihoodBranch(nb, dad);
 }
 
 double ref_branch_length(void *hv, const int32_t *leaves, int nleaves, int from_taxon) {

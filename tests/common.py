@@ -96,3 +96,82 @@ def site_engine(aln, models, rates, props, *, nslots, safe_numeric=False, lib_pa
     eng.set_site_models(models[0], models[1], models[2], rates, np.asarray(props) * (1.0 - p_invar),
                         W.state_indicators(aln.nstates))
     return eng
+
+
+# ---- non-reversible kernel family (tree/phylokernelnonrev.h) ---------------------------------------------------------
+class _RefModelShim:
+    """What oracle.RefRun reads from a model object, for a NonrevModel (the eigen-system fields are placeholders: the
+    non-reversible kernels never read them)."""
+
+    def __init__(self, nm):
+        n, k = nm.nstates, nm.nmix
+        self.nmix = k
+        self.eval = np.zeros((k, n))
+        self.evec = np.tile(np.eye(n), (k, 1, 1))
+        self.inv_evec = np.tile(np.eye(n), (k, 1, 1))
+        self.mixw, self.freqs = nm.mixw, nm.freqs
+
+
+def nonrev_engine(aln, nm, rates, props, *, nslots, rooted, safe_numeric=False, lib_path=None, prefix="b200lk_",
+                  p_invar=0.0, ptn_invar=None):
+    """A context of the non-reversible kernel family with the model loaded."""
+    from iqtree2_b200 import capi
+    eng = capi.Engine(ntaxa=aln.ntaxa, nstates=aln.nstates, ncat=len(rates), nmix=nm.nmix, nptn=aln.nptn, nslots=nslots,
+                      n_state_codes=aln.state_unknown + 1, safe_numeric=safe_numeric, nonrev=True,
+                      lib_path=lib_path or capi.LIB_PATH, prefix=prefix)
+    eng.upload_tips(aln.states, aln.ptn_freq)
+    eng.set_ptn_invar(np.zeros(aln.nptn) if ptn_invar is None else ptn_invar)
+    eng.set_model_nonrev(nm.Q, nm.ceval, nm.cevec, nm.cinv_evec, nm.freqs, W.state_indicators(aln.nstates), rates,
+                         np.asarray(props) * (1.0 - p_invar), nm.mixw, rooted)
+    return eng
+
+
+def nonrev_ends(tree, a, b, root_leaf):
+    """The two ends of branch (a, b) in the order the non-reversible kernels use after their swap
+    (tree/phylokernelnonrev.h:1060-1067): -> (dad, node); dad is the leaf end if there is one (the root leaf only when
+    it is ``a``, the caller's dad), otherwise the end farther from the root.  ``root_leaf`` None: unrooted tree
+    (params->kernel_nonrev), only the leaf rule applies."""
+    dad, node = a, b
+    if tree.is_leaf(node):
+        dad, node = node, dad
+    elif root_leaf is not None and not tree.is_leaf(dad):
+        parent = tree.parents_from(root_leaf)
+        if parent[node] == dad:      # dad_branch points AWAY from the root: swap
+            dad, node = node, dad
+    return dad, node
+
+
+def nonrev_eval(eng, tree, a, b, root_leaf, want_derv=True):
+    """All partials stale -> both traversals toward branch (a, b), lnL there, df/ddf, lnL again through the recorded
+    ends.  Works on either backend (CUDA engine / oracle)."""
+    from iqtree2_b200.capi import INTERNAL, LEAF, ROOT
+    dad, node = nonrev_ends(tree, a, b, root_leaf)
+    slot_of, entries = {}, []
+    trav = (lambda v, u: W.traversal_rooted(tree, v, u, root_leaf, slot_of)) if root_leaf is not None else \
+        (lambda v, u: W.traversal(tree, v, u, slot_of))
+    # hand out slots up front so that both sides share one numbering
+    for v, u in ((node, dad), (dad, node)):
+        if not tree.is_leaf(v):
+            for x, y, _, _ in W.traversal(tree, v, u):
+                slot_of.setdefault((x, y), len(slot_of))
+    for v, u in ((node, dad), (dad, node)):
+        if not tree.is_leaf(v):
+            entries += trav(v, u)
+    eng.update_partials(entries)
+    L = tree.get_length(a, b)
+    node_end = (INTERNAL, slot_of[(node, dad)])
+    if tree.is_leaf(dad):
+        dad_end = (ROOT, 0) if dad == root_leaf else (LEAF, dad)
+    else:
+        dad_end = (INTERNAL, slot_of[(dad, node)])
+    out = {"entries": entries, "ends": (dad_end, node_end)}
+    out["lnl"] = eng.branch_lnl(dad_end, node_end, L)
+    out["pattern_lh"] = eng.fetch_pattern_lh()
+    out["pattern_lh_cat"] = eng.fetch_pattern_lh_cat()
+    out["scale"] = {s: eng.fetch_scale_num(s) for (_, _, s, _) in entries}
+    out["partials"] = {s: eng.fetch_partial(s) for (_, _, s, _) in entries}
+    if want_derv and dad != root_leaf:
+        eng.build_theta(dad_end, node_end)
+        out["df"], out["ddf"] = eng.derv(L)
+        out["lnl_buf"] = eng.lnl_from_buffer(L * 1.3)
+    return out
