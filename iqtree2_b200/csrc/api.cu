@@ -27,6 +27,7 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
                  nchildren, c->nodes_cap, c->children_cap);
         return B200LK_ERR_ARG;
     }
+    if (c->nonrev) return enqueue_update_nonrev(c, nodes, nnodes, children, nchildren);
     const int n = c->d.nstates, block = c->block, nslots = c->d.nslots;
     // next slice of the pinned staging ring; wait only if its previous copy is still in flight
     const int ring = c->stage_idx++ % B200_STAGE_RING;
@@ -195,6 +196,7 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
 }
 
 int check_ends(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
+    if (c->nonrev) return nr_check_ends(c, dad, node);
     if (node.kind != B200LK_CHILD_INTERNAL || node.id < 0 || node.id >= c->d.nslots) return B200LK_ERR_ARG;
     if (dad.kind == B200LK_CHILD_LEAF) return (dad.id >= 0 && dad.id < c->d.ntaxa) ? B200LK_OK : B200LK_ERR_ARG;
     if (dad.kind != B200LK_CHILD_INTERNAL || dad.id < 0 || dad.id >= c->d.nslots || dad.id == node.id)
@@ -265,7 +267,9 @@ extern "C" int b200lk_build_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node
     if (rc) return rc;
     if (check_ends(c, dad, node)) return B200LK_ERR_ARG;
     CUDA_TRY(c, cudaSetDevice(c->device));
-    if (c->ntot > 0) {
+    if (c->nonrev) {
+        nr_record_ends(c, dad, node);
+    } else if (c->ntot > 0) {
         rc = launch_theta(c, dad, node);
         if (rc) return rc;
     }
@@ -302,6 +306,7 @@ extern "C" int b200lk_optimize_branch(b200lk_ctx *c, b200lk_end dad, b200lk_end 
     if (rc) return rc;
     if (!nr || !optx || check_ends(c, dad, node) || !(nr->min_len <= nr->max_len) || nr->max_steps < 1)
         return B200LK_ERR_ARG;
+    if (c->nonrev) return B200LK_ERR_UNSUPPORTED;  // no theta buffer: the host iteration drives b200lk_derv
     CUDA_TRY(c, cudaSetDevice(c->device));
     if (c->d.nptn == 0) {
         *optx = nr->guess;

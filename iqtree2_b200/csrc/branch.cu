@@ -650,6 +650,7 @@ static int launch_val(b200lk_ctx *c, double length, int want_tip) {
 }
 
 int launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length) {
+    if (c->nonrev) return nr_launch_branch_lnl(c, dad, node, length);
     int rc = launch_val(c, length, dad.kind == B200LK_CHILD_LEAF);
     if (rc) return rc;
     BranchArgs a;
@@ -677,6 +678,7 @@ int launch_repair(b200lk_ctx *c) {
 }
 
 int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
+    if (c->nonrev) return nr_record_ends(c, dad, node);
     BranchArgs a;
     fill_args(c, a, dad, node);
     fill_common(c, a);
@@ -689,6 +691,7 @@ int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
 }
 
 int launch_derv(b200lk_ctx *c, double length) {
+    if (c->nonrev) return nr_launch_derv(c, length);
     int rc = launch_val(c, length, 0);
     if (rc) return rc;
     BranchArgs a;
@@ -706,6 +709,7 @@ int launch_derv(b200lk_ctx *c, double length) {
 }
 
 int launch_from_buffer(b200lk_ctx *c, double length) {
+    if (c->nonrev) return nr_launch_from_buffer(c, length);
     int rc = launch_val(c, length, 0);
     if (rc) return rc;
     BranchArgs a;

@@ -128,6 +128,11 @@ struct b200lk_ctx {
     size_t pmax_bytes;
     bool site;  // dims.site_specific: per-pattern eigen-systems (site.cu); no P-factor tables, pattern-major layout
     double *s_eval, *s_evec, *s_inv, *s_tip, *s_tipvec;  // [nptn][n], [nptn][n][n] x2, [ntaxa][nptn][n], [codes][n]
+    // non-reversible kernel family (nonrev.cu): dims.site_specific == B200LK_MODEL_NONREV
+    bool nonrev, rooted;
+    double *nr_Q, *nr_ev, *nr_V, *nr_Vi, *nr_freq, *nr_tipvec;  // Q, complex eigen-system, frequencies, tip vectors
+    double *nr_T;                                               // branch tables T0/T1/T2 + tip-dad tables
+    b200lk_end nr_dad, nr_node;                                 // ends recorded by b200lk_build_theta
     double *eig_in, *eig_host;  // staging of b200lk_set_model_rates (eigen.cu): device inputs, pinned host mirror
     double *red_partial;   // [3][red_blocks] block partial sums
     int red_blocks;
@@ -187,3 +192,10 @@ int launch_tt_tables(b200lk_ctx *c, int nnodes);
 int launch_dense20_tt(b200lk_ctx *c, int node_base, int nnodes);
 int launch_denseN(b200lk_ctx *c, int node_base, int nnodes);
 int launch_site_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels);
+// nonrev.cu
+int enqueue_update_nonrev(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children, int32_t nchildren);
+int nr_check_ends(b200lk_ctx *c, b200lk_end dad, b200lk_end node);
+int nr_launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length);
+int nr_record_ends(b200lk_ctx *c, b200lk_end dad, b200lk_end node);
+int nr_launch_derv(b200lk_ctx *c, double length);
+int nr_launch_from_buffer(b200lk_ctx *c, double length);

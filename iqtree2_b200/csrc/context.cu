@@ -129,7 +129,22 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
         c->frag_cat = c->dense20 ? B200_FRAG20 : c->dense_nt * 2 * c->dense_nt * 32;
     }
     c->tile = (dims->nstates == 4 && c->ncat_mix <= 4 && !c->force_level_batched) ? 32 : 1;
-    c->site = dims->site_specific != 0;
+    c->site = dims->site_specific == B200LK_MODEL_SITE;
+    c->nonrev = dims->site_specific == B200LK_MODEL_NONREV;
+    if (dims->site_specific < 0 || dims->site_specific > B200LK_MODEL_NONREV) {
+        delete c;
+        return B200LK_ERR_ARG;
+    }
+    if (c->nonrev) {  // non-reversible family: own kernels (nonrev.cu) on the pattern-major layout, no +ASC
+        if (dims->n_unobserved != 0) {
+            delete c;
+            return B200LK_ERR_UNSUPPORTED;
+        }
+        c->tile = 1;
+        c->dense20 = false;
+        c->dense_nt = 0;
+        c->frag_cat = 0;
+    }
     if (c->site) {  // site-specific models: own kernels (site.cu) on the pattern-major layout
         if (dims->nmix != 1 || dims->n_unobserved != 0 || dims->nstates > 32 || dims->fused_mix_rate) {
             delete c;
@@ -175,6 +190,8 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (c->s_inv) cudaFree(c->s_inv);
     if (c->s_tip) cudaFree(c->s_tip);
     if (c->s_tipvec) cudaFree(c->s_tipvec);
+    for (double *p : {c->nr_Q, c->nr_ev, c->nr_V, c->nr_Vi, c->nr_freq, c->nr_tipvec, c->nr_T})
+        if (p) cudaFree(p);
     if (c->eig_in) cudaFree(c->eig_in);
     if (c->eig_host) cudaFreeHost(c->eig_host);
     free(c->h_evec);
@@ -238,7 +255,7 @@ extern "C" int b200lk_set_model(b200lk_ctx *c, const double *eval, const double 
                                 const double *rates, const double *props, const double *mixw,
                                 const double *tip_partial_lh) {
     if (!c || !eval || !evec || !inv_evec || !rates || !props || !mixw || !tip_partial_lh) return B200LK_ERR_ARG;
-    if (c->site) return B200LK_ERR_STATE;  // a site-specific context takes b200lk_set_site_models
+    if (c->site || c->nonrev) return B200LK_ERR_STATE;  // these contexts take b200lk_set_site_models / _set_model_nonrev
     CUDA_TRY(c, cudaSetDevice(c->device));
     const int n = c->d.nstates, nmix = c->d.nmix;
     cudaStream_t s = c->stream;

@@ -196,7 +196,7 @@ extern "C" int b200lk_set_model_rates(b200lk_ctx *c, const double *exch, const d
     CUDA_TRY(c, cudaSetDevice(c->device));
     const int n = c->d.nstates, nmix = c->d.nmix, codes = c->d.n_state_codes, ne = n * (n - 1) / 2;
     if (n > 64) return B200LK_ERR_UNSUPPORTED;
-    if (c->site) return B200LK_ERR_STATE;
+    if (c->site || c->nonrev) return B200LK_ERR_STATE;
     cudaStream_t s = c->stream;
     const size_t in_doubles = (size_t)nmix * (ne + n + 1) + (size_t)codes * n;
     if (!c->eig_in) {

@@ -84,3 +84,130 @@ def test_oracle_vs_reference_rooted(nstates, ncat, nmix, safe):
     assert max(lnls) - min(lnls) <= 1e-8 * abs(lnls[0])   # the likelihood does not depend on the branch it is taken at
     ref.close()
     eng.close()
+
+
+# NOTE: with an ODD state count (e.g. 5) the reference's generic non-reversible kernel crashes (SIGSEGV in
+# oracle/_ref, Vec4d) -- not a configuration the reference supports; even state counts are pinned above.
+
+
+def unrooted_problem(ntaxa, nsite, nstates=4, ncat=4, seed=5):
+    from tests.common import make_problem
+    tree, model, rates, props, aln = make_problem(ntaxa, nsite, nstates=nstates, ncat=ncat, seed=seed, gaps=0.05)
+    return tree, model, W.nonrev_from_reversible(model), rates, props, aln
+
+
+@needs_ref
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates,ncat", [(4, 4), (20, 2)])
+def test_oracle_vs_reference_unrooted_kernel_nonrev(nstates, ncat, safe):
+    """params->kernel_nonrev on an unrooted tree with a reversible model (what -asr and the marginal-state code use):
+    the non-reversible kernels weight the branch by the state frequencies."""
+    ntaxa = 8
+    tree, model, nm, rates, props, aln = unrooted_problem(ntaxa, 250, nstates, ncat)
+    ref = oracle.RefRun(tree, aln, model, rates, props, safe=safe, nonrev=(2, nm.Q, nm.ceval, nm.cevec, nm.cinv_evec))
+    eng = oracle_nonrev(aln, nm, rates, props, nslots=4 * ntaxa, rooted=False, safe_numeric=safe)
+    rev = oracle.oracle_engine(aln, model, rates, props, nslots=ntaxa, safe_numeric=safe)
+    from tests.common import full_eval
+    want_rev = full_eval(rev, tree, 0)["lnl"]
+    for a, b in [(0, tree.adj[0][0]), (3, tree.adj[3][0])] + internal_branches(tree)[:3]:
+        if tree.is_leaf(a):
+            want = ref.lnl_at_leaf(a)
+        else:
+            want = ref.lnl_at_branch(leaf_set(tree, b, a), from_taxon=leaf_set(tree, a, b)[0])
+        got = nonrev_eval(eng, tree, a, b, None)
+        assert rel(got["lnl"], want) <= 1e-10, (a, b, got["lnl"], want)
+        assert rel(got["pattern_lh"], ref.pattern_lh()) <= 1e-10
+        df, ddf = ref.derv()
+        assert rel(got["df"], df) <= 1e-9 and rel(got["ddf"], ddf) <= 1e-9
+        assert rel(got["lnl"], want_rev) <= 1e-9   # a reversible model: the same likelihood as the reversible family
+    ref.close()
+    eng.close()
+
+
+# ---- the CUDA path against the pinned restatement ---------------------------------------------------------------------
+def gpu_nonrev(aln, nm, rates, props, **kw):
+    return nonrev_engine(aln, nm, rates, props, **kw)
+
+
+def assert_nonrev_parity(g, o, tol=1e-9):
+    assert rel(g["lnl"], o["lnl"]) <= tol, (g["lnl"], o["lnl"])
+    assert rel(g["pattern_lh"], o["pattern_lh"]) <= tol
+    w = o["pattern_lh_cat"]
+    assert float(np.max(np.abs(g["pattern_lh_cat"] - w) / np.maximum(np.abs(w).max(axis=1, keepdims=True), 1e-300))) <= tol
+    for s in o["scale"]:
+        assert np.array_equal(g["scale"][s], o["scale"][s]), "scale counts of slot %d differ" % s
+        assert rel(g["partials"][s], o["partials"][s]) <= tol
+    if "df" in o:
+        assert rel(g["df"], o["df"]) <= tol and rel(g["ddf"], o["ddf"]) <= tol, (g["df"], o["df"], g["ddf"], o["ddf"])
+        assert rel(g["lnl_buf"], o["lnl_buf"]) <= tol
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates,ncat,nmix,ntaxa,nsite", [(4, 4, 1, 12, 700), (4, 1, 1, 6, 301), (20, 4, 1, 9, 260),
+                                                           (20, 2, 3, 6, 120), (5, 3, 2, 9, 257), (61, 2, 1, 5, 40)])
+def test_gpu_rooted_matches_oracle(oracle_lib, nstates, ncat, nmix, ntaxa, nsite, safe):
+    tree, nm, rates, props, aln = rooted_problem(ntaxa, nsite, nstates, ncat, nmix, seed=31)
+    root = ntaxa
+    kw = dict(nslots=4 * ntaxa, rooted=True, safe_numeric=safe)
+    g, o = gpu_nonrev(aln, nm, rates, props, **kw), oracle_nonrev(aln, nm, rates, props, **kw)
+    cases = [(root, tree.adj[root][0]), (0, tree.adj[0][0]), (ntaxa - 1, tree.adj[ntaxa - 1][0])] + internal_branches(tree)
+    for a, b in cases:
+        assert_nonrev_parity(nonrev_eval(g, tree, a, b, root), nonrev_eval(o, tree, a, b, root))
+    g.close()
+    o.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("safe", [False, True])
+def test_gpu_unrooted_kernel_nonrev_matches_oracle(oracle_lib, safe):
+    for nstates, ncat in ((4, 4), (20, 3)):
+        tree, model, nm, rates, props, aln = unrooted_problem(10, 300, nstates, ncat)
+        kw = dict(nslots=40, rooted=False, safe_numeric=safe)
+        g, o = gpu_nonrev(aln, nm, rates, props, **kw), oracle_nonrev(aln, nm, rates, props, **kw)
+        for a, b in [(0, tree.adj[0][0])] + internal_branches(tree)[:4]:
+            assert_nonrev_parity(nonrev_eval(g, tree, a, b, None), nonrev_eval(o, tree, a, b, None))
+        g.close()
+        o.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("safe", [False, True])
+def test_gpu_rooted_deep_tree_scale_counts(oracle_lib, safe):
+    """Long branches on many taxa: the rescaling path runs, scale counts stay bit-exact."""
+    ntaxa = 250
+    tree, nm, rates, props, aln = rooted_problem(ntaxa, 300, 4, 4, 1, seed=9, mean_len=0.5)
+    kw = dict(nslots=4 * ntaxa, rooted=True, safe_numeric=safe)
+    g, o = gpu_nonrev(aln, nm, rates, props, **kw), oracle_nonrev(aln, nm, rates, props, **kw)
+    for a, b in [(ntaxa, tree.adj[ntaxa][0]), (0, tree.adj[0][0])]:
+        rg, ro = nonrev_eval(g, tree, a, b, ntaxa), nonrev_eval(o, tree, a, b, ntaxa)
+        assert max(int(s.max()) for s in ro["scale"].values()) >= 1
+        assert_nonrev_parity(rg, ro)
+    g.close()
+    o.close()
+
+
+@pytest.mark.gpu
+def test_gpu_rooted_multifurcation(oracle_lib):
+    names = list("ABCDEFGH") + ["__root__"]
+    t = W.Tree.from_newick("(__root__:0.0,A:0.1,B:0.2,(C:0.1,D:0.3,(E:0.2,F:0.1):0.05,G:0.3,H:0.02):0.15);", names)
+    nm = W.random_nonrev_model(4, 77)
+    rates, props = W.discrete_gamma(0.7)
+    aln = W.simulate_alignment(W.random_tree(8, 4), W.gtr_model(), rates, props, 333, 11, compress=True)
+    for safe in (False, True):
+        kw = dict(nslots=40, rooted=True, safe_numeric=safe)
+        g, o = gpu_nonrev(aln, nm, rates, props, **kw), oracle_nonrev(aln, nm, rates, props, **kw)
+        for a, b in [(8, t.adj[8][0]), (0, t.adj[0][0]), (2, t.adj[2][0])]:
+            assert_nonrev_parity(nonrev_eval(g, t, a, b, 8), nonrev_eval(o, t, a, b, 8))
+
+
+@pytest.mark.gpu
+def test_gpu_nonrev_refusals(oracle_lib):
+    from iqtree2_b200.capi import B200LKError, INTERNAL, ROOT
+    tree, nm, rates, props, aln = rooted_problem(6, 50, 4, 2, 1)
+    g = gpu_nonrev(aln, nm, rates, props, nslots=24, rooted=True)
+    r = nonrev_eval(g, tree, 6, tree.adj[6][0], 6, want_derv=False)
+    g.build_theta(*r["ends"])
+    with pytest.raises(B200LKError):
+        g.derv(0.1)   # the virtual root branch has no length to optimise
+    g.close()
