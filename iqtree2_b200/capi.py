@@ -203,6 +203,61 @@ class Engine:
         self.last_status = self._check(f(self.ctx, length, C.byref(out)))
         return out.value
 
+    # -- +ASC flavour, heterotachy ---------------------------------------------
+    def set_asc(self, holder):
+        """0 / False: Lewis (default with unobserved patterns); 1 / True: Holder's correction for missing data
+        (n_unobserved = nstates * nptn, state-major)."""
+        return self._check(self._f("set_asc")(self.ctx, C.c_int32(int(holder))))
+
+    def set_ptn_freq(self, ptn_freq):
+        a = np.ascontiguousarray(ptn_freq, dtype=np.float64)
+        assert a.size == self.dims.nptn
+        return self._check(self._f("set_ptn_freq")(self.ctx, _dp(a)))
+
+    def update_partials_mixlen(self, entries, child_len):
+        """Heterotachy: child_len [nchildren][ncat], row j = class lengths of the branch to child j of the packed list."""
+        nodes, nn, kids, nk = pack_traversal(entries)
+        a = np.ascontiguousarray(child_len, dtype=np.float64)
+        assert a.shape == (nk, self.dims.ncat)
+        f = self._f("update_partials_mixlen")
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.POINTER(C.c_double)]
+        return self._check(f(self.ctx, nodes, nn, kids, nk, _dp(a)))
+
+    def branch_lnl_mixlen(self, dad, node, lens):
+        a = np.ascontiguousarray(lens, dtype=np.float64)
+        assert a.size == self.dims.ncat
+        out = C.c_double()
+        f = self._f("branch_lnl_mixlen")
+        f.argtypes = [C.c_void_p, End, End, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        self.last_status = self._check(f(self.ctx, End(*dad), End(*node), _dp(a), C.byref(out)))
+        return out.value
+
+    def lnl_from_buffer_mixlen(self, lens):
+        a = np.ascontiguousarray(lens, dtype=np.float64)
+        out = C.c_double()
+        f = self._f("lnl_from_buffer_mixlen")
+        f.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        self.last_status = self._check(f(self.ctx, _dp(a), C.byref(out)))
+        return out.value
+
+    def derv_mixlen(self, lens):
+        """-> (df [ncat], ddf [ncat][ncat], lnL): computeLikelihoodDerv under isMixlen()."""
+        k = self.dims.ncat
+        a = np.ascontiguousarray(lens, dtype=np.float64)
+        df, ddf, lnl = np.zeros(k), np.zeros((k, k)), C.c_double()
+        f = self._f("derv_mixlen")
+        f.argtypes = [C.c_void_p] + [C.POINTER(C.c_double)] * 4
+        self.last_status = self._check(f(self.ctx, _dp(a), _dp(df), _dp(ddf), C.byref(lnl)))
+        return df, ddf, lnl.value
+
+    def derv_mixlen_class(self, cls, length):
+        """-> (df, ddf) of heterotachy class `cls` alone (computeLikelihoodDervMixlen)."""
+        df, ddf = C.c_double(), C.c_double()
+        f = self._f("derv_mixlen_class")
+        f.argtypes = [C.c_void_p, C.c_int32, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        self.last_status = self._check(f(self.ctx, cls, length, C.byref(df), C.byref(ddf)))
+        return df.value, ddf.value
+
     def optimize_branch(self, dad, node, guess, min_len=1e-6, max_len=10.0, xacc=None, max_steps=100):
         """b200lk_optimize_branch: theta + the whole safeguarded Newton-Raphson iteration on the device.
         Returns (optimised length, d2l, derivative evaluations)."""
@@ -405,7 +460,7 @@ class Batch:
 
 
 def engine_for(aln, model, rates, props, *, nslots, p_invar=0.0, safe_numeric=False, device=0,
-               lib_path=LIB_PATH, prefix="b200lk_", unobserved=None, fused=False):
+               lib_path=LIB_PATH, prefix="b200lk_", unobserved=None, fused=False, asc_holder=False):
     """Create a context for a workload.Alignment + workload.EigenModel and load
     tips, pattern weights and the model (the one-time uploads of
     initializeAllPartialLh / computeTipPartialLikelihood)."""
@@ -415,6 +470,8 @@ def engine_for(aln, model, rates, props, *, nslots, p_invar=0.0, safe_numeric=Fa
                  device=device, lib_path=lib_path, prefix=prefix, fused_mix_rate=fused,
                  n_unobserved=0 if unobserved is None else np.asarray(unobserved).shape[1])
     eng.upload_tips(aln.states, aln.ptn_freq, unobserved)
+    if asc_holder:
+        eng.set_asc(1)
     inv = W.ptn_invar(aln, model, p_invar)
     if unobserved is not None:
         # +ASC: the unobserved patterns follow the observed ones; their ptn_invar entries are the reference's

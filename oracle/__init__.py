@@ -50,7 +50,7 @@ class RefRun:
     (ref_harness.cpp).  kernel: LK_SSE2 (Vec2d), LK_AVX (Vec4d), LK_AVX_FMA (Vec4d + FMA)."""
 
     def __init__(self, tree, aln, model, rates, props, *, kernel=LK_AVX_FMA, safe=False, threads=1, p_invar=0.0,
-                 unobserved=None, fused=False, site_models=None, nonrev=None):
+                 unobserved=None, fused=False, site_models=None, nonrev=None, mixlen=None, asc_holder=False):
         import ctypes as C
         import numpy as np
         from iqtree2_b200 import workload as W
@@ -98,6 +98,11 @@ class RefRun:
             q = f64(nonrev[1])
             self.lib.ref_set_next_nonrev(int(nonrev[0]), aln.nstates, model.nmix, C.c_void_p(q.ctypes.data),
                                          *[C.c_void_p(a.ctypes.data) for a in cx])
+        if mixlen is not None:  # heterotachy: class c of every branch has length (newick length) * mixlen[c]
+            mm = f64(mixlen)
+            self.lib.ref_set_next_mixlen(len(mm), C.c_void_p(mm.ctypes.data))
+        if asc_holder:  # the unobserved patterns are Holder's (ASC_VARIANT_MISSING)
+            self.lib.ref_set_next_asc_holder(1)
         if fused:  # model_factory->fused_mix_rate: category c = mixture class c at rate category c
             self.lib.ref_set_next_fused(1)
         self.lib.ref_create.restype = C.c_void_p
@@ -136,6 +141,28 @@ class RefRun:
 
     def set_current_length(self, t):
         self.lib.ref_set_current_length(self.h, self.C.c_double(t))
+
+    # heterotachy
+    def set_current_mixlen(self, lens):
+        a = self.np.ascontiguousarray(lens, dtype=self.np.float64)
+        self.lib.ref_set_current_mixlen(self.h, self.C.c_void_p(a.ctypes.data), len(a))
+
+    def derv_mixlen(self, nclass, again=False):
+        np, C = self.np, self.C
+        df, ddf, lnl = np.zeros(nclass), np.zeros((nclass, nclass)), C.c_double()
+        self.lib.ref_derv_mixlen(self.h, C.c_void_p(df.ctypes.data), C.c_void_p(ddf.ctypes.data), C.byref(lnl),
+                                 int(again))
+        return df, ddf, lnl.value
+
+    def derv_mixlen_class(self, cls, length, again=False):
+        C = self.C
+        df, ddf = C.c_double(), C.c_double()
+        self.lib.ref_derv_mixlen_class(self.h, int(cls), C.c_double(length), C.byref(df), C.byref(ddf), int(again))
+        return df.value, ddf.value
+
+    def set_ptn_freq(self, freq):
+        a = self.np.ascontiguousarray(freq, dtype=self.np.float64)
+        self.lib.ref_set_ptn_freq(self.h, self.C.c_void_p(a.ctypes.data))
 
     def from_buffer(self):
         return self.lib.ref_from_buffer(self.h)

@@ -59,6 +59,10 @@ typedef struct orc_ctx {
     int nonrev, rooted;
     double *nr_Q, *nr_ev, *nr_V, *nr_Vi, *nr_freq, *nr_tipvec;
     b200lk_end nr_dad, nr_node;
+    /* Holder's +ASC for missing data (ASC_VARIANT_MISSING): n_unobserved = nstates * nptn patterns, state-major
+     * (Alignment::getUnobservedConstPatterns, alignment/alignment.cpp:4150-4172); per-pattern derivative terms */
+    int asc_holder;
+    double *const_df, *const_ddf; /* [n_unobserved] */
 } orc_ctx;
 
 /* ------------------------------------------------------------------ helpers */
@@ -302,6 +306,7 @@ int orc_destroy(orc_ctx *c) {
     free(c->tip_partial_lh); free(c->theta_all); free(c->buffer_scale_all); free(c->pattern_lh);
     free(c->pattern_lh_cat); free(c->s_eval); free(c->s_evec); free(c->s_inv); free(c->s_tip);
     free(c->nr_Q); free(c->nr_ev); free(c->nr_V); free(c->nr_Vi); free(c->nr_freq); free(c->nr_tipvec);
+    free(c->const_df); free(c->const_ddf);
     free(c);
     return B200LK_OK;
 }
@@ -497,14 +502,15 @@ static void update_node_site(orc_ctx *c, const b200lk_node *nd, const b200lk_chi
 /* tree/phylokernelnew.h:1062-1108 (reversible, non-vectorised branch):
  * echild[c][x][i] = evec[m][x][i] * exp(eval[m][i] * rate[c%ncat] * len)
  * leaf[s][c][x]   = sum_i echild[c][x][i] * tip_partial_lh[s][m][i]; row s = STATE_UNKNOWN is 1.0 */
-static void partial_info(const orc_ctx *c, double len, int is_leaf, double *echild, double *leaf) {
+static void partial_info(const orc_ctx *c, double len, const double *lens, int is_leaf, double *echild, double *leaf) {
     int n = c->d.nstates, ncat = c->d.ncat, ncm = c->ncat_mix, block = c->block;
     int denom = c->d.fused_mix_rate ? 1 : ncat;
     int tip_block = n * c->d.nmix;
     double expchild[n];
     for (int cc = 0; cc < ncm; cc++) {
         int m = cc / denom;
-        double len_child = c->rates[cc % ncat] * len;
+        /* child->getLength(cat_id[c]): one length per category under heterotachy (:1017, 1069) */
+        double len_child = c->rates[cc % ncat] * (lens ? lens[cc % ncat] : len);
         const double *eval = c->eval + m * n, *evec = c->evec + (size_t)m * n * n;
         for (int i = 0; i < n; i++) expchild[i] = exp(eval[i] * len_child);
         double *e = echild + (size_t)cc * n * n;
@@ -693,10 +699,11 @@ static void update_node(orc_ctx *c, const b200lk_node *nd, const b200lk_child *c
  * tables for every entry, then every entry over every pattern range. */
 #include "nonrev_oracle.inc"
 
-int orc_update_partials(orc_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
-                        int32_t nchildren) {
+static int update_partials_impl(orc_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
+                                int32_t nchildren, const double *child_len) {
     const int n = c->d.nstates, block = c->block;
     if (nnodes <= 0) return B200LK_OK;
+    if (child_len && (c->d.site_specific != B200LK_MODEL_REV)) return B200LK_ERR_UNSUPPORTED;
     if (c->d.site_specific == B200LK_MODEL_NONREV)
         return c->nonrev ? nr_update_partials(c, nodes, nnodes, children, nchildren) : B200LK_ERR_STATE;
     if (c->site) { /* no P-factor tables: every pattern has its own eigen-system */
@@ -728,7 +735,8 @@ int orc_update_partials(orc_ctx *c, const b200lk_node *nodes, int32_t nnodes, co
             echild[j] = (double *)malloc(sizeof(double) * block * n);
             int is_leaf = children[j].kind == B200LK_CHILD_LEAF;
             if (is_leaf) leaf[j] = (double *)malloc(sizeof(double) * block * c->d.n_state_codes);
-            partial_info(c, children[j].length, is_leaf, echild[j], leaf[j]);
+            partial_info(c, children[j].length, child_len ? child_len + (size_t)j * c->d.ncat : NULL, is_leaf,
+                         echild[j], leaf[j]);
         }
     }
     int64_t ntot = c->ntot;
@@ -753,16 +761,28 @@ int orc_update_partials(orc_ctx *c, const b200lk_node *nodes, int32_t nnodes, co
     return B200LK_OK;
 }
 
+int orc_update_partials(orc_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
+                        int32_t nchildren) {
+    return update_partials_impl(c, nodes, nnodes, children, nchildren, NULL);
+}
+/* heterotachy: child_len[j][k] = children[j]->getLength(k), k < ncat (tree/phylokernelnew.h:1017, 1069) */
+int orc_update_partials_mixlen(orc_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
+                               int32_t nchildren, const double *child_len) {
+    if (!child_len) return B200LK_ERR_ARG;
+    return update_partials_impl(c, nodes, nnodes, children, nchildren, child_len);
+}
+
 /* ------------------------------------------------------- branch-level steps */
 
 /* val[c][i] = exp(eval[m][i]*rate*len) * prop*mixw; optionally val1 = cof*val, val2 = cof*val1
  * (tree/phylokernelnew.h:2342-2357, 2719-2730, 3255-3266) */
-static void branch_vals(const orc_ctx *c, double len, double *val0, double *val1, double *val2) {
+static void branch_vals_l(const orc_ctx *c, double len_, const double *lens, double *val0, double *val1, double *val2) {
     int n = c->d.nstates, ncat = c->d.ncat, ncm = c->ncat_mix;
     int denom = c->d.fused_mix_rate ? 1 : ncat;
     for (int cc = 0; cc < ncm; cc++) {
         int m = cc / denom, k = cc % ncat;
         double prop = c->props[k] * c->mixw[m];
+        double len = lens ? lens[k] : len_; /* dad_branch->getLength(mycat), :2325, 2348, 2711, 2725, 3248 */
         for (int i = 0; i < n; i++) {
             double cof = c->eval[m * n + i] * c->rates[k];
             double val = exp(cof * len) * prop;
@@ -776,6 +796,10 @@ static void branch_vals(const orc_ctx *c, double len, double *val0, double *val1
     }
 }
 
+static void branch_vals(const orc_ctx *c, double len, double *val0, double *val1, double *val2) {
+    branch_vals_l(c, len, NULL, val0, val1, val2);
+}
+
 static int check_ends(const orc_ctx *c, b200lk_end dad, b200lk_end node) {
     if (node.kind != B200LK_CHILD_INTERNAL || node.id < 0 || node.id >= c->d.nslots || !c->partial[node.id])
         return B200LK_ERR_ARG;
@@ -787,16 +811,35 @@ static int check_ends(const orc_ctx *c, b200lk_end dad, b200lk_end node) {
 /* computeLikelihoodBranchGenericSIMD, tree/phylokernelnew.h:2643-3185.
  * `node` = slot of dad_branch->partial_lh (subtree on the node side);
  * `dad`  = the leaf dad (tip-internal, :2740-2941) or the slot of node_branch->partial_lh (:2942-3074). */
-int orc_branch_lnl(orc_ctx *c, b200lk_end dad, b200lk_end node, double length, double *lnl) {
+/* Mark Holder's correction for missing data applied to the per-pattern and total lnL (:3137-3159, 3349-3368):
+ * const_lh[p] = sum over the n constant states of the unobserved pattern that copies p's gaps */
+static double holder_fix_lnl(orc_ctx *c) {
+    const int n = c->d.nstates;
+    const int64_t nptn = c->d.nptn, step = c->d.n_unobserved / n;
+    const double *const_lh = c->pattern_lh + nptn;
+    double sum_corr = 0.0;
+    for (int64_t p = 0; p < nptn; p++) {
+        double cl = const_lh[p];
+        for (int s = 1; s < n; s++) cl += const_lh[(size_t)s * step + p];
+        double prob_variant = log(1.0 - cl);
+        c->pattern_lh[p] -= prob_variant;
+        sum_corr += prob_variant * c->ptn_freq[p];
+    }
+    return sum_corr;
+}
+
+static int branch_lnl_impl(orc_ctx *c, b200lk_end dad, b200lk_end node, double length, const double *lens,
+                           double *lnl) {
     if (c->d.site_specific == B200LK_MODEL_NONREV)
         return c->nonrev ? nr_branch_lnl(c, dad, node, length, lnl) : B200LK_ERR_STATE;
+    if (lens && c->site) return B200LK_ERR_UNSUPPORTED;
     int rc = check_ends(c, dad, node);
     if (rc) return rc;
     const int n = c->d.nstates, ncm = c->ncat_mix, block = c->block, safe = c->d.safe_numeric;
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     const int64_t nptn = c->d.nptn, ntot = c->ntot;
     double val[block];
-    if (!c->site) branch_vals(c, length, val, NULL, NULL);
+    if (!c->site) branch_vals_l(c, length, lens, val, NULL, NULL);
     const double *pdad_all = c->partial[node.id]; /* "partial_lh_dad" = dad_branch->partial_lh */
     const uint8_t *sdad = c->scale[node.id];
     double *lh_node_tab = NULL;
@@ -896,7 +939,9 @@ int orc_branch_lnl(orc_ctx *c, b200lk_end dad, b200lk_end node, double length, d
             tree_lh += c->pattern_lh[p] * c->ptn_freq[p];
         }
     }
-    if (c->d.n_unobserved > 0) { /* ASC_Lewis, :3160-3182 */
+    if (c->asc_holder) { /* :3137-3159 */
+        tree_lh -= holder_fix_lnl(c);
+    } else if (c->d.n_unobserved > 0) { /* ASC_Lewis, :3160-3182 */
         double nsite = 0.0;
         for (int64_t p = 0; p < nptn; p++) nsite += c->ptn_freq[p];
         prob_const = log(1.0 - prob_const);
@@ -905,6 +950,30 @@ int orc_branch_lnl(orc_ctx *c, b200lk_end dad, b200lk_end node, double length, d
     }
     *lnl = tree_lh;
     return warn;
+}
+int orc_branch_lnl(orc_ctx *c, b200lk_end dad, b200lk_end node, double length, double *lnl) {
+    return branch_lnl_impl(c, dad, node, length, NULL, lnl);
+}
+/* heterotachy: len[k] = dad_branch->getLength(k) (:2711, 2725) */
+int orc_branch_lnl_mixlen(orc_ctx *c, b200lk_end dad, b200lk_end node, const double *len, double *lnl) {
+    if (!len) return B200LK_ERR_ARG;
+    return branch_lnl_impl(c, dad, node, len[0], len, lnl);
+}
+/* Which +ASC correction the unobserved patterns stand for (model_factory->getASC(), utils/tools.h:549-555):
+ * 0 = Lewis (ASC_VARIANT, the default when n_unobserved > 0), 1 = Holder for missing data (ASC_VARIANT_MISSING:
+ * n_unobserved = nstates * nptn, state-major) */
+int orc_set_asc(orc_ctx *c, int32_t type) {
+    if (type != 0 && type != 1) return B200LK_ERR_ARG;
+    if (type == 1) {
+        if (c->d.n_unobserved != (int64_t)c->d.nstates * c->d.nptn || c->d.n_unobserved == 0) return B200LK_ERR_ARG;
+        if (c->d.site_specific != B200LK_MODEL_REV) return B200LK_ERR_UNSUPPORTED;
+        if (!c->const_df) {
+            c->const_df = (double *)calloc(c->d.n_unobserved, sizeof(double));
+            c->const_ddf = (double *)calloc(c->d.n_unobserved, sizeof(double));
+        }
+    }
+    c->asc_holder = type;
+    return B200LK_OK;
 }
 
 /* computeLikelihoodBufferGenericSIMD, tree/phylokernelnew.h:2050-2231 */
@@ -1025,9 +1094,15 @@ int orc_derv(orc_ctx *c, double length, double *df, double *ddf) {
                     dfp *= SCALING_THRESHOLD;
                     ddfp *= SCALING_THRESHOLD;
                 }
-                prob_const += lh;
-                df_const += dfp;
-                ddf_const += ddfp;
+                if (c->asc_holder) { /* :2522-2525 */
+                    c->pattern_lh[p] = lh;
+                    c->const_df[p - nptn] = dfp;
+                    c->const_ddf[p - nptn] = ddfp;
+                } else {
+                    prob_const += lh;
+                    df_const += dfp;
+                    ddf_const += ddfp;
+                }
             }
         }
         all_df += my_df;
@@ -1035,7 +1110,25 @@ int orc_derv(orc_ctx *c, double length, double *df, double *ddf) {
     }
     *df = all_df;
     *ddf = all_ddf;
-    if (c->d.n_unobserved > 0 && isfinite(*df)) { /* :2620-2628 */
+    if (c->asc_holder) { /* :2580-2619; like the reference, applied whether or not df is finite */
+        const int64_t step = c->d.n_unobserved / n;
+        const double *const_lh = c->pattern_lh + nptn;
+        double sum_df = 0.0, sum_ddf = 0.0;
+        for (int64_t p = 0; p < nptn; p++) {
+            double cl = const_lh[p], cd = c->const_df[p], cdd = c->const_ddf[p];
+            for (int s = 1; s < n; s++) {
+                cl += const_lh[(size_t)s * step + p];
+                cd += c->const_df[(size_t)s * step + p];
+                cdd += c->const_ddf[(size_t)s * step + p];
+            }
+            double pc = 1.0 - cl;
+            double df_frac = cd / pc, ddf_frac = cdd / pc;
+            sum_df += c->ptn_freq[p] * df_frac;
+            sum_ddf += c->ptn_freq[p] * (ddf_frac + df_frac * df_frac);
+        }
+        *df += sum_df;
+        *ddf += sum_ddf;
+    } else if (c->d.n_unobserved > 0 && isfinite(*df)) { /* :2620-2628 */
         double nsite = 0.0;
         for (int64_t p = 0; p < nptn; p++) nsite += c->ptn_freq[p];
         prob_const = 1.0 - prob_const;
@@ -1051,13 +1144,14 @@ int orc_derv(orc_ctx *c, double length, double *df, double *ddf) {
 }
 
 /* computeLikelihoodFromBufferGenericSIMD, tree/phylokernelnew.h:3196-3392 */
-int orc_lnl_from_buffer(orc_ctx *c, double length, double *lnl) {
+static int from_buffer_impl(orc_ctx *c, double length, const double *lens, double *lnl) {
     if (!c->theta_computed) return B200LK_ERR_STATE;
     if (c->nonrev) return nr_branch_lnl(c, c->nr_dad, c->nr_node, length, lnl); /* tree/phylokernelfma.cpp:99 */
+    if (lens && c->site) return B200LK_ERR_UNSUPPORTED;
     const int block = c->block;
     const int64_t nptn = c->d.nptn, ntot = c->ntot;
     double val0[block];
-    if (!c->site) branch_vals(c, length, val0, NULL, NULL);
+    if (!c->site) branch_vals_l(c, length, lens, val0, NULL, NULL);
     double tree_lh = 0.0, prob_const = 0.0;
     int nthr = c->nthreads;
 #ifdef _OPENMP
@@ -1096,7 +1190,9 @@ int orc_lnl_from_buffer(orc_ctx *c, double length, double *lnl) {
             tree_lh += c->pattern_lh[p] * c->ptn_freq[p];
         }
     }
-    if (c->d.n_unobserved > 0) { /* :3369-3390 */
+    if (c->asc_holder) { /* :3349-3368 */
+        tree_lh -= holder_fix_lnl(c);
+    } else if (c->d.n_unobserved > 0) { /* :3369-3390 */
         double nsite = 0.0;
         for (int64_t p = 0; p < nptn; p++) nsite += c->ptn_freq[p];
         prob_const = log(1.0 - prob_const);
@@ -1105,6 +1201,118 @@ int orc_lnl_from_buffer(orc_ctx *c, double length, double *lnl) {
     }
     *lnl = tree_lh;
     return warn;
+}
+int orc_lnl_from_buffer(orc_ctx *c, double length, double *lnl) { return from_buffer_impl(c, length, NULL, lnl); }
+int orc_lnl_from_buffer_mixlen(orc_ctx *c, const double *len, double *lnl) {
+    if (!len) return B200LK_ERR_ARG;
+    return from_buffer_impl(c, len[0], len, lnl);
+}
+
+/* computeLikelihoodDerv*SIMD with isMixlen() (tree/phylokernelnew.h:2365-2462, 2556-2568): the gradient over the ncat
+ * class lengths of one branch, the Hessian, and the log-likelihood (the reference returns it in df[nmixlen]).
+ * +ASC is not supported there (ASSERT(0) at :2449). */
+int orc_derv_mixlen(orc_ctx *c, const double *len, double *df, double *ddf, double *lnl) {
+    if (!c->theta_computed) return B200LK_ERR_STATE;
+    if (!len || !df || !ddf) return B200LK_ERR_ARG;
+    if (c->site || c->nonrev || c->d.n_unobserved > 0) return B200LK_ERR_UNSUPPORTED;
+    const int n = c->d.nstates, block = c->block, ncat = c->d.ncat, ncm = c->ncat_mix;
+    const int64_t nptn = c->d.nptn;
+    double val0[block], val1[block], val2[block];
+    branch_vals_l(c, len[0], len, val0, val1, val2);
+    double all_lh = 0.0;
+    for (int i = 0; i < ncat; i++) df[i] = 0.0;
+    for (int i = 0; i < ncat * ncat; i++) ddf[i] = 0.0;
+    for (int64_t p = 0; p < nptn; p++) {
+        double df_ptn[ncat], ddf_ptn[ncat], lh_ptn = 0.0;
+        for (int i = 0; i < ncat; i++) df_ptn[i] = ddf_ptn[i] = 0.0;
+        const double *theta = c->theta_all + (size_t)p * block;
+        for (int cc = 0; cc < ncm; cc++) { /* dotProductTriple<..., ADD = true> per category, :2410-2423 */
+            double l, d1, d2;
+            int i = cc % ncat;
+            dot_triple(val0 + cc * n, val1 + cc * n, val2 + cc * n, theta + cc * n, &l, &d1, &d2, n, n);
+            lh_ptn += l;
+            df_ptn[i] += d1;
+            ddf_ptn[i] += d2;
+        }
+        lh_ptn = fabs(lh_ptn) + c->ptn_invar[p];
+        double freq = c->ptn_freq[p], inv = 1.0 / lh_ptn;
+        for (int i = 0; i < ncat; i++) {
+            df_ptn[i] *= inv;
+            ddf_ptn[i] *= inv;
+            df[i] = fma(df_ptn[i], freq, df[i]);
+        }
+        for (int i = 0; i < ncat; i++) {
+            ddf[i * ncat + i] += fma(-df_ptn[i], df_ptn[i], ddf_ptn[i]) * freq;
+            for (int k = 0; k < ncat; k++)
+                if (k != i) ddf[i * ncat + k] -= df_ptn[i] * df_ptn[k] * freq;
+        }
+        all_lh = fma(log(lh_ptn) + c->buffer_scale_all[p], freq, all_lh);
+    }
+    if (lnl) *lnl = all_lh;
+    return B200LK_OK;
+}
+
+/* computeLikelihoodDervMixlen*SIMD (tree/phylokernelnew.h:3397-3580): df, ddf of the EM sub-problem of class
+ * `cur_mixlen` (getCurMixture()): only that class's slice of theta enters, at length `len` =
+ * dad_branch->getLength(cur_mixlen); the caller has put the posterior weights into ptn_freq
+ * (tree/phylotreemixlen.cpp:449-481).  The reference indexes val with the mixture class alone (:3473-3485) and theta at
+ * cur_mixlen*nstates*nmix (:3512): with nmix > 1 and unfused rates that is not the category layout of the other
+ * kernels, so the entry is restricted to what PhyloTreeMixlen allows on this path (fused, or nmix == 1; :427-428). */
+int orc_derv_mixlen_class(orc_ctx *c, int32_t cur_mixlen, double len, double *df, double *ddf) {
+    if (!c->theta_computed) return B200LK_ERR_STATE;
+    if (c->site || c->nonrev || c->asc_holder) return B200LK_ERR_UNSUPPORTED;
+    if (!c->d.fused_mix_rate && c->d.nmix > 1) return B200LK_ERR_UNSUPPORTED;
+    if (cur_mixlen < 0 || cur_mixlen >= c->d.ncat) return B200LK_ERR_ARG;
+    const int n = c->d.nstates, block = c->block;
+    const int64_t nptn = c->d.nptn, ntot = c->ntot;
+    const int cur_mix = c->d.fused_mix_rate ? cur_mixlen : 0;
+    double val0[n], val1[n], val2[n];
+    double prop = c->mixw[cur_mix];
+    for (int i = 0; i < n; i++) { /* :3472-3486: no rate, no category proportion */
+        double cof = c->eval[cur_mix * n + i];
+        double val = exp(cof * len) * prop;
+        val0[i] = val;
+        val1[i] = cof * val;
+        val2[i] = cof * val1[i];
+    }
+    double all_df = 0.0, all_ddf = 0.0, prob_const = 0.0, df_const = 0.0, ddf_const = 0.0;
+    for (int64_t p = 0; p < ntot; p++) {
+        double lh, d1, d2;
+        dot_triple(val0, val1, val2, c->theta_all + (size_t)p * block + (size_t)cur_mixlen * n, &lh, &d1, &d2, n, n);
+        lh = fabs(lh) + c->ptn_invar[p];
+        if (p < nptn) {
+            double inv = 1.0 / lh, freq = c->ptn_freq[p];
+            d1 *= inv;
+            d2 *= inv;
+            all_df = fma(d1, freq, all_df);
+            all_ddf += fma(-d1, d1, d2) * freq;
+        } else {
+            prob_const += lh;
+            df_const += d1;
+            ddf_const += d2;
+        }
+    }
+    *df = all_df;
+    *ddf = all_ddf;
+    if (c->d.n_unobserved > 0) { /* :3560-3568 (Lewis) */
+        double nsite = 0.0;
+        for (int64_t p = 0; p < nptn; p++) nsite += c->ptn_freq[p];
+        prob_const = 1.0 / (1.0 - prob_const);
+        df_const *= prob_const;
+        ddf_const *= prob_const;
+        *df += nsite * df_const;
+        *ddf += nsite * (ddf_const + df_const * df_const);
+    }
+    if (!isfinite(*df)) {
+        *df = *ddf = 0.0;
+        return B200LK_WARN_DERV_NONFINITE;
+    }
+    return B200LK_OK;
+}
+/* new pattern weights (computePtnFreq, or the EM posteriors of tree/phylotreemixlen.cpp:470-474) */
+int orc_set_ptn_freq(orc_ctx *c, const double *ptn_freq) {
+    memcpy(c->ptn_freq, ptn_freq, sizeof(double) * c->d.nptn);
+    return B200LK_OK;
 }
 
 int orc_evaluate(orc_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,

@@ -30,6 +30,7 @@
 #define protected public
 #include "tree/phylotree.h"
 #include "tree/phylonode.h"
+#include "tree/phylonodemixlen.h"
 #include "model/modelsubst.h"
 #include "model/rateheterogeneity.h"
 #include "model/modelfactory.h"
@@ -182,6 +183,20 @@ public:
     virtual int isGammaRate() { return 0; }
 };
 
+// Heterotachy (PhyloTreeMixlen, tree/phylotreemixlen.h:89-98, 218; that class derives from IQTree and cannot be built
+// here): the three virtuals the kernels consult, and nodes whose neighbours carry one length per class
+// (PhyloNeighborMixlen::getLength(c), tree/phylonodemixlen.h:64-69)
+class HarnessMixlenTree : public PhyloTree {
+public:
+    int mixlen, cur_mixture;
+    explicit HarnessMixlenTree(int m) : PhyloTree(), mixlen(m), cur_mixture(-1) {}
+    virtual Node *newNode(int node_id = -1, const char *node_name = NULL) { return new PhyloNodeMixlen(node_id, node_name); }
+    virtual Node *newNode(int node_id, int node_name) { return new PhyloNodeMixlen(node_id, node_name); }
+    virtual bool isMixlen() { return true; }
+    virtual int getMixlen() { return mixlen; }
+    virtual int getCurMixture() { return cur_mixture; }
+};
+
 struct RefHandle {
     PhyloTree *tree;
     Alignment *aln;
@@ -262,6 +277,21 @@ static double *interleave_models(const std::vector<double> &src, size_t nptn, si
 
 // model_factory->fused_mix_rate of the NEXT ref_create (model/modelfactory.h; category c = mixture class c with rate
 // category c, tree/phylokernelnew.h:1322-1331)
+// Heterotachy for the NEXT ref_create: class c of every branch has length  newick length * mult[c]
+static std::vector<double> next_mixlen_mult;
+void ref_set_next_mixlen(int nclass, const double *mult) { next_mixlen_mult.assign(mult, mult + nclass); }
+// +ASC flavour of the NEXT ref_create's unobserved patterns: 0 Lewis (ASC_VARIANT), 1 Holder (ASC_VARIANT_MISSING)
+static int next_asc_holder = 0;
+void ref_set_next_asc_holder(int on) { next_asc_holder = on; }
+static void set_mix_lengths(Node *node, Node *dad, const std::vector<double> &mult) {
+    for (size_t i = 0; i < node->neighbors.size(); i++) {
+        PhyloNeighborMixlen *nb = (PhyloNeighborMixlen *)node->neighbors[i];
+        nb->lengths.resize(mult.size());
+        for (size_t c = 0; c < mult.size(); c++) nb->lengths[c] = nb->length * mult[c];
+        if (nb->node != dad) set_mix_lengths(nb->node, node, mult);
+    }
+}
+
 static int next_fused = 0;
 void ref_set_next_fused(int fused) { next_fused = fused; }
 
@@ -371,7 +401,8 @@ void *ref_create(const ref_problem *pb) {
     f->fused_mix_rate = next_fused != 0;
     next_fused = 0;
     if (next_n_unobserved > 0) {
-        f->ASC_type = ASC_VARIANT;  // Lewis (utils/tools.h:549-555)
+        f->ASC_type = next_asc_holder ? ASC_VARIANT_MISSING : ASC_VARIANT;  // Holder / Lewis (utils/tools.h:549-555)
+        next_asc_holder = 0;
         for (int u = 0; u < next_n_unobserved; u++) {
             Pattern pat;
             pat.resize(pb->ntaxa);
@@ -385,12 +416,15 @@ void *ref_create(const ref_problem *pb) {
     h->rate = r;
     h->factory = f;
     // tree
-    PhyloTree *tree = new PhyloTree();
+    std::vector<double> mixlen_mult;
+    mixlen_mult.swap(next_mixlen_mult);
+    PhyloTree *tree = mixlen_mult.empty() ? new PhyloTree() : new HarnessMixlenTree((int)mixlen_mult.size());
     tree->params = &params;
     std::stringstream ss;
     ss << pb->newick;
     bool rooted = nonrev_mode == 1;
     tree->readTree(ss, rooted);
+    if (!mixlen_mult.empty()) set_mix_lengths(tree->root, NULL, mixlen_mult);
     tree->setAlignment(aln);
     tree->setModelFactory(f);
     m->site = !next_site_eval.empty();
@@ -462,6 +496,43 @@ void ref_derv_again(void *hv, double *df, double *ddf) {
     RefHandle *h = (RefHandle *)hv;
     h->tree->computeLikelihoodDerv(h->cur_dad_branch, h->cur_dad, df, ddf);
 }
+// ---- heterotachy ----------------------------------------------------------------------------------------
+// class lengths of the current branch (both directions)
+void ref_set_current_mixlen(void *hv, const double *len, int nclass) {
+    RefHandle *h = (RefHandle *)hv;
+    DoubleVector v(len, len + nclass);
+    h->tree->current_it->setLength(v);
+    h->tree->current_it_back->setLength(v);
+}
+// computeLikelihoodDerv with isMixlen(): df[nclass], ddf[nclass][nclass] and lnL (df[nclass], tree/phylokernelnew.h:2566)
+void ref_derv_mixlen(void *hv, double *df, double *ddf, double *lnl, int again) {
+    RefHandle *h = (RefHandle *)hv;
+    const int m = h->tree->getMixlen();
+    std::vector<double> g(m + 1), hs((size_t)m * m);
+    if (!again) h->tree->theta_computed = false;
+    h->tree->computeLikelihoodDerv(h->cur_dad_branch, h->cur_dad, g.data(), hs.data());
+    memcpy(df, g.data(), sizeof(double) * m);
+    memcpy(ddf, hs.data(), sizeof(double) * m * m);
+    *lnl = g[m];
+}
+// computeLikelihoodDervMixlen (tree/phylokernelnew.h:3397-3580) for class `cls` at length `len`, as
+// PhyloTreeMixlen::computeFuncDerv calls it (tree/phylotreemixlen.cpp:728-737)
+void ref_derv_mixlen_class(void *hv, int cls, double len, double *df, double *ddf, int again) {
+    RefHandle *h = (RefHandle *)hv;
+    HarnessMixlenTree *t = (HarnessMixlenTree *)h->tree;
+    t->cur_mixture = cls;
+    t->current_it->setLength(cls, len);
+    t->current_it_back->setLength(cls, len);
+    if (!again) t->theta_computed = false;
+    (t->*(t->computeLikelihoodDervMixlenPointer))(h->cur_dad_branch, h->cur_dad, *df, *ddf);
+    t->cur_mixture = -1;
+}
+// pattern weights as the EM step rewrites them (tree/phylotreemixlen.cpp:470-474)
+void ref_set_ptn_freq(void *hv, const double *freq) {
+    RefHandle *h = (RefHandle *)hv;
+    memcpy(h->tree->ptn_freq, freq, sizeof(double) * h->aln->size());
+}
+
 double ref_from_buffer(void *hv) { return ((RefHandle *)hv)->tree->computeLikelihoodFromBuffer(); }
 
 // Newton-Raphson on the current branch exactly as the reference runs it (tree/phylotree.cpp:2585-2635)

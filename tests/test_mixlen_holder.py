@@ -1,0 +1,247 @@
+"""Heterotachy (mixed branch lengths) and Holder's +ASC -- SURVEY.md 8a rows a8/a9/a15, 8f rank 3.
+
+CPU half: the C restatement (oracle/) against the REFERENCE's own kernels run through oracle/_ref
+  * per-class branch lengths in computePartialInfo / computeLikelihoodBranch / FromBuffer
+    (child->getLength(c), tree/phylokernelnew.h:1017, 1069, 2711, 2725, 3248),
+  * computeLikelihoodDerv under isMixlen() (:2365-2462, 2556-2568): gradient, Hessian, lnL,
+  * computeLikelihoodDervMixlen (:3397-3580): the EM sub-problem of one class,
+  * ASC_VARIANT_MISSING (Holder): :2522-2525, 2580-2619, 3137-3159, 3349-3368.
+GPU half (-m gpu): the CUDA path against the pinned oracle on the same inputs, through the C ABI.
+Tolerances: 1e-11 relative oracle-vs-reference, 1e-9 relative CUDA-vs-oracle (north_star); scale counts bit-exact.
+"""
+import numpy as np
+import pytest
+
+import oracle
+from iqtree2_b200 import workload as W
+from iqtree2_b200.capi import INTERNAL, LEAF, engine_for
+from tests.common import make_problem, rel
+
+needs_ref = pytest.mark.skipif(not oracle.ref_available(), reason="oracle/_ref not built (needs /root/reference)")
+
+
+def mixlen_problem(nstates, nclass, seed, ntaxa=9, nsite=120, nmix=1, fused=False):
+    """Heterotachy-shaped problem: `nclass` classes at rate 1 with weights `props` (RateHeterotachy,
+    model/rateheterotachy.cpp: getRate() == 1), class c of every branch at length * mult[c]."""
+    tree = W.random_tree(ntaxa, seed)
+    model = W.gtr_model() if (nstates == 4 and nmix == 1) else W.random_reversible_model(nstates, seed + 100, nmix)
+    rng = np.random.default_rng(seed)
+    props = rng.dirichlet(np.full(nclass, 5.0))
+    rates = np.ones(nclass)
+    g_rates, g_props = W.discrete_gamma(0.7, 4)
+    aln = W.simulate_alignment(tree, model, g_rates, g_props, nsite, seed + 7, compress=True)
+    mult = np.linspace(0.4, 2.2, nclass)
+    return tree, model, rates, props, aln, mult
+
+
+def mix_child_len(tr, mult):
+    """[nchildren][nclass] in the order pack_traversal lays the children out"""
+    return np.array([[ln * m for m in mult] for e in tr for (_, _, ln) in e[3]])
+
+
+def mixlen_eval(eng, tree, mult, leaf=0):
+    c = tree.adj[leaf][0]
+    tr = W.traversal(tree, c, leaf)
+    eng.update_partials_mixlen(tr, mix_child_len(tr, mult))
+    lens = tree.get_length(leaf, c) * np.asarray(mult)
+    dad, node = (LEAF, leaf), (INTERNAL, tr[-1][2])
+    out = {"tr": tr, "lens": lens, "ends": (dad, node)}
+    out["lnl"] = eng.branch_lnl_mixlen(dad, node, lens)
+    out["pattern_lh"] = eng.fetch_pattern_lh()
+    out["pattern_lh_cat"] = eng.fetch_pattern_lh_cat()
+    out["scale"] = {e[2]: eng.fetch_scale_num(e[2]) for e in tr}
+    out["partial_top"] = eng.fetch_partial(tr[-1][2])
+    eng.build_theta(dad, node)
+    out["df"], out["ddf"], out["lnl_derv"] = eng.derv_mixlen(lens)
+    out["lnl_buf"] = eng.lnl_from_buffer_mixlen(lens * 1.25)
+    out["cls"] = [eng.derv_mixlen_class(k, lens[k] * 0.8) for k in range(len(mult))]
+    return out
+
+
+# ---------------------------------------------------------------------------------------------- CPU: oracle vs reference
+@needs_ref
+@pytest.mark.parametrize("kernel", [oracle.LK_SSE2, oracle.LK_AVX_FMA])
+@pytest.mark.parametrize("nstates,nclass,safe", [(4, 4, False), (4, 2, True), (20, 3, False), (7, 3, True)])
+def test_oracle_mixlen_matches_reference(nstates, nclass, safe, kernel):
+    tree, model, rates, props, aln, mult = mixlen_problem(nstates, nclass, seed=31 + nstates)
+    ref = oracle.RefRun(tree, aln, model, rates, props, kernel=kernel, safe=safe, mixlen=mult)
+    eng = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa, safe_numeric=safe)
+    got = mixlen_eval(eng, tree, mult)
+    want = ref.lnl_at_leaf(0)
+    # heterotachy is not a no-op: the same tree with every class at the plain length scores differently
+    eng2 = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa, safe_numeric=safe)
+    eng2.update_partials(got["tr"])
+    assert abs(eng2.branch_lnl(*got["ends"], tree.get_length(0, tree.adj[0][0])) - want) > 1e-3
+    assert abs(got["lnl"] - want) <= 1e-11 * abs(want)
+    assert np.allclose(got["pattern_lh"], ref.pattern_lh(), rtol=1e-11, atol=1e-11)
+    assert np.allclose(got["pattern_lh_cat"], ref.pattern_lh_cat(), rtol=1e-10, atol=1e-300)
+    df, ddf, lnl = ref.derv_mixlen(nclass)
+    assert rel(got["df"], df) <= 1e-10 and rel(got["ddf"], ddf) <= 1e-10
+    assert abs(got["lnl_derv"] - lnl) <= 1e-11 * abs(lnl) and abs(lnl - want) <= 1e-9 * abs(want)
+    ref.set_current_mixlen(got["lens"] * 1.25)
+    assert abs(got["lnl_buf"] - ref.from_buffer()) <= 1e-11 * abs(want)
+    ref.set_current_mixlen(got["lens"])
+    for k in range(nclass):
+        rdf, rddf = ref.derv_mixlen_class(k, got["lens"][k] * 0.8, again=True)
+        assert rel(got["cls"][k][0], rdf) <= 1e-10 and rel(got["cls"][k][1], rddf) <= 1e-10, k
+    ref.close()
+
+
+@needs_ref
+def test_oracle_mixlen_em_weights(tmp_path):
+    """The EM step of PhyloTreeMixlen::optimizeOneBranch (tree/phylotreemixlen.cpp:449-481): posterior class weights
+    replace ptn_freq, then the class derivative is taken."""
+    tree, model, rates, props, aln, mult = mixlen_problem(4, 3, seed=77)
+    ref = oracle.RefRun(tree, aln, model, rates, props, kernel=oracle.LK_AVX_FMA, mixlen=mult)
+    eng = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa)
+    got = mixlen_eval(eng, tree, mult)
+    ref.lnl_at_leaf(0)
+    ref.derv_mixlen(3)  # builds theta
+    lk = got["pattern_lh_cat"]
+    post = lk * (aln.ptn_freq / lk.sum(axis=1))[:, None]
+    for k in range(3):
+        eng.set_ptn_freq(post[:, k])
+        ref.set_ptn_freq(post[:, k])
+        a = eng.derv_mixlen_class(k, got["lens"][k])
+        b = ref.derv_mixlen_class(k, got["lens"][k], again=True)
+        assert rel(a[0], b[0]) <= 1e-10 and rel(a[1], b[1]) <= 1e-10
+    ref.close()
+
+
+def holder_unobserved(aln, V=1):
+    """Alignment::getUnobservedConstPatterns(ASC_VARIANT_MISSING), alignment/alignment.cpp:4150-4172: for every
+    state x and observed pattern p, the constant-x pattern that keeps p's gaps/ambiguities as UNKNOWN; each state's
+    block is padded with all-UNKNOWN patterns to the kernel's vector width V (1 for the C ABI)."""
+    n = aln.nstates
+    blocks = []
+    pad = (-aln.nptn) % V
+    for x in range(n):
+        blk = np.where(aln.states < n, np.uint8(x), np.uint8(aln.state_unknown))
+        if pad:
+            blk = np.concatenate([blk, np.full((aln.ntaxa, pad), aln.state_unknown, dtype=np.uint8)], axis=1)
+        blocks.append(blk)
+    return np.concatenate(blocks, axis=1).astype(np.uint8)  # [ntaxa][n * nptn]
+
+
+def holder_eval(eng, tree, leaf=0):
+    c = tree.adj[leaf][0]
+    tr = W.traversal(tree, c, leaf)
+    L = tree.get_length(leaf, c)
+    eng.update_partials(tr)
+    dad, node = (LEAF, leaf), (INTERNAL, tr[-1][2])
+    out = {"tr": tr, "L": L, "ends": (dad, node)}
+    out["lnl"] = eng.branch_lnl(dad, node, L)
+    out["pattern_lh"] = eng.fetch_pattern_lh()
+    eng.build_theta(dad, node)
+    out["df"], out["ddf"] = eng.derv(L)
+    out["buf"] = [eng.lnl_from_buffer(t) for t in (0.5 * L, 2.0 * L)]
+    out["derv2"] = eng.derv(1.7 * L)
+    return out
+
+
+def holder_problem(nstates, seed):
+    # morphological-style variable-sites data with missing entries
+    tree, model, rates, props, aln = make_problem(8, 90 if nstates == 4 else 40, nstates=nstates, seed=seed, gaps=0.0)
+    rng = np.random.default_rng(seed + 5)
+    mask = rng.random(aln.states.shape) < 0.15
+    aln.states[mask] = aln.state_unknown
+    return tree, model, rates, props, aln
+
+
+@needs_ref
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates", [4, 20, 5])
+def test_oracle_holder_asc_matches_reference(nstates, safe):
+    tree, model, rates, props, aln = holder_problem(nstates, seed=41 + nstates)
+    unobs = holder_unobserved(aln)
+    kernel = oracle.LK_SSE2 if nstates == 5 else oracle.LK_AVX_FMA
+    ref = oracle.RefRun(tree, aln, model, rates, props, kernel=kernel, safe=safe, asc_holder=True,
+                        unobserved=holder_unobserved(aln, V=2 if kernel == oracle.LK_SSE2 else 4))
+    eng = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa, safe_numeric=safe, unobserved=unobs,
+                               asc_holder=True)
+    got = holder_eval(eng, tree)
+    want = ref.lnl_at_leaf(0)
+    lewis = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa, safe_numeric=safe)
+    lewis.update_partials(got["tr"])
+    assert abs(lewis.branch_lnl(*got["ends"], got["L"]) - want) > 1e-3
+    assert abs(got["lnl"] - want) <= 1e-11 * abs(want)
+    assert np.allclose(got["pattern_lh"], ref.pattern_lh(), rtol=1e-11, atol=1e-11)
+    rdf, rddf = ref.derv()
+    assert rel(got["df"], rdf) <= 1e-10 and rel(got["ddf"], rddf) <= 1e-10
+    for t, v in zip((0.5 * got["L"], 2.0 * got["L"]), got["buf"]):
+        ref.set_current_length(t)
+        assert abs(v - ref.from_buffer()) <= 1e-11 * abs(want)
+    ref.set_current_length(1.7 * got["L"])
+    rdf, rddf = ref.derv(again=True)
+    assert rel(got["derv2"][0], rdf) <= 1e-10 and rel(got["derv2"][1], rddf) <= 1e-10
+    ref.close()
+
+
+# ------------------------------------------------------------------------------------------------ GPU: CUDA vs oracle
+def _cmp_mixlen(got, want, tol=1e-9):
+    for s in want["scale"]:
+        assert np.array_equal(got["scale"][s], want["scale"][s]), "scale_num differs in slot %d" % s
+    for k in ("lnl", "lnl_derv", "lnl_buf"):
+        assert rel(got[k], want[k]) <= tol, (k, got[k], want[k])
+    assert rel(got["df"], want["df"]) <= tol and rel(got["ddf"], want["ddf"]) <= tol
+    assert rel(got["pattern_lh"], want["pattern_lh"]) <= tol
+    for k in ("partial_top", "pattern_lh_cat"):
+        g, w = got[k].reshape(got[k].shape[0], -1), want[k].reshape(want[k].shape[0], -1)
+        denom = np.maximum(np.abs(w).max(axis=1, keepdims=True), 1e-300)
+        assert float(np.max(np.abs(g - w) / denom)) <= tol, k
+    for a, b in zip(got["cls"], want["cls"]):
+        assert rel(a[0], b[0]) <= tol and rel(a[1], b[1]) <= tol
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nstates,nclass,safe,nmix,fused", [
+    (4, 4, False, 1, False), (4, 2, True, 1, False), (20, 3, False, 1, False), (20, 4, True, 1, False),
+    (7, 3, False, 1, False), (61, 2, True, 1, False), (4, 3, False, 3, True), (20, 2, False, 2, True)])
+def test_cuda_mixlen_matches_oracle(nstates, nclass, safe, nmix, fused):
+    tree, model, rates, props, aln, mult = mixlen_problem(nstates, nclass, seed=131 + nstates + nclass, ntaxa=12,
+                                                          nsite=700 if nstates <= 20 else 150, nmix=nmix, fused=fused)
+    kw = dict(nslots=tree.ntaxa, safe_numeric=safe, fused=fused)
+    gpu = engine_for(aln, model, rates, props, **kw)
+    cpu = oracle.oracle_engine(aln, model, rates, props, **kw)
+    _cmp_mixlen(mixlen_eval(gpu, tree, mult), mixlen_eval(cpu, tree, mult))
+
+
+@pytest.mark.gpu
+def test_cuda_mixlen_deep_tree_rescaling():
+    tree, model, rates, props, aln, mult = mixlen_problem(4, 3, seed=5, ntaxa=260, nsite=300)
+    kw = dict(nslots=tree.ntaxa)
+    gpu = engine_for(aln, model, rates, props, **kw)
+    cpu = oracle.oracle_engine(aln, model, rates, props, **kw)
+    g, w = mixlen_eval(gpu, tree, mult), mixlen_eval(cpu, tree, mult)
+    assert max(int(v.max()) for v in w["scale"].values()) >= 1
+    _cmp_mixlen(g, w)
+
+
+@pytest.mark.gpu
+def test_cuda_mixlen_em_weights():
+    tree, model, rates, props, aln, mult = mixlen_problem(20, 3, seed=9, ntaxa=10, nsite=400)
+    gpu = engine_for(aln, model, rates, props, nslots=tree.ntaxa)
+    cpu = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa)
+    g, w = mixlen_eval(gpu, tree, mult), mixlen_eval(cpu, tree, mult)
+    lk = w["pattern_lh_cat"]
+    post = lk * (aln.ptn_freq / lk.sum(axis=1))[:, None]
+    for k in range(3):
+        gpu.set_ptn_freq(post[:, k])
+        cpu.set_ptn_freq(post[:, k])
+        a, b = gpu.derv_mixlen_class(k, w["lens"][k]), cpu.derv_mixlen_class(k, w["lens"][k])
+        assert rel(a[0], b[0]) <= 1e-9 and rel(a[1], b[1]) <= 1e-9
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("nstates", [4, 20, 5])
+def test_cuda_holder_asc_matches_oracle(nstates, safe):
+    tree, model, rates, props, aln = holder_problem(nstates, seed=141 + nstates)
+    unobs = holder_unobserved(aln)
+    kw = dict(nslots=tree.ntaxa, safe_numeric=safe, unobserved=unobs, asc_holder=True)
+    gpu = engine_for(aln, model, rates, props, **kw)
+    cpu = oracle.oracle_engine(aln, model, rates, props, **kw)
+    g, w = holder_eval(gpu, tree), holder_eval(cpu, tree)
+    assert rel(g["lnl"], w["lnl"]) <= 1e-9 and rel(g["pattern_lh"], w["pattern_lh"]) <= 1e-9
+    assert rel(g["df"], w["df"]) <= 1e-9 and rel(g["ddf"], w["ddf"]) <= 1e-9
+    assert rel(g["buf"], w["buf"]) <= 1e-9 and rel(g["derv2"], w["derv2"]) <= 1e-9
