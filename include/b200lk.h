@@ -202,6 +202,44 @@ int b200lk_derv(b200lk_ctx *ctx, double length, double *df, double *ddf);
 /* computeLikelihoodFromBuffer*SIMD (tree/phylokernelnew.h:3196-3392) from theta_all. */
 int b200lk_lnl_from_buffer(b200lk_ctx *ctx, double length, double *lnl);
 
+/* ---- +ASC flavour -------------------------------------------------------- */
+/* Which ascertainment-bias correction the unobserved patterns stand for (model_factory->getASC(), utils/tools.h:549-555).
+ * B200LK_ASC_LEWIS (the default when dims.n_unobserved > 0): the sum of their likelihoods is the probability of an
+ * unobservable constant site (tree/phylokernelnew.h:2620-2628, 3160-3182).  B200LK_ASC_HOLDER (ASC_VARIANT_MISSING):
+ * dims.n_unobserved == nstates * nptn, state-major -- unobserved pattern x*nptn + p is the constant-x column that keeps
+ * the missing entries of observed pattern p (Alignment::getUnobservedConstPatterns, alignment/alignment.cpp:4150-4172) --
+ * and every observed pattern is corrected by its own 1 - sum_x L(x*nptn + p) (:2522-2525, 2580-2619, 3137-3159,
+ * 3349-3368).  Reversible contexts only; b200lk_optimize_branch and batches refuse +ASC as before. */
+#define B200LK_ASC_LEWIS 0
+#define B200LK_ASC_HOLDER 1
+int b200lk_set_asc(b200lk_ctx *ctx, int32_t type);
+
+/* New pattern weights without re-uploading the tips: PhyloTree::computePtnFreq (tree/phylotreesse.cpp:537-547), or the
+ * posterior class weights the heterotachy EM step writes into ptn_freq (tree/phylotreemixlen.cpp:470-474). */
+int b200lk_set_ptn_freq(b200lk_ctx *ctx, const double *ptn_freq /* [nptn] */);
+
+/* ---- heterotachy: mixed branch lengths ------------------------------------------ */
+/* PhyloTreeMixlen (GHOST, +H models): every branch carries one length per rate category, and the kernels read
+ * child->getLength(c % ncat) / dad_branch->getLength(c % ncat) (tree/phylokernelnew.h:1017, 1069, 2325, 2348, 2711,
+ * 2725, 3248, 3263; PhyloNeighborMixlen::getLength, tree/phylonodemixlen.h:64-69).  These are the four kernel calls with
+ * that array in place of the single length, plus the two derivative forms the reference binds for isMixlen() trees.
+ * Reversible, non-site-specific contexts; not available through batches or b200lk_optimize_branch.
+ *   child_len[j*ncat + k]  length of class k on the branch to children[j]  (b200lk_child::length is ignored)
+ *   len[k]                 length of class k on the branch (dad, node) */
+int b200lk_update_partials_mixlen(b200lk_ctx *ctx, const b200lk_node *nodes, int32_t nnodes,
+                                  const b200lk_child *children, int32_t nchildren, const double *child_len);
+int b200lk_branch_lnl_mixlen(b200lk_ctx *ctx, b200lk_end dad, b200lk_end node, const double *len, double *lnl);
+int b200lk_lnl_from_buffer_mixlen(b200lk_ctx *ctx, const double *len, double *lnl);
+/* computeLikelihoodDerv*SIMD with isMixlen() (tree/phylokernelnew.h:2365-2462, 2556-2568): the gradient df[ncat] over
+ * the class lengths, the Hessian ddf[ncat][ncat], and the log-likelihood (the reference returns it in df[ncat]).
+ * ncat <= 8.  +ASC is refused like the reference does (ASSERT(0) at :2449). */
+int b200lk_derv_mixlen(b200lk_ctx *ctx, const double *len, double *df, double *ddf, double *lnl);
+/* computeLikelihoodDervMixlen*SIMD (tree/phylokernelnew.h:3397-3580; computeLikelihoodDervMixlenPointer,
+ * tree/phylotree.h:1339): df, ddf of the EM sub-problem of class cur_mixlen (getCurMixture()) at length `len`, under the
+ * pattern weights currently loaded (b200lk_set_ptn_freq).  Lewis +ASC terms included (:3560-3568).  Like the EM step
+ * itself (tree/phylotreemixlen.cpp:427-428) it requires fused_mix_rate or nmix == 1. */
+int b200lk_derv_mixlen_class(b200lk_ctx *ctx, int32_t cur_mixlen, double len, double *df, double *ddf);
+
 /* Newton-Raphson on one branch, whole iteration on the device: what PhyloTree::optimizeOneBranch asks of
  * Optimization::minimizeNewton (tree/phylotree.cpp:2585-2635, utils/optimization.cpp:422-499) with
  * computeFuncDerv = computeLikelihoodDerv (tree/phylotree.cpp:2520-2527).  Builds theta for branch (dad, node),

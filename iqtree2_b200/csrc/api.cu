@@ -390,3 +390,162 @@ extern "C" int b200lk_evaluate(b200lk_ctx *c, const b200lk_node *nodes, int32_t 
     if (rc) return rc;
     return b200lk_read_results(c, lnl, df, ddf);
 }
+
+// ---- +ASC flavour, pattern weights --------------------------------------------------------------------------------
+extern "C" int b200lk_set_asc(b200lk_ctx *c, int32_t type) {
+    if (!c || (type != B200LK_ASC_LEWIS && type != B200LK_ASC_HOLDER)) return B200LK_ERR_ARG;
+    if (type == B200LK_ASC_HOLDER) {
+        if (c->d.n_unobserved == 0 || c->d.n_unobserved != (int64_t)c->d.nstates * c->d.nptn) {
+            snprintf(c->err, sizeof(c->err), "Holder's +ASC needs n_unobserved == nstates * nptn");
+            return B200LK_ERR_ARG;
+        }
+        if (c->site || c->nonrev) return B200LK_ERR_UNSUPPORTED;
+        CUDA_TRY(c, cudaSetDevice(c->device));
+        if (!c->const_df) {
+            CUDA_TRY(c, cudaMalloc(&c->const_df, sizeof(double) * c->d.n_unobserved));
+            CUDA_TRY(c, cudaMalloc(&c->const_ddf, sizeof(double) * c->d.n_unobserved));
+        }
+    }
+    c->asc_holder = type == B200LK_ASC_HOLDER;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_set_ptn_freq(b200lk_ctx *c, const double *ptn_freq) {
+    if (!c || !ptn_freq) return B200LK_ERR_ARG;
+    if (!c->tips_set) return B200LK_ERR_STATE;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    // nsite stays aln->getNSite(): the EM step of the heterotachy model only re-weights the patterns
+    CUDA_TRY(c, cudaMemcpyAsync(c->ptn_freq, ptn_freq, sizeof(double) * c->d.nptn, cudaMemcpyHostToDevice, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return B200LK_OK;
+}
+
+// ---- heterotachy -----------------------------------------------------------------------------------------------------
+static int check_mixlen(b200lk_ctx *c) {
+    int rc = check_ready(c);
+    if (rc) return rc;
+    if (c->site || c->nonrev || c->batch) {
+        snprintf(c->err, sizeof(c->err), "mixed branch lengths: reversible, non-site-specific contexts only");
+        return B200LK_ERR_UNSUPPORTED;
+    }
+    return B200LK_OK;
+}
+
+// class lengths of the branch of a branch-level call -> device; the launchers read c->cur_branch_mixlen
+static int stage_branch_mixlen(b200lk_ctx *c, const double *len) {
+    if (!c->d_branch_mixlen) CUDA_TRY(c, cudaMalloc(&c->d_branch_mixlen, sizeof(double) * c->d.ncat));
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_branch_mixlen, len, sizeof(double) * c->d.ncat, cudaMemcpyHostToDevice, c->stream));
+    c->cur_branch_mixlen = c->d_branch_mixlen;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_update_partials_mixlen(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes,
+                                             const b200lk_child *children, int32_t nchildren, const double *child_len) {
+    int rc = check_mixlen(c);
+    if (rc) return rc;
+    if (!child_len) return B200LK_ERR_ARG;
+    if (nnodes == 0) return B200LK_OK;
+    if (nchildren < 0 || nchildren > c->children_cap) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (!c->d_child_mixlen)
+        CUDA_TRY(c, cudaMalloc(&c->d_child_mixlen, sizeof(double) * (size_t)c->children_cap * c->d.ncat));
+    // pageable source: the copy is staged before the call returns, so the caller may reuse child_len
+    CUDA_TRY(c, cudaMemcpyAsync(c->d_child_mixlen, child_len, sizeof(double) * (size_t)nchildren * c->d.ncat,
+                                cudaMemcpyHostToDevice, c->stream));
+    c->h_child_mixlen = child_len;
+    rc = enqueue_update(c, nodes, nnodes, children, nchildren);
+    c->h_child_mixlen = nullptr;
+    return rc;
+}
+
+extern "C" int b200lk_branch_lnl_mixlen(b200lk_ctx *c, b200lk_end dad, b200lk_end node, const double *len, double *lnl) {
+    int rc = check_mixlen(c);
+    if (rc) return rc;
+    if (!len || !lnl || check_ends(c, dad, node)) return B200LK_ERR_ARG;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->d.nptn == 0) { *lnl = 0.0; return B200LK_OK; }
+    rc = stage_branch_mixlen(c, len);
+    if (rc) return rc;
+    rc = launch_branch_lnl(c, dad, node, len[0]);
+    c->cur_branch_mixlen = nullptr;
+    if (rc) return rc;
+    return finish_lnl(c, lnl);
+}
+
+extern "C" int b200lk_lnl_from_buffer_mixlen(b200lk_ctx *c, const double *len, double *lnl) {
+    int rc = check_mixlen(c);
+    if (rc) return rc;
+    if (!len || !lnl) return B200LK_ERR_ARG;
+    if (!c->theta_computed) return B200LK_ERR_STATE;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->d.nptn == 0) { *lnl = 0.0; return B200LK_OK; }
+    rc = stage_branch_mixlen(c, len);
+    if (rc) return rc;
+    rc = launch_from_buffer(c, len[0]);
+    c->cur_branch_mixlen = nullptr;
+    if (rc) return rc;
+    return finish_lnl(c, lnl);
+}
+
+extern "C" int b200lk_derv_mixlen(b200lk_ctx *c, const double *len, double *df, double *ddf, double *lnl) {
+    int rc = check_mixlen(c);
+    if (rc) return rc;
+    if (!len || !df || !ddf) return B200LK_ERR_ARG;
+    if (!c->theta_computed) return B200LK_ERR_STATE;
+    const int ncat = c->d.ncat, K = 1 + ncat + ncat * ncat;
+    if (ncat > 8 || c->d.n_unobserved > 0) {  // the reference asserts on +ASC here (tree/phylokernelnew.h:2449)
+        snprintf(c->err, sizeof(c->err), "derv_mixlen: at most 8 classes, no +ASC");
+        return B200LK_ERR_UNSUPPORTED;
+    }
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->d.nptn == 0) {
+        for (int i = 0; i < ncat; i++) df[i] = 0.0;
+        for (int i = 0; i < ncat * ncat; i++) ddf[i] = 0.0;
+        if (lnl) *lnl = 0.0;
+        return B200LK_OK;
+    }
+    if (!c->mix_red) {
+        CUDA_TRY(c, cudaMalloc(&c->mix_red, sizeof(double) * (size_t)(1 + 8 + 64) * c->red_blocks));
+        CUDA_TRY(c, cudaMalloc(&c->mix_result, sizeof(double) * (1 + 8 + 64)));
+    }
+    rc = stage_branch_mixlen(c, len);
+    if (rc) return rc;
+    rc = launch_derv_mixlen(c, K);
+    c->cur_branch_mixlen = nullptr;
+    if (rc) return rc;
+    double out[1 + 8 + 64];
+    CUDA_TRY(c, cudaMemcpyAsync(out, c->mix_result, sizeof(double) * K, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    if (lnl) *lnl = out[0];
+    for (int i = 0; i < ncat; i++) df[i] = out[1 + i];
+    for (int i = 0; i < ncat * ncat; i++) ddf[i] = out[1 + ncat + i];
+    for (int i = 0; i < ncat; i++)
+        if (!isfinite(df[i])) return B200LK_WARN_DERV_NONFINITE;  // ASSERT(isfinite(df[i])) at :2560
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_derv_mixlen_class(b200lk_ctx *c, int32_t cur_mixlen, double len, double *df, double *ddf) {
+    int rc = check_mixlen(c);
+    if (rc) return rc;
+    if (cur_mixlen < 0 || cur_mixlen >= c->d.ncat) return B200LK_ERR_ARG;
+    if (!c->theta_computed) return B200LK_ERR_STATE;
+    if (c->asc_holder || (!c->d.fused_mix_rate && c->d.nmix > 1)) {  // ASSERT(!ASC_Holder) at :3432; EM needs fused rates
+        snprintf(c->err, sizeof(c->err), "derv_mixlen_class: fused_mix_rate or nmix == 1, no Holder +ASC");
+        return B200LK_ERR_UNSUPPORTED;
+    }
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->d.nptn == 0) { if (df) *df = 0; if (ddf) *ddf = 0; return B200LK_OK; }
+    rc = launch_derv_mixlen_class(c, cur_mixlen, len);
+    if (rc) return rc;
+    rc = read_results(c, 1, 2);
+    if (rc) return rc;
+    double a = c->h_result[1], b = c->h_result[2];
+    int warn = 0;
+    if (!isfinite(a)) {  // :3569-3572: warn and zero, in either scaling mode
+        warn = B200LK_WARN_DERV_NONFINITE;
+        a = b = 0.0;
+    }
+    if (df) *df = a;
+    if (ddf) *ddf = b;
+    return warn;
+}

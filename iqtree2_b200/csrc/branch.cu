@@ -35,6 +35,8 @@ struct BranchArgs {
     // and a leaf dad contributes its per-pattern tip vector site_tip[taxon][p][i]
     const double *site_eval, *site_tip, *rates, *props;
     double len;
+    // Holder's +ASC: the unobserved patterns keep their own lh (in pattern_lh), df and ddf (:2522-2525)
+    double *const_df, *const_ddf;
 };
 
 // coefficient of flat element j = c*n + i of pattern p: val0 (which = 0), val1 = cof*val0, val2 = cof*val1
@@ -82,14 +84,14 @@ __device__ __forceinline__ void rebind_branch(BranchArgs &a, const BatchLaunch &
 
 // val0[c][i] = exp(eval*rate*len)*prop*mixw, val1 = cof*val0, val2 = cof*val1 (:2342-2357);
 // tip_val[s][c][i] = val0[c][i] * tip_partial_lh[s][m][i] (:2757-2785)
-__global__ void val_kernel(DevModel m, double len, double *val, double *tip_val, int n, int ncat, int ncm,
-                           int denom, int nmix, int codes, int want_tip, BatchLaunch bl) {
+__global__ void val_kernel(DevModel m, double len_, const double *__restrict__ lens, double *val, double *tip_val,
+                           int n, int ncat, int ncm, int denom, int nmix, int codes, int want_tip, BatchLaunch bl) {
     if (bl.d_ctx) {
         const BatchCtxDev &b = bl.d_ctx[blockIdx.y];
         m = b.m;
         val = b.val;
         tip_val = b.tip_val;
-        len = bl.d_branch_len[blockIdx.y];
+        len_ = bl.d_branch_len[blockIdx.y];
     }
     const int block = n * ncm;
     // every CTA owns a slice of the block (mixtures: block = 4800); tip_val recomputes its val0 entry instead of
@@ -99,6 +101,7 @@ __global__ void val_kernel(DevModel m, double len, double *val, double *tip_val,
         int c = idx / n, i = idx - c * n, mm = c / denom, k = c % ncat;
         double prop = m.props[k] * m.mixw[mm];
         double cof = m.eval[mm * n + i] * m.rates[k];
+        const double len = lens ? lens[k] : len_;  // heterotachy: dad_branch->getLength(mycat), :2325, 2711, 3248
         double v = exp(cof * len) * prop;
         double v1 = cof * v;
         val[idx] = v;
@@ -255,6 +258,11 @@ __global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red
                     lh *= B200_SCALING_THRESHOLD;
                     df *= B200_SCALING_THRESHOLD;
                     ddf *= B200_SCALING_THRESHOLD;
+                }
+                if (a.const_df) {  // Holder: kept per pattern, combined by holder_kernel
+                    a.pattern_lh[p] = lh;
+                    a.const_df[p - a.nptn] = df;
+                    a.const_ddf[p - a.nptn] = ddf;
                 }
                 acc[2] += lh;
                 acc[3] += df;
@@ -611,6 +619,8 @@ static void fill_common(b200lk_ctx *c, BranchArgs &a) {
     a.rates = c->m.rates;
     a.props = c->m.props;
     a.len = 0.0;
+    a.const_df = c->asc_holder ? c->const_df : nullptr;
+    a.const_ddf = c->asc_holder ? c->const_ddf : nullptr;
 }
 
 static BatchLaunch batch_of(const b200lk_ctx *c) {
@@ -629,8 +639,10 @@ static int grid_for(const b200lk_ctx *c, int G, int64_t npat) {
     return (int)(need < c->red_blocks ? need : c->red_blocks);
 }
 
+static int launch_holder_fix(b200lk_ctx *c, int mode);
 static int launch_asc_fix(b200lk_ctx *c, int mode) {
     if (c->d.n_unobserved == 0) return B200LK_OK;
+    if (c->asc_holder) return launch_holder_fix(c, mode);
     const int grid = mode == 1 ? 1 : (int)std::min<int64_t>(c->red_blocks, (c->d.nptn + 255) / 256);
     asc_fix_kernel<<<grid, 256, 0, c->stream>>>(c->d_result, c->pattern_lh, c->d.nptn, c->nsite, mode);
     CUDA_TRY(c, cudaGetLastError());
@@ -641,7 +653,7 @@ static int launch_asc_fix(b200lk_ctx *c, int mode) {
 static int launch_val(b200lk_ctx *c, double length, int want_tip) {
     if (c->site) return B200LK_OK;  // per-pattern coefficients are formed inside the kernels
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
-    val_kernel<<<grid2(c, (c->block + 255) / 256), 256, 0, c->stream>>>(c->m, length, c->val, c->tip_val, c->d.nstates,
+    val_kernel<<<grid2(c, (c->block + 255) / 256), 256, 0, c->stream>>>(c->m, length, c->cur_branch_mixlen, c->val, c->tip_val, c->d.nstates,
                                                                         c->d.ncat, c->ncat_mix, denom, c->d.nmix,
                                                                         c->d.n_state_codes, want_tip, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
@@ -784,4 +796,223 @@ int launch_rell(b200lk_ctx *c) {
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
     return B200LK_OK;
+}
+
+// ---- Holder's +ASC for missing data (ASC_VARIANT_MISSING) ---------------------------------------------------------
+// Unobserved pattern x*nptn + p is the constant-x column with the gaps of observed pattern p; the kernels above left
+// its likelihood in pattern_lh[nptn + ...] (and const_df / const_ddf).  Per observed pattern:
+//   mode 0 (:3137-3159, 3349-3368)  pv = log(1 - sum_x L);  pattern_lh[p] -= pv;  lnL -= sum_p f_p pv
+//   mode 1 (:2580-2619)             df += sum_p f_p df_frac;  ddf += sum_p f_p (ddf_frac + df_frac^2)
+__global__ void __launch_bounds__(RED_THREADS) holder_kernel(double *pattern_lh, const double *const_df,
+                                                            const double *const_ddf, const double *ptn_freq,
+                                                            int64_t nptn, int n, int mode, double *red_partial,
+                                                            int red_blocks) {
+    double acc[2] = {0.0, 0.0};
+    const double *const_lh = pattern_lh + nptn;
+    for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < nptn; p += (int64_t)gridDim.x * RED_THREADS) {
+        double cl = const_lh[p];
+        for (int s = 1; s < n; s++) cl += const_lh[(size_t)s * nptn + p];
+        if (mode == 0) {
+            const double pv = log(1.0 - cl);
+            pattern_lh[p] -= pv;
+            acc[0] += pv * ptn_freq[p];
+        } else {
+            double cd = const_df[p], cdd = const_ddf[p];
+            for (int s = 1; s < n; s++) {
+                cd += const_df[(size_t)s * nptn + p];
+                cdd += const_ddf[(size_t)s * nptn + p];
+            }
+            const double pc = 1.0 - cl, df_frac = cd / pc, ddf_frac = cdd / pc;
+            acc[0] += ptn_freq[p] * df_frac;
+            acc[1] += ptn_freq[p] * (ddf_frac + df_frac * df_frac);
+        }
+    }
+    block_reduce_store<2>(acc, red_partial, red_blocks);
+}
+// result[dst + k] += sign * sum_b red_partial[k][b], fixed order
+__global__ void holder_final_kernel(const double *red_partial, int red_blocks, int K, double *result, int dst,
+                                    double sign) {
+    __shared__ double sh[RED_THREADS];
+    for (int k = 0; k < K; k++) {
+        double v = 0.0;
+        for (int b = threadIdx.x; b < red_blocks; b += RED_THREADS) v += red_partial[(size_t)k * red_blocks + b];
+        sh[threadIdx.x] = v;
+        __syncthreads();
+        for (int s = RED_THREADS / 2; s > 0; s >>= 1) {
+            if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) result[dst + k] += sign * sh[0];
+        __syncthreads();
+    }
+}
+static int launch_holder_fix(b200lk_ctx *c, int mode) {
+    const int grid = grid_for(c, 1, c->d.nptn);
+    holder_kernel<<<grid, RED_THREADS, 0, c->stream>>>(c->pattern_lh, c->const_df, c->const_ddf, c->ptn_freq, c->d.nptn,
+                                                      c->d.nstates, mode, c->red_partial, grid);
+    CUDA_TRY(c, cudaGetLastError());
+    holder_final_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, mode == 0 ? 1 : 2, c->d_result,
+                                                         mode == 0 ? 0 : 1, mode == 0 ? -1.0 : 1.0);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches += 2;
+    return B200LK_OK;
+}
+
+// ---- heterotachy: the two derivative forms of isMixlen() trees -------------------------------------------------------
+#define MIX_MAXCAT 8
+// computeLikelihoodDerv*SIMD with isMixlen() (:2365-2462): per pattern the class sums df_i, ddf_i (i = c % ncat) over
+// the flat block, then  g_i += f df_i/L,  H_ii += f (ddf_i/L - (df_i/L)^2),  H_ik -= f df_i df_k / L^2,
+// lnL += f (log L + buffer_scale).  Sums: [0] lnL, [1 + i] g_i, [1 + ncat + i*ncat + k] H_ik.
+__global__ void __launch_bounds__(RED_THREADS) derv_mixlen_kernel(BranchArgs a, int ncat, double *red, int red_blocks) {
+    const int G = a.G, g = threadIdx.x & (G - 1);
+    const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
+    const int block = a.block, n = a.n;
+    const double *v0 = a.val, *v1 = a.val + block, *v2 = a.val + 2 * block;
+    const int K = 1 + ncat + ncat * ncat;
+    double acc[1 + MIX_MAXCAT + MIX_MAXCAT * MIX_MAXCAT];
+    for (int k = 0; k < K; k++) acc[k] = 0.0;
+    for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.nptn; pb += groups_per_grid) {
+        int64_t p = pb + threadIdx.x / G;
+        const bool valid = p < a.nptn;
+        if (!valid) p = a.nptn - 1;
+        const double *th = a.theta;
+        double lh = 0.0, d1[MIX_MAXCAT], d2[MIX_MAXCAT];
+#pragma unroll
+        for (int k = 0; k < MIX_MAXCAT; k++) d1[k] = d2[k] = 0.0;
+        for (int j = g; j < block; j += G) {
+            const double t = th[E(j)];
+            const int i = (j / n) % ncat;
+            lh = fma(v0[j], t, lh);
+            const double x1 = v1[j] * t, x2 = v2[j] * t;
+#pragma unroll
+            for (int k = 0; k < MIX_MAXCAT; k++) {
+                d1[k] += (k == i) ? x1 : 0.0;
+                d2[k] += (k == i) ? x2 : 0.0;
+            }
+        }
+        lh = group_sum(lh, G);
+#pragma unroll
+        for (int k = 0; k < MIX_MAXCAT; k++) {
+            if (k < ncat) {  // ncat is launch-uniform
+                d1[k] = group_sum(d1[k], G);
+                d2[k] = group_sum(d2[k], G);
+            }
+        }
+        if (g == 0 && valid) {
+            lh = fabs(lh) + a.ptn_invar[p];
+            const double freq = a.ptn_freq[p], inv = 1.0 / lh;
+#pragma unroll
+            for (int i = 0; i < MIX_MAXCAT; i++) {
+                if (i < ncat) {
+                    d1[i] *= inv;
+                    d2[i] *= inv;
+                    acc[1 + i] = fma(d1[i], freq, acc[1 + i]);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < MIX_MAXCAT; i++) {
+                if (i >= ncat) continue;
+#pragma unroll
+                for (int k = 0; k < MIX_MAXCAT; k++) {
+                    if (k >= ncat) continue;
+                    const int idx = 1 + ncat + i * ncat + k;
+                    if (k == i) acc[idx] += fma(-d1[i], d1[i], d2[i]) * freq;
+                    else acc[idx] -= d1[i] * d1[k] * freq;
+                }
+            }
+            acc[0] = fma(log(lh) + a.buffer_scale_all[p], freq, acc[0]);
+        }
+    }
+    __shared__ double sh[RED_THREADS / 32];
+    for (int k = 0; k < K; k++) {
+        double v = acc[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double s = 0.0;
+            for (int w = 0; w < RED_THREADS / 32; w++) s += sh[w];
+            red[(size_t)k * red_blocks + blockIdx.x] = s;
+        }
+        __syncthreads();
+    }
+}
+
+int launch_derv_mixlen(b200lk_ctx *c, int K) {
+    int rc = launch_val(c, 0.0, 0);  // c->cur_branch_mixlen carries the class lengths
+    if (rc) return rc;
+    BranchArgs a;
+    memset(&a, 0, sizeof(a));
+    fill_common(c, a);
+    a.G = pick_group(c->block);
+    const int grid = grid_for(c, a.G, c->d.nptn);
+    derv_mixlen_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, c->d.ncat, c->mix_red, grid);
+    CUDA_TRY(c, cudaGetLastError());
+    BatchLaunch none;
+    memset(&none, 0, sizeof(none));
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->mix_red, grid, K, c->mix_result, 0, K, 0, none);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches += 2;
+    return B200LK_OK;
+}
+
+// computeLikelihoodDervMixlen*SIMD (:3397-3580): only the slice of class `cls` of theta enters, with
+// val[i] = exp(eval[m][i] * len) * mixw[m], m = cls (fused) or 0 -- no rate, no category proportion (:3472-3486).
+// Sums: df, ddf | +ASC (Lewis) prob_const, df_const, ddf_const (not rescaled here, :3536-3540).
+__global__ void __launch_bounds__(RED_THREADS) derv_mixlen_class_kernel(BranchArgs a, DevModel m, int cls, int cur_mix,
+                                                                       double len, int red_blocks) {
+    __shared__ double sv[3][64];
+    const int n = a.n, block = a.block;
+    if (threadIdx.x < n) {
+        const double cof = m.eval[cur_mix * n + threadIdx.x];
+        const double v = exp(cof * len) * m.mixw[cur_mix];
+        sv[0][threadIdx.x] = v;
+        sv[1][threadIdx.x] = cof * v;
+        sv[2][threadIdx.x] = cof * (cof * v);
+    }
+    __syncthreads();
+    double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < a.ntot; p += (int64_t)gridDim.x * RED_THREADS) {
+        const double *th = a.theta;
+        double lh = 0.0, df = 0.0, ddf = 0.0;
+        for (int i = 0; i < n; i++) {
+            const double t = th[E(cls * n + i)];
+            lh = fma(sv[0][i], t, lh);
+            df = fma(sv[1][i], t, df);
+            ddf = fma(sv[2][i], t, ddf);
+        }
+        lh = fabs(lh) + a.ptn_invar[p];
+        if (p < a.nptn) {
+            const double inv = 1.0 / lh, freq = a.ptn_freq[p];
+            df *= inv;
+            ddf *= inv;
+            acc[0] = fma(df, freq, acc[0]);
+            acc[1] += fma(-df, df, ddf) * freq;
+        } else {
+            acc[2] += lh;
+            acc[3] += df;
+            acc[4] += ddf;
+        }
+    }
+    if (a.ntot > a.nptn) block_reduce_store<5>(acc, a.red_partial, red_blocks);
+    else {
+        double acc2[2] = {acc[0], acc[1]};
+        block_reduce_store<2>(acc2, a.red_partial, red_blocks);
+    }
+}
+
+int launch_derv_mixlen_class(b200lk_ctx *c, int cls, double length) {
+    BranchArgs a;
+    memset(&a, 0, sizeof(a));
+    fill_common(c, a);
+    const int grid = grid_for(c, 1, c->ntot);
+    derv_mixlen_class_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, c->m, cls, c->d.fused_mix_rate ? cls : 0, length, grid);
+    CUDA_TRY(c, cudaGetLastError());
+    BatchLaunch none;
+    memset(&none, 0, sizeof(none));
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(c->red_partial, grid, c->d.n_unobserved ? 5 : 2, c->d_result, 1, 2, 8, none);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches += 2;
+    return launch_asc_fix(c, 1);
 }

@@ -139,6 +139,15 @@ struct b200lk_ctx {
     double nsite;          // sum of ptn_freq (aln->getNSite()), for the +ASC correction
     double *d_result;      // [16] lnL, df, ddf, -, optx, d2l, evals, status, prob_const, df_const, ddf_const
     double *h_result;      // pinned
+    // heterotachy (b200lk_*_mixlen, branch.cu): per-class lengths of the call being enqueued
+    const double *h_child_mixlen;     // host [nchildren][ncat]; non-null only inside b200lk_update_partials_mixlen
+    double *d_child_mixlen;           // its device copy [children_cap][ncat]
+    double *d_branch_mixlen;          // device [ncat]: class lengths of the branch of a *_mixlen branch-level call
+    const double *cur_branch_mixlen;  // == d_branch_mixlen while such a call is being enqueued, else null
+    double *mix_red, *mix_result;     // derv_mixlen: [K][red_blocks] partial sums, [K] sums (K = 1 + ncat + ncat^2)
+    // Holder's +ASC (b200lk_set_asc): per-pattern derivative terms of the unobserved patterns
+    bool asc_holder;
+    double *const_df, *const_ddf;  // [n_unobserved]
     bool model_set, tips_set, theta_computed;
     int theta_dad_kind;
     int64_t n_updates, n_launches;
@@ -181,6 +190,8 @@ int launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double len
 int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node);
 int launch_derv(b200lk_ctx *c, double length);
 int launch_from_buffer(b200lk_ctx *c, double length);
+int launch_derv_mixlen(b200lk_ctx *c, int K);
+int launch_derv_mixlen_class(b200lk_ctx *c, int cls, double length);
 int launch_repair(b200lk_ctx *c);
 int launch_newton(b200lk_ctx *c, const b200lk_newton *nr);
 int launch_rell(b200lk_ctx *c);

@@ -192,6 +192,8 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (c->s_tipvec) cudaFree(c->s_tipvec);
     for (double *p : {c->nr_Q, c->nr_ev, c->nr_V, c->nr_Vi, c->nr_freq, c->nr_tipvec, c->nr_T})
         if (p) cudaFree(p);
+    for (double *p : {c->d_child_mixlen, c->d_branch_mixlen, c->mix_red, c->mix_result, c->const_df, c->const_ddf})
+        if (p) cudaFree(p);
     if (c->eig_in) cudaFree(c->eig_in);
     if (c->eig_host) cudaFreeHost(c->eig_host);
     free(c->h_evec);

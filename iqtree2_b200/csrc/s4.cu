@@ -405,10 +405,12 @@ static void fill_model(const b200lk_ctx *c, S4Model<NCM> &m) {
 
 // expv[c][i] = exp(eval[m][i] * rate[c % ncat] * len), the factor of computePartialInfo (:1016-1031)
 template <int NCM>
-static void fill_expv(const b200lk_ctx *c, double len, double *ev) {
+static void fill_expv(const b200lk_ctx *c, const DevChild &ch, double *ev) {
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
+    // heterotachy: one length per category (child->getLength(cat_id[c]), :1017, 1069)
+    const double *lens = c->h_child_mixlen ? c->h_child_mixlen + (size_t)ch.src * c->d.ncat : nullptr;
     for (int cc = 0; cc < NCM; cc++) {
-        const double len_child = c->h_rates[cc % c->d.ncat] * len;
+        const double len_child = c->h_rates[cc % c->d.ncat] * (lens ? lens[cc % c->d.ncat] : ch.length);
         for (int i = 0; i < 4; i++) ev[cc * 4 + i] = exp(c->h_eval[(cc / denom) * 4 + i] * len_child);
     }
 }
@@ -467,7 +469,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
                 kind[k] = SRC_LEAF; id[k] = nseq % chunk; tab[k] = (int)ch.leaf_off;
                 leaf_seq[nseq++] = ch.id;
             } else {
-                fill_expv<NCM>(c, ch.length, k == 0 ? f.lexp : f.rexp);
+                fill_expv<NCM>(c, ch, k == 0 ? f.lexp : f.rexp);
                 (k == 0 ? f.lexp_off : f.rexp_off) = (int32_t)(ch.echild_off + (int64_t)c->block * c->d.nstates);
                 const int pr = producer[ch.id];
                 if (pr >= 0 && consumer[pr] == i && pr == i - 1) {

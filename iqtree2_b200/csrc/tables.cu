@@ -12,7 +12,7 @@
 __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict__ children, DevModel m,
                                                       double *__restrict__ tables, int n, int ncat, int ncm,
                                                       int denom, int nmix, int codes, int frag_nt, int frag_ks,
-                                                      BatchLaunch bl) {
+                                                      const double *__restrict__ mixlen, BatchLaunch bl) {
     DevChild ch = children[blockIdx.x];
     if (bl.d_ctx) {  // batched: context blockIdx.y, its own model, tables and branch lengths
         const BatchCtxDev &b = bl.d_ctx[blockIdx.y];
@@ -26,14 +26,16 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
     for (int idx = threadIdx.x; idx < block * n; idx += blockDim.x) {
         int c = idx / nn, r = idx - c * nn, i = r % n;
         int mm = c / denom;
-        double len_child = m.rates[c % ncat] * ch.length;
+        // heterotachy: child->getLength(cat_id[c]) (:1017, 1069), one length per category
+        double len_child = m.rates[c % ncat] * (mixlen ? mixlen[(size_t)ch.src * ncat + c % ncat] : ch.length);
         echild[idx] = m.evec[(size_t)mm * nn + r] * exp(m.eval[mm * n + i] * len_child);
     }
     // expv[c][i] = exp(eval[m][i] * rate * len): what the 4-state path reads per child (s4.cu)
     double *expv = echild + (size_t)block * n;
     for (int idx = threadIdx.x; idx < block; idx += blockDim.x) {
         int c = idx / n, i = idx - c * n;
-        expv[idx] = exp(m.eval[(c / denom) * n + i] * (m.rates[c % ncat] * ch.length));
+        expv[idx] = exp(m.eval[(c / denom) * n + i] *
+                        (m.rates[c % ncat] * (mixlen ? mixlen[(size_t)ch.src * ncat + c % ncat] : ch.length)));
     }
     if (ch.frag_off >= 0) {
         // tensor paths (dense.cu: 3 n-tiles x 5 k-steps for 20 states; densen.cu: NT x 2NT): echild as the B operand
@@ -77,7 +79,8 @@ int launch_tables(b200lk_ctx *c, int nchildren) {
     if (c->batch) bl = *c->batch;
     tables_kernel<<<dim3(nchildren, c->batch ? c->batch->n : 1), 256, 0, c->stream>>>(
         c->d_children, c->m, c->tables, c->d.nstates, c->d.ncat, c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes,
-        c->dense20 ? 3 : c->dense_nt, c->dense20 ? 5 : 2 * c->dense_nt, bl);
+        c->dense20 ? 3 : c->dense_nt, c->dense20 ? 5 : 2 * c->dense_nt,
+        c->h_child_mixlen ? c->d_child_mixlen : nullptr, bl);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
     return B200LK_OK;

@@ -62,6 +62,7 @@ typedef struct orc_ctx {
     /* Holder's +ASC for missing data (ASC_VARIANT_MISSING): n_unobserved = nstates * nptn patterns, state-major
      * (Alignment::getUnobservedConstPatterns, alignment/alignment.cpp:4150-4172); per-pattern derivative terms */
     int asc_holder;
+    double nsite; /* aln->getNSite(): sum of the pattern frequencies uploaded with the tips */
     double *const_df, *const_ddf; /* [n_unobserved] */
 } orc_ctx;
 
@@ -333,6 +334,8 @@ int orc_upload_tips(orc_ctx *c, const uint8_t *states, const uint8_t *unobserved
         if (nun) memcpy(c->states + (size_t)t * c->ntot + nptn, unobserved + (size_t)t * nun, (size_t)nun);
     }
     memcpy(c->ptn_freq, ptn_freq, (size_t)nptn * sizeof(double));
+    c->nsite = 0.0;
+    for (int64_t p = 0; p < nptn; p++) c->nsite += ptn_freq[p];
     return B200LK_OK;
 }
 
@@ -942,8 +945,7 @@ static int branch_lnl_impl(orc_ctx *c, b200lk_end dad, b200lk_end node, double l
     if (c->asc_holder) { /* :3137-3159 */
         tree_lh -= holder_fix_lnl(c);
     } else if (c->d.n_unobserved > 0) { /* ASC_Lewis, :3160-3182 */
-        double nsite = 0.0;
-        for (int64_t p = 0; p < nptn; p++) nsite += c->ptn_freq[p];
+        double nsite = c->nsite; /* aln->getNSite() */
         prob_const = log(1.0 - prob_const);
         for (int64_t p = 0; p < nptn; p++) c->pattern_lh[p] -= prob_const;
         tree_lh -= nsite * prob_const;
@@ -1129,8 +1131,7 @@ int orc_derv(orc_ctx *c, double length, double *df, double *ddf) {
         *df += sum_df;
         *ddf += sum_ddf;
     } else if (c->d.n_unobserved > 0 && isfinite(*df)) { /* :2620-2628 */
-        double nsite = 0.0;
-        for (int64_t p = 0; p < nptn; p++) nsite += c->ptn_freq[p];
+        double nsite = c->nsite; /* aln->getNSite() */
         prob_const = 1.0 - prob_const;
         double df_frac = df_const / prob_const, ddf_frac = ddf_const / prob_const;
         *df += nsite * df_frac;
@@ -1193,8 +1194,7 @@ static int from_buffer_impl(orc_ctx *c, double length, const double *lens, doubl
     if (c->asc_holder) { /* :3349-3368 */
         tree_lh -= holder_fix_lnl(c);
     } else if (c->d.n_unobserved > 0) { /* :3369-3390 */
-        double nsite = 0.0;
-        for (int64_t p = 0; p < nptn; p++) nsite += c->ptn_freq[p];
+        double nsite = c->nsite; /* aln->getNSite() */
         prob_const = log(1.0 - prob_const);
         for (int64_t p = 0; p < nptn; p++) c->pattern_lh[p] -= prob_const;
         tree_lh -= nsite * prob_const;
@@ -1295,8 +1295,7 @@ int orc_derv_mixlen_class(orc_ctx *c, int32_t cur_mixlen, double len, double *df
     *df = all_df;
     *ddf = all_ddf;
     if (c->d.n_unobserved > 0) { /* :3560-3568 (Lewis) */
-        double nsite = 0.0;
-        for (int64_t p = 0; p < nptn; p++) nsite += c->ptn_freq[p];
+        double nsite = c->nsite; /* aln->getNSite() */
         prob_const = 1.0 / (1.0 - prob_const);
         df_const *= prob_const;
         ddf_const *= prob_const;

@@ -17,6 +17,15 @@ from iqtree2_b200 import workload as W
 from iqtree2_b200.capi import INTERNAL, LEAF, engine_for
 from tests.common import make_problem, rel
 
+@pytest.fixture(autouse=True)
+def _quirks(request):
+    # odd nstates: the reference's dotProductTriple counts the last block entry twice; the oracle reproduces it for the
+    # oracle-vs-reference half, the CUDA path computes the true sums
+    oracle.set_ref_quirks(request.node.get_closest_marker("gpu") is None)
+    yield
+    oracle.set_ref_quirks(True)
+
+
 needs_ref = pytest.mark.skipif(not oracle.ref_available(), reason="oracle/_ref not built (needs /root/reference)")
 
 
