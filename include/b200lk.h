@@ -214,6 +214,14 @@ int b200lk_lnl_from_buffer(b200lk_ctx *ctx, double length, double *lnl);
 #define B200LK_ASC_HOLDER 1
 int b200lk_set_asc(b200lk_ctx *ctx, int32_t type);
 
+/* "Robust phylogeny" scoring of computeLikelihoodBranch (tree/phylokernelnew.h:3096-3135): with keep < 1 (params->
+ * robust_phy_keep) b200lk_branch_lnl returns the sum of the per-site log-likelihoods without the (int)((1-keep)*nsite)
+ * worst sites; with median != 0 (params->robust_median) the median per-site log-likelihood.  keep = 1, median = 0
+ * (the default) is the plain sum.  The reference selects with nth_element over a per-site array on the host; here the
+ * per-pattern values are sorted with their frequencies on the device.  Like the reference: b200lk_lnl_from_buffer is
+ * unaffected, and +ASC contexts refuse it (B200LK_ERR_UNSUPPORTED from b200lk_branch_lnl). */
+int b200lk_set_robust(b200lk_ctx *ctx, double keep, int32_t median);
+
 /* New pattern weights without re-uploading the tips: PhyloTree::computePtnFreq (tree/phylotreesse.cpp:537-547), or the
  * posterior class weights the heterotachy EM step writes into ptn_freq (tree/phylotreemixlen.cpp:470-474). */
 int b200lk_set_ptn_freq(b200lk_ctx *ctx, const double *ptn_freq /* [nptn] */);

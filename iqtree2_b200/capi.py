@@ -209,6 +209,12 @@ class Engine:
         (n_unobserved = nstates * nptn, state-major)."""
         return self._check(self._f("set_asc")(self.ctx, C.c_int32(int(holder))))
 
+    def set_robust(self, keep=1.0, median=False):
+        """params->robust_phy_keep / robust_median for branch_lnl (tree/phylokernelnew.h:3096-3135)."""
+        f = self._f("set_robust")
+        f.argtypes = [C.c_void_p, C.c_double, C.c_int32]
+        return self._check(f(self.ctx, keep, int(median)))
+
     def set_ptn_freq(self, ptn_freq):
         a = np.ascontiguousarray(ptn_freq, dtype=np.float64)
         assert a.size == self.dims.nptn

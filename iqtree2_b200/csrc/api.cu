@@ -212,7 +212,7 @@ static int read_results(b200lk_ctx *c, int first, int count) {
     return B200LK_OK;
 }
 
-static int finish_lnl(b200lk_ctx *c, double *lnl) {
+static int finish_lnl(b200lk_ctx *c, double *lnl, bool from_branch = false) {
     int rc = read_results(c, 0, 1);
     if (rc) return rc;
     int warn = 0;
@@ -220,6 +220,10 @@ static int finish_lnl(b200lk_ctx *c, double *lnl) {
         warn = B200LK_WARN_LNL_NONFINITE;
         rc = launch_repair(c);
         if (rc) return rc;
+        if (from_branch && (c->robust_keep < 1.0 || c->robust_median)) {  // the robust score is taken from the repaired per-pattern values (:3096)
+            rc = launch_robust(c);
+            if (rc) return rc;
+        }
         rc = read_results(c, 0, 1);
         if (rc) return rc;
     }
@@ -259,7 +263,7 @@ extern "C" int b200lk_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node,
     if (c->d.nptn == 0) { *lnl = 0.0; return B200LK_OK; }
     rc = launch_branch_lnl(c, dad, node, length);
     if (rc) return rc;
-    return finish_lnl(c, lnl);
+    return finish_lnl(c, lnl, true);
 }
 
 extern "C" int b200lk_build_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
@@ -363,7 +367,7 @@ extern "C" int b200lk_read_results(b200lk_ctx *c, double *lnl, double *df, doubl
     if (rc) return rc;
     if (lnl) {
         if (!isfinite(c->h_result[0]) && c->d.nptn > 0) {
-            rc = finish_lnl(c, lnl);
+            rc = finish_lnl(c, lnl, true);
             if (rc < 0) return rc;
             warn |= rc;
         } else {
@@ -389,6 +393,15 @@ extern "C" int b200lk_evaluate(b200lk_ctx *c, const b200lk_node *nodes, int32_t 
                                    df != nullptr || ddf != nullptr);
     if (rc) return rc;
     return b200lk_read_results(c, lnl, df, ddf);
+}
+
+// params->robust_phy_keep / robust_median as computeLikelihoodBranch reads them (tree/phylokernelnew.h:3096-3135)
+extern "C" int b200lk_set_robust(b200lk_ctx *c, double keep, int32_t median) {
+    if (!c || !(keep > 0.0) || keep > 1.0) return B200LK_ERR_ARG;
+    if ((keep < 1.0 || median) && (c->nonrev || c->site)) return B200LK_ERR_UNSUPPORTED;
+    c->robust_keep = keep;
+    c->robust_median = median != 0;
+    return B200LK_OK;
 }
 
 // ---- +ASC flavour, pattern weights --------------------------------------------------------------------------------
@@ -469,7 +482,7 @@ extern "C" int b200lk_branch_lnl_mixlen(b200lk_ctx *c, b200lk_end dad, b200lk_en
     rc = launch_branch_lnl(c, dad, node, len[0]);
     c->cur_branch_mixlen = nullptr;
     if (rc) return rc;
-    return finish_lnl(c, lnl);
+    return finish_lnl(c, lnl, true);
 }
 
 extern "C" int b200lk_lnl_from_buffer_mixlen(b200lk_ctx *c, const double *len, double *lnl) {

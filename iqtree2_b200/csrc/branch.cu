@@ -676,6 +676,10 @@ int launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double len
     final_reduce_kernel<<<grid2(c, 1), RED_THREADS, 0, c->stream>>>(c->red_partial, grid, 2, c->d_result, 0, 1, 8, batch_of(c));
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches += 2;
+    if (c->robust_keep < 1.0 || c->robust_median) {  // :3096-3135; "+ASC not supported with robust phylo"
+        if (c->d.n_unobserved > 0 || c->batch) return B200LK_ERR_UNSUPPORTED;
+        return launch_robust(c);
+    }
     return launch_asc_fix(c, 0);
 }
 

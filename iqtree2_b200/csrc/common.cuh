@@ -148,6 +148,12 @@ struct b200lk_ctx {
     // Holder's +ASC (b200lk_set_asc): per-pattern derivative terms of the unobserved patterns
     bool asc_holder;
     double *const_df, *const_ddf;  // [n_unobserved]
+    // robust phylogeny (b200lk_set_robust, robust.cu)
+    double robust_keep;  // params->robust_phy_keep; 1.0 = off
+    bool robust_median;  // params->robust_median
+    double *rob_buf;     // sorted per-pattern lnL, sorted frequencies, their inclusive scan, 2 picks
+    void *rob_temp;
+    size_t rob_temp_bytes;
     bool model_set, tips_set, theta_computed;
     int theta_dad_kind;
     int64_t n_updates, n_launches;
@@ -193,6 +199,7 @@ int launch_from_buffer(b200lk_ctx *c, double length);
 int launch_derv_mixlen(b200lk_ctx *c, int K);
 int launch_derv_mixlen_class(b200lk_ctx *c, int cls, double length);
 int launch_repair(b200lk_ctx *c);
+int launch_robust(b200lk_ctx *c);  // robust.cu: replaces result[0] by the robust score of the per-pattern lnL
 int launch_newton(b200lk_ctx *c, const b200lk_newton *nr);
 int launch_rell(b200lk_ctx *c);
 int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used);

@@ -109,6 +109,7 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
     b200lk_ctx *c = new b200lk_ctx();
     memset(c, 0, sizeof(*c));
     c->d = *dims;
+    c->robust_keep = 1.0;
     c->device = dims->device;
     c->ncat_mix = dims->fused_mix_rate ? dims->ncat : dims->ncat * dims->nmix;  // tree/phylokernelnew.h:1323
     c->block = dims->nstates * c->ncat_mix;
@@ -194,6 +195,8 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
         if (p) cudaFree(p);
     for (double *p : {c->d_child_mixlen, c->d_branch_mixlen, c->mix_red, c->mix_result, c->const_df, c->const_ddf})
         if (p) cudaFree(p);
+    if (c->rob_buf) cudaFree(c->rob_buf);
+    if (c->rob_temp) cudaFree(c->rob_temp);
     if (c->eig_in) cudaFree(c->eig_in);
     if (c->eig_host) cudaFreeHost(c->eig_host);
     free(c->h_evec);

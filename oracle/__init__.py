@@ -50,7 +50,8 @@ class RefRun:
     (ref_harness.cpp).  kernel: LK_SSE2 (Vec2d), LK_AVX (Vec4d), LK_AVX_FMA (Vec4d + FMA)."""
 
     def __init__(self, tree, aln, model, rates, props, *, kernel=LK_AVX_FMA, safe=False, threads=1, p_invar=0.0,
-                 unobserved=None, fused=False, site_models=None, nonrev=None, mixlen=None, asc_holder=False):
+                 unobserved=None, fused=False, site_models=None, nonrev=None, mixlen=None, asc_holder=False,
+                 robust=None):
         import ctypes as C
         import numpy as np
         from iqtree2_b200 import workload as W
@@ -101,6 +102,8 @@ class RefRun:
         if mixlen is not None:  # heterotachy: class c of every branch has length (newick length) * mixlen[c]
             mm = f64(mixlen)
             self.lib.ref_set_next_mixlen(len(mm), C.c_void_p(mm.ctypes.data))
+        if robust is not None:  # (keep, median): params->robust_phy_keep / robust_median
+            self.lib.ref_set_next_robust(C.c_double(robust[0]), int(robust[1]))
         if asc_holder:  # the unobserved patterns are Holder's (ASC_VARIANT_MISSING)
             self.lib.ref_set_next_asc_holder(1)
         if fused:  # model_factory->fused_mix_rate: category c = mixture class c at rate category c

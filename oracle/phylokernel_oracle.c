@@ -62,6 +62,8 @@ typedef struct orc_ctx {
     /* Holder's +ASC for missing data (ASC_VARIANT_MISSING): n_unobserved = nstates * nptn patterns, state-major
      * (Alignment::getUnobservedConstPatterns, alignment/alignment.cpp:4150-4172); per-pattern derivative terms */
     int asc_holder;
+    double robust_keep; /* params->robust_phy_keep (1.0 = off) */
+    int robust_median;  /* params->robust_median */
     double nsite; /* aln->getNSite(): sum of the pattern frequencies uploaded with the tips */
     double *const_df, *const_ddf; /* [n_unobserved] */
 } orc_ctx;
@@ -292,6 +294,7 @@ int orc_create(orc_ctx **out, const b200lk_dims *dims) {
     c->buffer_scale_all = (double *)calloc(ntot + 1, sizeof(double));
     c->pattern_lh = (double *)calloc(ntot + 1, sizeof(double));
     c->pattern_lh_cat = (double *)calloc(ntot * c->ncat_mix + 1, sizeof(double));
+    c->robust_keep = 1.0;
     *out = c;
     return B200LK_OK;
 }
@@ -831,6 +834,19 @@ static double holder_fix_lnl(orc_ctx *c) {
     return sum_corr;
 }
 
+static int cmp_double(const void *a, const void *b) {
+    double x = *(const double *)a, y = *(const double *)b;
+    return (x > y) - (x < y);
+}
+/* params->robust_phy_keep (fraction of best sites summed; 1.0 = off) and params->robust_median: read by
+ * computeLikelihoodBranch only (tree/phylokernelnew.h:3096-3135) */
+int orc_set_robust(orc_ctx *c, double keep, int32_t median) {
+    if (!(keep > 0.0) || keep > 1.0) return B200LK_ERR_ARG;
+    c->robust_keep = keep;
+    c->robust_median = median != 0;
+    return B200LK_OK;
+}
+
 static int branch_lnl_impl(orc_ctx *c, b200lk_end dad, b200lk_end node, double length, const double *lens,
                            double *lnl) {
     if (c->d.site_specific == B200LK_MODEL_NONREV)
@@ -941,6 +957,24 @@ static int branch_lnl_impl(orc_ctx *c, b200lk_end dad, b200lk_end node, double l
             if (!isfinite(c->pattern_lh[p])) c->pattern_lh[p] = LOG_SCALING_THRESHOLD * 4;
             tree_lh += c->pattern_lh[p] * c->ptn_freq[p];
         }
+    }
+    if (c->robust_keep < 1.0 || c->robust_median) { /* :3096-3135: robust phylogeny, the best sites only / the median */
+        if (c->d.n_unobserved > 0) return B200LK_ERR_UNSUPPORTED; /* outError("+ASC not supported with robust phylo") */
+        size_t sites = (size_t)c->nsite, site = 0;
+        double *site_lh = (double *)malloc(sizeof(double) * (sites + 1));
+        for (int64_t p = 0; p < nptn; p++)
+            for (int64_t i = 0; i < (int64_t)c->ptn_freq[p]; i++) site_lh[site++] = c->pattern_lh[p];
+        qsort(site_lh, sites, sizeof(double), cmp_double);
+        if (c->robust_keep < 1.0) {
+            size_t sites_drop = (size_t)(int)((1.0 - c->robust_keep) * sites);
+            tree_lh = 0.0;
+            for (size_t i = sites_drop; i < sites; i++) tree_lh += site_lh[i];
+        } else if (sites & 1) {
+            tree_lh = site_lh[sites / 2];
+        } else {
+            tree_lh = 0.5 * (site_lh[sites / 2] + site_lh[sites / 2 - 1]);
+        }
+        free(site_lh);
     }
     if (c->asc_holder) { /* :3137-3159 */
         tree_lh -= holder_fix_lnl(c);

@@ -292,6 +292,12 @@ static void set_mix_lengths(Node *node, Node *dad, const std::vector<double> &mu
     }
 }
 
+// robust phylogeny (tree/phylokernelnew.h:3096-3135) for the NEXT ref_create: params->robust_phy_keep / robust_median.
+// Params is the reference's process-wide singleton, so every ref_create sets both (default: off).
+static double next_robust_keep = 1.0;
+static int next_robust_median = 0;
+void ref_set_next_robust(double keep, int median) { next_robust_keep = keep; next_robust_median = median; }
+
 static int next_fused = 0;
 void ref_set_next_fused(int fused) { next_fused = fused; }
 
@@ -336,6 +342,10 @@ void *ref_create(const ref_problem *pb) {
     }
     Params &params = Params::getInstance();
     params.lk_safe_scaling = pb->safe != 0;
+    params.robust_phy_keep = next_robust_keep;
+    params.robust_median = next_robust_median != 0;
+    next_robust_keep = 1.0;
+    next_robust_median = 0;
     RefHandle *h = new RefHandle();
     const int n = pb->nstates;
     // alignment: pattern-major vector<Pattern>, aln->at(ptn)[taxon] (alignment/pattern.h:29)

@@ -254,3 +254,43 @@ def test_cuda_holder_asc_matches_oracle(nstates, safe):
     assert rel(g["lnl"], w["lnl"]) <= 1e-9 and rel(g["pattern_lh"], w["pattern_lh"]) <= 1e-9
     assert rel(g["df"], w["df"]) <= 1e-9 and rel(g["ddf"], w["ddf"]) <= 1e-9
     assert rel(g["buf"], w["buf"]) <= 1e-9 and rel(g["derv2"], w["derv2"]) <= 1e-9
+
+
+# --------------------------------------------------------------------------------------------- robust phylogeny
+def robust_eval(eng, tree, keep, median, leaf=0):
+    c = tree.adj[leaf][0]
+    tr = W.traversal(tree, c, leaf)
+    eng.update_partials(tr)
+    eng.set_robust(keep, median)
+    dad, node = (LEAF, leaf), (INTERNAL, tr[-1][2])
+    lnl = eng.branch_lnl(dad, node, tree.get_length(leaf, c))
+    eng.set_robust(1.0, False)
+    return lnl, eng.branch_lnl(dad, node, tree.get_length(leaf, c))
+
+
+@needs_ref
+@pytest.mark.parametrize("keep,median", [(0.9, False), (0.5, False), (0.999, False), (1.0, True)])
+@pytest.mark.parametrize("nsite", [150, 151])
+def test_oracle_robust_phylo_matches_reference(keep, median, nsite):
+    """tree/phylokernelnew.h:3096-3135: sum over the best sites / median site (odd and even site counts)."""
+    tree, model, rates, props, aln = make_problem(9, nsite, nstates=4, seed=61)
+    ref = oracle.RefRun(tree, aln, model, rates, props, kernel=oracle.LK_AVX_FMA, robust=(keep, median))
+    eng = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa)
+    got, plain = robust_eval(eng, tree, keep, median)
+    want = ref.lnl_at_leaf(0)
+    assert abs(got - want) <= 1e-11 * abs(want)
+    if keep < 0.999 or median:
+        assert abs(plain - want) > 1e-3
+    ref.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("keep,median", [(0.9, False), (0.37, False), (1.0, True)])
+@pytest.mark.parametrize("nstates,nsite", [(4, 3001), (20, 800)])
+def test_cuda_robust_phylo_matches_oracle(keep, median, nstates, nsite):
+    tree, model, rates, props, aln = make_problem(12, nsite, nstates=nstates, seed=71)
+    gpu = engine_for(aln, model, rates, props, nslots=tree.ntaxa)
+    cpu = oracle.oracle_engine(aln, model, rates, props, nslots=tree.ntaxa)
+    g, w = robust_eval(gpu, tree, keep, median), robust_eval(cpu, tree, keep, median)
+    assert rel(g[0], w[0]) <= 1e-9 and rel(g[1], w[1]) <= 1e-9
+    assert abs(w[0] - w[1]) > 1e-3
