@@ -158,16 +158,26 @@ class HostTree:
     """b200::PhyloTree set up in the reference's order (readTree, setAlignment, setModel, setLikelihoodKernel
     (LK_CUDA), initializeAllPartialLh)."""
 
-    def __init__(self, newick, aln, model, rate, safe=False, device=0, device_newton=True, asc=False, mem_save=None):
+    def __init__(self, newick, aln, model, rate, safe=False, device=0, device_newton=True, asc=False, mem_save=None,
+                 asc_holder=False, robust=None, mixlen=None):
         """mem_save: None = one slot per internal node; a number = -mem (LM_MEM_SAVE) with that Params::max_mem_size
-        (0: the minimum log2(ntaxa)+1 slots; <= 1: that fraction of ntaxa-2)."""
+        (0: the minimum log2(ntaxa)+1 slots; <= 1: that fraction of ntaxa-2).  asc_holder: +ASC with missing data.
+        robust: (keep, median) = Params::robust_phy_keep / robust_median.  mixlen: class multipliers -> a
+        b200::PhyloTreeMixlen (heterotachy) whose class c of every branch starts at length x mixlen[c]."""
         self.h = C.c_void_p()
         self._keep = (aln, model, rate)
         if mem_save is not None:
             lib().b200host_set_mem_fraction(C.c_double(float(mem_save)))
+        if robust is not None:
+            lib().b200host_set_robust(C.c_double(float(robust[0])), int(bool(robust[1])))
+        self.mixlen = 0
+        if mixlen is not None:
+            mm = np.ascontiguousarray(mixlen, dtype=np.float64)
+            lib().b200host_set_next_mixlen(_dp(mm), len(mm))
+            self.mixlen = len(mm)
         _ck(lib().b200host_tree_new(C.byref(self.h), newick.encode(), aln.h, model.h, rate.h,
-                                    int(bool(safe)) | (2 if asc else 0) | (4 if mem_save is not None else 0), device,
-                                    int(device_newton)))
+                                    int(bool(safe)) | (2 if asc else 0) | (4 if mem_save is not None else 0) |
+                                    (8 if asc_holder else 0), device, int(device_newton)))
         self.aln = aln
 
     def close(self):
@@ -215,6 +225,26 @@ class HostTree:
         out = C.c_double()
         _ck(lib().b200host_tree_optimize_one_branch(self.h, bid, max_steps, C.byref(out)))
         return out.value
+
+    def pattern_lh_cat(self, wsl=2):
+        """computePatternLhCat(wsl): -> (lnL, [nptn][columns]); wsl 2 = WSL_RATECAT, 3 = WSL_MIXTURE, 4 = both."""
+        ncols, lnl = C.c_int32(), C.c_double()
+        _ck(lib().b200host_tree_pattern_lh_cat(self.h, wsl, None, C.byref(ncols), C.byref(lnl)))
+        out = np.empty((self.aln.nptn, ncols.value))
+        _ck(lib().b200host_tree_pattern_lh_cat(self.h, wsl, _dp(out), C.byref(ncols), C.byref(lnl)))
+        return lnl.value, out
+
+    def derv_multi(self, bid, lens):
+        """heterotachy: gradient [mixlen], Hessian [mixlen][mixlen] and lnL at class lengths `lens` of branch bid."""
+        a = np.ascontiguousarray(lens, dtype=np.float64)
+        df, ddf, lnl = np.zeros(self.mixlen), np.zeros((self.mixlen, self.mixlen)), C.c_double()
+        _ck(lib().b200host_tree_derv_multi(self.h, bid, _dp(a), _dp(df), _dp(ddf), C.byref(lnl)))
+        return df, ddf, lnl.value
+
+    def mix_lengths(self):
+        v = np.empty((self.nbranches, self.mixlen))
+        lib().b200host_tree_get_mix_lengths(self.h, _dp(v))
+        return v
 
     def from_buffer(self):
         out = C.c_double()

@@ -26,6 +26,8 @@ namespace b200 {
 // utils/tools.h:526-528, with LK_CUDA appended (keeps `>=` comparisons such as get_safe_upper_limit meaningful)
 enum LikelihoodKernel { LK_386, LK_SSE, LK_SSE2, LK_AVX, LK_AVX_FMA, LK_AVX512, LK_CUDA };
 enum SeqType { SEQ_DNA, SEQ_PROTEIN, SEQ_MORPH };
+enum SiteLoglType { WSL_NONE, WSL_SITE, WSL_RATECAT, WSL_MIXTURE, WSL_MIXTURE_RATECAT };  // utils/tools.h:534-536
+enum ASCType { ASC_NONE, ASC_VARIANT, ASC_VARIANT_MISSING };                               // utils/tools.h:549-555
 
 const double TOL_BRANCH_LEN = 0.000001;  // tree/phylotree.h:64
 const double TOL_LIKELIHOOD = 0.001;     // tree/phylotree.h:65
@@ -59,6 +61,16 @@ struct KernelABI {
     int (*fetch_scale_num)(b200lk_ctx *, int32_t, uint8_t *);
     int (*optimize_branch)(b200lk_ctx *, b200lk_end, b200lk_end, const b200lk_newton *, double *, double *,
                            int32_t *);                                    // optional
+    // optional: +ASC flavour, robust scoring, pattern weights, heterotachy (NULL when the library has none)
+    int (*set_asc)(b200lk_ctx *, int32_t);
+    int (*set_robust)(b200lk_ctx *, double, int32_t);
+    int (*set_ptn_freq)(b200lk_ctx *, const double *);
+    int (*update_partials_mixlen)(b200lk_ctx *, const b200lk_node *, int32_t, const b200lk_child *, int32_t,
+                                  const double *);
+    int (*branch_lnl_mixlen)(b200lk_ctx *, b200lk_end, b200lk_end, const double *, double *);
+    int (*lnl_from_buffer_mixlen)(b200lk_ctx *, const double *, double *);
+    int (*derv_mixlen)(b200lk_ctx *, const double *, double *, double *, double *);
+    int (*derv_mixlen_class)(b200lk_ctx *, int32_t, double, double *, double *);
     const char *(*last_error)(const b200lk_ctx *);                        // optional
     int (*get_counters)(b200lk_ctx *, int64_t *, int64_t *);              // optional
     // batched launches over the partitions of a supermatrix (optional; NULL when the library has none)
@@ -171,8 +183,15 @@ public:
     int slot = -1;          // device slot holding the partial of the subtree at `node` seen from the owner; -1 none
                             // == (partial_lh - central_partial_lh) / block_size in the reference
     int size = 0;           // leaves in the subtree at `node` (computeSizes)
+    // heterotachy (PhyloNeighborMixlen, tree/phylonodemixlen.h:20-140): one length per class; `length` is their mean
+    std::vector<double> lengths;
     PhyloNeighbor(PhyloNode *n, double len, int bid) : node(n), length(len), id(bid) {}
     void clearPartialLh() { partial_lh_computed = 0; }
+    double getLength(int c) const { return lengths.empty() ? length : lengths[c]; }
+    void setLength(int c, double len) {
+        if (lengths.empty()) length = len;
+        else lengths[c] = len;
+    }
 };
 class PhyloNode {
 public:
@@ -204,7 +223,10 @@ struct Params {  // the few fields of utils/tools.h Params the path reads
     double min_branch_length = 1e-6;  // utils/tools.cpp:1209, main/phyloanalysis.cpp:4171-4175
     double max_branch_length = 10.0;  // utils/tools.cpp:1212
     bool lk_safe_scaling = false;     // -safe
-    bool asc_lewis = false;           // +ASC: Lewis' correction for variable-sites-only data
+    bool asc_lewis = false;           // +ASC: Lewis' correction for variable-sites-only data (ASC_VARIANT)
+    bool asc_holder = false;          // +ASC with missing data: Holder's correction (ASC_VARIANT_MISSING)
+    double robust_phy_keep = 1.0;     // --robust-phy: fraction of best sites summed (utils/tools.cpp:1294)
+    bool robust_median = false;       // --robust-median (utils/tools.cpp:1295)
     int numseq_safe_scaling = 2000;   // utils/tools.cpp:1235-1236
     int device = 0;
     bool device_newton = true;        // run minimizeNewton's iteration on the device when the library offers it
@@ -243,6 +265,7 @@ public:
     typedef double (PhyloTree::*ComputeLikelihoodBranchType)(PhyloNeighbor *, PhyloNode *);
     typedef void (PhyloTree::*ComputeLikelihoodDervType)(PhyloNeighbor *, PhyloNode *, double *, double *);
     typedef double (PhyloTree::*ComputeLikelihoodFromBufferType)();
+    typedef void (PhyloTree::*ComputeLikelihoodDervMixlenType)(PhyloNeighbor *, PhyloNode *, double &, double &);
 
     PhyloTree();
     virtual ~PhyloTree();
@@ -273,9 +296,16 @@ public:
     // -- callers of the dispatch API that the parity tests exercise
     virtual double computeLikelihood(double *pattern_lh = NULL);             // tree/phylotree.cpp:1227-1268
     void computePatternLikelihood(double *pattern_lh, double *cur_logl = NULL, double *pattern_lh_cat = NULL);
+    // tree/phylotree.cpp:1330-1388: lnL at the root branch; _pattern_lh_cat then holds the per-pattern likelihood of
+    // every category, folded per mixture class (WSL_MIXTURE) or per rate category (WSL_RATECAT) for unfused mixtures
+    double computePatternLhCat(SiteLoglType wsl);
     double computeFunction(double value);                                    // tree/phylotree.cpp:2505-2518
-    void computeFuncDerv(double value, double &df, double &ddf);             // tree/phylotree.cpp:2520-2527
-    void optimizeOneBranch(PhyloNode *node1, PhyloNode *node2, bool clearLH = true, int maxNRStep = 100);
+    virtual void computeFuncDerv(double value, double &df, double &ddf);     // tree/phylotree.cpp:2520-2527
+    virtual void optimizeOneBranch(PhyloNode *node1, PhyloNode *node2, bool clearLH = true, int maxNRStep = 100);
+    // heterotachy hooks (tree/phylotree.h:546, 556, 1306)
+    virtual bool isMixlen() const { return false; }
+    virtual int getMixlen() const { return 1; }
+    virtual int getCurMixture() const { return 0; }
     virtual double optimizeAllBranches(int my_iterations = 100, double tolerance = TOL_LIKELIHOOD, int maxNRStep = 100);
     virtual void clearAllPartialLH();
     // utils/optimization.cpp:422-499
@@ -323,6 +353,10 @@ protected:
     ComputeLikelihoodBranchType computeLikelihoodBranchPointer = NULL;
     ComputeLikelihoodDervType computeLikelihoodDervPointer = NULL;
     ComputeLikelihoodFromBufferType computeLikelihoodFromBufferPointer = NULL;
+    ComputeLikelihoodDervMixlenType computeLikelihoodDervMixlenPointer = NULL;  // tree/phylotree.h:1339
+    void computeLikelihoodDervMixlenCUDA(PhyloNeighbor *dad_branch, PhyloNode *dad, double &df, double &ddf);
+    void ensureTheta(PhyloNeighbor *dad_branch, PhyloNode *dad);
+    void branchLengths(const PhyloNeighbor *nb, std::vector<double> &out) const;  // [ncat] class lengths of a branch
     void setLikelihoodKernelCUDA();
     // the LK_CUDA members bound by setLikelihoodKernelCUDA
     void computePartialLikelihoodCUDA(TraversalInfo &info, size_t ptn_lower, size_t ptn_upper, int packet_id);
@@ -343,6 +377,26 @@ protected:
     bool buffers_ready = false;
     std::map<int, int> leaf_row;  // leaf node id -> alignment row
     friend class PhyloSuperTree;
+};
+
+// ---- heterotachy (tree/phylotreemixlen.h, tree/phylotreemixlen.cpp) ---------------------------------------
+// A tree whose branches carry one length per rate category of a RateHeterotachy-like rate model (all rates 1, class
+// weights as proportions): the dispatch members send per-class lengths through the *_mixlen entry points of the C ABI,
+// computeLikelihoodDerv returns the gradient / Hessian / lnL form, and optimizeOneBranch runs the reference's EM step.
+class PhyloTreeMixlen : public PhyloTree {
+public:
+    int mixlen = 1;
+    int cur_mixture = -1;
+    void setMixlen(int m) { mixlen = m; }
+    bool isMixlen() const override { return true; }
+    int getMixlen() const override { return mixlen; }
+    int getCurMixture() const override { return cur_mixture; }
+    // class c of every branch = its current length x mult[c] (the relative class rates initializeMixBranches
+    // starts from, tree/phylotreemixlen.cpp:137-190)
+    void initializeMixBranches(const std::vector<double> &mult);
+    void computeFuncDerv(double value, double &df, double &ddf) override;         // :728-737
+    void computeFuncDervMulti(const double *value, double *df, double *ddf);       // :544-559
+    void optimizeOneBranch(PhyloNode *node1, PhyloNode *node2, bool clearLH = true, int maxNRStep = 100) override;  // EM, :425-495
 };
 
 // ---- partitions (tree/phylosupertree.cpp, tree/phylosupertreeplen.cpp) -----------------------------------

@@ -50,6 +50,7 @@ void PhyloTree::setLikelihoodKernelCUDA() {
     computeLikelihoodBranchPointer = &PhyloTree::computeLikelihoodBranchCUDA;
     computeLikelihoodDervPointer = &PhyloTree::computeLikelihoodDervCUDA;
     computeLikelihoodFromBufferPointer = &PhyloTree::computeLikelihoodFromBufferCUDA;
+    computeLikelihoodDervMixlenPointer = &PhyloTree::computeLikelihoodDervMixlenCUDA;
 }
 
 // tree/phylotreesse.cpp:212-236
@@ -127,8 +128,12 @@ void PhyloTree::initializeAllPartialLh() {
     d.nptn = (int64_t)aln->getNPattern();
     // +ASC (Lewis): the nstates constant patterns are the unobserved ones (ModelFactory, model/modelfactory.cpp:
     // "unobserved_ptns" built by Alignment::getUnobservedConstPatterns for ASC_VARIANT)
-    const bool asc = params && params->asc_lewis;
-    d.n_unobserved = asc ? aln->num_states : 0;
+    // +ASC with missing data (Holder, ASC_VARIANT_MISSING): for every state x and observed pattern p the constant-x
+    // column that keeps p's missing entries (Alignment::getUnobservedConstPatterns, alignment/alignment.cpp:4150-4172)
+    const bool holder = params && params->asc_holder;
+    const bool asc = params && (params->asc_lewis || holder);
+    if (holder && !k.set_asc) outError("the kernel library has no Holder +ASC (b200lk_set_asc)");
+    d.n_unobserved = holder ? (int64_t)aln->num_states * (int64_t)aln->getNPattern() : (asc ? aln->num_states : 0);
     d.device = params ? params->device : 0;
     int rc = k.create(&ctx, &d);
     if (rc != B200LK_OK || !ctx) {
@@ -139,13 +144,28 @@ void PhyloTree::initializeAllPartialLh() {
     kernel_calls++;
     // tip states in alignment-row order == taxon id used in traversal descriptors
     std::vector<uint8_t> unobs;
-    if (asc) {
+    if (holder) {
+        const size_t np = aln->getNPattern(), nu = (size_t)d.n_unobserved;
+        unobs.resize((size_t)leafNum * nu);
+        for (int t = 0; t < leafNum; t++)
+            for (int x = 0; x < aln->num_states; x++)
+                for (size_t p = 0; p < np; p++)
+                    unobs[(size_t)t * nu + (size_t)x * np + p] =
+                        aln->states[(size_t)t * np + p] < aln->num_states ? (uint8_t)x : (uint8_t)aln->STATE_UNKNOWN;
+    } else if (asc) {
         unobs.resize((size_t)leafNum * aln->num_states);
         for (int t = 0; t < leafNum; t++)
             for (int x = 0; x < aln->num_states; x++) unobs[(size_t)t * aln->num_states + x] = (uint8_t)x;
     }
     check(k.upload_tips(ctx, aln->states.data(), asc ? unobs.data() : NULL, aln->ptn_freq.data()), "b200lk_upload_tips");
     kernel_calls++;
+    if (holder) check(k.set_asc(ctx, B200LK_ASC_HOLDER), "b200lk_set_asc");
+    if (params && (params->robust_phy_keep < 1.0 || params->robust_median)) {  // tree/phylokernelnew.h:3096-3135
+        if (!k.set_robust) outError("the kernel library has no robust-phylogeny scoring (b200lk_set_robust)");
+        check(k.set_robust(ctx, params->robust_phy_keep, params->robust_median ? 1 : 0), "b200lk_set_robust");
+    }
+    if (isMixlen() && (!k.update_partials_mixlen || !k.branch_lnl_mixlen || !k.derv_mixlen))
+        outError("the kernel library has no mixed-branch-length entry points (b200lk_*_mixlen)");
     model_changed = true;
     buffers_ready = true;
     _pattern_lh.assign(aln->getNPattern(), 0.0);
@@ -176,7 +196,7 @@ void PhyloTree::syncModel() {
           "b200lk_set_model");
     // ptn_invar
     const size_t nptn = aln->getNPattern();
-    const size_t nunobs = (params && params->asc_lewis) ? (size_t)n : 0;
+    const size_t nunobs = (params && params->asc_holder) ? (size_t)n * nptn : ((params && params->asc_lewis) ? (size_t)n : 0);
     const double p_invar = site_rate->getPInvar();
     // entries of the unobserved (+ASC) patterns are the reference's "dummy values" p_invar (:607-609)
     std::vector<double> inv(nptn + nunobs, p_invar), fr(n);
@@ -373,6 +393,18 @@ void PhyloTree::flushTraversal() {
     std::vector<b200lk_node> nodes;
     std::vector<b200lk_child> children;
     packTraversal(nodes, children);
+    if (isMixlen()) {  // child->getLength(c), tree/phylokernelnew.h:1017, 1069
+        const int m = getMixlen();
+        std::vector<double> child_len;
+        child_len.reserve(children.size() * m);
+        for (const TraversalInfo &info : traversal_info)
+            for (PhyloNeighbor *nb : info.dad_branch->node->neighbors)
+                if (nb->node != info.dad)
+                    for (int c = 0; c < m; c++) child_len.push_back(nb->getLength(c));
+        check(kernelABI().update_partials_mixlen(ctx, nodes.data(), (int32_t)nodes.size(), children.data(),
+                                                 (int32_t)children.size(), child_len.data()),
+              "b200lk_update_partials_mixlen");
+    } else
     check(kernelABI().update_partials(ctx, nodes.data(), (int32_t)nodes.size(), children.data(), (int32_t)children.size()),
           "b200lk_update_partials");
     kernel_calls++;
@@ -421,31 +453,69 @@ double PhyloTree::computeLikelihoodBranchCUDA(PhyloNeighbor *dad_branch, PhyloNo
     b200lk_end de, ne;
     branchEnds(dad_branch, dad, de, ne);
     double lnl = 0.0;
+    if (isMixlen()) {  // dad_branch->getLength(mycat), :2711, 2725
+        std::vector<double> lens;
+        branchLengths(dad_branch, lens);
+        check(kernelABI().branch_lnl_mixlen(ctx, de, ne, lens.data(), &lnl), "b200lk_branch_lnl_mixlen");
+    } else
     check(kernelABI().branch_lnl(ctx, de, ne, dad_branch->length, &lnl), "b200lk_branch_lnl");
     kernel_calls++;
     return lnl;
 }
 
+void PhyloTree::branchLengths(const PhyloNeighbor *nb, std::vector<double> &out) const {
+    const int m = site_rate->getNRate();
+    out.resize(m);
+    for (int c = 0; c < m; c++) out[c] = nb->getLength(c);
+}
+
+void PhyloTree::ensureTheta(PhyloNeighbor *dad_branch, PhyloNode *dad) {
+    if (theta_computed) return;  // tree/phylokernelnew.h:2263-2266, 2554
+    PhyloNode *node = dad_branch->node;
+    computeTraversalInfo(node, dad);
+    flushTraversal();
+    b200lk_end de, ne;
+    branchEnds(dad_branch, dad, de, ne);
+    check(kernelABI().build_theta(ctx, de, ne), "b200lk_build_theta");
+    kernel_calls++;
+    theta_computed = true;
+}
+
 void PhyloTree::computeLikelihoodDervCUDA(PhyloNeighbor *dad_branch, PhyloNode *dad, double *df, double *ddf) {
     syncModel();
     const KernelABI &k = kernelABI();
-    if (!theta_computed) {  // tree/phylokernelnew.h:2263-2266, 2554
-        PhyloNode *node = dad_branch->node;
-        computeTraversalInfo(node, dad);
-        flushTraversal();
-        b200lk_end de, ne;
-        branchEnds(dad_branch, dad, de, ne);
-        check(k.build_theta(ctx, de, ne), "b200lk_build_theta");
-        kernel_calls++;
-        theta_computed = true;
-    }
+    ensureTheta(dad_branch, dad);
+    if (isMixlen()) {
+        // the reference's isMixlen() form (:2365-2462, 2556-2568): df[mixlen] gradient + the lnL in df[mixlen],
+        // ddf[mixlen][mixlen] Hessian
+        const int m = getMixlen();
+        std::vector<double> lens;
+        branchLengths(dad_branch, lens);
+        check(k.derv_mixlen(ctx, lens.data(), df, ddf, df + m), "b200lk_derv_mixlen");
+    } else
     check(k.derv(ctx, dad_branch->length, df, ddf), "b200lk_derv");
+    kernel_calls++;
+}
+
+// computeLikelihoodDervMixlen*SIMD (tree/phylokernelnew.h:3397-3580): the class getCurMixture() alone
+void PhyloTree::computeLikelihoodDervMixlenCUDA(PhyloNeighbor *dad_branch, PhyloNode *dad, double &df, double &ddf) {
+    syncModel();
+    const KernelABI &k = kernelABI();
+    if (!k.derv_mixlen_class) outError("the kernel library has no b200lk_derv_mixlen_class");
+    ensureTheta(dad_branch, dad);
+    const int cls = getCurMixture();
+    check(k.derv_mixlen_class(ctx, cls, dad_branch->getLength(cls), &df, &ddf), "b200lk_derv_mixlen_class");
     kernel_calls++;
 }
 
 double PhyloTree::computeLikelihoodFromBufferCUDA() {
     if (!theta_computed) outError("computeLikelihoodFromBuffer: theta has not been computed");
     double lnl = 0.0;
+    if (isMixlen()) {  // current_it->getLength(mycat), :3248, 3263
+        std::vector<double> lens;
+        branchLengths(current_it, lens);
+        check(kernelABI().lnl_from_buffer_mixlen(ctx, lens.data(), &lnl), "b200lk_lnl_from_buffer_mixlen");
+    } else
     check(kernelABI().lnl_from_buffer(ctx, current_it->length, &lnl), "b200lk_lnl_from_buffer");
     kernel_calls++;
     return lnl;
@@ -479,6 +549,48 @@ void PhyloTree::computePatternLikelihood(double *pattern_lh, double *cur_logl, d
         check(kernelABI().fetch_pattern_lh_cat(ctx, _pattern_lh_cat.data()), "b200lk_fetch_pattern_lh_cat");
         memcpy(pattern_lh_cat, _pattern_lh_cat.data(), sizeof(double) * _pattern_lh_cat.size());
     }
+}
+
+// tree/phylotree.cpp:1330-1388 (transformPatternLhCat is the identity: vector_size == 1)
+double PhyloTree::computePatternLhCat(SiteLoglType wsl) {
+    if (!current_it) {
+        PhyloNode *leaf = findFarthestLeaf();
+        current_it = leaf->neighbors[0];
+        current_it_back = current_it->node->findNeighbor(leaf);
+    }
+    const double score = computeLikelihoodBranch(current_it, current_it_back->node);
+    const size_t nptn = aln->getNPattern(), ncat = site_rate->getNRate(), nmixture = model->getNMixtures();
+    _pattern_lh_cat.resize(nptn * ncat * nmixture);
+    check(kernelABI().fetch_pattern_lh_cat(ctx, _pattern_lh_cat.data()), "b200lk_fetch_pattern_lh_cat");
+    kernel_calls++;
+    if (model->isMixture() && (wsl == WSL_MIXTURE || wsl == WSL_RATECAT)) {  // unfused mixtures only exist here
+        double *lh_cat = _pattern_lh_cat.data(), *lh_res = _pattern_lh_cat.data();
+        if (wsl == WSL_MIXTURE && ncat > 1) {  // likelihood per mixture class (:1356-1366)
+            for (size_t ptn = 0; ptn < nptn; ptn++) {
+                for (size_t m = 0; m < nmixture; m++) {
+                    double lh = lh_cat[0];
+                    for (size_t c = 1; c < ncat; c++) lh += lh_cat[c];
+                    lh_res[m] = lh;
+                    lh_cat += ncat;
+                }
+                lh_res += nmixture;
+            }
+            _pattern_lh_cat.resize(nptn * nmixture);
+        } else if (wsl == WSL_RATECAT && nmixture > 1) {  // likelihood per rate category (:1367-1381)
+            for (size_t ptn = 0; ptn < nptn; ptn++) {
+                if (lh_res != lh_cat) memmove(lh_res, lh_cat, ncat * sizeof(double));
+                lh_cat += ncat;
+                for (size_t m = 1; m < nmixture; m++) {
+                    for (size_t c = 0; c < ncat; c++) lh_res[c] += lh_cat[c];
+                    lh_cat += ncat;
+                }
+                lh_res += ncat;
+            }
+            _pattern_lh_cat.resize(nptn * ncat);
+        }
+    }
+    curScore = score;
+    return score;
 }
 
 double PhyloTree::computeFunction(double value) {
@@ -540,7 +652,7 @@ void PhyloTree::optimizeOneBranch(PhyloNode *node1, PhyloNode *node2, bool clear
     const double lo = params ? params->min_branch_length : 1e-6, hi = params ? params->max_branch_length : 10.0;
     double negative_lh, optx;
     const KernelABI &k = kernelABI();
-    if (k.optimize_branch && (!params || params->device_newton)) {
+    if (k.optimize_branch && (!params || params->device_newton) && !isMixlen()) {
         // the same iteration, run on the device in one call: partial updates still pending for the two directions
         // are flushed first, then theta + every derivative evaluation + the safeguarded update stay in HBM
         syncModel();

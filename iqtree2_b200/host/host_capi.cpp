@@ -111,6 +111,11 @@ void b200host_rate_free(void *r) { delete (RateHeterogeneity *)r; }
 
 // ---- tree ------------------------------------------------------------------------------------------------------
 // the reference's set-up order: readTree, setAlignment, setModelFactory, setLikelihoodKernel, initializeAllPartialLh
+static double g_robust_keep = 1.0;  // Params::robust_phy_keep / robust_median of the next tree
+static int g_robust_median = 0;
+void b200host_set_robust(double keep, int median) { g_robust_keep = keep; g_robust_median = median; }
+static std::vector<double> g_mixlen_mult;  // non-empty: the next tree is a PhyloTreeMixlen with these class multipliers
+void b200host_set_next_mixlen(const double *mult, int nclass) { g_mixlen_mult.assign(mult, mult + nclass); }
 static double g_mem_fraction = 0.0;  // Params::max_mem_size of the next -mem tree (0: the minimum number of slots)
 void b200host_set_mem_fraction(double f) { g_mem_fraction = f; }
 
@@ -120,13 +125,26 @@ int b200host_tree_new(void **out, const char *newick, void *aln, void *model, vo
     try {
         h->params.lk_safe_scaling = (safe & 1) != 0;
         h->params.asc_lewis = (safe & 2) != 0;  // bit 1 of `safe`: +ASC
+        h->params.asc_holder = (safe & 8) != 0; // bit 3: +ASC with missing data (Holder)
+        h->params.robust_phy_keep = g_robust_keep;
+        h->params.robust_median = g_robust_median != 0;
+        g_robust_keep = 1.0;
+        g_robust_median = 0;
         if (safe & 4) {                         // bit 2: -mem (LM_MEM_SAVE)
             h->params.lh_mem_save = LM_MEM_SAVE;
             h->params.max_mem_size = g_mem_fraction;
         }
         h->params.device = device;
         h->params.device_newton = device_newton != 0;
-        h->tree = new PhyloTree();
+        std::vector<double> mult;
+        mult.swap(g_mixlen_mult);
+        if (mult.empty()) {
+            h->tree = new PhyloTree();
+        } else {
+            PhyloTreeMixlen *mt = new PhyloTreeMixlen();
+            mt->setMixlen((int)mult.size());
+            h->tree = mt;
+        }
         h->tree->setParams(&h->params);
         h->tree->readTreeString(newick);
         h->tree->setAlignment((Alignment *)aln);
@@ -134,6 +152,7 @@ int b200host_tree_new(void **out, const char *newick, void *aln, void *model, vo
         h->tree->setRate((RateHeterogeneity *)rate);
         h->tree->setLikelihoodKernel(LK_CUDA);
         h->tree->initializeAllPartialLh();
+        if (!mult.empty()) ((PhyloTreeMixlen *)h->tree)->initializeMixBranches(mult);
         h->tree->getBranches(h->b1, h->b2);
         *out = h;
         return 0;
@@ -192,6 +211,34 @@ int b200host_tree_optimize_one_branch(void *hv, int bid, int max_steps, double *
         *length = h->b1[bid]->findNeighbor(h->b2[bid])->length;
     })
 }
+// computePatternLhCat(wsl): lnL and the per-pattern category likelihoods; *ncols = columns per pattern after folding
+int b200host_tree_pattern_lh_cat(void *hv, int wsl, double *out, int32_t *ncols, double *lnl) {
+    GUARD({
+        PhyloTree *t = T(hv);
+        *lnl = t->computePatternLhCat((SiteLoglType)wsl);
+        const size_t np = t->aln->getNPattern();
+        *ncols = (int32_t)(t->_pattern_lh_cat.size() / (np ? np : 1));
+        if (out) memcpy(out, t->_pattern_lh_cat.data(), sizeof(double) * t->_pattern_lh_cat.size());
+    })
+}
+// heterotachy: computeFuncDervMulti at branch `bid` (gradient [mixlen] + lnL, Hessian [mixlen][mixlen]; signs as the
+// kernel returns them)
+int b200host_tree_derv_multi(void *hv, int bid, const double *lens, double *df, double *ddf, double *lnl) {
+    HostTree *h = (HostTree *)hv;
+    GUARD({
+        PhyloTreeMixlen *t = dynamic_cast<PhyloTreeMixlen *>(h->tree);
+        if (!t) outError("not a mixed-branch-length tree");
+        t->current_it = h->b1[bid]->findNeighbor(h->b2[bid]);
+        t->current_it_back = h->b2[bid]->findNeighbor(h->b1[bid]);
+        t->theta_computed = false;
+        const int m = t->getMixlen();
+        std::vector<double> g(m + 1), hs((size_t)m * m);
+        t->computeFuncDervMulti(lens, g.data(), hs.data());
+        for (int i = 0; i < m; i++) df[i] = -g[i];
+        for (int i = 0; i < m * m; i++) ddf[i] = -hs[i];
+        *lnl = -g[m];
+    })
+}
 int b200host_tree_from_buffer(void *hv, double *lnl) { GUARD(*lnl = T(hv)->computeLikelihoodFromBuffer()) }
 int b200host_tree_optimize_all_branches(void *hv, int iterations, double tolerance, double *lnl) {
     GUARD(*lnl = T(hv)->optimizeAllBranches(iterations, tolerance))
@@ -199,7 +246,15 @@ int b200host_tree_optimize_all_branches(void *hv, int iterations, double toleran
 int b200host_tree_get_lengths(void *hv, double *out) {
     std::vector<double> v;
     T(hv)->saveBranchLengths(v);
-    memcpy(out, v.data(), sizeof(double) * v.size());
+    memcpy(out, v.data(), sizeof(double) * T(hv)->branchNum);
+    return 0;
+}
+// heterotachy: class lengths [branchNum][mixlen] by branch id
+int b200host_tree_get_mix_lengths(void *hv, double *out) {
+    PhyloTree *t = T(hv);
+    std::vector<double> v;
+    t->saveBranchLengths(v);
+    memcpy(out, v.data() + t->branchNum, sizeof(double) * (v.size() - t->branchNum));
     return 0;
 }
 int b200host_tree_set_lengths(void *hv, const double *in) {

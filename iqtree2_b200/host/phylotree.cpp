@@ -64,6 +64,14 @@ const KernelABI &kernelABI() {
     bind(g_abi.evaluate_async, "evaluate_async", false);
     bind(g_abi.read_results, "read_results", false);
     bind(g_abi.optimize_branch, "optimize_branch", false);
+    bind(g_abi.set_asc, "set_asc", false);
+    bind(g_abi.set_robust, "set_robust", false);
+    bind(g_abi.set_ptn_freq, "set_ptn_freq", false);
+    bind(g_abi.update_partials_mixlen, "update_partials_mixlen", false);
+    bind(g_abi.branch_lnl_mixlen, "branch_lnl_mixlen", false);
+    bind(g_abi.lnl_from_buffer_mixlen, "lnl_from_buffer_mixlen", false);
+    bind(g_abi.derv_mixlen, "derv_mixlen", false);
+    bind(g_abi.derv_mixlen_class, "derv_mixlen_class", false);
     bind(g_abi.last_error, "last_error", false);
     bind(g_abi.get_counters, "get_counters", false);
     bind(g_abi.batch_create, "batch_create", false);
@@ -347,15 +355,27 @@ void PhyloTree::scaleLength(double factor) {
         for (PhyloNeighbor *nb : n->neighbors) nb->length *= factor;
 }
 
+// with heterotachy the class lengths follow the plain ones: v[branchNum + id*mixlen + c]
 void PhyloTree::saveBranchLengths(std::vector<double> &v) const {
-    v.assign(branchNum, 0.0);
+    const int m = isMixlen() ? getMixlen() : 0;
+    v.assign((size_t)branchNum * (1 + m), 0.0);
     for (PhyloNode *n : all_nodes)
-        for (PhyloNeighbor *nb : n->neighbors) v[nb->id] = nb->length;
+        for (PhyloNeighbor *nb : n->neighbors) {
+            v[nb->id] = nb->length;
+            for (int c = 0; c < m && c < (int)nb->lengths.size(); c++) v[branchNum + (size_t)nb->id * m + c] = nb->lengths[c];
+        }
 }
 
 void PhyloTree::restoreBranchLengths(const std::vector<double> &v) {
+    const int m = isMixlen() ? getMixlen() : 0;
     for (PhyloNode *n : all_nodes)
-        for (PhyloNeighbor *nb : n->neighbors) nb->length = v[nb->id];
+        for (PhyloNeighbor *nb : n->neighbors) {
+            nb->length = v[nb->id];
+            if (m && v.size() >= (size_t)branchNum * (1 + m)) {
+                nb->lengths.resize(m);
+                for (int c = 0; c < m; c++) nb->lengths[c] = v[branchNum + (size_t)nb->id * m + c];
+            }
+        }
 }
 
 void PhyloTree::clearAllPartialLH() {
