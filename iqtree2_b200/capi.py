@@ -13,7 +13,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb200lk.so")
+# B200LK_LIB: A/B hook for kernel experiments (another build of the SAME library); the default is the in-tree build
+LIB_PATH = os.environ.get("B200LK_LIB") or os.path.join(HERE, "libb200lk.so")
 
 LEAF, INTERNAL = 0, 1
 ROOT, TOWARD_ROOT = 2, 0x100          # non-reversible contexts: the root leaf; child->direction == TOWARD_ROOT

@@ -165,12 +165,238 @@ __device__ __forceinline__ int group_min(int v, int G) {
     return v;
 }
 
+// ---- T32 fast paths (4-state contexts, tile == 32) ---------------------------------------------------------------
+// The generic kernels below give a pattern to a group of lanes that stride over its block; on the T32 layout that turns
+// every warp access into eight scattered 32-byte sectors (measured on cfg2: derv 0.56 TB/s, theta 2.4 TB/s).  Here one
+// THREAD owns a pattern and reads its PAIRS = block/2 element pairs with 128-bit loads, so a warp access is one
+// contiguous 512-byte segment, exactly like the traversal kernel that wrote the vectors (s4.cu).
+__device__ __forceinline__ const double2 *t32_ptr(const double *base, int64_t p, int pairs) {
+    return reinterpret_cast<const double2 *>(base + (size_t)(p >> 5) * (64 * (size_t)pairs) + (size_t)(p & 31) * 2);
+}
+template <int PAIRS>
+__device__ __forceinline__ void t32_load(const double *base, int64_t p, double *v) {
+    const double2 *g = t32_ptr(base, p, PAIRS);
+#pragma unroll
+    for (int j = 0; j < PAIRS; j++) {
+        const double2 u = __ldcs(g + j * 32);
+        v[2 * j] = u.x;
+        v[2 * j + 1] = u.y;
+    }
+}
+// lh, df, ddf = sum_e val{0,1,2}[e] * theta[p][e]; sv = [3][block] in shared memory
+template <int PAIRS>
+__device__ __forceinline__ void t32_triple(const double *theta, int64_t p, const double *sv, double &lh, double &df,
+                                           double &ddf) {
+    constexpr int B = 2 * PAIRS;
+    double t[B];
+    t32_load<PAIRS>(theta, p, t);
+    double l0 = 0.0, l1 = 0.0, d0 = 0.0, d1 = 0.0, e0 = 0.0, e1 = 0.0;  // two interleaved accumulators, as dotProductTriple
+#pragma unroll
+    for (int j = 0; j < PAIRS; j++) {
+        l0 = fma(sv[2 * j], t[2 * j], l0);
+        l1 = fma(sv[2 * j + 1], t[2 * j + 1], l1);
+        d0 = fma(sv[B + 2 * j], t[2 * j], d0);
+        d1 = fma(sv[B + 2 * j + 1], t[2 * j + 1], d1);
+        e0 = fma(sv[2 * B + 2 * j], t[2 * j], e0);
+        e1 = fma(sv[2 * B + 2 * j + 1], t[2 * j + 1], e1);
+    }
+    lh = l0 + l1;
+    df = d0 + d1;
+    ddf = e0 + e1;
+}
+// per-pattern epilogue of computeLikelihoodDerv (:2494-2534), shared by the generic and the T32 kernels
+__device__ __forceinline__ void derv_accumulate(const BranchArgs &a, int64_t p, double lh, double df, double ddf,
+                                                double (&acc)[5]) {
+    lh = fabs(lh) + a.ptn_invar[p];  // :2494
+    if (p < a.nptn) {
+        double inv = 1.0 / lh;           // :2497-2505
+        double df_frac = df * inv, ddf_frac = ddf * inv, freq = a.ptn_freq[p];
+        double tmp1 = df_frac * freq, tmp2 = ddf_frac * freq;
+        acc[0] += tmp1;
+        acc[1] += fma(-tmp1, df_frac, tmp2);
+    } else {  // +ASC unobserved pattern, :2506-2534
+        if (a.buffer_scale_all[p] != 0.0) {
+            lh *= B200_SCALING_THRESHOLD;
+            df *= B200_SCALING_THRESHOLD;
+            ddf *= B200_SCALING_THRESHOLD;
+        }
+        if (a.const_df) {  // Holder: kept per pattern, combined by holder_kernel
+            a.pattern_lh[p] = lh;
+            a.const_df[p - a.nptn] = df;
+            a.const_ddf[p - a.nptn] = ddf;
+        }
+        acc[2] += lh;
+        acc[3] += df;
+        acc[4] += ddf;
+    }
+}
+template <int PAIRS>
+__device__ __forceinline__ void derv_t32(const BranchArgs &a, int red_blocks) {
+    __shared__ double sv[48];
+    if (threadIdx.x < 6 * PAIRS) sv[threadIdx.x] = a.val[threadIdx.x];
+    __syncthreads();
+    double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < a.ntot; p += (int64_t)gridDim.x * RED_THREADS) {
+        double lh, df, ddf;
+        t32_triple<PAIRS>(a.theta, p, sv, lh, df, ddf);
+        derv_accumulate(a, p, lh, df, ddf, acc);
+    }
+    if (a.ntot > a.nptn) block_reduce_store<5>(acc, a.red_partial, red_blocks);
+    else {
+        double acc2[2] = {acc[0], acc[1]};
+        block_reduce_store<2>(acc2, a.red_partial, red_blocks);
+    }
+}
+template <int PAIRS>
+__device__ __forceinline__ void frombuf_t32(const BranchArgs &a, int red_blocks) {
+    __shared__ double sv[16];
+    if (threadIdx.x < 2 * PAIRS) sv[threadIdx.x] = a.val[threadIdx.x];
+    __syncthreads();
+    double acc[2] = {0.0, 0.0};
+    for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < a.ntot; p += (int64_t)gridDim.x * RED_THREADS) {
+        double t[2 * PAIRS];
+        t32_load<PAIRS>(a.theta, p, t);
+        double l0 = 0.0, l1 = 0.0;
+#pragma unroll
+        for (int j = 0; j < PAIRS; j++) {
+            l0 = fma(sv[2 * j], t[2 * j], l0);
+            l1 = fma(sv[2 * j + 1], t[2 * j + 1], l1);
+        }
+        double lh = fabs(l0 + l1) + a.ptn_invar[p];  // :3295
+        if (p < a.nptn) {
+            lh = log(fabs(lh)) + a.buffer_scale_all[p];  // :3300
+            a.pattern_lh[p] = lh;
+            acc[0] = fma(lh, a.ptn_freq[p], acc[0]);
+        } else {  // +ASC unobserved pattern
+            if (a.buffer_scale_all[p] != 0.0) lh *= B200_SCALING_THRESHOLD;
+            a.pattern_lh[p] = lh;
+            acc[1] += lh;
+        }
+    }
+    block_reduce_store<2>(acc, a.red_partial, red_blocks);
+}
+// theta (computeLikelihoodBuffer) and the branch lnL on T32: NCM = categories = PAIRS / 2
+template <int PAIRS>
+__device__ __forceinline__ void theta_t32(const BranchArgs &a) {
+    constexpr int B = 2 * PAIRS, NCM = PAIRS / 2;
+    const bool tip_mode = a.pnode == nullptr;
+    for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < a.ntot; p += (int64_t)gridDim.x * RED_THREADS) {
+        double d[B], o[B];
+        t32_load<PAIRS>(a.pdad, p, d);
+        int sc[NCM], min_scale;
+        if (tip_mode) {
+            const double2 *tp = reinterpret_cast<const double2 *>(a.tip_partial_lh + (size_t)a.dad_states[p] * (4 * a.nmix));
+#pragma unroll
+            for (int c = 0; c < NCM; c++) {  // tip vector of the category's mixture class
+                const double2 u0 = __ldg(tp + (c / a.denom) * 2), u1 = __ldg(tp + (c / a.denom) * 2 + 1);
+                o[4 * c] = u0.x; o[4 * c + 1] = u0.y; o[4 * c + 2] = u1.x; o[4 * c + 3] = u1.y;
+            }
+        } else {
+            t32_load<PAIRS>(a.pnode, p, o);
+        }
+        if (a.safe) {
+            min_scale = 0x7fffffff;
+#pragma unroll
+            for (int c = 0; c < NCM; c++) {
+                sc[c] = (a.sdad[p * NCM + c] + (tip_mode ? 0 : a.snode[p * NCM + c])) & 0xff;
+                min_scale = min(min_scale, sc[c]);
+            }
+        } else {
+            min_scale = a.sdad[p] + (tip_mode ? 0 : a.snode[p]);
+        }
+        double2 *th = const_cast<double2 *>(t32_ptr(a.theta, p, PAIRS));
+#pragma unroll
+        for (int j = 0; j < PAIRS; j++) {
+            double t0 = o[2 * j] * d[2 * j], t1 = o[2 * j + 1] * d[2 * j + 1];
+            if (a.safe) {
+                const int s = sc[j / 2];
+                if (s == min_scale + 1) { t0 *= B200_SCALING_THRESHOLD; t1 *= B200_SCALING_THRESHOLD; }
+                else if (s > min_scale + 1) { t0 = 0.0; t1 = 0.0; }
+            }
+            th[j * 32] = make_double2(t0, t1);
+        }
+        a.buffer_scale_all[p] = (double)min_scale * B200_LOG_SCALING_THRESHOLD;
+    }
+}
+template <int PAIRS>
+__device__ __forceinline__ void lnl_t32(const BranchArgs &a, int red_blocks) {
+    constexpr int B = 2 * PAIRS, NCM = PAIRS / 2;
+    __shared__ double sv[16];
+    if (threadIdx.x < B) sv[threadIdx.x] = a.val[threadIdx.x];
+    __syncthreads();
+    const bool tip_mode = a.pnode == nullptr;
+    double acc[2] = {0.0, 0.0};
+    for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < a.ntot; p += (int64_t)gridDim.x * RED_THREADS) {
+        double d[B], w[B];
+        t32_load<PAIRS>(a.pdad, p, d);
+        if (tip_mode) {  // tip_val[state][c][i] = val0 * tip_partial_lh (:2757-2785)
+            const double2 *tv = reinterpret_cast<const double2 *>(a.tip_val + (size_t)a.dad_states[p] * B);
+#pragma unroll
+            for (int j = 0; j < PAIRS; j++) {
+                const double2 u = __ldg(tv + j);
+                w[2 * j] = u.x;
+                w[2 * j + 1] = u.y;
+            }
+        } else {
+            t32_load<PAIRS>(a.pnode, p, w);
+#pragma unroll
+            for (int e = 0; e < B; e++) w[e] *= sv[e];
+        }
+        int min_scale, sc[NCM];
+        if (a.safe) {
+            min_scale = 0x7fffffff;
+#pragma unroll
+            for (int c = 0; c < NCM; c++) {
+                sc[c] = (a.sdad[p * NCM + c] + (tip_mode ? 0 : a.snode[p * NCM + c])) & 0xff;
+                min_scale = min(min_scale, sc[c]);
+            }
+        } else {
+            min_scale = a.sdad[p] + (tip_mode ? 0 : a.snode[p]);
+        }
+        double lh = 0.0;
+#pragma unroll
+        for (int c = 0; c < NCM; c++) {
+            const double s0 = fma(w[4 * c + 2], d[4 * c + 2], w[4 * c] * d[4 * c]);
+            const double s1 = fma(w[4 * c + 3], d[4 * c + 3], w[4 * c + 1] * d[4 * c + 1]);
+            double lc = s0 + s1;
+            if (a.safe) {  // :2886-2893, 3018-3025
+                if (sc[c] == min_scale + 1) lc *= B200_SCALING_THRESHOLD;
+                else if (sc[c] > min_scale + 1) lc = 0.0;
+            }
+            a.pattern_lh_cat[(size_t)p * NCM + c] = lc;
+            lh += lc;
+        }
+        lh = fabs(lh) + a.ptn_invar[p];  // :2907, 3038
+        if (p < a.nptn) {
+            lh = log(lh) + (double)min_scale * B200_LOG_SCALING_THRESHOLD;  // :2909, 3041
+            a.pattern_lh[p] = lh;
+            acc[0] = fma(lh, a.ptn_freq[p], acc[0]);
+        } else {  // +ASC unobserved pattern (:2912-2930)
+            if (min_scale != 0) lh *= B200_SCALING_THRESHOLD;
+            a.pattern_lh[p] = lh;
+            acc[1] += lh;
+        }
+    }
+    block_reduce_store<2>(acc, a.red_partial, red_blocks);
+}
+#define T32_DISPATCH(fn, ...)                                  \
+    switch (a.block) {                                         \
+        case 4: fn<2>(__VA_ARGS__); break;                     \
+        case 8: fn<4>(__VA_ARGS__); break;                     \
+        case 12: fn<6>(__VA_ARGS__); break;                    \
+        default: fn<8>(__VA_ARGS__); break;                    \
+    }
+
 // ---- theta ---------------------------------------------------------------
 // theta[p][c][i] = partial_dad * partial_node (or * tip_partial_lh[state][m][i] when dad is a leaf);
 // buffer_scale_all[p] = LOG_SCALING_THRESHOLD * (NORM: summed scale; SAFE: min over categories, with
 // categories scaled once more multiplied by 2^-256 and those scaled more set to 0) (:2142-2175, 2190-2228)
 __global__ void __launch_bounds__(RED_THREADS) theta_kernel(BranchArgs a, BatchLaunch bl) {
     rebind_branch(a, bl);
+    if (a.tile == 32) {
+        T32_DISPATCH(theta_t32, a)
+        return;
+    }
     const int G = a.G, g = threadIdx.x & (G - 1);
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int n = a.n, ncm = a.ncm, block = a.block;
@@ -215,6 +441,10 @@ __global__ void __launch_bounds__(RED_THREADS) theta_kernel(BranchArgs a, BatchL
 // ---- df, ddf -------------------------------------------------------------
 __global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red_blocks, BatchLaunch bl) {
     rebind_branch(a, bl);
+    if (a.tile == 32) {
+        T32_DISPATCH(derv_t32, a, red_blocks)
+        return;
+    }
     const int G = a.G, g = threadIdx.x & (G - 1);
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int block = a.block;
@@ -245,30 +475,7 @@ __global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red
         lh = group_sum(lh, G);
         df = group_sum(df, G);
         ddf = group_sum(ddf, G);
-        if (g == 0 && valid) {
-            lh = fabs(lh) + a.ptn_invar[p];  // :2494
-            if (p < a.nptn) {
-                double inv = 1.0 / lh;           // :2497-2505
-                double df_frac = df * inv, ddf_frac = ddf * inv, freq = a.ptn_freq[p];
-                double tmp1 = df_frac * freq, tmp2 = ddf_frac * freq;
-                acc[0] += tmp1;
-                acc[1] += fma(-tmp1, df_frac, tmp2);
-            } else {  // +ASC (Lewis) unobserved pattern, :2506-2534
-                if (a.buffer_scale_all[p] != 0.0) {
-                    lh *= B200_SCALING_THRESHOLD;
-                    df *= B200_SCALING_THRESHOLD;
-                    ddf *= B200_SCALING_THRESHOLD;
-                }
-                if (a.const_df) {  // Holder: kept per pattern, combined by holder_kernel
-                    a.pattern_lh[p] = lh;
-                    a.const_df[p - a.nptn] = df;
-                    a.const_ddf[p - a.nptn] = ddf;
-                }
-                acc[2] += lh;
-                acc[3] += df;
-                acc[4] += ddf;
-            }
-        }
+        if (g == 0 && valid) derv_accumulate(a, p, lh, df, ddf, acc);
     }
     if (a.ntot > a.nptn) block_reduce_store<5>(acc, a.red_partial, red_blocks);
     else {
@@ -335,6 +542,23 @@ __global__ void __launch_bounds__(RED_THREADS) newton_kernel(BranchArgs a, Newto
         }
         __syncthreads();
         double acc[2] = {0.0, 0.0};
+        if (a.tile == 32) {  // thread per pattern, 128-bit loads (see the T32 fast paths above)
+            for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < a.nptn; p += (int64_t)gridDim.x * RED_THREADS) {
+                double lh, df, ddf;
+                switch (block) {
+                    case 4: t32_triple<2>(a.theta, p, sval, lh, df, ddf); break;
+                    case 8: t32_triple<4>(a.theta, p, sval, lh, df, ddf); break;
+                    case 12: t32_triple<6>(a.theta, p, sval, lh, df, ddf); break;
+                    default: t32_triple<8>(a.theta, p, sval, lh, df, ddf); break;
+                }
+                lh = fabs(lh) + a.ptn_invar[p];
+                const double inv = 1.0 / lh;
+                const double df_frac = df * inv, ddf_frac = ddf * inv, freq = a.ptn_freq[p];
+                const double tmp1 = df_frac * freq, tmp2 = ddf_frac * freq;
+                acc[0] += tmp1;
+                acc[1] += fma(-tmp1, df_frac, tmp2);
+            }
+        } else
         for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.nptn; pb += groups_per_grid) {
             int64_t p = pb + threadIdx.x / G;
             const bool valid = p < a.nptn;
@@ -440,6 +664,10 @@ __global__ void __launch_bounds__(RED_THREADS) newton_kernel(BranchArgs a, Newto
 // ---- lnL from theta --------------------------------------------------------
 __global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(BranchArgs a, int red_blocks, BatchLaunch bl) {
     rebind_branch(a, bl);
+    if (a.tile == 32) {
+        T32_DISPATCH(frombuf_t32, a, red_blocks)
+        return;
+    }
     const int G = a.G, g = threadIdx.x & (G - 1);
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int block = a.block;
@@ -481,6 +709,10 @@ __global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(BranchArgs a, int 
 // (or tip_val[state][c][i]*dad[c][i] when dad is a leaf).
 __global__ void __launch_bounds__(RED_THREADS) lnl_kernel(BranchArgs a, int red_blocks, BatchLaunch bl) {
     rebind_branch(a, bl);
+    if (a.tile == 32) {
+        T32_DISPATCH(lnl_t32, a, red_blocks)
+        return;
+    }
     const int G = a.G, g = threadIdx.x & (G - 1);
     const int64_t groups_per_grid = (int64_t)gridDim.x * (RED_THREADS / G);
     const int n = a.n, ncm = a.ncm, block = a.block;
