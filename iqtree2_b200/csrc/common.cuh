@@ -154,6 +154,8 @@ struct b200lk_ctx {
     double *rob_buf;     // sorted per-pattern lnL, sorted frequencies, their inclusive scan, 2 picks
     void *rob_temp;
     size_t rob_temp_bytes;
+    bool s4_sym;       // 4-state path: inv_evec[i][x] == evec[x][i] * s4_pi[x] (s4_detect_sym at set_model)
+    double s4_pi[4];
     bool model_set, tips_set, theta_computed;
     int theta_dad_kind;
     int64_t n_updates, n_launches;
@@ -204,6 +206,7 @@ int launch_newton(b200lk_ctx *c, const b200lk_newton *nr);
 int launch_rell(b200lk_ctx *c);
 int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used);
 int launch_partial_multi(b200lk_ctx *c, int node_index);
+bool s4_detect_sym(const b200lk_ctx *c, double pi[4]);
 int launch_dense20(b200lk_ctx *c, int node_base, int nnodes);
 int launch_inv_frag(b200lk_ctx *c);
 int launch_tt_tables(b200lk_ctx *c, int nnodes);

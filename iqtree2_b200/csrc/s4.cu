@@ -150,7 +150,7 @@ __device__ __forceinline__ void child_load(const TravArgs &a, int kind, int id, 
 // timing experiment: eigenvectors as compile-time literals (WRONG results)
 #define S4X_LIT {0.31, -0.42, 0.53, 0.64, 0.75, -0.86, 0.97, 0.18, -0.29, 0.41, 0.52, -0.63, 0.74, 0.85, -0.96, 0.17}
 #endif
-template <int NCM, bool PLAIN>
+template <int NCM, bool PLAIN, bool SYM = false>
 __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const double *ev, double *v) {
 #pragma unroll
     for (int c = 0; c < NCM; c++) {
@@ -163,14 +163,20 @@ __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const doubl
         for (int x = 0; x < 4; x++) f[x] = PLAIN ? s4_plain(&UL[4 * x], w) : s4_tree(&UL[4 * x], w);
 #else
 #pragma unroll
-        for (int x = 0; x < 4; x++) f[x] = PLAIN ? s4_plain(&mdl.U[c][4 * x], w) : s4_tree(&mdl.U[c][4 * x], w);
+        for (int x = 0; x < 4; x++) f[x] = PLAIN ? s4_plain(&mdl.U[SYM ? 0 : c][4 * x], w) : s4_tree(&mdl.U[SYM ? 0 : c][4 * x], w);
 #endif
 #pragma unroll
         for (int x = 0; x < 4; x++) v[c * 4 + x] = f[x];
     }
 }
 
-template <int NCM, bool SAFE>
+// SYM: every category shares the eigenvectors and the inverse is M[i][x] = U[x][i] * pi[x] (what a reversible model's
+// eigen-solver produces: evec = Pi^-1/2 V, inv_evec = V^T Pi^1/2, utils/eigendecomposition.cpp:165-317), checked on the
+// host at set_model.  The back-transformation then reads U again -- out[i] = sum_x U[x][i] (pi[x] tmp[x]), same
+// reduction tree over x -- so only U and pi (40 uniform registers) are live across the node loop instead of U and M
+// (64: more than the uniform register file holds, which made the kernel re-load both for every category of every
+// node; that constant traffic, not HBM, was what bounded it -- profiles/r1s_s4_experiments.log).  P.mdl.M[0][0..3] = pi.
+template <int NCM, bool SAFE, bool SYM>
 __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const __grid_constant__ S4Launch<NCM> P) {
     constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
     const TravArgs &a = P.a;
@@ -217,10 +223,10 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
         unsigned sc = 0;
         child_load<NCM, SAFE>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
         child_load<NCM, SAFE>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
-        if (lk != SRC_LEAF) child_apply<NCM, false>(P.mdl, ndx.lexp, l);
+        if (lk != SRC_LEAF) child_apply<NCM, false, SYM>(P.mdl, ndx.lexp, l);
         if (rk != SRC_LEAF) {
-            if (lk == SRC_LEAF) child_apply<NCM, true>(P.mdl, ndx.rexp, r);   // tip-internal: dotProductVec (:1853)
-            else child_apply<NCM, false>(P.mdl, ndx.rexp, r);                 // internal-internal (:1975-1983)
+            if (lk == SRC_LEAF) child_apply<NCM, true, SYM>(P.mdl, ndx.rexp, r);   // tip-internal: dotProductVec (:1853)
+            else child_apply<NCM, false, SYM>(P.mdl, ndx.rexp, r);                 // internal-internal (:1975-1983)
         }
         // ---- product, back to eigen-space (productVecMat), rescale --------------------------------
         const bool tiptip = lk == SRC_LEAF && rk == SRC_LEAF;
@@ -230,6 +236,10 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
             double tmp[4];
 #pragma unroll
             for (int x = 0; x < 4; x++) tmp[x] = __dmul_rn(l[c * 4 + x], r[c * 4 + x]);
+            if (SYM) {
+#pragma unroll
+                for (int x = 0; x < 4; x++) tmp[x] = __dmul_rn(tmp[x], P.mdl.M[0][x]);  // pi[x]
+            }
             unsigned long long mx = 0ull;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
@@ -237,7 +247,13 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
                 const double ML[16] = S4X_LIT;
                 const double o = s4_tree(&ML[4 * k], tmp);
 #else
-                const double o = s4_tree(&P.mdl.M[c][4 * k], tmp);
+                double o;
+                if (SYM) {
+                    const double ut[4] = {P.mdl.U[0][k], P.mdl.U[0][4 + k], P.mdl.U[0][8 + k], P.mdl.U[0][12 + k]};
+                    o = s4_tree(ut, tmp);
+                } else {
+                    o = s4_tree(&P.mdl.M[c][4 * k], tmp);
+                }
 #endif
                 prev[c * 4 + k] = o;
                 const unsigned long long b = abs_bits(o);  // |x| order == unsigned order of the bit pattern
@@ -620,6 +636,31 @@ static void fill_model(const b200lk_ctx *c, S4Model<NCM> &m) {
         memcpy(m.U[cc], c->h_evec + (size_t)mm * 16, sizeof(double) * 16);
         memcpy(m.M[cc], c->h_inv_evec + (size_t)mm * 16, sizeof(double) * 16);
     }
+    if (c->s4_sym)  // s4_traverse_kernel<.., SYM = true> reads pi[x] from M[0][0..3] and never touches the rest of M
+        for (int x = 0; x < 4; x++) m.M[0][x] = c->s4_pi[x];
+}
+
+// inv_evec[i][x] == evec[x][i] * pi[x] to rounding for one shared eigen-system?  (reversible models: evec = Pi^-1/2 V,
+// inv_evec = V^T Pi^1/2.)  pi[x] is read off the eigenvector whose entries are farthest from zero (the constant one of
+// eigenvalue 0); every entry is then checked, so an eigen-system normalised any other way keeps the general kernel.
+bool s4_detect_sym(const b200lk_ctx *c, double pi[4]) {
+    if (c->d.nstates != 4 || c->d.nmix != 1) return false;
+    const double *U = c->h_evec, *M = c->h_inv_evec;
+    int i0 = 0;
+    double best = -1.0;
+    for (int i = 0; i < 4; i++) {
+        double mn = 1e300;
+        for (int x = 0; x < 4; x++) mn = std::min(mn, fabs(U[x * 4 + i]));
+        if (mn > best) { best = mn; i0 = i; }
+    }
+    if (!(best > 1e-8)) return false;
+    for (int x = 0; x < 4; x++) pi[x] = M[i0 * 4 + x] / U[x * 4 + i0];
+    double scale = 0.0;
+    for (int k = 0; k < 16; k++) scale = std::max(scale, fabs(M[k]));
+    for (int i = 0; i < 4; i++)
+        for (int x = 0; x < 4; x++)
+            if (!(fabs(M[i * 4 + x] - U[x * 4 + i] * pi[x]) <= 8e-16 * scale)) return false;
+    return true;
 }
 
 // expv[c][i] = exp(eval[m][i] * rate[c % ncat] * len), the factor of computePartialInfo (:1016-1031)
@@ -740,8 +781,10 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     if (!c->trav_attr_set) {
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         c->trav_attr_set = true;
     }
     // two threads per pattern (s4_split_kernel) when every category shares the eigenvectors; B200LK_S4_SPLIT=0/1 is an
@@ -772,8 +815,11 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         const dim3 g2(grid, c->batch->n);
         if (c->d.safe_numeric) s4_traverse_batch_kernel<NCM, true><<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
         else s4_traverse_batch_kernel<NCM, false><<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
-    } else if (c->d.safe_numeric) s4_traverse_kernel<NCM, true><<<grid, S4_THREADS, smem, c->stream>>>(P);
-    else s4_traverse_kernel<NCM, false><<<grid, S4_THREADS, smem, c->stream>>>(P);
+    } else if (c->s4_sym) {
+        if (c->d.safe_numeric) s4_traverse_kernel<NCM, true, true><<<grid, S4_THREADS, smem, c->stream>>>(P);
+        else s4_traverse_kernel<NCM, false, true><<<grid, S4_THREADS, smem, c->stream>>>(P);
+    } else if (c->d.safe_numeric) s4_traverse_kernel<NCM, true, false><<<grid, S4_THREADS, smem, c->stream>>>(P);
+    else s4_traverse_kernel<NCM, false, false><<<grid, S4_THREADS, smem, c->stream>>>(P);
     prof_mark(c);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
