@@ -74,6 +74,7 @@ struct S4Launch {
 };
 
 #define S4_THREADS 128
+#define S4_THRESHOLD_HI 0x2ff00000  // high word of 2^-256 = B200_SCALING_THRESHOLD (exponent 1023 - 256, mantissa 0)
 #ifndef S4_EXPERIMENT
 #define S4_EXPERIMENT 0
 #endif
@@ -230,7 +231,7 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
         }
         // ---- product, back to eigen-space (productVecMat), rescale --------------------------------
         const bool tiptip = lk == SRC_LEAF && rk == SRC_LEAF;
-        unsigned long long mxall = 0ull;
+        int mxall = 0;
 #pragma unroll
         for (int c = 0; c < NCM; c++) {
             double tmp[4];
@@ -240,7 +241,7 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
 #pragma unroll
                 for (int x = 0; x < 4; x++) tmp[x] = __dmul_rn(tmp[x], P.mdl.M[0][x]);  // pi[x]
             }
-            unsigned long long mx = 0ull;
+            int mx = 0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
 #if S4_EXPERIMENT == 2
@@ -256,21 +257,22 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
                 }
 #endif
                 prev[c * 4 + k] = o;
-                const unsigned long long b = abs_bits(o);  // |x| order == unsigned order of the bit pattern
-                mx = b > mx ? b : mx;
+                // |x| < 2^-256  <=>  high word of |x| < high word of 2^-256 (whose low word is 0): the test needs only
+                // the maximum of the high words -- one LOP3 + one integer max per value
+                mx = max(mx, __double2hiint(o) & 0x7fffffff);
             }
             if (SAFE) {
-                if (!tiptip && __longlong_as_double((long long)mx) < B200_SCALING_THRESHOLD && invar0) {
+                if (!tiptip && mx < S4_THRESHOLD_HI && invar0) {
 #pragma unroll
                     for (int k = 0; k < 4; k++) prev[c * 4 + k] *= B200_TWO_256;
                     sc = __vadd4(sc, 1u << (8 * c));
                 }
             } else {
-                mxall = mx > mxall ? mx : mxall;
+                mxall = max(mxall, mx);
             }
         }
         if (!SAFE) {
-            if (!tiptip && __longlong_as_double((long long)mxall) < B200_SCALING_THRESHOLD && invar0) {
+            if (!tiptip && mxall < S4_THRESHOLD_HI && invar0) {
 #pragma unroll
                 for (int j = 0; j < BLOCK; j++) prev[j] *= B200_TWO_256;
                 sc += 1;
