@@ -75,9 +75,6 @@ struct S4Launch {
 
 #define S4_THREADS 128
 #define S4_THRESHOLD_HI 0x2ff00000  // high word of 2^-256 = B200_SCALING_THRESHOLD (exponent 1023 - 256, mantissa 0)
-#ifndef S4_EXPERIMENT
-#define S4_EXPERIMENT 0
-#endif
 #ifndef S4_MINB
 #define S4_MINB 4  // resident CTAs per SM the register allocation is sized for
 #endif
@@ -147,10 +144,6 @@ __device__ __forceinline__ void child_load(const TravArgs &a, int kind, int id, 
 }
 
 // internal child: v <- U (expv (.) v) per category, in place
-#if S4_EXPERIMENT == 2
-// timing experiment: eigenvectors as compile-time literals (WRONG results)
-#define S4X_LIT {0.31, -0.42, 0.53, 0.64, 0.75, -0.86, 0.97, 0.18, -0.29, 0.41, 0.52, -0.63, 0.74, 0.85, -0.96, 0.17}
-#endif
 template <int NCM, bool PLAIN, bool SYM = false>
 __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const double *ev, double *v) {
 #pragma unroll
@@ -158,14 +151,8 @@ __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const doubl
         double w[4], f[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) w[i] = __dmul_rn(ev[c * 4 + i], v[c * 4 + i]);
-#if S4_EXPERIMENT == 2
-        const double UL[16] = S4X_LIT;
-#pragma unroll
-        for (int x = 0; x < 4; x++) f[x] = PLAIN ? s4_plain(&UL[4 * x], w) : s4_tree(&UL[4 * x], w);
-#else
 #pragma unroll
         for (int x = 0; x < 4; x++) f[x] = PLAIN ? s4_plain(&mdl.U[SYM ? 0 : c][4 * x], w) : s4_tree(&mdl.U[SYM ? 0 : c][4 * x], w);
-#endif
 #pragma unroll
         for (int x = 0; x < 4; x++) v[c * 4 + x] = f[x];
     }
@@ -177,8 +164,8 @@ __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const doubl
 // reduction tree over x -- so only U and pi (40 uniform registers) are live across the node loop instead of U and M
 // (64: more than the uniform register file holds, which made the kernel re-load both for every category of every
 // node; that constant traffic, not HBM, was what bounded it -- profiles/r1s_s4_experiments.log).  P.mdl.M[0][0..3] = pi.
-template <int NCM, bool SAFE, bool SYM>
-__global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const __grid_constant__ S4Launch<NCM> P) {
+template <int NCM, bool SAFE, bool SYM, int MINB = S4_MINB>
+__global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __grid_constant__ S4Launch<NCM> P) {
     constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
     const TravArgs &a = P.a;
     // [depth][PAIRS][S4_THREADS] double2 | unsigned [depth][S4_THREADS] scale | uint8 [chunk][S4_THREADS] tip states
@@ -199,11 +186,6 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
 
     for (int i = 0; i < a.nnodes; i++) {
         const PNode<NCM> &nd = P.nodes[i];  // constant bank, uniform index
-#if S4_EXPERIMENT == 1
-        const PNode<NCM> &ndx = P.nodes[0];  // timing experiment: loop-invariant expv (WRONG results)
-#else
-        const PNode<NCM> &ndx = nd;
-#endif
         const int info = nd.info;
         const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 12) - 1;
         if (refill >= 0) {
@@ -224,10 +206,10 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
         unsigned sc = 0;
         child_load<NCM, SAFE>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
         child_load<NCM, SAFE>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
-        if (lk != SRC_LEAF) child_apply<NCM, false, SYM>(P.mdl, ndx.lexp, l);
+        if (lk != SRC_LEAF) child_apply<NCM, false, SYM>(P.mdl, nd.lexp, l);
         if (rk != SRC_LEAF) {
-            if (lk == SRC_LEAF) child_apply<NCM, true, SYM>(P.mdl, ndx.rexp, r);   // tip-internal: dotProductVec (:1853)
-            else child_apply<NCM, false, SYM>(P.mdl, ndx.rexp, r);                 // internal-internal (:1975-1983)
+            if (lk == SRC_LEAF) child_apply<NCM, true, SYM>(P.mdl, nd.rexp, r);   // tip-internal: dotProductVec (:1853)
+            else child_apply<NCM, false, SYM>(P.mdl, nd.rexp, r);                 // internal-internal (:1975-1983)
         }
         // ---- product, back to eigen-space (productVecMat), rescale --------------------------------
         const bool tiptip = lk == SRC_LEAF && rk == SRC_LEAF;
@@ -244,10 +226,6 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
             int mx = 0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-#if S4_EXPERIMENT == 2
-                const double ML[16] = S4X_LIT;
-                const double o = s4_tree(&ML[4 * k], tmp);
-#else
                 double o;
                 if (SYM) {
                     const double ut[4] = {P.mdl.U[0][k], P.mdl.U[0][4 + k], P.mdl.U[0][8 + k], P.mdl.U[0][12 + k]};
@@ -255,7 +233,6 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
                 } else {
                     o = s4_tree(&P.mdl.M[c][4 * k], tmp);
                 }
-#endif
                 prev[c * 4 + k] = o;
                 // |x| < 2^-256  <=>  high word of |x| < high word of 2^-256 (whose low word is 0): the test needs only
                 // the maximum of the high words -- one LOP3 + one integer max per value
@@ -280,11 +257,7 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
             sc &= 0xff;  // UBYTE arithmetic of the reference
         }
         prev_sc = sc;
-#if S4_EXPERIMENT == 3
-        if (valid && prev[0] == 1.2345e-300) {  // timing experiment: no stores (the compute side alone)
-#else
         if (valid) {
-#endif
             double2 *g = reinterpret_cast<double2 *>(a.partial + (size_t)nd.out_slot * a.slot_doubles + poff);
 #pragma unroll
             for (int j = 0; j < PAIRS; j++) g[j * 32] = make_double2(prev[2 * j], prev[2 * j + 1]);
@@ -301,195 +274,6 @@ __global__ void __launch_bounds__(S4_THREADS, S4_MINB) s4_traverse_kernel(const 
             for (int j = 0; j < PAIRS; j++)
                 stk[(out_stack * PAIRS + j) * S4_THREADS + tid] = make_double2(prev[2 * j], prev[2 * j + 1]);
             stk_sc[out_stack * S4_THREADS + tid] = sc;
-        }
-    }
-}
-
-// ---- split variant: TWO threads per pattern ------------------------------------------------------------------------
-// The kernel above is bound by latency, not by a pipe (ncu r1s: 4 warps per scheduler at 128 registers, issue slots
-// 47 % busy, long_scoreboard the top stall, DRAM writes at 4.5 of the 6.6 TB/s a pure T32 write stream reaches --
-// profiles/r1s_hbm_streams.json).  Here lanes l and l + 16 of a warp share one pattern and own half of its categories
-// each: half the live state per thread (l, r, prev: 3 x NCM*2 doubles), so twice the warps fit an SM, and the
-// per-node dependency chain of a thread is half as long.  What it costs:
-//   * exp(lambda r t) differs between the two halves of a warp, so it cannot come from the uniform datapath: it is read
-//     from the child's device table (tables_kernel writes expv[c][i] next to echild) -- one 128-byte line per child,
-//     a single L1 wavefront per 128-bit load;
-//   * NORM_LH needs the maximum over the whole block: one 64-bit xor-shuffle per node;
-//   * a warp's 128-bit access is two 256-byte segments instead of one 512-byte segment (still whole sectors).
-// Eigenvectors stay launch parameters; the variant is used when all categories share them (no mixture classes
-// inside the block), which is every 4-state configuration of BASELINE.json.
-#define S4H_PPC (S4_THREADS / 2)  // patterns per CTA
-#ifndef S4_SPLIT_DEFAULT
-#define S4_SPLIT_DEFAULT 0
-#endif
-
-template <int NCM, bool SAFE, int MINB>
-__global__ void __launch_bounds__(S4_THREADS, MINB) s4_split_kernel(const __grid_constant__ S4Launch<NCM> P) {
-    constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2, CPT = NCM / 2, HB = CPT * 4, HP = CPT * 2, PPC = S4H_PPC;
-    const TravArgs &a = P.a;
-    // [depth][PAIRS][PPC] double2 | unsigned [depth][2][PPC] scale | uint8 [chunk][PPC] tip states
-    extern __shared__ double2 stk[];
-    unsigned *stk_sc = reinterpret_cast<unsigned *>(stk + (size_t)a.depth * PAIRS * PPC);
-    uint8_t *st_buf = reinterpret_cast<uint8_t *>(stk_sc + (size_t)a.depth * 2 * PPC);
-    const int tid = threadIdx.x, lane = tid & 31, h = lane >> 4;
-    const int pl = (tid >> 5) * 16 + (lane & 15);  // pattern inside the CTA's tile
-    const int c0 = h * CPT, j0 = h * HP;           // first category / first element pair of this half
-    const int64_t p0 = (int64_t)blockIdx.x * PPC;
-    int64_t p = p0 + pl;
-    const bool valid = p < a.ntot;
-    if (!valid) p = a.ntot - 1;
-    const size_t poff = (size_t)(p >> 5) * (32 * BLOCK) + (size_t)(p & 31) * 2;  // T32 layout
-    const bool invar0 = a.ptn_invar[p] == 0.0;
-    const double *U = P.mdl.U[0], *M = P.mdl.M[0];
-    double prev[HB];
-#pragma unroll
-    for (int j = 0; j < HB; j++) prev[j] = 0.0;
-    unsigned prev_sc = 0;
-
-    for (int i = 0; i < a.nnodes; i++) {
-        const PNode<NCM> &nd = P.nodes[i];
-        const int info = nd.info;
-        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 12) - 1;
-        if (refill >= 0) {
-            __syncthreads();
-            constexpr int VPR = PPC / 16;
-            const int nvec = a.chunk * VPR;
-            const int32_t *seq = a.leaf_seq + (size_t)refill * a.chunk;
-            for (int v = tid; v < nvec; v += S4_THREADS) {
-                const int row = v / VPR, q = v - row * VPR;
-                const uint4 *src = reinterpret_cast<const uint4 *>(a.states + (size_t)seq[row] * a.ntot_pad + p0) + q;
-                reinterpret_cast<uint4 *>(st_buf)[v] = __ldg(src);
-            }
-            __syncthreads();
-        }
-        double v2[2][HB], ev[2][HB];
-        unsigned sc = 0;
-#pragma unroll
-        for (int k = 0; k < 2; k++) {
-            const int kind = k ? rk : lk, id = k ? nd.rid : nd.lid;
-            double *v = v2[k];
-            if (kind == SRC_LEAF) {
-                const int st = st_buf[id * PPC + pl];
-                const double2 *lf = reinterpret_cast<const double2 *>(a.tables + (k ? nd.rtab : nd.ltab) + (size_t)st * BLOCK) + j0;
-#pragma unroll
-                for (int j = 0; j < HP; j++) {
-                    const double2 u = __ldg(lf + j);
-                    v[2 * j] = u.x;
-                    v[2 * j + 1] = u.y;
-                }
-                continue;
-            }
-            // exp(lambda_i r_c t) of this half's categories, from the child's device table
-            const double2 *et = reinterpret_cast<const double2 *>(a.tables + (k ? nd.rexp_off : nd.lexp_off)) + j0;
-#pragma unroll
-            for (int j = 0; j < HP; j++) {
-                const double2 u = __ldg(et + j);
-                ev[k][2 * j] = u.x;
-                ev[k][2 * j + 1] = u.y;
-            }
-            unsigned s;
-            if (kind == SRC_PREV) {
-#pragma unroll
-                for (int j = 0; j < HB; j++) v[j] = prev[j];
-                s = prev_sc;
-            } else if (kind == SRC_STACK) {
-#pragma unroll
-                for (int j = 0; j < HP; j++) {
-                    const double2 u = stk[(id * PAIRS + j0 + j) * PPC + pl];
-                    v[2 * j] = u.x;
-                    v[2 * j + 1] = u.y;
-                }
-                s = stk_sc[(id * 2 + h) * PPC + pl];
-            } else {
-                const double2 *g = reinterpret_cast<const double2 *>(a.partial + (size_t)id * a.slot_doubles + poff) + j0 * 32;
-#pragma unroll
-                for (int j = 0; j < HP; j++) {
-                    const double2 u = __ldcg(g + j * 32);
-                    v[2 * j] = u.x;
-                    v[2 * j + 1] = u.y;
-                }
-                const uint8_t *gs = a.scale + (size_t)id * a.slot_scale_bytes;
-                if (SAFE) {
-                    s = 0;
-#pragma unroll
-                    for (int c = 0; c < CPT; c++) s |= (unsigned)__ldcg(gs + p * NCM + c0 + c) << (8 * c);
-                } else {
-                    s = __ldcg(gs + p);
-                }
-            }
-            sc = SAFE ? __vadd4(sc, s) : sc + s;
-        }
-        // internal children: v <- U (expv (.) v) per category (same association and reduction trees as above)
-#pragma unroll
-        for (int k = 0; k < 2; k++) {
-            const int kind = k ? rk : lk;
-            if (kind == SRC_LEAF) continue;
-            const bool plain = k == 1 && lk == SRC_LEAF;  // tip-internal: dotProductVec (:1853)
-            double *v = v2[k];
-#pragma unroll
-            for (int c = 0; c < CPT; c++) {
-                double w[4], f[4];
-#pragma unroll
-                for (int x = 0; x < 4; x++) w[x] = __dmul_rn(ev[k][c * 4 + x], v[c * 4 + x]);
-#pragma unroll
-                for (int x = 0; x < 4; x++) f[x] = plain ? s4_plain(U + 4 * x, w) : s4_tree(U + 4 * x, w);
-#pragma unroll
-                for (int x = 0; x < 4; x++) v[c * 4 + x] = f[x];
-            }
-        }
-        const bool tiptip = lk == SRC_LEAF && rk == SRC_LEAF;
-        unsigned long long mxall = 0ull;
-#pragma unroll
-        for (int c = 0; c < CPT; c++) {
-            double tmp[4];
-#pragma unroll
-            for (int x = 0; x < 4; x++) tmp[x] = __dmul_rn(v2[0][c * 4 + x], v2[1][c * 4 + x]);
-            unsigned long long mx = 0ull;
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const double o = s4_tree(M + 4 * k, tmp);
-                prev[c * 4 + k] = o;
-                const unsigned long long b = abs_bits(o);
-                mx = b > mx ? b : mx;
-            }
-            if (SAFE) {
-                if (!tiptip && __longlong_as_double((long long)mx) < B200_SCALING_THRESHOLD && invar0) {
-#pragma unroll
-                    for (int k = 0; k < 4; k++) prev[c * 4 + k] *= B200_TWO_256;
-                    sc = __vadd4(sc, 1u << (8 * c));
-                }
-            } else {
-                mxall = mx > mxall ? mx : mxall;
-            }
-        }
-        if (!SAFE) {
-            const unsigned long long other = __shfl_xor_sync(0xffffffffu, mxall, 16);  // the pattern's other half
-            mxall = other > mxall ? other : mxall;
-            if (!tiptip && __longlong_as_double((long long)mxall) < B200_SCALING_THRESHOLD && invar0) {
-#pragma unroll
-                for (int j = 0; j < HB; j++) prev[j] *= B200_TWO_256;
-                sc += 1;
-            }
-            sc &= 0xff;
-        }
-        prev_sc = sc;
-        if (valid) {
-            double2 *g = reinterpret_cast<double2 *>(a.partial + (size_t)nd.out_slot * a.slot_doubles + poff) + j0 * 32;
-#pragma unroll
-            for (int j = 0; j < HP; j++) g[j * 32] = make_double2(prev[2 * j], prev[2 * j + 1]);
-            uint8_t *gs = a.scale + (size_t)nd.out_slot * a.slot_scale_bytes;
-            if (SAFE) {
-#pragma unroll
-                for (int c = 0; c < CPT; c++) gs[p * NCM + c0 + c] = (uint8_t)(sc >> (8 * c));
-            } else if (h == 0) {
-                gs[p] = (uint8_t)sc;
-            }
-        }
-        if (out_stack >= 0) {
-#pragma unroll
-            for (int j = 0; j < HP; j++)
-                stk[(out_stack * PAIRS + j0 + j) * PPC + pl] = make_double2(prev[2 * j], prev[2 * j + 1]);
-            stk_sc[(out_stack * 2 + h) * PPC + pl] = sc;
         }
     }
 }
@@ -789,37 +573,20 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         c->trav_attr_set = true;
     }
-    // two threads per pattern (s4_split_kernel) when every category shares the eigenvectors; B200LK_S4_SPLIT=0/1 is an
-    // A/B switch
-    static const int split_env = [] { const char *e = getenv("B200LK_S4_SPLIT"); return e ? atoi(e) : S4_SPLIT_DEFAULT; }();
-    if constexpr (NCM == 2 || NCM == 4) {
-        if (split_env && !c->batch && c->d.nmix == 1) {
-            const size_t smem2 = (size_t)depth_used * S4H_PPC * (2 * NCM * sizeof(double2) + 2 * sizeof(unsigned)) + (size_t)chunk * S4H_PPC;
-            const unsigned grid2 = (unsigned)((c->ntot + S4H_PPC - 1) / S4H_PPC);
-            const bool safe = c->d.safe_numeric != 0;
-            // split_env = resident CTAs per SM the register allocation is sized for (5..8; 1 = the default, 6)
-            auto kern = safe ? s4_split_kernel<NCM, true, 6> : s4_split_kernel<NCM, false, 6>;
-            if (split_env == 5) kern = safe ? s4_split_kernel<NCM, true, 5> : s4_split_kernel<NCM, false, 5>;
-            if (split_env == 7) kern = safe ? s4_split_kernel<NCM, true, 7> : s4_split_kernel<NCM, false, 7>;
-            if (split_env == 8) kern = safe ? s4_split_kernel<NCM, true, 8> : s4_split_kernel<NCM, false, 8>;
-            if (smem2 > 48 * 1024)
-                CUDA_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            prof_mark(c);
-            kern<<<grid2, S4_THREADS, smem2, c->stream>>>(P);
-            prof_mark(c);
-            CUDA_TRY(c, cudaGetLastError());
-            c->n_launches++;
-            return B200LK_OK;
-        }
-    }
     prof_mark(c);
     if (c->batch) {
         const dim3 g2(grid, c->batch->n);
         if (c->d.safe_numeric) s4_traverse_batch_kernel<NCM, true><<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
         else s4_traverse_batch_kernel<NCM, false><<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
     } else if (c->s4_sym) {
-        if (c->d.safe_numeric) s4_traverse_kernel<NCM, true, true><<<grid, S4_THREADS, smem, c->stream>>>(P);
-        else s4_traverse_kernel<NCM, false, true><<<grid, S4_THREADS, smem, c->stream>>>(P);
+        // resident CTAs per SM the registers are sized for: 4 (128 registers) or more with a shallower stack
+        static const int minb = [] { const char *e = getenv("B200LK_S4_MINB"); return e ? atoi(e) : S4_MINB; }();
+        const bool safe = c->d.safe_numeric != 0;
+        auto kern = safe ? s4_traverse_kernel<NCM, true, true, S4_MINB> : s4_traverse_kernel<NCM, false, true, S4_MINB>;
+        if (minb == 5) kern = safe ? s4_traverse_kernel<NCM, true, true, 5> : s4_traverse_kernel<NCM, false, true, 5>;
+        if (minb == 6) kern = safe ? s4_traverse_kernel<NCM, true, true, 6> : s4_traverse_kernel<NCM, false, true, 6>;
+        if (minb != S4_MINB) CUDA_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        kern<<<grid, S4_THREADS, smem, c->stream>>>(P);
     } else if (c->d.safe_numeric) s4_traverse_kernel<NCM, true, false><<<grid, S4_THREADS, smem, c->stream>>>(P);
     else s4_traverse_kernel<NCM, false, false><<<grid, S4_THREADS, smem, c->stream>>>(P);
     prof_mark(c);
