@@ -17,7 +17,10 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 
 import oracle  # noqa: E402
 from tests.common import make_problem  # noqa: E402
+from tests.common import _RefModelShim, site_models_for  # noqa: E402
 from tests.test_mixlen_holder import holder_problem, holder_unobserved, mixlen_problem  # noqa: E402
+from tests.test_nonrev import internal_branches, leaf_set, rooted_problem  # noqa: E402
+from iqtree2_b200 import workload as W  # noqa: E402
 
 
 def base(tree, model, rates, props, aln, **extra):
@@ -82,6 +85,48 @@ def main():
         ref.close()
     out.update(settings=np.array(settings, dtype=np.float64), lnl=np.array(vals))
     save("robust_dna", out)
+    # site-specific models (PMSF / ModelSet): SITE_MODEL kernel variants
+    for name, (n, ncat, safe) in {"site_aa": (20, 4, False), "site_dna_safe": (4, 3, True)}.items():
+        tree, _, rates, props, aln = make_problem(9, 61 if n == 20 else 150, nstates=n, ncat=ncat, seed=331, gaps=0.06)
+        models = site_models_for(aln, n, 332)
+        dummy = W.random_reversible_model(n, 1)
+        ref = oracle.RefRun(tree, aln, dummy, rates, props, kernel=oracle.LK_AVX_FMA, safe=safe, site_models=models)
+        out = base(tree, dummy, rates, props, aln, kind="site", safe=ref.safe_numeric, s_eval=models[0], s_evec=models[1],
+                   s_inv=models[2])
+        L = tree.get_length(2, tree.adj[2][0])
+        out["lnl"] = ref.lnl_at_leaf(2)
+        out["pattern_lh"] = ref.pattern_lh()
+        out["derv"] = np.array(ref.derv())
+        out["lnl_buf"] = ref.from_buffer()
+        ref.set_current_length(2.5 * L)
+        out["derv2"] = np.array(ref.derv(again=True))
+        out["lnl_buf2"] = ref.from_buffer()
+        ref.close()
+        save(name, out)
+    # non-reversible family on a rooted tree
+    for name, (n, ncat, nmix) in {"nonrev_dna": (4, 4, 1), "nonrev_aa": (20, 2, 1)}.items():
+        ntaxa = 9
+        tree, nm, rates, props, aln = rooted_problem(ntaxa, 200, n, ncat, nmix, seed=341)
+        ref = oracle.RefRun(tree, aln, _RefModelShim(nm), rates, props, safe=False,
+                            nonrev=(1, nm.Q, nm.ceval, nm.cevec, nm.cinv_evec))
+        out = dict(nstates=aln.nstates, states=aln.states, ptn_freq=aln.ptn_freq, kind="nonrev", ntaxa=ntaxa,
+                   blen=np.array([(a, b, tree.get_length(a, b)) for a, b in tree.branches()]),
+                   adj_pad=np.array([list(x) + [-1] * (3 - len(x)) for x in tree.adj], dtype=np.int32),
+                   Q=nm.Q, ceval=nm.ceval, cevec=nm.cevec, cinv_evec=nm.cinv_evec, freqs=nm.freqs, mixw=nm.mixw,
+                   rates=rates, props=props)
+        cases = [(ntaxa, tree.adj[ntaxa][0]), (0, tree.adj[0][0])] + internal_branches(tree)[:3]
+        res = []
+        for a, b in cases:
+            if tree.is_leaf(a):
+                lnl = ref.lnl_at_leaf(a)
+            else:
+                lnl = ref.lnl_at_branch(leaf_set(tree, b, a), from_taxon=leaf_set(tree, a, b)[0])
+            df, ddf = (0.0, 0.0) if a == ntaxa else ref.derv()
+            res.append((a, b, lnl, df, ddf))
+        out["cases"] = np.array(res)
+        out["pattern_lh"] = ref.pattern_lh()
+        ref.close()
+        save(name, out)
 
 
 if __name__ == "__main__":
