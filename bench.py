@@ -556,6 +556,19 @@ def main():
             line["roofline"]["traffic"] = json.load(open(tr_file)).get(args.workload)
         except Exception:
             pass
+    # physical side of the same kernel: measured DRAM bytes per launch / live launch duration, against the measured
+    # stream ceilings of this pool's B200 (tools/hbm_streams.cu; the 4-state traversal is 98 % writes)
+    st_file = os.path.join(ROOT, "profiles", "r1s_hbm_streams.json")
+    tb = line["roofline"].get("traffic")
+    if tb and partial_ms and partial_launches and os.path.exists(st_file) and n == 4:
+        try:
+            st = json.load(open(st_file))
+            gbs = tb / (partial_ms / partial_launches * 1e-3) / 1e9
+            line["roofline"]["physical"] = {"dram_gbs": gbs, "write_peak_gbs": st["write_t32_gbs"],
+                                            "frac_of_write_peak": gbs / st["write_t32_gbs"],
+                                            "peak_source": "profiles/r1s_hbm_streams.json (write-only stream in the kernel's store shape)"}
+        except Exception:
+            pass
     emit(line)
     if world > 1:
         dist.destroy_process_group()
