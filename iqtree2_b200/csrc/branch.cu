@@ -450,6 +450,44 @@ __global__ void __launch_bounds__(RED_THREADS) derv_kernel(BranchArgs a, int red
     const int block = a.block;
     const double *v0 = a.val, *v1 = a.val + block, *v2 = a.val + 2 * block;
     double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};  // df, ddf | +ASC: prob_const, df_const, ddf_const
+    if (!a.site_eval && block >= 512 && G == 32 && a.tile == 1) {
+        // mixtures (block = 4800 for 60 classes x 4 rates): the three coefficient tables are 115 kB, so a warp that
+        // owns one pattern re-reads them from L2 for every pattern -- three table loads per theta load.  A warp takes
+        // four patterns at a time instead and uses each coefficient four times.
+        constexpr int PP = 4;
+        const int64_t warps_per_grid = (int64_t)gridDim.x * (RED_THREADS / 32);
+        for (int64_t pb = ((int64_t)blockIdx.x * (RED_THREADS / 32) + (threadIdx.x >> 5)) * PP; pb < a.ntot;
+             pb += warps_per_grid * PP) {
+            const double *th[PP];
+            double lh[PP], df[PP], ddf[PP];
+#pragma unroll
+            for (int q = 0; q < PP; q++) {
+                th[q] = a.theta + (size_t)min(pb + q, a.ntot - 1) * block;
+                lh[q] = df[q] = ddf[q] = 0.0;
+            }
+            for (int j = g; j < block; j += 32) {
+                const double w0 = v0[j], w1 = v1[j], w2 = v2[j];
+#pragma unroll
+                for (int q = 0; q < PP; q++) {
+                    const double t = __ldcs(th[q] + j);
+                    lh[q] = fma(w0, t, lh[q]);
+                    df[q] = fma(w1, t, df[q]);
+                    ddf[q] = fma(w2, t, ddf[q]);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < PP; q++) {
+                const double l = group_sum(lh[q], 32), d1 = group_sum(df[q], 32), d2 = group_sum(ddf[q], 32);
+                if (g == 0 && pb + q < a.ntot) derv_accumulate(a, pb + q, l, d1, d2, acc);
+            }
+        }
+        if (a.ntot > a.nptn) block_reduce_store<5>(acc, a.red_partial, red_blocks);
+        else {
+            double acc2[2] = {acc[0], acc[1]};
+            block_reduce_store<2>(acc2, a.red_partial, red_blocks);
+        }
+        return;
+    }
     for (int64_t pb = (int64_t)blockIdx.x * (RED_THREADS / G); pb < a.ntot; pb += groups_per_grid) {
         int64_t p = pb + threadIdx.x / G;  // loop bound is CTA-uniform so every lane reaches the shuffles
         const bool valid = p < a.ntot;

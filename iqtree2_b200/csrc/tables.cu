@@ -22,8 +22,12 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
     }
     const int block = n * ncm, nn = n * n;
     double *echild = tables + ch.echild_off;
+    // grid.z splits the categories of a child over CTAs (mixtures: 240 categories per child); every phase below only
+    // reads what the same category produced, so the CTA-local barriers stay sufficient
+    const int cpc = (ncm + gridDim.z - 1) / gridDim.z, c0 = blockIdx.z * cpc, c1 = min(ncm, c0 + cpc);
+    if (c0 >= c1) return;
     // phase 1: echild
-    for (int idx = threadIdx.x; idx < block * n; idx += blockDim.x) {
+    for (int idx = c0 * nn + threadIdx.x; idx < c1 * nn; idx += blockDim.x) {
         int c = idx / nn, r = idx - c * nn, i = r % n;
         int mm = c / denom;
         // heterotachy: child->getLength(cat_id[c]) (:1017, 1069), one length per category
@@ -32,7 +36,7 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
     }
     // expv[c][i] = exp(eval[m][i] * rate * len): what the 4-state path reads per child (s4.cu)
     double *expv = echild + (size_t)block * n;
-    for (int idx = threadIdx.x; idx < block; idx += blockDim.x) {
+    for (int idx = c0 * n + threadIdx.x; idx < c1 * n; idx += blockDim.x) {
         int c = idx / n, i = idx - c * n;
         expv[idx] = exp(m.eval[(c / denom) * n + i] *
                         (m.rates[c % ncat] * (mixlen ? mixlen[(size_t)ch.src * ncat + c % ncat] : ch.length)));
@@ -44,7 +48,7 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
         __syncthreads();
         double *frag = tables + ch.frag_off;
         const int fc = frag_nt * frag_ks * 32;
-        for (int idx = threadIdx.x; idx < ncm * fc; idx += blockDim.x) {
+        for (int idx = c0 * fc + threadIdx.x; idx < c1 * fc; idx += blockDim.x) {
             int c = idx / fc, r = idx - c * fc;
             int j = r / (frag_ks * 32), s = (r >> 5) % frag_ks, lane = r & 31;
             int x = 8 * j + (lane >> 2), i = 4 * s + (lane & 3);
@@ -55,8 +59,10 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
     __syncthreads();
     double *leaf = tables + ch.leaf_off;
     const int tip_block = n * nmix;
-    for (int idx = threadIdx.x; idx < codes * block; idx += blockDim.x) {
-        int s = idx / block, r = idx - s * block;  // r = c*n + x
+    const int span = (c1 - c0) * n;
+    for (int k = threadIdx.x; k < codes * span; k += blockDim.x) {
+        int s = k / span, r = c0 * n + (k - s * span);  // r = c*n + x
+        const int idx = s * block + r;
         double v;
         if (s == codes - 1) {
             v = 1.0;
@@ -77,7 +83,8 @@ int launch_tables(b200lk_ctx *c, int nchildren) {
     BatchLaunch bl;
     memset(&bl, 0, sizeof(bl));
     if (c->batch) bl = *c->batch;
-    tables_kernel<<<dim3(nchildren, c->batch ? c->batch->n : 1), 256, 0, c->stream>>>(
+    const int zsplit = std::min(64, (c->ncat_mix + 15) / 16);  // <= 16 categories per CTA
+    tables_kernel<<<dim3(nchildren, c->batch ? c->batch->n : 1, zsplit), 256, 0, c->stream>>>(
         c->d_children, c->m, c->tables, c->d.nstates, c->d.ncat, c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes,
         c->dense20 ? 3 : c->dense_nt, c->dense20 ? 5 : 2 * c->dense_nt,
         c->h_child_mixlen ? c->d_child_mixlen : nullptr, bl);
