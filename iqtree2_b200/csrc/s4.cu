@@ -283,16 +283,23 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
 // per context (own model, own branch lengths x partition rate): they are read from the context's device tables
 // (warp-uniform loads through L1) instead of the launch parameters.  Used for many small alignments, where launch
 // count, not per-launch speed, is what matters.
-template <int NCM, bool PLAIN>
-__device__ __forceinline__ void child_apply_batch(const double *U, int denom, const double *ev, double *v) {
+template <int NCM, bool PLAIN, bool SHARED>
+__device__ __forceinline__ void child_apply_batch(const double *U, const double *Ur, int denom, const double *ev, double *v) {
 #pragma unroll
     for (int c = 0; c < NCM; c++) {
         const double *Uc = U + (c / denom) * 16;
         double w[4], f[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) w[i] = __dmul_rn(__ldg(ev + c * 4 + i), v[c * 4 + i]);
+        const double2 e0 = __ldg(reinterpret_cast<const double2 *>(ev + c * 4)), e1 = __ldg(reinterpret_cast<const double2 *>(ev + c * 4) + 1);
+        w[0] = __dmul_rn(e0.x, v[c * 4]);
+        w[1] = __dmul_rn(e0.y, v[c * 4 + 1]);
+        w[2] = __dmul_rn(e1.x, v[c * 4 + 2]);
+        w[3] = __dmul_rn(e1.y, v[c * 4 + 3]);
 #pragma unroll
         for (int x = 0; x < 4; x++) {
+            if (SHARED) {  // one model class: eigenvectors held in registers for the whole traversal
+                f[x] = PLAIN ? s4_plain(Ur + 4 * x, w) : s4_tree(Ur + 4 * x, w);
+                continue;
+            }
             const double u[4] = {__ldg(Uc + 4 * x), __ldg(Uc + 4 * x + 1), __ldg(Uc + 4 * x + 2), __ldg(Uc + 4 * x + 3)};
             f[x] = PLAIN ? s4_plain(u, w) : s4_tree(u, w);
         }
@@ -301,7 +308,7 @@ __device__ __forceinline__ void child_apply_batch(const double *U, int denom, co
     }
 }
 
-template <int NCM, bool SAFE>
+template <int NCM, bool SAFE, bool SHARED>
 __global__ void __launch_bounds__(S4_THREADS, 2) s4_traverse_batch_kernel(const __grid_constant__ S4Launch<NCM> P, BatchLaunch bl) {
     constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
     TravArgs a = P.a;
@@ -316,6 +323,14 @@ __global__ void __launch_bounds__(S4_THREADS, 2) s4_traverse_batch_kernel(const 
     a.ntot = bc.ntot;
     a.ntot_pad = bc.ntot_pad;
     const double *Ug = bc.m.evec, *Mg = bc.m.inv_evec;
+    double Ur[16], Mr[16];  // SHARED (every category uses model class 0): the context's eigenvectors, loaded once
+    if (SHARED) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            Ur[k] = __ldg(Ug + k);
+            Mr[k] = __ldg(Mg + k);
+        }
+    }
     const int64_t p0 = (int64_t)blockIdx.x * S4_THREADS;
     if (p0 >= a.ntot) return;  // smaller context than the grid
     extern __shared__ double2 stk[];
@@ -351,10 +366,10 @@ __global__ void __launch_bounds__(S4_THREADS, 2) s4_traverse_batch_kernel(const 
         unsigned sc = 0;
         child_load<NCM, SAFE>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
         child_load<NCM, SAFE>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
-        if (lk != SRC_LEAF) child_apply_batch<NCM, false>(Ug, a.denom, a.tables + nd.lexp_off, l);
+        if (lk != SRC_LEAF) child_apply_batch<NCM, false, SHARED>(Ug, Ur, a.denom, a.tables + nd.lexp_off, l);
         if (rk != SRC_LEAF) {
-            if (lk == SRC_LEAF) child_apply_batch<NCM, true>(Ug, a.denom, a.tables + nd.rexp_off, r);
-            else child_apply_batch<NCM, false>(Ug, a.denom, a.tables + nd.rexp_off, r);
+            if (lk == SRC_LEAF) child_apply_batch<NCM, true, SHARED>(Ug, Ur, a.denom, a.tables + nd.rexp_off, r);
+            else child_apply_batch<NCM, false, SHARED>(Ug, Ur, a.denom, a.tables + nd.rexp_off, r);
         }
         const bool tiptip = lk == SRC_LEAF && rk == SRC_LEAF;
         unsigned long long mxall = 0ull;
@@ -367,8 +382,13 @@ __global__ void __launch_bounds__(S4_THREADS, 2) s4_traverse_batch_kernel(const 
             unsigned long long mx = 0ull;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-                const double m4[4] = {__ldg(Mc + 4 * k), __ldg(Mc + 4 * k + 1), __ldg(Mc + 4 * k + 2), __ldg(Mc + 4 * k + 3)};
-                const double o = s4_tree(m4, tmp);
+                double o;
+                if (SHARED) {
+                    o = s4_tree(Mr + 4 * k, tmp);
+                } else {
+                    const double m4[4] = {__ldg(Mc + 4 * k), __ldg(Mc + 4 * k + 1), __ldg(Mc + 4 * k + 2), __ldg(Mc + 4 * k + 3)};
+                    o = s4_tree(m4, tmp);
+                }
                 prev[c * 4 + k] = o;
                 const unsigned long long b = abs_bits(o);
                 mx = b > mx ? b : mx;
@@ -565,8 +585,10 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     const size_t smem = (size_t)depth_used * S4_THREADS * (2 * NCM * sizeof(double2) + sizeof(unsigned)) + S4_STATE_BYTES;
     const unsigned grid = (unsigned)(((c->batch ? c->batch->max_ntot : c->ntot) + S4_THREADS - 1) / S4_THREADS);
     if (!c->trav_attr_set) {
-        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
@@ -576,8 +598,10 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     prof_mark(c);
     if (c->batch) {
         const dim3 g2(grid, c->batch->n);
-        if (c->d.safe_numeric) s4_traverse_batch_kernel<NCM, true><<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
-        else s4_traverse_batch_kernel<NCM, false><<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
+        const bool safe = c->d.safe_numeric != 0, one_class = c->d.nmix == 1;
+        auto kern = one_class ? (safe ? s4_traverse_batch_kernel<NCM, true, true> : s4_traverse_batch_kernel<NCM, false, true>)
+                              : (safe ? s4_traverse_batch_kernel<NCM, true, false> : s4_traverse_batch_kernel<NCM, false, false>);
+        kern<<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
     } else if (c->s4_sym) {
         // resident CTAs per SM the registers are sized for: 4 (128 registers) or more with a shallower stack
         static const int minb = [] { const char *e = getenv("B200LK_S4_MINB"); return e ? atoi(e) : S4_MINB; }();
