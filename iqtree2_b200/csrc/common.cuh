@@ -110,7 +110,7 @@ struct b200lk_ctx {
     size_t prog_stride;
     void *h_prog, *h_prog_ring, *d_prog;  // device program of the pattern-stationary traversal (traverse.cu)
     bool trav_attr_set, dense_attr_set, force_level_batched;
-    int max_stack_depth;  // shared-memory stack entries per thread (default 8; B200LK_STACK_DEPTH)
+    int max_stack_depth;  // shared-memory stack entries per thread (B200LK_STACK_DEPTH; -1 = chosen at launch)
     cudaEvent_t stage_ev[B200_STAGE_RING];
     bool stage_used[B200_STAGE_RING];
     int stage_idx;

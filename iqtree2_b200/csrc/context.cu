@@ -75,8 +75,8 @@ static int alloc_all(b200lk_ctx *c) {
     c->h_prog = c->h_prog_ring;
     {
         const char *sd = getenv("B200LK_STACK_DEPTH");  // test hook: force the stack-overflow path
-        c->max_stack_depth = sd ? atoi(sd) : 3;  // 3 entries keep 4 CTAs per SM resident (measured best on cfg2)
-        if (c->max_stack_depth < 0) c->max_stack_depth = 0;
+        c->max_stack_depth = sd ? atoi(sd) : -1;  // -1: chosen per kernel at launch (s4.cu, measured on cfg2)
+        if (sd && c->max_stack_depth < 0) c->max_stack_depth = 0;
         if (c->max_stack_depth > 12) c->max_stack_depth = 12;
     }
     c->h_nodes = c->h_nodes_ring;

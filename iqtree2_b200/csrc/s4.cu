@@ -76,7 +76,7 @@ struct S4Launch {
 #define S4_THREADS 128
 #define S4_THRESHOLD_HI 0x2ff00000  // high word of 2^-256 = B200_SCALING_THRESHOLD (exponent 1023 - 256, mantissa 0)
 #ifndef S4_MINB
-#define S4_MINB 4  // resident CTAs per SM the register allocation is sized for
+#define S4_MINB 5  // resident CTAs per SM the register allocation is sized for (SYM kernels; the general ones use 4)
 #endif
 #define S4_STATE_BYTES 4096  // staged tip states per CTA: chunk rows x S4_THREADS patterns
 
@@ -145,14 +145,17 @@ __device__ __forceinline__ void child_load(const TravArgs &a, int kind, int id, 
 
 // internal child: v <- U (expv (.) v) per category, in place
 template <int NCM, bool PLAIN, bool SYM = false>
-__device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const double *ev, double *v) {
+__device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const double *ev, double *v, const double *Ur = nullptr) {
 #pragma unroll
     for (int c = 0; c < NCM; c++) {
         double w[4], f[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) w[i] = __dmul_rn(ev[c * 4 + i], v[c * 4 + i]);
 #pragma unroll
-        for (int x = 0; x < 4; x++) f[x] = PLAIN ? s4_plain(&mdl.U[SYM ? 0 : c][4 * x], w) : s4_tree(&mdl.U[SYM ? 0 : c][4 * x], w);
+        for (int x = 0; x < 4; x++) {
+            const double *u = SYM ? Ur + 4 * x : &mdl.U[c][4 * x];  // SYM: register copy of the shared eigenvectors
+            f[x] = PLAIN ? s4_plain(u, w) : s4_tree(u, w);
+        }
 #pragma unroll
         for (int x = 0; x < 4; x++) v[c * 4 + x] = f[x];
     }
@@ -164,6 +167,9 @@ __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const doubl
 // reduction tree over x -- so only U and pi (40 uniform registers) are live across the node loop instead of U and M
 // (64: more than the uniform register file holds, which made the kernel re-load both for every category of every
 // node; that constant traffic, not HBM, was what bounded it -- profiles/r1s_s4_experiments.log).  P.mdl.M[0][0..3] = pi.
+// The 20 values are copied into vector registers once per thread (through shared memory, so that the compiler cannot
+// turn them back into constant-bank reads); the kernel then fits 96 registers: five resident CTAs per SM with two
+// stack entries (profiles/r1t_s4_ureg_ab.log).
 template <int NCM, bool SAFE, bool SYM, int MINB = S4_MINB>
 __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __grid_constant__ S4Launch<NCM> P) {
     constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
@@ -183,6 +189,19 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
 #pragma unroll
     for (int j = 0; j < BLOCK; j++) prev[j] = 0.0;
     unsigned prev_sc = 0;
+    double Ur[16], pir[4];
+    if (SYM) {
+        // through shared memory so that the values live in vector registers for the whole loop instead of being
+        // re-read from the constant bank into uniform registers by every code path of every node
+        __shared__ double u_sh[20];
+        if (tid < 16) u_sh[tid] = P.mdl.U[0][tid];
+        else if (tid < 20) u_sh[tid] = P.mdl.M[0][tid - 16];
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 16; j++) Ur[j] = reinterpret_cast<volatile double *>(u_sh)[j];
+#pragma unroll
+        for (int j = 0; j < 4; j++) pir[j] = reinterpret_cast<volatile double *>(u_sh)[16 + j];
+    }
 
     for (int i = 0; i < a.nnodes; i++) {
         const PNode<NCM> &nd = P.nodes[i];  // constant bank, uniform index
@@ -206,10 +225,10 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
         unsigned sc = 0;
         child_load<NCM, SAFE>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
         child_load<NCM, SAFE>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
-        if (lk != SRC_LEAF) child_apply<NCM, false, SYM>(P.mdl, nd.lexp, l);
+        if (lk != SRC_LEAF) child_apply<NCM, false, SYM>(P.mdl, nd.lexp, l, Ur);
         if (rk != SRC_LEAF) {
-            if (lk == SRC_LEAF) child_apply<NCM, true, SYM>(P.mdl, nd.rexp, r);   // tip-internal: dotProductVec (:1853)
-            else child_apply<NCM, false, SYM>(P.mdl, nd.rexp, r);                 // internal-internal (:1975-1983)
+            if (lk == SRC_LEAF) child_apply<NCM, true, SYM>(P.mdl, nd.rexp, r, Ur);   // tip-internal: dotProductVec (:1853)
+            else child_apply<NCM, false, SYM>(P.mdl, nd.rexp, r, Ur);                 // internal-internal (:1975-1983)
         }
         // ---- product, back to eigen-space (productVecMat), rescale --------------------------------
         const bool tiptip = lk == SRC_LEAF && rk == SRC_LEAF;
@@ -221,14 +240,14 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
             for (int x = 0; x < 4; x++) tmp[x] = __dmul_rn(l[c * 4 + x], r[c * 4 + x]);
             if (SYM) {
 #pragma unroll
-                for (int x = 0; x < 4; x++) tmp[x] = __dmul_rn(tmp[x], P.mdl.M[0][x]);  // pi[x]
+                for (int x = 0; x < 4; x++) tmp[x] = __dmul_rn(tmp[x], pir[x]);
             }
             int mx = 0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
                 double o;
                 if (SYM) {
-                    const double ut[4] = {P.mdl.U[0][k], P.mdl.U[0][4 + k], P.mdl.U[0][8 + k], P.mdl.U[0][12 + k]};
+                    const double ut[4] = {Ur[k], Ur[4 + k], Ur[8 + k], Ur[12 + k]};
                     o = s4_tree(ut, tmp);
                 } else {
                     o = s4_tree(&P.mdl.M[c][4 * k], tmp);
@@ -491,7 +510,8 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     if (!Lp) Lp = new S4Launch<NCM>();
     S4Launch<NCM> &P = *Lp;
     const int nslots = c->d.nslots;
-    const int max_depth = c->max_stack_depth;
+    // unset: two entries for the SYM kernel (five resident CTAs per SM), three otherwise (four)
+    const int max_depth = c->max_stack_depth >= 0 ? c->max_stack_depth : (c->s4_sym && !c->batch ? 2 : 3);
     std::vector<int> producer(nslots, -1);  // slot -> index of the node of this launch that last wrote it
     std::vector<int> consumer(count, -1);   // node -> index of the node that consumes its output
     for (int i = 0; i < count; i++) {
@@ -589,8 +609,8 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         c->trav_attr_set = true;
@@ -603,16 +623,16 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
                               : (safe ? s4_traverse_batch_kernel<NCM, true, false> : s4_traverse_batch_kernel<NCM, false, false>);
         kern<<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
     } else if (c->s4_sym) {
-        // resident CTAs per SM the registers are sized for: 4 (128 registers) or more with a shallower stack
+        // resident CTAs per SM the registers are sized for: 5 (96 registers, two stack entries) unless overridden
         static const int minb = [] { const char *e = getenv("B200LK_S4_MINB"); return e ? atoi(e) : S4_MINB; }();
         const bool safe = c->d.safe_numeric != 0;
         auto kern = safe ? s4_traverse_kernel<NCM, true, true, S4_MINB> : s4_traverse_kernel<NCM, false, true, S4_MINB>;
-        if (minb == 5) kern = safe ? s4_traverse_kernel<NCM, true, true, 5> : s4_traverse_kernel<NCM, false, true, 5>;
+        if (minb == 4) kern = safe ? s4_traverse_kernel<NCM, true, true, 4> : s4_traverse_kernel<NCM, false, true, 4>;
         if (minb == 6) kern = safe ? s4_traverse_kernel<NCM, true, true, 6> : s4_traverse_kernel<NCM, false, true, 6>;
         if (minb != S4_MINB) CUDA_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         kern<<<grid, S4_THREADS, smem, c->stream>>>(P);
-    } else if (c->d.safe_numeric) s4_traverse_kernel<NCM, true, false><<<grid, S4_THREADS, smem, c->stream>>>(P);
-    else s4_traverse_kernel<NCM, false, false><<<grid, S4_THREADS, smem, c->stream>>>(P);
+    } else if (c->d.safe_numeric) s4_traverse_kernel<NCM, true, false, 4><<<grid, S4_THREADS, smem, c->stream>>>(P);
+    else s4_traverse_kernel<NCM, false, false, 4><<<grid, S4_THREADS, smem, c->stream>>>(P);
     prof_mark(c);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;
