@@ -624,7 +624,8 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         kern<<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
     } else if (c->s4_sym) {
         // resident CTAs per SM the registers are sized for: 5 (96 registers, two stack entries) unless overridden
-        static const int minb = [] { const char *e = getenv("B200LK_S4_MINB"); return e ? atoi(e) : S4_MINB; }();
+        const char *mb = getenv("B200LK_S4_MINB");  // test / sweep hook: the 4- and 6-CTA instantiations
+        const int minb = mb ? atoi(mb) : S4_MINB;
         const bool safe = c->d.safe_numeric != 0;
         auto kern = safe ? s4_traverse_kernel<NCM, true, true, S4_MINB> : s4_traverse_kernel<NCM, false, true, S4_MINB>;
         if (minb == 4) kern = safe ? s4_traverse_kernel<NCM, true, true, 4> : s4_traverse_kernel<NCM, false, true, 4>;

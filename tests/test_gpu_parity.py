@@ -114,12 +114,14 @@ def test_large_problem_properties():
 
 
 @pytest.mark.parametrize("env", [{"B200LK_LEVEL_BATCHED": "1"}, {"B200LK_STACK_DEPTH": "0"},
-                                 {"B200LK_STACK_DEPTH": "1"}, {}])
+                                 {"B200LK_STACK_DEPTH": "1"}, {"B200LK_STACK_DEPTH": "3"}, {"B200LK_S4_SYM": "0"},
+                                 {"B200LK_S4_MINB": "4"}, {"B200LK_S4_MINB": "6", "B200LK_STACK_DEPTH": "1"}, {}])
 @pytest.mark.parametrize("safe", [False, True])
 def test_dna_paths_agree_with_oracle(oracle_lib, monkeypatch, env, safe):
     """The 4-state traversal has three routes -- one pattern-stationary launch (default), the same with
-    the shared-memory stack overflowing into global re-reads, and the level-batched kernels -- and all
-    of them must match the oracle, scale counts included (deep tree so that rescaling fires)."""
+    the shared-memory stack overflowing into global re-reads, and the level-batched kernels -- plus the
+    general (non-SYM) kernel and the other register-budget instantiations of the SYM one; all of them
+    must match the oracle, scale counts included (deep tree so that rescaling fires)."""
     for k, v in env.items():
         monkeypatch.setenv(k, v)
     tree, model, rates, props, aln = make_problem(300, 300, seed=5, mean_len=0.4, gaps=0.02)
