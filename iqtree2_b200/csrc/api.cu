@@ -318,10 +318,9 @@ extern "C" int b200lk_optimize_branch(b200lk_ctx *c, b200lk_end dad, b200lk_end 
         if (nsteps) *nsteps = 0;
         return B200LK_OK;
     }
-    rc = launch_theta(c, dad, node);
-    if (rc) return rc;
-    c->theta_computed = true;
-    rc = launch_newton(c, nr);
+    const b200lk_end ends[2] = {dad, node};
+    rc = launch_newton(c, nr, ends);  // theta for the branch, then the iteration (one launch on the T32 layout)
+    if (rc == B200LK_OK || rc == B200LK_ERR_UNSUPPORTED) c->theta_computed = true;  // refused: theta is built all the same
     if (rc) return rc;
     rc = read_results(c, 4, 4);  // optx, d2l, evaluations, status: the only D2H of the whole iteration
     if (rc) return rc;

@@ -185,11 +185,8 @@ __device__ __forceinline__ void t32_load(const double *base, int64_t p, double *
 }
 // lh, df, ddf = sum_e val{0,1,2}[e] * theta[p][e]; sv = [3][block] in shared memory
 template <int PAIRS>
-__device__ __forceinline__ void t32_triple(const double *theta, int64_t p, const double *sv, double &lh, double &df,
-                                           double &ddf) {
+__device__ __forceinline__ void t32_triple_regs(const double *t, const double *sv, double &lh, double &df, double &ddf) {
     constexpr int B = 2 * PAIRS;
-    double t[B];
-    t32_load<PAIRS>(theta, p, t);
     double l0 = 0.0, l1 = 0.0, d0 = 0.0, d1 = 0.0, e0 = 0.0, e1 = 0.0;  // two interleaved accumulators, as dotProductTriple
 #pragma unroll
     for (int j = 0; j < PAIRS; j++) {
@@ -203,6 +200,13 @@ __device__ __forceinline__ void t32_triple(const double *theta, int64_t p, const
     lh = l0 + l1;
     df = d0 + d1;
     ddf = e0 + e1;
+}
+template <int PAIRS>
+__device__ __forceinline__ void t32_triple(const double *theta, int64_t p, const double *sv, double &lh, double &df,
+                                           double &ddf) {
+    double t[2 * PAIRS];
+    t32_load<PAIRS>(theta, p, t);
+    t32_triple_regs<PAIRS>(t, sv, lh, df, ddf);
 }
 // per-pattern epilogue of computeLikelihoodDerv (:2494-2534), shared by the generic and the T32 kernels
 __device__ __forceinline__ void derv_accumulate(const BranchArgs &a, int64_t p, double lh, double df, double ddf,
@@ -276,11 +280,11 @@ __device__ __forceinline__ void frombuf_t32(const BranchArgs &a, int red_blocks)
     block_reduce_store<2>(acc, a.red_partial, red_blocks);
 }
 // theta (computeLikelihoodBuffer) and the branch lnL on T32: NCM = categories = PAIRS / 2
+// one pattern: theta[p] is stored AND left in th_out (the fused first Newton-Raphson evaluation reads it from there)
 template <int PAIRS>
-__device__ __forceinline__ void theta_t32(const BranchArgs &a) {
+__device__ __forceinline__ void theta_t32_pattern(const BranchArgs &a, int64_t p, bool tip_mode, double *th_out) {
     constexpr int B = 2 * PAIRS, NCM = PAIRS / 2;
-    const bool tip_mode = a.pnode == nullptr;
-    for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < a.ntot; p += (int64_t)gridDim.x * RED_THREADS) {
+    {
         double d[B], o[B];
         t32_load<PAIRS>(a.pdad, p, d);
         int sc[NCM], min_scale;
@@ -314,9 +318,28 @@ __device__ __forceinline__ void theta_t32(const BranchArgs &a) {
                 else if (s > min_scale + 1) { t0 = 0.0; t1 = 0.0; }
             }
             th[j * 32] = make_double2(t0, t1);
+            th_out[2 * j] = t0;
+            th_out[2 * j + 1] = t1;
         }
         a.buffer_scale_all[p] = (double)min_scale * B200_LOG_SCALING_THRESHOLD;
     }
+}
+template <int PAIRS>
+__device__ __forceinline__ void theta_t32(const BranchArgs &a) {
+    const bool tip_mode = a.pnode == nullptr;
+    for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < a.ntot; p += (int64_t)gridDim.x * RED_THREADS) {
+        double t[2 * PAIRS];
+        theta_t32_pattern<PAIRS>(a, p, tip_mode, t);
+    }
+}
+// first evaluation of the device Newton-Raphson loop fused with the theta pass: theta is formed from the two partial
+// vectors, stored for the later iterations, and its triple product taken from registers
+template <int PAIRS>
+__device__ __forceinline__ void theta_triple_t32(const BranchArgs &a, int64_t p, bool tip_mode, const double *sv, double &lh,
+                                                 double &df, double &ddf) {
+    double t[2 * PAIRS];
+    theta_t32_pattern<PAIRS>(a, p, tip_mode, t);
+    t32_triple_regs<PAIRS>(t, sv, lh, df, ddf);
 }
 template <int PAIRS>
 __device__ __forceinline__ void lnl_t32(const BranchArgs &a, int red_blocks) {
@@ -554,7 +577,7 @@ struct NewtonArgs {
     double *red;  // [2 parities][2][red_blocks]
 };
 
-__global__ void __launch_bounds__(RED_THREADS) newton_kernel(BranchArgs a, NewtonArgs nr, int red_blocks) {
+__global__ void __launch_bounds__(RED_THREADS) newton_kernel(BranchArgs a, NewtonArgs nr, int red_blocks, int fuse_theta) {
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     extern __shared__ double sval[];  // [3][block]
     __shared__ double sh_red[RED_THREADS];
@@ -583,6 +606,15 @@ __global__ void __launch_bounds__(RED_THREADS) newton_kernel(BranchArgs a, Newto
         if (a.tile == 32) {  // thread per pattern, 128-bit loads (see the T32 fast paths above)
             for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < a.nptn; p += (int64_t)gridDim.x * RED_THREADS) {
                 double lh, df, ddf;
+                if (fuse_theta && iter == 0) {  // theta does not exist yet: build it on the way (b200lk_optimize_branch)
+                    const bool tip_mode = a.pnode == nullptr;
+                    switch (block) {
+                        case 4: theta_triple_t32<2>(a, p, tip_mode, sval, lh, df, ddf); break;
+                        case 8: theta_triple_t32<4>(a, p, tip_mode, sval, lh, df, ddf); break;
+                        case 12: theta_triple_t32<6>(a, p, tip_mode, sval, lh, df, ddf); break;
+                        default: theta_triple_t32<8>(a, p, tip_mode, sval, lh, df, ddf); break;
+                    }
+                } else
                 switch (block) {
                     case 4: t32_triple<2>(a.theta, p, sval, lh, df, ddf); break;
                     case 8: t32_triple<4>(a.theta, p, sval, lh, df, ddf); break;
@@ -1012,11 +1044,22 @@ int launch_from_buffer(b200lk_ctx *c, double length) {
     return launch_asc_fix(c, 0);
 }
 
-// b200lk_optimize_branch: theta for (dad, node) must already be built
-int launch_newton(b200lk_ctx *c, const b200lk_newton *nr) {
+// b200lk_optimize_branch.  ends == nullptr: theta for the branch is already built.  Otherwise ends = {dad, node} and theta is
+// built here: inside the first iteration on the T32 layout (one launch and one pass over theta less per branch), by
+// theta_kernel first everywhere else.
+bool newton_fuses_theta(const b200lk_ctx *c) {
+    return c->tile == 32 && !c->site && !c->nonrev && !c->batch && c->d.n_unobserved == 0 && c->ntot == c->d.nptn;
+}
+int launch_newton(b200lk_ctx *c, const b200lk_newton *nr, const b200lk_end *ends) {
+    int fuse_theta = ends && newton_fuses_theta(c);
+    if (ends && !fuse_theta) {
+        int rc = launch_theta(c, ends[0], ends[1]);
+        if (rc) return rc;
+    }
     if (c->site) return B200LK_ERR_UNSUPPORTED;  // per-pattern coefficients: the host iteration drives b200lk_derv
     BranchArgs a;
-    memset(&a, 0, sizeof(a));
+    if (fuse_theta) fill_args(c, a, ends[0], ends[1]);
+    else memset(&a, 0, sizeof(a));
     fill_common(c, a);
     a.G = pick_group(c->block);
     NewtonArgs na;
@@ -1032,17 +1075,24 @@ int launch_newton(b200lk_ctx *c, const b200lk_newton *nr) {
     na.red = c->red_partial;  // [2 parities][2][red_blocks] of its 8 * red_blocks doubles
     const size_t smem = sizeof(double) * 3 * c->block;
     if (smem > 200 * 1024 || c->d.n_unobserved > 0) return B200LK_ERR_UNSUPPORTED;  // +ASC: host-driven iteration
+    auto unsupported = [&]() {  // the caller falls back to the host-driven iteration, which expects theta to exist
+        if (fuse_theta) {
+            int rc = launch_theta(c, ends[0], ends[1]);
+            if (rc) return rc;
+        }
+        return (int)B200LK_ERR_UNSUPPORTED;
+    };
     if (smem > 48 * 1024)
         CUDA_TRY(c, cudaFuncSetAttribute(newton_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0, sms = 148, coop = 0;
     CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, newton_kernel, RED_THREADS, smem));
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device);
-    if (!coop || per_sm < 1) return B200LK_ERR_UNSUPPORTED;
+    if (!coop || per_sm < 1) return unsupported();
     int grid = grid_for(c, a.G, c->d.nptn);
     if (grid > per_sm * sms) grid = per_sm * sms;
     int red_blocks = c->red_blocks;
-    void *args[] = {&a, &na, &red_blocks};
+    void *args[] = {&a, &na, &red_blocks, &fuse_theta};
     CUDA_TRY(c, cudaLaunchCooperativeKernel((void *)newton_kernel, dim3(grid), dim3(RED_THREADS), args, smem, c->stream));
     c->n_launches++;
     return B200LK_OK;
