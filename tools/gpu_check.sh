@@ -1,6 +1,6 @@
 #!/bin/bash
 # One GPU-box pass.  Usage (repo root, on the GPU box): bash tools/gpu_check.sh <tag> [stages...]
-# stages: test bench bench45 launches launches5 traffic prof_s4 prof_d20   (default: test bench)
+# stages: test bench bench45 sweep launches launches5 traffic prof_s4 prof_d20   (default: test bench)
 # gpurun copies back at most 64 MiB of gpurun_out/: keep full ncu captures to a few launches.
 TAG=${1:-rX}; shift
 STAGES=${@:-test bench}
@@ -29,6 +29,11 @@ if has bench45; then
 python bench.py --workload cfg4 --steps 5 > $OUT/bench_cfg4_$TAG.json 2> $OUT/bench_cfg4_$TAG.err
 python bench.py --workload cfg5 --steps 5 > $OUT/bench_cfg5_$TAG.json 2> $OUT/bench_cfg5_$TAG.err
 cut -c1-300 $OUT/bench_cfg4_$TAG.json; cut -c1-300 $OUT/bench_cfg5_$TAG.json
+fi
+if has sweep; then
+# one optimizeAllBranches sweep of cfg2 through the host mirror against the reference's own sweep on the host cores
+python tools/sweep_bench.py > $OUT/sweep_cfg2_$TAG.json 2> $OUT/sweep_cfg2_$TAG.err
+cut -c1-400 $OUT/sweep_cfg2_$TAG.json
 fi
 if has launches5; then
 # cfg5 through the batched partition dispatch: 4 evaluations (3 warm-up + 1 timed) of ~30 launches each
