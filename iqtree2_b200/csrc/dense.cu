@@ -690,9 +690,11 @@ __global__ void __launch_bounds__(DN_THREADS, 3) dense20_rp_kernel(DenseArgs a, 
                 }
                 if (p[mt] < a.ntot) {
                     double *po = out_base + (size_t)p[mt] * block + c * 20 + 2 * q;
-                    *reinterpret_cast<double2 *>(po) = make_double2(o[0], o[1]);
-                    *reinterpret_cast<double2 *>(po + 8) = make_double2(o[2], o[3]);
-                    if (q < 2) *reinterpret_cast<double2 *>(po + 16) = make_double2(o[4], o[5]);
+                    // streaming stores: the vector is next read a level later, after more than an L2 of other writes
+                    // (cfg3 33.6 -> 32.7 ms, profiles/r1t_dense20_stream_ab.log; streaming LOADS of the children cost 5 %)
+                    __stcs(reinterpret_cast<double2 *>(po), make_double2(o[0], o[1]));
+                    __stcs(reinterpret_cast<double2 *>(po + 8), make_double2(o[2], o[3]));
+                    if (q < 2) __stcs(reinterpret_cast<double2 *>(po + 16), make_double2(o[4], o[5]));
                     if (SAFE && q == 0) sc_out[p[mt] * ncm + c] = (uint8_t)sc;
                 }
             }
