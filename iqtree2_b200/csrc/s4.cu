@@ -642,8 +642,34 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
 
 template <int NCM>
 static int launch_run(b200lk_ctx *c, const b200lk_node *nl, int count, int *seq_used) {
+    constexpr int MAXN = S4Launch<NCM>::MAXN;
+    // A list longer than one launch's parameter space is cut where the fewest vectors are live across the cut (each
+    // of them is re-read from HBM by the next launch instead of coming from registers or the stack):
+    // live[s] = #{i < s : the node consuming i's output has index >= s}.
+    std::vector<int> live;
+    if (count > MAXN) {
+        std::vector<int> producer(c->d.nslots, -1), diff(count + 2, 0);
+        for (int i = 0; i < count; i++) {
+            for (int k = 0; k < 2; k++) {
+                const DevChild &ch = c->h_children[nl[i].child_begin + k];
+                if (ch.kind == B200LK_CHILD_LEAF || producer[ch.id] < 0) continue;
+                diff[producer[ch.id] + 1]++;  // cuts s in (producer, i] separate the two
+                diff[i + 1]--;
+                producer[ch.id] = -1;
+            }
+            producer[nl[i].out_slot] = i;
+        }
+        live.assign(count + 1, 0);
+        for (int s2 = 1; s2 <= count; s2++) live[s2] = live[s2 - 1] + diff[s2];
+    }
     for (int done = 0; done < count;) {
-        const int seg = std::min(count - done, (int)S4Launch<NCM>::MAXN);
+        int seg = std::min(count - done, MAXN);
+        if (count - done > MAXN) {
+            const int launches_left = (count - done + MAXN - 1) / MAXN;  // keep the launch count minimal
+            const int lo = std::max(1, count - done - (launches_left - 1) * MAXN);
+            for (int t = lo; t <= MAXN; t++)
+                if (live[done + t] <= live[done + seg]) seg = t;
+        }
         int rc = launch_segment<NCM>(c, nl + done, seg, seq_used);
         if (rc) return rc;
         done += seg;
