@@ -73,10 +73,12 @@ struct S4Launch {
     PNode<NCM> nodes[MAXN];
 };
 
-#define S4_THREADS 128
+#ifndef S4_THREADS
+#define S4_THREADS 64  // two warps per CTA: 4.71 ms per cfg2 traversal against 5.03 ms with four (profiles/r1t_s4_cta64_ab.log)
+#endif
 #define S4_THRESHOLD_HI 0x2ff00000  // high word of 2^-256 = B200_SCALING_THRESHOLD (exponent 1023 - 256, mantissa 0)
 #ifndef S4_MINB
-#define S4_MINB 5  // resident CTAs per SM the register allocation is sized for (SYM kernels; the general ones use 4)
+#define S4_MINB 10  // resident CTAs per SM the register allocation is sized for (SYM kernels: 96 registers; the general ones use 8)
 #endif
 #define S4_STATE_BYTES 4096  // staged tip states per CTA: chunk rows x S4_THREADS patterns
 
@@ -169,7 +171,7 @@ __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const doubl
 // node; that constant traffic, not HBM, was what bounded it -- profiles/r1s_s4_experiments.log).  P.mdl.M[0][0..3] = pi.
 // The 20 values are copied into vector registers once per thread (through shared memory, so that the compiler cannot
 // turn them back into constant-bank reads); the kernel then fits 96 registers: five resident CTAs per SM with two
-// stack entries (profiles/r1t_s4_ureg_ab.log).
+// stack entries (profiles/r1t_s4_ureg_ab.log), later as ten CTAs of 64 threads.
 template <int NCM, bool SAFE, bool SYM, int MINB = S4_MINB>
 __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __grid_constant__ S4Launch<NCM> P) {
     constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
@@ -510,7 +512,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     if (!Lp) Lp = new S4Launch<NCM>();
     S4Launch<NCM> &P = *Lp;
     const int nslots = c->d.nslots;
-    // unset: two entries for the SYM kernel (five resident CTAs per SM), three otherwise (four)
+    // unset: two entries for the SYM kernel (ten resident CTAs of 64 threads per SM), three otherwise (eight)
     const int max_depth = c->max_stack_depth >= 0 ? c->max_stack_depth : (c->s4_sym && !c->batch ? 2 : 3);
     std::vector<int> producer(nslots, -1);  // slot -> index of the node of this launch that last wrote it
     std::vector<int> consumer(count, -1);   // node -> index of the node that consumes its output
@@ -609,8 +611,8 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_batch_kernel<NCM, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         c->trav_attr_set = true;
@@ -623,17 +625,17 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
                               : (safe ? s4_traverse_batch_kernel<NCM, true, false> : s4_traverse_batch_kernel<NCM, false, false>);
         kern<<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
     } else if (c->s4_sym) {
-        // resident CTAs per SM the registers are sized for: 5 (96 registers, two stack entries) unless overridden
-        const char *mb = getenv("B200LK_S4_MINB");  // test / sweep hook: the 4- and 6-CTA instantiations
+        // resident CTAs per SM the registers are sized for: 10 x 64 threads (96 registers, two stack entries) unless overridden
+        const char *mb = getenv("B200LK_S4_MINB");  // test / sweep hook: the 8- and 12-CTA instantiations
         const int minb = mb ? atoi(mb) : S4_MINB;
         const bool safe = c->d.safe_numeric != 0;
         auto kern = safe ? s4_traverse_kernel<NCM, true, true, S4_MINB> : s4_traverse_kernel<NCM, false, true, S4_MINB>;
-        if (minb == 4) kern = safe ? s4_traverse_kernel<NCM, true, true, 4> : s4_traverse_kernel<NCM, false, true, 4>;
-        if (minb == 6) kern = safe ? s4_traverse_kernel<NCM, true, true, 6> : s4_traverse_kernel<NCM, false, true, 6>;
+        if (minb == 8) kern = safe ? s4_traverse_kernel<NCM, true, true, 8> : s4_traverse_kernel<NCM, false, true, 8>;
+        if (minb == 12) kern = safe ? s4_traverse_kernel<NCM, true, true, 12> : s4_traverse_kernel<NCM, false, true, 12>;
         if (minb != S4_MINB) CUDA_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         kern<<<grid, S4_THREADS, smem, c->stream>>>(P);
-    } else if (c->d.safe_numeric) s4_traverse_kernel<NCM, true, false, 4><<<grid, S4_THREADS, smem, c->stream>>>(P);
-    else s4_traverse_kernel<NCM, false, false, 4><<<grid, S4_THREADS, smem, c->stream>>>(P);
+    } else if (c->d.safe_numeric) s4_traverse_kernel<NCM, true, false, 8><<<grid, S4_THREADS, smem, c->stream>>>(P);
+    else s4_traverse_kernel<NCM, false, false, 8><<<grid, S4_THREADS, smem, c->stream>>>(P);
     prof_mark(c);
     CUDA_TRY(c, cudaGetLastError());
     c->n_launches++;

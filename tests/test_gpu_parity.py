@@ -115,7 +115,7 @@ def test_large_problem_properties():
 
 @pytest.mark.parametrize("env", [{"B200LK_LEVEL_BATCHED": "1"}, {"B200LK_STACK_DEPTH": "0"},
                                  {"B200LK_STACK_DEPTH": "1"}, {"B200LK_STACK_DEPTH": "3"}, {"B200LK_S4_SYM": "0"},
-                                 {"B200LK_S4_MINB": "4"}, {"B200LK_S4_MINB": "6", "B200LK_STACK_DEPTH": "1"}, {}])
+                                 {"B200LK_S4_MINB": "8"}, {"B200LK_S4_MINB": "12", "B200LK_STACK_DEPTH": "1"}, {}])
 @pytest.mark.parametrize("safe", [False, True])
 def test_dna_paths_agree_with_oracle(oracle_lib, monkeypatch, env, safe):
     """The 4-state traversal has three routes -- one pattern-stationary launch (default), the same with
