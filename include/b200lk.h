@@ -202,6 +202,23 @@ int b200lk_derv(b200lk_ctx *ctx, double length, double *df, double *ddf);
 /* computeLikelihoodFromBuffer*SIMD (tree/phylokernelnew.h:3196-3392) from theta_all. */
 int b200lk_lnl_from_buffer(b200lk_ctx *ctx, double length, double *lnl);
 
+/* b200lk_lnl_from_buffer for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.  Same
+ * inputs (theta_all of the last b200lk_build_theta / b200lk_evaluate / b200lk_optimize_branch, the model, `length`),
+ * same outputs (*lnl, _pattern_lh on the device) as b200lk_lnl_from_buffer, but the scratch of the computation -- the
+ * branch coefficient table val[3][nstates*ncat_mix] and the per-CTA partial sums -- lives in one file-scope
+ * `static __device__` array of the library (B200LK_NOALLOC_SCRATCH_BYTES on every GPU that loads it, until exit)
+ * whose device address is looked up once per device at b200lk_create.  The call allocates and frees nothing.
+ * Limits: nstates * ncat_mix <= B200LK_NOALLOC_MAX_BLOCK, otherwise B200LK_ERR_ARG with a message in
+ * b200lk_last_error; reversible, non-site-specific contexts without Holder's +ASC and without mixed branch lengths
+ * (B200LK_ERR_UNSUPPORTED otherwise).  The array is SHARED by every call on a device and keeps the last call's
+ * contents (each call overwrites all it reads, nothing needs clearing): calls that overlap on one GPU -- two streams,
+ * two host threads, two contexts -- race on it; serialise them. */
+#define B200LK_NOALLOC_MAX_BLOCK 4800 /* doubles per pattern: LG+C60+G4 (20 states x 240 categories) still fits */
+#define B200LK_NOALLOC_MAX_CTAS 2048  /* per-CTA partial sums kept: 2 per CTA */
+#define B200LK_NOALLOC_SCRATCH_BYTES (8 * (3 * B200LK_NOALLOC_MAX_BLOCK + 2 * B200LK_NOALLOC_MAX_CTAS)) /* 147 968 */
+int b200lk_lnl_from_buffer_noalloc(b200lk_ctx *ctx, double length, double *lnl);
+
 /* ---- +ASC flavour -------------------------------------------------------- */
 /* Which ascertainment-bias correction the unobserved patterns stand for (model_factory->getASC(), utils/tools.h:549-555).
  * B200LK_ASC_LEWIS (the default when dims.n_unobserved > 0): the sum of their likelihoods is the probability of an

@@ -204,6 +204,14 @@ class Engine:
         self.last_status = self._check(f(self.ctx, length, C.byref(out)))
         return out.value
 
+    def lnl_from_buffer_noalloc(self, length):
+        """b200lk_lnl_from_buffer_noalloc: the same result from the library's static device scratch (no allocation)."""
+        out = C.c_double()
+        f = self._f("lnl_from_buffer_noalloc")
+        f.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_double)]
+        self.last_status = self._check(f(self.ctx, length, C.byref(out)))
+        return out.value
+
     # -- +ASC flavour, heterotachy ---------------------------------------------
     def set_asc(self, holder):
         """0 / False: Lewis (default with unobserved patterns); 1 / True: Holder's correction for missing data

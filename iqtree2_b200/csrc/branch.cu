@@ -1340,3 +1340,92 @@ int launch_derv_mixlen_class(b200lk_ctx *c, int cls, double length) {
     c->n_launches += 2;
     return launch_asc_fix(c, 1);
 }
+
+// ---- b200lk_lnl_from_buffer_noalloc: from-buffer lnL whose scratch lives in a file-scope device array ----------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch that
+// b200lk_lnl_from_buffer keeps in per-context cudaMalloc'ed buffers -- the branch coefficient table val[3][block] and
+// the per-CTA partial sums [2][grid] -- lives here in ONE static array per GPU that loads the library.  Every call on
+// a device shares it and it keeps the last call's contents: the kernels overwrite every entry they later read (val for
+// all 3*block entries, the partial sums for every launched CTA), so nothing has to start at zero; calls that overlap
+// on the same GPU (two streams, two host threads) race on it.
+#define NOALLOC_VAL_DOUBLES (3 * B200LK_NOALLOC_MAX_BLOCK)
+#define NOALLOC_RED_DOUBLES (2 * B200LK_NOALLOC_MAX_CTAS)
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_VAL_DOUBLES + NOALLOC_RED_DOUBLES];
+
+#define NOALLOC_MAX_DEVICES 64
+static double *g_noalloc_ptr[NOALLOC_MAX_DEVICES];  // device address of the array on each device (the symbol's name is
+                                                    // only a host-side stand-in, never a pointer a kernel may be given)
+
+// set-up, once per device, with that device current (called from b200lk_create; the entry point repeats it only for
+// a device it has never seen)
+int noalloc_setup(b200lk_ctx *c) {
+    if (c->device < 0 || c->device >= NOALLOC_MAX_DEVICES) return B200LK_ERR_ARG;
+    if (g_noalloc_ptr[c->device]) return B200LK_OK;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    double *ptr = nullptr;
+    CUDA_TRY(c, cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch));
+    g_noalloc_ptr[c->device] = ptr;
+    return B200LK_OK;
+}
+
+extern "C" int b200lk_lnl_from_buffer_noalloc(b200lk_ctx *c, double length, double *lnl) {
+    if (!c || !lnl) return B200LK_ERR_ARG;
+    if (!c->model_set || !c->tips_set || !c->theta_computed) {
+        snprintf(c->err, sizeof(c->err), "lnl_from_buffer_noalloc: set the model, upload the tips and build theta first");
+        return B200LK_ERR_STATE;
+    }
+    if (c->nonrev || c->site || c->batch || c->cur_branch_mixlen || c->asc_holder) {
+        snprintf(c->err, sizeof(c->err), "lnl_from_buffer_noalloc: reversible, non-site-specific contexts without Holder +ASC only");
+        return B200LK_ERR_UNSUPPORTED;
+    }
+    if (c->block > B200LK_NOALLOC_MAX_BLOCK) {
+        snprintf(c->err, sizeof(c->err),
+                 "lnl_from_buffer_noalloc: nstates * ncat_mix = %d exceeds the static scratch (B200LK_NOALLOC_MAX_BLOCK = %d); "
+                 "use b200lk_lnl_from_buffer",
+                 c->block, B200LK_NOALLOC_MAX_BLOCK);
+        return B200LK_ERR_ARG;
+    }
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->d.nptn == 0) { *lnl = 0.0; return B200LK_OK; }
+    int rc = noalloc_setup(c);
+    if (rc) return rc;
+    double *sval = g_noalloc_ptr[c->device], *sred = sval + NOALLOC_VAL_DOUBLES;
+    BatchLaunch nobatch;
+    memset(&nobatch, 0, sizeof(nobatch));
+    const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
+    val_kernel<<<(c->block + 255) / 256, 256, 0, c->stream>>>(c->m, length, nullptr, sval, c->tip_val, c->d.nstates, c->d.ncat,
+                                                             c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes, 0, nobatch);
+    CUDA_TRY(c, cudaGetLastError());
+    BranchArgs a;
+    memset(&a, 0, sizeof(a));
+    fill_common(c, a);
+    a.val = sval;
+    a.red_partial = sred;
+    a.len = length;
+    a.G = pick_group(c->block);
+    int grid = std::min(grid_for(c, a.G, c->ntot), B200LK_NOALLOC_MAX_CTAS);  // grid-stride loops: any grid covers ntot
+    frombuf_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, grid, nobatch);
+    CUDA_TRY(c, cudaGetLastError());
+    final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(sred, grid, 2, c->d_result, 0, 1, 8, nobatch);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches += 3;
+    rc = launch_asc_fix(c, 0);  // works on d_result and pattern_lh only
+    if (rc) return rc;
+    CUDA_TRY(c, cudaMemcpyAsync(c->h_result, c->d_result, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    int warn = 0;
+    if (!isfinite(c->h_result[0])) {  // tree/phylokernelnew.h:3338-3347, with the scratch for the repair pass's sums too
+        warn = B200LK_WARN_LNL_NONFINITE;
+        grid = std::min(grid_for(c, 1, c->d.nptn), B200LK_NOALLOC_MAX_CTAS);
+        repair_kernel<<<grid, RED_THREADS, 0, c->stream>>>(c->pattern_lh, c->ptn_freq, c->d.nptn, sred, grid);
+        CUDA_TRY(c, cudaGetLastError());
+        final_reduce_kernel<<<1, RED_THREADS, 0, c->stream>>>(sred, grid, 1, c->d_result, 0, 8, 0, nobatch);
+        CUDA_TRY(c, cudaGetLastError());
+        c->n_launches += 2;
+        CUDA_TRY(c, cudaMemcpyAsync(c->h_result, c->d_result, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    }
+    *lnl = c->h_result[0];
+    return warn;
+}

@@ -204,6 +204,7 @@ int launch_repair(b200lk_ctx *c);
 int launch_robust(b200lk_ctx *c);  // robust.cu: replaces result[0] by the robust score of the per-pattern lnL
 int launch_newton(b200lk_ctx *c, const b200lk_newton *nr, const b200lk_end *ends);  // ends = {dad, node}: builds theta too
 int launch_rell(b200lk_ctx *c);
+int noalloc_setup(b200lk_ctx *c);  // branch.cu: device address of the static scratch of b200lk_lnl_from_buffer_noalloc
 int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used);
 int launch_partial_multi(b200lk_ctx *c, int node_index);
 bool s4_detect_sym(const b200lk_ctx *c, double pi[4]);

@@ -91,7 +91,7 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->d_result, sizeof(double) * 16));
     CUDA_TRY(c, cudaMemset(c->d_result, 0, sizeof(double) * 16));
     CUDA_TRY(c, cudaMallocHost(&c->h_result, sizeof(double) * 8));
-    return B200LK_OK;
+    return noalloc_setup(c);  // once per device: where the static scratch of b200lk_lnl_from_buffer_noalloc lives
 }
 
 extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
