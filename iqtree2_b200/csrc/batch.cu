@@ -174,12 +174,47 @@ static int unpack(b200lk_batch *b, double *lnl, double *df, double *ddf) {
     return warn;
 }
 
+// The reference repairs a non-finite lnL per partition tree (tree/phylokernelnew.h:3077-3094, 3338-3347: non-finite
+// per-pattern values are replaced by 4 * LOG_SCALING_THRESHOLD and the sum retaken); the per-context calls do the same in
+// finish_lnl.  A batch does it here for the members concerned, each on its own context, so that results do not depend
+// on whether batching is on.  The warning bit stays set.
+static int repair_members(b200lk_batch *b, double *lnl) {
+    if (!lnl) return B200LK_OK;
+    for (int i = 0; i < b->n; i++) {
+        if (isfinite(lnl[i])) continue;
+        b200lk_ctx *c = b->ctx[i];
+        if (c->d.nptn == 0) continue;
+        cudaStream_t saved = c->stream;
+        c->stream = b->stream;
+        int rc = launch_repair(c);
+        if (rc == B200LK_OK) {
+            cudaError_t e = cudaMemcpyAsync(c->h_result, c->d_result, sizeof(double), cudaMemcpyDeviceToHost, b->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
+            if (e != cudaSuccess) {
+                snprintf(b->err, sizeof(b->err), "repair of batch member %d: %s", i, cudaGetErrorString(e));
+                rc = B200LK_ERR_CUDA;
+            }
+        } else {
+            snprintf(b->err, sizeof(b->err), "%s", c->err);
+        }
+        c->stream = saved;
+        if (rc) return rc;
+        lnl[i] = c->h_result[0];
+    }
+    return B200LK_OK;
+}
+
 static int collect(b200lk_batch *b, double *lnl, double *df, double *ddf) {
     batch_gather_kernel<<<(b->n + 127) / 128, 128, 0, b->stream>>>(b->d_ctx, b->n, b->d_results);
     BATCH_TRY(b, cudaGetLastError());
     BATCH_TRY(b, cudaMemcpyAsync(b->h_results, b->d_results, sizeof(double) * 4 * b->n, cudaMemcpyDeviceToHost, b->stream));
     BATCH_TRY(b, cudaStreamSynchronize(b->stream));
-    return unpack(b, lnl, df, ddf);
+    const int warn = unpack(b, lnl, df, ddf);
+    if (warn & B200LK_WARN_LNL_NONFINITE) {
+        int rc = repair_members(b, lnl);
+        if (rc) return rc;
+    }
+    return warn;
 }
 
 extern "C" int b200lk_batch_evaluate_async(b200lk_batch *b, const b200lk_node *nodes, int32_t nnodes,
@@ -235,7 +270,12 @@ extern "C" int b200lk_batch_read_results(b200lk_batch *b, double *lnl, double *d
     BATCH_TRY(b, cudaSetDevice(b->device));
     BATCH_TRY(b, cudaStreamSynchronize(b->stream));
     b->pending = false;
-    return unpack(b, lnl, b->pending_derv ? df : nullptr, b->pending_derv ? ddf : nullptr);
+    const int warn = unpack(b, lnl, b->pending_derv ? df : nullptr, b->pending_derv ? ddf : nullptr);
+    if (warn & B200LK_WARN_LNL_NONFINITE) {
+        int rc = repair_members(b, lnl);
+        if (rc) return rc;
+    }
+    return warn;
 }
 
 extern "C" int b200lk_batch_evaluate(b200lk_batch *b, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,

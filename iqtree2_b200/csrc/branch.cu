@@ -1084,7 +1084,7 @@ int launch_newton(b200lk_ctx *c, const b200lk_newton *nr, const b200lk_end *ends
     };
     if (smem > 48 * 1024)
         CUDA_TRY(c, cudaFuncSetAttribute(newton_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 0, sms = 148, coop = 0;
+    int per_sm = 0, sms = c->sms, coop = 0;
     CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, newton_kernel, RED_THREADS, smem));
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device);

@@ -75,7 +75,24 @@ struct BatchLaunch {           // non-null in b200lk_ctx::batch while a batched 
     const double *d_branch_len;  // [n] length of the branch the likelihood is taken at
 };
 
+// process-wide A/B and test hooks, read from the environment ONCE (context.cu) -- never on a launch path
+struct B200Env {
+    int s4_minb;       // B200LK_S4_MINB: resident-CTA instantiation of s4_traverse_kernel (8 / 10 / 12); 0 = default
+    bool s4_sym;       // B200LK_S4_SYM=0 keeps the general 4-state kernel
+    int stack_depth;   // B200LK_STACK_DEPTH: shared-memory stack entries per thread (-1 = chosen at launch)
+    bool level_batched, no_dmma;  // B200LK_LEVEL_BATCHED=1, B200LK_NO_DMMA=1: generic kernels only
+    int dense_pipe, dense_occ;    // B200LK_DENSE_PIPE (0 direct, 1 cp.async, 2 register prefetch), B200LK_DENSE_OCC (3 / 4)
+    bool site_dmma;               // B200LK_SITE_DMMA=0 keeps the shuffle kernel for 20-state site models
+    bool no_fused_tail;           // B200LK_NO_FUSED_TAIL=1: separate lnl / theta / derv launches in b200lk_evaluate*
+};
+const B200Env &b200_env();
+
 struct b200lk_ctx {
+    int sms;                          // multiprocessors of the device
+    double *m_block, *h_model_stage;  // the DevModel arrays as ONE device block + its pinned staging mirror
+    size_t m_block_doubles, m_off[8];
+    cudaEvent_t model_ev;             // recorded after the H2D copy of the staging mirror
+    bool model_ev_used;
     const BatchLaunch *batch;
     b200lk_dims d;
     int ncat_mix, block, scale_per_ptn;

@@ -7,7 +7,35 @@
 
 #include "common.cuh"
 
-extern "C" const char *b200lk_version(void) { return "b200lk 0.1 (sm_100a)"; }
+extern "C" const char *b200lk_version(void) { return "b200lk 0.2 (sm_100a)"; }
+
+const B200Env &b200_env() {
+    static const B200Env env = [] {
+        B200Env e;
+        const char *v = getenv("B200LK_S4_MINB");
+        e.s4_minb = v ? atoi(v) : 0;
+        v = getenv("B200LK_S4_SYM");
+        e.s4_sym = !(v && *v == '0');
+        v = getenv("B200LK_STACK_DEPTH");  // test hook: force the stack-overflow path
+        e.stack_depth = v ? atoi(v) : -1;
+        if (v && e.stack_depth < 0) e.stack_depth = 0;
+        if (e.stack_depth > 12) e.stack_depth = 12;
+        v = getenv("B200LK_LEVEL_BATCHED");
+        e.level_batched = v && *v == '1';
+        v = getenv("B200LK_NO_DMMA");
+        e.no_dmma = v && *v == '1';
+        v = getenv("B200LK_DENSE_PIPE");
+        e.dense_pipe = v ? atoi(v) : 2;
+        v = getenv("B200LK_DENSE_OCC");
+        e.dense_occ = (v && atoi(v) == 3) ? 3 : 4;
+        v = getenv("B200LK_SITE_DMMA");
+        e.site_dmma = !(v && *v == '0');
+        v = getenv("B200LK_NO_FUSED_TAIL");
+        e.no_fused_tail = v && *v == '1';
+        return e;
+    }();
+    return env;
+}
 
 extern "C" const char *b200lk_last_error(const b200lk_ctx *c) { return c ? c->err : "null context"; }
 
@@ -38,13 +66,30 @@ static int alloc_all(b200lk_ctx *c) {
         CUDA_TRY(c, cudaMalloc(&c->scale, c->slot_scale_bytes * d.nslots));
         CUDA_TRY(c, cudaMemset(c->scale, 0, c->slot_scale_bytes * d.nslots));
     }
-    CUDA_TRY(c, cudaMalloc(&c->m.eval, sizeof(double) * nmix * n));
-    CUDA_TRY(c, cudaMalloc(&c->m.evec, sizeof(double) * nmix * n * n));
-    CUDA_TRY(c, cudaMalloc(&c->m.inv_evec, sizeof(double) * nmix * n * n));
-    CUDA_TRY(c, cudaMalloc(&c->m.rates, sizeof(double) * d.ncat));
-    CUDA_TRY(c, cudaMalloc(&c->m.props, sizeof(double) * d.ncat));
-    CUDA_TRY(c, cudaMalloc(&c->m.mixw, sizeof(double) * nmix));
-    CUDA_TRY(c, cudaMalloc(&c->m.tip_partial_lh, sizeof(double) * d.n_state_codes * nmix * n));
+    {
+        // the model arrays are ONE device block (each array 256-byte aligned) with a pinned staging mirror, so that
+        // b200lk_set_model is a memcpy into pinned memory + ONE asynchronous H2D copy per model probe
+        const size_t sz[7] = {(size_t)nmix * n, (size_t)nmix * n * n, (size_t)nmix * n * n, (size_t)d.ncat, (size_t)d.ncat,
+                              (size_t)nmix, (size_t)d.n_state_codes * nmix * n};
+        size_t off = 0;
+        for (int k = 0; k < 7; k++) {
+            c->m_off[k] = off;
+            off += (sz[k] + 31) & ~(size_t)31;
+        }
+        c->m_off[7] = c->m_block_doubles = off;
+        CUDA_TRY(c, cudaMalloc(&c->m_block, sizeof(double) * off));
+        CUDA_TRY(c, cudaMemset(c->m_block, 0, sizeof(double) * off));
+        CUDA_TRY(c, cudaMallocHost(&c->h_model_stage, sizeof(double) * off));
+        memset(c->h_model_stage, 0, sizeof(double) * off);
+        CUDA_TRY(c, cudaEventCreateWithFlags(&c->model_ev, cudaEventDisableTiming));
+        c->m.eval = c->m_block + c->m_off[0];
+        c->m.evec = c->m_block + c->m_off[1];
+        c->m.inv_evec = c->m_block + c->m_off[2];
+        c->m.rates = c->m_block + c->m_off[3];
+        c->m.props = c->m_block + c->m_off[4];
+        c->m.mixw = c->m_block + c->m_off[5];
+        c->m.tip_partial_lh = c->m_block + c->m_off[6];
+    }
     CUDA_TRY(c, cudaMalloc(&c->theta_all, sizeof(double) * (c->slot_doubles + 2)));
     CUDA_TRY(c, cudaMalloc(&c->buffer_scale_all, sizeof(double) * c->ntot_pad));
     CUDA_TRY(c, cudaMalloc(&c->pattern_lh, sizeof(double) * c->ntot_pad));
@@ -67,26 +112,24 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->d_children, sizeof(DevChild) * c->children_cap));
     CUDA_TRY(c, cudaMallocHost(&c->h_nodes_ring, sizeof(DevNode) * c->nodes_cap * B200_STAGE_RING));
     CUDA_TRY(c, cudaMallocHost(&c->h_children_ring, sizeof(DevChild) * c->children_cap * B200_STAGE_RING));
-    // tip-state row sequence of the pattern-stationary traversal (chunk-padded: the children themselves,
-    // at most one pad row per node and one pad chunk per launch)
-    c->prog_stride = sizeof(int32_t) * (2 * (size_t)c->children_cap + 8192);
+    // tip-state row sequence of the pattern-stationary traversal (s4.cu: launch_segment): per traversal list at most
+    // 3 entries per node (two leaf children and one pad row) + one chunk of rows read past the end by the last refill,
+    // whatever the number of launches the list is cut into
+    c->prog_stride = sizeof(int32_t) * (3 * (size_t)c->nodes_cap + 2 * 256);
     CUDA_TRY(c, cudaMallocHost(&c->h_prog_ring, c->prog_stride * B200_STAGE_RING));
+    memset(c->h_prog_ring, 0, c->prog_stride * B200_STAGE_RING);
     CUDA_TRY(c, cudaMalloc(&c->d_prog, c->prog_stride));
+    CUDA_TRY(c, cudaMemset(c->d_prog, 0, c->prog_stride));
     c->h_prog = c->h_prog_ring;
-    {
-        const char *sd = getenv("B200LK_STACK_DEPTH");  // test hook: force the stack-overflow path
-        c->max_stack_depth = sd ? atoi(sd) : -1;  // -1: chosen per kernel at launch (s4.cu, measured on cfg2)
-        if (sd && c->max_stack_depth < 0) c->max_stack_depth = 0;
-        if (c->max_stack_depth > 12) c->max_stack_depth = 12;
-    }
+    c->max_stack_depth = b200_env().stack_depth;  // -1: chosen per kernel at launch (s4.cu, measured on cfg2)
     c->h_nodes = c->h_nodes_ring;
     c->h_children = c->h_children_ring;
     for (int i = 0; i < B200_STAGE_RING; i++)
         CUDA_TRY(c, cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming));
     c->prof_events = new std::vector<cudaEvent_t>();
-    int sms = 148;
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
-    c->red_blocks = sms * 8;
+    c->sms = 148;
+    cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, c->device);
+    c->red_blocks = c->sms * 8;
     CUDA_TRY(c, cudaMalloc(&c->red_partial, sizeof(double) * 8 * c->red_blocks));
     CUDA_TRY(c, cudaMalloc(&c->d_result, sizeof(double) * 16));
     CUDA_TRY(c, cudaMemset(c->d_result, 0, sizeof(double) * 16));
@@ -117,14 +160,10 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
     c->ntot = dims->nptn + dims->n_unobserved;
     c->ntot_pad = ((c->ntot + 255) / 256) * 256;  // a CTA tile of tip states never leaves its row
     if (c->ntot_pad == 0) c->ntot_pad = 256;
-    {
-        const char *e = getenv("B200LK_LEVEL_BATCHED");  // A/B switch: generic level-batched kernels only
-        c->force_level_batched = e && *e == '1';
-    }
+    c->force_level_batched = b200_env().level_batched;  // A/B switch: generic level-batched kernels only
     // 4-state models with <= 4 categories run the pattern-stationary path on the T32 layout (s4.cu)
     {
-        const char *e = getenv("B200LK_NO_DMMA");  // A/B switch: generic kernels for 20-state models
-        const bool dmma = !(e && *e == '1') && !c->force_level_batched;
+        const bool dmma = !b200_env().no_dmma && !c->force_level_batched;  // A/B switch: generic kernels for 20-state models
         c->dense20 = dims->nstates == 20 && dmma;
         c->dense_nt = (dmma && !c->dense20 && dims->nstates >= 9 && dims->nstates <= 64) ? (dims->nstates + 7) / 8 : 0;
         c->frag_cat = c->dense20 ? B200_FRAG20 : c->dense_nt * 2 * c->dense_nt * 32;
@@ -171,12 +210,13 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (!c) return B200LK_OK;
     cudaSetDevice(c->device);
     if (c->own_stream) cudaStreamSynchronize(c->own_stream);
-    void *dev[] = {c->states, c->ptn_freq, c->ptn_invar, c->partial, c->scale, c->m.eval, c->m.evec,
-                   c->m.inv_evec, c->m.inv_frag, c->m.rates, c->m.props, c->m.mixw, c->m.tip_partial_lh, c->theta_all,
+    void *dev[] = {c->states, c->ptn_freq, c->ptn_invar, c->partial, c->scale, c->m_block, c->m.inv_frag, c->theta_all,
                    c->buffer_scale_all, c->pattern_lh, c->pattern_lh_cat, c->val, c->tip_val, c->tables,
                    c->d_nodes, c->d_children, c->red_partial, c->d_result};
     for (void *p : dev)
         if (p) cudaFree(p);
+    if (c->h_model_stage) cudaFreeHost(c->h_model_stage);
+    if (c->model_ev) cudaEventDestroy(c->model_ev);
     if (c->h_nodes_ring) cudaFreeHost(c->h_nodes_ring);
     if (c->h_children_ring) cudaFreeHost(c->h_children_ring);
     if (c->h_prog_ring) cudaFreeHost(c->h_prog_ring);
@@ -264,27 +304,29 @@ extern "C" int b200lk_set_model(b200lk_ctx *c, const double *eval, const double 
     CUDA_TRY(c, cudaSetDevice(c->device));
     const int n = c->d.nstates, nmix = c->d.nmix;
     cudaStream_t s = c->stream;
-    CUDA_TRY(c, cudaMemcpyAsync(c->m.eval, eval, sizeof(double) * nmix * n, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaMemcpyAsync(c->m.evec, evec, sizeof(double) * nmix * n * n, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaMemcpyAsync(c->m.inv_evec, inv_evec, sizeof(double) * nmix * n * n, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaMemcpyAsync(c->m.rates, rates, sizeof(double) * c->d.ncat, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaMemcpyAsync(c->m.props, props, sizeof(double) * c->d.ncat, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaMemcpyAsync(c->m.mixw, mixw, sizeof(double) * nmix, cudaMemcpyHostToDevice, s));
-    CUDA_TRY(c, cudaMemcpyAsync(c->m.tip_partial_lh, tip_partial_lh, sizeof(double) * c->d.n_state_codes * nmix * n,
-                                cudaMemcpyHostToDevice, s));
+    // one pinned staging block, one H2D copy; the previous probe's copy must have left the staging block first
+    if (c->model_ev_used) CUDA_TRY(c, cudaEventSynchronize(c->model_ev));
+    double *st = c->h_model_stage;
+    memcpy(st + c->m_off[0], eval, sizeof(double) * nmix * n);
+    memcpy(st + c->m_off[1], evec, sizeof(double) * nmix * n * n);
+    memcpy(st + c->m_off[2], inv_evec, sizeof(double) * nmix * n * n);
+    memcpy(st + c->m_off[3], rates, sizeof(double) * c->d.ncat);
+    memcpy(st + c->m_off[4], props, sizeof(double) * c->d.ncat);
+    memcpy(st + c->m_off[5], mixw, sizeof(double) * nmix);
+    memcpy(st + c->m_off[6], tip_partial_lh, sizeof(double) * c->d.n_state_codes * nmix * n);
+    CUDA_TRY(c, cudaMemcpyAsync(c->m_block, st, sizeof(double) * c->m_block_doubles, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(c, cudaEventRecord(c->model_ev, s));
+    c->model_ev_used = true;
     if (c->dense20 || c->dense_nt) {
         int rc = launch_inv_frag(c);
         if (rc) return rc;
     }
-    CUDA_TRY(c, cudaStreamSynchronize(s));  // the host arrays may be reused by the caller
+    // no stream sync: the caller's arrays were copied into the staging block and may be reused at once
     memcpy(c->h_evec, evec, sizeof(double) * nmix * n * n);
     memcpy(c->h_inv_evec, inv_evec, sizeof(double) * nmix * n * n);
     memcpy(c->h_eval, eval, sizeof(double) * nmix * n);
     memcpy(c->h_rates, rates, sizeof(double) * c->d.ncat);
-    {
-        const char *e = getenv("B200LK_S4_SYM");  // A/B switch: 0 keeps the general 4-state kernel
-        c->s4_sym = c->tile == 32 && !(e && *e == '0') && s4_detect_sym(c, c->s4_pi);
-    }
+    c->s4_sym = c->tile == 32 && b200_env().s4_sym && s4_detect_sym(c, c->s4_pi);
     c->model_set = true;
     c->theta_computed = false;
     return B200LK_OK;

@@ -844,7 +844,7 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes) {
     if (c->batch && a.split) return B200LK_ERR_UNSUPPORTED;  // grid.z is taken by the category groups
     a.pmax = nullptr;
     int tpc = DN_MAX_TILES;
-    while (tpc > 1 && (tiles + tpc - 1) / tpc * nnodes * (a.split ? ngroups : 1) * (c->batch ? c->batch->n : 1) < 148 * 6) tpc >>= 1;
+    while (tpc > 1 && (tiles + tpc - 1) / tpc * nnodes * (a.split ? ngroups : 1) * (c->batch ? c->batch->n : 1) < c->sms * 6) tpc >>= 1;
     a.tiles_per_cta = tpc;
     if (a.split && !c->d.safe_numeric) {
         const size_t need = sizeof(unsigned long long) * (size_t)nnodes * c->ntot;
@@ -861,17 +861,9 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes) {
     const int leaf_doubles = a.codes * DN_CG * 20, frag_doubles = DN_CG * B200_FRAG20;
     const size_t smem = sizeof(double) * (2 * (size_t)std::max(leaf_doubles, frag_doubles) + frag_doubles) +
                         sizeof(unsigned long long) * tpc * DN_PT;
-    static int pipe = -1;  // A/B switch: cp.async operand pipeline (default) / direct loads (B200LK_DENSE_PIPE=0)
-    if (pipe < 0) {
-        const char *e = getenv("B200LK_DENSE_PIPE");
-        pipe = e ? atoi(e) : 2;  // 0 direct loads, 1 cp.async double buffer, 2 register prefetch (default)
-    }
+    const int pipe = b200_env().dense_pipe;  // A/B switch: 0 direct loads, 1 cp.async double buffer, 2 register prefetch (default)
     const size_t smem_pipe = smem + sizeof(double) * (DN_THREADS / 32) * 2 * DN_STAGE_DOUBLES;
-    static int occ = -1;  // A/B switch: resident CTAs per SM the kernel is compiled for (registers 160 / 128)
-    if (occ < 0) {
-        const char *e = getenv("B200LK_DENSE_OCC");
-        occ = (e && atoi(e) == 3) ? 3 : 4;
-    }
+    const int occ = b200_env().dense_occ;  // A/B switch: resident CTAs per SM the kernel is compiled for (registers 160 / 128)
     if (!c->dense_attr_set) {
         CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));

@@ -250,7 +250,7 @@ static int launch_nt(b200lk_ctx *c, DenseNArgs &a, int nnodes) {
     a.child_doubles = std::max(a.codes * LP, FRAG);
     const int64_t tiles = (c->ntot + PT - 1) / PT;
     int tpc = DX_MAX_TILES;  // amortise the table staging, but keep enough CTAs to fill the machine a few times
-    while (tpc > 1 && (tiles + tpc - 1) / tpc * nnodes < 148 * 4) tpc >>= 1;
+    while (tpc > 1 && (tiles + tpc - 1) / tpc * nnodes < c->sms * 4) tpc >>= 1;
     a.tiles_per_cta = tpc;
     const size_t smem = sizeof(double) * (2 * (size_t)a.child_doubles + FRAG) + sizeof(unsigned long long) * tpc * PT;
     if (smem > 200 * 1024) return B200LK_ERR_UNSUPPORTED;

@@ -242,10 +242,7 @@ extern "C" int b200lk_set_model_rates(b200lk_ctx *c, const double *exch, const d
     memcpy(c->h_evec, h_out + (size_t)nmix * n, sizeof(double) * nmix * n * n);
     memcpy(c->h_inv_evec, h_out + (size_t)nmix * (n + n * n), sizeof(double) * nmix * n * n);
     memcpy(c->h_rates, rates, sizeof(double) * c->d.ncat);
-    {
-        const char *e = getenv("B200LK_S4_SYM");  // A/B switch: 0 keeps the general 4-state kernel
-        c->s4_sym = c->tile == 32 && !(e && *e == '0') && s4_detect_sym(c, c->s4_pi);
-    }
+    c->s4_sym = c->tile == 32 && b200_env().s4_sym && s4_detect_sym(c, c->s4_pi);
     c->model_set = true;
     c->theta_computed = false;
     return B200LK_OK;

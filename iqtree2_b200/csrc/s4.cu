@@ -532,6 +532,16 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     int32_t *leaf_seq = reinterpret_cast<int32_t *>(c->h_prog) + *seq_used;
     const int chunk = S4_STATE_BYTES / S4_THREADS;
     int nseq = 0;
+    // staged tip-state rows of this segment: its leaf children plus at most one pad row per node (a node never
+    // straddles two chunks).  Nothing is padded at the END of a segment: a refill always reads a whole chunk of rows,
+    // and the rows behind the last one used are the next segment's, or left-overs of an earlier call -- valid taxon ids
+    // either way (both copies of the buffer start zeroed and only ever receive taxon ids), loaded and never looked at.
+    // `prog_stride` holds children_cap + nodes_cap entries + one chunk of slack, which bounds every traversal list.
+    if ((size_t)*seq_used + 3 * (size_t)count + chunk > c->prog_stride / sizeof(int32_t)) {
+        snprintf(c->err, sizeof(c->err), "tip-state staging sequence overflow: %d + %d entries (capacity %zu)", *seq_used,
+                 3 * count + chunk, c->prog_stride / sizeof(int32_t));
+        return B200LK_ERR_NOMEM;
+    }
     for (int i = 0; i < count; i++) {
         PNode<NCM> &f = P.nodes[i];
         memset(&f, 0, sizeof(f));
@@ -583,7 +593,6 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         f.info = kind[0] | kind[1] << 2 | (out_stack + 1) << 4 | (refill + 1) << 12;
         producer[nl[i].out_slot] = i;
     }
-    while (nseq % chunk) leaf_seq[nseq++] = 0;  // a refill always reads a whole chunk of rows
     int32_t *d_seq = reinterpret_cast<int32_t *>(c->d_prog) + *seq_used;
     if (nseq)
         CUDA_TRY(c, cudaMemcpyAsync(d_seq, leaf_seq, sizeof(int32_t) * nseq, cudaMemcpyHostToDevice, c->stream));
@@ -626,8 +635,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         kern<<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
     } else if (c->s4_sym) {
         // resident CTAs per SM the registers are sized for: 10 x 64 threads (96 registers, two stack entries) unless overridden
-        const char *mb = getenv("B200LK_S4_MINB");  // test / sweep hook: the 8- and 12-CTA instantiations
-        const int minb = mb ? atoi(mb) : S4_MINB;
+        const int minb = b200_env().s4_minb ? b200_env().s4_minb : S4_MINB;  // test / sweep hook: the 8- and 12-CTA instantiations
         const bool safe = c->d.safe_numeric != 0;
         auto kern = safe ? s4_traverse_kernel<NCM, true, true, S4_MINB> : s4_traverse_kernel<NCM, false, true, S4_MINB>;
         if (minb == 8) kern = safe ? s4_traverse_kernel<NCM, true, true, 8> : s4_traverse_kernel<NCM, false, true, 8>;

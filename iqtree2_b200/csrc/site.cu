@@ -270,14 +270,10 @@ int launch_site_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &lev
         if (!nb) continue;
         a.node_base = base;
         const int64_t per = SITE_THREADS / 32;
-        const unsigned gx = (unsigned)std::min<int64_t>((c->d.nptn + per - 1) / per, 148 * 16);
+        const unsigned gx = (unsigned)std::min<int64_t>((c->d.nptn + per - 1) / per, (int64_t)c->sms * 16);
         dim3 grid(gx, nb);
         prof_mark(c);
-        static int use_dmma = -1;  // A/B switch: B200LK_SITE_DMMA=0 keeps the shuffle kernel for 20 states
-        if (use_dmma < 0) {
-            const char *e = getenv("B200LK_SITE_DMMA");
-            use_dmma = !(e && *e == '0');
-        }
+        const bool use_dmma = b200_env().site_dmma;  // A/B switch: B200LK_SITE_DMMA=0 keeps the shuffle kernel for 20 states
         if (a.n == 20 && use_dmma) {
             if (safe) site_partial20_kernel<true><<<grid, SITE_THREADS, 0, c->stream>>>(a);
             else site_partial20_kernel<false><<<grid, SITE_THREADS, 0, c->stream>>>(a);
@@ -323,7 +319,7 @@ extern "C" int b200lk_set_site_models(b200lk_ctx *c, const double *eval, const d
     CUDA_TRY(c, cudaMemcpyAsync(c->m.props, props, sizeof(double) * c->d.ncat, cudaMemcpyHostToDevice, s));
     if (nptn > 0) {
         const int64_t total = (int64_t)c->d.ntaxa * nptn * n;
-        site_tip_kernel<<<(unsigned)std::min<int64_t>((total + 255) / 256, 148 * 32), 256, 0, s>>>(
+        site_tip_kernel<<<(unsigned)std::min<int64_t>((total + 255) / 256, (int64_t)c->sms * 32), 256, 0, s>>>(
             c->states, c->s_inv, c->s_tipvec, c->s_tip, nptn, c->ntot_pad, n, c->d.ntaxa);
         CUDA_TRY(c, cudaGetLastError());
         c->n_launches++;

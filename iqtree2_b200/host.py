@@ -18,17 +18,23 @@ class HostError(RuntimeError):
     pass
 
 
+def _load(path):
+    if not os.path.exists(path):
+        raise HostError("%s is missing: build it first (python -m iqtree2_b200.build_host)" % path)
+    L = C.CDLL(path)
+    L.b200host_last_error.restype = C.c_char_p
+    L.b200host_alignment_npattern.restype = C.c_int64
+    L.b200host_alignment_name.restype = C.c_char_p
+    L.b200host_tree_kernel_calls.restype = C.c_int64
+    L.b200host_tree_gpu_launches.restype = C.c_int64
+    return L
+
+
 def lib():
+    """The host library in use: the product build, unless a test has switched to the testing build."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            raise HostError("%s is missing: build it first (python -m iqtree2_b200.build_host)" % LIB_PATH)
-        _lib = C.CDLL(LIB_PATH)
-        _lib.b200host_last_error.restype = C.c_char_p
-        _lib.b200host_alignment_npattern.restype = C.c_int64
-        _lib.b200host_alignment_name.restype = C.c_char_p
-        _lib.b200host_tree_kernel_calls.restype = C.c_int64
-        _lib.b200host_tree_gpu_launches.restype = C.c_int64
+        _lib = _load(LIB_PATH)
     return _lib
 
 
@@ -41,10 +47,33 @@ def _dp(a):
     return a.ctypes.data_as(C.POINTER(C.c_double))
 
 
+_product_lib = None
+_testing_lib = None
+
+
 def set_kernel_library(path=None, prefix=None):
-    """Test hook: bind the host layer to another library exporting the C ABI (tests pass the CPU oracle);
-    None restores the product library (libb200lk.so, prefix b200lk_)."""
-    _ck(lib().b200host_set_kernel_library((path or "").encode(), (prefix or "").encode()))
+    """TEST HOOK.  Bind the host layer to another library exporting the C ABI (tests pass the CPU oracle).  The
+    product build (libb200host.so) has no such switch: this loads the -DB200_TESTING build of the same sources
+    (libb200host_testing.so) and makes it the library `lib()` returns; None restores the product library.  Objects
+    created under one library must be released before switching."""
+    global _lib, _product_lib, _testing_lib
+    if path is None and prefix is None:
+        if _testing_lib is not None:
+            _ck_on(_testing_lib, _testing_lib.b200host_set_kernel_library(b"", b""))
+        if _product_lib is None:
+            _product_lib = _load(LIB_PATH)
+        _lib = _product_lib
+        return
+    if _testing_lib is None:
+        from . import build_host
+        _testing_lib = _load(build_host.build(testing=True))
+    _lib = _testing_lib
+    _ck(_lib.b200host_set_kernel_library((path or "").encode(), (prefix or "").encode()))
+
+
+def _ck_on(L, rc):
+    if rc != 0:
+        raise HostError((L.b200host_last_error() or b"").decode())
 
 
 def _seq_type(nstates):

@@ -36,9 +36,10 @@ const double TOL_LIKELIHOOD = 0.001;     // tree/phylotree.h:65
 void outWarning(const std::string &msg);
 
 // ---- kernel library binding ------------------------------------------------------------------------------
-// The C ABI resolved at run time from libb200lk.so (dlopen next to this library).  A test may point the host at
-// another library exporting the same ABI under another prefix (tests/ do this with the CPU oracle to check the
-// host logic where no GPU exists); the product never does.
+// The C ABI resolved at run time from libb200lk.so (dlopen next to this library).  Only a TEST build of this layer
+// (-DB200_TESTING -> libb200host_testing.so, never loaded by bench.py or smoke()) can be pointed at another library
+// exporting the same ABI under another prefix (tests/ do this with the CPU oracle to check the host logic where no
+// GPU exists); the product library has no such switch.
 struct KernelABI {
     void *dl;
     std::string path, prefix;
@@ -85,8 +86,10 @@ struct KernelABI {
     int (*batch_derv)(b200lk_batch *, const double *, double *, double *);
     int (*batch_lnl_from_buffer)(b200lk_batch *, const double *, double *);
 };
-// default: libb200lk.so beside this library, prefix "b200lk_"
+// libb200lk.so beside this library, prefix "b200lk_"
+#ifdef B200_TESTING
 void setKernelLibrary(const std::string &path, const std::string &prefix);
+#endif
 const KernelABI &kernelABI();  // loads on first use; outError if the library or a required symbol is missing
 
 // ---- alignment (alignment/alignment.h, alignment/pattern.h) ----------------------------------------------

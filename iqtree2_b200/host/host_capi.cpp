@@ -30,9 +30,11 @@ extern "C" {
 
 const char *b200host_last_error(void) { return g_err.c_str(); }
 
+#ifdef B200_TESTING
 int b200host_set_kernel_library(const char *path, const char *prefix) {
     GUARD(setKernelLibrary(path ? path : "", prefix ? prefix : ""))
 }
+#endif
 
 // ---- alignment ---------------------------------------------------------------------------------------------
 int b200host_alignment_from_states(void **out, int ntaxa, int64_t nsite, const uint8_t *codes, int seq_type, int nstates,

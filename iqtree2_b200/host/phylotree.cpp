@@ -27,11 +27,15 @@ static std::string default_library_path() {
     return "libb200lk.so";
 }
 
+#ifdef B200_TESTING
+// Test builds only (libb200host_testing.so, -DB200_TESTING): the product library binds libb200lk.so beside it and
+// nothing else -- there is no way to re-point it at another backend.
 void setKernelLibrary(const std::string &path, const std::string &prefix) {
     if (g_abi.dl) { dlclose(g_abi.dl); g_abi = KernelABI(); }
     g_lib_path = path;
     g_lib_prefix = prefix.empty() ? "b200lk_" : prefix;
 }
+#endif
 
 template <class F>
 static void bind(F &fn, const char *name, bool required) {

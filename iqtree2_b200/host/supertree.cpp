@@ -80,6 +80,13 @@ void PhyloSuperTree::buildBatches() {
 void PhyloSuperTree::addPartition(const std::string &name, Alignment *a, ModelSubst *m, RateHeterogeneity *r,
                                   double part_rate) {
     if (!root) outError("PhyloSuperTree: read the tree before adding partitions");
+    // the reference maps a gene with missing taxa onto an induced subtree (SuperNeighbor::link_neighbors,
+    // tree/phylosupertree.cpp:528-650); that mapping is not built here (scope): every partition must hold
+    // all taxa of the super-tree -- refuse anything else instead of evaluating the wrong tree
+    if (!a || (int)a->getNSeq() != leafNum)
+        outError("PhyloSuperTree::addPartition(" + name + "): the alignment has " + std::to_string(a ? a->getNSeq() : 0) +
+                 " sequences but the tree has " + std::to_string(leafNum) +
+                 " taxa; partitions with missing taxa are not supported by this build");
     PhyloTree *t = new PhyloTree();
     t->setParams(params);
     t->copyTree(*this);
@@ -281,6 +288,9 @@ void PhyloSuperTree::readBatch(PartitionBatch &b, std::vector<double> &lnl, std:
     if (rc < 0)
         outError(std::string("b200lk_batch_read_results failed with status ") + std::to_string(rc) + " " +
                  (k.batch_last_error ? k.batch_last_error(b.handle) : ""));
+    // positive = numerical warning mask, as PhyloTree::check treats it for the per-partition calls; the library has
+    // already repaired the members concerned (tree/phylokernelnew.h:3077-3094)
+    if (rc & B200LK_WARN_LNL_NONFINITE) outWarning("Numerical underflow for lh-branch");
 }
 
 double PhyloSuperTree::computeLikelihood(double *pattern_lh) {

@@ -48,6 +48,11 @@ class ShardedEngine:
                               device=0 if device is None else device, lib_path=lib_path or LIB_PATH, prefix=prefix)
         self.on_device = prefix == "b200lk_"
         self._res = self.eng.result_tensor() if self.on_device else None
+        if self.on_device and world > 1:
+            # the context's own stream is cudaStreamNonBlocking: NCCL (torch's current stream) would not be ordered
+            # after the lnL / derv kernels.  Run the engine on the stream the collective is enqueued on.
+            import torch
+            self.eng.set_stream(torch.cuda.current_stream().cuda_stream)
 
     def evaluate(self, entries, dad, node, length):
         """Full evaluation on this shard, then the sum over shards.  Returns (lnL, df, ddf) of the whole alignment."""

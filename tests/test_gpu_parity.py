@@ -404,3 +404,77 @@ def test_fused_mixture_rate_categories(oracle_lib, nstates, k, safe):
     g, o = both(aln, model, rates, props, nslots=11, safe_numeric=safe, fused=True)
     assert g.ncat_mix == k
     assert_parity(full_eval(g, tree, 2), full_eval(o, tree, 2), TOL)
+
+
+def _alternating_polytomy_newick(ntaxa):
+    """Caterpillar whose internal nodes alternate between two and three children: every run of bifurcating nodes is
+    one node long, so the 4-state traversal is cut into as many launches as a tree can force."""
+    text, used, tri = "(T0:0.1,T1:0.12)", 2, True
+    while used < ntaxa - 2:
+        if tri and used + 2 <= ntaxa - 2:
+            text = "(%s:0.05,T%d:0.1,T%d:0.07)" % (text, used, used + 1)
+            used += 2
+        else:
+            text = "(%s:0.04,T%d:0.09)" % (text, used)
+            used += 1
+        tri = not tri
+    return "(%s:0.03,T%d:0.1,T%d:0.2);" % (text, used, used + 1)
+
+
+@pytest.mark.parametrize("safe", [False, True])
+def test_polytomy_heavy_tree_tip_state_staging(oracle_lib, safe):
+    """every launch of the 4-state traversal used to pad its tip-state row sequence to a whole chunk, and a
+    tree of ~550+ taxa with alternating bi-/trifurcations overflowed the staging buffer.  The padding is now shared
+    across launches and the capacity is checked."""
+    ntaxa = 640
+    names = ["T%d" % i for i in range(ntaxa)]
+    t = W.Tree.from_newick(_alternating_polytomy_newick(ntaxa), names)
+    model = W.gtr_model()
+    rates, props = W.discrete_gamma(0.7)
+    aln = W.simulate_alignment(W.random_tree(ntaxa, 4, mean_len=0.02), model, rates, props, 97, 11, compress=True)
+    aln.names = names
+    g, o = both(aln, model, rates, props, nslots=ntaxa, safe_numeric=safe)
+    rg, ro = full_eval(g, t, 0), full_eval(o, t, 0)
+    assert sum(1 for e in ro["traversal"] if len(e[3]) > 2) > 150
+    assert_parity(rg, ro, TOL)
+    # a second evaluation reuses the staging ring slices behind the first one's
+    assert_parity(full_eval(g, t, ntaxa - 1), full_eval(o, t, ntaxa - 1), TOL)
+
+
+@pytest.mark.parametrize("nstates", [4, 20])
+def test_batched_evaluation_repairs_non_finite_lnl_like_the_per_context_path(oracle_lib, nstates):
+    """one gene with a NaN pattern must not poison a batched supermatrix evaluation: the reference replaces
+    non-finite per-pattern values by 4 * LOG_SCALING_THRESHOLD and re-sums (tree/phylokernelnew.h:3077-3094), the
+    per-context path does the same (finish_lnl), and so must the batch."""
+    from iqtree2_b200.capi import WARN_LNL_NONFINITE, Batch
+    ntaxa, ngenes = 9, 3
+    base, _, rates, props, _ = make_problem(ntaxa, 10, nstates=nstates, seed=31)
+    engines, oracles = [], []
+    for gene in range(ngenes):
+        model = W.gtr_model() if nstates == 4 else W.random_reversible_model(nstates, 500 + gene)
+        aln = W.simulate_alignment(base, model, rates, props, 150 + 40 * gene, 900 + gene)
+        g, o = both(aln, model, rates, props, nslots=ntaxa)
+        if gene == 1:  # poison pattern 5 of gene 1: lh = |x| + NaN
+            inv = np.zeros(aln.nptn)
+            inv[5] = np.nan
+            g.set_ptn_invar(inv)
+            o.set_ptn_invar(inv)
+        engines.append(g)
+        oracles.append(o)
+    leaf = 2
+    c = base.adj[leaf][0]
+    tr = W.traversal(base, c, leaf)
+    top = tr[-1][2]
+    L = base.get_length(leaf, c)
+    child_len = np.array([[base.get_length(e[0], ch_node) for e, ch_node in _children_of(base, tr)]] * ngenes)
+    blen = np.full(ngenes, L)
+    lnl, _, _ = Batch(engines).evaluate(tr, child_len, (LEAF, leaf), (INTERNAL, top), blen)
+    for gene in range(ngenes):
+        oracles[gene].update_partials(tr)
+        want = oracles[gene].branch_lnl((LEAF, leaf), (INTERNAL, top), L)
+        alone = engines[gene].evaluate(tr, (LEAF, leaf), (INTERNAL, top), L)[0]  # unbatched path, same context
+        assert np.isfinite(want) and np.isfinite(lnl[gene])
+        assert rel(lnl[gene], want) <= TOL and rel(alone, want) <= TOL
+        if gene == 1:
+            assert engines[gene].last_status & WARN_LNL_NONFINITE
+            assert engines[gene].fetch_pattern_lh()[5] == 4 * -177.4456782233459932741
