@@ -356,6 +356,14 @@ int b200lk_batch_lnl_from_buffer(b200lk_batch *batch, const double *branch_len /
 /* Counters for the metric: pattern-node updates and kernel launches since create/reset. */
 int b200lk_get_counters(b200lk_ctx *ctx, int64_t *pattern_node_updates, int64_t *kernel_launches);
 int b200lk_reset_counters(b200lk_ctx *ctx);
+/* Minimum DRAM bytes of the partial-update kernels launched since create/reset, counted from the node programs the
+ * library actually launched (not from the reference's loop nest): every partial vector written once with its scale
+ * counters, every child vector a launch must fetch from HBM (all internal children for the level-batched kernels;
+ * for the 4-state pattern-stationary traversal only children produced by an earlier launch -- a vector of the same
+ * launch that no longer fits the per-thread stack is re-read by the CTA that just wrote it, from L2), one byte per
+ * tip state.  The denominator-free half of bench.py's roofline fraction.  Replaces
+ * nothing in the reference. */
+int b200lk_get_min_traffic(b200lk_ctx *ctx, int64_t *min_dram_bytes);
 int b200lk_synchronize(b200lk_ctx *ctx);
 /* Optional per-launch CUDA-event timing of the partial-update kernels (the dominant kernel):
  * accumulated milliseconds and launch count since the last reset.  Replaces nothing in the

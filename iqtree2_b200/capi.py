@@ -385,6 +385,12 @@ class Engine:
         self._check(self._f("get_counters")(self.ctx, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def min_traffic(self):
+        """Minimum DRAM bytes of the partial updates launched since the last reset (b200lk_get_min_traffic)."""
+        b = C.c_int64()
+        self._check(self._f("get_min_traffic")(self.ctx, C.byref(b)))
+        return b.value
+
     def reset_counters(self):
         self._check(self._f("reset_counters")(self.ctx))
 

@@ -182,6 +182,12 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
         c->theta_computed = false;
         return B200LK_OK;
     }
+    if (!c->batch) {  // level-batched kernels fetch every internal child from HBM and write every vector once
+        const int64_t vec_bytes = 8 * (int64_t)c->block + c->scale_per_ptn;
+        int64_t vecs = nnodes, tips = 0;
+        for (int j = 0; j < nchildren; j++) (children[j].kind == B200LK_CHILD_LEAF ? tips : vecs)++;
+        c->n_min_bytes += c->ntot * (vec_bytes * vecs + tips);
+    }
     int rc = launch_tables(c, nchildren);
     if (rc) return rc;
     if (tt_off > 0) {

@@ -176,6 +176,11 @@ struct b200lk_ctx {
     bool model_set, tips_set, theta_computed;
     int theta_dad_kind;
     int64_t n_updates, n_launches;
+    // minimum DRAM bytes of the partial-update launches enqueued since the last reset, counted from the node programs
+    // actually launched: every vector written once (+ scale bytes), every child vector that a launch has to fetch
+    // from HBM (level-batched kernels: all internal children; 4-state traversal: only children produced by an
+    // earlier launch; a vector evicted from the per-thread stack is re-read from L2), one byte per tip state read
+    int64_t n_min_bytes;
 };
 
 #define CUDA_TRY(ctx, expr)                                                                      \

@@ -380,7 +380,12 @@ extern "C" int b200lk_get_counters(b200lk_ctx *c, int64_t *updates, int64_t *lau
 }
 extern "C" int b200lk_reset_counters(b200lk_ctx *c) {
     if (!c) return B200LK_ERR_ARG;
-    c->n_updates = c->n_launches = 0;
+    c->n_updates = c->n_launches = c->n_min_bytes = 0;
+    return B200LK_OK;
+}
+extern "C" int b200lk_get_min_traffic(b200lk_ctx *c, int64_t *bytes) {
+    if (!c || !bytes) return B200LK_ERR_ARG;
+    *bytes = c->n_min_bytes;
     return B200LK_OK;
 }
 extern "C" int b200lk_result_device_ptr(b200lk_ctx *c, void **dptr) {

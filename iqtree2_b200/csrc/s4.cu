@@ -532,6 +532,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     int32_t *leaf_seq = reinterpret_cast<int32_t *>(c->h_prog) + *seq_used;
     const int chunk = S4_STATE_BYTES / S4_THREADS;
     int nseq = 0;
+    int64_t cross_reads = 0;
     // staged tip-state rows of this segment: its leaf children plus at most one pad row per node (a node never
     // straddles two chunks).  Nothing is padded at the END of a segment: a refill always reads a whole chunk of rows,
     // and the rows behind the last one used are the next segment's, or left-overs of an earlier call -- valid taxon ids
@@ -578,6 +579,9 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
                     entry_of[pr] = -1;
                 } else {
                     kind[k] = SRC_GLOBAL; id[k] = ch.id;
+                    // produced by an EARLIER launch (or call): a DRAM read.  A vector of this launch that no longer
+                    // fits the stack is re-read a few nodes after the same CTA wrote it: an L2 hit, not DRAM traffic
+                    if (pr < 0) cross_reads++;
                 }
             }
         }
@@ -625,6 +629,10 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(s4_traverse_kernel<NCM, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         c->trav_attr_set = true;
+    }
+    if (!c->batch) {
+        const int64_t vec_bytes = 8 * (int64_t)c->block + c->scale_per_ptn;
+        c->n_min_bytes += c->ntot * (vec_bytes * (count + cross_reads) + nseq);
     }
     prof_mark(c);
     if (c->batch) {
