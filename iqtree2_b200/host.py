@@ -130,6 +130,14 @@ class HostModel:
         return cls(h, 4, 1)
 
     @classmethod
+    def named(cls, name):
+        """The protein models BASELINE names, from the data compiled into the host layer: "LG", "LG+C60" (and "JC")."""
+        h = C.c_void_p()
+        _ck(lib().b200host_model_named(C.byref(h), name.encode()))
+        n, nmix = {"LG": (20, 1), "LG+C60": (20, 60), "JC": (4, 1)}[name]
+        return cls(h, n, nmix)
+
+    @classmethod
     def reversible(cls, exch, freqs):
         e, f = np.ascontiguousarray(exch, dtype=np.float64), np.asarray(freqs, dtype=np.float64)
         h = C.c_void_p()

@@ -146,6 +146,8 @@ public:
     static ModelSubst reversible(int n, const double *exch, const double *freqs, const std::string &name = "REV");
     static ModelSubst GTR(const double rates[6], const double freqs[4]);  // AC AG AT CG CT GT (model/modeldna.cpp)
     static ModelSubst JC();
+    static ModelSubst LG();     // model/modelprotein.cpp:287-310 (Le & Gascuel 2008), as data
+    static ModelSubst LGC60();  // LG + the C60 profile mixture, model/modelmixture.cpp:917-977, as data
     static ModelSubst mixture(const std::vector<ModelSubst> &classes, const std::vector<double> &weights);
     static ModelSubst fromEigen(int n, int nmix, const double *eval, const double *evec, const double *inv_evec,
                                 const double *freqs, const double *mixw);

@@ -71,6 +71,15 @@ void b200host_alignment_free(void *a) { delete (Alignment *)a; }
 int b200host_model_gtr(void **out, const double *rates6, const double *freqs4) {
     GUARD(*out = new ModelSubst(ModelSubst::GTR(rates6, freqs4)))
 }
+int b200host_model_named(void **out, const char *name) {  // "LG", "LG+C60", "JC"
+    GUARD({
+        const std::string nm(name ? name : "");
+        if (nm == "LG") *out = new ModelSubst(ModelSubst::LG());
+        else if (nm == "LG+C60") *out = new ModelSubst(ModelSubst::LGC60());
+        else if (nm == "JC") *out = new ModelSubst(ModelSubst::JC());
+        else outError("unknown model name " + nm);
+    })
+}
 int b200host_model_reversible(void **out, int n, const double *exch, const double *freqs) {
     GUARD(*out = new ModelSubst(ModelSubst::reversible(n, exch, freqs)))
 }

@@ -315,6 +315,39 @@ ModelSubst ModelSubst::JC() {
     return m;
 }
 
+// ---- the protein models BASELINE configs 3 and 4 name, as data (host/protein_data.inc, generated by
+// tools/extract_model_data.py from the published tables: model/modelprotein.cpp:287-310, model/modelmixture.cpp:917-977)
+#include "protein_data.inc"
+
+static void lgExchangeabilities(double *R) {  // [20][20] symmetric from the lower triangle, rows 1..19
+    for (int i = 0, k = 0; i < 20; i++) {
+        R[i * 20 + i] = 0.0;
+        for (int j = 0; j < i; j++, k++) R[i * 20 + j] = R[j * 20 + i] = B200_LG_LOWER[k];
+    }
+}
+
+// `-m LG`: LG exchangeabilities with LG's own frequencies (ModelProtein, model/modelprotein.cpp)
+ModelSubst ModelSubst::LG() {
+    double R[400];
+    lgExchangeabilities(R);
+    return reversible(20, R, B200_LG_FREQS, "LG");
+}
+
+// `-m LG+C60`: the POISSON of `model C60 = POISSON+G+FMIX{C60pi1:1:w1,...}` replaced by LG -- 60 classes sharing the LG
+// exchangeabilities, class k with frequency profile C60pi_k, rate 1 and fixed weight w_k; every class is normalised to
+// one expected substitution, and with weights summing to 1 the global rate is 1 (ModelMixture::initMixture,
+// model/modelmixture.cpp:1411-1437)
+ModelSubst ModelSubst::LGC60() {
+    double R[400];
+    lgExchangeabilities(R);
+    std::vector<ModelSubst> classes;
+    std::vector<double> w(B200_C60_WEIGHTS, B200_C60_WEIGHTS + 60);
+    for (int k = 0; k < 60; k++) classes.push_back(reversible(20, R, B200_C60_PROFILES + 20 * k, "LG+FC60pi" + std::to_string(k + 1)));
+    ModelSubst m = mixture(classes, w);
+    m.name = "LG+C60";
+    return m;
+}
+
 ModelSubst ModelSubst::mixture(const std::vector<ModelSubst> &classes, const std::vector<double> &weights) {
     if (classes.empty() || classes.size() != weights.size()) outError("mixture: classes and weights do not match");
     ModelSubst m;

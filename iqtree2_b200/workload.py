@@ -436,6 +436,46 @@ def gtr_model(rates=(1.0, 2.0, 1.5, 1.2, 2.5, 1.0), freqs=(0.3, 0.2, 0.2, 0.3)) 
     return make_model([(R, np.asarray(freqs))])
 
 
+_PROTEIN_DATA = None
+
+
+def protein_data():
+    """LG and C60 as data (iqtree2_b200/data/protein_models.json, written by tools/extract_model_data.py from the
+    published tables the reference carries: model/modelprotein.cpp:287-310, model/modelmixture.cpp:917-977)."""
+    global _PROTEIN_DATA
+    if _PROTEIN_DATA is None:
+        import json
+        import os
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "protein_models.json")) as f:
+            _PROTEIN_DATA = json.load(f)
+    return _PROTEIN_DATA
+
+
+def lg_exchangeabilities() -> np.ndarray:
+    low = protein_data()["LG"]["lower_triangle"]
+    R = np.zeros((20, 20))
+    k = 0
+    for i in range(20):
+        for j in range(i):
+            R[i, j] = R[j, i] = low[k]
+            k += 1
+    return R
+
+
+def lg_model() -> EigenModel:
+    """`-m LG`: LG exchangeabilities and LG's own frequencies."""
+    return make_model([(lg_exchangeabilities(), np.asarray(protein_data()["LG"]["freqs"]))])
+
+
+def lg_c60_model() -> EigenModel:
+    """`-m LG+C60`: 60 classes over the LG exchangeabilities, class k with profile C60pi_k, rate 1, fixed weight w_k
+    (`model C60 = POISSON+G+FMIX{C60pi1:1:w1,...}` with POISSON replaced by LG; every class normalised to one expected
+    substitution, so the global rate is 1: ModelMixture::initMixture, model/modelmixture.cpp:1411-1437)."""
+    d = protein_data()["C60"]
+    R = lg_exchangeabilities()
+    return make_model([(R, np.asarray(p)) for p in d["profiles"]], mixw=np.asarray(d["weights"]))
+
+
 def random_reversible_model(nstates: int, seed: int, nmix: int = 1) -> EigenModel:
     """A seeded random reversible model (stand-in where a named empirical matrix
     is not needed: the kernels only see the eigen-system)."""

@@ -31,7 +31,32 @@ CASES = {
     "aa_g4": (dict(ntaxa=8, nsite=80, nstates=20, seed=4, gaps=0.03), False, 0.0, 0),
     "aa_mix3_g4": (dict(ntaxa=6, nsite=50, nstates=20, nmix=3, seed=5), False, 0.0, 1),
     "example_phy": (None, False, 0.0, 0),
+    # the protein models BASELINE configs 3 and 4 name, from the published tables (iqtree2_b200/data/protein_models.json);
+    # their eigen-systems come from the REFERENCE's own solver (EigenDecomposition::eigensystem_sym in oracle/_ref)
+    "aa_lg_g4": (dict(ntaxa=9, nsite=90, nstates=20, seed=14, gaps=0.03, model="LG"), False, 0.0, 0),
+    "aa_lg_c60_g4": (dict(ntaxa=6, nsite=40, nstates=20, nmix=60, seed=15, model="LG+C60"), False, 0.0, 2),
 }
+NO_PARTIALS = ("dna_deep_scaling", "example_phy", "aa_lg_c60_g4")
+
+
+def reference_solved_model(name):
+    """LG / LG+C60 with every class decomposed by the reference's own eigen-solver."""
+    from tests.test_eigen import ref_eigen
+    R = W.lg_exchangeabilities()
+    exch = R[np.triu_indices(20, 1)]
+    d = W.protein_data()
+    if name == "LG":
+        classes, mixw = [np.asarray(d["LG"]["freqs"])], np.ones(1)
+    else:
+        classes, mixw = [np.asarray(p) for p in d["C60"]["profiles"]], np.asarray(d["C60"]["weights"])
+    ev, U, Ui, F = [], [], [], []
+    for fr in classes:
+        fr = fr / fr.sum()
+        e, u, ui = ref_eigen(exch, fr, 1.0)
+        ev.append(e); U.append(u); Ui.append(ui); F.append(fr)
+    return W.EigenModel(nstates=20, eval=np.ascontiguousarray(ev), evec=np.ascontiguousarray(U),
+                        inv_evec=np.ascontiguousarray(Ui), freqs=np.ascontiguousarray(F), mixw=mixw / mixw.sum(),
+                        Q=np.zeros(0))
 
 
 def problem(name):
@@ -41,11 +66,20 @@ def problem(name):
         tree = W.Tree.from_newick(open(os.path.join(HERE, "example17.nwk")).read(), aln.names)
         rates, props = W.discrete_gamma(0.5)
         return tree, W.gtr_model(), rates, props, aln
-    return make_problem(**kw)
+    kw = dict(kw)
+    named = kw.pop("model", None)
+    tree, model, rates, props, aln = make_problem(**kw)
+    if named:
+        model = reference_solved_model(named)
+        aln = W.simulate_alignment(tree, model, rates, props, kw["nsite"], kw["seed"] + 7, compress=True)
+    return tree, model, rates, props, aln
 
 
 def main():
+    only = sys.argv[1:]  # case names; none = all
     for name, (_, safe, pinv, leaf) in CASES.items():
+        if only and name not in only:
+            continue
         tree, model, rates, props, aln = problem(name)
         ref = oracle.RefRun(tree, aln, model, rates, props, kernel=oracle.LK_AVX_FMA, safe=safe, p_invar=pinv)
         out = dict(nstates=aln.nstates, states=aln.states, ptn_freq=aln.ptn_freq, newick=tree.to_newick(0, 17),
@@ -60,7 +94,7 @@ def main():
         for slot, ls in leaf_sets(tree, tr).items():
             part, sc = ref.fetch_branch(ls, leaf)
             out["scale_%d" % slot] = sc
-            if name not in ("dna_deep_scaling", "example_phy"):
+            if name not in NO_PARTIALS:
                 out["partial_%d" % slot] = part
         out["df"], out["ddf"] = ref.derv()
         out["lnl_buf"] = ref.from_buffer()
