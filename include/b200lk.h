@@ -106,6 +106,22 @@ typedef struct b200lk_end {
 
 /* ---- life cycle ------------------------------------------------------- */
 int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims);
+/* One problem over several GPUs of THIS process (SURVEY.md 8b "device_mask", 8e): the reference is one process whose
+ * kernels split the pattern range into packets for its OpenMP threads and sum the per-packet lnL / df / ddf
+ * (tree/phylokernelnew.h:1114-1142, 2377, 2792, 3273); this is the device form of that.  `devices` lists ndev CUDA
+ * ordinals (dims->device is ignored; an ordinal may repeat -- several shards on one GPU -- which only tests use).  The context owns one ordinary context per device over a contiguous range of
+ * whole 32-pattern tiles of EVERY partial vector (b200lk_shard_info); model tables are computed redundantly per GPU,
+ * nothing is exchanged during a traversal.  Every entry point below works unchanged on the returned context: it
+ * enqueues on all shards first (they run concurrently, driven from the one calling thread), then adds the per-shard
+ * sums on the host in device-index order -- bit-reproducible from run to run -- and the b200lk_fetch_* readers gather
+ * the shards' ranges.  b200lk_optimize_branch runs the reference's safeguarded Newton iteration with one fan-out and
+ * one ordered sum per step.  Not available on a sharded context (B200LK_ERR_UNSUPPORTED, at create or at the call):
+ * +ASC (its sums must be combined before the non-linear correction), site-specific and non-reversible contexts,
+ * heterotachy, robust scoring, batches, b200lk_set_stream / b200lk_result_device_ptr, b200lk_lnl_from_buffer_noalloc. */
+int b200lk_create_sharded(b200lk_ctx **out, const b200lk_dims *dims, const int32_t *devices, int32_t ndev);
+/* Shards of a context: their count, devices and observed-pattern ranges [begin, end) (any pointer may be NULL; arrays of
+ * at least *nshards entries).  An ordinary context reports one shard covering [0, nptn). */
+int b200lk_shard_info(b200lk_ctx *ctx, int32_t *nshards, int32_t *devices, int64_t *begin, int64_t *end);
 int b200lk_destroy(b200lk_ctx *ctx);
 const char *b200lk_last_error(const b200lk_ctx *ctx);
 const char *b200lk_version(void);

@@ -74,7 +74,9 @@ class Engine:
 
     def __init__(self, *, ntaxa, nstates, ncat, nmix=1, nptn, nslots, n_state_codes, safe_numeric=False,
                  fused_mix_rate=False, n_unobserved=0, device=0, lib_path=LIB_PATH, prefix="b200lk_",
-                 site_specific=False, nonrev=False):
+                 site_specific=False, nonrev=False, devices=None):
+        """devices: a list of CUDA ordinals -> b200lk_create_sharded (the problem split by site pattern over them, all
+        driven from this process); None -> b200lk_create on `device`."""
         if not os.path.exists(lib_path):
             raise B200LKError(
                 "%s is missing: build it first (python -c 'import __graft_entry__ as g; g.build()'). "
@@ -86,7 +88,11 @@ class Engine:
         self.ncat_mix = ncat if fused_mix_rate else ncat * nmix
         self.block = nstates * self.ncat_mix
         self.ctx = C.c_void_p()
-        self._check(self._f("create")(C.byref(self.ctx), C.byref(self.dims)))
+        if devices is not None:
+            arr = (C.c_int32 * len(devices))(*devices)
+            self._check(self._f("create_sharded")(C.byref(self.ctx), C.byref(self.dims), arr, len(devices)))
+        else:
+            self._check(self._f("create")(C.byref(self.ctx), C.byref(self.dims)))
         self._keep = []
 
     # -- plumbing ------------------------------------------------------------
@@ -380,6 +386,14 @@ class Engine:
         self._check(self._f("rell")(self.ctx, _dp(out)))
         return out
 
+    def shard_info(self):
+        """-> [(device, begin, end), ...]: the pattern range every shard holds (one entry for an ordinary context)."""
+        n = C.c_int32()
+        self._check(self._f("shard_info")(self.ctx, C.byref(n), None, None, None))
+        dev, b, e = (C.c_int32 * n.value)(), (C.c_int64 * n.value)(), (C.c_int64 * n.value)()
+        self._check(self._f("shard_info")(self.ctx, C.byref(n), dev, b, e))
+        return [(dev[i], b[i], e[i]) for i in range(n.value)]
+
     def counters(self):
         a, b = C.c_int64(), C.c_int64()
         self._check(self._f("get_counters")(self.ctx, C.byref(a), C.byref(b)))
@@ -481,7 +495,7 @@ class Batch:
 
 
 def engine_for(aln, model, rates, props, *, nslots, p_invar=0.0, safe_numeric=False, device=0,
-               lib_path=LIB_PATH, prefix="b200lk_", unobserved=None, fused=False, asc_holder=False):
+               lib_path=LIB_PATH, prefix="b200lk_", unobserved=None, fused=False, asc_holder=False, devices=None):
     """Create a context for a workload.Alignment + workload.EigenModel and load
     tips, pattern weights and the model (the one-time uploads of
     initializeAllPartialLh / computeTipPartialLikelihood)."""
@@ -489,7 +503,7 @@ def engine_for(aln, model, rates, props, *, nslots, p_invar=0.0, safe_numeric=Fa
     eng = Engine(ntaxa=aln.ntaxa, nstates=aln.nstates, ncat=len(rates), nmix=model.nmix, nptn=aln.nptn,
                  nslots=nslots, n_state_codes=aln.state_unknown + 1, safe_numeric=safe_numeric,
                  device=device, lib_path=lib_path, prefix=prefix, fused_mix_rate=fused,
-                 n_unobserved=0 if unobserved is None else np.asarray(unobserved).shape[1])
+                 n_unobserved=0 if unobserved is None else np.asarray(unobserved).shape[1], devices=devices)
     eng.upload_tips(aln.states, aln.ptn_freq, unobserved)
     if asc_holder:
         eng.set_asc(1)

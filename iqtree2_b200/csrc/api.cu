@@ -211,14 +211,14 @@ int check_ends(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
 }
 
 // copy `count` result doubles to the pinned host buffer and wait: the only D2H of an evaluation
-static int read_results(b200lk_ctx *c, int first, int count) {
+int read_results(b200lk_ctx *c, int first, int count) {
     CUDA_TRY(c, cudaMemcpyAsync(c->h_result + first, c->d_result + first, sizeof(double) * count,
                                 cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     return B200LK_OK;
 }
 
-static int finish_lnl(b200lk_ctx *c, double *lnl, bool from_branch = false) {
+int finish_lnl(b200lk_ctx *c, double *lnl, bool from_branch) {
     int rc = read_results(c, 0, 1);
     if (rc) return rc;
     int warn = 0;
@@ -237,7 +237,7 @@ static int finish_lnl(b200lk_ctx *c, double *lnl, bool from_branch = false) {
     return warn;
 }
 
-static int finish_derv(b200lk_ctx *c, double *df, double *ddf) {
+int finish_derv(b200lk_ctx *c, double *df, double *ddf) {
     int rc = read_results(c, 1, 2);
     if (rc) return rc;
     double a = c->h_result[1], b = c->h_result[2];
@@ -253,6 +253,7 @@ static int finish_derv(b200lk_ctx *c, double *df, double *ddf) {
 
 extern "C" int b200lk_update_partials(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes,
                                       const b200lk_child *children, int32_t nchildren) {
+    SHARD_FORWARD(c, shard_update_partials(c, nodes, nnodes, children, nchildren));
     int rc = check_ready(c);
     if (rc) return rc;
     CUDA_TRY(c, cudaSetDevice(c->device));
@@ -262,6 +263,7 @@ extern "C" int b200lk_update_partials(b200lk_ctx *c, const b200lk_node *nodes, i
 }
 
 extern "C" int b200lk_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length, double *lnl) {
+    SHARD_FORWARD(c, shard_branch_lnl(c, dad, node, length, lnl));
     int rc = check_ready(c);
     if (rc) return rc;
     if (!lnl || check_ends(c, dad, node)) return B200LK_ERR_ARG;
@@ -273,6 +275,7 @@ extern "C" int b200lk_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node,
 }
 
 extern "C" int b200lk_build_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
+    SHARD_FORWARD(c, shard_build_theta(c, dad, node));
     int rc = check_ready(c);
     if (rc) return rc;
     if (check_ends(c, dad, node)) return B200LK_ERR_ARG;
@@ -288,6 +291,7 @@ extern "C" int b200lk_build_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node
 }
 
 extern "C" int b200lk_derv(b200lk_ctx *c, double length, double *df, double *ddf) {
+    SHARD_FORWARD(c, shard_derv(c, length, df, ddf));
     int rc = check_ready(c);
     if (rc) return rc;
     if (!c->theta_computed) return B200LK_ERR_STATE;
@@ -299,6 +303,7 @@ extern "C" int b200lk_derv(b200lk_ctx *c, double length, double *df, double *ddf
 }
 
 extern "C" int b200lk_lnl_from_buffer(b200lk_ctx *c, double length, double *lnl) {
+    SHARD_FORWARD(c, shard_lnl_from_buffer(c, length, lnl));
     int rc = check_ready(c);
     if (rc) return rc;
     if (!lnl) return B200LK_ERR_ARG;
@@ -307,11 +312,12 @@ extern "C" int b200lk_lnl_from_buffer(b200lk_ctx *c, double length, double *lnl)
     if (c->d.nptn == 0) { *lnl = 0.0; return B200LK_OK; }
     rc = launch_from_buffer(c, length);
     if (rc) return rc;
-    return finish_lnl(c, lnl);
+    return finish_lnl(c, lnl, false);
 }
 
 extern "C" int b200lk_optimize_branch(b200lk_ctx *c, b200lk_end dad, b200lk_end node, const b200lk_newton *nr,
                                       double *optx, double *d2l, int32_t *nsteps) {
+    SHARD_FORWARD(c, shard_optimize_branch(c, dad, node, nr, optx, d2l, nsteps));
     int rc = check_ready(c);
     if (rc) return rc;
     if (!nr || !optx || check_ends(c, dad, node) || !(nr->min_len <= nr->max_len) || nr->max_steps < 1)
@@ -339,6 +345,7 @@ extern "C" int b200lk_optimize_branch(b200lk_ctx *c, b200lk_end dad, b200lk_end 
 extern "C" int b200lk_evaluate_async(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes,
                                      const b200lk_child *children, int32_t nchildren, b200lk_end dad,
                                      b200lk_end node, double length, int want_lnl, int want_derv) {
+    SHARD_FORWARD(c, shard_evaluate_async(c, nodes, nnodes, children, nchildren, dad, node, length, want_lnl, want_derv));
     int rc = check_ready(c);
     if (rc) return rc;
     if (check_ends(c, dad, node)) return B200LK_ERR_ARG;
@@ -364,6 +371,7 @@ extern "C" int b200lk_evaluate_async(b200lk_ctx *c, const b200lk_node *nodes, in
 }
 
 extern "C" int b200lk_read_results(b200lk_ctx *c, double *lnl, double *df, double *ddf) {
+    SHARD_FORWARD(c, shard_read_results(c, lnl, df, ddf));
     if (!c) return B200LK_ERR_ARG;
     CUDA_TRY(c, cudaSetDevice(c->device));
     // one synchronising read for everything
@@ -402,6 +410,7 @@ extern "C" int b200lk_evaluate(b200lk_ctx *c, const b200lk_node *nodes, int32_t 
 
 // params->robust_phy_keep / robust_median as computeLikelihoodBranch reads them (tree/phylokernelnew.h:3096-3135)
 extern "C" int b200lk_set_robust(b200lk_ctx *c, double keep, int32_t median) {
+    SHARD_FORWARD(c, shard_set_robust(c, keep, median));
     if (!c || !(keep > 0.0) || keep > 1.0) return B200LK_ERR_ARG;
     if ((keep < 1.0 || median) && (c->nonrev || c->site)) return B200LK_ERR_UNSUPPORTED;
     c->robust_keep = keep;
@@ -411,6 +420,7 @@ extern "C" int b200lk_set_robust(b200lk_ctx *c, double keep, int32_t median) {
 
 // ---- +ASC flavour, pattern weights --------------------------------------------------------------------------------
 extern "C" int b200lk_set_asc(b200lk_ctx *c, int32_t type) {
+    SHARD_REFUSE(c, "+ASC");
     if (!c || (type != B200LK_ASC_LEWIS && type != B200LK_ASC_HOLDER)) return B200LK_ERR_ARG;
     if (type == B200LK_ASC_HOLDER) {
         if (c->d.n_unobserved == 0 || c->d.n_unobserved != (int64_t)c->d.nstates * c->d.nptn) {
@@ -429,6 +439,7 @@ extern "C" int b200lk_set_asc(b200lk_ctx *c, int32_t type) {
 }
 
 extern "C" int b200lk_set_ptn_freq(b200lk_ctx *c, const double *ptn_freq) {
+    SHARD_FORWARD(c, shard_set_ptn_freq(c, ptn_freq));
     if (!c || !ptn_freq) return B200LK_ERR_ARG;
     if (!c->tips_set) return B200LK_ERR_STATE;
     CUDA_TRY(c, cudaSetDevice(c->device));
@@ -459,6 +470,7 @@ static int stage_branch_mixlen(b200lk_ctx *c, const double *len) {
 
 extern "C" int b200lk_update_partials_mixlen(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes,
                                              const b200lk_child *children, int32_t nchildren, const double *child_len) {
+    SHARD_REFUSE(c, "heterotachy (mixed branch lengths)");
     int rc = check_mixlen(c);
     if (rc) return rc;
     if (!child_len) return B200LK_ERR_ARG;
@@ -477,6 +489,7 @@ extern "C" int b200lk_update_partials_mixlen(b200lk_ctx *c, const b200lk_node *n
 }
 
 extern "C" int b200lk_branch_lnl_mixlen(b200lk_ctx *c, b200lk_end dad, b200lk_end node, const double *len, double *lnl) {
+    SHARD_REFUSE(c, "heterotachy (mixed branch lengths)");
     int rc = check_mixlen(c);
     if (rc) return rc;
     if (!len || !lnl || check_ends(c, dad, node)) return B200LK_ERR_ARG;
@@ -491,6 +504,7 @@ extern "C" int b200lk_branch_lnl_mixlen(b200lk_ctx *c, b200lk_end dad, b200lk_en
 }
 
 extern "C" int b200lk_lnl_from_buffer_mixlen(b200lk_ctx *c, const double *len, double *lnl) {
+    SHARD_REFUSE(c, "heterotachy (mixed branch lengths)");
     int rc = check_mixlen(c);
     if (rc) return rc;
     if (!len || !lnl) return B200LK_ERR_ARG;
@@ -502,10 +516,11 @@ extern "C" int b200lk_lnl_from_buffer_mixlen(b200lk_ctx *c, const double *len, d
     rc = launch_from_buffer(c, len[0]);
     c->cur_branch_mixlen = nullptr;
     if (rc) return rc;
-    return finish_lnl(c, lnl);
+    return finish_lnl(c, lnl, false);
 }
 
 extern "C" int b200lk_derv_mixlen(b200lk_ctx *c, const double *len, double *df, double *ddf, double *lnl) {
+    SHARD_REFUSE(c, "heterotachy (mixed branch lengths)");
     int rc = check_mixlen(c);
     if (rc) return rc;
     if (!len || !df || !ddf) return B200LK_ERR_ARG;
@@ -543,6 +558,7 @@ extern "C" int b200lk_derv_mixlen(b200lk_ctx *c, const double *len, double *df, 
 }
 
 extern "C" int b200lk_derv_mixlen_class(b200lk_ctx *c, int32_t cur_mixlen, double len, double *df, double *ddf) {
+    SHARD_REFUSE(c, "heterotachy (mixed branch lengths)");
     int rc = check_mixlen(c);
     if (rc) return rc;
     if (cur_mixlen < 0 || cur_mixlen >= c->d.ncat) return B200LK_ERR_ARG;

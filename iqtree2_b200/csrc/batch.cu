@@ -58,6 +58,8 @@ extern "C" int b200lk_batch_create(b200lk_batch **out, b200lk_ctx **ctxs, int32_
     *out = nullptr;
     const b200lk_ctx *c0 = ctxs[0];
     if (!c0) return B200LK_ERR_ARG;
+    for (int i = 0; i < n; i++)
+        if (ctxs[i] && ctxs[i]->shards) return B200LK_ERR_UNSUPPORTED;  // a sharded parent owns no device buffers
     // what a batched launch can express: the 4-state and the 20-state tensor path, one category group, no +ASC
     if (!(c0->tile == 32 || (c0->dense20 && c0->ncat_mix <= 4)) || c0->d.n_unobserved != 0) return B200LK_ERR_UNSUPPORTED;
     for (int i = 0; i < n; i++) {

@@ -1370,6 +1370,7 @@ int noalloc_setup(b200lk_ctx *c) {
 }
 
 extern "C" int b200lk_lnl_from_buffer_noalloc(b200lk_ctx *c, double length, double *lnl) {
+    SHARD_REFUSE(c, "b200lk_lnl_from_buffer_noalloc");
     if (!c || !lnl) return B200LK_ERR_ARG;
     if (!c->model_set || !c->tips_set || !c->theta_computed) {
         snprintf(c->err, sizeof(c->err), "lnl_from_buffer_noalloc: set the model, upload the tips and build theta first");

@@ -75,6 +75,14 @@ struct BatchLaunch {           // non-null in b200lk_ctx::batch while a batched 
     const double *d_branch_len;  // [n] length of the branch the likelihood is taken at
 };
 
+// b200lk_create_sharded (shard.cu): one problem split by site pattern over several devices of THIS process.  The parent
+// context owns no device memory; every entry point fans out to the per-device contexts and sums on the host in
+// device-index order.
+struct ShardSet {
+    std::vector<b200lk_ctx *> ctx;    // one ordinary context per device, in the order the caller listed the devices
+    std::vector<int64_t> begin, end;  // observed-pattern range [begin, end) of each shard (whole 32-pattern tiles)
+};
+
 // process-wide A/B and test hooks, read from the environment ONCE (context.cu) -- never on a launch path
 struct B200Env {
     int s4_minb;       // B200LK_S4_MINB: resident-CTA instantiation of s4_traverse_kernel (8 / 10 / 12); 0 = default
@@ -88,6 +96,7 @@ struct B200Env {
 const B200Env &b200_env();
 
 struct b200lk_ctx {
+    ShardSet *shards;  // non-null: a sharded parent
     int sms;                          // multiprocessors of the device
     double *m_block, *h_model_stage;  // the DevModel arrays as ONE device block + its pinned staging mirror
     size_t m_block_doubles, m_off[8];
@@ -212,6 +221,53 @@ static inline void prof_mark(b200lk_ctx *c) {
 }
 
 // launchers implemented in tables.cu / partial.cu / branch.cu
+// shard.cu: what the entry points forward to when the context is a sharded parent
+#define SHARD_FORWARD(c, call) \
+    if ((c) && (c)->shards) return call
+#define SHARD_REFUSE(c, what) \
+    if ((c) && (c)->shards) return shard_refuse(c, what)
+int shard_refuse(b200lk_ctx *c, const char *what);
+int shard_destroy(b200lk_ctx *c);
+int shard_upload_tips(b200lk_ctx *c, const uint8_t *states, const uint8_t *unobserved, const double *ptn_freq);
+int shard_set_ptn_invar(b200lk_ctx *c, const double *v);
+int shard_set_ptn_freq(b200lk_ctx *c, const double *v);
+int shard_set_model(b200lk_ctx *c, const double *eval, const double *evec, const double *inv_evec, const double *rates,
+                    const double *props, const double *mixw, const double *tip);
+int shard_set_model_rates(b200lk_ctx *c, const double *exch, const double *freqs, const double *tot, const double *tipvec,
+                          const double *rates, const double *props, const double *mixw);
+int shard_set_robust(b200lk_ctx *c, double keep, int32_t median);
+int shard_update_partials(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children, int32_t nchildren);
+int shard_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length, double *lnl);
+int shard_build_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node);
+int shard_derv(b200lk_ctx *c, double length, double *df, double *ddf);
+int shard_lnl_from_buffer(b200lk_ctx *c, double length, double *lnl);
+int shard_evaluate_async(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
+                         int32_t nchildren, b200lk_end dad, b200lk_end node, double length, int want_lnl, int want_derv);
+int shard_read_results(b200lk_ctx *c, double *lnl, double *df, double *ddf);
+int shard_optimize_branch(b200lk_ctx *c, b200lk_end dad, b200lk_end node, const b200lk_newton *nr, double *optx, double *d2l,
+                          int32_t *nsteps);
+int shard_fetch_pattern_lh(b200lk_ctx *c, double *out);
+int shard_fetch_pattern_lh_cat(b200lk_ctx *c, double *out);
+int shard_fetch_scale_num(b200lk_ctx *c, int32_t slot, uint8_t *out);
+int shard_fetch_partial(b200lk_ctx *c, int32_t slot, double *out);
+int shard_fetch_theta(b200lk_ctx *c, double *theta, double *bscale);
+int shard_fetch_model(b200lk_ctx *c, double *eval, double *evec, double *inv_evec);
+int shard_get_counters(b200lk_ctx *c, int64_t *updates, int64_t *launches);
+int shard_reset_counters(b200lk_ctx *c);
+int shard_get_min_traffic(b200lk_ctx *c, int64_t *bytes);
+int shard_synchronize(b200lk_ctx *c);
+int shard_set_profiling(b200lk_ctx *c, int on);
+int shard_get_profile(b200lk_ctx *c, double *partial_ms, int64_t *partial_launches, int reset);
+int shard_upload_boot_samples(b200lk_ctx *c, const float *samples, int32_t nsamples);
+int shard_rell(b200lk_ctx *c, double *rell);
+// api.cu: the blocking halves of the entry points (one synchronising D2H of the result doubles)
+int read_results(b200lk_ctx *c, int first, int count);
+int finish_lnl(b200lk_ctx *c, double *lnl, bool from_branch);
+int finish_derv(b200lk_ctx *c, double *df, double *ddf);
+// context.cu: the uploads with an explicit source pitch (a shard takes a column range of the caller's matrix)
+int upload_tips_pitched(b200lk_ctx *c, const uint8_t *states, size_t spitch, const uint8_t *unobserved, size_t upitch,
+                        const double *ptn_freq);
+int upload_boot_samples_pitched(b200lk_ctx *c, const float *samples, size_t pitch_floats, int32_t nsamples);
 int launch_tables(b200lk_ctx *c, int nchildren);
 int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children, int32_t nchildren);
 int check_ends(b200lk_ctx *c, b200lk_end dad, b200lk_end node);

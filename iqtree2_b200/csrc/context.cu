@@ -207,6 +207,7 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
 }
 
 extern "C" int b200lk_destroy(b200lk_ctx *c) {
+    SHARD_FORWARD(c, shard_destroy(c));
     if (!c) return B200LK_OK;
     cudaSetDevice(c->device);
     if (c->own_stream) cudaStreamSynchronize(c->own_stream);
@@ -256,28 +257,30 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
 }
 
 extern "C" int b200lk_set_stream(b200lk_ctx *c, void *stream) {
+    SHARD_REFUSE(c, "a caller-owned stream (every shard runs on its own device and stream)");
     if (!c) return B200LK_ERR_ARG;
     c->stream = stream ? (cudaStream_t)stream : c->own_stream;
     return B200LK_OK;
 }
 
 extern "C" int b200lk_synchronize(b200lk_ctx *c) {
+    SHARD_FORWARD(c, shard_synchronize(c));
     if (!c) return B200LK_ERR_ARG;
     CUDA_TRY(c, cudaSetDevice(c->device));
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     return B200LK_OK;
 }
 
-extern "C" int b200lk_upload_tips(b200lk_ctx *c, const uint8_t *states, const uint8_t *unobserved,
-                                  const double *ptn_freq) {
+int upload_tips_pitched(b200lk_ctx *c, const uint8_t *states, size_t spitch, const uint8_t *unobserved, size_t upitch,
+                        const double *ptn_freq) {
     if (!c || (!states && c->d.nptn) || !ptn_freq || (c->d.n_unobserved && !unobserved)) return B200LK_ERR_ARG;
     CUDA_TRY(c, cudaSetDevice(c->device));
     const int64_t nptn = c->d.nptn, nun = c->d.n_unobserved;
     if (nptn)
-        CUDA_TRY(c, cudaMemcpy2DAsync(c->states, c->ntot_pad, states, nptn, nptn, c->d.ntaxa,
+        CUDA_TRY(c, cudaMemcpy2DAsync(c->states, c->ntot_pad, states, spitch, nptn, c->d.ntaxa,
                                       cudaMemcpyHostToDevice, c->stream));
     if (nun)
-        CUDA_TRY(c, cudaMemcpy2DAsync(c->states + nptn, c->ntot_pad, unobserved, nun, nun, c->d.ntaxa,
+        CUDA_TRY(c, cudaMemcpy2DAsync(c->states + nptn, c->ntot_pad, unobserved, upitch, nun, c->d.ntaxa,
                                       cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(c, cudaMemcpyAsync(c->ptn_freq, ptn_freq, sizeof(double) * nptn, cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
@@ -287,7 +290,15 @@ extern "C" int b200lk_upload_tips(b200lk_ctx *c, const uint8_t *states, const ui
     return B200LK_OK;
 }
 
+extern "C" int b200lk_upload_tips(b200lk_ctx *c, const uint8_t *states, const uint8_t *unobserved,
+                                  const double *ptn_freq) {
+    SHARD_FORWARD(c, shard_upload_tips(c, states, unobserved, ptn_freq));
+    if (!c) return B200LK_ERR_ARG;
+    return upload_tips_pitched(c, states, (size_t)c->d.nptn, unobserved, (size_t)c->d.n_unobserved, ptn_freq);
+}
+
 extern "C" int b200lk_set_ptn_invar(b200lk_ctx *c, const double *ptn_invar) {
+    SHARD_FORWARD(c, shard_set_ptn_invar(c, ptn_invar));
     if (!c || !ptn_invar) return B200LK_ERR_ARG;
     CUDA_TRY(c, cudaSetDevice(c->device));
     CUDA_TRY(c, cudaMemcpyAsync(c->ptn_invar, ptn_invar, sizeof(double) * c->ntot, cudaMemcpyHostToDevice, c->stream));
@@ -299,6 +310,7 @@ extern "C" int b200lk_set_ptn_invar(b200lk_ctx *c, const double *ptn_invar) {
 extern "C" int b200lk_set_model(b200lk_ctx *c, const double *eval, const double *evec, const double *inv_evec,
                                 const double *rates, const double *props, const double *mixw,
                                 const double *tip_partial_lh) {
+    SHARD_FORWARD(c, shard_set_model(c, eval, evec, inv_evec, rates, props, mixw, tip_partial_lh));
     if (!c || !eval || !evec || !inv_evec || !rates || !props || !mixw || !tip_partial_lh) return B200LK_ERR_ARG;
     if (c->site || c->nonrev) return B200LK_ERR_STATE;  // these contexts take b200lk_set_site_models / _set_model_nonrev
     CUDA_TRY(c, cudaSetDevice(c->device));
@@ -341,14 +353,17 @@ static int d2h(b200lk_ctx *c, void *dst, const void *src, size_t bytes) {
 }
 
 extern "C" int b200lk_fetch_pattern_lh(b200lk_ctx *c, double *out) {
+    SHARD_FORWARD(c, shard_fetch_pattern_lh(c, out));
     if (!c || !out) return B200LK_ERR_ARG;
     return d2h(c, out, c->pattern_lh, sizeof(double) * c->d.nptn);
 }
 extern "C" int b200lk_fetch_pattern_lh_cat(b200lk_ctx *c, double *out) {
+    SHARD_FORWARD(c, shard_fetch_pattern_lh_cat(c, out));
     if (!c || !out) return B200LK_ERR_ARG;
     return d2h(c, out, c->pattern_lh_cat, sizeof(double) * c->d.nptn * c->ncat_mix);
 }
 extern "C" int b200lk_fetch_scale_num(b200lk_ctx *c, int32_t slot, uint8_t *out) {
+    SHARD_FORWARD(c, shard_fetch_scale_num(c, slot, out));
     if (!c || !out || slot < 0 || slot >= c->d.nslots) return B200LK_ERR_ARG;
     return d2h(c, out, slot_scale(c, slot), (size_t)c->d.nptn * c->scale_per_ptn);
 }
@@ -363,32 +378,38 @@ static int d2h_vector(b200lk_ctx *c, double *out, const double *dev) {
     return B200LK_OK;
 }
 extern "C" int b200lk_fetch_partial(b200lk_ctx *c, int32_t slot, double *out) {
+    SHARD_FORWARD(c, shard_fetch_partial(c, slot, out));
     if (!c || !out || slot < 0 || slot >= c->d.nslots) return B200LK_ERR_ARG;
     return d2h_vector(c, out, slot_partial(c, slot));
 }
 extern "C" int b200lk_fetch_theta(b200lk_ctx *c, double *theta, double *bscale) {
+    SHARD_FORWARD(c, shard_fetch_theta(c, theta, bscale));
     if (!c || !theta) return B200LK_ERR_ARG;
     int rc = d2h_vector(c, theta, c->theta_all);
     if (rc == B200LK_OK && bscale) rc = d2h(c, bscale, c->buffer_scale_all, sizeof(double) * c->d.nptn);
     return rc;
 }
 extern "C" int b200lk_get_counters(b200lk_ctx *c, int64_t *updates, int64_t *launches) {
+    SHARD_FORWARD(c, shard_get_counters(c, updates, launches));
     if (!c) return B200LK_ERR_ARG;
     if (updates) *updates = c->n_updates;
     if (launches) *launches = c->n_launches;
     return B200LK_OK;
 }
 extern "C" int b200lk_reset_counters(b200lk_ctx *c) {
+    SHARD_FORWARD(c, shard_reset_counters(c));
     if (!c) return B200LK_ERR_ARG;
     c->n_updates = c->n_launches = c->n_min_bytes = 0;
     return B200LK_OK;
 }
 extern "C" int b200lk_get_min_traffic(b200lk_ctx *c, int64_t *bytes) {
+    if (c && c->shards && bytes) return shard_get_min_traffic(c, bytes);
     if (!c || !bytes) return B200LK_ERR_ARG;
     *bytes = c->n_min_bytes;
     return B200LK_OK;
 }
 extern "C" int b200lk_result_device_ptr(b200lk_ctx *c, void **dptr) {
+    SHARD_REFUSE(c, "a single device result buffer (the shards' sums are added on the host)");
     if (!c || !dptr) return B200LK_ERR_ARG;
     *dptr = c->d_result;
     return B200LK_OK;
@@ -396,12 +417,14 @@ extern "C" int b200lk_result_device_ptr(b200lk_ctx *c, void **dptr) {
 
 // ---- per-launch timing of the partial-update kernels -------------------------
 extern "C" int b200lk_set_profiling(b200lk_ctx *c, int on) {
+    SHARD_FORWARD(c, shard_set_profiling(c, on));
     if (!c) return B200LK_ERR_ARG;
     c->profiling = on != 0;
     return B200LK_OK;
 }
 
 extern "C" int b200lk_get_profile(b200lk_ctx *c, double *partial_ms, int64_t *partial_launches, int reset) {
+    SHARD_FORWARD(c, shard_get_profile(c, partial_ms, partial_launches, reset));
     if (!c) return B200LK_ERR_ARG;
     CUDA_TRY(c, cudaSetDevice(c->device));
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
@@ -421,7 +444,7 @@ extern "C" int b200lk_get_profile(b200lk_ctx *c, double *partial_ms, int64_t *pa
 }
 
 // ---- UFBoot RELL ---------------------------------------------------------------------------------------------
-extern "C" int b200lk_upload_boot_samples(b200lk_ctx *c, const float *samples, int32_t nsamples) {
+int upload_boot_samples_pitched(b200lk_ctx *c, const float *samples, size_t pitch_floats, int32_t nsamples) {
     if (!c || !samples || nsamples < 1) return B200LK_ERR_ARG;
     CUDA_TRY(c, cudaSetDevice(c->device));
     if (c->boot_samples) CUDA_TRY(c, cudaFree(c->boot_samples));
@@ -430,7 +453,7 @@ extern "C" int b200lk_upload_boot_samples(b200lk_ctx *c, const float *samples, i
     c->boot_samples = nullptr;
     c->d_rell = c->h_rell = nullptr;
     c->nboot = 0;
-    const size_t bytes = sizeof(float) * (size_t)nsamples * c->d.nptn;
+    const size_t row = sizeof(float) * (size_t)c->d.nptn, bytes = row * nsamples;
     if (cudaMalloc(&c->boot_samples, bytes ? bytes : 4) != cudaSuccess) {
         cudaGetLastError();
         snprintf(c->err, sizeof(c->err), "cannot allocate %zu bytes for %d bootstrap resamples", bytes, nsamples);
@@ -438,13 +461,22 @@ extern "C" int b200lk_upload_boot_samples(b200lk_ctx *c, const float *samples, i
     }
     CUDA_TRY(c, cudaMalloc(&c->d_rell, sizeof(double) * nsamples));
     CUDA_TRY(c, cudaMallocHost(&c->h_rell, sizeof(double) * nsamples));
-    CUDA_TRY(c, cudaMemcpyAsync(c->boot_samples, samples, bytes, cudaMemcpyHostToDevice, c->stream));
+    if (row)
+        CUDA_TRY(c, cudaMemcpy2DAsync(c->boot_samples, row, samples, sizeof(float) * pitch_floats, row, nsamples,
+                                      cudaMemcpyHostToDevice, c->stream));
     CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     c->nboot = nsamples;
     return B200LK_OK;
 }
 
+extern "C" int b200lk_upload_boot_samples(b200lk_ctx *c, const float *samples, int32_t nsamples) {
+    SHARD_FORWARD(c, shard_upload_boot_samples(c, samples, nsamples));
+    if (!c) return B200LK_ERR_ARG;
+    return upload_boot_samples_pitched(c, samples, (size_t)c->d.nptn, nsamples);
+}
+
 extern "C" int b200lk_rell(b200lk_ctx *c, double *rell) {
+    SHARD_FORWARD(c, shard_rell(c, rell));
     if (!c || !rell) return B200LK_ERR_ARG;
     if (c->nboot < 1) {
         snprintf(c->err, sizeof(c->err), "b200lk_rell: upload the bootstrap resamples first");

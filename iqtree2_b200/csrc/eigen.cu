@@ -192,6 +192,7 @@ __global__ void __launch_bounds__(EIG_THREADS) jacobi_model_kernel(const double 
 extern "C" int b200lk_set_model_rates(b200lk_ctx *c, const double *exch, const double *freqs, const double *total_num_subst,
                                       const double *tipvec, const double *rates, const double *props,
                                       const double *mixw) {
+    SHARD_FORWARD(c, shard_set_model_rates(c, exch, freqs, total_num_subst, tipvec, rates, props, mixw));
     if (!c || !exch || !freqs || !tipvec || !rates || !props || !mixw) return B200LK_ERR_ARG;
     CUDA_TRY(c, cudaSetDevice(c->device));
     const int n = c->d.nstates, nmix = c->d.nmix, codes = c->d.n_state_codes, ne = n * (n - 1) / 2;
@@ -249,6 +250,7 @@ extern "C" int b200lk_set_model_rates(b200lk_ctx *c, const double *exch, const d
 }
 
 extern "C" int b200lk_fetch_model(b200lk_ctx *c, double *eval, double *evec, double *inv_evec) {
+    SHARD_FORWARD(c, shard_fetch_model(c, eval, evec, inv_evec));
     if (!c || !eval || !evec || !inv_evec) return B200LK_ERR_ARG;
     if (!c->model_set) return B200LK_ERR_STATE;
     CUDA_TRY(c, cudaSetDevice(c->device));

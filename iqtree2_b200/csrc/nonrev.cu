@@ -26,6 +26,7 @@ __device__ __forceinline__ int d_kind(int kind) { return kind & B200LK_CHILD_KIN
 extern "C" int b200lk_set_model_nonrev(b200lk_ctx *c, const double *rate_matrix, const double *ceval, const double *cevec,
                                        const double *cinv_evec, const double *freqs, const double *tipvec,
                                        const double *rates, const double *props, const double *mixw, int rooted) {
+    SHARD_REFUSE(c, "the non-reversible kernel family");
     if (!c || !rate_matrix || !ceval || !cevec || !cinv_evec || !freqs || !tipvec || !rates || !props || !mixw)
         return B200LK_ERR_ARG;
     if (!c->nonrev) return B200LK_ERR_STATE;

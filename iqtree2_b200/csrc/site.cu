@@ -297,6 +297,7 @@ int launch_site_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &lev
 
 extern "C" int b200lk_set_site_models(b200lk_ctx *c, const double *eval, const double *evec, const double *inv_evec,
                                       const double *rates, const double *props, const double *tipvec) {
+    SHARD_REFUSE(c, "site-specific models");
     if (!c || !eval || !evec || !inv_evec || !rates || !props || !tipvec) return B200LK_ERR_ARG;
     if (!c->site) return B200LK_ERR_STATE;  // the context was not created with dims.site_specific
     if (!c->tips_set) return B200LK_ERR_STATE;  // the tip vectors are derived from the uploaded states

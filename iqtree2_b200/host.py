@@ -196,7 +196,7 @@ class HostTree:
     (LK_CUDA), initializeAllPartialLh)."""
 
     def __init__(self, newick, aln, model, rate, safe=False, device=0, device_newton=True, asc=False, mem_save=None,
-                 asc_holder=False, robust=None, mixlen=None):
+                 asc_holder=False, robust=None, mixlen=None, devices=None):
         """mem_save: None = one slot per internal node; a number = -mem (LM_MEM_SAVE) with that Params::max_mem_size
         (0: the minimum log2(ntaxa)+1 slots; <= 1: that fraction of ntaxa-2).  asc_holder: +ASC with missing data.
         robust: (keep, median) = Params::robust_phy_keep / robust_median.  mixlen: class multipliers -> a
@@ -207,6 +207,9 @@ class HostTree:
             lib().b200host_set_mem_fraction(C.c_double(float(mem_save)))
         if robust is not None:
             lib().b200host_set_robust(C.c_double(float(robust[0])), int(bool(robust[1])))
+        if devices is not None:  # Params::devices: the alignment split by site pattern over these GPUs
+            arr = (C.c_int32 * len(devices))(*devices)
+            lib().b200host_set_next_devices(arr, len(devices))
         self.mixlen = 0
         if mixlen is not None:
             mm = np.ascontiguousarray(mixlen, dtype=np.float64)

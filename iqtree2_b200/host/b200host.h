@@ -44,6 +44,7 @@ struct KernelABI {
     void *dl;
     std::string path, prefix;
     int (*create)(b200lk_ctx **, const b200lk_dims *);
+    int (*create_sharded)(b200lk_ctx **, const b200lk_dims *, const int32_t *, int32_t);  // optional
     int (*destroy)(b200lk_ctx *);
     int (*upload_tips)(b200lk_ctx *, const uint8_t *, const uint8_t *, const double *);
     int (*set_ptn_invar)(b200lk_ctx *, const double *);
@@ -234,6 +235,9 @@ struct Params {  // the few fields of utils/tools.h Params the path reads
     bool robust_median = false;       // --robust-median (utils/tools.cpp:1295)
     int numseq_safe_scaling = 2000;   // utils/tools.cpp:1235-1236
     int device = 0;
+    // more than one entry: the alignment is split by site pattern over these GPUs, all driven from this process
+    // (b200lk_create_sharded; the device form of the reference's packets, tree/phylokernelnew.h:1114-1142)
+    std::vector<int> devices;
     bool device_newton = true;        // run minimizeNewton's iteration on the device when the library offers it
 };
 

@@ -135,7 +135,17 @@ void PhyloTree::initializeAllPartialLh() {
     if (holder && !k.set_asc) outError("the kernel library has no Holder +ASC (b200lk_set_asc)");
     d.n_unobserved = holder ? (int64_t)aln->num_states * (int64_t)aln->getNPattern() : (asc ? aln->num_states : 0);
     d.device = params ? params->device : 0;
-    int rc = k.create(&ctx, &d);
+    int rc;
+    if (params && params->devices.size() > 1) {
+        if (!k.create_sharded) outError("the kernel library has no b200lk_create_sharded (Params::devices)");
+        std::vector<int32_t> devs(params->devices.begin(), params->devices.end());
+        rc = k.create_sharded(&ctx, &d, devs.data(), (int32_t)devs.size());
+        if (rc == B200LK_ERR_UNSUPPORTED)
+            outError("this model / +ASC setting cannot be split over several devices (b200lk_create_sharded refused it)");
+    } else {
+        if (params && params->devices.size() == 1) d.device = params->devices[0];
+        rc = k.create(&ctx, &d);
+    }
     if (rc != B200LK_OK || !ctx) {
         ctx = NULL;
         outError("b200lk_create failed with status " + std::to_string(rc) +

@@ -130,6 +130,9 @@ void b200host_set_next_mixlen(const double *mult, int nclass) { g_mixlen_mult.as
 static double g_mem_fraction = 0.0;  // Params::max_mem_size of the next -mem tree (0: the minimum number of slots)
 void b200host_set_mem_fraction(double f) { g_mem_fraction = f; }
 
+static std::vector<int> g_next_devices;  // Params::devices of the next tree (more than one: pattern shards over these GPUs)
+void b200host_set_next_devices(const int32_t *devices, int n) { g_next_devices.assign(devices, devices + n); }
+
 int b200host_tree_new(void **out, const char *newick, void *aln, void *model, void *rate, int safe, int device,
                       int device_newton) {
     HostTree *h = new HostTree();
@@ -146,6 +149,8 @@ int b200host_tree_new(void **out, const char *newick, void *aln, void *model, vo
             h->params.max_mem_size = g_mem_fraction;
         }
         h->params.device = device;
+        h->params.devices.swap(g_next_devices);
+        g_next_devices.clear();
         h->params.device_newton = device_newton != 0;
         std::vector<double> mult;
         mult.swap(g_mixlen_mult);

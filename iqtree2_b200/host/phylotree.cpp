@@ -53,6 +53,7 @@ const KernelABI &kernelABI() {
         outError("cannot load the CUDA likelihood kernel " + g_abi.path + " (" + dlerror() +
                  "); build it first -- there is no CPU fallback on this path");
     bind(g_abi.create, "create", true);
+    bind(g_abi.create_sharded, "create_sharded", false);
     bind(g_abi.destroy, "destroy", true);
     bind(g_abi.upload_tips, "upload_tips", true);
     bind(g_abi.set_ptn_invar, "set_ptn_invar", true);
