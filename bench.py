@@ -473,6 +473,62 @@ def timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup):
             "clocks": clocks, "collective_us": coll_us}
 
 
+def timed_sharded_run(eng, packed, dad, node, L, model_args, steps, warmup, ndev):
+    """The same two regions for a b200lk_create_sharded context: ONE process drives every device.  A step enqueues the
+    evaluation on all shards and then reads the per-shard sums back (added on the host in device-index order), so
+    every step ends with a blocking read and the wall clock around K steps is the device time of the slowest shard
+    plus the fan-out; no stream or event spans the devices."""
+    import torch
+
+    def sync_all():
+        eng.synchronize()
+        for d in range(ndev):
+            torch.cuda.synchronize(d)
+
+    def step():
+        eng.evaluate_async(packed, dad, node, L)
+        return eng.read_results()
+
+    def step_e2e():
+        eng.set_model(*model_args)
+        eng.evaluate_async(packed, dad, node, L)
+        return eng.read_results()
+
+    for _ in range(max(3, warmup)):
+        step()
+    sync_all()
+    eng.get_profile(reset=True)
+    eng.reset_counters()
+    samplers = [ClockSampler(d) for d in range(ndev)]
+    for sp in samplers:
+        sp.start()
+    eng.set_profiling(True)
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        result = step()
+    sync_all()
+    ms = (time.perf_counter() - t0) * 1e3
+    eng.set_profiling(False)
+    partial_ms, partial_launches = eng.get_profile(reset=True)
+    _, launches = eng.counters()
+    min_bytes = eng.min_traffic()
+    for _ in range(2):
+        step_e2e()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        result = step_e2e()
+    sync_all()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    clocks = [sp.finish() for sp in samplers]
+    worst = min(clocks, key=lambda c: c["sm_mhz"] or 1e9)
+    worst = dict(worst, reasons=sorted(set(r for c in clocks for r in c["reasons"])), per_device_sm_mhz=[c["sm_mhz"] for c in clocks])
+    return {"ms": ms, "e2e_ms": e2e_ms, "partial_ms": partial_ms, "partial_launches": partial_launches,
+            "launches": launches, "min_bytes": min_bytes, "result": result, "local_result": None,
+            "clocks": worst, "collective_us": None}
+
+
 def roofline_of(n, ncm, tr, N_local, r, steps):
     """roofline object of the partial-update kernel(s) from one timed_engine_run on N_local patterns."""
     (hbm, hbm_src), (f64, f64_src) = peaks()
@@ -526,10 +582,12 @@ def measure_alignment(args, D, name, steps, warmup, want_cpu_baseline, cpu_patte
     gen_s = time.perf_counter() - t0
     log("%s: alignment %d x %d simulated in %.1f s" % (name, T, N, gen_s))
     world, rank = D.world, D.rank
+    # --gpus N without torchrun: ONE process, the alignment sharded over N devices behind the C ABI (b200lk_create_sharded)
+    ndev_sp = args.gpus if (world == 1 and args.gpus > 1) else 0
     b, e = MG.shard_range(N, world, rank) if world > 1 else (0, N)
     shard = aln if world == 1 else W.Alignment(aln.nstates, aln.names, np.ascontiguousarray(aln.states[:, b:e]),
                                                np.ascontiguousarray(aln.ptn_freq[b:e]))
-    eng = engine_for(shard, model, rates, props, nslots=T, device=D.local)
+    eng = engine_for(shard, model, rates, props, nslots=T, device=D.local, devices=list(range(ndev_sp)) if ndev_sp else None)
     root = tree.adj[0][0]
     tr = W.traversal(tree, root, 0)
     packed = pack_traversal(tr)
@@ -537,7 +595,10 @@ def measure_alignment(args, D, name, steps, warmup, want_cpu_baseline, cpu_patte
     tipl = W.tip_partial_lh(model)
     model_args = (model.eval, model.evec, model.inv_evec, np.asarray(rates), np.asarray(props), model.mixw, tipl)
     h2d = sum(np.asarray(a).nbytes for a in model_args) + 16 * packed[1] + 16 * packed[3]
-    r = timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup)
+    if ndev_sp:
+        r = timed_sharded_run(eng, packed, dad, node, L, model_args, steps, warmup, ndev_sp)
+    else:
+        r = timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup)
     gpu_plh = eng.fetch_pattern_lh()
     gpu_scale = eng.fetch_scale_num(tr[-1][2])
     eng.close()
@@ -558,14 +619,27 @@ def measure_alignment(args, D, name, steps, warmup, want_cpu_baseline, cpu_patte
     log("%s: GPU timed (%.3f ms per step, e2e %.3f ms)" % (name, r["ms"] / steps, r["e2e_ms"] / steps))
     ncm = ncat * nmix
     roof, kinds = roofline_of(n, ncm, tr, e - b, r, steps)
+    if ndev_sp:  # bytes are summed over the shards, the kernel time is the slowest shard's: per-device bandwidth
+        for obj in (roof, roof.get("hbm", {})):
+            if obj.get("achieved") is not None and obj.get("unit") == "GB/s":
+                obj["achieved"] /= ndev_sp
+                obj["frac"] = obj["achieved"] / obj["peak"]
+                obj["per_device"] = True
+        if roof.get("unit") == "TFLOP/s" and roof.get("achieved") is not None:
+            roof["achieved"] /= ndev_sp
+            roof["frac"] = roof["achieved"] / roof["peak"]
+            roof["per_device"] = True
     updates_per_step = len(tr) * N  # strong scaling: the named shape is the total over all ranks
     line = {
         "metric": METRIC, "value": updates_per_step * steps / (r["ms"] * 1e-3), "unit": UNIT,
-        "n_gpus": world, "steps": steps, "warmup": max(3, warmup), "ms_per_step": r["ms"] / steps,
+        "n_gpus": ndev_sp or world, "steps": steps, "warmup": max(3, warmup), "ms_per_step": r["ms"] / steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic (seeded AliSim-equivalent sampler, every column its own pattern; the same alignment on every rank)",
+        "process_model": ("one process drives %d devices through b200lk_create_sharded; per-shard sums added on the host in "
+                          "device-index order; timed by wall clock around blocking steps" % ndev_sp) if ndev_sp
+        else "one process per GPU (torchrun), NCCL all-reduce of 3 doubles" if world > 1 else "one process, one GPU",
         "config": {"workload": name + ": " + WORKLOADS[name][7], "model": model_name, "ntaxa": T, "patterns": N,
-                   "patterns_per_gpu": e - b, "nstates": n, "ncat": ncat, "nmix": nmix,
+                   "patterns_per_gpu": (e - b) // (ndev_sp or 1), "nstates": n, "ncat": ncat, "nmix": nmix,
                    "node_kinds_TT_TI_II": [kinds[0], kinds[1], kinds[2]],
                    "sharding": "contiguous pattern ranges (whole 32-pattern tiles) of ONE alignment, one per GPU; "
                                "NCCL all-reduce of [lnL, df, ddf] only",
@@ -964,8 +1038,8 @@ def main():
     if D.rank == 0:
         want = args.shapes
         if want == "auto":
-            want = "branch_sweep_cfg2,cfg3,cfg4_full_mem,cfg5" if (args.workload == "cfg2" and D.world == 1 and not args.patterns
-                                                                   and args.mem_save is None) else "none"
+            want = "branch_sweep_cfg2,cfg3,cfg4_full_mem,cfg5" if (args.workload == "cfg2" and D.world == 1 and args.gpus == 1
+                                                                   and not args.patterns and args.mem_save is None) else "none"
         shapes = {}
         for sh in [x for x in want.split(",") if x and x != "none"]:
             if time.perf_counter() - T_START > args.time_budget:

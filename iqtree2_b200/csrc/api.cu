@@ -22,6 +22,7 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
                           int32_t nchildren) {
     if (nnodes == 0) return B200LK_OK;
     if (!nodes || !children || nnodes < 0 || nchildren < 0) return B200LK_ERR_ARG;
+    if (c->ntot == 0) return B200LK_OK;  // no patterns (e.g. a trailing shard of a small alignment): nothing to launch
     if (nnodes > c->nodes_cap || nchildren > c->children_cap) {
         snprintf(c->err, sizeof(c->err), "traversal too long: %d nodes / %d children (cap %d / %d)", nnodes,
                  nchildren, c->nodes_cap, c->children_cap);

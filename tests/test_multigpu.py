@@ -97,3 +97,20 @@ def test_two_rank_pattern_shards_sum_to_the_whole(oracle_lib):
         for a, b in zip(res, want):
             assert abs(a - b) <= 1e-9 * max(1.0, abs(b))
         assert np.allclose(plh, want_plh, rtol=1e-12, atol=0)
+
+
+@pytest.mark.gpu
+def test_nccl_sharded_engine_matches_single_gpu():
+    """ShardedEngine's NCCL path on real devices -- the all-reduce must be ordered after the
+    engine's kernels (the engine runs on the stream NCCL is enqueued on) and equal the single-GPU result."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    import os
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29571", os.path.join(here, "nccl_shard_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
