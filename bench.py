@@ -24,11 +24,23 @@ reduced values must equal the reference's.  The weak-scaling figure (the whole a
 
 `--impl reference` times the CPU implementation only (oracle/_ref when built, else the oracle port).
 """
+import ctypes
 import os
 
-# the reference's OpenMP loops: threads pinned to cores, set before any OpenMP runtime is loaded
+# The reference's OpenMP loops run with their threads pinned to cores (OMP_PROC_BIND=close, OMP_PLACES=cores).  libgomp
+# reads those variables once, when it is loaded, and at that moment also binds the CALLING thread to the first place --
+# which would put the main thread of every torchrun rank, and the NCCL threads that inherit its mask, on core 0.  So: load
+# the OpenMP runtime here, under the binding variables, and give the main thread its full affinity mask back at once.
+# OpenMP worker threads are pinned individually when a team starts; nothing else in the process is.
+_AFFINITY = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
 os.environ.setdefault("OMP_PROC_BIND", "close")
 os.environ.setdefault("OMP_PLACES", "cores")
+try:
+    ctypes.CDLL("libgomp.so.1", mode=ctypes.RTLD_GLOBAL)
+except OSError:
+    pass
+if _AFFINITY is not None:
+    os.sched_setaffinity(0, _AFFINITY)
 
 import argparse  # noqa: E402
 import json  # noqa: E402
@@ -160,7 +172,7 @@ def host_cores():
 
 
 def _host_cores():
-    logical = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    logical = len(_AFFINITY) if _AFFINITY is not None else (os.cpu_count() or 1)
     physical = None
     try:
         import psutil

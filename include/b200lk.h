@@ -127,7 +127,8 @@ const char *b200lk_last_error(const b200lk_ctx *ctx);
 const char *b200lk_version(void);
 
 /* Optional: run on a caller-owned stream (e.g. the stream NCCL is enqueued on).
- * `stream` is a cudaStream_t passed as void*; NULL restores the context's own. */
+ * `stream` is a cudaStream_t passed as void*; NULL restores the context's own -- so the default stream, whose handle
+ * is 0, cannot be selected this way: share a dedicated stream, or pass cudaStreamLegacy / cudaStreamPerThread. */
 int b200lk_set_stream(b200lk_ctx *ctx, void *stream);
 
 /* ---- inputs (one-time / per model change) ----------------------------- */

@@ -48,11 +48,14 @@ class ShardedEngine:
                               device=0 if device is None else device, lib_path=lib_path or LIB_PATH, prefix=prefix)
         self.on_device = prefix == "b200lk_"
         self._res = self.eng.result_tensor() if self.on_device else None
+        self._stream = None
         if self.on_device and world > 1:
-            # the context's own stream is cudaStreamNonBlocking: NCCL (torch's current stream) would not be ordered
-            # after the lnL / derv kernels.  Run the engine on the stream the collective is enqueued on.
+            # The context's own stream is cudaStreamNonBlocking: a collective enqueued on another stream is NOT ordered
+            # after the lnL / derv kernels.  The engine and NCCL share ONE dedicated stream (not torch's default stream:
+            # its handle is 0, which b200lk_set_stream reads as "restore the context's own stream").
             import torch
-            self.eng.set_stream(torch.cuda.current_stream().cuda_stream)
+            self._stream = torch.cuda.Stream(device=self.eng.dims.device)
+            self.eng.set_stream(self._stream.cuda_stream)
 
     def evaluate(self, entries, dad, node, length):
         """Full evaluation on this shard, then the sum over shards.  Returns (lnL, df, ddf) of the whole alignment."""
@@ -60,11 +63,11 @@ class ShardedEngine:
             from .capi import pack_traversal
             self.eng.evaluate_async(pack_traversal(entries), dad, node, length)
             if self.world > 1:
-                self.dist.all_reduce(self._res)  # NCCL, in place on the device result buffer, same stream
-            if self.world > 1:
                 import torch
-                torch.cuda.current_stream().synchronize()
-                return tuple(float(x) for x in self._res.cpu())
+                with torch.cuda.stream(self._stream):
+                    self.dist.all_reduce(self._res)  # NCCL, in place on the device result buffer, same stream
+                    out = self._res.to("cpu", non_blocking=False)
+                return tuple(float(x) for x in out)
             return self.eng.read_results()
         import torch
         part = torch.tensor(self.eng.evaluate(entries, dad, node, length), dtype=torch.float64)
