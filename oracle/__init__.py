@@ -39,6 +39,20 @@ def set_ref_quirks(on: bool) -> None:
 
 # ---- the reference's own kernels (oracle/_ref, built by Makefile.ref where /root/reference exists) ----------
 LK_SSE2, LK_AVX, LK_AVX_FMA = 2, 7, 8   # enum LikelihoodKernel, utils/tools.h:526-528
+LK_CUDA = 10                            # appended by adapter/lk_cuda.patch; only adapter/_build/libiqtree_cuda.so knows it
+# the reference's own PhyloTree with the LK_CUDA selector patch and the adapter TU (adapter/Makefile): same harness,
+# SSE/AVX/FMA kernels AND the four pointers bound to libb200lk.so
+ADAPTER_LIB = os.path.join(os.path.dirname(HERE), "adapter", "_build", "libiqtree_cuda.so")
+
+
+def adapter_available() -> bool:
+    return os.path.exists(ADAPTER_LIB)
+
+
+def build_adapter(verbose: bool = False) -> None:
+    """adapter/_build/libiqtree_cuda.so -- needs /root/reference (this container) and the built libb200lk.so."""
+    out = None if verbose else subprocess.DEVNULL
+    subprocess.check_call(["make", "-s", "-C", os.path.join(os.path.dirname(HERE), "adapter"), "-j8"], stdout=out)
 
 
 def ref_available() -> bool:
@@ -51,14 +65,14 @@ class RefRun:
 
     def __init__(self, tree, aln, model, rates, props, *, kernel=LK_AVX_FMA, safe=False, threads=1, p_invar=0.0,
                  unobserved=None, fused=False, site_models=None, nonrev=None, mixlen=None, asc_holder=False,
-                 robust=None):
+                 robust=None, lib_path=None):
         import ctypes as C
         import numpy as np
         from iqtree2_b200 import workload as W
-        if not ref_available():
+        if lib_path is None and not ref_available():
             raise RuntimeError("oracle/_ref/libiqtree_ref.so is not built (needs /root/reference)")
         self.C, self.np = C, np
-        self.lib = C.CDLL(REF_LIB)
+        self.lib = C.CDLL(lib_path or REF_LIB)
 
         class Problem(C.Structure):
             _fields_ = [(k, C.c_int32) for k in ("ntaxa", "nstates", "ncat", "nmix", "n_state_codes", "kernel",
@@ -127,6 +141,19 @@ class RefRun:
     def branch_length(self, leaves, from_taxon=0):
         arr = self.np.ascontiguousarray(sorted(leaves), dtype=self.np.int32)
         return self.lib.ref_branch_length(self.h, self.C.c_void_p(arr.ctypes.data), len(arr), from_taxon)
+
+    def nni(self, leaves, from_taxon=0, nni5=False):
+        """getBestNNIForBran on the internal branch behind `leaves`: -> (winner, [lnL NNI 1, lnL NNI 2], [central
+        lengths], lnL before, lnL after restoring)."""
+        np, C = self.np, self.C
+        arr = np.ascontiguousarray(sorted(leaves), dtype=np.int32)
+        ll, ln = np.zeros(2), np.zeros(2)
+        before, after = C.c_double(), C.c_double()
+        w = self.lib.ref_nni(self.h, C.c_void_p(arr.ctypes.data), len(arr), from_taxon, int(nni5), C.c_void_p(ll.ctypes.data),
+                             C.c_void_p(ln.ctypes.data), C.byref(before), C.byref(after))
+        if w < 0:
+            raise RuntimeError("ref_nni failed (%d)" % w)
+        return w, ll, ln, before.value, after.value
 
     def lnl_at_leaf(self, taxon):
         return self.lib.ref_lnl_at_leaf(self.h, taxon)

@@ -671,6 +671,40 @@ double ref_branch_length(void *hv, const int32_t *leaves, int nleaves, int from_
     return nb ? nb->length : -2.0;
 }
 
+// PhyloTree::getBestNNIForBran (tree/phylotree.cpp:4058-4288), the dominant caller of a tree search (IQTree::evaluateNNIs):
+// on the internal branch whose far side (seen from leaf `from_taxon`) carries exactly `leaves`, both NNI topologies are
+// scored -- nni_partial_lh takes the place of the two central directions (:4119-4128), optimizeOneBranch runs on the
+// central branch (and with nni5 on the four around it), computeLikelihoodFromBuffer gives the score -- and the tree is
+// restored.  Out: newloglh[2], the re-optimised central length of each, and (return value) the index of the better one.
+int ref_nni(void *hv, const int32_t *leaves, int nleaves, int from_taxon, int nni5, double *newloglh, double *newlen,
+            double *lnl_before, double *lnl_after) {
+    RefHandle *h = (RefHandle *)hv;
+    PhyloTree *tree = h->tree;
+    std::vector<int> want(leaves, leaves + nleaves);
+    PhyloNode *start = find_leaf(tree, from_taxon);
+    if (!start) return -1;
+    PhyloNeighbor *nb = find_branch(start, NULL, want);
+    if (!nb) return -2;
+    PhyloNode *node1 = owner_of(tree, nb), *node2 = (PhyloNode *)nb->node;
+    if (!node1 || node1->isLeaf() || node2->isLeaf()) return -3;
+    tree->params->nni5 = nni5 != 0;
+    tree->params->nni5_num_eval = 1;
+    tree->clearAllPartialLH();
+    tree->curScore = tree->computeLikelihood();
+    if (lnl_before) *lnl_before = tree->curScore;
+    NNIMove moves[2];
+    moves[0].ptnlh = moves[1].ptnlh = NULL;
+    moves[0].node1 = NULL;
+    tree->getBestNNIForBran(node1, node2, moves);
+    for (int k = 0; k < 2; k++) {
+        newloglh[k] = moves[k].newloglh;
+        newlen[k] = moves[k].newLen[0].empty() ? -1.0 : moves[k].newLen[0][0];
+    }
+    // the tree (topology, lengths, validity flags, slot ownership) must be as before: same likelihood without clearing
+    if (lnl_after) *lnl_after = tree->computeLikelihood();
+    return moves[0].newloglh >= moves[1].newloglh ? 0 : 1;
+}
+
 void ref_destroy(void *hv) {
     RefHandle *h = (RefHandle *)hv;
     // the tree owns its buffers; model/rate/factory are ours
