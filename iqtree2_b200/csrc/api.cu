@@ -357,6 +357,12 @@ extern "C" int b200lk_evaluate_async(b200lk_ctx *c, const b200lk_node *nodes, in
         CUDA_TRY(c, cudaMemsetAsync(c->d_result, 0, sizeof(double) * 3, c->stream));
         return B200LK_OK;
     }
+    if (want_lnl && want_derv && can_fuse_tail(c)) {  // one launch for lnL + theta + df/ddf (branch.cu)
+        rc = launch_eval_tail(c, dad, node, length);
+        if (rc) return rc;
+        c->theta_computed = true;
+        return B200LK_OK;
+    }
     if (want_lnl) {
         rc = launch_branch_lnl(c, dad, node, length);
         if (rc) return rc;

@@ -1341,6 +1341,164 @@ int launch_derv_mixlen_class(b200lk_ctx *c, int cls, double length) {
     return launch_asc_fix(c, 1);
 }
 
+// ---- fused tail of a whole evaluation on the T32 layout ------------------------------------------------------------------
+// b200lk_evaluate* needs, at ONE branch and ONE length, the branch lnL (computeLikelihoodBranch), theta
+// (computeLikelihoodBuffer) and df/ddf (computeLikelihoodDerv).  As separate launches that is val -> lnl -> reduce ->
+// theta -> val -> derv -> reduce: seven launches that read the same two partial vectors three times.  Here one thread
+// owns a pattern, loads both vectors once, writes theta / _pattern_lh / _pattern_lh_cat, and accumulates lnL, df and ddf
+// with exactly the per-pattern arithmetic of lnl_t32, theta_t32_pattern and t32_triple_regs.  The branch coefficient
+// table (val0/1/2, 3 * block <= 48 doubles) is rebuilt per CTA in shared memory with val_kernel's formula, and the CTA
+// that finishes last adds the per-CTA partial sums in the fixed order of final_reduce_kernel (deterministic).
+struct TailArgs {
+    DevModel m;
+    double len;
+    int ncat;
+    unsigned *counter;  // CTAs finished so far; the last one resets it
+    double *result;     // [0] lnL, [1] df, [2] ddf
+};
+
+template <int PAIRS>
+__device__ __forceinline__ void eval_tail_t32(const BranchArgs &a, const TailArgs &ta) {
+    constexpr int B = 2 * PAIRS, NCM = PAIRS / 2;
+    __shared__ double sv[48];
+    __shared__ unsigned s_ticket;
+    if (threadIdx.x < B) {  // val_kernel's formula (:2342-2357)
+        const int idx = threadIdx.x, c = idx >> 2, i = idx & 3, mm = c / a.denom, k = c % ta.ncat;
+        const double prop = ta.m.props[k] * ta.m.mixw[mm];
+        const double cof = ta.m.eval[mm * 4 + i] * ta.m.rates[k];
+        const double v = exp(cof * ta.len) * prop, v1 = cof * v;
+        sv[idx] = v;
+        sv[B + idx] = v1;
+        sv[2 * B + idx] = cof * v1;
+    }
+    __syncthreads();
+    const bool tip_mode = a.pnode == nullptr;
+    double acc[3] = {0.0, 0.0, 0.0};
+    for (int64_t p = (int64_t)blockIdx.x * RED_THREADS + threadIdx.x; p < a.ntot; p += (int64_t)gridDim.x * RED_THREADS) {
+        double d[B], o[B];
+        t32_load<PAIRS>(a.pdad, p, d);
+        if (tip_mode) {
+            const double2 *tp = reinterpret_cast<const double2 *>(a.tip_partial_lh + (size_t)a.dad_states[p] * (4 * a.nmix));
+#pragma unroll
+            for (int c = 0; c < NCM; c++) {
+                const double2 u0 = __ldg(tp + (c / a.denom) * 2), u1 = __ldg(tp + (c / a.denom) * 2 + 1);
+                o[4 * c] = u0.x; o[4 * c + 1] = u0.y; o[4 * c + 2] = u1.x; o[4 * c + 3] = u1.y;
+            }
+        } else {
+            t32_load<PAIRS>(a.pnode, p, o);
+        }
+        int min_scale, sc[NCM];
+        if (a.safe) {
+            min_scale = 0x7fffffff;
+#pragma unroll
+            for (int c = 0; c < NCM; c++) {
+                sc[c] = (a.sdad[p * NCM + c] + (tip_mode ? 0 : a.snode[p * NCM + c])) & 0xff;
+                min_scale = min(min_scale, sc[c]);
+            }
+        } else {
+            min_scale = a.sdad[p] + (tip_mode ? 0 : a.snode[p]);
+        }
+        // ---- branch lnL, as lnl_t32 (w = val0 * node side; the tip table tip_val is val0 * tip_partial_lh) ----
+        double lhb = 0.0;
+#pragma unroll
+        for (int c = 0; c < NCM; c++) {
+            const double w0 = o[4 * c] * sv[4 * c], w1 = o[4 * c + 1] * sv[4 * c + 1], w2 = o[4 * c + 2] * sv[4 * c + 2],
+                         w3 = o[4 * c + 3] * sv[4 * c + 3];
+            const double s0 = fma(w2, d[4 * c + 2], w0 * d[4 * c]);
+            const double s1 = fma(w3, d[4 * c + 3], w1 * d[4 * c + 1]);
+            double lc = s0 + s1;
+            if (a.safe) {
+                if (sc[c] == min_scale + 1) lc *= B200_SCALING_THRESHOLD;
+                else if (sc[c] > min_scale + 1) lc = 0.0;
+            }
+            a.pattern_lh_cat[(size_t)p * NCM + c] = lc;
+            lhb += lc;
+        }
+        lhb = log(fabs(lhb) + a.ptn_invar[p]) + (double)min_scale * B200_LOG_SCALING_THRESHOLD;
+        a.pattern_lh[p] = lhb;
+        const double freq = a.ptn_freq[p];
+        acc[0] = fma(lhb, freq, acc[0]);
+        // ---- theta, as theta_t32_pattern ----
+        double t[B];
+        double2 *th = const_cast<double2 *>(t32_ptr(a.theta, p, PAIRS));
+#pragma unroll
+        for (int j = 0; j < PAIRS; j++) {
+            double t0 = o[2 * j] * d[2 * j], t1 = o[2 * j + 1] * d[2 * j + 1];
+            if (a.safe) {
+                const int s2 = sc[j / 2];
+                if (s2 == min_scale + 1) { t0 *= B200_SCALING_THRESHOLD; t1 *= B200_SCALING_THRESHOLD; }
+                else if (s2 > min_scale + 1) { t0 = 0.0; t1 = 0.0; }
+            }
+            th[j * 32] = make_double2(t0, t1);
+            t[2 * j] = t0;
+            t[2 * j + 1] = t1;
+        }
+        a.buffer_scale_all[p] = (double)min_scale * B200_LOG_SCALING_THRESHOLD;
+        // ---- df, ddf, as derv_t32 (observed patterns only: the caller rules +ASC out) ----
+        double lh, df, ddf;
+        t32_triple_regs<PAIRS>(t, sv, lh, df, ddf);
+        lh = fabs(lh) + a.ptn_invar[p];
+        const double inv = 1.0 / lh, df_frac = df * inv, ddf_frac = ddf * inv;
+        const double tmp1 = df_frac * freq, tmp2 = ddf_frac * freq;
+        acc[1] += tmp1;
+        acc[2] += fma(-tmp1, df_frac, tmp2);
+    }
+    block_reduce_store<3>(acc, a.red_partial, (int)gridDim.x);
+    // the CTA that finishes last adds the partial sums in a fixed order (final_reduce_kernel's)
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_ticket = atomicAdd(ta.counter, 1u);
+    __syncthreads();
+    if (s_ticket != gridDim.x - 1) return;
+    __threadfence();
+    __shared__ double sh[RED_THREADS];
+    for (int k = 0; k < 3; k++) {
+        double v = 0.0;
+        for (int b = threadIdx.x; b < (int)gridDim.x; b += RED_THREADS) v += __ldcg(a.red_partial + (size_t)k * gridDim.x + b);
+        sh[threadIdx.x] = v;
+        __syncthreads();
+        for (int s2 = RED_THREADS / 2; s2 > 0; s2 >>= 1) {
+            if (threadIdx.x < s2) sh[threadIdx.x] += sh[threadIdx.x + s2];
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) ta.result[k] = sh[0];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *ta.counter = 0u;
+}
+
+__global__ void __launch_bounds__(RED_THREADS) eval_tail_kernel(BranchArgs a, TailArgs ta) {
+    T32_DISPATCH(eval_tail_t32, a, ta)
+}
+
+bool can_fuse_tail(const b200lk_ctx *c) {
+    return c->tile == 32 && !c->site && !c->nonrev && !c->batch && c->d.n_unobserved == 0 && c->ntot == c->d.nptn &&
+           c->robust_keep >= 1.0 && !c->robust_median && !c->cur_branch_mixlen && !b200_env().no_fused_tail;
+}
+
+int launch_eval_tail(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length) {
+    if (!c->tail_counter) {
+        CUDA_TRY(c, cudaMalloc(&c->tail_counter, sizeof(unsigned)));
+        CUDA_TRY(c, cudaMemsetAsync(c->tail_counter, 0, sizeof(unsigned), c->stream));
+    }
+    BranchArgs a;
+    fill_args(c, a, dad, node);
+    fill_common(c, a);
+    a.len = length;
+    a.G = 1;
+    TailArgs ta;
+    ta.m = c->m;
+    ta.len = length;
+    ta.ncat = c->d.ncat;
+    ta.counter = c->tail_counter;
+    ta.result = c->d_result;
+    const int grid = grid_for(c, 1, c->ntot);
+    eval_tail_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, ta);
+    CUDA_TRY(c, cudaGetLastError());
+    c->n_launches++;
+    return B200LK_OK;
+}
+
 // ---- b200lk_lnl_from_buffer_noalloc: from-buffer lnL whose scratch lives in a file-scope device array ----------------
 // No counterpart in the reference; added for callers that cannot call cudaMalloc
 // (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch that

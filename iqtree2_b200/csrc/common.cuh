@@ -184,6 +184,7 @@ struct b200lk_ctx {
     double s4_pi[4];
     bool model_set, tips_set, theta_computed;
     int theta_dad_kind;
+    unsigned *tail_counter;  // eval_tail_kernel: CTAs finished (device)
     int64_t n_updates, n_launches;
     // minimum DRAM bytes of the partial-update launches enqueued since the last reset, counted from the node programs
     // actually launched: every vector written once (+ scale bytes), every child vector that a launch has to fetch
@@ -282,6 +283,8 @@ int launch_repair(b200lk_ctx *c);
 int launch_robust(b200lk_ctx *c);  // robust.cu: replaces result[0] by the robust score of the per-pattern lnL
 int launch_newton(b200lk_ctx *c, const b200lk_newton *nr, const b200lk_end *ends);  // ends = {dad, node}: builds theta too
 int launch_rell(b200lk_ctx *c);
+bool can_fuse_tail(const b200lk_ctx *c);  // branch.cu: lnL + theta + df/ddf of one evaluation as ONE launch (T32 layout)
+int launch_eval_tail(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length);
 int noalloc_setup(b200lk_ctx *c);  // branch.cu: device address of the static scratch of b200lk_lnl_from_buffer_noalloc
 int launch_s4_traverse(b200lk_ctx *c, const b200lk_node *nodes, int first, int count, int *prog_used, int *seq_used);
 int launch_partial_multi(b200lk_ctx *c, int node_index);

@@ -216,6 +216,7 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
                    c->d_nodes, c->d_children, c->red_partial, c->d_result};
     for (void *p : dev)
         if (p) cudaFree(p);
+    if (c->tail_counter) cudaFree(c->tail_counter);
     if (c->h_model_stage) cudaFreeHost(c->h_model_stage);
     if (c->model_ev) cudaEventDestroy(c->model_ev);
     if (c->h_nodes_ring) cudaFreeHost(c->h_nodes_ring);

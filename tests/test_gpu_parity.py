@@ -478,3 +478,49 @@ def test_batched_evaluation_repairs_non_finite_lnl_like_the_per_context_path(ora
         if gene == 1:
             assert engines[gene].last_status & WARN_LNL_NONFINITE
             assert engines[gene].fetch_pattern_lh()[5] == 4 * -177.4456782233459932741
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("ncat,nmix,p_invar", [(4, 1, 0.0), (2, 2, 0.0), (3, 1, 0.15), (1, 1, 0.0)])
+def test_fused_evaluation_tail_equals_the_separate_kernels(oracle_lib, safe, ncat, nmix, p_invar):
+    """b200lk_evaluate on the 4-state layout runs lnL + theta + df/ddf as ONE launch (eval_tail_kernel).  Its per-pattern
+    outputs must be bit-identical to the separate lnl / theta kernels', its sums equal to theirs and to the oracle's."""
+    tree, model, rates, props, aln = make_problem(40, 3000, ncat=ncat, nmix=nmix, seed=51, gaps=0.05, mean_len=0.4)
+    g, o = both(aln, model, rates, props, nslots=40, safe_numeric=safe, p_invar=p_invar)
+    internal = next(v for v in range(tree.ntaxa, tree.nnodes) if all(not tree.is_leaf(u) for u in tree.adj[v][:2]))
+    for dad_node, node in ((0, tree.adj[0][0]), (internal, tree.adj[internal][0])):
+        tr = W.traversal(tree, node, dad_node) + ([] if tree.is_leaf(dad_node) else W.traversal(tree, dad_node, node))
+        slot = {(e[0], e[1]): e[2] for e in tr}
+        if tree.is_leaf(dad_node):
+            dad, nd = (LEAF, dad_node), (INTERNAL, slot[(node, dad_node)])
+        else:
+            tr = _two_sided(tree, node, dad_node)
+            slot = {(e[0], e[1]): e[2] for e in tr}
+            dad, nd = (INTERNAL, slot[(dad_node, node)]), (INTERNAL, slot[(node, dad_node)])
+        L = tree.get_length(dad_node, node)
+        fused = g.evaluate(tr, dad, nd, L)
+        f_plh, f_cat = g.fetch_pattern_lh(), g.fetch_pattern_lh_cat()
+        f_theta, f_bs = g.fetch_theta()
+        lnl = g.branch_lnl(dad, nd, L)
+        s_plh, s_cat = g.fetch_pattern_lh(), g.fetch_pattern_lh_cat()
+        g.build_theta(dad, nd)
+        s_theta, s_bs = g.fetch_theta()
+        df, ddf = g.derv(L)
+        assert np.array_equal(f_plh, s_plh) and np.array_equal(f_cat, s_cat)
+        assert np.array_equal(f_theta, s_theta) and np.array_equal(f_bs, s_bs)
+        assert rel(fused, (lnl, df, ddf)) <= 1e-12
+        assert rel(fused, o.evaluate(tr, dad, nd, L)) <= TOL
+        assert g.evaluate(tr, dad, nd, L) == fused  # deterministic last-block reduction
+
+
+def _two_sided(tree, node, dad):
+    """post-order lists of both directions of branch (dad, node) with distinct slots"""
+    a = W.traversal(tree, node, dad)
+    used = {e[2] for e in a}
+    free = iter(s for s in range(tree.ntaxa) if s not in used)
+    remap = {}
+    b = []
+    for (v, u, s, ch) in W.traversal(tree, dad, node):
+        remap[s] = next(free)
+        b.append((v, u, remap[s], [(k, remap[i] if k == INTERNAL else i, l) for k, i, l in ch]))
+    return a + b
