@@ -406,7 +406,7 @@ class Dist:
             self.dist.destroy_process_group()
 
 
-def timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup):
+def timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup, collective="peer"):
     """W warm-up + `steps` device-timed evaluations of `eng` (CUDA events on the launching stream, barrier +
     synchronize on both sides), then the same through the blocking host-facing calls (e2e).  Returns a dict."""
     import torch
@@ -414,16 +414,21 @@ def timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup):
     torch.cuda.set_stream(stream)
     eng.set_stream(stream.cuda_stream)  # one stream for the engine, NCCL and the timing events
     res_t = eng.result_tensor()
+    # the sums over the ranks: exchanged inside the finishing kernel over NVLink peer memory (b200lk_peer_connect), or
+    # with --collective nccl by an ncclAllReduce of the 3 doubles behind it
+    use_nccl = D.dist is not None and collective == "nccl"
+    if D.dist is not None and not use_nccl:
+        eng.connect_peers(D.dist)
 
     def step_device():
         eng.evaluate_async(packed, dad, node, L)
-        if D.dist:
+        if use_nccl:
             D.dist.all_reduce(res_t)
 
     def step_e2e():
         eng.set_model(*model_args)
         eng.evaluate_async(packed, dad, node, L)
-        if D.dist:
+        if use_nccl:
             D.dist.all_reduce(res_t)
         return eng.read_results()
 
@@ -449,7 +454,7 @@ def timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup):
     _, launches = eng.counters()
     min_bytes = eng.min_traffic()
     local_res = None
-    if D.dist:  # this rank's own sums, for the check that the all-reduce really summed finished kernels
+    if use_nccl:  # this rank's own sums, for the check that the all-reduce really summed finished kernels
         eng.evaluate_async(packed, dad, node, L)
         local_res = eng.read_results()
     # ---- end to end: host buffers in, scalars out, every step ----
@@ -475,7 +480,7 @@ def timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup):
         c1.record(stream)
         torch.cuda.synchronize()
         coll_us = c0.elapsed_time(c1) * 1e3 / 200
-        # leave the true (all-reduced) result of one more evaluation in the buffer
+        # leave the true (summed over ranks) result of one more evaluation in the buffer
         result = step_e2e()
     ms, e2e_ms = D.max(ms, e2e_ms)
     torch.cuda.set_stream(torch.cuda.default_stream())
@@ -610,7 +615,7 @@ def measure_alignment(args, D, name, steps, warmup, want_cpu_baseline, cpu_patte
     if ndev_sp:
         r = timed_sharded_run(eng, packed, dad, node, L, model_args, steps, warmup, ndev_sp)
     else:
-        r = timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup)
+        r = timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup, args.collective)
     gpu_plh = eng.fetch_pattern_lh()
     gpu_scale = eng.fetch_scale_num(tr[-1][2])
     eng.close()
@@ -619,8 +624,15 @@ def measure_alignment(args, D, name, steps, warmup, want_cpu_baseline, cpu_patte
         # secondary figure: the WHOLE alignment on every GPU (weak scaling).  Every rank holds the same data, so the
         # all-reduced sums must be world x one rank's own
         engw = engine_for(aln, model, rates, props, nslots=T, device=D.local)
-        rw = timed_engine_run(D, engw, packed, dad, node, L, model_args, steps, warmup)
+        rw = timed_engine_run(D, engw, packed, dad, node, L, model_args, steps, warmup, args.collective)
         engw.close()
+        one = rw["local_result"]
+        if one is None:  # peer exchange: every rank holds the same data, so one rank's own sums are total / world;
+            # checked against an evaluation of the same alignment without peers
+            eng1 = engine_for(aln, model, rates, props, nslots=T, device=D.local)
+            one = eng1.evaluate(tr, dad, node, L)
+            eng1.close()
+            rw["local_result"] = one
         weak = {"value": len(tr) * N * world * steps / (rw["ms"] * 1e-3), "unit": UNIT, "scaling": "weak",
                 "patterns_per_gpu": N, "ms_per_step": rw["ms"] / steps, "kernel_ms_per_step": rw["partial_ms"] / steps,
                 "e2e_value": len(tr) * N * world * steps / (rw["e2e_ms"] * 1e-3),
@@ -664,7 +676,11 @@ def measure_alignment(args, D, name, steps, warmup, want_cpu_baseline, cpu_patte
         "clocks": r["clocks"], "roofline": roof, "lnl_df_ddf": list(r["result"]),
     }
     if world > 1:
-        line["collective"] = {"what": "ncclAllReduce(sum) of 3 doubles on the evaluation's stream", "us": r["collective_us"]}
+        line["collective"] = {
+            "used": "in-kernel exchange over NVLink peer memory (b200lk_peer_connect): the last CTA of the finishing kernel "
+                    "stores the 3 sums into every peer's buffer, waits for the peers' and adds in rank order" if args.collective == "peer"
+            else "ncclAllReduce(sum) of 3 doubles on the evaluation's stream",
+            "nccl_allreduce_3_doubles_us": r["collective_us"]}
         line["weak_scaling"] = weak
     # ---- parity against the reference kernel on the same patterns, and the CPU baseline ----
     if not args.no_cpu:
@@ -1030,6 +1046,8 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=0, help="patterns in the CPU legs (0 = the full workload)")
     ap.add_argument("--cpu-steps", type=int, default=3, help="evaluations timed for cpu_baseline")
     ap.add_argument("--no-cpu", action="store_true", help="skip the parity and cpu_baseline legs")
+    ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: how [lnL, df, ddf] are summed over the ranks (in-kernel peer exchange, or ncclAllReduce)")
     ap.add_argument("--genes", type=int, default=1000, help="cfg5: number of genes")
     ap.add_argument("--parity-genes", type=int, default=8, help="cfg5: genes compared with the reference")
     ap.add_argument("--shapes", default="auto", help="sub-results for the other BASELINE shapes in the same line: "

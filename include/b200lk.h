@@ -315,6 +315,19 @@ int b200lk_evaluate_async(b200lk_ctx *ctx, const b200lk_node *nodes, int32_t nno
                           double length, int want_lnl, int want_derv);
 int b200lk_read_results(b200lk_ctx *ctx, double *lnl, double *df, double *ddf);
 
+/* ---- pattern shards in several PROCESSES: the sums exchanged inside the finishing kernel ------------------------------
+ * One process per GPU (MPI ranks, torchrun), each with a context over its pattern range.  The reference adds the
+ * per-packet lnL / df / ddf of its OpenMP threads with reduction(+) (tree/phylokernelnew.h:2377, 2792, 3273); across
+ * GPUs that is an all-reduce of 3 doubles.  Instead of a collective library call per evaluation, the kernel that
+ * finishes b200lk_evaluate_async stores the rank's sums into every peer's exchange buffer over NVLink (CUDA IPC peer
+ * memory), waits for the peers' and adds them in rank order: every rank's result buffer then holds bit-identical
+ * totals and b200lk_read_results returns them.  Set-up, once: each rank calls b200lk_peer_handle, the 64-byte handles
+ * are gathered by whatever the host has (MPI_Allgather, torch.distributed), each rank calls b200lk_peer_connect.
+ * Every rank must then issue the same sequence of b200lk_evaluate* calls (a rank waits in the kernel for the others,
+ * like in any collective).  Only b200lk_evaluate_async / b200lk_evaluate exchange; the other entry points stay local. */
+int b200lk_peer_handle(b200lk_ctx *ctx, void *handle64 /* 64 bytes out */);
+int b200lk_peer_connect(b200lk_ctx *ctx, int32_t rank, int32_t world, const void *handles /* [world][64] */);
+
 /* ---- device-resident results on demand --------------------------------- */
 /* Unreduced per-shard sums for multi-GPU runs: out[0] = lnL (if requested), out[1] = df,
  * out[2] = ddf are left in a device buffer; this returns its device pointer (3 doubles)

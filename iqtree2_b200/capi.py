@@ -326,6 +326,28 @@ class Engine:
         """Run on a caller-owned stream (an int cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream)."""
         return self._check(self._f("set_stream")(self.ctx, C.c_void_p(cuda_stream_ptr)))
 
+    def peer_handle(self):
+        """64-byte CUDA IPC handle of this rank's exchange buffer (b200lk_peer_handle)."""
+        buf = C.create_string_buffer(64)
+        self._check(self._f("peer_handle")(self.ctx, buf))
+        return buf.raw
+
+    def peer_connect(self, rank, world, handles):
+        """handles: bytes, world x 64, rank-ordered.  From then on evaluate_async / evaluate leave the sums over ALL ranks in
+        every rank's result buffer: the finishing kernel exchanges them over NVLink peer memory (b200lk_peer_connect)."""
+        assert len(handles) == 64 * world
+        self._check(self._f("peer_connect")(self.ctx, C.c_int32(rank), C.c_int32(world), C.c_char_p(handles)))
+
+    def connect_peers(self, dist):
+        """Gather every rank's handle over torch.distributed and connect (one process per GPU)."""
+        import torch
+        rank, world = dist.get_rank(), dist.get_world_size()
+        dev = "cuda:%d" % self.dims.device if dist.get_backend() == "nccl" else "cpu"
+        mine = torch.frombuffer(bytearray(self.peer_handle()), dtype=torch.uint8).to(dev)
+        allh = [torch.empty(64, dtype=torch.uint8, device=dev) for _ in range(world)]
+        dist.all_gather(allh, mine)
+        self.peer_connect(rank, world, b"".join(bytes(t.cpu().numpy().tobytes()) for t in allh))
+
     def set_profiling(self, on=True):
         return self._check(self._f("set_profiling")(self.ctx, int(on)))
 

@@ -353,9 +353,9 @@ extern "C" int b200lk_evaluate_async(b200lk_ctx *c, const b200lk_node *nodes, in
     CUDA_TRY(c, cudaSetDevice(c->device));
     rc = enqueue_update(c, nodes, nnodes, children, nchildren);
     if (rc) return rc;
-    if (c->d.nptn == 0) {
+    if (c->d.nptn == 0) {  // an empty shard still takes part in the exchange, or its peers would wait for ever
         CUDA_TRY(c, cudaMemsetAsync(c->d_result, 0, sizeof(double) * 3, c->stream));
-        return B200LK_OK;
+        return launch_peer_exchange(c, 3);
     }
     if (want_lnl && want_derv && can_fuse_tail(c)) {  // one launch for lnL + theta + df/ddf (branch.cu)
         rc = launch_eval_tail(c, dad, node, length);
@@ -374,7 +374,7 @@ extern "C" int b200lk_evaluate_async(b200lk_ctx *c, const b200lk_node *nodes, in
         rc = launch_derv(c, length);
         if (rc) return rc;
     }
-    return B200LK_OK;
+    return launch_peer_exchange(c, 3);  // pattern shards in other processes (b200lk_peer_connect): sums over all ranks
 }
 
 extern "C" int b200lk_read_results(b200lk_ctx *c, double *lnl, double *df, double *ddf) {
@@ -385,7 +385,20 @@ extern "C" int b200lk_read_results(b200lk_ctx *c, double *lnl, double *df, doubl
     int warn = 0;
     int rc = read_results(c, 0, 3);
     if (rc) return rc;
-    if (lnl) {
+    if (lnl && c->peer_world > 1 && !isfinite(c->h_result[0])) {
+        // the TOTAL is non-finite, on every rank alike: each repairs its own patterns (tree/phylokernelnew.h:3077-3094),
+        // then the repaired sums are exchanged again
+        warn |= B200LK_WARN_LNL_NONFINITE;
+        if (c->d.nptn > 0) {
+            rc = launch_repair(c);
+            if (rc) return rc;
+        }
+        rc = launch_peer_exchange(c, 1);
+        if (rc) return rc;
+        rc = read_results(c, 0, 1);
+        if (rc) return rc;
+        *lnl = c->h_result[0];
+    } else if (lnl) {
         if (!isfinite(c->h_result[0]) && c->d.nptn > 0) {
             rc = finish_lnl(c, lnl, true);
             if (rc < 0) return rc;

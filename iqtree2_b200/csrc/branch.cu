@@ -13,6 +13,7 @@
 #include <algorithm>
 
 #include "common.cuh"
+#include "peer.cuh"
 
 #define RED_THREADS 256
 // element e of the current pattern p under the context's layout (common.cuh)
@@ -1355,6 +1356,7 @@ struct TailArgs {
     int ncat;
     unsigned *counter;  // CTAs finished so far; the last one resets it
     double *result;     // [0] lnL, [1] df, [2] ddf
+    PeerArgs peer;      // pattern shards in other processes: the last CTA exchanges the sums with them (peer.cuh)
 };
 
 template <int PAIRS>
@@ -1464,7 +1466,10 @@ __device__ __forceinline__ void eval_tail_t32(const BranchArgs &a, const TailArg
         if (threadIdx.x == 0) ta.result[k] = sh[0];
         __syncthreads();
     }
-    if (threadIdx.x == 0) *ta.counter = 0u;
+    if (threadIdx.x == 0) {
+        *ta.counter = 0u;
+        peer_exchange(ta.result, 3, ta.peer);
+    }
 }
 
 __global__ void __launch_bounds__(RED_THREADS) eval_tail_kernel(BranchArgs a, TailArgs ta) {
@@ -1492,6 +1497,7 @@ int launch_eval_tail(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double leng
     ta.ncat = c->d.ncat;
     ta.counter = c->tail_counter;
     ta.result = c->d_result;
+    ta.peer = peer_args_next(c);
     const int grid = grid_for(c, 1, c->ntot);
     eval_tail_kernel<<<grid, RED_THREADS, 0, c->stream>>>(a, ta);
     CUDA_TRY(c, cudaGetLastError());

@@ -185,6 +185,14 @@ struct b200lk_ctx {
     bool model_set, tips_set, theta_computed;
     int theta_dad_kind;
     unsigned *tail_counter;  // eval_tail_kernel: CTAs finished (device)
+    // exchange of [lnL, df, ddf] between the pattern shards of several PROCESSES over NVLink peer memory (peer.cu):
+    // every rank's exchange buffer is mapped into every other rank (CUDA IPC); the kernel that finishes an evaluation
+    // stores its sums into all peers' buffers and adds what the peers stored, in rank order
+    double *peer_buf;              // this rank's buffer: vals[2][B200_PEER_MAX][4], then flags[2][B200_PEER_MAX]
+    double **d_peer_bufs;          // device array [world]: every rank's buffer as mapped here
+    void *peer_mapped[64];         // what cudaIpcOpenMemHandle returned (to close)
+    int peer_rank, peer_world;
+    unsigned long long peer_seq;   // evaluations exchanged so far
     int64_t n_updates, n_launches;
     // minimum DRAM bytes of the partial-update launches enqueued since the last reset, counted from the node programs
     // actually launched: every vector written once (+ scale bytes), every child vector that a launch has to fetch
@@ -283,6 +291,14 @@ int launch_repair(b200lk_ctx *c);
 int launch_robust(b200lk_ctx *c);  // robust.cu: replaces result[0] by the robust score of the per-pattern lnL
 int launch_newton(b200lk_ctx *c, const b200lk_newton *nr, const b200lk_end *ends);  // ends = {dad, node}: builds theta too
 int launch_rell(b200lk_ctx *c);
+#define B200_PEER_MAX 64
+struct PeerArgs {            // kernel-side view of the exchange; world <= 1: nothing to exchange
+    double *const *bufs;     // [world]
+    int rank, world;
+    unsigned long long seq;  // sequence number of THIS evaluation (>= 1)
+};
+PeerArgs peer_args_next(b200lk_ctx *c);  // peer.cu: the exchange of the evaluation being enqueued (advances the sequence)
+int launch_peer_exchange(b200lk_ctx *c, int count);  // peer.cu: exchange d_result[0..count) in a kernel of its own
 bool can_fuse_tail(const b200lk_ctx *c);  // branch.cu: lnL + theta + df/ddf of one evaluation as ONE launch (T32 layout)
 int launch_eval_tail(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double length);
 int noalloc_setup(b200lk_ctx *c);  // branch.cu: device address of the static scratch of b200lk_lnl_from_buffer_noalloc

@@ -7,6 +7,8 @@
 
 #include "common.cuh"
 
+void peer_release(b200lk_ctx *c);  // peer.cu
+
 extern "C" const char *b200lk_version(void) { return "b200lk 0.2 (sm_100a)"; }
 
 const B200Env &b200_env() {
@@ -216,6 +218,7 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
                    c->d_nodes, c->d_children, c->red_partial, c->d_result};
     for (void *p : dev)
         if (p) cudaFree(p);
+    peer_release(c);
     if (c->tail_counter) cudaFree(c->tail_counter);
     if (c->h_model_stage) cudaFreeHost(c->h_model_stage);
     if (c->model_ev) cudaEventDestroy(c->model_ev);

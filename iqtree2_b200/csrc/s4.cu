@@ -648,6 +648,8 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         auto kern = safe ? s4_traverse_kernel<NCM, true, true, S4_MINB> : s4_traverse_kernel<NCM, false, true, S4_MINB>;
         if (minb == 8) kern = safe ? s4_traverse_kernel<NCM, true, true, 8> : s4_traverse_kernel<NCM, false, true, 8>;
         if (minb == 12) kern = safe ? s4_traverse_kernel<NCM, true, true, 12> : s4_traverse_kernel<NCM, false, true, 12>;
+        if (minb == 14) kern = safe ? s4_traverse_kernel<NCM, true, true, 14> : s4_traverse_kernel<NCM, false, true, 14>;
+        if (minb == 16) kern = safe ? s4_traverse_kernel<NCM, true, true, 16> : s4_traverse_kernel<NCM, false, true, 16>;
         if (minb != S4_MINB) CUDA_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         kern<<<grid, S4_THREADS, smem, c->stream>>>(P);
     } else if (c->d.safe_numeric) s4_traverse_kernel<NCM, true, false, 8><<<grid, S4_THREADS, smem, c->stream>>>(P);

@@ -32,13 +32,33 @@ def main():
         if got is not None:
             worst = max(worst, max(abs(a - b) for a, b in zip(r, got)))
         got = r
+    # the same sums exchanged inside the finishing kernel over NVLink peer memory (b200lk_peer_connect): no collective call
+    b, e = MG.shard_range(aln.nptn, world, rank)
+    sub = W.Alignment(aln.nstates, aln.names, np.ascontiguousarray(aln.states[:, b:e]), np.ascontiguousarray(aln.ptn_freq[b:e]))
+    pe = engine_for(sub, model, rates, props, nslots=40, device=local)
+    pe.connect_peers(dist)
+    peer_got, peer_worst = None, 0.0
+    for _ in range(20):
+        r = pe.evaluate(*args)
+        if peer_got is not None:
+            peer_worst = max(peer_worst, max(abs(a - c2) for a, c2 in zip(r, peer_got)))
+        peer_got = r
+    # every rank must hold bit-identical totals (rank-ordered sum)
+    mine = torch.tensor(peer_got, dtype=torch.float64, device="cuda")
+    lo, hi = mine.clone(), mine.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    same_everywhere = bool(torch.equal(lo, hi))
     ok = True
     if rank == 0:
         one = engine_for(aln, model, rates, props, nslots=40, device=local)
         want = one.evaluate(*args)
         err = max(abs(a - b) / max(1.0, abs(b)) for a, b in zip(got, want))
         print("nccl sharded: got %r want %r rel %.2e repeat-diff %.2e" % (got, want, err, worst), flush=True)
-        ok = err <= 1e-9 and worst == 0.0
+        perr = max(abs(a - b2) / max(1.0, abs(b2)) for a, b2 in zip(peer_got, want))
+        print("peer exchange: got %r rel %.2e repeat-diff %.2e identical on all ranks: %s" % (peer_got, perr, peer_worst, same_everywhere),
+              flush=True)
+        ok = err <= 1e-9 and worst == 0.0 and perr <= 1e-9 and peer_worst == 0.0 and same_everywhere
     flag = torch.tensor([0 if ok else 1], device="cuda")
     dist.all_reduce(flag)
     dist.destroy_process_group()
