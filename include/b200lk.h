@@ -46,6 +46,13 @@ extern "C" {
  * outError texts at tree/phylokernelnew.h:2573-2578, 3077-3094, 3333-3336 */
 #define B200LK_WARN_LNL_NONFINITE 1  /* "Numerical underflow for lh-branch" */
 #define B200LK_WARN_DERV_NONFINITE 2 /* "Numerical underflow (lh-derivative)" */
+/* informational: df/ddf deliberately differ from what the reference's kernels return for this context.  With an odd
+ * number of states and an even number of categories the reference's dotProductTriple tests the parity of nstates while
+ * it loops over nstates*ncat_mix entries (tree/phylokernelnew.h:2491, 700-724) and counts the last (category, eigen
+ * index) entry of the block twice; this library returns the mathematically right sums.  4- and 20-state data are
+ * unaffected.  Set by b200lk_derv, b200lk_evaluate / b200lk_read_results (when derivatives are read) and
+ * b200lk_optimize_branch. */
+#define B200LK_INFO_DERV_NOT_AS_REFERENCE 4
 
 #define B200LK_CHILD_LEAF 0
 #define B200LK_CHILD_INTERNAL 1

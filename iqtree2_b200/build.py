@@ -10,8 +10,8 @@ LIB = os.path.join(HERE, "libb200lk.so")
 OBJDIR = os.path.join(HERE, "csrc", "build")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 CFLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-          "-Xcompiler", "-fPIC"]
-LFLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC"]
+          "-Xcompiler", "-fPIC,-fopenmp"]  # OpenMP: the per-shard host fan-out of shard.cu
+LFLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC,-fopenmp"]
 
 
 def sources():

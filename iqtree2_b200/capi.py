@@ -19,7 +19,7 @@ LIB_PATH = os.environ.get("B200LK_LIB") or os.path.join(HERE, "libb200lk.so")
 LEAF, INTERNAL = 0, 1
 ROOT, TOWARD_ROOT = 2, 0x100          # non-reversible contexts: the root leaf; child->direction == TOWARD_ROOT
 MODEL_REV, MODEL_SITE, MODEL_NONREV = 0, 1, 2   # b200lk_dims.site_specific
-WARN_LNL_NONFINITE, WARN_DERV_NONFINITE = 1, 2
+WARN_LNL_NONFINITE, WARN_DERV_NONFINITE, INFO_DERV_NOT_AS_REFERENCE = 1, 2, 4
 
 
 class Dims(C.Structure):

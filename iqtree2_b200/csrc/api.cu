@@ -249,7 +249,7 @@ int finish_derv(b200lk_ctx *c, double *df, double *ddf) {
     }
     if (df) *df = a;
     if (ddf) *ddf = b;
-    return warn;
+    return warn | derv_info_bits(c);
 }
 
 extern "C" int b200lk_update_partials(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes,
@@ -340,7 +340,7 @@ extern "C" int b200lk_optimize_branch(b200lk_ctx *c, b200lk_end dad, b200lk_end 
     *optx = c->h_result[4];
     if (d2l) *d2l = c->h_result[5];
     if (nsteps) *nsteps = (int32_t)c->h_result[6];
-    return c->h_result[7] != 0.0 ? B200LK_WARN_DERV_NONFINITE : B200LK_OK;
+    return (c->h_result[7] != 0.0 ? B200LK_WARN_DERV_NONFINITE : B200LK_OK) | derv_info_bits(c);
 }
 
 extern "C" int b200lk_evaluate_async(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes,
@@ -415,6 +415,7 @@ extern "C" int b200lk_read_results(b200lk_ctx *c, double *lnl, double *df, doubl
         }
         if (df) *df = a;
         if (ddf) *ddf = b;
+        warn |= derv_info_bits(c);
     }
     return warn;
 }

@@ -217,6 +217,10 @@ __host__ __device__ __forceinline__ size_t elem_off(int64_t p, int e, int block,
     return (size_t)(p >> 5) * ((size_t)32 * block) + (size_t)(e >> 1) * 64 + (size_t)(p & 31) * 2 + (e & 1);
 }
 
+// B200LK_INFO_DERV_NOT_AS_REFERENCE: odd nstates with an even number of categories (include/b200lk.h)
+static inline int derv_info_bits(const b200lk_ctx *c) {
+    return ((c->d.nstates & 1) && !(c->ncat_mix & 1) && !c->nonrev) ? B200LK_INFO_DERV_NOT_AS_REFERENCE : 0;
+}
 static inline double *slot_partial(const b200lk_ctx *c, int s) { return c->partial + (size_t)s * c->slot_doubles; }
 static inline uint8_t *slot_scale(const b200lk_ctx *c, int s) { return c->scale + (size_t)s * c->slot_scale_bytes; }
 

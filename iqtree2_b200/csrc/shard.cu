@@ -115,6 +115,22 @@ int shard_upload_tips(b200lk_ctx *c, const uint8_t *states, const uint8_t *unobs
         if (rc < 0) return shard_fail(c, i, rc);    \
     }
 
+// The same on one host thread per shard: what a call does on the host before it launches (levels, node programs, the
+// exp(lambda r t) factors of every child -- ~0.2 ms for a cfg2 traversal) would otherwise be paid once per shard in
+// turn.  Contexts are independently thread-safe (own stream, own staging, thread-local launch parameters).
+#define EACH_SHARD_PARALLEL(expr)                                                   \
+    {                                                                               \
+        const int nsh__ = NSHARD(c);                                                \
+        std::vector<int> rcs__(nsh__, 0);                                           \
+        _Pragma("omp parallel for schedule(static, 1) num_threads(nsh__)")          \
+        for (int i = 0; i < nsh__; i++) {                                           \
+            b200lk_ctx *sc = SHARD(c, i);                                           \
+            rcs__[i] = (expr);                                                      \
+        }                                                                           \
+        for (int i = 0; i < nsh__; i++)                                             \
+            if (rcs__[i] < 0) return shard_fail(c, i, rcs__[i]);                    \
+    }
+
 int shard_set_ptn_invar(b200lk_ctx *c, const double *v) {
     if (!v) return B200LK_ERR_ARG;
     EACH_SHARD(b200lk_set_ptn_invar(sc, v + b));
@@ -146,7 +162,7 @@ int shard_set_robust(b200lk_ctx *c, double keep, int32_t median) {
 
 // ---- the four kernel entry points ------------------------------------------------------------------------------------
 int shard_update_partials(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children, int32_t nchildren) {
-    EACH_SHARD(b200lk_update_partials(sc, nodes, nnodes, children, nchildren));  // asynchronous on every shard
+    EACH_SHARD_PARALLEL(b200lk_update_partials(sc, nodes, nnodes, children, nchildren));  // asynchronous on every shard
     c->theta_computed = false;
     return B200LK_OK;
 }
@@ -248,7 +264,7 @@ int shard_lnl_from_buffer(b200lk_ctx *c, double length, double *lnl) {
 
 int shard_evaluate_async(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
                          int32_t nchildren, b200lk_end dad, b200lk_end node, double length, int want_lnl, int want_derv) {
-    EACH_SHARD(b200lk_evaluate_async(sc, nodes, nnodes, children, nchildren, dad, node, length, want_lnl, want_derv));
+    EACH_SHARD_PARALLEL(b200lk_evaluate_async(sc, nodes, nnodes, children, nchildren, dad, node, length, want_lnl, want_derv));
     if (want_derv) c->theta_computed = true;
     return B200LK_OK;
 }

@@ -524,3 +524,20 @@ def _two_sided(tree, node, dad):
         remap[s] = next(free)
         b.append((v, u, remap[s], [(k, remap[i] if k == INTERNAL else i, l) for k, i, l in ch]))
     return a + b
+
+
+def test_status_bit_marks_the_documented_derivative_deviation(oracle_lib):
+    """INTEGRATION.md 'Deviations': with odd nstates and an even number of categories the reference counts the last block
+    entry twice in df/ddf; the library returns the true sums and says so with B200LK_INFO_DERV_NOT_AS_REFERENCE."""
+    from iqtree2_b200.capi import INFO_DERV_NOT_AS_REFERENCE
+    for nstates, ncat, expect in ((5, 2, True), (5, 3, False), (4, 4, False), (20, 4, False)):
+        tree, model, rates, props, aln = make_problem(6, 60, nstates=nstates, ncat=ncat, seed=3)
+        g = engine_for(aln, model, rates, props, nslots=6)
+        c = tree.adj[0][0]
+        tr = W.traversal(tree, c, 0)
+        g.evaluate(tr, (LEAF, 0), (INTERNAL, tr[-1][2]), 0.1)
+        assert bool(g.last_status & INFO_DERV_NOT_AS_REFERENCE) == expect
+        g.derv(0.2)
+        assert bool(g.last_status & INFO_DERV_NOT_AS_REFERENCE) == expect
+        g.branch_lnl((LEAF, 0), (INTERNAL, tr[-1][2]), 0.1)
+        assert g.last_status == 0
