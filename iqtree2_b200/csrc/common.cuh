@@ -92,6 +92,7 @@ struct B200Env {
     int dense_pipe, dense_occ;    // B200LK_DENSE_PIPE (0 direct, 1 cp.async, 2 register prefetch), B200LK_DENSE_OCC (3 / 4)
     bool site_dmma;               // B200LK_SITE_DMMA=0 keeps the shuffle kernel for 20-state site models
     bool no_fused_tail;           // B200LK_NO_FUSED_TAIL=1: separate lnl / theta / derv launches in b200lk_evaluate*
+    bool s4_tt;                   // B200LK_S4_TT=0: tip-tip nodes of the 4-state traversal computed, not looked up
 };
 const B200Env &b200_env();
 
@@ -150,6 +151,7 @@ struct b200lk_ctx {
     int nboot;
     double *tt_tables;  // 20-state path: per tip-tip node, the partial vector of every (left state, right state) pair
     size_t tt_cap;      // doubles
+    size_t s4_tt_used;  // 4-state path: doubles of tt_tables handed to the tip-tip nodes of the traversal being enqueued
     unsigned long long *pmax;  // mixture launches of dense.cu: per (node of the level, pattern) max|x| bits
     size_t pmax_bytes;
     bool site;  // dims.site_specific: per-pattern eigen-systems (site.cu); no P-factor tables, pattern-major layout

@@ -34,6 +34,8 @@ const B200Env &b200_env() {
         e.site_dmma = !(v && *v == '0');
         v = getenv("B200LK_NO_FUSED_TAIL");
         e.no_fused_tail = v && *v == '1';
+        v = getenv("B200LK_S4_TT");
+        e.s4_tt = !(v && *v == '0');
         return e;
     }();
     return env;
@@ -117,7 +119,7 @@ static int alloc_all(b200lk_ctx *c) {
     // tip-state row sequence of the pattern-stationary traversal (s4.cu: launch_segment): per traversal list at most
     // 3 entries per node (two leaf children and one pad row) + one chunk of rows read past the end by the last refill,
     // whatever the number of launches the list is cut into
-    c->prog_stride = sizeof(int32_t) * (3 * (size_t)c->nodes_cap + 2 * 256);
+    c->prog_stride = sizeof(int32_t) * (7 * (size_t)c->nodes_cap + 2 * 256 + 64);  // + 4 per tip-tip table descriptor
     CUDA_TRY(c, cudaMallocHost(&c->h_prog_ring, c->prog_stride * B200_STAGE_RING));
     memset(c->h_prog_ring, 0, c->prog_stride * B200_STAGE_RING);
     CUDA_TRY(c, cudaMalloc(&c->d_prog, c->prog_stride));

@@ -40,7 +40,7 @@
 template <int NCM>
 struct PNode {
     int32_t out_slot;
-    int32_t info;        // lk | rk << 2 | (out_stack + 1) << 4 | (refill + 1) << 12
+    int32_t info;        // lk | rk << 2 | (out_stack + 1) << 4 | tiptip_table << 12 | (refill + 1) << 13
     int32_t lid, rid;    // SRC_LEAF: row in the staged chunk; SRC_STACK: entry; SRC_GLOBAL: slot
     int32_t ltab, rtab;  // SRC_LEAF: offset (doubles) of the child's leaf lookup table in `tables`
     int32_t lexp_off, rexp_off;  // batched launches: offset (doubles) of the child's expv[c][i] in the context's tables
@@ -56,12 +56,13 @@ struct S4Model {        // per category: eigenvectors of its mixture class
 struct TravArgs {
     const int32_t *leaf_seq;  // taxon of every staged tip-state row, in order of use, chunk-padded
     const double *tables, *ptn_invar;
+    const double *tt;  // state-pair tables of the tip-tip nodes (s4_tt_tables_kernel): [node][sa * codes + sb][block]
     const uint8_t *states;
     double *partial;
     uint8_t *scale;
     size_t slot_doubles, slot_scale_bytes;
     int64_t ntot, ntot_pad;
-    int nnodes, depth, chunk, denom;
+    int nnodes, depth, chunk, denom, codes;
 };
 
 #define S4_PARAM_BYTES 32000
@@ -208,7 +209,8 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
     for (int i = 0; i < a.nnodes; i++) {
         const PNode<NCM> &nd = P.nodes[i];  // constant bank, uniform index
         const int info = nd.info;
-        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 12) - 1;
+        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 13) - 1;
+        const bool tt = (info >> 12) & 1;
         if (refill >= 0) {
             // stage the next chunk of tip-state rows of this CTA's pattern tile: all loads in flight at once
             __syncthreads();
@@ -222,9 +224,22 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
             }
             __syncthreads();
         }
+        unsigned sc = 0;
+        if (tt) {
+            // tip-tip node: its vector depends on the two tip states only, and was computed for every state pair by
+            // s4_tt_tables_kernel with this kernel's own arithmetic.  One row load instead of two, no FP64 work, never
+            // rescaled (tree/phylokernelnew.h:1632-1746)
+            const int sa = st_buf[nd.lid * S4_THREADS + tid], sb = st_buf[nd.rid * S4_THREADS + tid];
+            const double2 *row = reinterpret_cast<const double2 *>(a.tt + (size_t)nd.ltab + (size_t)(sa * a.codes + sb) * BLOCK);
+#pragma unroll
+            for (int j = 0; j < PAIRS; j++) {
+                const double2 u = __ldg(row + j);
+                prev[2 * j] = u.x;
+                prev[2 * j + 1] = u.y;
+            }
+        } else {
         // both children's operands are requested before either is used: one memory latency per node
         double l[BLOCK], r[BLOCK];
-        unsigned sc = 0;
         child_load<NCM, SAFE>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
         child_load<NCM, SAFE>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
         if (lk != SRC_LEAF) child_apply<NCM, false, SYM>(P.mdl, nd.lexp, l, Ur);
@@ -277,6 +292,7 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
             }
             sc &= 0xff;  // UBYTE arithmetic of the reference
         }
+        }  // !tt
         prev_sc = sc;
         if (valid) {
             double2 *g = reinterpret_cast<double2 *>(a.partial + (size_t)nd.out_slot * a.slot_doubles + poff);
@@ -295,6 +311,40 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
             for (int j = 0; j < PAIRS; j++)
                 stk[(out_stack * PAIRS + j) * S4_THREADS + tid] = make_double2(prev[2 * j], prev[2 * j + 1]);
             stk_sc[out_stack * S4_THREADS + tid] = sc;
+        }
+    }
+}
+
+// State-pair tables of tip-tip nodes: tt[node][sa * codes + sb][c * 4 + k] = the partial vector s4_traverse_kernel computes
+// for a pattern whose two tips carry states (sa, sb) -- the same operations in the same order (product of the two leaf
+// table rows, SYM: times pi, then the back-transformation on the reference's reduction tree), so using the table changes
+// no bit.  One thread per (node, state pair, category).
+struct S4TTNode { int32_t ltab, rtab, out_off, pad; };  // leaf-table offsets of the two children (doubles into tables), table offset
+template <int NCM, bool SYM>
+__global__ void s4_tt_tables_kernel(const S4TTNode *__restrict__ nodes, const double *__restrict__ tables, double *__restrict__ tt,
+                                    DevModel m, int denom, int codes, double pi0, double pi1, double pi2, double pi3) {
+    constexpr int BLOCK = NCM * 4;
+    const S4TTNode nd = nodes[blockIdx.y];
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= codes * codes * NCM) return;
+    const int c = idx % NCM, pair = idx / NCM, sa = pair / codes, sb = pair - sa * codes;
+    const double *la = tables + nd.ltab + (size_t)sa * BLOCK + c * 4, *lb = tables + nd.rtab + (size_t)sb * BLOCK + c * 4;
+    const double pir[4] = {pi0, pi1, pi2, pi3};
+    double tmp[4];
+#pragma unroll
+    for (int x = 0; x < 4; x++) {
+        tmp[x] = __dmul_rn(la[x], lb[x]);
+        if (SYM) tmp[x] = __dmul_rn(tmp[x], pir[x]);
+    }
+    const double *U = m.evec + (size_t)(c / denom) * 16, *M = m.inv_evec + (size_t)(c / denom) * 16;
+    double *out = tt + nd.out_off + (size_t)pair * BLOCK + c * 4;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        if (SYM) {
+            const double ut[4] = {U[k], U[4 + k], U[8 + k], U[12 + k]};
+            out[k] = s4_tree(ut, tmp);
+        } else {
+            out[k] = s4_tree(M + 4 * k, tmp);
         }
     }
 }
@@ -370,7 +420,7 @@ __global__ void __launch_bounds__(S4_THREADS, 2) s4_traverse_batch_kernel(const 
     for (int i = 0; i < a.nnodes; i++) {
         const PNode<NCM> &nd = P.nodes[i];
         const int info = nd.info;
-        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 12) - 1;
+        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 13) - 1;
         if (refill >= 0) {
             __syncthreads();
             constexpr int VPR = S4_THREADS / 16;
@@ -538,11 +588,17 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     // and the rows behind the last one used are the next segment's, or left-overs of an earlier call -- valid taxon ids
     // either way (both copies of the buffer start zeroed and only ever receive taxon ids), loaded and never looked at.
     // `prog_stride` holds children_cap + nodes_cap entries + one chunk of slack, which bounds every traversal list.
-    if ((size_t)*seq_used + 3 * (size_t)count + chunk > c->prog_stride / sizeof(int32_t)) {
+    if ((size_t)*seq_used + 7 * (size_t)count + chunk + 8 > c->prog_stride / sizeof(int32_t)) {
         snprintf(c->err, sizeof(c->err), "tip-state staging sequence overflow: %d + %d entries (capacity %zu)", *seq_used,
-                 3 * count + chunk, c->prog_stride / sizeof(int32_t));
+                 7 * count + chunk + 8, c->prog_stride / sizeof(int32_t));
         return B200LK_ERR_NOMEM;
     }
+    // tip-tip nodes answered from a per-node state-pair table (s4_tt_tables_kernel): worth it when there are clearly
+    // more patterns than state pairs
+    const int codes = c->d.n_state_codes;
+    const bool use_tt = !c->batch && b200_env().s4_tt && (int64_t)codes * codes * 4 <= c->ntot;
+    const size_t tt_doubles = (size_t)codes * codes * NCM * 4;
+    std::vector<S4TTNode> tt_nodes;
     for (int i = 0; i < count; i++) {
         PNode<NCM> &f = P.nodes[i];
         memset(&f, 0, sizeof(f));
@@ -594,13 +650,48 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
             entry_of[i] = out_stack;
             depth_used = std::max(depth_used, out_stack + 1);
         }
-        f.info = kind[0] | kind[1] << 2 | (out_stack + 1) << 4 | (refill + 1) << 12;
+        int tt = 0;
+        if (use_tt && kind[0] == SRC_LEAF && kind[1] == SRC_LEAF && c->s4_tt_used + tt_doubles <= (size_t)INT32_MAX) {
+            S4TTNode tn = {tab[0], tab[1], (int32_t)c->s4_tt_used, 0};
+            tt_nodes.push_back(tn);
+            f.ltab = (int32_t)c->s4_tt_used;
+            c->s4_tt_used += tt_doubles;
+            tt = 1;
+        }
+        f.info = kind[0] | kind[1] << 2 | (out_stack + 1) << 4 | tt << 12 | (refill + 1) << 13;
         producer[nl[i].out_slot] = i;
     }
     int32_t *d_seq = reinterpret_cast<int32_t *>(c->d_prog) + *seq_used;
-    if (nseq)
-        CUDA_TRY(c, cudaMemcpyAsync(d_seq, leaf_seq, sizeof(int32_t) * nseq, cudaMemcpyHostToDevice, c->stream));
-    *seq_used += nseq;
+    // the descriptors of the tip-tip tables ride behind the row sequence in the same staging copy (16-byte aligned)
+    const int tt_at = (nseq + 3) & ~3, ntt = (int)tt_nodes.size();
+    if (ntt) {
+        for (int k = nseq; k < tt_at; k++) leaf_seq[k] = 0;
+        memcpy(leaf_seq + tt_at, tt_nodes.data(), sizeof(S4TTNode) * ntt);
+    }
+    const int staged = ntt ? tt_at + 4 * ntt : nseq;
+    if (staged)
+        CUDA_TRY(c, cudaMemcpyAsync(d_seq, leaf_seq, sizeof(int32_t) * staged, cudaMemcpyHostToDevice, c->stream));
+    *seq_used += (staged + 3) & ~3;
+    if (ntt) {
+        if (c->s4_tt_used > c->tt_cap) {  // grows only: a larger traversal than any before (cudaFree waits for the device)
+            const size_t want = std::max<size_t>(c->s4_tt_used, 2 * tt_doubles * (size_t)(c->d.ntaxa / 2 + 1));
+            if (c->tt_tables) CUDA_TRY(c, cudaFree(c->tt_tables));
+            c->tt_tables = nullptr;
+            c->tt_cap = 0;
+            CUDA_TRY(c, cudaMalloc(&c->tt_tables, sizeof(double) * want));
+            c->tt_cap = want;
+        }
+        const S4TTNode *d_tt = reinterpret_cast<const S4TTNode *>(d_seq + tt_at);
+        const dim3 g((codes * codes * NCM + 127) / 128, ntt);
+        const int denom2 = c->d.fused_mix_rate ? 1 : c->d.ncat;
+        if (c->s4_sym)
+            s4_tt_tables_kernel<NCM, true><<<g, 128, 0, c->stream>>>(d_tt, c->tables, c->tt_tables, c->m, denom2, codes, c->s4_pi[0],
+                                                                   c->s4_pi[1], c->s4_pi[2], c->s4_pi[3]);
+        else
+            s4_tt_tables_kernel<NCM, false><<<g, 128, 0, c->stream>>>(d_tt, c->tables, c->tt_tables, c->m, denom2, codes, 0, 0, 0, 0);
+        CUDA_TRY(c, cudaGetLastError());
+        c->n_launches++;
+    }
     TravArgs &a = P.a;
     a.leaf_seq = d_seq;
     a.tables = c->tables;
@@ -616,6 +707,8 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     a.depth = depth_used;
     a.chunk = chunk;
     a.denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
+    a.tt = c->tt_tables;
+    a.codes = codes;
     fill_model<NCM>(c, P.mdl);
     const size_t smem = (size_t)depth_used * S4_THREADS * (2 * NCM * sizeof(double2) + sizeof(unsigned)) + S4_STATE_BYTES;
     const unsigned grid = (unsigned)(((c->batch ? c->batch->max_ntot : c->ntot) + S4_THREADS - 1) / S4_THREADS);

@@ -541,3 +541,22 @@ def test_status_bit_marks_the_documented_derivative_deviation(oracle_lib):
         assert bool(g.last_status & INFO_DERV_NOT_AS_REFERENCE) == expect
         g.branch_lnl((LEAF, 0), (INTERNAL, tr[-1][2]), 0.1)
         assert g.last_status == 0
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("ncat,nmix", [(4, 1), (2, 2)])  # (2, 2): two model classes -> the general (non-SYM) kernel
+def test_tip_tip_state_pair_tables_change_no_bit(oracle_lib, safe, ncat, nmix):
+    """4-state traversal: with clearly more patterns than state pairs a tip-tip node is looked up in a per-node state-pair
+    table (s4_tt_tables_kernel).  Patterns are independent, so the first 1000 patterns evaluated inside a 3000-pattern
+    context (tables on) and alone (tables off: 1000 < 4 * 19^2) must give bit-identical vectors and scale counts."""
+    tree, model, rates, props, aln = make_problem(30, 3000, ncat=ncat, nmix=nmix, seed=61, gaps=0.08, compress=False)
+    sub = W.Alignment(aln.nstates, aln.names, np.ascontiguousarray(aln.states[:, :1000]), np.ascontiguousarray(aln.ptn_freq[:1000]))
+    big, o = both(aln, model, rates, props, nslots=30, safe_numeric=safe)
+    small = engine_for(sub, model, rates, props, nslots=30, safe_numeric=safe)
+    rb, rs = full_eval(big, tree, 0), full_eval(small, tree, 0)
+    assert sum(1 for e in rb["traversal"] if all(ch[0] == LEAF for ch in e[3])) >= 5  # there are tip-tip nodes
+    for (_, _, s, _) in rb["traversal"]:
+        assert np.array_equal(big.fetch_partial(s)[:1000], small.fetch_partial(s))
+        assert np.array_equal(big.fetch_scale_num(s)[:1000], small.fetch_scale_num(s))
+    assert np.array_equal(rb["pattern_lh"][:1000], rs["pattern_lh"])
+    assert_parity(rb, full_eval(o, tree, 0), TOL)
