@@ -113,6 +113,7 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
                                         c->stream));
         int prog_used = 0, seq_used = 0;
         c->s4_tt_used = 0;
+        c->s4_ttdesc_used = 0;
         for (int i = 0; i < nnodes;) {
             if (nodes[i].nchild > 2) {
                 rc = launch_partial_multi(c, i);

@@ -151,6 +151,7 @@ struct b200lk_ctx {
     int nboot;
     double *tt_tables;  // 20-state path: per tip-tip node, the partial vector of every (left state, right state) pair
     size_t tt_cap;      // doubles
+    size_t s4_ttdesc_used;  // 4-state path: tip-tip table descriptors staged for the traversal being enqueued
     size_t s4_tt_used;  // 4-state path: doubles of tt_tables handed to the tip-tip nodes of the traversal being enqueued
     unsigned long long *pmax;  // mixture launches of dense.cu: per (node of the level, pattern) max|x| bits
     size_t pmax_bytes;

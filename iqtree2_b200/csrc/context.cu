@@ -119,7 +119,8 @@ static int alloc_all(b200lk_ctx *c) {
     // tip-state row sequence of the pattern-stationary traversal (s4.cu: launch_segment): per traversal list at most
     // 3 entries per node (two leaf children and one pad row) + one chunk of rows read past the end by the last refill,
     // whatever the number of launches the list is cut into
-    c->prog_stride = sizeof(int32_t) * (7 * (size_t)c->nodes_cap + 2 * 256 + 64);  // + 4 per tip-tip table descriptor
+    // rows region (taxon ids only) + 4 ints per node for the descriptors of the tip-tip tables, out of the refills' reach
+    c->prog_stride = sizeof(int32_t) * ((3 * (size_t)c->nodes_cap + 512) + 4 * (size_t)c->nodes_cap);
     CUDA_TRY(c, cudaMallocHost(&c->h_prog_ring, c->prog_stride * B200_STAGE_RING));
     memset(c->h_prog_ring, 0, c->prog_stride * B200_STAGE_RING);
     CUDA_TRY(c, cudaMalloc(&c->d_prog, c->prog_stride));

@@ -588,9 +588,12 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     // and the rows behind the last one used are the next segment's, or left-overs of an earlier call -- valid taxon ids
     // either way (both copies of the buffer start zeroed and only ever receive taxon ids), loaded and never looked at.
     // `prog_stride` holds children_cap + nodes_cap entries + one chunk of slack, which bounds every traversal list.
-    if ((size_t)*seq_used + 7 * (size_t)count + chunk + 8 > c->prog_stride / sizeof(int32_t)) {
+    // The staging buffer has two regions: [0, rows_cap) holds ONLY taxon ids (so whatever a refill reads is valid), and
+    // [rows_cap, ...) the descriptors of the tip-tip tables, 4 ints per node, which no refill can reach.
+    const size_t rows_cap = 3 * (size_t)c->nodes_cap + 512;
+    if ((size_t)*seq_used + 3 * (size_t)count + chunk > rows_cap || c->s4_ttdesc_used + (size_t)count > (size_t)c->nodes_cap) {
         snprintf(c->err, sizeof(c->err), "tip-state staging sequence overflow: %d + %d entries (capacity %zu)", *seq_used,
-                 7 * count + chunk + 8, c->prog_stride / sizeof(int32_t));
+                 3 * count + chunk, rows_cap);
         return B200LK_ERR_NOMEM;
     }
     // tip-tip nodes answered from a per-node state-pair table (s4_tt_tables_kernel): worth it when there are clearly
@@ -662,16 +665,19 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         producer[nl[i].out_slot] = i;
     }
     int32_t *d_seq = reinterpret_cast<int32_t *>(c->d_prog) + *seq_used;
-    // the descriptors of the tip-tip tables ride behind the row sequence in the same staging copy (16-byte aligned)
-    const int tt_at = (nseq + 3) & ~3, ntt = (int)tt_nodes.size();
+    if (nseq)
+        CUDA_TRY(c, cudaMemcpyAsync(d_seq, leaf_seq, sizeof(int32_t) * nseq, cudaMemcpyHostToDevice, c->stream));
+    *seq_used += nseq;
+    // the descriptors of the tip-tip tables: their own region of the staging buffer, their own copy
+    const int ntt = (int)tt_nodes.size();
+    const size_t desc_at = rows_cap + 4 * c->s4_ttdesc_used;  // ints from the start of the buffer (16-byte aligned)
     if (ntt) {
-        for (int k = nseq; k < tt_at; k++) leaf_seq[k] = 0;
-        memcpy(leaf_seq + tt_at, tt_nodes.data(), sizeof(S4TTNode) * ntt);
+        int32_t *h_desc = reinterpret_cast<int32_t *>(c->h_prog) + desc_at;
+        memcpy(h_desc, tt_nodes.data(), sizeof(S4TTNode) * ntt);
+        CUDA_TRY(c, cudaMemcpyAsync(reinterpret_cast<int32_t *>(c->d_prog) + desc_at, h_desc, sizeof(S4TTNode) * ntt,
+                                    cudaMemcpyHostToDevice, c->stream));
+        c->s4_ttdesc_used += ntt;
     }
-    const int staged = ntt ? tt_at + 4 * ntt : nseq;
-    if (staged)
-        CUDA_TRY(c, cudaMemcpyAsync(d_seq, leaf_seq, sizeof(int32_t) * staged, cudaMemcpyHostToDevice, c->stream));
-    *seq_used += (staged + 3) & ~3;
     if (ntt) {
         if (c->s4_tt_used > c->tt_cap) {  // grows only: a larger traversal than any before (cudaFree waits for the device)
             const size_t want = std::max<size_t>(c->s4_tt_used, 2 * tt_doubles * (size_t)(c->d.ntaxa / 2 + 1));
@@ -681,7 +687,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
             CUDA_TRY(c, cudaMalloc(&c->tt_tables, sizeof(double) * want));
             c->tt_cap = want;
         }
-        const S4TTNode *d_tt = reinterpret_cast<const S4TTNode *>(d_seq + tt_at);
+        const S4TTNode *d_tt = reinterpret_cast<const S4TTNode *>(reinterpret_cast<int32_t *>(c->d_prog) + desc_at);
         const dim3 g((codes * codes * NCM + 127) / 128, ntt);
         const int denom2 = c->d.fused_mix_rate ? 1 : c->d.ncat;
         if (c->s4_sym)
