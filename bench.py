@@ -546,6 +546,25 @@ def timed_sharded_run(eng, packed, dad, node, L, model_args, steps, warmup, ndev
             "clocks": worst, "collective_us": None}
 
 
+def attach_ncu_traffic(roof, name, full_size):
+    """roofline.traffic: dram__bytes_read + dram__bytes_write of the dominant kernel PER LAUNCH from the committed ncu pass
+    of this workload (profiles/traffic.json, tagged with the commit it was captured at) -- only when this run is the
+    size that pass measured; otherwise null."""
+    roof.pop("_workload_key", None)
+    if isinstance(roof.get("hbm"), dict):
+        roof["hbm"].pop("_workload_key", None)
+    tr_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if not full_size or not os.path.exists(tr_file):
+        return
+    try:
+        t = json.load(open(tr_file)).get(name)
+    except Exception:
+        return
+    if t:
+        roof["traffic"] = t["dram_bytes_per_launch"]
+        roof["traffic_source"] = {k: t[k] for k in ("dram_bytes_per_step", "launches_per_step", "commit", "source") if k in t}
+
+
 def roofline_of(n, ncm, tr, N_local, r, steps):
     """roofline object of the partial-update kernel(s) from one timed_engine_run on N_local patterns."""
     (hbm, hbm_src), (f64, f64_src) = peaks()
@@ -567,12 +586,7 @@ def roofline_of(n, ncm, tr, N_local, r, steps):
         hbm_obj["kernel"] = "s4_traverse_kernel (4-state partial update, whole traversal)"
     else:
         hbm_obj["kernel"] = "partial update (pruning step), level-batched"
-    tr_file = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tr_file):  # dram__bytes_read+write per step from a committed ncu --set full capture, tagged
-        try:
-            hbm_obj["traffic_ncu"] = json.load(open(tr_file))
-        except Exception:
-            pass
+    hbm_obj["_workload_key"] = None
     if n < 9:
         return hbm_obj, kinds
     # dense paths: the FP64 tensor pipe (DMMA) bounds the kernel next to HBM (20 states: AI ~ 5 flop/B, at the ridge)
@@ -653,6 +667,7 @@ def measure_alignment(args, D, name, steps, warmup, want_cpu_baseline, cpu_patte
             roof["achieved"] /= ndev_sp
             roof["frac"] = roof["achieved"] / roof["peak"]
             roof["per_device"] = True
+    attach_ncu_traffic(roof, name, world == 1 and not ndev_sp and N == N0)
     updates_per_step = len(tr) * N  # strong scaling: the named shape is the total over all ranks
     line = {
         "metric": METRIC, "value": updates_per_step * steps / (r["ms"] * 1e-3), "unit": UNIT,

@@ -14,16 +14,16 @@ python -c "import __graft_entry__ as g; g.smoke()" > $OUT/smoke_$TAG.log 2>&1; e
 tail -3 $OUT/pytest_$TAG.log; tail -2 $OUT/smoke_$TAG.log
 fi
 if has bench; then
-python bench.py > $OUT/bench_cfg2_$TAG.json 2> $OUT/bench_cfg2_$TAG.err
-python bench.py --workload cfg3 --steps 5 > $OUT/bench_cfg3_$TAG.json 2> $OUT/bench_cfg3_$TAG.err
-python bench.py --impl reference --steps 3 --warmup 1 > $OUT/bench_ref_$TAG.json 2> $OUT/bench_ref_$TAG.err
-cut -c1-300 $OUT/bench_cfg2_$TAG.json; cut -c1-300 $OUT/bench_cfg3_$TAG.json
+# the driver's command: the headline cfg2 line with parity, cpu_baseline and the cfg3 / cfg4-full / cfg5 / sweep sub-results
+python bench.py --steps 20 --warmup 5 > $OUT/bench_cfg2_$TAG.json 2> $OUT/bench_cfg2_$TAG.err; echo "bench rc=$?"
+python bench.py --impl reference --steps 20 --warmup 5 > $OUT/bench_ref_$TAG.json 2> $OUT/bench_ref_$TAG.err; echo "reference rc=$?"
+cut -c1-300 $OUT/bench_cfg2_$TAG.json; cut -c1-400 $OUT/bench_ref_$TAG.json
 fi
 if has launches; then
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_cfg2_$TAG.csv \
-    python bench.py --steps 2 --warmup 3 --no-cpu > $OUT/ncu_l2_$TAG.log 2>&1
+    python bench.py --steps 2 --warmup 3 --no-cpu --shapes none > $OUT/ncu_l2_$TAG.log 2>&1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches_cfg3_$TAG.csv \
-    python bench.py --workload cfg3 --patterns 50000 --steps 2 --warmup 3 --no-cpu > $OUT/ncu_l3_$TAG.log 2>&1
+    python bench.py --workload cfg3 --patterns 50000 --steps 2 --warmup 3 --no-cpu --shapes none > $OUT/ncu_l3_$TAG.log 2>&1
 fi
 if has bench45; then
 python bench.py --workload cfg4 --steps 5 > $OUT/bench_cfg4_$TAG.json 2> $OUT/bench_cfg4_$TAG.err
@@ -44,17 +44,17 @@ fi
 if has traffic; then
 # DRAM bytes of every partial-update launch of cfg2 / cfg3 at the bench's full size (roofline.traffic)
 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:'s4_traverse' \
-    --csv --log-file $OUT/traffic_cfg2_$TAG.csv python bench.py --steps 1 --warmup 3 --no-cpu > $OUT/ncu_t2_$TAG.log 2>&1
+    --csv --log-file $OUT/traffic_cfg2_$TAG.csv python bench.py --steps 1 --warmup 3 --no-cpu --shapes none > $OUT/ncu_t2_$TAG.log 2>&1
 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:'dense20' \
-    --csv --log-file $OUT/traffic_cfg3_$TAG.csv python bench.py --workload cfg3 --steps 1 --warmup 3 --no-cpu > $OUT/ncu_t3_$TAG.log 2>&1
+    --csv --log-file $OUT/traffic_cfg3_$TAG.csv python bench.py --workload cfg3 --steps 1 --warmup 3 --no-cpu --shapes none > $OUT/ncu_t3_$TAG.log 2>&1
 fi
 if has prof_s4; then
-ncu --set full --clock-control none --import-source on -k regex:s4_traverse --launch-skip 6 -c 2 -f -o $OUT/prof_s4_$TAG \
-    python bench.py --steps 1 --warmup 3 --no-cpu > $OUT/ncu_s4_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'s4_traverse|eval_tail' --launch-skip 9 -c 3 -f -o $OUT/prof_s4_$TAG \
+    python bench.py --steps 1 --warmup 3 --no-cpu --shapes none > $OUT/ncu_s4_$TAG.log 2>&1
 fi
 if has prof_d20; then
 # one step of cfg3 at 50k patterns has 31 dense20 launches (levels); take the first (TT-heavy), and three deeper ones
 ncu --set full --clock-control none --import-source on -k regex:dense20 --launch-skip 93 -c 4 -f -o $OUT/prof_dense20_$TAG \
-    python bench.py --workload cfg3 --patterns 50000 --steps 1 --warmup 3 --no-cpu > $OUT/ncu_d20_$TAG.log 2>&1
+    python bench.py --workload cfg3 --patterns 50000 --steps 1 --warmup 3 --no-cpu --shapes none > $OUT/ncu_d20_$TAG.log 2>&1
 fi
 du -sh $OUT
