@@ -602,6 +602,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     const bool use_tt = !c->batch && b200_env().s4_tt && (int64_t)codes * codes * 4 <= c->ntot;
     const size_t tt_doubles = (size_t)codes * codes * NCM * 4;
     std::vector<S4TTNode> tt_nodes;
+    std::vector<const DevChild *> exp_src(2 * (size_t)count, nullptr);
     for (int i = 0; i < count; i++) {
         PNode<NCM> &f = P.nodes[i];
         memset(&f, 0, sizeof(f));
@@ -627,7 +628,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
                 kind[k] = SRC_LEAF; id[k] = nseq % chunk; tab[k] = (int)ch.leaf_off;
                 leaf_seq[nseq++] = ch.id;
             } else {
-                fill_expv<NCM>(c, ch, k == 0 ? f.lexp : f.rexp);
+                exp_src[2 * i + k] = &ch;  // exp(lambda r t) of this child: filled below, all children in parallel
                 (k == 0 ? f.lexp_off : f.rexp_off) = (int32_t)(ch.echild_off + (int64_t)c->block * c->d.nstates);
                 const int pr = producer[ch.id];
                 if (pr >= 0 && consumer[pr] == i && pr == i - 1) {
@@ -663,6 +664,14 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         }
         f.info = kind[0] | kind[1] << 2 | (out_stack + 1) << 4 | tt << 12 | (refill + 1) << 13;
         producer[nl[i].out_slot] = i;
+    }
+    // the per-child factors: 16 exp() per internal child, ~6000 for a cfg2 traversal -- what a blocking evaluation spends
+    // most of its host time on, so a few threads share it (the calling thread alone for short lists)
+    {
+        const int nexp = 2 * count;
+#pragma omp parallel for schedule(static) num_threads(4) if (nexp >= 64)
+        for (int j = 0; j < nexp; j++)
+            if (exp_src[j]) fill_expv<NCM>(c, *exp_src[j], (j & 1) ? P.nodes[j >> 1].rexp : P.nodes[j >> 1].lexp);
     }
     int32_t *d_seq = reinterpret_cast<int32_t *>(c->d_prog) + *seq_used;
     if (nseq)
