@@ -417,8 +417,21 @@ def timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup, co
     # the sums over the ranks: exchanged inside the finishing kernel over NVLink peer memory (b200lk_peer_connect), or
     # with --collective nccl by an ncclAllReduce of the 3 doubles behind it
     use_nccl = D.dist is not None and collective == "nccl"
+    peer_note = None
     if D.dist is not None and not use_nccl:
-        eng.connect_peers(D.dist)
+        try:
+            eng.connect_peers(D.dist)
+            ok = 1
+        except Exception as ex:  # no CUDA IPC / peer access on this box: every rank falls back to NCCL together
+            peer_note, ok = "%s: %s" % (type(ex).__name__, ex), 0
+        import torch
+        flag = torch.tensor([ok], device="cuda")
+        D.dist.all_reduce(flag, op=D.dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            if ok:
+                eng.peer_disconnect()
+            use_nccl = True
+            log("peer exchange unavailable (%s): using ncclAllReduce" % peer_note)
 
     def step_device():
         eng.evaluate_async(packed, dad, node, L)
@@ -487,7 +500,7 @@ def timed_engine_run(D, eng, packed, dad, node, L, model_args, steps, warmup, co
     eng.set_stream(None)
     return {"ms": ms, "e2e_ms": e2e_ms, "partial_ms": partial_ms, "partial_launches": partial_launches,
             "launches": launches, "min_bytes": min_bytes, "result": result, "local_result": local_res,
-            "clocks": clocks, "collective_us": coll_us}
+            "clocks": clocks, "collective_us": coll_us, "used_nccl": use_nccl, "peer_note": peer_note}
 
 
 def timed_sharded_run(eng, packed, dad, node, L, model_args, steps, warmup, ndev):
@@ -693,8 +706,8 @@ def measure_alignment(args, D, name, steps, warmup, want_cpu_baseline, cpu_patte
     if world > 1:
         line["collective"] = {
             "used": "in-kernel exchange over NVLink peer memory (b200lk_peer_connect): the last CTA of the finishing kernel "
-                    "stores the 3 sums into every peer's buffer, waits for the peers' and adds in rank order" if args.collective == "peer"
-            else "ncclAllReduce(sum) of 3 doubles on the evaluation's stream",
+                    "stores the 3 sums into every peer's buffer, waits for the peers' and adds in rank order" if not r.get("used_nccl")
+            else "ncclAllReduce(sum) of 3 doubles on the evaluation's stream" + (" (peer exchange unavailable: %s)" % r["peer_note"] if r.get("peer_note") else ""),
             "nccl_allreduce_3_doubles_us": r["collective_us"]}
         line["weak_scaling"] = weak
     # ---- parity against the reference kernel on the same patterns, and the CPU baseline ----

@@ -334,6 +334,7 @@ int b200lk_read_results(b200lk_ctx *ctx, double *lnl, double *df, double *ddf);
  * like in any collective).  Only b200lk_evaluate_async / b200lk_evaluate exchange; the other entry points stay local. */
 int b200lk_peer_handle(b200lk_ctx *ctx, void *handle64 /* 64 bytes out */);
 int b200lk_peer_connect(b200lk_ctx *ctx, int32_t rank, int32_t world, const void *handles /* [world][64] */);
+int b200lk_peer_disconnect(b200lk_ctx *ctx); /* back to purely local sums */
 
 /* ---- device-resident results on demand --------------------------------- */
 /* Unreduced per-shard sums for multi-GPU runs: out[0] = lnL (if requested), out[1] = df,

@@ -338,6 +338,9 @@ class Engine:
         assert len(handles) == 64 * world
         self._check(self._f("peer_connect")(self.ctx, C.c_int32(rank), C.c_int32(world), C.c_char_p(handles)))
 
+    def peer_disconnect(self):
+        self._check(self._f("peer_disconnect")(self.ctx))
+
     def connect_peers(self, dist):
         """Gather every rank's handle over torch.distributed and connect (one process per GPU)."""
         import torch

@@ -22,10 +22,17 @@
 #include "common.cuh"
 
 #define DN_THREADS 128
+#ifndef DN_MT
 #define DN_MT 2                                   // row tiles (8 patterns) per warp
+#endif
+#ifndef DN_RP_MINB
+#define DN_RP_MINB 3                              // resident CTAs per SM dense20_rp_kernel's registers are sized for
+#endif
 #define DN_PT (DN_THREADS / 32 * 8 * DN_MT)       // 64 patterns per CTA tile
 #define DN_CG 4                                   // categories per staged group
+#ifndef DN_MAX_TILES
 #define DN_MAX_TILES 8
+#endif
 
 struct DenseArgs {
     const DevNode *nodes;
@@ -161,7 +168,7 @@ __global__ void __launch_bounds__(DN_THREADS, MINB) dense20_kernel(DenseArgs a) 
                 pc[mt] = p[mt] < a.ntot ? p[mt] : a.ntot - 1;
                 invar0[mt] = a.ptn_invar[pc[mt]] == 0.0;
             }
-            unsigned long long rmax[DN_MT] = {0ull, 0ull};
+            unsigned long long rmax[DN_MT] = {};
             for (int cl = 0; cl < cg; cl++) {
                 const int c = c0 + cl;
                 double fl[DN_MT][6], fr[DN_MT][6];
@@ -389,10 +396,10 @@ __global__ void __launch_bounds__(DN_THREADS, 2) dense20_pipe_kernel(DenseArgs a
         };
         if (nsteps > 0 && !tiptip) prefetch(0, 0);
         cp_async_commit();
-        int stL[DN_MT] = {0, 0}, stR[DN_MT] = {0, 0};
-        int64_t p[DN_MT] = {0, 0}, pc[DN_MT] = {0, 0};
-        bool invar0[DN_MT] = {false, false};
-        unsigned long long rmax[DN_MT] = {0ull, 0ull};
+        int stL[DN_MT] = {}, stR[DN_MT] = {};
+        int64_t p[DN_MT] = {}, pc[DN_MT] = {};
+        bool invar0[DN_MT] = {};
+        unsigned long long rmax[DN_MT] = {};
         for (int step = 0; step < nsteps; step++) {
             const int t = step / cg, cl = step - t * cg, c = c0 + cl;
             if (step + 1 < nsteps && !tiptip) prefetch(step + 1, (step + 1) & 1);
@@ -533,7 +540,7 @@ __device__ __forceinline__ void dense_mma_child(const double (&A)[DN_MT][5], con
 }
 
 template <bool SAFE>
-__global__ void __launch_bounds__(DN_THREADS, 3) dense20_rp_kernel(DenseArgs a, BatchLaunch bl) {
+__global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(DenseArgs a, BatchLaunch bl) {
     extern __shared__ double sm[];
     if (bl.d_ctx) {  // batched launch: grid.z = context of the supermatrix, same node structure, own data
         const BatchCtxDev &b = bl.d_ctx[blockIdx.z];
@@ -616,15 +623,15 @@ __global__ void __launch_bounds__(DN_THREADS, 3) dense20_rp_kernel(DenseArgs a, 
             }
         };
         double AL[DN_MT][5], AR[DN_MT][5];
-        int64_t p[DN_MT] = {0, 0}, pc[DN_MT] = {0, 0}, pn[DN_MT], pcn[DN_MT];
+        int64_t p[DN_MT] = {}, pc[DN_MT] = {}, pn[DN_MT], pcn[DN_MT];
         if (nsteps > 0) {
             rows_of(0, pn, pcn);
             if (!Lleaf) dense_load_A(pL, block, c0, pcn, q, AL);
             if (!Rleaf) dense_load_A(pR, block, c0, pcn, q, AR);
         }
-        int stL[DN_MT] = {0, 0}, stR[DN_MT] = {0, 0};
-        bool invar0[DN_MT] = {false, false};
-        unsigned long long rmax[DN_MT] = {0ull, 0ull};
+        int stL[DN_MT] = {}, stR[DN_MT] = {};
+        bool invar0[DN_MT] = {};
+        unsigned long long rmax[DN_MT] = {};
         for (int step = 0; step < nsteps; step++) {
             const int t = step / cg, cl = step - t * cg, c = c0 + cl;
             const bool more = step + 1 < nsteps;

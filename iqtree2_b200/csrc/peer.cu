@@ -48,6 +48,25 @@ extern "C" int b200lk_peer_connect(b200lk_ctx *c, int32_t rank, int32_t world, c
     return B200LK_OK;
 }
 
+// Back to purely local sums (e.g. when another rank could not map the buffers and everybody falls back to a collective).
+extern "C" int b200lk_peer_disconnect(b200lk_ctx *c) {
+    if (!c) return B200LK_ERR_ARG;
+    SHARD_REFUSE(c, "the cross-process peer exchange");
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    for (int r = 0; r < B200_PEER_MAX; r++)
+        if (c->peer_mapped[r]) {
+            cudaIpcCloseMemHandle(c->peer_mapped[r]);
+            c->peer_mapped[r] = nullptr;
+        }
+    if (c->d_peer_bufs) cudaFree(c->d_peer_bufs);
+    c->d_peer_bufs = nullptr;
+    c->peer_world = 0;
+    c->peer_rank = 0;
+    c->peer_seq = 0;
+    return B200LK_OK;
+}
+
 void peer_release(b200lk_ctx *c) {
     for (int r = 0; r < B200_PEER_MAX; r++)
         if (c->peer_mapped[r]) cudaIpcCloseMemHandle(c->peer_mapped[r]);
