@@ -306,6 +306,21 @@ typedef struct b200lk_newton {
 int b200lk_optimize_branch(b200lk_ctx *ctx, b200lk_end dad, b200lk_end node, const b200lk_newton *nr,
                            double *optx, double *d2l, int32_t *nsteps);
 
+/* ---- branch lengths resident on the device: a whole optimizeAllBranches sweep without a read-back --------------------
+ * PhyloTree::optimizeAllBranches (tree/phylotree.cpp:2689-2765) re-roots at every branch in turn: one partial update across
+ * the branch just optimised, theta, Newton-Raphson.  The next update needs the length just found; when the host forms the
+ * exp(lambda r t) factors, that is a device->host round trip per branch.  With these entry points the lengths live in a
+ * device table indexed by the caller's own branch id: the children of an update name slots (len_slot[j] >= 0; -1 keeps
+ * children[j].length), the Newton-Raphson launch starts from lengths[len_slot] and writes the optimum back, and the host
+ * reads the table ONCE per sweep -- with each slot's evaluation count and status (aux[slot][0..1]; status 1 = non-finite
+ * derivative), from which it applies the checks optimizeOneBranch makes per branch (:2607-2616).  Reversible,
+ * non-site-specific, non-sharded contexts without +ASC; bifurcating nodes on the 4-state path. */
+int b200lk_set_lengths(b200lk_ctx *ctx, const double *lengths, int32_t n);
+int b200lk_get_lengths(b200lk_ctx *ctx, double *lengths, double *aux /* [n][2] or NULL */, int32_t n);
+int b200lk_update_partials_slots(b200lk_ctx *ctx, const b200lk_node *nodes, int32_t nnodes, const b200lk_child *children,
+                                 int32_t nchildren, const int32_t *len_slot /* [nchildren] */);
+int b200lk_optimize_branch_slot(b200lk_ctx *ctx, b200lk_end dad, b200lk_end node, const b200lk_newton *nr, int32_t len_slot);
+
 /* One round trip for a whole evaluation: update_partials + branch_lnl + build_theta + derv
  * (what computeLikelihood followed by the first computeFuncDerv of optimizeOneBranch costs,
  * tree/phylotree.cpp:1227-1268, 2520-2527).  Any of lnl/df/ddf may be NULL. */

@@ -295,6 +295,40 @@ class Engine:
                                          C.byref(steps)))
         return optx.value, d2l.value, steps.value
 
+    # -- branch lengths resident on the device --------------------------------------
+    def set_lengths(self, lengths):
+        a = np.ascontiguousarray(lengths, dtype=np.float64)
+        self._nlens = a.size
+        self._check(self._f("set_lengths")(self.ctx, _dp(a), C.c_int32(a.size)))
+
+    def get_lengths(self):
+        """-> (lengths [n], aux [n][2]: derivative evaluations and status of each slot's last optimisation)"""
+        n = self._nlens
+        ln, aux = np.empty(n), np.empty((n, 2))
+        self._check(self._f("get_lengths")(self.ctx, _dp(ln), _dp(aux), C.c_int32(n)))
+        return ln, aux
+
+    def update_partials_slots(self, entries, slots):
+        """update_partials with the children's lengths taken from the device table: slots[j] >= 0 names the slot of child j
+        of the packed list, -1 keeps the length in the entry."""
+        nodes, nn, kids, nk = pack_traversal(entries)
+        sl = np.ascontiguousarray(slots, dtype=np.int32)
+        assert sl.size == nk
+        f = self._f("update_partials_slots")
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]
+        return self._check(f(self.ctx, nodes, nn, kids, nk, sl.ctypes.data_as(C.c_void_p)))
+
+    def optimize_branch_slot(self, dad, node, slot, min_len=1e-6, max_len=10.0, xacc=None, max_steps=100):
+        """Newton-Raphson from lengths[slot] to lengths[slot], nothing read back."""
+
+        class Newton(C.Structure):
+            _fields_ = [("min_len", C.c_double), ("max_len", C.c_double), ("xacc", C.c_double),
+                        ("guess", C.c_double), ("max_steps", C.c_int32), ("reserved", C.c_int32)]
+        nr = Newton(min_len, max_len, min_len if xacc is None else xacc, 0.0, max_steps, 0)
+        f = self._f("optimize_branch_slot")
+        f.argtypes = [C.c_void_p, End, End, C.c_void_p, C.c_int32]
+        self.last_status = self._check(f(self.ctx, End(*dad), End(*node), C.byref(nr), C.c_int32(slot)))
+
     def evaluate(self, entries, dad, node, length, want_lnl=True, want_derv=True):
         nodes, nn, kids, nk = pack_traversal(entries)
         lnl, df, ddf = C.c_double(), C.c_double(), C.c_double()

@@ -80,6 +80,7 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
         dc.frag_off = -1;
         dc.aux_off = -1;
         dc.src = j;
+        dc.len_slot = c->cur_len_slots ? c->cur_len_slots[j] : -1;
         if (c->frag_cat) {
             dc.frag_off = (int64_t)off;
             off += (size_t)c->ncat_mix * c->frag_cat;

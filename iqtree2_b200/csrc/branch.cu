@@ -575,6 +575,8 @@ struct NewtonArgs {
     double x1, x2, xacc, guess;
     int max_steps, ncat, safe_zero;
     double *out;  // [0] optx, [1] d2l, [2] derivative evaluations, [3] status (0 ok, 1 non-finite derivative)
+    const double *guess_dev;  // non-null: the starting length is read from the device (device-resident lengths, sweep.cu)
+    double *len_out, *aux_out;  // non-null: the optimum goes into the length table, evaluations and status beside it
     double *red;  // [2 parities][2][red_blocks]
 };
 
@@ -588,7 +590,8 @@ __global__ void __launch_bounds__(RED_THREADS) newton_kernel(BranchArgs a, Newto
     const int block = a.block, n = a.n;
     const double *v0 = sval, *v1 = sval + block, *v2 = sval + 2 * block;
     // Newton state, replicated in thread 0 of every CTA
-    double rts = fmin(fmax(nr.guess, nr.x1), nr.x2), xl = 0.0, xh = 0.0, dx = 0.0, rts_old = rts, d2l = 0.0, result = rts;
+    const double guess0 = nr.guess_dev ? *nr.guess_dev : nr.guess;  // read by every CTA before the first grid barrier
+    double rts = fmin(fmax(guess0, nr.x1), nr.x2), xl = 0.0, xh = 0.0, dx = 0.0, rts_old = rts, d2l = 0.0, result = rts;
     int j = 0, evals = 0, status = 0;
     bool started = false;
     for (int iter = 0;; iter++) {
@@ -722,6 +725,11 @@ __global__ void __launch_bounds__(RED_THREADS) newton_kernel(BranchArgs a, Newto
                 nr.out[1] = d2l;
                 nr.out[2] = (double)evals;
                 nr.out[3] = (double)status;
+                if (nr.len_out) {  // written after at least one grid barrier: no CTA still needs the old value
+                    *nr.len_out = result;
+                    nr.aux_out[0] = (double)evals;
+                    nr.aux_out[1] = (double)status;
+                }
             }
         }
         __syncthreads();
@@ -1073,6 +1081,10 @@ int launch_newton(b200lk_ctx *c, const b200lk_newton *nr, const b200lk_end *ends
     na.ncat = c->d.ncat;
     na.safe_zero = c->d.safe_numeric;
     na.out = c->d_result + 4;
+    const int slot = c->cur_newton_slot;
+    na.guess_dev = slot >= 0 ? c->d_lens + slot : nullptr;
+    na.len_out = slot >= 0 ? c->d_lens + slot : nullptr;
+    na.aux_out = slot >= 0 ? c->d_lens_aux + 2 * (size_t)slot : nullptr;
     na.red = c->red_partial;  // [2 parities][2][red_blocks] of its 8 * red_blocks doubles
     const size_t smem = sizeof(double) * 3 * c->block;
     if (smem > 200 * 1024 || c->d.n_unobserved > 0) return B200LK_ERR_UNSUPPORTED;  // +ASC: host-driven iteration

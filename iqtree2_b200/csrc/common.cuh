@@ -45,6 +45,7 @@ struct DevChild {
     int64_t aux_off;     // left child of a tip-tip node (20-state path): offset of the node's state-pair table in tt_tables
     int64_t src;         // position in the caller's children array (entries are reordered leaf-first): indexes
                          // BatchLaunch::d_child_len
+    int64_t len_slot;    // >= 0: the branch length is lengths[len_slot] of the context's device-resident table (sweep.cu)
 };
 
 struct DevNode {
@@ -73,6 +74,7 @@ struct BatchLaunch {           // non-null in b200lk_ctx::batch while a batched 
     const double *d_child_len; // [n][nchildren] branch length to every child, per context
     int nchildren;
     const double *d_branch_len;  // [n] length of the branch the likelihood is taken at
+    const double *d_lens;        // device-resident branch-length table of a single context (sweep.cu), or null
 };
 
 // b200lk_create_sharded (shard.cu): one problem split by site pattern over several devices of THIS process.  The parent
@@ -187,6 +189,13 @@ struct b200lk_ctx {
     double s4_pi[4];
     bool model_set, tips_set, theta_computed;
     int theta_dad_kind;
+    // device-resident branch lengths (sweep.cu): a whole optimizeAllBranches sweep is enqueued without reading a length back
+    double *d_lens, *d_lens_aux;       // [lens_cap] lengths, [lens_cap][2] evaluations and status of the last optimisation
+    int lens_cap;
+    const int32_t *cur_len_slots;      // host [nchildren]; non-null only inside b200lk_update_partials_slots
+    int cur_newton_slot;               // slot the Newton-Raphson launch being enqueued reads its guess from / writes to; -1 none
+    BatchCtxDev *self_dev;             // this context as a batch of one (4-state path: exp factors from the tables)
+    BatchLaunch self_bl;
     unsigned *tail_counter;  // eval_tail_kernel: CTAs finished (device)
     // exchange of [lnL, df, ddf] between the pattern shards of several PROCESSES over NVLink peer memory (peer.cu):
     // every rank's exchange buffer is mapped into every other rank (CUDA IPC); the kernel that finishes an evaluation

@@ -158,6 +158,7 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
     memset(c, 0, sizeof(*c));
     c->d = *dims;
     c->robust_keep = 1.0;
+    c->cur_newton_slot = -1;
     c->device = dims->device;
     c->ncat_mix = dims->fused_mix_rate ? dims->ncat : dims->ncat * dims->nmix;  // tree/phylokernelnew.h:1323
     c->block = dims->nstates * c->ncat_mix;
@@ -222,6 +223,8 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     for (void *p : dev)
         if (p) cudaFree(p);
     peer_release(c);
+    for (void *p2 : {(void *)c->d_lens, (void *)c->d_lens_aux, (void *)c->self_dev})
+        if (p2) cudaFree(p2);
     if (c->tail_counter) cudaFree(c->tail_counter);
     if (c->h_model_stage) cudaFreeHost(c->h_model_stage);
     if (c->model_ev) cudaEventDestroy(c->model_ev);

@@ -52,6 +52,7 @@ extern "C" int b200lk_create_sharded(b200lk_ctx **out, const b200lk_dims *dims, 
     c->scale_per_ptn = dims->safe_numeric ? c->ncat_mix : 1;
     c->ntot = dims->nptn;
     c->robust_keep = 1.0;
+    c->cur_newton_slot = -1;
     c->shards = new ShardSet();
     for (int i = 0; i < ndev; i++) {
         int64_t b, e;

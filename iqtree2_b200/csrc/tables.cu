@@ -18,8 +18,9 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
         const BatchCtxDev &b = bl.d_ctx[blockIdx.y];
         m = b.m;
         tables = b.tables;
-        ch.length = bl.d_child_len[(size_t)blockIdx.y * bl.nchildren + ch.src];
+        if (bl.d_child_len) ch.length = bl.d_child_len[(size_t)blockIdx.y * bl.nchildren + ch.src];
     }
+    if (bl.d_lens && ch.len_slot >= 0) ch.length = bl.d_lens[ch.len_slot];  // device-resident lengths (sweep.cu)
     const int block = n * ncm, nn = n * n;
     double *echild = tables + ch.echild_off;
     // grid.z splits the categories of a child over CTAs (mixtures: 240 categories per child); every phase below only
@@ -83,6 +84,7 @@ int launch_tables(b200lk_ctx *c, int nchildren) {
     BatchLaunch bl;
     memset(&bl, 0, sizeof(bl));
     if (c->batch) bl = *c->batch;
+    bl.d_lens = c->cur_len_slots ? c->d_lens : nullptr;
     const int zsplit = std::min(64, (c->ncat_mix + 15) / 16);  // <= 16 categories per CTA
     tables_kernel<<<dim3(nchildren, c->batch ? c->batch->n : 1, zsplit), 256, 0, c->stream>>>(
         c->d_children, c->m, c->tables, c->d.nstates, c->d.ncat, c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes,

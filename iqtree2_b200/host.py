@@ -316,6 +316,15 @@ class HostTree:
         _ck(lib().b200host_tree_newick(self.h, buf, len(buf)))
         return buf.value.decode()
 
+    def set_device_sweep(self, on):
+        """Params::device_sweep: optimizeAllBranches keeps the lengths on the device for a whole sweep (default on)."""
+        lib().b200host_tree_set_device_sweep(self.h, int(bool(on)))
+
+    def device_sweeps(self):
+        f = lib().b200host_tree_device_sweeps
+        f.restype = C.c_int64
+        return f(self.h)
+
     def kernel_calls(self):
         return lib().b200host_tree_kernel_calls(self.h)
 

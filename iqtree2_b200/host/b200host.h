@@ -63,6 +63,11 @@ struct KernelABI {
     int (*fetch_scale_num)(b200lk_ctx *, int32_t, uint8_t *);
     int (*optimize_branch)(b200lk_ctx *, b200lk_end, b200lk_end, const b200lk_newton *, double *, double *,
                            int32_t *);                                    // optional
+    // optional: branch lengths resident on the device (a whole sweep without a read-back)
+    int (*set_lengths)(b200lk_ctx *, const double *, int32_t);
+    int (*get_lengths)(b200lk_ctx *, double *, double *, int32_t);
+    int (*update_partials_slots)(b200lk_ctx *, const b200lk_node *, int32_t, const b200lk_child *, int32_t, const int32_t *);
+    int (*optimize_branch_slot)(b200lk_ctx *, b200lk_end, b200lk_end, const b200lk_newton *, int32_t);
     // optional: +ASC flavour, robust scoring, pattern weights, heterotachy (NULL when the library has none)
     int (*set_asc)(b200lk_ctx *, int32_t);
     int (*set_robust)(b200lk_ctx *, double, int32_t);
@@ -239,6 +244,7 @@ struct Params {  // the few fields of utils/tools.h Params the path reads
     // (b200lk_create_sharded; the device form of the reference's packets, tree/phylokernelnew.h:1114-1142)
     std::vector<int> devices;
     bool device_newton = true;        // run minimizeNewton's iteration on the device when the library offers it
+    bool device_sweep = true;         // optimizeAllBranches: keep the lengths on the device for a whole sweep (one read-back)
 };
 
 // ---- memory slots of the -mem mode (tree/memslot.h:38-109) ------------------------------------------------
@@ -353,6 +359,7 @@ public:
     double curScore = 0.0;
     std::vector<double> _pattern_lh, _pattern_lh_cat;  // filled lazily (computePatternLikelihood)
     int64_t kernel_calls = 0;  // C-ABI calls made (host-side statistic)
+    int64_t device_sweeps = 0; // optimizeAllBranches sweeps that ran with device-resident lengths (sweepOnDevice)
     b200lk_ctx *ctx = NULL;    // device residency of this tree
     MemSlotVector mem_slots;   // -mem (tree/phylotree.h: mem_slots)
     int max_lh_slots = 0;      // partial-vector slots handed out (leafNum-2, or fewer with LM_MEM_SAVE)
@@ -375,7 +382,12 @@ protected:
 
     bool computeTraversalInfo(PhyloNeighbor *dad_branch, PhyloNode *dad);
     void reorientPartialLh(PhyloNeighbor *dad_branch, PhyloNode *dad);  // tree/phylotree.cpp:5887-5901
-    void packTraversal(std::vector<b200lk_node> &nodes, std::vector<b200lk_child> &children);
+    void packTraversal(std::vector<b200lk_node> &nodes, std::vector<b200lk_child> &children, std::vector<int32_t> *slots = NULL);
+    // one sweep of optimizeAllBranches with the lengths resident on the device: 1 done; 0 not applicable (nothing touched);
+    // -1 given up midway (a per-branch check of optimizeOneBranch fired) -- the caller restores the lengths, invalidates
+    // and runs the sweep branch by branch
+    int sweepOnDevice(const std::vector<PhyloNode *> &nodes, const std::vector<PhyloNode *> &nodes2, int maxNRStep);
+
     void flushTraversal();  // traversal_info -> b200lk_update_partials
     void syncModel();
     void check(int rc, const char *what);

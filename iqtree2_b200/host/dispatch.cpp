@@ -369,9 +369,10 @@ void MemSlotVector::takeover(PhyloNeighbor *nei, PhyloNeighbor *taken_nei) {
     if ((*this)[id].nei == taken_nei) (*this)[id].nei = nei;
 }
 
-void PhyloTree::packTraversal(std::vector<b200lk_node> &nodes, std::vector<b200lk_child> &children) {
+void PhyloTree::packTraversal(std::vector<b200lk_node> &nodes, std::vector<b200lk_child> &children, std::vector<int32_t> *slots) {
     nodes.clear();
     children.clear();
+    if (slots) slots->clear();
     for (const TraversalInfo &info : traversal_info) {
         PhyloNode *node = info.dad_branch->node;
         b200lk_node nd;
@@ -392,6 +393,7 @@ void PhyloTree::packTraversal(std::vector<b200lk_node> &nodes, std::vector<b200l
             }
             ch.length = nb->length;
             children.push_back(ch);
+            if (slots) slots->push_back(nb->id);  // device-resident lengths are indexed by branch id
             nd.nchild++;
         }
         nodes.push_back(nd);
@@ -701,6 +703,65 @@ void PhyloTree::optimizeOneBranch(PhyloNode *node1, PhyloNode *node2, bool clear
     }
 }
 
+// One sweep over the branches with the lengths resident on the device (b200lk_*_slots, include/b200lk.h): every branch is
+// enqueued -- the partial update across the branch just optimised, theta, the whole Newton-Raphson iteration -- and the
+// lengths come back in ONE copy at the end.  The per-branch host logic of optimizeOneBranch that needs the optimum
+// (tree/phylotree.cpp:2607-2616: an optimum above 0.95 max_branch_length is compared with the old length) cannot run
+// inside such a sweep; it is checked afterwards, and when it would have fired the caller repeats the sweep branch by branch.
+int PhyloTree::sweepOnDevice(const std::vector<PhyloNode *> &nodes, const std::vector<PhyloNode *> &nodes2, int maxNRStep) {
+    const KernelABI &k = kernelABI();
+    if (!k.set_lengths || !k.get_lengths || !k.update_partials_slots || !k.optimize_branch_slot || !k.optimize_branch) return 0;
+    if (!params || !params->device_sweep || !params->device_newton || isMixlen() || params->devices.size() > 1) return 0;
+    if (params->asc_lewis || params->asc_holder || aln->num_states > 64) return 0;
+    syncModel();
+    std::vector<double> len, aux;
+    saveBranchLengths(len);
+    len.resize(branchNum);
+    if (k.set_lengths(ctx, len.data(), branchNum) != B200LK_OK) return 0;
+    kernel_calls++;
+    const double lo = params->min_branch_length, hi = params->max_branch_length;
+    std::vector<b200lk_node> tn;
+    std::vector<b200lk_child> tc;
+    std::vector<int32_t> slots;
+    for (size_t j = 0; j < nodes.size(); j++) {
+        current_it = nodes[j]->findNeighbor(nodes2[j]);
+        current_it_back = nodes2[j]->findNeighbor(nodes[j]);
+        theta_computed = false;
+        computeTraversalInfo(current_it->node, current_it_back->node);
+        if (!traversal_info.empty()) {
+            packTraversal(tn, tc, &slots);
+            traversal_info.clear();
+            const int rc = k.update_partials_slots(ctx, tn.data(), (int32_t)tn.size(), tc.data(), (int32_t)tc.size(), slots.data());
+            kernel_calls++;
+            if (rc == B200LK_ERR_UNSUPPORTED) return -1;  // e.g. a multifurcation on the 4-state path
+            check(rc, "b200lk_update_partials_slots");
+        }
+        b200lk_end de, ne;
+        branchEnds(current_it, current_it_back->node, de, ne);
+        b200lk_newton nr;
+        nr.min_len = lo; nr.max_len = hi; nr.xacc = lo; nr.guess = current_it->length;  // the kernel starts from lengths[id]
+        nr.max_steps = maxNRStep; nr.reserved = 0;
+        const int rc = k.optimize_branch_slot(ctx, de, ne, &nr, current_it->id);
+        kernel_calls++;
+        if (rc == B200LK_ERR_UNSUPPORTED) return -1;
+        check(rc, "b200lk_optimize_branch_slot");
+        theta_computed = true;
+        // the new length is not known here: treat it as changed (optimizeOneBranch clears only when it did change)
+        nodes[j]->clearReversePartialLh(nodes2[j]);
+        nodes2[j]->clearReversePartialLh(nodes[j]);
+    }
+    aux.assign((size_t)2 * branchNum, 0.0);
+    check(k.get_lengths(ctx, len.data(), aux.data(), branchNum), "b200lk_get_lengths");
+    kernel_calls++;
+    for (int b = 0; b < branchNum; b++) {
+        if (aux[2 * b + 1] != 0.0) check(B200LK_WARN_DERV_NONFINITE, "b200lk_optimize_branch_slot");
+        if (!(len[b] <= hi * 0.95)) return -1;  // optimizeOneBranch would have compared with the old length here
+    }
+    restoreBranchLengths(len);
+    device_sweeps++;
+    return 1;
+}
+
 double PhyloTree::optimizeAllBranches(int my_iterations, double tolerance, int maxNRStep) {
     std::vector<PhyloNode *> nodes, nodes2;
     PhyloNode *farleaf = findFarthestLeaf();  // computeBestTraversal, tree/phylotree.cpp:2680-2687
@@ -710,7 +771,13 @@ double PhyloTree::optimizeAllBranches(int my_iterations, double tolerance, int m
     std::vector<double> lenvec;
     for (int i = 0; i < my_iterations; i++) {
         saveBranchLengths(lenvec);
-        for (size_t j = 0; j < nodes.size(); j++) optimizeOneBranch(nodes[j], nodes2[j], true, maxNRStep);
+        const int swept = sweepOnDevice(nodes, nodes2, maxNRStep);
+        if (swept < 0) {  // given up midway (a per-branch check of optimizeOneBranch fired): back to where the sweep started
+            restoreBranchLengths(lenvec);
+            clearAllPartialLH();
+        }
+        if (swept <= 0)  // the reference's loop, branch by branch
+            for (size_t j = 0; j < nodes.size(); j++) optimizeOneBranch(nodes[j], nodes2[j], true, maxNRStep);
         double new_tree_lh = computeLikelihoodFromBuffer();
         if (new_tree_lh < tree_lh - tolerance * 0.1) {
             // rare: the likelihood decreased; restore and stop (tree/phylotree.cpp:2724-2752)

@@ -297,6 +297,13 @@ int b200host_tree_branch_split(void *hv, int bid, int32_t *rows, int32_t *nrows)
         *nrows = k;
     })
 }
+// Params::device_sweep of an existing tree, and how many optimizeAllBranches sweeps ran with device-resident lengths
+int b200host_tree_set_device_sweep(void *hv, int on) {
+    ((HostTree *)hv)->params.device_sweep = on != 0;
+    return 0;
+}
+int64_t b200host_tree_device_sweeps(void *hv) { return T(hv)->device_sweeps; }
+
 int b200host_tree_newick(void *hv, char *buf, int cap) {
     GUARD({
         std::string s = T(hv)->getTreeString(17);

@@ -69,6 +69,10 @@ const KernelABI &kernelABI() {
     bind(g_abi.evaluate_async, "evaluate_async", false);
     bind(g_abi.read_results, "read_results", false);
     bind(g_abi.optimize_branch, "optimize_branch", false);
+    bind(g_abi.set_lengths, "set_lengths", false);
+    bind(g_abi.get_lengths, "get_lengths", false);
+    bind(g_abi.update_partials_slots, "update_partials_slots", false);
+    bind(g_abi.optimize_branch_slot, "optimize_branch_slot", false);
     bind(g_abi.set_asc, "set_asc", false);
     bind(g_abi.set_robust, "set_robust", false);
     bind(g_abi.set_ptn_freq, "set_ptn_freq", false);
