@@ -971,25 +971,33 @@ def measure_sweep(args, D, name, sweeps, cpu_patterns):
     start = t.lengths()
     lnl0 = t.compute_likelihood()
     t.optimize_all_branches(iterations=1)  # warm-up: allocations, first launches
-    runs = []
     sampler = ClockSampler(D.local)
     sampler.start()
-    for _ in range(sweeps):
-        t.set_lengths(start)
-        t.clear_partials()
-        t.compute_likelihood()
-        torch.cuda.synchronize()
-        l0 = t.gpu_launches()
-        t0 = time.perf_counter()
-        lnl = t.optimize_all_branches(iterations=1)
-        torch.cuda.synchronize()
-        runs.append(((time.perf_counter() - t0) * 1e3, lnl, t.gpu_launches() - l0))
+    modes = {}
+    for mode, on in (("device_resident_lengths", True), ("branch_by_branch", False)):
+        t.set_device_sweep(on)
+        runs = []
+        for _ in range(sweeps):
+            t.set_lengths(start)
+            t.clear_partials()
+            t.compute_likelihood()
+            torch.cuda.synchronize()
+            l0, k0, d0 = t.gpu_launches(), t.kernel_calls(), t.device_sweeps()
+            t0 = time.perf_counter()
+            lnl = t.optimize_all_branches(iterations=1)
+            torch.cuda.synchronize()
+            runs.append(((time.perf_counter() - t0) * 1e3, lnl, t.gpu_launches() - l0, t.kernel_calls() - k0, t.device_sweeps() - d0))
+        modes[mode] = {"ms_per_sweep": min(r[0] for r in runs), "lnl_after_one_sweep": runs[-1][1], "launches_per_sweep": int(runs[-1][2]),
+                       "abi_calls_per_sweep": int(runs[-1][3]), "ran_on_device": bool(runs[-1][4])}
+    t.set_device_sweep(True)
     clocks = sampler.finish()
     nb = int(t.nbranches)
-    best = min(r[0] for r in runs)
+    best = modes["device_resident_lengths"]["ms_per_sweep"]
     out = {"workload": name, "model": model_name, "ntaxa": T, "patterns": int(aln.nptn), "branches": nb, "lnl_start": lnl0,
-           "ms_per_sweep": best, "us_per_branch": best * 1e3 / nb, "launches_per_sweep": int(runs[-1][2]),
-           "lnl_after_one_sweep": runs[-1][1], "pattern_branches_per_sec": nb * aln.nptn / (best * 1e-3), "clocks": clocks}
+           "ms_per_sweep": best, "us_per_branch": best * 1e3 / nb, "launches_per_sweep": modes["device_resident_lengths"]["launches_per_sweep"],
+           "lnl_after_one_sweep": modes["device_resident_lengths"]["lnl_after_one_sweep"], "modes": modes,
+           "modes_agree_rel": rel(modes["device_resident_lengths"]["lnl_after_one_sweep"], modes["branch_by_branch"]["lnl_after_one_sweep"]),
+           "pattern_branches_per_sec": nb * aln.nptn / (best * 1e-3), "clocks": clocks}
     t.close()
     if not args.no_cpu and cpu_patterns:
         import oracle

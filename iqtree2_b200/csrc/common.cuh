@@ -94,6 +94,7 @@ struct B200Env {
     int dense_pipe, dense_occ;    // B200LK_DENSE_PIPE (0 direct, 1 cp.async, 2 register prefetch), B200LK_DENSE_OCC (3 / 4)
     bool site_dmma;               // B200LK_SITE_DMMA=0 keeps the shuffle kernel for 20-state site models
     bool no_fused_tail;           // B200LK_NO_FUSED_TAIL=1: separate lnl / theta / derv launches in b200lk_evaluate*
+    int batch_minb;               // B200LK_BATCH_MINB=2|8: force one build of s4_traverse_batch_kernel (A/B); 0 = per use
     bool s4_tt;                   // B200LK_S4_TT=0: tip-tip nodes of the 4-state traversal computed, not looked up
 };
 const B200Env &b200_env();

@@ -34,6 +34,8 @@ const B200Env &b200_env() {
         e.site_dmma = !(v && *v == '0');
         v = getenv("B200LK_NO_FUSED_TAIL");
         e.no_fused_tail = v && *v == '1';
+        v = getenv("B200LK_BATCH_MINB");
+        e.batch_minb = v ? atoi(v) : 0;  // 0: chosen per use
         v = getenv("B200LK_S4_TT");
         e.s4_tt = !(v && *v == '0');
         return e;

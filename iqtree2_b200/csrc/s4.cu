@@ -379,8 +379,12 @@ __device__ __forceinline__ void child_apply_batch(const double *U, const double 
     }
 }
 
-template <int NCM, bool SAFE, bool SHARED>
-__global__ void __launch_bounds__(S4_THREADS, 2) s4_traverse_batch_kernel(const __grid_constant__ S4Launch<NCM> P, BatchLaunch bl) {
+// MINB: resident CTAs per SM the registers are sized for.  2 (220 registers, no spills) for the batches of many small genes
+// it was written for -- cfg5 33.6 ms against 34.0 ms with 8 (profiles/r2j_batch_minb_cfg5.log); 8 (128 registers) when ONE
+// large context runs as a batch of one (device-resident branch lengths, sweep.cu): the one-node updates of a branch sweep
+// are HBM-bound streams that need the bytes in flight (cfg2 sweep 88.8 -> 81.9 ms).  B200LK_BATCH_MINB overrides for A/B.
+template <int NCM, bool SAFE, bool SHARED, int MINB = 2>
+__global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_batch_kernel(const __grid_constant__ S4Launch<NCM> P, BatchLaunch bl) {
     constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
     TravArgs a = P.a;
     const BatchCtxDev &bc = bl.d_ctx[blockIdx.y];
@@ -748,6 +752,10 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         const bool safe = c->d.safe_numeric != 0, one_class = c->d.nmix == 1;
         auto kern = one_class ? (safe ? s4_traverse_batch_kernel<NCM, true, true> : s4_traverse_batch_kernel<NCM, false, true>)
                               : (safe ? s4_traverse_batch_kernel<NCM, true, false> : s4_traverse_batch_kernel<NCM, false, false>);
+        const int minb = b200_env().batch_minb ? b200_env().batch_minb : (c->batch == &c->self_bl ? 8 : 2);
+        if (minb == 8)
+            kern = one_class ? (safe ? s4_traverse_batch_kernel<NCM, true, true, 8> : s4_traverse_batch_kernel<NCM, false, true, 8>)
+                             : (safe ? s4_traverse_batch_kernel<NCM, true, false, 8> : s4_traverse_batch_kernel<NCM, false, false, 8>);
         kern<<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
     } else if (c->s4_sym) {
         // resident CTAs per SM the registers are sized for: 10 x 64 threads (96 registers, two stack entries) unless overridden
