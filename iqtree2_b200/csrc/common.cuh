@@ -85,7 +85,7 @@ struct ShardSet {
     std::vector<int64_t> begin, end;  // observed-pattern range [begin, end) of each shard (whole 32-pattern tiles)
 };
 
-// process-wide A/B and test hooks, read from the environment ONCE (context.cu) -- never on a launch path
+// process-wide A/B and test hooks, read from the environment when a context is created (context.cu) -- never on a launch path
 struct B200Env {
     int s4_minb;       // B200LK_S4_MINB: resident-CTA instantiation of s4_traverse_kernel (8 / 10 / 12); 0 = default
     bool s4_sym;       // B200LK_S4_SYM=0 keeps the general 4-state kernel
@@ -96,8 +96,13 @@ struct B200Env {
     bool no_fused_tail;           // B200LK_NO_FUSED_TAIL=1: separate lnl / theta / derv launches in b200lk_evaluate*
     int batch_minb;               // B200LK_BATCH_MINB=2|8: force one build of s4_traverse_batch_kernel (A/B); 0 = per use
     bool s4_tt;                   // B200LK_S4_TT=0: tip-tip nodes of the 4-state traversal computed, not looked up
+    bool s4_bulk;                 // B200LK_S4_BULK=1: node vectors leave through cp.async.bulk instead of the threads' STG (slower: A/B log)
+    bool s4_evict;                // B200LK_S4_EVICT=0: a full stack keeps what it holds (first come) instead of the soonest-wanted vectors
+    bool s4_prefetch;             // B200LK_S4_PREFETCH=1: L1 prefetch of the next node's tip-child table rows (slower: A/B log)
+    int s4_ring;                  // B200LK_S4_RING: shared-memory slots of the bulk-store traversal (0 = default 3)
 };
 const B200Env &b200_env();
+void b200_env_reload();  // b200lk_create*: the hooks in force are those of the latest context creation
 
 struct b200lk_ctx {
     ShardSet *shards;  // non-null: a sharded parent

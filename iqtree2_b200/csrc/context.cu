@@ -11,8 +11,9 @@ void peer_release(b200lk_ctx *c);  // peer.cu
 
 extern "C" const char *b200lk_version(void) { return "b200lk 0.2 (sm_100a)"; }
 
-const B200Env &b200_env() {
-    static const B200Env env = [] {
+// The A/B and test hooks: read when a context is created (b200lk_create*), never on a launch path.
+static B200Env read_env() {
+    {
         B200Env e;
         const char *v = getenv("B200LK_S4_MINB");
         e.s4_minb = v ? atoi(v) : 0;
@@ -38,10 +39,21 @@ const B200Env &b200_env() {
         e.batch_minb = v ? atoi(v) : 0;  // 0: chosen per use
         v = getenv("B200LK_S4_TT");
         e.s4_tt = !(v && *v == '0');
+        v = getenv("B200LK_S4_BULK");
+        e.s4_bulk = v && *v == '1';
+        v = getenv("B200LK_S4_PREFETCH");
+        e.s4_prefetch = v && *v == '1';
+        v = getenv("B200LK_S4_EVICT");
+        e.s4_evict = !(v && *v == '0');
+        v = getenv("B200LK_S4_RING");
+        e.s4_ring = v ? atoi(v) : 0;
+        if (e.s4_ring > 12) e.s4_ring = 12;
         return e;
-    }();
-    return env;
+    }
 }
+static B200Env g_env = read_env();
+const B200Env &b200_env() { return g_env; }
+void b200_env_reload() { g_env = read_env(); }
 
 extern "C" const char *b200lk_last_error(const b200lk_ctx *c) { return c ? c->err : "null context"; }
 
@@ -156,6 +168,7 @@ extern "C" int b200lk_create(b200lk_ctx **out, const b200lk_dims *dims) {
         cudaGetLastError();
         return B200LK_ERR_CUDA;  // no CPU fallback on this path
     }
+    b200_env_reload();
     b200lk_ctx *c = new b200lk_ctx();
     memset(c, 0, sizeof(*c));
     c->d = *dims;

@@ -63,6 +63,7 @@ struct TravArgs {
     size_t slot_doubles, slot_scale_bytes;
     int64_t ntot, ntot_pad;
     int nnodes, depth, chunk, denom, codes;
+    int prefetch;  // 1: the table rows of the NEXT node's tip children are pulled into L1 while this node computes
 };
 
 #define S4_PARAM_BYTES 32000
@@ -95,8 +96,16 @@ __device__ __forceinline__ unsigned long long abs_bits(double x) {
     return (unsigned long long)__double_as_longlong(x) & 0x7fffffffffffffffull;
 }
 
+// Shared-memory slot of a node vector.  Classic layout: [slot][pair][thread].  Warp-major layout (WL, the bulk-store
+// kernel): [slot][warp][pair][lane] -- a warp's part of a slot is then the byte image of its 32-pattern tile in HBM
+// (T32: pair j of lane l at j*32 + l double2), which is what one cp.async.bulk copies out.
+template <bool WL, int PAIRS>
+__device__ __forceinline__ int stk_at(int slot, int j, int tid) {
+    return WL ? ((slot * (S4_THREADS / 32) + (tid >> 5)) * PAIRS + j) * 32 + (tid & 31) : (slot * PAIRS + j) * S4_THREADS + tid;
+}
+
 // raw operand of one child: the leaf-table row (SRC_LEAF, already the factor) or the child's partial vector
-template <int NCM, bool SAFE>
+template <int NCM, bool SAFE, bool WL = false>
 __device__ __forceinline__ void child_load(const TravArgs &a, int kind, int id, int tab, const double *prev,
                                            unsigned prev_sc, const double2 *stk, const unsigned *stk_sc,
                                            const uint8_t *st_buf, int tid, size_t poff, int64_t p, double *v,
@@ -121,7 +130,7 @@ __device__ __forceinline__ void child_load(const TravArgs &a, int kind, int id, 
     } else if (kind == SRC_STACK) {
 #pragma unroll
         for (int j = 0; j < BLOCK / 2; j++) {
-            const double2 u = stk[(id * (BLOCK / 2) + j) * S4_THREADS + tid];
+            const double2 u = stk[stk_at<WL, BLOCK / 2>(id, j, tid)];
             v[2 * j] = u.x;
             v[2 * j + 1] = u.y;
         }
@@ -173,7 +182,16 @@ __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const doubl
 // The 20 values are copied into vector registers once per thread (through shared memory, so that the compiler cannot
 // turn them back into constant-bank reads); the kernel then fits 96 registers: five resident CTAs per SM with two
 // stack entries (profiles/r1t_s4_ureg_ab.log), later as ten CTAs of 64 threads.
-template <int NCM, bool SAFE, bool SYM, int MINB = S4_MINB>
+//
+// BULK: the node vector leaves through the TMA engine instead of the LSU.  Measured (profiles/r2h_s4_traverse_cfg2.md,
+// source page): the traversal is a pure 12.7 GB write stream per launch, and a warp's 512-byte STG.E.128 costs the L1
+// data pipe one wavefront per 32-byte sector (16 per instruction) -- 87 % of that pipe, the limiter ahead of HBM.  An
+// STS.128 costs 4.  So every node writes its vector to a shared-memory slot laid out as the byte image of the warp's
+// T32 tile (stk_at<WL>), and one elected lane hands the 32*BLOCK*8 bytes to cp.async.bulk.global.shared::cta.  The
+// slot IS the stack entry when a later node wants the vector (the host keeps it held), else it is free again at the
+// next node: the only wait is cp.async.bulk.wait_group.read at the top of the next store, a whole node later.
+// A consumer that re-reads a vector of this launch from HBM (stack full) first waits for the warp's copies to complete.
+template <int NCM, bool SAFE, bool SYM, int MINB = S4_MINB, bool BULK = false>
 __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __grid_constant__ S4Launch<NCM> P) {
     constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
     const TravArgs &a = P.a;
@@ -187,6 +205,9 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
     const bool valid = p < a.ntot;
     if (!valid) p = a.ntot - 1;  // the lane stays alive for the barriers; nothing is stored
     const size_t poff = (size_t)(p >> 5) * (32 * BLOCK) + (size_t)(p & 31) * 2;  // T32 layout
+    // BULK: does this warp own a whole 32-pattern tile?  (p0 is a multiple of 32; the one ragged warp of the grid stores
+    // lane by lane, a warp past the end stores nothing)
+    const bool warp_full = p0 + (tid | 31) < a.ntot;
     const bool invar0 = a.ptn_invar[p] == 0.0;
     double prev[BLOCK];
 #pragma unroll
@@ -225,6 +246,26 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
             __syncthreads();
         }
         unsigned sc = 0;
+        if (a.prefetch && i + 1 < a.nnodes) {
+            // The tip-child rows (one 128-byte line each, leaf table or state-pair table) miss L1 about every other time --
+            // shared memory leaves it ~40 KB and the CTAs of an SM are spread over the whole node list -- and the wait for
+            // them is the largest stall of the kernel (long scoreboard at the first use).  The next node's rows depend only
+            // on the staged tip states, so they are requested now and arrive while this node computes.  No register is held.
+            const PNode<NCM> &nx = P.nodes[i + 1];
+            const int ni = nx.info;
+            if ((ni >> 13) == 0) {  // same staged chunk
+                const double *row = nullptr, *row2 = nullptr;
+                if ((ni >> 12) & 1) {
+                    const int sa = st_buf[nx.lid * S4_THREADS + tid], sb = st_buf[nx.rid * S4_THREADS + tid];
+                    row = a.tt + (size_t)nx.ltab + (size_t)(sa * a.codes + sb) * BLOCK;
+                } else {
+                    if ((ni & 3) == SRC_LEAF) row = a.tables + nx.ltab + (size_t)st_buf[nx.lid * S4_THREADS + tid] * BLOCK;
+                    if (((ni >> 2) & 3) == SRC_LEAF) row2 = a.tables + nx.rtab + (size_t)st_buf[nx.rid * S4_THREADS + tid] * BLOCK;
+                }
+                if (row) asm volatile("prefetch.global.L1 [%0];" ::"l"(row));
+                if (row2) asm volatile("prefetch.global.L1 [%0];" ::"l"(row2));
+            }
+        }
         if (tt) {
             // tip-tip node: its vector depends on the two tip states only, and was computed for every state pair by
             // s4_tt_tables_kernel with this kernel's own arithmetic.  One row load instead of two, no FP64 work, never
@@ -240,8 +281,13 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
         } else {
         // both children's operands are requested before either is used: one memory latency per node
         double l[BLOCK], r[BLOCK];
-        child_load<NCM, SAFE>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
-        child_load<NCM, SAFE>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
+        if (BULK && (lk == SRC_GLOBAL || rk == SRC_GLOBAL)) {
+            // the vector may be one this warp handed to the copy engine earlier in this launch: complete, then read
+            if ((tid & 31) == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+            __syncwarp();
+        }
+        child_load<NCM, SAFE, BULK>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
+        child_load<NCM, SAFE, BULK>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
         if (lk != SRC_LEAF) child_apply<NCM, false, SYM>(P.mdl, nd.lexp, l, Ur);
         if (rk != SRC_LEAF) {
             if (lk == SRC_LEAF) child_apply<NCM, true, SYM>(P.mdl, nd.rexp, r, Ur);   // tip-internal: dotProductVec (:1853)
@@ -294,10 +340,36 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
         }
         }  // !tt
         prev_sc = sc;
-        if (valid) {
+        if (BULK) {
+            // every node of a BULK program has a slot (held as a stack entry or free again at the next node)
+            if ((tid & 31) == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // earlier copies have left shared memory
+            __syncwarp();
+            double2 *s = stk + stk_at<true, PAIRS>(out_stack, 0, tid);
+#pragma unroll
+            for (int j = 0; j < PAIRS; j++) s[j * 32] = make_double2(prev[2 * j], prev[2 * j + 1]);
+            stk_sc[out_stack * S4_THREADS + tid] = sc;
+            if (warp_full) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the copy engine
+                __syncwarp();
+                if ((tid & 31) == 0) {
+                    const double *g = a.partial + (size_t)nd.out_slot * a.slot_doubles + (size_t)((p0 + tid) >> 5) * (32 * BLOCK);
+                    const uint32_t src = (uint32_t)__cvta_generic_to_shared(s);
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g), "r"(src),
+                                 "r"(32 * BLOCK * 8)
+                                 : "memory");
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
+            } else if (valid) {
+                double2 *g = reinterpret_cast<double2 *>(a.partial + (size_t)nd.out_slot * a.slot_doubles + poff);
+#pragma unroll
+                for (int j = 0; j < PAIRS; j++) g[j * 32] = make_double2(prev[2 * j], prev[2 * j + 1]);
+            }
+        } else if (valid) {
             double2 *g = reinterpret_cast<double2 *>(a.partial + (size_t)nd.out_slot * a.slot_doubles + poff);
 #pragma unroll
             for (int j = 0; j < PAIRS; j++) g[j * 32] = make_double2(prev[2 * j], prev[2 * j + 1]);
+        }
+        if (valid) {
             uint8_t *gs = a.scale + (size_t)nd.out_slot * a.slot_scale_bytes;
             if (SAFE) {
 #pragma unroll
@@ -306,12 +378,15 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
                 gs[p] = (uint8_t)sc;
             }
         }
-        if (out_stack >= 0) {
+        if (!BULK && out_stack >= 0) {
 #pragma unroll
             for (int j = 0; j < PAIRS; j++)
                 stk[(out_stack * PAIRS + j) * S4_THREADS + tid] = make_double2(prev[2 * j], prev[2 * j + 1]);
             stk_sc[out_stack * S4_THREADS + tid] = sc;
         }
+    }
+    if (BULK) {  // shared memory must outlive the copies that read it
+        if ((tid & 31) == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
 }
 
@@ -581,7 +656,11 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     std::fill(producer.begin(), producer.end(), -1);
     std::vector<int> entry_of(count, -1);
     std::vector<int> free_list;
-    for (int e = max_depth - 1; e >= 0; e--) free_list.push_back(e);
+    // bulk-store kernel (SYM, one context): a ring of shared-memory slots, one per node output; a slot stays held as a
+    // stack entry only while another one is left to stage the next outputs (ring 3 = two stack entries + staging)
+    const bool bulk = !c->batch && c->s4_sym && b200_env().s4_bulk;
+    const int ring = b200_env().s4_ring > 0 ? b200_env().s4_ring : (c->max_stack_depth >= 0 ? c->max_stack_depth + 1 : 3);
+    for (int e = (bulk ? ring : max_depth) - 1; e >= 0; e--) free_list.push_back(e);
     int depth_used = 0;
     int32_t *leaf_seq = reinterpret_cast<int32_t *>(c->h_prog) + *seq_used;
     const int chunk = S4_STATE_BYTES / S4_THREADS;
@@ -652,7 +731,28 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         f.lid = id[0]; f.ltab = tab[0];
         f.rid = id[1]; f.rtab = tab[1];
         int out_stack = -1;
-        if (consumer[i] >= 0 && consumer[i] != i + 1 && !free_list.empty()) {
+        const bool wanted = consumer[i] >= 0 && consumer[i] != i + 1;
+        if (wanted && b200_env().s4_evict && free_list.size() <= (bulk ? 1u : 0u) && (bulk ? ring > 1 : max_depth > 0)) {
+            // Stack full.  Every vector is in HBM anyway, so dropping an entry costs nothing now and one re-read at its
+            // consumer: keep the vectors that are wanted soonest (Belady) -- the held one whose consumer is farthest away
+            // gives its entry up if this node's consumer comes first.  cfg2: 14 -> 5 re-reads per traversal with two
+            // entries, 43 -> 18 with one.
+            int far = -1;
+            for (int h = 0; h < i; h++)
+                if (entry_of[h] >= 0 && (far < 0 || consumer[h] > consumer[far])) far = h;
+            if (far >= 0 && consumer[far] > consumer[i]) {
+                free_list.push_back(entry_of[far]);
+                entry_of[far] = -1;
+                if (!bulk) P.nodes[far].info &= ~(0xff << 4);  // its push is no longer needed
+            }
+        }
+        if (bulk) {
+            out_stack = free_list.back();  // never empty: at most ring - 1 slots are held
+            free_list.pop_back();
+            if (wanted && !free_list.empty()) entry_of[i] = out_stack;
+            else free_list.insert(free_list.begin(), out_stack);  // staging only: free again, reused last
+            depth_used = std::max(depth_used, out_stack + 1);
+        } else if (wanted && !free_list.empty()) {
             out_stack = free_list.back();
             free_list.pop_back();
             entry_of[i] = out_stack;
@@ -728,6 +828,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     a.denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     a.tt = c->tt_tables;
     a.codes = codes;
+    a.prefetch = b200_env().s4_prefetch && !c->batch;
     fill_model<NCM>(c, P.mdl);
     const size_t smem = (size_t)depth_used * S4_THREADS * (2 * NCM * sizeof(double2) + sizeof(unsigned)) + S4_STATE_BYTES;
     const unsigned grid = (unsigned)(((c->batch ? c->batch->max_ntot : c->ntot) + S4_THREADS - 1) / S4_THREADS);
@@ -757,6 +858,15 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
             kern = one_class ? (safe ? s4_traverse_batch_kernel<NCM, true, true, 8> : s4_traverse_batch_kernel<NCM, false, true, 8>)
                              : (safe ? s4_traverse_batch_kernel<NCM, true, false, 8> : s4_traverse_batch_kernel<NCM, false, false, 8>);
         kern<<<g2, S4_THREADS, smem, c->stream>>>(P, *c->batch);
+    } else if (bulk) {
+        // ring 3 (29 KB per CTA): seven resident CTAs, the 128-register build; ring 2 (21 KB): ten, the 96-register one
+        const int minb = b200_env().s4_minb ? b200_env().s4_minb : (depth_used >= 3 ? 8 : S4_MINB);
+        const bool safe = c->d.safe_numeric != 0;
+        auto kern = safe ? s4_traverse_kernel<NCM, true, true, 8, true> : s4_traverse_kernel<NCM, false, true, 8, true>;
+        if (minb >= 10) kern = safe ? s4_traverse_kernel<NCM, true, true, 10, true> : s4_traverse_kernel<NCM, false, true, 10, true>;
+        if (minb <= 6) kern = safe ? s4_traverse_kernel<NCM, true, true, 6, true> : s4_traverse_kernel<NCM, false, true, 6, true>;
+        CUDA_TRY(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        kern<<<grid, S4_THREADS, smem, c->stream>>>(P);
     } else if (c->s4_sym) {
         // resident CTAs per SM the registers are sized for: 10 x 64 threads (96 registers, two stack entries) unless overridden
         const int minb = b200_env().s4_minb ? b200_env().s4_minb : S4_MINB;  // test / sweep hook: the 8- and 12-CTA instantiations

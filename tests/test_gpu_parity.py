@@ -115,13 +115,20 @@ def test_large_problem_properties():
 
 @pytest.mark.parametrize("env", [{"B200LK_LEVEL_BATCHED": "1"}, {"B200LK_STACK_DEPTH": "0"},
                                  {"B200LK_STACK_DEPTH": "1"}, {"B200LK_STACK_DEPTH": "3"}, {"B200LK_S4_SYM": "0"},
-                                 {"B200LK_S4_MINB": "8"}, {"B200LK_S4_MINB": "12", "B200LK_STACK_DEPTH": "1"}, {}])
+                                 {"B200LK_S4_MINB": "8"}, {"B200LK_S4_MINB": "12", "B200LK_STACK_DEPTH": "1"}, {},
+                                 {"B200LK_S4_PREFETCH": "1"}, {"B200LK_S4_EVICT": "0"}, {"B200LK_S4_EVICT": "0", "B200LK_STACK_DEPTH": "1"},
+                                 {"B200LK_S4_BULK": "1"},
+                                 {"B200LK_S4_BULK": "1", "B200LK_S4_RING": "1"}, {"B200LK_S4_BULK": "1", "B200LK_S4_RING": "2"},
+                                 {"B200LK_S4_BULK": "1", "B200LK_S4_RING": "4", "B200LK_S4_MINB": "6"}])
 @pytest.mark.parametrize("safe", [False, True])
 def test_dna_paths_agree_with_oracle(oracle_lib, monkeypatch, env, safe):
     """The 4-state traversal has three routes -- one pattern-stationary launch (default), the same with
     the shared-memory stack overflowing into global re-reads, and the level-batched kernels -- plus the
-    general (non-SYM) kernel and the other register-budget instantiations of the SYM one; all of them
-    must match the oracle, scale counts included (deep tree so that rescaling fires)."""
+    general (non-SYM) kernel and the other register-budget instantiations of the SYM one, with the L1 prefetch of
+    the next node's table rows, without the farthest-consumer replacement of stack entries, and with the node vectors leaving through cp.async.bulk (ring of 1 / 2 / 3 / 4
+    shared-memory slots) instead of the threads' stores; all of them must match the oracle, scale counts included
+    (deep tree so that rescaling fires).
+    The hooks are read when a context is created."""
     for k, v in env.items():
         monkeypatch.setenv(k, v)
     tree, model, rates, props, aln = make_problem(300, 300, seed=5, mean_len=0.4, gaps=0.02)
@@ -560,3 +567,32 @@ def test_tip_tip_state_pair_tables_change_no_bit(oracle_lib, safe, ncat, nmix):
         assert np.array_equal(big.fetch_scale_num(s)[:1000], small.fetch_scale_num(s))
     assert np.array_equal(rb["pattern_lh"][:1000], rs["pattern_lh"])
     assert_parity(rb, full_eval(o, tree, 0), TOL)
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("ncat", [1, 4])
+@pytest.mark.parametrize("nptn", [1000, 1017, 1056])  # whole tiles / a ragged last warp / a whole last warp + an empty one
+def test_bulk_store_changes_no_bit(oracle_lib, monkeypatch, safe, ncat, nptn):
+    """B200LK_S4_BULK=1: the node vectors of the SYM traversal leave through cp.async.bulk from a shared-memory image of
+    the warp's tile (s4_traverse_kernel<.., BULK>); the arithmetic is untouched, so every vector, scale count and pattern
+    likelihood must be bit-identical to the default build that stores from the threads (with and without the
+    farthest-consumer replacement of stack entries and the L1 prefetch, which change the order of memory operations only) -- also with a ring of one slot (every non-adjacent consumer re-reads what the copy engine wrote) and
+    when the pattern count leaves a ragged or an empty warp."""
+    tree, model, rates, props, aln = make_problem(120, nptn, ncat=ncat, seed=83, mean_len=0.3, gaps=0.05, compress=False)
+    res = {}
+    for tag, env in (("stg", {"B200LK_S4_EVICT": "0"}), ("evict", {}), ("prefetch", {"B200LK_S4_PREFETCH": "1"}), ("bulk", {"B200LK_S4_BULK": "1"}),
+                     ("ring1", {"B200LK_S4_BULK": "1", "B200LK_S4_RING": "1"})):
+        with monkeypatch.context() as m:
+            for k, v in env.items():
+                m.setenv(k, v)
+            g = engine_for(aln, model, rates, props, nslots=120, safe_numeric=safe)
+        r = full_eval(g, tree, 0)
+        res[tag] = (r, {s: (g.fetch_partial(s), g.fetch_scale_num(s)) for (_, _, s, _) in r["traversal"]})
+    (r0, v0) = res["stg"]
+    for tag in ("evict", "prefetch", "bulk", "ring1"):
+        r, v = res[tag]
+        for s in v0:
+            assert np.array_equal(v[s][0], v0[s][0]), (tag, s)
+            assert np.array_equal(v[s][1], v0[s][1]), (tag, s)
+        assert np.array_equal(r["pattern_lh"], r0["pattern_lh"])
+        assert r["lnl"] == r0["lnl"] and r["df"] == r0["df"] and r["ddf"] == r0["ddf"]
