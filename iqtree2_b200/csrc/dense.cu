@@ -585,31 +585,30 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
     for (int c0 = cbeg; c0 < cend; c0 += DN_CG) {
         const int cg = min(DN_CG, ncm - c0);
         __syncthreads();
-        if (Lleaf) {
-            const double *src = a.tables + L.leaf_off;
-            for (int i = tid; i < a.codes * cg * 20; i += DN_THREADS) {
-                const int s = i / (cg * 20), r = i - s * (cg * 20);
-                sL[i] = src[(size_t)s * block + c0 * 20 + r];
+        // The three tables of the group (<= 45 KB) go to shared memory as 16-byte cp.async copies: every copy of a
+        // thread is in flight at once and no register holds the data.  (The element-by-element loop this replaces had
+        // ONE load in flight per thread and iteration: 14 % of the kernel's stall samples sat on its stores,
+        // profiles/r2k_dense20_rp_cfg3_50k.md.)  All offsets are even numbers of doubles: rows of 20 * cg, fragments of 480.
+        auto stage_child = [&](const DevChild &ch, bool leaf, double *dst) {
+            if (leaf) {
+                const double *src = a.tables + ch.leaf_off + c0 * 20;
+                const int rowc = cg * 10;  // 16-byte chunks per state row
+                for (int i = tid; i < a.codes * rowc; i += DN_THREADS) {
+                    const int s = i / rowc, r = i - s * rowc;
+                    cp_async16(dst + (size_t)s * (cg * 20) + 2 * r, src + (size_t)s * block + 2 * r);
+                }
+            } else {
+                const double *src = a.tables + ch.frag_off + (size_t)c0 * B200_FRAG20;
+                for (int i = tid; i < cg * (B200_FRAG20 / 2); i += DN_THREADS) cp_async16(dst + 2 * i, src + 2 * i);
             }
-        } else {
-            const double *src = a.tables + L.frag_off + (size_t)c0 * B200_FRAG20;
-            for (int i = tid; i < cg * B200_FRAG20; i += DN_THREADS) sL[i] = src[i];
+        };
+        stage_child(L, Lleaf, sL);
+        stage_child(R, Rleaf, sR);
+        for (int i = tid; i < cg * (B200_FRAG20 / 2); i += DN_THREADS) {
+            const int cl = i / (B200_FRAG20 / 2), r = i - cl * (B200_FRAG20 / 2);
+            cp_async16(sI + (size_t)cl * B200_FRAG20 + 2 * r, a.inv_frag + (size_t)((c0 + cl) / a.denom) * B200_FRAG20 + 2 * r);
         }
-        if (Rleaf) {
-            const double *src = a.tables + R.leaf_off;
-            for (int i = tid; i < a.codes * cg * 20; i += DN_THREADS) {
-                const int s = i / (cg * 20), r = i - s * (cg * 20);
-                sR[i] = src[(size_t)s * block + c0 * 20 + r];
-            }
-        } else {
-            const double *src = a.tables + R.frag_off + (size_t)c0 * B200_FRAG20;
-            for (int i = tid; i < cg * B200_FRAG20; i += DN_THREADS) sR[i] = src[i];
-        }
-        for (int i = tid; i < cg * B200_FRAG20; i += DN_THREADS) {
-            const int cl = i / B200_FRAG20;
-            sI[i] = a.inv_frag[(size_t)((c0 + cl) / a.denom) * B200_FRAG20 + (i - cl * B200_FRAG20)];
-        }
-        __syncthreads();
+        cp_async_commit();
 
         const int nsteps = my_tiles * cg;
         // rows of the tile a step belongs to (clamped so that out-of-range rows read the last pattern)
@@ -624,28 +623,45 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
         };
         double AL[DN_MT][5], AR[DN_MT][5];
         int64_t p[DN_MT] = {}, pc[DN_MT] = {}, pn[DN_MT], pcn[DN_MT];
+        // per-tile inputs (tip states, invariant-site flag): requested one step before the tile starts, so that the
+        // first table lookup of a tile does not wait for them
+        int stL[DN_MT] = {}, stR[DN_MT] = {}, stLn[DN_MT] = {}, stRn[DN_MT] = {};
+        double invn[DN_MT] = {};
+        bool invar0[DN_MT] = {};
+        auto tile_inputs = [&](const int64_t (&rows)[DN_MT]) {
+#pragma unroll
+            for (int mt = 0; mt < DN_MT; mt++) {
+                invn[mt] = __ldg(a.ptn_invar + rows[mt]);
+                if (Lleaf) stLn[mt] = __ldg(a.states + (size_t)L.id * a.ntot_pad + rows[mt]);
+                if (Rleaf) stRn[mt] = __ldg(a.states + (size_t)R.id * a.ntot_pad + rows[mt]);
+            }
+        };
         if (nsteps > 0) {
             rows_of(0, pn, pcn);
             if (!Lleaf) dense_load_A(pL, block, c0, pcn, q, AL);
             if (!Rleaf) dense_load_A(pR, block, c0, pcn, q, AR);
+            tile_inputs(pcn);
         }
-        int stL[DN_MT] = {}, stR[DN_MT] = {};
-        bool invar0[DN_MT] = {};
+        cp_async_wait<0>();  // the tables; the first operands above stay in flight across the barrier
+        __syncthreads();
         unsigned long long rmax[DN_MT] = {};
         for (int step = 0; step < nsteps; step++) {
             const int t = step / cg, cl = step - t * cg, c = c0 + cl;
             const bool more = step + 1 < nsteps;
             const int cn = c0 + (more ? (step + 1) % cg : 0);
-            if (more) rows_of(step + 1, pn, pcn);
             if (cl == 0) {
                 rows_of(step, p, pc);
 #pragma unroll
                 for (int mt = 0; mt < DN_MT; mt++) {
-                    invar0[mt] = a.ptn_invar[pc[mt]] == 0.0;
-                    if (Lleaf) stL[mt] = a.states[(size_t)L.id * a.ntot_pad + pc[mt]];
-                    if (Rleaf) stR[mt] = a.states[(size_t)R.id * a.ntot_pad + pc[mt]];
+                    invar0[mt] = invn[mt] == 0.0;
+                    stL[mt] = stLn[mt];
+                    stR[mt] = stRn[mt];
                     rmax[mt] = 0ull;
                 }
+            }
+            if (more) {
+                rows_of(step + 1, pn, pcn);
+                if (cl == cg - 1) tile_inputs(pcn);  // the next step opens a tile
             }
             double fl[DN_MT][6], fr[DN_MT][6];
             if (Lleaf) dense_leaf_lookup(sL, cg, cl, stL, lane, fl);
@@ -721,24 +737,51 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
     }
     if (SAFE) return;
     __syncwarp();
-    for (int t = 0; t < a.tiles_per_cta; t++) {
-        const int64_t pbase = (tile0 + t) * DN_PT + warp * (8 * DN_MT);
-        if (pbase >= a.ntot) break;
+    if (a.split) {
+        for (int t = 0; t < a.tiles_per_cta; t++) {
+            const int64_t pbase = (tile0 + t) * DN_PT + warp * (8 * DN_MT);
+            if (pbase >= a.ntot) break;
+#pragma unroll
+            for (int mt = 0; mt < DN_MT; mt++) {
+                const int64_t pp = pbase + mt * 8 + g;
+                if (pp < a.ntot && q == 0)
+                    atomicMax(&a.pmax[(size_t)blockIdx.y * a.ntot + pp], smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g]);
+            }
+        }
+        return;
+    }
+    // NORM_LH decision per pattern.  Two phases, so that the scale counters of the children and the invariant-site flags
+    // of ALL the warp's patterns are in flight together (one dependent load chain per pattern left 5 % of the stall
+    // samples here); the children's counters are other slots than the one written.
+    int scsum[DN_MAX_TILES][DN_MT];
+    double inv[DN_MAX_TILES][DN_MT];
+#pragma unroll
+    for (int t = 0; t < DN_MAX_TILES; t++) {
 #pragma unroll
         for (int mt = 0; mt < DN_MT; mt++) {
-            const int64_t pp = pbase + mt * 8 + g;
-            if (pp >= a.ntot) continue;
-            if (a.split) {
-                if (q == 0) atomicMax(&a.pmax[(size_t)blockIdx.y * a.ntot + pp], smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g]);
-                continue;
+            const int64_t pp = (tile0 + t) * DN_PT + warp * (8 * DN_MT) + mt * 8 + g;
+            const bool on = t < a.tiles_per_cta && pp < a.ntot;
+            scsum[t][mt] = 0;
+            inv[t][mt] = 1.0;
+            if (on) {
+                scsum[t][mt] = (Lleaf ? 0 : (int)__ldg(scL + pp)) + (Rleaf ? 0 : (int)__ldg(scR + pp));
+                inv[t][mt] = __ldg(a.ptn_invar + pp);
             }
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < DN_MAX_TILES; t++) {
+#pragma unroll
+        for (int mt = 0; mt < DN_MT; mt++) {
+            const int64_t pp = (tile0 + t) * DN_PT + warp * (8 * DN_MT) + mt * 8 + g;
+            if (!(t < a.tiles_per_cta && pp < a.ntot)) continue;
             const double mx = __longlong_as_double((long long)smax[t * DN_PT + warp * (8 * DN_MT) + mt * 8 + g]);
-            const bool under = !tiptip && mx < B200_SCALING_THRESHOLD && a.ptn_invar[pp] == 0.0;
+            const bool under = !tiptip && mx < B200_SCALING_THRESHOLD && inv[t][mt] == 0.0;
             if (under) {
                 double *po = out_base + (size_t)pp * block;
                 for (int e = q; e < block; e += 4) po[e] *= B200_TWO_256;
             }
-            if (q == 0) sc_out[pp] = (uint8_t)((Lleaf ? 0 : scL[pp]) + (Rleaf ? 0 : scR[pp]) + (under ? 1 : 0));
+            if (q == 0) sc_out[pp] = (uint8_t)(scsum[t][mt] + (under ? 1 : 0));
         }
     }
 }
