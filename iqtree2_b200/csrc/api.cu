@@ -98,7 +98,9 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
         // a multifurcating node is its own launch in between (stream order keeps the dependencies)
         CUDA_TRY(c, cudaMemcpyAsync(c->d_children, c->h_children, sizeof(DevChild) * nchildren,
                                     cudaMemcpyHostToDevice, c->stream));
-        int rc = launch_tables(c, nchildren);
+        int rc = s4_before_update(c, nodes, nnodes, children);  // virtual tip-tip vectors this list reads or leaves alone
+        if (rc) return rc;
+        rc = launch_tables(c, nchildren);
         if (rc) return rc;
         bool any_multi = false;
         for (int i = 0; i < nnodes; i++) {
@@ -115,6 +117,18 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
         int prog_used = 0, seq_used = 0;
         c->s4_tt_used = 0;
         c->s4_ttdesc_used = 0;
+        // how many nodes of THIS list read each node's output (before its slot is rewritten): a tip-tip vector may stay
+        // virtual only if its single reader takes it from registers or the stack (s4.cu)
+        std::vector<int> last_writer(nslots, -1), nreaders(nnodes, 0);
+        for (int i = 0; i < nnodes; i++) {
+            for (int k = 0; k < nodes[i].nchild; k++) {
+                const b200lk_child &ch = children[nodes[i].child_begin + k];
+                if (ch.kind != B200LK_CHILD_LEAF && last_writer[ch.id] >= 0) nreaders[last_writer[ch.id]]++;
+            }
+            last_writer[nodes[i].out_slot] = i;
+        }
+        c->cur_nodes = nodes;
+        c->cur_nreaders = nreaders.data();
         for (int i = 0; i < nnodes;) {
             if (nodes[i].nchild > 2) {
                 rc = launch_partial_multi(c, i);
@@ -128,6 +142,8 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
             if (rc) return rc;
             i = j;
         }
+        c->cur_nodes = nullptr;
+        c->cur_nreaders = nullptr;
         CUDA_TRY(c, cudaEventRecord(c->stage_ev[ring], c->stream));
         c->stage_used[ring] = true;
         c->n_updates += (int64_t)nnodes * c->ntot;

@@ -147,8 +147,14 @@ static int with_batch(b200lk_batch *b, F body) {
 // a member may have work of its own calls still in flight on its own stream (model upload, a per-context update)
 static int wait_for_members(b200lk_batch *b) {
     if (b->pending) return B200LK_ERR_STATE;  // read the results of the evaluation in flight first
-    for (b200lk_ctx *c : b->ctx)
+    for (b200lk_ctx *c : b->ctx) {
+        // vectors a member's own 4-state traversal left virtual (s4.cu): the batched kernels read slots from HBM
+        if (int rc = s4_realize(c)) {
+            snprintf(b->err, sizeof(b->err), "%s", c->err);
+            return rc;
+        }
         if (c->stream != b->stream) BATCH_TRY(b, cudaStreamSynchronize(c->stream));
+    }
     return B200LK_OK;
 }
 

@@ -888,7 +888,11 @@ static int pick_group(int count) {  // largest power of two <= min(32, count)
     return G;
 }
 
-static void fill_args(b200lk_ctx *c, BranchArgs &a, b200lk_end dad, b200lk_end node) {
+static int fill_args(b200lk_ctx *c, BranchArgs &a, b200lk_end dad, b200lk_end node) {
+    // a slot the 4-state traversal left virtual (tip-tip vector, s4.cu) is gathered before a branch kernel reads it
+    if (int rc = s4_realize_slot(c, node.id)) return rc;
+    if (dad.kind != B200LK_CHILD_LEAF)
+        if (int rc = s4_realize_slot(c, dad.id)) return rc;
     memset(&a, 0, sizeof(a));
     a.pdad = slot_partial(c, node.id);
     a.sdad = slot_scale(c, node.id);
@@ -903,6 +907,7 @@ static void fill_args(b200lk_ctx *c, BranchArgs &a, b200lk_end dad, b200lk_end n
         a.snode = slot_scale(c, dad.id);
         a.slot_pnode = dad.id;
     }
+    return B200LK_OK;
 }
 
 static void fill_common(b200lk_ctx *c, BranchArgs &a) {
@@ -977,7 +982,7 @@ int launch_branch_lnl(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double len
     int rc = launch_val(c, length, dad.kind == B200LK_CHILD_LEAF);
     if (rc) return rc;
     BranchArgs a;
-    fill_args(c, a, dad, node);
+    if (int rc = fill_args(c, a, dad, node)) return rc;
     fill_common(c, a);
     a.len = length;
     a.G = pick_group(c->ncat_mix);
@@ -1007,7 +1012,7 @@ int launch_repair(b200lk_ctx *c) {
 int launch_theta(b200lk_ctx *c, b200lk_end dad, b200lk_end node) {
     if (c->nonrev) return nr_record_ends(c, dad, node);
     BranchArgs a;
-    fill_args(c, a, dad, node);
+    if (int rc = fill_args(c, a, dad, node)) return rc;
     fill_common(c, a);
     a.G = pick_group(c->block);
     int grid = grid_for(c, a.G, c->ntot);
@@ -1067,8 +1072,11 @@ int launch_newton(b200lk_ctx *c, const b200lk_newton *nr, const b200lk_end *ends
     }
     if (c->site) return B200LK_ERR_UNSUPPORTED;  // per-pattern coefficients: the host iteration drives b200lk_derv
     BranchArgs a;
-    if (fuse_theta) fill_args(c, a, ends[0], ends[1]);
-    else memset(&a, 0, sizeof(a));
+    if (fuse_theta) {
+        if (int rc = fill_args(c, a, ends[0], ends[1])) return rc;
+    } else {
+        memset(&a, 0, sizeof(a));
+    }
     fill_common(c, a);
     a.G = pick_group(c->block);
     NewtonArgs na;
@@ -1499,7 +1507,7 @@ int launch_eval_tail(b200lk_ctx *c, b200lk_end dad, b200lk_end node, double leng
         CUDA_TRY(c, cudaMemsetAsync(c->tail_counter, 0, sizeof(unsigned), c->stream));
     }
     BranchArgs a;
-    fill_args(c, a, dad, node);
+    if (int rc = fill_args(c, a, dad, node)) return rc;
     fill_common(c, a);
     a.len = length;
     a.G = 1;

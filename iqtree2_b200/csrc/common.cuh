@@ -85,6 +85,8 @@ struct ShardSet {
     std::vector<int64_t> begin, end;  // observed-pattern range [begin, end) of each shard (whole 32-pattern tiles)
 };
 
+struct S4Virt { int32_t slot, tt_off, ta, tb; };  // a virtual tip-tip vector: rows (state of taxon ta, state of taxon tb) of the table at tt_off
+
 // process-wide A/B and test hooks, read from the environment when a context is created (context.cu) -- never on a launch path
 struct B200Env {
     int s4_minb;       // B200LK_S4_MINB: resident-CTA instantiation of s4_traverse_kernel (8 / 10 / 12); 0 = default
@@ -95,8 +97,9 @@ struct B200Env {
     bool site_dmma;               // B200LK_SITE_DMMA=0 keeps the shuffle kernel for 20-state site models
     bool no_fused_tail;           // B200LK_NO_FUSED_TAIL=1: separate lnl / theta / derv launches in b200lk_evaluate*
     int batch_minb;               // B200LK_BATCH_MINB=2|8: force one build of s4_traverse_batch_kernel (A/B); 0 = per use
-    bool s4_tt;                   // B200LK_S4_TT=0: tip-tip nodes of the 4-state traversal computed, not looked up
+    int s4_tt;                    // B200LK_S4_TT=0: tip-tip nodes of the 4-state traversal computed, not looked up; 2: looked up at any size (tests)
     bool s4_bulk;                 // B200LK_S4_BULK=1: node vectors leave through cp.async.bulk instead of the threads' STG (slower: A/B log)
+    bool s4_virtual;              // B200LK_S4_VIRTUAL=0: every tip-tip vector is written by the traversal that computes it
     bool s4_evict;                // B200LK_S4_EVICT=0: a full stack keeps what it holds (first come) instead of the soonest-wanted vectors
     bool s4_prefetch;             // B200LK_S4_PREFETCH=1: L1 prefetch of the next node's tip-child table rows (slower: A/B log)
     int s4_ring;                  // B200LK_S4_RING: shared-memory slots of the bulk-store traversal (0 = default 3)
@@ -160,6 +163,11 @@ struct b200lk_ctx {
     double *tt_tables;  // 20-state path: per tip-tip node, the partial vector of every (left state, right state) pair
     size_t tt_cap;      // doubles
     size_t s4_ttdesc_used;  // 4-state path: tip-tip table descriptors staged for the traversal being enqueued
+    uint8_t *virt;          // 4-state path, host [nslots]: 1 = the slot's vector is virtual (s4.cu: s4_realize)
+    S4Virt *virt_desc;      // host [nslots]: where a virtual slot's rows are
+    int n_virtual;
+    const b200lk_node *cur_nodes;  // non-null only inside enqueue_update's 4-state branch: the caller's list ...
+    const int *cur_nreaders;       // ... and how many of its nodes read each node's output
     size_t s4_tt_used;  // 4-state path: doubles of tt_tables handed to the tip-tip nodes of the traversal being enqueued
     unsigned long long *pmax;  // mixture launches of dense.cu: per (node of the level, pattern) max|x| bits
     size_t pmax_bytes;
@@ -330,6 +338,9 @@ bool s4_detect_sym(const b200lk_ctx *c, double pi[4]);
 int launch_dense20(b200lk_ctx *c, int node_base, int nnodes);
 int launch_inv_frag(b200lk_ctx *c);
 int launch_tt_tables(b200lk_ctx *c, int nnodes);
+int s4_realize(b200lk_ctx *c);  // s4.cu: gather every virtual tip-tip vector into its slot (no-op when there is none)
+int s4_before_update(b200lk_ctx *c, const b200lk_node *nodes, int nnodes, const b200lk_child *children);
+static inline int s4_realize_slot(b200lk_ctx *c, int slot) { return (c->n_virtual && c->virt[slot]) ? s4_realize(c) : 0; }
 int launch_dense20_tt(b200lk_ctx *c, int node_base, int nnodes);
 int launch_denseN(b200lk_ctx *c, int node_base, int nnodes);
 int launch_site_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels);

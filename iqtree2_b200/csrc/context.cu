@@ -38,11 +38,13 @@ static B200Env read_env() {
         v = getenv("B200LK_BATCH_MINB");
         e.batch_minb = v ? atoi(v) : 0;  // 0: chosen per use
         v = getenv("B200LK_S4_TT");
-        e.s4_tt = !(v && *v == '0');
+        e.s4_tt = (v && *v == '0') ? 0 : ((v && *v == '2') ? 2 : 1);
         v = getenv("B200LK_S4_BULK");
         e.s4_bulk = v && *v == '1';
         v = getenv("B200LK_S4_PREFETCH");
         e.s4_prefetch = v && *v == '1';
+        v = getenv("B200LK_S4_VIRTUAL");
+        e.s4_virtual = !(v && *v == '0');
         v = getenv("B200LK_S4_EVICT");
         e.s4_evict = !(v && *v == '0');
         v = getenv("B200LK_S4_RING");
@@ -153,6 +155,11 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->d_result, sizeof(double) * 16));
     CUDA_TRY(c, cudaMemset(c->d_result, 0, sizeof(double) * 16));
     CUDA_TRY(c, cudaMallocHost(&c->h_result, sizeof(double) * 8));
+    if (c->tile == 32) {  // virtual tip-tip vectors of the 4-state traversal (s4.cu)
+        c->virt = (uint8_t *)calloc(d.nslots > 0 ? d.nslots : 1, 1);
+        c->virt_desc = (S4Virt *)calloc(d.nslots > 0 ? d.nslots : 1, sizeof(S4Virt));
+        if (!c->virt || !c->virt_desc) return B200LK_ERR_NOMEM;
+    }
     return noalloc_setup(c);  // once per device: where the static scratch of b200lk_lnl_from_buffer_noalloc lives
 }
 
@@ -252,6 +259,8 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (c->h_rell) cudaFreeHost(c->h_rell);
     if (c->pmax) cudaFree(c->pmax);
     if (c->tt_tables) cudaFree(c->tt_tables);
+    free(c->virt);
+    free(c->virt_desc);
     if (c->s_eval) cudaFree(c->s_eval);
     if (c->s_evec) cudaFree(c->s_evec);
     if (c->s_inv) cudaFree(c->s_inv);
@@ -390,6 +399,7 @@ extern "C" int b200lk_fetch_pattern_lh_cat(b200lk_ctx *c, double *out) {
 extern "C" int b200lk_fetch_scale_num(b200lk_ctx *c, int32_t slot, uint8_t *out) {
     SHARD_FORWARD(c, shard_fetch_scale_num(c, slot, out));
     if (!c || !out || slot < 0 || slot >= c->d.nslots) return B200LK_ERR_ARG;
+    if (int rc = s4_realize_slot(c, slot)) return rc;
     return d2h(c, out, slot_scale(c, slot), (size_t)c->d.nptn * c->scale_per_ptn);
 }
 // device layout -> the host's pattern-major [nptn][ncat_mix][nstates]
@@ -405,6 +415,7 @@ static int d2h_vector(b200lk_ctx *c, double *out, const double *dev) {
 extern "C" int b200lk_fetch_partial(b200lk_ctx *c, int32_t slot, double *out) {
     SHARD_FORWARD(c, shard_fetch_partial(c, slot, out));
     if (!c || !out || slot < 0 || slot >= c->d.nslots) return B200LK_ERR_ARG;
+    if (int rc = s4_realize_slot(c, slot)) return rc;
     return d2h_vector(c, out, slot_partial(c, slot));
 }
 extern "C" int b200lk_fetch_theta(b200lk_ctx *c, double *theta, double *bscale) {

@@ -40,7 +40,7 @@
 template <int NCM>
 struct PNode {
     int32_t out_slot;
-    int32_t info;        // lk | rk << 2 | (out_stack + 1) << 4 | tiptip_table << 12 | (refill + 1) << 13
+    int32_t info;        // lk | rk << 2 | (out_stack + 1) << 4 | tiptip_table << 12 | virtual << 13 | (refill + 1) << 14
     int32_t lid, rid;    // SRC_LEAF: row in the staged chunk; SRC_STACK: entry; SRC_GLOBAL: slot
     int32_t ltab, rtab;  // SRC_LEAF: offset (doubles) of the child's leaf lookup table in `tables`
     int32_t lexp_off, rexp_off;  // batched launches: offset (doubles) of the child's expv[c][i] in the context's tables
@@ -230,8 +230,11 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
     for (int i = 0; i < a.nnodes; i++) {
         const PNode<NCM> &nd = P.nodes[i];  // constant bank, uniform index
         const int info = nd.info;
-        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 13) - 1;
+        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 14) - 1;
         const bool tt = (info >> 12) & 1;
+        // a tip-tip vector that only this launch's next consumer needs (from registers or the stack) is not written at
+        // all: it stays "virtual" -- (table, two taxa) on the host -- until something else asks for the slot (s4_realize)
+        const bool store = valid && !((info >> 13) & 1);
         if (refill >= 0) {
             // stage the next chunk of tip-state rows of this CTA's pattern tile: all loads in flight at once
             __syncthreads();
@@ -253,7 +256,7 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
             // on the staged tip states, so they are requested now and arrive while this node computes.  No register is held.
             const PNode<NCM> &nx = P.nodes[i + 1];
             const int ni = nx.info;
-            if ((ni >> 13) == 0) {  // same staged chunk
+            if ((ni >> 14) == 0) {  // same staged chunk
                 const double *row = nullptr, *row2 = nullptr;
                 if ((ni >> 12) & 1) {
                     const int sa = st_buf[nx.lid * S4_THREADS + tid], sb = st_buf[nx.rid * S4_THREADS + tid];
@@ -348,7 +351,8 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
 #pragma unroll
             for (int j = 0; j < PAIRS; j++) s[j * 32] = make_double2(prev[2 * j], prev[2 * j + 1]);
             stk_sc[out_stack * S4_THREADS + tid] = sc;
-            if (warp_full) {
+            if (!store) {
+            } else if (warp_full) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the copy engine
                 __syncwarp();
                 if ((tid & 31) == 0) {
@@ -359,17 +363,17 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
                                  : "memory");
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 }
-            } else if (valid) {
+            } else {
                 double2 *g = reinterpret_cast<double2 *>(a.partial + (size_t)nd.out_slot * a.slot_doubles + poff);
 #pragma unroll
                 for (int j = 0; j < PAIRS; j++) g[j * 32] = make_double2(prev[2 * j], prev[2 * j + 1]);
             }
-        } else if (valid) {
+        } else if (store) {
             double2 *g = reinterpret_cast<double2 *>(a.partial + (size_t)nd.out_slot * a.slot_doubles + poff);
 #pragma unroll
             for (int j = 0; j < PAIRS; j++) g[j * 32] = make_double2(prev[2 * j], prev[2 * j + 1]);
         }
-        if (valid) {
+        if (store) {
             uint8_t *gs = a.scale + (size_t)nd.out_slot * a.slot_scale_bytes;
             if (SAFE) {
 #pragma unroll
@@ -422,6 +426,118 @@ __global__ void s4_tt_tables_kernel(const S4TTNode *__restrict__ nodes, const do
             out[k] = s4_tree(M + 4 * k, tmp);
         }
     }
+}
+
+// ---- virtual tip-tip vectors ---------------------------------------------------------------------------------------
+// A tip-tip node's vector is row (state a, state b) of its state-pair table.  When the only reader inside the launch takes
+// it from registers or the stack, s4_traverse_kernel does not write it (a third of the HBM traffic of a cfg2 traversal:
+// 65 of 198 nodes); the slot is then "virtual": the host keeps (table offset, taxon a, taxon b).  Whoever else needs the
+// slot -- a branch-level kernel, a later traversal that reads it or rebuilds the tables, a host reader, the batched and
+// sweep paths -- calls s4_realize first, which gathers ALL virtual slots from the tables that are still in place: the same
+// rows the traversal would have stored, so no result changes by a bit.
+#define S4_VIRT_PER_LAUNCH 120
+struct S4RealizeArgs {
+    const double *tt;
+    const uint8_t *states;
+    double *partial;
+    uint8_t *scale;
+    size_t slot_doubles, slot_scale_bytes;
+    int64_t ntot, ntot_pad;
+    int codes;
+    S4Virt v[S4_VIRT_PER_LAUNCH];
+};
+template <int NCM, bool SAFE>
+__global__ void __launch_bounds__(256) s4_realize_kernel(const __grid_constant__ S4RealizeArgs a) {
+    constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
+    const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (p >= a.ntot) return;
+    const S4Virt &v = a.v[blockIdx.y];
+    const int sa = a.states[(size_t)v.ta * a.ntot_pad + p], sb = a.states[(size_t)v.tb * a.ntot_pad + p];
+    const double2 *row = reinterpret_cast<const double2 *>(a.tt + (size_t)v.tt_off + (size_t)(sa * a.codes + sb) * BLOCK);
+    const size_t poff = (size_t)(p >> 5) * (32 * BLOCK) + (size_t)(p & 31) * 2;  // T32 layout
+    double2 *g = reinterpret_cast<double2 *>(a.partial + (size_t)v.slot * a.slot_doubles + poff);
+#pragma unroll
+    for (int j = 0; j < PAIRS; j++) g[j * 32] = __ldg(row + j);
+    uint8_t *gs = a.scale + (size_t)v.slot * a.slot_scale_bytes;  // a tip-tip node is never rescaled (:1640)
+    if (SAFE) {
+#pragma unroll
+        for (int c = 0; c < NCM; c++) gs[p * NCM + c] = 0;
+    } else {
+        gs[p] = 0;
+    }
+}
+
+template <int NCM>
+static int realize_run(b200lk_ctx *c) {
+    static thread_local S4RealizeArgs *Ap = nullptr;
+    if (!Ap) Ap = new S4RealizeArgs();
+    S4RealizeArgs &a = *Ap;
+    a.tt = c->tt_tables;
+    a.states = c->states;
+    a.partial = c->partial;
+    a.scale = c->scale;
+    a.slot_doubles = c->slot_doubles;
+    a.slot_scale_bytes = c->slot_scale_bytes;
+    a.ntot = c->ntot;
+    a.ntot_pad = c->ntot_pad;
+    a.codes = c->d.n_state_codes;
+    const unsigned gx = (unsigned)((c->ntot + 255) / 256);
+    int n = 0, total = 0;
+    auto flush = [&]() -> int {
+        if (!n) return B200LK_OK;
+        if (c->d.safe_numeric) s4_realize_kernel<NCM, true><<<dim3(gx, n), 256, 0, c->stream>>>(a);
+        else s4_realize_kernel<NCM, false><<<dim3(gx, n), 256, 0, c->stream>>>(a);
+        CUDA_TRY(c, cudaGetLastError());
+        c->n_launches++;
+        total += n;
+        n = 0;
+        return B200LK_OK;
+    };
+    for (int s = 0; s < c->d.nslots; s++) {
+        if (!c->virt[s]) continue;
+        a.v[n++] = c->virt_desc[s];
+        c->virt[s] = 0;
+        if (n == S4_VIRT_PER_LAUNCH) {
+            int rc = flush();
+            if (rc) return rc;
+        }
+    }
+    int rc = flush();
+    if (rc) return rc;
+    c->n_virtual = 0;
+    c->n_min_bytes += c->ntot * (8 * (int64_t)c->block + c->scale_per_ptn) * total;  // what the traversal had left out
+    return B200LK_OK;
+}
+
+int s4_realize(b200lk_ctx *c) {
+    if (!c->n_virtual) return B200LK_OK;
+    CUDA_TRY(c, cudaSetDevice(c->device));
+    switch (c->ncat_mix) {
+        case 1: return realize_run<1>(c);
+        case 2: return realize_run<2>(c);
+        case 3: return realize_run<3>(c);
+        default: return realize_run<4>(c);
+    }
+}
+
+// Before a traversal is enqueued (it rebuilds the state-pair tables): a virtual slot that the new list overwrites without
+// reading it first is simply forgotten; every other one is gathered now, while its table is still there.
+int s4_before_update(b200lk_ctx *c, const b200lk_node *nodes, int nnodes, const b200lk_child *children) {
+    if (!c->n_virtual) return B200LK_OK;
+    std::vector<char> written(c->d.nslots, 0), read_first(c->d.nslots, 0);
+    for (int i = 0; i < nnodes; i++) {
+        for (int k = 0; k < nodes[i].nchild; k++) {
+            const b200lk_child &ch = children[nodes[i].child_begin + k];
+            if (ch.kind != B200LK_CHILD_LEAF && !written[ch.id]) read_first[ch.id] = 1;
+        }
+        written[nodes[i].out_slot] = 1;
+    }
+    for (int s = 0; s < c->d.nslots; s++)
+        if (c->virt[s] && written[s] && !read_first[s]) {
+            c->virt[s] = 0;
+            c->n_virtual--;
+        }
+    return s4_realize(c);
 }
 
 // ---- batched variant: one launch for all 4-state contexts of a supermatrix (grid.y = context) -----------------------
@@ -499,7 +615,7 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_batch_kernel(con
     for (int i = 0; i < a.nnodes; i++) {
         const PNode<NCM> &nd = P.nodes[i];
         const int info = nd.info;
-        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 13) - 1;
+        const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 14) - 1;
         if (refill >= 0) {
             __syncthreads();
             constexpr int VPR = S4_THREADS / 16;
@@ -682,8 +798,11 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     // tip-tip nodes answered from a per-node state-pair table (s4_tt_tables_kernel): worth it when there are clearly
     // more patterns than state pairs
     const int codes = c->d.n_state_codes;
-    const bool use_tt = !c->batch && b200_env().s4_tt && (int64_t)codes * codes * 4 <= c->ntot;
+    const bool use_tt = !c->batch && b200_env().s4_tt && (b200_env().s4_tt == 2 || (int64_t)codes * codes * 4 <= c->ntot);
     const size_t tt_doubles = (size_t)codes * codes * NCM * 4;
+    const bool virt_ok = use_tt && b200_env().s4_virtual && c->virt && c->cur_nreaders;
+    const int *nreaders = virt_ok ? c->cur_nreaders + (nl - c->cur_nodes) : nullptr;  // of this segment's nodes, over the whole list
+    std::vector<int> tip_a(count, -1), tip_b(count, -1);  // taxa of the two tips of a tip-tip node
     std::vector<S4TTNode> tt_nodes;
     std::vector<const DevChild *> exp_src(2 * (size_t)count, nullptr);
     for (int i = 0; i < count; i++) {
@@ -716,10 +835,12 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
                 const int pr = producer[ch.id];
                 if (pr >= 0 && consumer[pr] == i && pr == i - 1) {
                     kind[k] = SRC_PREV; id[k] = 0;
+                    if (virt_ok && nreaders[pr] == 1 && ((P.nodes[pr].info >> 12) & 1)) P.nodes[pr].info |= 1 << 13;  // tip-tip, read from registers: not stored
                 } else if (pr >= 0 && consumer[pr] == i && entry_of[pr] >= 0) {
                     kind[k] = SRC_STACK; id[k] = entry_of[pr];
                     free_list.push_back(entry_of[pr]);
                     entry_of[pr] = -1;
+                    if (virt_ok && nreaders[pr] == 1 && ((P.nodes[pr].info >> 12) & 1)) P.nodes[pr].info |= 1 << 13;  // ... or from the stack
                 } else {
                     kind[k] = SRC_GLOBAL; id[k] = ch.id;
                     // produced by an EARLIER launch (or call): a DRAM read.  A vector of this launch that no longer
@@ -762,13 +883,30 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         if (use_tt && kind[0] == SRC_LEAF && kind[1] == SRC_LEAF && c->s4_tt_used + tt_doubles <= (size_t)INT32_MAX) {
             S4TTNode tn = {tab[0], tab[1], (int32_t)c->s4_tt_used, 0};
             tt_nodes.push_back(tn);
+            tip_a[i] = c->h_children[nl[i].child_begin + order[0]].id;
+            tip_b[i] = c->h_children[nl[i].child_begin + order[1]].id;
             f.ltab = (int32_t)c->s4_tt_used;
             c->s4_tt_used += tt_doubles;
             tt = 1;
         }
-        f.info = kind[0] | kind[1] << 2 | (out_stack + 1) << 4 | tt << 12 | (refill + 1) << 13;
+        f.info = kind[0] | kind[1] << 2 | (out_stack + 1) << 4 | tt << 12 | (refill + 1) << 14;  // bit 13 (virtual) is set by the consumer
         producer[nl[i].out_slot] = i;
     }
+    // which slots this launch leaves virtual (the last writer of a slot decides)
+    int nvirtual = 0;
+    if (c->virt)
+        for (int i = 0; i < count; i++) {
+            const int slot = nl[i].out_slot;
+            const bool v = (P.nodes[i].info >> 13) & 1;
+            if (c->virt[slot] && !v) c->n_virtual--;
+            if (!c->virt[slot] && v) c->n_virtual++;
+            c->virt[slot] = v;
+            if (v) {
+                const S4Virt d = {slot, P.nodes[i].ltab, tip_a[i], tip_b[i]};
+                c->virt_desc[slot] = d;
+                nvirtual++;
+            }
+        }
     // the per-child factors: 16 exp() per internal child, ~6000 for a cfg2 traversal -- what a blocking evaluation spends
     // most of its host time on, so a few threads share it (the calling thread alone for short lists)
     {
@@ -845,7 +983,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     }
     if (!c->batch) {
         const int64_t vec_bytes = 8 * (int64_t)c->block + c->scale_per_ptn;
-        c->n_min_bytes += c->ntot * (vec_bytes * (count + cross_reads) + nseq);
+        c->n_min_bytes += c->ntot * (vec_bytes * (count - nvirtual + cross_reads) + nseq);
     }
     prof_mark(c);
     if (c->batch) {

@@ -596,3 +596,86 @@ def test_bulk_store_changes_no_bit(oracle_lib, monkeypatch, safe, ncat, nptn):
             assert np.array_equal(v[s][1], v0[s][1]), (tag, s)
         assert np.array_equal(r["pattern_lh"], r0["pattern_lh"])
         assert r["lnl"] == r0["lnl"] and r["df"] == r0["df"] and r["ddf"] == r0["ddf"]
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("ncat", [1, 4])
+def test_virtual_tip_tip_vectors_change_no_bit(oracle_lib, monkeypatch, safe, ncat):
+    """A tip-tip vector that the traversal's next consumer takes from registers or the stack is not written by
+    s4_traverse_kernel: the slot stays virtual until something else needs it (s4_realize gathers it from the state-pair
+    table).  Every slot, scale count and result must be bit-identical to the build that writes everything
+    (B200LK_S4_VIRTUAL=0) -- read back right after the traversal, after a second traversal with other branch lengths,
+    and after a partial re-traversal whose children outside the list are virtual slots."""
+    monkeypatch.setenv("B200LK_S4_TT", "2")
+    tree, model, rates, props, aln = make_problem(60, 1500, ncat=ncat, seed=29, mean_len=0.25, gaps=0.05, compress=False)
+    out = {}
+    for tag, env in (("real", {"B200LK_S4_VIRTUAL": "0"}), ("virtual", {})):
+        with monkeypatch.context() as m:
+            for k, v in env.items():
+                m.setenv(k, v)
+            g = engine_for(aln, model, rates, props, nslots=60, safe_numeric=safe)
+        t = W.Tree.from_newick(tree.to_newick(), aln.names)  # a private copy: the lengths change below
+        c = t.adj[0][0]
+        snaps = []
+        r = full_eval(g, t, 0)
+        tr = r["traversal"]
+        assert sum(1 for e in tr if all(ch[0] == LEAF for ch in e[3])) >= 8
+        snaps.append((r["lnl"], r["df"], r["ddf"], r["pattern_lh"], {s: (g.fetch_partial(s), g.fetch_scale_num(s)) for (_, _, s, _) in tr}))
+        # second traversal, other lengths: every virtual slot is overwritten, nothing is gathered
+        for (u, v) in list(t.branches()):
+            t.set_length(u, v, 0.7 * t.get_length(u, v) + 0.01)
+        g.update_partials(W.traversal(t, c, 0))
+        # partial re-traversal: the last five nodes; their other children (virtual tip-tip slots among them) stay resident
+        tail = W.traversal(t, c, 0)[-5:]
+        t.set_length(tail[0][0], tail[0][1], 0.33)
+        tr2 = W.traversal(t, c, 0)[-5:]
+        g.update_partials(tr2)
+        lnl = g.branch_lnl((LEAF, 0), (INTERNAL, tr2[-1][2]), t.get_length(0, c))
+        snaps.append((lnl, g.fetch_pattern_lh(), {s: (g.fetch_partial(s), g.fetch_scale_num(s)) for (_, _, s, _) in tr}))
+        out[tag] = snaps
+    a, b = out["real"], out["virtual"]
+    assert a[0][0] == b[0][0] and a[0][1] == b[0][1] and a[0][2] == b[0][2]
+    assert np.array_equal(a[0][3], b[0][3])
+    for s in a[0][4]:
+        assert np.array_equal(a[0][4][s][0], b[0][4][s][0]) and np.array_equal(a[0][4][s][1], b[0][4][s][1]), s
+    assert a[1][0] == b[1][0] and np.array_equal(a[1][1], b[1][1])
+    for s in a[1][2]:
+        assert np.array_equal(a[1][2][s][0], b[1][2][s][0]) and np.array_equal(a[1][2][s][1], b[1][2][s][1]), s
+
+
+def test_virtual_slot_read_by_a_branch_kernel(oracle_lib, monkeypatch):
+    """lnL and Newton-Raphson on the branch ABOVE a tip-tip node right after the traversal that left it virtual: the
+    branch kernels gather the slot first (fill_args -> s4_realize) and agree with the oracle."""
+    monkeypatch.setenv("B200LK_S4_TT", "2")
+    names = list("ABCDEF")
+    t = W.Tree.from_newick("((A:0.1,B:0.2):0.15,(C:0.1,D:0.3):0.05,(E:0.2,F:0.1):0.3);", names)
+    model = W.gtr_model()
+    rates, props = W.discrete_gamma(0.7)
+    aln = W.simulate_alignment(W.random_tree(6, 4), model, rates, props, 700, 11, compress=False)
+    aln.names = names
+    g, o = both(aln, model, rates, props, nslots=12)
+    root = [u for u in range(t.nnodes) if not t.is_leaf(u) and sum(1 for w in t.adj[u] if not t.is_leaf(w)) == 3][0]
+    kids = t.adj[root]
+    # slots: cherry k -> slot k (seen from the root), root seen from cherry 0 -> slot 5 (children: cherries 1 and 2)
+    cherries = []
+    for k, v in enumerate(kids):
+        leaves = [w for w in t.adj[v] if w != root]
+        cherries.append((v, root, k, [(LEAF, w, t.get_length(v, w)) for w in leaves]))
+    top = (root, kids[0], 5, [(INTERNAL, 1, t.get_length(root, kids[1])), (INTERNAL, 2, t.get_length(root, kids[2]))])
+    top1 = (root, kids[1], 6, [(INTERNAL, 0, t.get_length(root, kids[0])), (INTERNAL, 2, t.get_length(root, kids[2]))])
+    tr = cherries + [top, top1]
+    L = t.get_length(root, kids[0])
+    for e in (g, o):
+        e.update_partials(tr)
+    # cherry 2 (slot 2) has two readers in the list: stored.  Cherries 0 and 1 have one reader each, which takes them from
+    # the stack: virtual.  The branch kernels below read slot 0.
+    a = g.branch_lnl((INTERNAL, 5), (INTERNAL, 0), L)
+    b = o.branch_lnl((INTERNAL, 5), (INTERNAL, 0), L)
+    assert rel(a, b) <= TOL
+    a = g.branch_lnl((INTERNAL, 0), (INTERNAL, 5), L)
+    assert rel(a, b) <= TOL
+    L1 = t.get_length(root, kids[1])
+    assert rel(g.branch_lnl((INTERNAL, 6), (INTERNAL, 1), L1), o.branch_lnl((INTERNAL, 6), (INTERNAL, 1), L1)) <= TOL
+    for s in (0, 1, 2, 5, 6):
+        assert rel(g.fetch_partial(s), o.fetch_partial(s)) <= TOL
+        assert np.array_equal(g.fetch_scale_num(s), o.fetch_scale_num(s))
