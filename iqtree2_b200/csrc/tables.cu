@@ -27,20 +27,25 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
     // reads what the same category produced, so the CTA-local barriers stay sufficient
     const int cpc = (ncm + gridDim.z - 1) / gridDim.z, c0 = blockIdx.z * cpc, c1 = min(ncm, c0 + cpc);
     if (c0 >= c1) return;
+    // expv[c][i] = exp(eval[m][i] * rate * len): ONE exp() per (category, eigenvalue) -- n of them per category, not the
+    // n * n of echild's elements (supermatrix batches spent 11 % of a step on those, profiles/launches_cfg5_r1t.csv).
+    // Also what the 4-state path reads per child (s4.cu).  <= 16 categories per CTA (launch_tables), n <= 64.
+    __shared__ double s_expv[16 * 64];
+    double *expv = echild + (size_t)block * n;
+    for (int idx = c0 * n + threadIdx.x; idx < c1 * n; idx += blockDim.x) {
+        int c = idx / n, i = idx - c * n;
+        // heterotachy: child->getLength(cat_id[c]) (:1017, 1069), one length per category
+        const double e = exp(m.eval[(c / denom) * n + i] *
+                             (m.rates[c % ncat] * (mixlen ? mixlen[(size_t)ch.src * ncat + c % ncat] : ch.length)));
+        expv[idx] = e;
+        s_expv[idx - c0 * n] = e;
+    }
+    __syncthreads();
     // phase 1: echild
     for (int idx = c0 * nn + threadIdx.x; idx < c1 * nn; idx += blockDim.x) {
         int c = idx / nn, r = idx - c * nn, i = r % n;
         int mm = c / denom;
-        // heterotachy: child->getLength(cat_id[c]) (:1017, 1069), one length per category
-        double len_child = m.rates[c % ncat] * (mixlen ? mixlen[(size_t)ch.src * ncat + c % ncat] : ch.length);
-        echild[idx] = m.evec[(size_t)mm * nn + r] * exp(m.eval[mm * n + i] * len_child);
-    }
-    // expv[c][i] = exp(eval[m][i] * rate * len): what the 4-state path reads per child (s4.cu)
-    double *expv = echild + (size_t)block * n;
-    for (int idx = c0 * n + threadIdx.x; idx < c1 * n; idx += blockDim.x) {
-        int c = idx / n, i = idx - c * n;
-        expv[idx] = exp(m.eval[(c / denom) * n + i] *
-                        (m.rates[c % ncat] * (mixlen ? mixlen[(size_t)ch.src * ncat + c % ncat] : ch.length)));
+        echild[idx] = m.evec[(size_t)mm * nn + r] * s_expv[(c - c0) * n + i];
     }
     if (ch.frag_off >= 0) {
         // tensor paths (dense.cu: 3 n-tiles x 5 k-steps for 20 states; densen.cu: NT x 2NT): echild as the B operand
@@ -85,7 +90,7 @@ int launch_tables(b200lk_ctx *c, int nchildren) {
     memset(&bl, 0, sizeof(bl));
     if (c->batch) bl = *c->batch;
     bl.d_lens = c->cur_len_slots ? c->d_lens : nullptr;
-    const int zsplit = std::min(64, (c->ncat_mix + 15) / 16);  // <= 16 categories per CTA
+    const int zsplit = (c->ncat_mix + 15) / 16;  // <= 16 categories per CTA (the size of its shared exp() table)
     tables_kernel<<<dim3(nchildren, c->batch ? c->batch->n : 1, zsplit), 256, 0, c->stream>>>(
         c->d_children, c->m, c->tables, c->d.nstates, c->d.ncat, c->ncat_mix, denom, c->d.nmix, c->d.n_state_codes,
         c->dense20 ? 3 : c->dense_nt, c->dense20 ? 5 : 2 * c->dense_nt,
