@@ -63,6 +63,7 @@ struct TravArgs {
     size_t slot_doubles, slot_scale_bytes;
     int64_t ntot, ntot_pad;
     int nnodes, depth, chunk, denom, codes;
+    int nchunks;   // staged tip-state chunks of this launch (s4_traverse_kernel fetches chunk k + 1 while chunk k is in use)
     int prefetch;  // 1: the table rows of the NEXT node's tip children are pulled into L1 while this node computes
 };
 
@@ -198,9 +199,28 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
     // [depth][PAIRS][S4_THREADS] double2 | unsigned [depth][S4_THREADS] scale | uint8 [chunk][S4_THREADS] tip states
     extern __shared__ double2 stk[];
     unsigned *stk_sc = reinterpret_cast<unsigned *>(stk + (size_t)a.depth * PAIRS * S4_THREADS);
-    uint8_t *st_buf = reinterpret_cast<uint8_t *>(stk_sc + (size_t)a.depth * S4_THREADS);
+    uint8_t *st_base = reinterpret_cast<uint8_t *>(stk_sc + (size_t)a.depth * S4_THREADS);
+    const uint8_t *st_buf = st_base;  // the half of the staging buffer the current chunk lives in
     const int tid = threadIdx.x;
     const int64_t p0 = (int64_t)blockIdx.x * S4_THREADS;
+    // Tip states are staged chunk by chunk (a.chunk rows x S4_THREADS patterns) into the two halves of the buffer: chunk
+    // k + 1 is fetched with cp.async while the nodes of chunk k run, so a refill is one barrier with nothing to wait for.
+    // (Fetched at the refill itself it was two dependent global round trips -- taxon id, then its states -- taken by the
+    // whole CTA between two barriers: 12 % of the stall samples, profiles/r2n_s4_traverse_cfg2.md.)
+    auto fetch_chunk = [&](int k) {
+        constexpr int VPR = S4_THREADS / 16;
+        const int nvec = a.chunk * VPR;
+        const int32_t *seq = a.leaf_seq + (size_t)k * a.chunk;
+        uint8_t *dst = st_base + (size_t)(k & 1) * a.chunk * S4_THREADS;
+        for (int v = tid; v < nvec; v += S4_THREADS) {
+            const int row = v / VPR, q = v - row * VPR;
+            const uint8_t *src = a.states + (size_t)__ldg(seq + row) * a.ntot_pad + p0 + 16 * q;
+            const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst + 16 * v);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if (a.nchunks > 0) fetch_chunk(0);
     int64_t p = p0 + tid;
     const bool valid = p < a.ntot;
     if (!valid) p = a.ntot - 1;  // the lane stays alive for the barriers; nothing is stored
@@ -236,17 +256,12 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
         // all: it stays "virtual" -- (table, two taxa) on the host -- until something else asks for the slot (s4_realize)
         const bool store = valid && !((info >> 13) & 1);
         if (refill >= 0) {
-            // stage the next chunk of tip-state rows of this CTA's pattern tile: all loads in flight at once
+            // chunk `refill` was requested a chunk ago: complete this thread's copies, then the barrier makes everybody's
+            // visible and says that nobody reads the other half any more -- which chunk refill + 1 may now overwrite
+            asm volatile("cp.async.wait_all;" ::: "memory");
             __syncthreads();
-            constexpr int VPR = S4_THREADS / 16;
-            const int nvec = a.chunk * VPR;
-            const int32_t *seq = a.leaf_seq + (size_t)refill * a.chunk;
-            for (int v = tid; v < nvec; v += S4_THREADS) {
-                const int row = v / VPR, q = v - row * VPR;
-                const uint4 *src = reinterpret_cast<const uint4 *>(a.states + (size_t)seq[row] * a.ntot_pad + p0) + q;
-                reinterpret_cast<uint4 *>(st_buf)[v] = __ldg(src);
-            }
-            __syncthreads();
+            st_buf = st_base + (size_t)(refill & 1) * a.chunk * S4_THREADS;
+            if (refill + 1 < a.nchunks) fetch_chunk(refill + 1);
         }
         unsigned sc = 0;
         if (a.prefetch && i + 1 < a.nnodes) {
@@ -779,7 +794,8 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     for (int e = (bulk ? ring : max_depth) - 1; e >= 0; e--) free_list.push_back(e);
     int depth_used = 0;
     int32_t *leaf_seq = reinterpret_cast<int32_t *>(c->h_prog) + *seq_used;
-    const int chunk = S4_STATE_BYTES / S4_THREADS;
+    // rows per staged chunk: the whole buffer for the batched kernel, half of it for s4_traverse_kernel (two halves in turn)
+    const int chunk = c->batch ? S4_STATE_BYTES / S4_THREADS : S4_STATE_BYTES / S4_THREADS / 2;
     int nseq = 0;
     int64_t cross_reads = 0;
     // staged tip-state rows of this segment: its leaf children plus at most one pad row per node (a node never
@@ -963,6 +979,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     a.nnodes = count;
     a.depth = depth_used;
     a.chunk = chunk;
+    a.nchunks = (nseq + chunk - 1) / chunk;
     a.denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     a.tt = c->tt_tables;
     a.codes = codes;
