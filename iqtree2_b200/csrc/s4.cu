@@ -26,6 +26,8 @@
 //    judged at 1e-9; a scale count could flip only if max|x| were within ~1e-15 relative of 2^-256).
 //  * NORM_LH takes the max over the whole block in-thread; SAFE_LH keeps one counter per category, packed
 //    four to a word.
+#include <omp.h>
+
 #include "common.cuh"
 
 #define SRC_LEAF 0    // id = row of the staged tip-state chunk
@@ -927,7 +929,10 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     // most of its host time on, so a few threads share it (the calling thread alone for short lists)
     {
         const int nexp = 2 * count;
-#pragma omp parallel for schedule(static) num_threads(4) if (nexp >= 64)
+        // at most four threads, and never more than OMP_NUM_THREADS allows: torchrun sets it to 1 for every rank, and eight
+        // ranks forking four workers each onto the same pinned cores cost 70 ms per step instead of saving 0.03
+        const int nthr = std::min(4, omp_get_max_threads());
+#pragma omp parallel for schedule(static) num_threads(nthr) if (nexp >= 64 && nthr > 1)
         for (int j = 0; j < nexp; j++)
             if (exp_src[j]) fill_expv<NCM>(c, *exp_src[j], (j & 1) ? P.nodes[j >> 1].rexp : P.nodes[j >> 1].lexp);
     }
