@@ -35,24 +35,19 @@
 #define SRC_GLOBAL 2  // id = slot: resident partial vector
 #define SRC_PREV 3    // the node computed immediately before (still in registers)
 
-// One node of the device program.  The program, the per-child factors expv[c][i] = exp(lambda_i r_c t)
-// and the eigenvectors travel as KERNEL PARAMETERS: they sit in the constant bank, are read through the
-// uniform datapath (LDCU -> uniform registers -> operands of DFMA/DMUL) and never touch L1, shared
-// memory or a vector register.  A launch carries at most S4_MAXN nodes (parameter space is 32 KB).
-template <int NCM>
+// One node of the device program: 32 bytes.  The program, the per-child factors expv[c][i] = exp(lambda_i r_c t) and
+// the eigenvectors travel as KERNEL PARAMETERS: they sit in the constant bank, are read through the uniform datapath
+// (LDCU -> uniform registers -> operands of DFMA/DMUL) and never touch L1, shared memory or a vector register.
+// The factors are a separate packed array, one block of NCM * 4 doubles per INTERNAL child (a tip child needs none), so a
+// launch carries as many nodes as 32 * nodes + 8 * NCM * 4 * internal children + the model fit the 32 KB parameter window:
+// all 198 nodes of cfg2 (31.8 KB), where a fixed 288-byte node took two launches of <= 107.
 struct PNode {
     int32_t out_slot;
     int32_t info;        // lk | rk << 2 | (out_stack + 1) << 4 | tiptip_table << 12 | virtual << 13 | (refill + 1) << 14
     int32_t lid, rid;    // SRC_LEAF: row in the staged chunk; SRC_STACK: entry; SRC_GLOBAL: slot
     int32_t ltab, rtab;  // SRC_LEAF: offset (doubles) of the child's leaf lookup table in `tables`
-    int32_t lexp_off, rexp_off;  // batched launches: offset (doubles) of the child's expv[c][i] in the context's tables
-    double lexp[NCM * 4], rexp[NCM * 4];
-};
-
-template <int NCM>
-struct S4Model {        // per category: eigenvectors of its mixture class
-    double U[NCM][16];  // evec[x][i]
-    double M[NCM][16];  // inv_evec[i][x]
+    int32_t lexp, rexp;  // internal child: index of its factor block in the launch's factor array; batched launches: offset
+                         // (doubles) of the same factors in the context's tables
 };
 
 struct TravArgs {
@@ -69,14 +64,30 @@ struct TravArgs {
     int prefetch;  // 1: the table rows of the NEXT node's tip children are pulled into L1 while this node computes
 };
 
-#define S4_PARAM_BYTES 32000
+#define S4_PARAM_BYTES 32640  // of the 32764 a kernel may take
+// blob: [ model | PNode nodes[NMAX] | double factors[FMAX][NCM * 4] ]
+//   model, SYM kernels:   U[16] (evec[x][i]), pi[4]                               160 bytes
+//   model, general:       U[NCM][16], M[NCM][16] (inv_evec[i][x]) per category    256 * NCM bytes
+// Both arrays start at COMPILE-TIME offsets and grow upwards (element address = constant + counter * stride: ptxas
+// keeps such loads on the uniform datapath); the window is split so that as many factor blocks fit as nodes.
 template <int NCM>
 struct S4Launch {
-    static constexpr int MAXN = (S4_PARAM_BYTES - (int)sizeof(S4Model<NCM>) - (int)sizeof(TravArgs)) / (int)sizeof(PNode<NCM>);
+    static constexpr int BLOB = (S4_PARAM_BYTES - (int)sizeof(TravArgs)) / 32 * 32;
+    static constexpr int FAC = NCM * 4 * (int)sizeof(double);  // bytes of one factor block
+    __host__ __device__ static constexpr int nmax(int model_bytes) { return (BLOB - model_bytes) / (32 + FAC); }  // nodes AND factor blocks
+    __host__ __device__ static constexpr int fac_off(int model_bytes) { return model_bytes + 32 * nmax(model_bytes); }
     TravArgs a;
-    S4Model<NCM> mdl;
-    PNode<NCM> nodes[MAXN];
+    alignas(16) unsigned char blob[BLOB];
 };
+template <int NCM, int MODEL_BYTES>
+__device__ __forceinline__ const PNode &s4_node(const S4Launch<NCM> &P, int i) {
+    return reinterpret_cast<const PNode *>(P.blob + MODEL_BYTES)[i];
+}
+template <int NCM, int MODEL_BYTES>
+__device__ __forceinline__ const double *s4_factors(const S4Launch<NCM> &P, int idx) {
+    constexpr int FAC_OFF = S4Launch<NCM>::fac_off(MODEL_BYTES);
+    return reinterpret_cast<const double *>(P.blob + FAC_OFF) + (size_t)idx * (NCM * 4);
+}
 
 #ifndef S4_THREADS
 #define S4_THREADS 64  // two warps per CTA: 4.71 ms per cfg2 traversal against 5.03 ms with four (profiles/r1t_s4_cta64_ab.log)
@@ -160,7 +171,7 @@ __device__ __forceinline__ void child_load(const TravArgs &a, int kind, int id, 
 
 // internal child: v <- U (expv (.) v) per category, in place
 template <int NCM, bool PLAIN, bool SYM = false>
-__device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const double *ev, double *v, const double *Ur = nullptr) {
+__device__ __forceinline__ void child_apply(const double *U, const double *ev, double *v, const double *Ur = nullptr) {
 #pragma unroll
     for (int c = 0; c < NCM; c++) {
         double w[4], f[4];
@@ -168,7 +179,7 @@ __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const doubl
         for (int i = 0; i < 4; i++) w[i] = __dmul_rn(ev[c * 4 + i], v[c * 4 + i]);
 #pragma unroll
         for (int x = 0; x < 4; x++) {
-            const double *u = SYM ? Ur + 4 * x : &mdl.U[c][4 * x];  // SYM: register copy of the shared eigenvectors
+            const double *u = SYM ? Ur + 4 * x : U + c * 16 + 4 * x;  // SYM: register copy of the shared eigenvectors
             f[x] = PLAIN ? s4_plain(u, w) : s4_tree(u, w);
         }
 #pragma unroll
@@ -181,7 +192,7 @@ __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const doubl
 // host at set_model.  The back-transformation then reads U again -- out[i] = sum_x U[x][i] (pi[x] tmp[x]), same
 // reduction tree over x -- so only U and pi (40 uniform registers) are live across the node loop instead of U and M
 // (64: more than the uniform register file holds, which made the kernel re-load both for every category of every
-// node; that constant traffic, not HBM, was what bounded it -- profiles/r1s_s4_experiments.log).  P.mdl.M[0][0..3] = pi.
+// node; that constant traffic, not HBM, was what bounded it -- profiles/r1s_s4_experiments.log).  The SYM model block is U[16], pi[4].
 // The 20 values are copied into vector registers once per thread (through shared memory, so that the compiler cannot
 // turn them back into constant-bank reads); the kernel then fits 96 registers: five resident CTAs per SM with two
 // stack entries (profiles/r1t_s4_ureg_ab.log), later as ten CTAs of 64 threads.
@@ -197,6 +208,7 @@ __device__ __forceinline__ void child_apply(const S4Model<NCM> &mdl, const doubl
 template <int NCM, bool SAFE, bool SYM, int MINB = S4_MINB, bool BULK = false>
 __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __grid_constant__ S4Launch<NCM> P) {
     constexpr int BLOCK = NCM * 4, PAIRS = BLOCK / 2;
+    constexpr int MODEL_BYTES = SYM ? 160 : 2 * NCM * 16 * (int)sizeof(double);  // == model_bytes() on the host
     const TravArgs &a = P.a;
     // [depth][PAIRS][S4_THREADS] double2 | unsigned [depth][S4_THREADS] scale | uint8 [chunk][S4_THREADS] tip states
     extern __shared__ double2 stk[];
@@ -240,8 +252,7 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
         // through shared memory so that the values live in vector registers for the whole loop instead of being
         // re-read from the constant bank into uniform registers by every code path of every node
         __shared__ double u_sh[20];
-        if (tid < 16) u_sh[tid] = P.mdl.U[0][tid];
-        else if (tid < 20) u_sh[tid] = P.mdl.M[0][tid - 16];
+        if (tid < 20) u_sh[tid] = reinterpret_cast<const double *>(P.blob)[tid];  // U[16], pi[4]
         __syncthreads();
 #pragma unroll
         for (int j = 0; j < 16; j++) Ur[j] = reinterpret_cast<volatile double *>(u_sh)[j];
@@ -249,8 +260,9 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
         for (int j = 0; j < 4; j++) pir[j] = reinterpret_cast<volatile double *>(u_sh)[16 + j];
     }
 
+    int nfac = 0;  // internal children met so far = index of the next factor block
     for (int i = 0; i < a.nnodes; i++) {
-        const PNode<NCM> &nd = P.nodes[i];  // constant bank, uniform index
+        const PNode &nd = s4_node<NCM, MODEL_BYTES>(P, i);  // constant bank, uniform index
         const int info = nd.info;
         const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 14) - 1;
         const bool tt = (info >> 12) & 1;
@@ -271,7 +283,7 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
             // shared memory leaves it ~40 KB and the CTAs of an SM are spread over the whole node list -- and the wait for
             // them is the largest stall of the kernel (long scoreboard at the first use).  The next node's rows depend only
             // on the staged tip states, so they are requested now and arrive while this node computes.  No register is held.
-            const PNode<NCM> &nx = P.nodes[i + 1];
+            const PNode &nx = s4_node<NCM, MODEL_BYTES>(P, i + 1);
             const int ni = nx.info;
             if ((ni >> 14) == 0) {  // same staged chunk
                 const double *row = nullptr, *row2 = nullptr;
@@ -308,10 +320,14 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
         }
         child_load<NCM, SAFE, BULK>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
         child_load<NCM, SAFE, BULK>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
-        if (lk != SRC_LEAF) child_apply<NCM, false, SYM>(P.mdl, nd.lexp, l, Ur);
+        const double *mU = reinterpret_cast<const double *>(P.blob);  // general kernel: U[NCM][16], then M[NCM][16]
+        // The factor blocks lie in the order the node loop meets the internal children, so their position is a running
+        // count (nd.lexp / nd.rexp hold the same numbers).  An address formed from a LOADED index makes ptxas fetch the
+        // factors with register-indexed LDC instead of uniform LDCU: 4.09 against 3.78 ms (profiles/r2r_s4_compact_ab.log).
+        if (lk != SRC_LEAF) child_apply<NCM, false, SYM>(mU, s4_factors<NCM, MODEL_BYTES>(P, nfac++), l, Ur);
         if (rk != SRC_LEAF) {
-            if (lk == SRC_LEAF) child_apply<NCM, true, SYM>(P.mdl, nd.rexp, r, Ur);   // tip-internal: dotProductVec (:1853)
-            else child_apply<NCM, false, SYM>(P.mdl, nd.rexp, r, Ur);                 // internal-internal (:1975-1983)
+            if (lk == SRC_LEAF) child_apply<NCM, true, SYM>(mU, s4_factors<NCM, MODEL_BYTES>(P, nfac++), r, Ur);   // tip-internal: dotProductVec (:1853)
+            else child_apply<NCM, false, SYM>(mU, s4_factors<NCM, MODEL_BYTES>(P, nfac++), r, Ur);                 // internal-internal (:1975-1983)
         }
         // ---- product, back to eigen-space (productVecMat), rescale --------------------------------
         const bool tiptip = lk == SRC_LEAF && rk == SRC_LEAF;
@@ -333,7 +349,7 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_kernel(const __g
                     const double ut[4] = {Ur[k], Ur[4 + k], Ur[8 + k], Ur[12 + k]};
                     o = s4_tree(ut, tmp);
                 } else {
-                    o = s4_tree(&P.mdl.M[c][4 * k], tmp);
+                    o = s4_tree(mU + NCM * 16 + c * 16 + 4 * k, tmp);
                 }
                 prev[c * 4 + k] = o;
                 // |x| < 2^-256  <=>  high word of |x| < high word of 2^-256 (whose low word is 0): the test needs only
@@ -630,7 +646,7 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_batch_kernel(con
     for (int j = 0; j < BLOCK; j++) prev[j] = 0.0;
     unsigned prev_sc = 0;
     for (int i = 0; i < a.nnodes; i++) {
-        const PNode<NCM> &nd = P.nodes[i];
+        const PNode &nd = s4_node<NCM, 2 * NCM * 16 * (int)sizeof(double)>(P, i);
         const int info = nd.info;
         const int lk = info & 3, rk = (info >> 2) & 3, out_stack = ((info >> 4) & 0xff) - 1, refill = (info >> 14) - 1;
         if (refill >= 0) {
@@ -649,10 +665,10 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_batch_kernel(con
         unsigned sc = 0;
         child_load<NCM, SAFE>(a, lk, nd.lid, nd.ltab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, l, sc);
         child_load<NCM, SAFE>(a, rk, nd.rid, nd.rtab, prev, prev_sc, stk, stk_sc, st_buf, tid, poff, p, r, sc);
-        if (lk != SRC_LEAF) child_apply_batch<NCM, false, SHARED>(Ug, Ur, a.denom, a.tables + nd.lexp_off, l);
+        if (lk != SRC_LEAF) child_apply_batch<NCM, false, SHARED>(Ug, Ur, a.denom, a.tables + nd.lexp, l);
         if (rk != SRC_LEAF) {
-            if (lk == SRC_LEAF) child_apply_batch<NCM, true, SHARED>(Ug, Ur, a.denom, a.tables + nd.rexp_off, r);
-            else child_apply_batch<NCM, false, SHARED>(Ug, Ur, a.denom, a.tables + nd.rexp_off, r);
+            if (lk == SRC_LEAF) child_apply_batch<NCM, true, SHARED>(Ug, Ur, a.denom, a.tables + nd.rexp, r);
+            else child_apply_batch<NCM, false, SHARED>(Ug, Ur, a.denom, a.tables + nd.rexp, r);
         }
         const bool tiptip = lk == SRC_LEAF && rk == SRC_LEAF;
         unsigned long long mxall = 0ull;
@@ -717,16 +733,24 @@ __global__ void __launch_bounds__(S4_THREADS, MINB) s4_traverse_batch_kernel(con
 }
 
 // ---- host side -------------------------------------------------------------------------------------------
+// the model block at the start of S4Launch::blob; returns its size in bytes (a multiple of 32)
 template <int NCM>
-static void fill_model(const b200lk_ctx *c, S4Model<NCM> &m) {
+static int model_bytes(const b200lk_ctx *c, bool batch) {
+    return (c->s4_sym && !batch) ? 160 : 2 * NCM * 16 * (int)sizeof(double);
+}
+template <int NCM>
+static void fill_model(const b200lk_ctx *c, double *m, bool batch) {
+    if (c->s4_sym && !batch) {  // s4_traverse_kernel<.., SYM = true>: U[16], pi[4]
+        memcpy(m, c->h_evec, sizeof(double) * 16);
+        for (int x = 0; x < 4; x++) m[16 + x] = c->s4_pi[x];
+        return;
+    }
     const int denom = c->d.fused_mix_rate ? 1 : c->d.ncat;
     for (int cc = 0; cc < NCM; cc++) {
         const int mm = cc / denom;
-        memcpy(m.U[cc], c->h_evec + (size_t)mm * 16, sizeof(double) * 16);
-        memcpy(m.M[cc], c->h_inv_evec + (size_t)mm * 16, sizeof(double) * 16);
+        memcpy(m + cc * 16, c->h_evec + (size_t)mm * 16, sizeof(double) * 16);
+        memcpy(m + NCM * 16 + cc * 16, c->h_inv_evec + (size_t)mm * 16, sizeof(double) * 16);
     }
-    if (c->s4_sym)  // s4_traverse_kernel<.., SYM = true> reads pi[x] from M[0][0..3] and never touches the rest of M
-        for (int x = 0; x < 4; x++) m.M[0][x] = c->s4_pi[x];
 }
 
 // inv_evec[i][x] == evec[x][i] * pi[x] to rounding for one shared eigen-system?  (reversible models: evec = Pi^-1/2 V,
@@ -774,6 +798,10 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     if (!Lp) Lp = new S4Launch<NCM>();
     S4Launch<NCM> &P = *Lp;
     const int nslots = c->d.nslots;
+    const int mdl_bytes = model_bytes<NCM>(c, c->batch != nullptr);
+    PNode *const pn = reinterpret_cast<PNode *>(P.blob + mdl_bytes);                 // nodes[count]
+    double *const pev = reinterpret_cast<double *>(P.blob + S4Launch<NCM>::fac_off(mdl_bytes));  // factor blocks, one per internal child
+    int nev = 0;
     // unset: two entries for the SYM kernel (ten resident CTAs of 64 threads per SM), three otherwise (eight)
     const int max_depth = c->max_stack_depth >= 0 ? c->max_stack_depth : (c->s4_sym && !c->batch ? 2 : 3);
     std::vector<int> producer(nslots, -1);  // slot -> index of the node of this launch that last wrote it
@@ -824,7 +852,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     std::vector<S4TTNode> tt_nodes;
     std::vector<const DevChild *> exp_src(2 * (size_t)count, nullptr);
     for (int i = 0; i < count; i++) {
-        PNode<NCM> &f = P.nodes[i];
+        PNode &f = pn[i];
         memset(&f, 0, sizeof(f));
         f.out_slot = nl[i].out_slot;
         int kind[2], id[2], tab[2];
@@ -848,17 +876,23 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
                 kind[k] = SRC_LEAF; id[k] = nseq % chunk; tab[k] = (int)ch.leaf_off;
                 leaf_seq[nseq++] = ch.id;
             } else {
-                exp_src[2 * i + k] = &ch;  // exp(lambda r t) of this child: filled below, all children in parallel
-                (k == 0 ? f.lexp_off : f.rexp_off) = (int32_t)(ch.echild_off + (int64_t)c->block * c->d.nstates);
+                // exp(lambda r t) of this child: its own block of the factor array, filled below (all children in parallel);
+                // batched launches read the same factors from the context's tables instead
+                if (c->batch) {
+                    (k == 0 ? f.lexp : f.rexp) = (int32_t)(ch.echild_off + (int64_t)c->block * c->d.nstates);
+                } else {
+                    (k == 0 ? f.lexp : f.rexp) = nev;
+                    exp_src[nev++] = &ch;
+                }
                 const int pr = producer[ch.id];
                 if (pr >= 0 && consumer[pr] == i && pr == i - 1) {
                     kind[k] = SRC_PREV; id[k] = 0;
-                    if (virt_ok && nreaders[pr] == 1 && ((P.nodes[pr].info >> 12) & 1)) P.nodes[pr].info |= 1 << 13;  // tip-tip, read from registers: not stored
+                    if (virt_ok && nreaders[pr] == 1 && ((pn[pr].info >> 12) & 1)) pn[pr].info |= 1 << 13;  // tip-tip, read from registers: not stored
                 } else if (pr >= 0 && consumer[pr] == i && entry_of[pr] >= 0) {
                     kind[k] = SRC_STACK; id[k] = entry_of[pr];
                     free_list.push_back(entry_of[pr]);
                     entry_of[pr] = -1;
-                    if (virt_ok && nreaders[pr] == 1 && ((P.nodes[pr].info >> 12) & 1)) P.nodes[pr].info |= 1 << 13;  // ... or from the stack
+                    if (virt_ok && nreaders[pr] == 1 && ((pn[pr].info >> 12) & 1)) pn[pr].info |= 1 << 13;  // ... or from the stack
                 } else {
                     kind[k] = SRC_GLOBAL; id[k] = ch.id;
                     // produced by an EARLIER launch (or call): a DRAM read.  A vector of this launch that no longer
@@ -882,7 +916,7 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
             if (far >= 0 && consumer[far] > consumer[i]) {
                 free_list.push_back(entry_of[far]);
                 entry_of[far] = -1;
-                if (!bulk) P.nodes[far].info &= ~(0xff << 4);  // its push is no longer needed
+                if (!bulk) pn[far].info &= ~(0xff << 4);  // its push is no longer needed
             }
         }
         if (bulk) {
@@ -910,17 +944,23 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
         f.info = kind[0] | kind[1] << 2 | (out_stack + 1) << 4 | tt << 12 | (refill + 1) << 14;  // bit 13 (virtual) is set by the consumer
         producer[nl[i].out_slot] = i;
     }
+    // launch_run sized the segment for the window; nothing has been written behind the node array yet
+    if (c->batch ? mdl_bytes + 32 * count > S4Launch<NCM>::BLOB
+                 : (count > S4Launch<NCM>::nmax(mdl_bytes) || nev > S4Launch<NCM>::nmax(mdl_bytes))) {
+        snprintf(c->err, sizeof(c->err), "node program of %d nodes / %d internal children exceeds the parameter window", count, nev);
+        return B200LK_ERR_ARG;
+    }
     // which slots this launch leaves virtual (the last writer of a slot decides)
     int nvirtual = 0;
     if (c->virt)
         for (int i = 0; i < count; i++) {
             const int slot = nl[i].out_slot;
-            const bool v = (P.nodes[i].info >> 13) & 1;
+            const bool v = (pn[i].info >> 13) & 1;
             if (c->virt[slot] && !v) c->n_virtual--;
             if (!c->virt[slot] && v) c->n_virtual++;
             c->virt[slot] = v;
             if (v) {
-                const S4Virt d = {slot, P.nodes[i].ltab, tip_a[i], tip_b[i]};
+                const S4Virt d = {slot, pn[i].ltab, tip_a[i], tip_b[i]};
                 c->virt_desc[slot] = d;
                 nvirtual++;
             }
@@ -928,13 +968,13 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     // the per-child factors: 16 exp() per internal child, ~6000 for a cfg2 traversal -- what a blocking evaluation spends
     // most of its host time on, so a few threads share it (the calling thread alone for short lists)
     {
-        const int nexp = 2 * count;
+        const int nexp = nev;
         // at most four threads, and never more than OMP_NUM_THREADS allows: torchrun sets it to 1 for every rank, and eight
         // ranks forking four workers each onto the same pinned cores cost 70 ms per step instead of saving 0.03
         const int nthr = std::min(4, omp_get_max_threads());
 #pragma omp parallel for schedule(static) num_threads(nthr) if (nexp >= 64 && nthr > 1)
         for (int j = 0; j < nexp; j++)
-            if (exp_src[j]) fill_expv<NCM>(c, *exp_src[j], (j & 1) ? P.nodes[j >> 1].rexp : P.nodes[j >> 1].lexp);
+            fill_expv<NCM>(c, *exp_src[j], pev + (size_t)j * (NCM * 4));
     }
     int32_t *d_seq = reinterpret_cast<int32_t *>(c->d_prog) + *seq_used;
     if (nseq)
@@ -989,7 +1029,8 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
     a.tt = c->tt_tables;
     a.codes = codes;
     a.prefetch = b200_env().s4_prefetch && !c->batch;
-    fill_model<NCM>(c, P.mdl);
+    fill_model<NCM>(c, reinterpret_cast<double *>(P.blob), c->batch != nullptr);
+
     const size_t smem = (size_t)depth_used * S4_THREADS * (2 * NCM * sizeof(double2) + sizeof(unsigned)) + S4_STATE_BYTES;
     const unsigned grid = (unsigned)(((c->batch ? c->batch->max_ntot : c->ntot) + S4_THREADS - 1) / S4_THREADS);
     if (!c->trav_attr_set) {
@@ -1048,12 +1089,24 @@ static int launch_segment(b200lk_ctx *c, const b200lk_node *nl, int count, int *
 
 template <int NCM>
 static int launch_run(b200lk_ctx *c, const b200lk_node *nl, int count, int *seq_used) {
-    constexpr int MAXN = S4Launch<NCM>::MAXN;
+    // What a launch can carry: `cap` nodes and, unless it is a batched launch (which reads the factors from the tables),
+    // `cap` factor blocks -- one per internal child.  pre[i] = internal children of nodes [0, i).
+    const int mdl_bytes = model_bytes<NCM>(c, c->batch != nullptr);
+    int cap = c->batch ? (S4Launch<NCM>::BLOB - mdl_bytes) / 32 : S4Launch<NCM>::nmax(mdl_bytes);
+    if (b200_env().s4_budget > 0) cap = std::max(2, std::min(cap, b200_env().s4_budget));  // A/B hook: shorter launches
+    std::vector<int> pre(count + 1, 0);
+    for (int i = 0; i < count; i++) {
+        int internal = 0;
+        if (!c->batch)
+            for (int k = 0; k < 2; k++) internal += c->h_children[nl[i].child_begin + k].kind != B200LK_CHILD_LEAF;
+        pre[i + 1] = pre[i] + internal;
+    }
+    auto fits = [&](int j, int e) { return e - j <= cap && pre[e] - pre[j] <= cap; };  // nodes [j, e) in one launch?
     // A list longer than one launch's parameter space is cut where the fewest vectors are live across the cut (each
     // of them is re-read from HBM by the next launch instead of coming from registers or the stack):
     // live[s] = #{i < s : the node consuming i's output has index >= s}.
-    std::vector<int> live;
-    if (count > MAXN) {
+    std::vector<int> live, maxfit, need;
+    if (!fits(0, count)) {
         std::vector<int> producer(c->d.nslots, -1), diff(count + 2, 0);
         for (int i = 0; i < count; i++) {
             for (int k = 0; k < 2; k++) {
@@ -1067,14 +1120,23 @@ static int launch_run(b200lk_ctx *c, const b200lk_node *nl, int count, int *seq_
         }
         live.assign(count + 1, 0);
         for (int s2 = 1; s2 <= count; s2++) live[s2] = live[s2 - 1] + diff[s2];
+        // maxfit[j] = longest segment starting at j that fits; need[j] = fewest launches for [j, count)
+        maxfit.assign(count + 1, 0);
+        need.assign(count + 1, 0);
+        for (int j = 0, e = 0; j < count; j++) {
+            if (e < j) e = j;
+            while (e < count && fits(j, e + 1)) e++;
+            maxfit[j] = e - j;
+        }
+        for (int j = count - 1; j >= 0; j--) need[j] = 1 + need[j + std::max(1, maxfit[j])];
     }
     for (int done = 0; done < count;) {
-        int seg = std::min(count - done, MAXN);
-        if (count - done > MAXN) {
-            const int launches_left = (count - done + MAXN - 1) / MAXN;  // keep the launch count minimal
-            const int lo = std::max(1, count - done - (launches_left - 1) * MAXN);
-            for (int t = lo; t <= MAXN; t++)
-                if (live[done + t] <= live[done + seg]) seg = t;
+        int seg = count - done;
+        if (!fits(done, count)) {
+            seg = std::max(1, maxfit[done]);
+            // any shorter segment that keeps the launch count minimal and leaves fewer vectors live across the cut
+            for (int t = 1; t <= maxfit[done]; t++)
+                if (need[done + t] == need[done] - 1 && live[done + t] <= live[done + seg]) seg = t;
         }
         int rc = launch_segment<NCM>(c, nl + done, seg, seq_used);
         if (rc) return rc;

@@ -119,14 +119,16 @@ def test_large_problem_properties():
                                  {"B200LK_S4_PREFETCH": "1"}, {"B200LK_S4_EVICT": "0"}, {"B200LK_S4_EVICT": "0", "B200LK_STACK_DEPTH": "1"},
                                  {"B200LK_S4_BULK": "1"},
                                  {"B200LK_S4_BULK": "1", "B200LK_S4_RING": "1"}, {"B200LK_S4_BULK": "1", "B200LK_S4_RING": "2"},
-                                 {"B200LK_S4_BULK": "1", "B200LK_S4_RING": "4", "B200LK_S4_MINB": "6"}])
+                                 {"B200LK_S4_BULK": "1", "B200LK_S4_RING": "4", "B200LK_S4_MINB": "6"},
+                                 {"B200LK_S4_BUDGET": "37"}, {"B200LK_S4_BUDGET": "2", "B200LK_STACK_DEPTH": "1"}])
 @pytest.mark.parametrize("safe", [False, True])
 def test_dna_paths_agree_with_oracle(oracle_lib, monkeypatch, env, safe):
     """The 4-state traversal has three routes -- one pattern-stationary launch (default), the same with
     the shared-memory stack overflowing into global re-reads, and the level-batched kernels -- plus the
     general (non-SYM) kernel and the other register-budget instantiations of the SYM one, with the L1 prefetch of
     the next node's table rows, without the farthest-consumer replacement of stack entries, and with the node vectors leaving through cp.async.bulk (ring of 1 / 2 / 3 / 4
-    shared-memory slots) instead of the threads' stores; all of them must match the oracle, scale counts included
+    shared-memory slots) instead of the threads' stores, and with the node list cut into many short launches (37 or 2
+    nodes each: vectors crossing a cut are re-read from HBM); all of them must match the oracle, scale counts included
     (deep tree so that rescaling fires).
     The hooks are read when a context is created."""
     for k, v in env.items():
