@@ -47,22 +47,22 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
         int mm = c / denom;
         echild[idx] = m.evec[(size_t)mm * nn + r] * s_expv[(c - c0) * n + i];
     }
+    // The two derived tables below form echild's elements again as evec * expv (the same product, the same bits) instead of
+    // reading them back: no barrier, no global round trip between the phases (supermatrix batches: 99 k such CTAs per launch).
     if (ch.frag_off >= 0) {
         // tensor paths (dense.cu: 3 n-tiles x 5 k-steps for 20 states; densen.cu: NT x 2NT): echild as the B operand
         // of mma.m8n8k4, fragment order
         //   frag[c][j][s][lane] = echild[c][x = 8j + lane/4][i = 4s + lane%4]   (x >= n or i >= n -> 0)
-        __syncthreads();
         double *frag = tables + ch.frag_off;
         const int fc = frag_nt * frag_ks * 32;
         for (int idx = c0 * fc + threadIdx.x; idx < c1 * fc; idx += blockDim.x) {
             int c = idx / fc, r = idx - c * fc;
             int j = r / (frag_ks * 32), s = (r >> 5) % frag_ks, lane = r & 31;
             int x = 8 * j + (lane >> 2), i = 4 * s + (lane & 3);
-            frag[idx] = (x < n && i < n) ? echild[(size_t)c * nn + x * n + i] : 0.0;
+            frag[idx] = (x < n && i < n) ? m.evec[(size_t)(c / denom) * nn + x * n + i] * s_expv[(c - c0) * n + i] : 0.0;
         }
     }
     if (ch.leaf_off < 0) return;
-    __syncthreads();
     double *leaf = tables + ch.leaf_off;
     const int tip_block = n * nmix;
     const int span = (c1 - c0) * n;
@@ -73,11 +73,12 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
         if (s == codes - 1) {
             v = 1.0;
         } else {
-            int c = r / n;
-            const double *e = echild + (size_t)r * n;
+            int c = r / n, x = r - c * n;
+            const double *ev = m.evec + (size_t)(c / denom) * nn + (size_t)x * n;
+            const double *ex = s_expv + (c - c0) * n;
             const double *tip = m.tip_partial_lh + (size_t)s * tip_block + (c / denom) * n;
-            v = e[0] * tip[0];
-            for (int i = 1; i < n; i++) v += e[i] * tip[i];
+            v = (ev[0] * ex[0]) * tip[0];
+            for (int i = 1; i < n; i++) v += (ev[i] * ex[i]) * tip[i];
         }
         leaf[idx] = v;
     }
