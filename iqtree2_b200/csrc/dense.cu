@@ -521,6 +521,15 @@ __device__ __forceinline__ void dense_load_A(const double *base, size_t block, i
         for (int s = 0; s < 5; s++) A[mt][s] = __ldg(src + 4 * s);
     }
 }
+// the same with the rows' element offsets (row * block + q) formed once per tile instead of once per step
+__device__ __forceinline__ void dense_load_A_at(const double *base, int c, const int64_t (&off)[DN_MT], double (&A)[DN_MT][5]) {
+#pragma unroll
+    for (int mt = 0; mt < DN_MT; mt++) {
+        const double *src = base + off[mt] + c * 20;
+#pragma unroll
+        for (int s = 0; s < 5; s++) A[mt][s] = __ldg(src + 4 * s);
+    }
+}
 __device__ __forceinline__ void dense_mma_child(const double (&A)[DN_MT][5], const double *sT, int cl, int lane,
                                                 double (&f)[DN_MT][6]) {
 #pragma unroll
@@ -611,18 +620,24 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
         cp_async_commit();
 
         const int nsteps = my_tiles * cg;
-        // rows of the tile a step belongs to (clamped so that out-of-range rows read the last pattern)
-        auto rows_of = [&](int step, int64_t (&pp)[DN_MT], int64_t (&ppc)[DN_MT]) {
-            const int t = step / cg;
+        // Loop bookkeeping is incremental: (t, cl) count up instead of step / cg and step % cg, and everything that depends
+        // on the tile only -- its rows (clamped so that out-of-range rows read the last pattern), their element offsets
+        // row * block for the operand loads and the output -- is formed when a tile opens, not at every step (on the source
+        // page of the r2l capture this arithmetic was 22 % of the instructions and 16 % of the stall samples).
+        double AL[DN_MT][5], AR[DN_MT][5];
+        int64_t pc[DN_MT] = {}, pcn[DN_MT] = {};          // clamped rows: current tile, tile of the NEXT step
+        int64_t offn[DN_MT] = {}, offo[DN_MT] = {};       // element offsets: next step's operands, this tile's output
+        bool live[DN_MT] = {}, liven[DN_MT] = {};         // row < ntot
+        auto rows_of_tile = [&](int t) {
             const int64_t pbase = (tile0 + t) * DN_PT + warp * (8 * DN_MT);
 #pragma unroll
             for (int mt = 0; mt < DN_MT; mt++) {
-                pp[mt] = pbase + mt * 8 + g;
-                ppc[mt] = pp[mt] < a.ntot ? pp[mt] : a.ntot - 1;
+                const int64_t pp = pbase + mt * 8 + g;
+                liven[mt] = pp < a.ntot;
+                pcn[mt] = liven[mt] ? pp : a.ntot - 1;
+                offn[mt] = pcn[mt] * block + q;
             }
         };
-        double AL[DN_MT][5], AR[DN_MT][5];
-        int64_t p[DN_MT] = {}, pc[DN_MT] = {}, pn[DN_MT], pcn[DN_MT];
         // per-tile inputs (tip states, invariant-site flag): requested one step before the tile starts, so that the
         // first table lookup of a tile does not wait for them
         int stL[DN_MT] = {}, stR[DN_MT] = {}, stLn[DN_MT] = {}, stRn[DN_MT] = {};
@@ -637,42 +652,45 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
             }
         };
         if (nsteps > 0) {
-            rows_of(0, pn, pcn);
-            if (!Lleaf) dense_load_A(pL, block, c0, pcn, q, AL);
-            if (!Rleaf) dense_load_A(pR, block, c0, pcn, q, AR);
+            rows_of_tile(0);
+            if (!Lleaf) dense_load_A_at(pL, c0, offn, AL);
+            if (!Rleaf) dense_load_A_at(pR, c0, offn, AR);
             tile_inputs(pcn);
         }
         cp_async_wait<0>();  // the tables; the first operands above stay in flight across the barrier
         __syncthreads();
         unsigned long long rmax[DN_MT] = {};
+        int t = 0, cl = 0;
         for (int step = 0; step < nsteps; step++) {
-            const int t = step / cg, cl = step - t * cg, c = c0 + cl;
-            const bool more = step + 1 < nsteps;
-            const int cn = c0 + (more ? (step + 1) % cg : 0);
-            if (cl == 0) {
-                rows_of(step, p, pc);
+            const int c = c0 + cl;
+            const bool more = step + 1 < nsteps, last_cl = cl == cg - 1;
+            const int cn = c0 + ((more && !last_cl) ? cl + 1 : 0);
+            if (cl == 0) {  // a tile opens: what was "next" is current
 #pragma unroll
                 for (int mt = 0; mt < DN_MT; mt++) {
+                    pc[mt] = pcn[mt];
+                    live[mt] = liven[mt];
+                    offo[mt] = offn[mt] + q;  // row * block + 2 q
                     invar0[mt] = invn[mt] == 0.0;
                     stL[mt] = stLn[mt];
                     stR[mt] = stRn[mt];
                     rmax[mt] = 0ull;
                 }
             }
-            if (more) {
-                rows_of(step + 1, pn, pcn);
-                if (cl == cg - 1) tile_inputs(pcn);  // the next step opens a tile
+            if (more && last_cl) {  // the next step opens a tile
+                rows_of_tile(t + 1);
+                tile_inputs(pcn);
             }
             double fl[DN_MT][6], fr[DN_MT][6];
             if (Lleaf) dense_leaf_lookup(sL, cg, cl, stL, lane, fl);
             else {
                 dense_mma_child(AL, sL, cl, lane, fl);
-                if (more) dense_load_A(pL, block, cn, pcn, q, AL);  // next step's left operands, in flight from here
+                if (more) dense_load_A_at(pL, cn, offn, AL);  // next step's left operands, in flight from here
             }
             if (Rleaf) dense_leaf_lookup(sR, cg, cl, stR, lane, fr);
             else {
                 dense_mma_child(AR, sR, cl, lane, fr);
-                if (more) dense_load_A(pR, block, cn, pcn, q, AR);
+                if (more) dense_load_A_at(pR, cn, offn, AR);
             }
             const double *B = sI + (size_t)cl * B200_FRAG20 + lane;
 #pragma unroll
@@ -711,14 +729,14 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
                 } else {
                     rmax[mt] = mx > rmax[mt] ? mx : rmax[mt];
                 }
-                if (p[mt] < a.ntot) {
-                    double *po = out_base + (size_t)p[mt] * block + c * 20 + 2 * q;
+                if (live[mt]) {
+                    double *po = out_base + offo[mt] + c * 20;
                     // streaming stores: the vector is next read a level later, after more than an L2 of other writes
                     // (cfg3 33.6 -> 32.7 ms, profiles/r1t_dense20_stream_ab.log; streaming LOADS of the children cost 5 %)
                     __stcs(reinterpret_cast<double2 *>(po), make_double2(o[0], o[1]));
                     __stcs(reinterpret_cast<double2 *>(po + 8), make_double2(o[2], o[3]));
                     if (q < 2) __stcs(reinterpret_cast<double2 *>(po + 16), make_double2(o[4], o[5]));
-                    if (SAFE && q == 0) sc_out[p[mt] * ncm + c] = (uint8_t)sc;
+                    if (SAFE && q == 0) sc_out[pc[mt] * ncm + c] = (uint8_t)sc;
                 }
             }
             if (!SAFE && cl == cg - 1) {
@@ -732,6 +750,12 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
                         if (mx > *slot) *slot = mx;
                     }
                 }
+            }
+            if (last_cl) {
+                cl = 0;
+                t++;
+            } else {
+                cl++;
             }
         }
     }
