@@ -693,21 +693,33 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
                 if (more) dense_load_A_at(pR, cn, offn, AR);
             }
             const double *B = sI + (size_t)cl * B200_FRAG20 + lane;
+            // back-transformation of BOTH row tiles together: every B fragment is fetched once and feeds two DMMAs, and six
+            // accumulator chains (3 n-tiles x 2 row tiles) are in flight instead of three
+            double tmpa[DN_MT][6], a4a[DN_MT], oa[DN_MT][6];
 #pragma unroll
             for (int mt = 0; mt < DN_MT; mt++) {
-                double tmp[6];
 #pragma unroll
-                for (int k = 0; k < 6; k++) tmp[k] = fl[mt][k] * fr[mt][k];
+                for (int k = 0; k < 6; k++) {
+                    tmpa[mt][k] = fl[mt][k] * fr[mt][k];
+                    oa[mt][k] = 0.0;
+                }
                 const int srcl = (lane & ~3) | (q >> 1);
-                const double v0 = __shfl_sync(0xffffffffu, tmp[4], srcl), v1 = __shfl_sync(0xffffffffu, tmp[5], srcl);
-                const double a4 = (q & 1) ? v1 : v0;
-                double o[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+                const double v0 = __shfl_sync(0xffffffffu, tmpa[mt][4], srcl), v1 = __shfl_sync(0xffffffffu, tmpa[mt][5], srcl);
+                a4a[mt] = (q & 1) ? v1 : v0;
+            }
+#pragma unroll
+            for (int kk = 0; kk < 5; kk++) {
 #pragma unroll
                 for (int jo = 0; jo < 3; jo++) {
+                    const double b = B[(jo * 5 + kk) * 32];
 #pragma unroll
-                    for (int kk = 0; kk < 4; kk++) dmma(o[2 * jo], o[2 * jo + 1], tmp[kk], B[(jo * 5 + kk) * 32]);
-                    dmma(o[2 * jo], o[2 * jo + 1], a4, B[(jo * 5 + 4) * 32]);
+                    for (int mt = 0; mt < DN_MT; mt++)
+                        dmma(oa[mt][2 * jo], oa[mt][2 * jo + 1], kk < 4 ? tmpa[mt][kk] : a4a[mt], b);
                 }
+            }
+#pragma unroll
+            for (int mt = 0; mt < DN_MT; mt++) {
+                double (&o)[6] = oa[mt];
                 // |x| < 2^-256  <=>  high word of |x| < 0x2FF00000: the running maximum needs the high words only
                 unsigned hmx = 0u;
 #pragma unroll
