@@ -79,6 +79,7 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
         off += (size_t)block * n + block;  // echild, then expv
         dc.frag_off = -1;
         dc.aux_off = -1;
+        dc.vtt_off = dc.vpair_off = -1;
         dc.src = j;
         dc.len_slot = c->cur_len_slots ? c->cur_len_slots[j] : -1;
         if (c->frag_cat) {
@@ -159,14 +160,63 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
         if (a.kind != B200LK_CHILD_LEAF && b.kind == B200LK_CHILD_LEAF) std::swap(a, b);  // a single leaf goes first
         kind_of[i] = (a.kind == B200LK_CHILD_LEAF) ? (b.kind == B200LK_CHILD_LEAF ? 0 : 1) : 2;
     }
+    // 20-state path: a tip-tip node answered from its state-pair table whose ONLY reader in this list is a bifurcating
+    // node of the tensor kernel stays VIRTUAL -- it is not gathered into its slot; the reader addresses the table itself
+    // (dense20_rp_kernel), and anybody else who wants the slot later gets it gathered first (s4_realize).  A third of the
+    // vectors of a full traversal are such nodes; their gather launches were 12 % of a cfg3 evaluation.
+    const bool tt_ok = c->dense20 && !c->batch && b200_env().s4_tt &&
+                       (b200_env().s4_tt == 2 || (int64_t)c->d.n_state_codes * c->d.n_state_codes * 4 <= c->ntot);
+    const bool virt_ok = tt_ok && c->virt && b200_env().s4_virtual && b200_env().dense_pipe == 2 && !c->site;
+    std::vector<int> nreaders(nnodes, 0), reader(nnodes, -1);
+    std::vector<char> vnode(nnodes, 0);
+    if (c->virt) {
+        int rb = s4_before_update(c, nodes, nnodes, children);  // the tables are about to be rebuilt
+        if (rb) return rb;
+    }
+    if (virt_ok) {
+        std::vector<int> last_writer(nslots, -1);
+        for (int i = 0; i < nnodes; i++) {
+            for (int k = 0; k < nodes[i].nchild; k++) {
+                const b200lk_child &ch = children[nodes[i].child_begin + k];
+                if (ch.kind != B200LK_CHILD_LEAF && last_writer[ch.id] >= 0) {
+                    nreaders[last_writer[ch.id]]++;
+                    reader[last_writer[ch.id]] = i;
+                }
+            }
+            last_writer[nodes[i].out_slot] = i;
+        }
+        for (int i = 0; i < nnodes; i++)
+            vnode[i] = kind_of[i] == 0 && nreaders[i] == 1 && nodes[reader[i]].nchild == 2;
+    }
     std::vector<std::vector<int>> levels(nlevels);
     int pos = 0;
     size_t tt_off = 0;
     const size_t tt_doubles = (size_t)c->d.n_state_codes * c->d.n_state_codes * block;
+    std::vector<S4Virt> vdesc;          // the virtual nodes of this list ...
+    std::vector<int64_t> vpair_off;     // ... and where their pair indices go
+    for (int i = 0; i < nnodes && virt_ok; i++) {
+        if (!vnode[i]) continue;
+        if (tt_off + tt_doubles > (size_t)INT32_MAX) { vnode[i] = 0; continue; }  // descriptors carry 32-bit offsets
+        const DevChild &a = c->h_children[nodes[i].child_begin], &b = c->h_children[nodes[i].child_begin + 1];
+        const S4Virt d = {nodes[i].out_slot, (int32_t)tt_off, a.id, b.id};
+        // the reader's entry for this child
+        const b200lk_node &rn = nodes[reader[i]];
+        for (int k = 0; k < 2; k++) {
+            DevChild &rc = c->h_children[rn.child_begin + k];
+            if (rc.kind != B200LK_CHILD_LEAF && rc.id == nodes[i].out_slot) {
+                rc.vtt_off = (int64_t)tt_off;
+                rc.vpair_off = (int64_t)vdesc.size() * c->ntot_pad;
+            }
+        }
+        c->h_children[nodes[i].child_begin].aux_off = (int64_t)tt_off;  // tt_tables_kernel builds the table as for any tip-tip node
+        vpair_off.push_back((int64_t)vdesc.size() * c->ntot_pad);
+        vdesc.push_back(d);
+        tt_off += tt_doubles;
+    }
     for (int lv = 0; lv < nlevels; lv++) {
         for (int pass = 0; pass < 3; pass++)
             for (int i = 0; i < nnodes; i++) {
-                if (level[i] != lv) continue;
+                if (level[i] != lv || vnode[i]) continue;
                 const int want = kind_of[i] == 0 ? 0 : (kind_of[i] == 3 ? 2 : 1);
                 if (want != pass) continue;
                 DevNode &dn = c->h_nodes[pos];
@@ -175,7 +225,7 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
                 dn.nchild = nodes[i].nchild;
                 dn.kind = kind_of[i];
                 // state-pair table of a tip-tip node: worth building when there are clearly more patterns than pairs
-                if (dn.kind == 0 && c->dense20 && !c->batch && (int64_t)c->d.n_state_codes * c->d.n_state_codes * 4 <= c->ntot) {
+                if (dn.kind == 0 && tt_ok) {
                     c->h_children[dn.child_begin].aux_off = (int64_t)tt_off;
                     tt_off += tt_doubles;
                 }
@@ -183,6 +233,24 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
                 pos++;
             }
     }
+    // virtual nodes: behind every level in the device node array (tt_tables_kernel visits them, no update launch does)
+    for (int i = 0; i < nnodes; i++) {
+        if (!vnode[i]) continue;
+        DevNode &dn = c->h_nodes[pos++];
+        dn.out_slot = nodes[i].out_slot;
+        dn.child_begin = nodes[i].child_begin;
+        dn.nchild = 2;
+        dn.kind = 0;
+    }
+    // bookkeeping in list order: the last writer of a slot decides whether it is virtual
+    if (c->virt)
+        for (int i = 0, k = 0; i < nnodes; i++) {
+            const int slot = nodes[i].out_slot;
+            if (c->virt[slot] && !vnode[i]) c->n_virtual--;
+            if (!c->virt[slot] && vnode[i]) c->n_virtual++;
+            c->virt[slot] = vnode[i];
+            if (vnode[i]) c->virt_desc[slot] = vdesc[k++];
+        }
     if (tt_off > c->tt_cap) {
         if (c->tt_tables) CUDA_TRY(c, cudaFree(c->tt_tables));
         c->tt_tables = nullptr;
@@ -204,7 +272,7 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
     }
     if (!c->batch) {  // level-batched kernels fetch every internal child from HBM and write every vector once
         const int64_t vec_bytes = 8 * (int64_t)c->block + c->scale_per_ptn;
-        int64_t vecs = nnodes, tips = 0;
+        int64_t vecs = nnodes - 2 * (int64_t)vdesc.size(), tips = 2 * (int64_t)vdesc.size();  // a virtual node: no write, no read, two tip rows at its reader
         for (int j = 0; j < nchildren; j++) (children[j].kind == B200LK_CHILD_LEAF ? tips : vecs)++;
         c->n_min_bytes += c->ntot * (vec_bytes * vecs + tips);
     }
@@ -212,6 +280,10 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
     if (rc) return rc;
     if (tt_off > 0) {
         rc = launch_tt_tables(c, nnodes);
+        if (rc) return rc;
+    }
+    if (!vdesc.empty()) {
+        rc = launch_tt_pairs(c, vdesc.data(), (int)vdesc.size(), vpair_off.data());
         if (rc) return rc;
     }
     rc = launch_partials(c, levels);

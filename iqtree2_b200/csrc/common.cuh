@@ -46,6 +46,9 @@ struct DevChild {
     int64_t src;         // position in the caller's children array (entries are reordered leaf-first): indexes
                          // BatchLaunch::d_child_len
     int64_t len_slot;    // >= 0: the branch length is lengths[len_slot] of the context's device-resident table (sweep.cu)
+    // 20-state path: >= 0 when this INTERNAL child is a tip-tip node left virtual (its vector is not in its slot): offset
+    // (doubles) of its state-pair table in tt_tables, and offset (elements) of its per-pattern pair indices in pair_idx
+    int64_t vtt_off, vpair_off;
 };
 
 struct DevNode {
@@ -97,7 +100,7 @@ struct B200Env {
     bool site_dmma;               // B200LK_SITE_DMMA=0 keeps the shuffle kernel for 20-state site models
     bool no_fused_tail;           // B200LK_NO_FUSED_TAIL=1: separate lnl / theta / derv launches in b200lk_evaluate*
     int batch_minb;               // B200LK_BATCH_MINB=2|8: force one build of s4_traverse_batch_kernel (A/B); 0 = per use
-    int s4_tt;                    // B200LK_S4_TT=0: tip-tip nodes of the 4-state traversal computed, not looked up; 2: looked up at any size (tests)
+    int s4_tt;                    // B200LK_S4_TT=0: tip-tip nodes (4- and 20-state paths) computed, not looked up in state-pair tables; 2: looked up at any size (tests)
     bool s4_bulk;                 // B200LK_S4_BULK=1: node vectors leave through cp.async.bulk instead of the threads' STG (slower: A/B log)
     int s4_budget;                // B200LK_S4_BUDGET: nodes per launch of the 4-state traversal (A/B: more, shorter launches); 0 = what the window holds
     bool s4_virtual;              // B200LK_S4_VIRTUAL=0: every tip-tip vector is written by the traversal that computes it
@@ -164,7 +167,9 @@ struct b200lk_ctx {
     double *tt_tables;  // 20-state path: per tip-tip node, the partial vector of every (left state, right state) pair
     size_t tt_cap;      // doubles
     size_t s4_ttdesc_used;  // 4-state path: tip-tip table descriptors staged for the traversal being enqueued
-    uint8_t *virt;          // 4-state path, host [nslots]: 1 = the slot's vector is virtual (s4.cu: s4_realize)
+    uint16_t *pair_idx;     // 20-state path: per virtual tip-tip node, sa * codes + sb of every pattern (dense.cu)
+    size_t pair_cap;        // elements
+    uint8_t *virt;          // host [nslots]: 1 = the slot's vector is virtual (4-state: s4.cu, 20-state: dense.cu; s4_realize)
     S4Virt *virt_desc;      // host [nslots]: where a virtual slot's rows are
     int n_virtual;
     const b200lk_node *cur_nodes;  // non-null only inside enqueue_update's 4-state branch: the caller's list ...
@@ -339,7 +344,9 @@ bool s4_detect_sym(const b200lk_ctx *c, double pi[4]);
 int launch_dense20(b200lk_ctx *c, int node_base, int nnodes);
 int launch_inv_frag(b200lk_ctx *c);
 int launch_tt_tables(b200lk_ctx *c, int nnodes);
-int s4_realize(b200lk_ctx *c);  // s4.cu: gather every virtual tip-tip vector into its slot (no-op when there is none)
+int s4_realize(b200lk_ctx *c);  // s4.cu: gather every virtual tip-tip vector into its slot (no-op when there is none; either layout)
+int dense_realize(b200lk_ctx *c);                               // dense.cu: the pattern-major form of the same
+int launch_tt_pairs(b200lk_ctx *c, const S4Virt *v, int n, const int64_t *pair_off);  // dense.cu: pair indices of virtual nodes
 int s4_before_update(b200lk_ctx *c, const b200lk_node *nodes, int nnodes, const b200lk_child *children);
 static inline int s4_realize_slot(b200lk_ctx *c, int slot) { return (c->n_virtual && c->virt[slot]) ? s4_realize(c) : 0; }
 int launch_dense20_tt(b200lk_ctx *c, int node_base, int nnodes);

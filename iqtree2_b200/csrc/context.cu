@@ -157,7 +157,7 @@ static int alloc_all(b200lk_ctx *c) {
     CUDA_TRY(c, cudaMalloc(&c->d_result, sizeof(double) * 16));
     CUDA_TRY(c, cudaMemset(c->d_result, 0, sizeof(double) * 16));
     CUDA_TRY(c, cudaMallocHost(&c->h_result, sizeof(double) * 8));
-    if (c->tile == 32) {  // virtual tip-tip vectors of the 4-state traversal (s4.cu)
+    if (c->tile == 32 || c->dense20) {  // virtual tip-tip vectors of the 4-state traversal (s4.cu) / the 20-state path (dense.cu)
         c->virt = (uint8_t *)calloc(d.nslots > 0 ? d.nslots : 1, 1);
         c->virt_desc = (S4Virt *)calloc(d.nslots > 0 ? d.nslots : 1, sizeof(S4Virt));
         if (!c->virt || !c->virt_desc) return B200LK_ERR_NOMEM;
@@ -261,6 +261,7 @@ extern "C" int b200lk_destroy(b200lk_ctx *c) {
     if (c->h_rell) cudaFreeHost(c->h_rell);
     if (c->pmax) cudaFree(c->pmax);
     if (c->tt_tables) cudaFree(c->tt_tables);
+    if (c->pair_idx) cudaFree(c->pair_idx);
     free(c->virt);
     free(c->virt_desc);
     if (c->s_eval) cudaFree(c->s_eval);

@@ -38,6 +38,8 @@ struct DenseArgs {
     const DevNode *nodes;
     const DevChild *children;
     const double *tables, *inv_frag, *ptn_invar;
+    const double *tt;            // state-pair tables (virtual tip-tip children are read from them, dense20_rp_kernel)
+    const uint16_t *pair_idx;    // their per-pattern pair indices
     const uint8_t *states;
     double *partial;
     uint8_t *scale;
@@ -530,6 +532,15 @@ __device__ __forceinline__ void dense_load_A_at(const double *base, int c, const
         for (int s = 0; s < 5; s++) A[mt][s] = __ldg(src + 4 * s);
     }
 }
+// ... and for a virtual tip-tip child: the rows are those of its state-pair table (32-bit offsets: api.cu keeps them small)
+__device__ __forceinline__ void dense_load_A_at(const double *base, int c, const int (&off)[DN_MT], double (&A)[DN_MT][5]) {
+#pragma unroll
+    for (int mt = 0; mt < DN_MT; mt++) {
+        const double *src = base + off[mt] + c * 20;
+#pragma unroll
+        for (int s = 0; s < 5; s++) A[mt][s] = __ldg(src + 4 * s);
+    }
+}
 __device__ __forceinline__ void dense_mma_child(const double (&A)[DN_MT][5], const double *sT, int cl, int lane,
                                                 double (&f)[DN_MT][6]) {
 #pragma unroll
@@ -571,6 +582,9 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
     const DevChild R = a.children[nd.child_begin + 1];
     const bool Lleaf = L.kind == B200LK_CHILD_LEAF, Rleaf = R.kind == B200LK_CHILD_LEAF;
     const bool tiptip = Lleaf && Rleaf;
+    // a tip-tip child left virtual (api.cu): its rows are read from the node's state-pair table by per-pattern pair index,
+    // not from a resident vector; its scale counters are zero
+    const bool Lvirt = !Lleaf && L.vtt_off >= 0, Rvirt = !Rleaf && R.vtt_off >= 0;
     const int leaf_doubles = a.codes * DN_CG * 20, frag_doubles = DN_CG * B200_FRAG20;
     const int child_doubles = leaf_doubles > frag_doubles ? leaf_doubles : frag_doubles;
     double *sL = sm, *sR = sL + child_doubles, *sI = sR + child_doubles;
@@ -579,10 +593,12 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
     const int64_t tile0 = (int64_t)blockIdx.x * a.tiles_per_cta;
     double *out_base = a.partial + (size_t)nd.out_slot * a.slot_doubles;
     uint8_t *sc_out = a.scale + (size_t)nd.out_slot * a.slot_scale_bytes;
-    const uint8_t *scL = Lleaf ? nullptr : a.scale + (size_t)L.id * a.slot_scale_bytes;
-    const uint8_t *scR = Rleaf ? nullptr : a.scale + (size_t)R.id * a.slot_scale_bytes;
-    const double *pL = Lleaf ? nullptr : a.partial + (size_t)L.id * a.slot_doubles;
-    const double *pR = Rleaf ? nullptr : a.partial + (size_t)R.id * a.slot_doubles;
+    const bool Lsc0 = Lleaf || Lvirt, Rsc0 = Rleaf || Rvirt;  // children that contribute no scale count
+    const uint8_t *scL = Lsc0 ? nullptr : a.scale + (size_t)L.id * a.slot_scale_bytes;
+    const uint8_t *scR = Rsc0 ? nullptr : a.scale + (size_t)R.id * a.slot_scale_bytes;
+    const double *pL = Lleaf ? nullptr : (Lvirt ? a.tt + L.vtt_off : a.partial + (size_t)L.id * a.slot_doubles);
+    const double *pR = Rleaf ? nullptr : (Rvirt ? a.tt + R.vtt_off : a.partial + (size_t)R.id * a.slot_doubles);
+    const uint16_t *vpL = Lvirt ? a.pair_idx + L.vpair_off : nullptr, *vpR = Rvirt ? a.pair_idx + R.vpair_off : nullptr;
     if (!SAFE)
         for (int i = tid; i < a.tiles_per_cta * DN_PT; i += DN_THREADS) smax[i] = 0ull;
     int my_tiles = 0;
@@ -638,6 +654,26 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
                 offn[mt] = pcn[mt] * block + q;
             }
         };
+        // virtual children: pair indices of the tile AFTER the current one (requested when a tile opens, a whole tile before
+        // the boundary step turns them into the element offsets of the next tile's operand loads)
+        int vpnL[DN_MT] = {}, vpnR[DN_MT] = {}, voffL[DN_MT] = {}, voffR[DN_MT] = {};
+        auto pairs_of_tile = [&](int t) {
+            const int64_t pbase = (tile0 + t) * DN_PT + warp * (8 * DN_MT);
+#pragma unroll
+            for (int mt = 0; mt < DN_MT; mt++) {
+                int64_t pp = pbase + mt * 8 + g;
+                pp = pp < a.ntot ? pp : a.ntot - 1;
+                if (Lvirt) vpnL[mt] = __ldg(vpL + pp);
+                if (Rvirt) vpnR[mt] = __ldg(vpR + pp);
+            }
+        };
+        auto pairs_to_offsets = [&]() {
+#pragma unroll
+            for (int mt = 0; mt < DN_MT; mt++) {
+                voffL[mt] = vpnL[mt] * block + q;
+                voffR[mt] = vpnR[mt] * block + q;
+            }
+        };
         // per-tile inputs (tip states, invariant-site flag): requested one step before the tile starts, so that the
         // first table lookup of a tile does not wait for them
         int stL[DN_MT] = {}, stR[DN_MT] = {}, stLn[DN_MT] = {}, stRn[DN_MT] = {};
@@ -653,8 +689,14 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
         };
         if (nsteps > 0) {
             rows_of_tile(0);
-            if (!Lleaf) dense_load_A_at(pL, c0, offn, AL);
-            if (!Rleaf) dense_load_A_at(pR, c0, offn, AR);
+            if (Lvirt || Rvirt) {
+                pairs_of_tile(0);
+                pairs_to_offsets();
+            }
+            if (Lvirt) dense_load_A_at(pL, c0, voffL, AL);
+            else if (!Lleaf) dense_load_A_at(pL, c0, offn, AL);
+            if (Rvirt) dense_load_A_at(pR, c0, voffR, AR);
+            else if (!Rleaf) dense_load_A_at(pR, c0, offn, AR);
             tile_inputs(pcn);
         }
         cp_async_wait<0>();  // the tables; the first operands above stay in flight across the barrier
@@ -676,21 +718,29 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
                     stR[mt] = stRn[mt];
                     rmax[mt] = 0ull;
                 }
+                if ((Lvirt || Rvirt) && t + 1 < my_tiles) pairs_of_tile(t + 1);
             }
             if (more && last_cl) {  // the next step opens a tile
                 rows_of_tile(t + 1);
                 tile_inputs(pcn);
+                if (Lvirt || Rvirt) pairs_to_offsets();
             }
             double fl[DN_MT][6], fr[DN_MT][6];
             if (Lleaf) dense_leaf_lookup(sL, cg, cl, stL, lane, fl);
             else {
                 dense_mma_child(AL, sL, cl, lane, fl);
-                if (more) dense_load_A_at(pL, cn, offn, AL);  // next step's left operands, in flight from here
+                if (more) {  // next step's left operands, in flight from here
+                    if (Lvirt) dense_load_A_at(pL, cn, voffL, AL);
+                    else dense_load_A_at(pL, cn, offn, AL);
+                }
             }
             if (Rleaf) dense_leaf_lookup(sR, cg, cl, stR, lane, fr);
             else {
                 dense_mma_child(AR, sR, cl, lane, fr);
-                if (more) dense_load_A_at(pR, cn, offn, AR);
+                if (more) {
+                    if (Rvirt) dense_load_A_at(pR, cn, voffR, AR);
+                    else dense_load_A_at(pR, cn, offn, AR);
+                }
             }
             const double *B = sI + (size_t)cl * B200_FRAG20 + lane;
             // back-transformation of BOTH row tiles together: every B fragment is fetched once and feeds two DMMAs, and six
@@ -732,7 +782,7 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
                 if (SAFE) {
                     mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
                     mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-                    sc = (Lleaf ? 0 : scL[pc[mt] * ncm + c]) + (Rleaf ? 0 : scR[pc[mt] * ncm + c]);
+                    sc = (Lsc0 ? 0 : scL[pc[mt] * ncm + c]) + (Rsc0 ? 0 : scR[pc[mt] * ncm + c]);
                     if (!tiptip && __longlong_as_double((long long)mx) < B200_SCALING_THRESHOLD && invar0[mt]) {
 #pragma unroll
                         for (int k = 0; k < 6; k++) o[k] *= B200_TWO_256;
@@ -800,7 +850,7 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
             scsum[t][mt] = 0;
             inv[t][mt] = 1.0;
             if (on) {
-                scsum[t][mt] = (Lleaf ? 0 : (int)__ldg(scL + pp)) + (Rleaf ? 0 : (int)__ldg(scR + pp));
+                scsum[t][mt] = (Lsc0 ? 0 : (int)__ldg(scL + pp)) + (Rsc0 ? 0 : (int)__ldg(scR + pp));
                 inv[t][mt] = __ldg(a.ptn_invar + pp);
             }
         }
@@ -834,8 +884,9 @@ __global__ void __launch_bounds__(256) dense20_fix_kernel(DenseArgs a) {
     if (valid) {
         const double mx = __longlong_as_double((long long)a.pmax[(size_t)blockIdx.y * a.ntot + p]);
         under = !(Lleaf && Rleaf) && mx < B200_SCALING_THRESHOLD && a.ptn_invar[p] == 0.0;
-        const int sl = Lleaf ? 0 : a.scale[(size_t)L.id * a.slot_scale_bytes + p];
-        const int sr = Rleaf ? 0 : a.scale[(size_t)R.id * a.slot_scale_bytes + p];
+        // a tip child and a virtual tip-tip child (vtt_off >= 0: nothing is in its slot) contribute no scale count
+        const int sl = (Lleaf || L.vtt_off >= 0) ? 0 : a.scale[(size_t)L.id * a.slot_scale_bytes + p];
+        const int sr = (Rleaf || R.vtt_off >= 0) ? 0 : a.scale[(size_t)R.id * a.slot_scale_bytes + p];
         a.scale[(size_t)nd.out_slot * a.slot_scale_bytes + p] = (uint8_t)(sl + sr + (under ? 1 : 0));
     }
     // underflowing patterns are rescaled by the whole warp, one pattern at a time (coalesced over the block)
@@ -880,6 +931,124 @@ __global__ void __launch_bounds__(256) dense20_tt_kernel(DenseTTArgs a) {
     for (int k = q; k < a.scale_per_ptn; k += 4) sc[k] = 0;
 }
 
+// ---- virtual tip-tip nodes (api.cu decides which) ------------------------------------------------------------------
+// pair_idx[v][p] = state(ta, p) * codes + state(tb, p): what the reader of a virtual node loads per row instead of the row's
+// position in a resident vector (4 bytes of traffic per pattern and node instead of the 2 * 8 * block of gather + re-read)
+#define DN_VIRT_PER_LAUNCH 120
+struct TTPairArgs {
+    const uint8_t *states;
+    uint16_t *pair_idx;
+    int64_t ntot, ntot_pad;
+    int codes;
+    S4Virt v[DN_VIRT_PER_LAUNCH];
+    int64_t off[DN_VIRT_PER_LAUNCH];
+};
+__global__ void __launch_bounds__(256) tt_pair_kernel(const __grid_constant__ TTPairArgs a) {
+    const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (p >= a.ntot) return;
+    const S4Virt &v = a.v[blockIdx.y];
+    a.pair_idx[a.off[blockIdx.y] + p] =
+        (uint16_t)(a.states[(size_t)v.ta * a.ntot_pad + p] * a.codes + a.states[(size_t)v.tb * a.ntot_pad + p]);
+}
+
+int launch_tt_pairs(b200lk_ctx *c, const S4Virt *v, int n, const int64_t *pair_off) {
+    const size_t need = (size_t)n * c->ntot_pad;
+    if (need > c->pair_cap) {  // grows only (cudaFree waits for the device)
+        const size_t want = std::max(need, (size_t)(c->d.ntaxa / 2 + 1) * c->ntot_pad);
+        if (c->pair_idx) CUDA_TRY(c, cudaFree(c->pair_idx));
+        c->pair_idx = nullptr;
+        c->pair_cap = 0;
+        CUDA_TRY(c, cudaMalloc(&c->pair_idx, sizeof(uint16_t) * want));
+        c->pair_cap = want;
+    }
+    static thread_local TTPairArgs *Ap = nullptr;
+    if (!Ap) Ap = new TTPairArgs();
+    TTPairArgs &a = *Ap;
+    a.states = c->states;
+    a.pair_idx = c->pair_idx;
+    a.ntot = c->ntot;
+    a.ntot_pad = c->ntot_pad;
+    a.codes = c->d.n_state_codes;
+    for (int done = 0; done < n; done += DN_VIRT_PER_LAUNCH) {
+        const int m = std::min(DN_VIRT_PER_LAUNCH, n - done);
+        for (int k = 0; k < m; k++) {
+            a.v[k] = v[done + k];
+            a.off[k] = pair_off[done + k];
+        }
+        tt_pair_kernel<<<dim3((unsigned)((c->ntot + 255) / 256), m), 256, 0, c->stream>>>(a);
+        CUDA_TRY(c, cudaGetLastError());
+        c->n_launches++;
+    }
+    return B200LK_OK;
+}
+
+// s4_realize for the pattern-major layout: every virtual slot gathered from its table (the rows the update would have stored)
+struct DenseRealizeArgs {
+    const double *tt;
+    const uint8_t *states;
+    double *partial;
+    uint8_t *scale;
+    size_t slot_doubles, slot_scale_bytes;
+    int64_t ntot, ntot_pad;
+    int block, codes, scale_per_ptn;
+    S4Virt v[DN_VIRT_PER_LAUNCH];
+};
+__global__ void __launch_bounds__(256) dense_realize_kernel(const __grid_constant__ DenseRealizeArgs a) {
+    const S4Virt &v = a.v[blockIdx.y];
+    const int q = threadIdx.x & 3;
+    const int64_t p = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 2;  // four lanes copy one pattern's block
+    if (p >= a.ntot) return;
+    const int sl = a.states[(size_t)v.ta * a.ntot_pad + p], sr = a.states[(size_t)v.tb * a.ntot_pad + p];
+    const double2 *src = reinterpret_cast<const double2 *>(a.tt + (size_t)v.tt_off + (size_t)(sl * a.codes + sr) * a.block);
+    double2 *dst = reinterpret_cast<double2 *>(a.partial + (size_t)v.slot * a.slot_doubles + (size_t)p * a.block);
+    const int pairs = a.block >> 1;
+    for (int e = q; e < pairs; e += 4) __stcs(dst + e, __ldg(src + e));
+    uint8_t *sc = a.scale + (size_t)v.slot * a.slot_scale_bytes + (size_t)p * a.scale_per_ptn;
+    for (int k = q; k < a.scale_per_ptn; k += 4) sc[k] = 0;
+}
+
+int dense_realize(b200lk_ctx *c) {
+    if (!c->n_virtual) return B200LK_OK;
+    static thread_local DenseRealizeArgs *Ap = nullptr;
+    if (!Ap) Ap = new DenseRealizeArgs();
+    DenseRealizeArgs &a = *Ap;
+    a.tt = c->tt_tables;
+    a.states = c->states;
+    a.partial = c->partial;
+    a.scale = c->scale;
+    a.slot_doubles = c->slot_doubles;
+    a.slot_scale_bytes = c->slot_scale_bytes;
+    a.ntot = c->ntot;
+    a.ntot_pad = c->ntot_pad;
+    a.block = c->block;
+    a.codes = c->d.n_state_codes;
+    a.scale_per_ptn = c->scale_per_ptn;
+    int n = 0, total = 0;
+    auto flush = [&]() -> int {
+        if (!n) return B200LK_OK;
+        dense_realize_kernel<<<dim3((unsigned)((c->ntot * 4 + 255) / 256), n), 256, 0, c->stream>>>(a);
+        CUDA_TRY(c, cudaGetLastError());
+        c->n_launches++;
+        total += n;
+        n = 0;
+        return B200LK_OK;
+    };
+    for (int s = 0; s < c->d.nslots; s++) {
+        if (!c->virt[s]) continue;
+        a.v[n++] = c->virt_desc[s];
+        c->virt[s] = 0;
+        if (n == DN_VIRT_PER_LAUNCH) {
+            int rc = flush();
+            if (rc) return rc;
+        }
+    }
+    int rc = flush();
+    if (rc) return rc;
+    c->n_virtual = 0;
+    c->n_min_bytes += c->ntot * (8 * (int64_t)c->block + c->scale_per_ptn) * total;
+    return B200LK_OK;
+}
+
 int launch_dense20_tt(b200lk_ctx *c, int node_base, int nnodes) {
     DenseTTArgs a;
     a.nodes = c->d_nodes;
@@ -912,6 +1081,8 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes) {
     a.tables = c->tables;
     a.inv_frag = c->m.inv_frag;
     a.ptn_invar = c->ptn_invar;
+    a.tt = c->tt_tables;
+    a.pair_idx = c->pair_idx;
     a.states = c->states;
     a.partial = c->partial;
     a.scale = c->scale;

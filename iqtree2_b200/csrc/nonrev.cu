@@ -388,6 +388,7 @@ int enqueue_update_nonrev(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnode
         dc.echild_off = (int64_t)off;
         off += (size_t)block * n;
         dc.frag_off = dc.aux_off = -1;
+        dc.vtt_off = dc.vpair_off = -1;
         dc.src = j;
         if (nr_kind(dc.kind) != B200LK_CHILD_INTERNAL) {
             dc.leaf_off = (int64_t)off;

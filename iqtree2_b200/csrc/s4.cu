@@ -545,6 +545,7 @@ static int realize_run(b200lk_ctx *c) {
 int s4_realize(b200lk_ctx *c) {
     if (!c->n_virtual) return B200LK_OK;
     CUDA_TRY(c, cudaSetDevice(c->device));
+    if (c->tile != 32) return dense_realize(c);
     switch (c->ncat_mix) {
         case 1: return realize_run<1>(c);
         case 2: return realize_run<2>(c);

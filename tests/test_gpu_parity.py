@@ -681,3 +681,37 @@ def test_virtual_slot_read_by_a_branch_kernel(oracle_lib, monkeypatch):
     for s in (0, 1, 2, 5, 6):
         assert rel(g.fetch_partial(s), o.fetch_partial(s)) <= TOL
         assert np.array_equal(g.fetch_scale_num(s), o.fetch_scale_num(s))
+
+
+@pytest.mark.parametrize("safe", [False, True])
+@pytest.mark.parametrize("ncat,nmix", [(4, 1), (2, 3)])  # (2, 3): six categories -> the split (mixture) launch and its fix-up kernel
+def test_virtual_tip_tip_vectors_20_state(oracle_lib, monkeypatch, safe, ncat, nmix):
+    """20-state path: a tip-tip node whose only reader is a bifurcating node of the tensor kernel is not gathered into its
+    slot; the reader takes its operand rows from the node's state-pair table by per-pattern pair index
+    (dense20_rp_kernel, Lvirt / Rvirt).  Same bits as the build that gathers every node (B200LK_S4_VIRTUAL=0), parity with
+    the oracle, and the slots read back afterwards (s4_realize -> dense_realize) hold the same vectors."""
+    monkeypatch.setenv("B200LK_S4_TT", "2")
+    tree, model, rates, props, aln = make_problem(24, 700, nstates=20, ncat=ncat, nmix=nmix, seed=37, mean_len=0.3, gaps=0.04,
+                                                  compress=False)
+    out = {}
+    for tag, env in (("real", {"B200LK_S4_VIRTUAL": "0"}), ("virtual", {})):
+        with monkeypatch.context() as m:
+            for k, v in env.items():
+                m.setenv(k, v)
+            g = engine_for(aln, model, rates, props, nslots=24, safe_numeric=safe)
+        r = full_eval(g, tree, 0)
+        tr = r["traversal"]
+        assert sum(1 for e in tr if all(ch[0] == LEAF for ch in e[3])) >= 4
+        vecs = {s: (g.fetch_partial(s), g.fetch_scale_num(s)) for (_, _, s, _) in tr}
+        # a second evaluation from the other end, into other slots, reads the (realized) vectors of the first where it can
+        r2 = full_eval(g, tree, 5, slot_base=0)
+        out[tag] = (r, vecs, r2)
+    (ra, va, ra2), (rb, vb, rb2) = out["real"], out["virtual"]
+    assert ra["lnl"] == rb["lnl"] and ra["df"] == rb["df"] and ra["ddf"] == rb["ddf"]
+    assert np.array_equal(ra["pattern_lh"], rb["pattern_lh"])
+    for s in va:
+        assert np.array_equal(va[s][0], vb[s][0]) and np.array_equal(va[s][1], vb[s][1]), s
+    assert ra2["lnl"] == rb2["lnl"] and np.array_equal(ra2["pattern_lh"], rb2["pattern_lh"])
+    oracle.set_ref_quirks(False)
+    o = oracle.oracle_engine(aln, model, rates, props, nslots=24, safe_numeric=safe)
+    assert_parity(rb, full_eval(o, tree, 0), TOL)
