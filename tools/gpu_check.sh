@@ -53,8 +53,8 @@ ncu --set full --clock-control none --import-source on -k regex:'s4_traverse|eva
     python bench.py --steps 1 --warmup 3 --no-cpu --shapes none > $OUT/ncu_s4_$TAG.log 2>&1
 fi
 if has prof_d20; then
-# one step of cfg3 at 50k patterns has 31 dense20 launches (levels); take the first (TT-heavy), and three deeper ones
-ncu --set full --clock-control none --import-source on -k regex:dense20 --launch-skip 93 -c 4 -f -o $OUT/prof_dense20_$TAG \
+# one step of cfg3 at 50k patterns has 30 dense20_rp launches (levels); four of them from the fourth evaluation
+ncu --set full --clock-control none --import-source on -k regex:dense20_rp --launch-skip 92 -c 4 -f -o $OUT/prof_dense20_$TAG \
     python bench.py --workload cfg3 --patterns 50000 --steps 1 --warmup 3 --no-cpu --shapes none > $OUT/ncu_d20_$TAG.log 2>&1
 fi
 du -sh $OUT
