@@ -559,7 +559,9 @@ __device__ __forceinline__ void dense_mma_child(const double (&A)[DN_MT][5], con
     }
 }
 
-template <bool SAFE>
+// VIRT: the build that can read a virtual tip-tip child from its state-pair table (168 registers); launches without such a
+// child -- batched ones never have any -- take the lean build (160 registers: cfg5 31.1 -> 30.1 ms).
+template <bool SAFE, bool VIRT = true>
 __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(DenseArgs a, BatchLaunch bl) {
     extern __shared__ double sm[];
     if (bl.d_ctx) {  // batched launch: grid.z = context of the supermatrix, same node structure, own data
@@ -584,7 +586,7 @@ __global__ void __launch_bounds__(DN_THREADS, DN_RP_MINB) dense20_rp_kernel(Dens
     const bool tiptip = Lleaf && Rleaf;
     // a tip-tip child left virtual (api.cu): its rows are read from the node's state-pair table by per-pattern pair index,
     // not from a resident vector; its scale counters are zero
-    const bool Lvirt = !Lleaf && L.vtt_off >= 0, Rvirt = !Rleaf && R.vtt_off >= 0;
+    const bool Lvirt = VIRT && !Lleaf && L.vtt_off >= 0, Rvirt = VIRT && !Rleaf && R.vtt_off >= 0;
     const int leaf_doubles = a.codes * DN_CG * 20, frag_doubles = DN_CG * B200_FRAG20;
     const int child_doubles = leaf_doubles > frag_doubles ? leaf_doubles : frag_doubles;
     double *sL = sm, *sR = sL + child_doubles, *sI = sR + child_doubles;
@@ -1128,8 +1130,10 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes) {
         CUDA_TRY(c, cudaFuncSetAttribute(dense20_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(dense20_pipe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
         CUDA_TRY(c, cudaFuncSetAttribute(dense20_pipe_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
-        CUDA_TRY(c, cudaFuncSetAttribute(dense20_rp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        CUDA_TRY(c, cudaFuncSetAttribute(dense20_rp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_rp_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_rp_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_rp_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_TRY(c, cudaFuncSetAttribute(dense20_rp_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         c->dense_attr_set = true;
     }
     dim3 grid((unsigned)((tiles + tpc - 1) / tpc), nnodes, a.split ? ngroups : (c->batch ? c->batch->n : 1));
@@ -1138,8 +1142,16 @@ int launch_dense20(b200lk_ctx *c, int node_base, int nnodes) {
     if (c->batch) bl = *c->batch;
     prof_mark(c);
     if (pipe == 2 || c->batch) {
-        if (c->d.safe_numeric) dense20_rp_kernel<true><<<grid, DN_THREADS, smem, c->stream>>>(a, bl);
-        else dense20_rp_kernel<false><<<grid, DN_THREADS, smem, c->stream>>>(a, bl);
+        bool any_virt = false;  // does a node of this launch read a virtual tip-tip child?
+        for (int i = node_base; i < node_base + nnodes && !any_virt && !c->batch; i++)
+            for (int k = 0; k < 2; k++) any_virt |= c->h_children[c->h_nodes[i].child_begin + k].vtt_off >= 0;
+        if (any_virt) {
+            if (c->d.safe_numeric) dense20_rp_kernel<true, true><<<grid, DN_THREADS, smem, c->stream>>>(a, bl);
+            else dense20_rp_kernel<false, true><<<grid, DN_THREADS, smem, c->stream>>>(a, bl);
+        } else {
+            if (c->d.safe_numeric) dense20_rp_kernel<true, false><<<grid, DN_THREADS, smem, c->stream>>>(a, bl);
+            else dense20_rp_kernel<false, false><<<grid, DN_THREADS, smem, c->stream>>>(a, bl);
+        }
     } else if (pipe == 1) {
         if (c->d.safe_numeric) dense20_pipe_kernel<true><<<grid, DN_THREADS, smem_pipe, c->stream>>>(a);
         else dense20_pipe_kernel<false><<<grid, DN_THREADS, smem_pipe, c->stream>>>(a);
