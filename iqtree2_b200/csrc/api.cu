@@ -214,10 +214,15 @@ int enqueue_update(b200lk_ctx *c, const b200lk_node *nodes, int32_t nnodes, cons
         tt_off += tt_doubles;
     }
     for (int lv = 0; lv < nlevels; lv++) {
-        for (int pass = 0; pass < 3; pass++)
+        // inside a level: tip-tip nodes, bifurcating nodes without a virtual child (lean tensor kernel), bifurcating nodes
+        // with one (the build that reads state-pair tables), multifurcating nodes
+        for (int pass = 0; pass < 4; pass++)
             for (int i = 0; i < nnodes; i++) {
                 if (level[i] != lv || vnode[i]) continue;
-                const int want = kind_of[i] == 0 ? 0 : (kind_of[i] == 3 ? 2 : 1);
+                int want = kind_of[i] == 0 ? 0 : (kind_of[i] == 3 ? 3 : 1);
+                if (want == 1 && b200_env().dense_split_virt)
+                    for (int k = 0; k < 2; k++)
+                        if (c->h_children[nodes[i].child_begin + k].vtt_off >= 0) want = 2;
                 if (want != pass) continue;
                 DevNode &dn = c->h_nodes[pos];
                 dn.out_slot = nodes[i].out_slot;

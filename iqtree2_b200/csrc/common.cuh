@@ -102,6 +102,7 @@ struct B200Env {
     int batch_minb;               // B200LK_BATCH_MINB=2|8: force one build of s4_traverse_batch_kernel (A/B); 0 = per use
     int s4_tt;                    // B200LK_S4_TT=0: tip-tip nodes (4- and 20-state paths) computed, not looked up in state-pair tables; 2: looked up at any size (tests)
     bool s4_bulk;                 // B200LK_S4_BULK=1: node vectors leave through cp.async.bulk instead of the threads' STG (slower: A/B log)
+    bool dense_split_virt;        // B200LK_DENSE_SPLIT_VIRT=0: a level's nodes with and without a virtual child in ONE launch of the larger build (A/B)
     int s4_budget;                // B200LK_S4_BUDGET: nodes per launch of the 4-state traversal (A/B: more, shorter launches); 0 = what the window holds
     bool s4_virtual;              // B200LK_S4_VIRTUAL=0: every tip-tip vector is written by the traversal that computes it
     bool s4_evict;                // B200LK_S4_EVICT=0: a full stack keeps what it holds (first come) instead of the soonest-wanted vectors

@@ -43,6 +43,8 @@ static B200Env read_env() {
         e.s4_bulk = v && *v == '1';
         v = getenv("B200LK_S4_PREFETCH");
         e.s4_prefetch = v && *v == '1';
+        v = getenv("B200LK_DENSE_SPLIT_VIRT");
+        e.dense_split_virt = !(v && *v == '0');
         v = getenv("B200LK_S4_BUDGET");
         e.s4_budget = v ? atoi(v) : 0;
         v = getenv("B200LK_S4_VIRTUAL");

@@ -329,8 +329,26 @@ int launch_partials(b200lk_ctx *c, const std::vector<std::vector<int>> &levels) 
                 if (rc) return rc;
             }
             if (nb > ntt) {
-                int rc = launch_dense20(c, base + ntt, nb - ntt);  // FP64 tensor-core path (dense.cu)
-                if (rc) return rc;
+                // nodes that read a virtual tip-tip child come last among the bifurcating ones (api.cu): their own launch,
+                // so that the others run the lean build of the tensor kernel
+                int nv = 0;
+                if (b200_env().dense_split_virt)
+                    for (int idx : levels[l]) {
+                        const DevNode &dn = c->h_nodes[idx];
+                        if (dn.kind == 3 || (dn.kind == 0 && c->h_children[dn.child_begin].aux_off >= 0)) continue;
+                        bool v = false;
+                        for (int k = 0; k < 2; k++) v |= c->h_children[dn.child_begin + k].vtt_off >= 0;
+                        nv += v;
+                    }
+                const int nlean = nb - ntt - nv;
+                if (nlean > 0) {
+                    int rc = launch_dense20(c, base + ntt, nlean);  // FP64 tensor-core path (dense.cu)
+                    if (rc) return rc;
+                }
+                if (nv > 0) {
+                    int rc = launch_dense20(c, base + ntt + nlean, nv);
+                    if (rc) return rc;
+                }
             }
         } else if (nb && c->dense_nt) {
             int rc = launch_denseN(c, base, nb);  // generic FP64 tensor-core path (densen.cu)
