@@ -66,21 +66,43 @@ __global__ void __launch_bounds__(256) tables_kernel(const DevChild *__restrict_
     double *leaf = tables + ch.leaf_off;
     const int tip_block = n * nmix;
     const int span = (c1 - c0) * n;
-    for (int k = threadIdx.x; k < codes * span; k += blockDim.x) {
-        int s = k / span, r = c0 * n + (k - s * span);  // r = c*n + x
-        const int idx = s * block + r;
+    // One thread per (category, state row x) and group of tip states: the row's products evec * expv are the same for every
+    // tip state, so they are formed once (registers for n <= 20) and the loop over the states only reads the tip vectors --
+    // the same address for a whole warp, i.e. broadcasts.  One thread per OUTPUT element re-read evec and expv for each of
+    // the `codes` states: 60 L1 loads per element, which made this phase -- not exp(), not the barriers -- what a
+    // supermatrix batch spent 3 ms per evaluation on (profiles/launches_cfg5_r3b.csv).  Same terms, same order.
+    const bool fits = span <= (int)blockDim.x;  // else (many categories of many states) the threads stride over the rows
+    const int ngroups = fits ? (int)blockDim.x / span : 1;
+    const int grp = fits ? threadIdx.x / span : 0;
+    if (grp >= ngroups) return;
+    for (int k = fits ? threadIdx.x - grp * span : threadIdx.x; k < span; k += fits ? span : (int)blockDim.x) {
+    const int r = c0 * n + k, c = r / n, x = r - c * n;  // r = c*n + x
+    const double *ev = m.evec + (size_t)(c / denom) * nn + (size_t)x * n;
+    const double *ex = s_expv + (c - c0) * n;
+    constexpr int NREG = 20;
+    double w[NREG];
+    if (n <= NREG) {
+#pragma unroll
+        for (int i = 0; i < NREG; i++) w[i] = i < n ? ev[i] * ex[i] : 0.0;
+    }
+    for (int s = grp; s < codes; s += ngroups) {
         double v;
         if (s == codes - 1) {
             v = 1.0;
         } else {
-            int c = r / n, x = r - c * n;
-            const double *ev = m.evec + (size_t)(c / denom) * nn + (size_t)x * n;
-            const double *ex = s_expv + (c - c0) * n;
             const double *tip = m.tip_partial_lh + (size_t)s * tip_block + (c / denom) * n;
-            v = (ev[0] * ex[0]) * tip[0];
-            for (int i = 1; i < n; i++) v += (ev[i] * ex[i]) * tip[i];
+            if (n <= NREG) {
+                v = w[0] * tip[0];
+#pragma unroll
+                for (int i = 1; i < NREG; i++)
+                    if (i < n) v += w[i] * tip[i];
+            } else {
+                v = (ev[0] * ex[0]) * tip[0];
+                for (int i = 1; i < n; i++) v += (ev[i] * ex[i]) * tip[i];
+            }
         }
-        leaf[idx] = v;
+        leaf[s * block + r] = v;
+    }
     }
 }
 
